@@ -1,0 +1,255 @@
+// C ABI of lib3dgs_mcmc_b200.so (declared in include/gs_b200.h): argument checking, workspace carving
+// and stage orchestration. No torch types, no global state; everything runs on the caller's stream.
+#include "../../include/gs_b200.h"
+
+#include <cstdio>
+
+#include "kernels.cuh"
+
+using namespace gs;
+
+namespace {
+
+inline uint32_t tiles_of(int W, int H, uint2* grid) {
+    const uint32_t gx = (uint32_t)((W + GS_TILE_X - 1) / GS_TILE_X), gy = (uint32_t)((H + GS_TILE_Y - 1) / GS_TILE_Y);
+    if (grid) *grid = make_uint2(gx, gy);
+    return gx * gy;
+}
+
+struct BwdScratch {
+    float4* acc_color_opacity;
+    float4* acc_mean_conic;
+    float* acc_conic_w;
+    size_t bytes;
+    static BwdScratch carve(char* base, size_t P) {
+        Carver c(base);
+        BwdScratch s;
+        s.acc_color_opacity = c.take<float4>(P);
+        s.acc_mean_conic = c.take<float4>(P);
+        s.acc_conic_w = c.take<float>(P);
+        s.bytes = align_up(c.off, kAlign);
+        return s;
+    }
+};
+
+}  // namespace
+
+extern "C" {
+
+int gs_abi_version(void) { return 100; }
+
+const char* gs_error_string(int code) {
+    if (code == GS_OK) return "ok";
+    if (code == GS_ERR_ARG) return "gs_b200: invalid argument";
+    if (code == GS_ERR_WORKSPACE) return "gs_b200: workspace too small or misaligned";
+    if (code > 0) return cudaGetErrorString((cudaError_t)code);
+    return "gs_b200: unknown error";
+}
+
+size_t gs_geom_bytes(int P) { return GeomWS::carve(nullptr, (size_t)(P > 0 ? P : 0)).bytes + kAlign; }
+size_t gs_image_bytes(int W, int H) { return ImageWS::carve(nullptr, (size_t)W, (size_t)H).bytes + kAlign; }
+size_t gs_binning_bytes(unsigned int R, int W, int H) {
+    return BinningWS::carve(nullptr, R, sort_passes(tiles_of(W, H, nullptr))).bytes + kAlign;
+}
+size_t gs_backward_scratch_bytes(int P) { return BwdScratch::carve(nullptr, (size_t)(P > 0 ? P : 0)).bytes + kAlign; }
+
+static inline char* aligned_base(const void* p) {
+    return reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(p), kAlign));
+}
+
+int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means3D, const float* shs,
+                          const float* colors_precomp, const float* opacities, const float* scales,
+                          float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                          const float* viewmatrix, const float* projmatrix, const float* campos, int W, int H,
+                          float tan_fovx, float tan_fovy, int prefiltered, int* radii, int* is_used, void* geom_ws,
+                          unsigned int* num_rendered_host) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return GS_ERR_ARG;
+    if (P > 0 && (!means3D || !opacities || !viewmatrix || !projmatrix || !radii || !is_used || !geom_ws)) return GS_ERR_ARG;
+    if (P > 0 && !colors_precomp && (!shs || !campos || M < (D + 1) * (D + 1))) return GS_ERR_ARG;
+    if (P > 0 && !cov3D_precomp && (!scales || !rotations)) return GS_ERR_ARG;
+    if (P == 0) {
+        if (num_rendered_host) *num_rendered_host = 0;
+        return GS_OK;
+    }
+    GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
+
+    PreprocessParams pp;
+    pp.P = P; pp.D = D; pp.M = M;
+    pp.means3D = means3D; pp.scales = scales; pp.scale_modifier = scale_modifier; pp.rotations = rotations;
+    pp.opacities = opacities; pp.shs = shs; pp.cov3D_precomp = cov3D_precomp; pp.colors_precomp = colors_precomp;
+    pp.viewmatrix = viewmatrix; pp.projmatrix = projmatrix; pp.campos = campos;
+    pp.W = W; pp.H = H; pp.tan_fovx = tan_fovx; pp.tan_fovy = tan_fovy;
+    pp.focal_y = H / (2.0f * tan_fovy);
+    pp.focal_x = W / (2.0f * tan_fovx);
+    tiles_of(W, H, &pp.grid);
+    pp.prefiltered = prefiltered;
+    pp.radii = radii; pp.is_used = is_used; pp.means2D = g.means2D; pp.depths = g.depths; pp.cov3D = g.cov3D;
+    pp.rgb = g.rgb; pp.conic_opacity = g.conic_opacity; pp.tiles_touched = g.tiles_touched; pp.clamped = g.clamped;
+    int rc = launch_preprocess_fwd(pp, stream);
+    if (rc) return rc;
+    rc = launch_inclusive_scan(g.tiles_touched, P, g.point_offsets, g.scan_block_sums, g.num_rendered, stream);
+    if (rc) return rc;
+    if (num_rendered_host)
+        GS_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, g.num_rendered, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
+    return GS_OK;
+}
+
+int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const float* background,
+                      const float* colors_precomp, const int* radii, void* geom_ws, void* binning_ws, void* image_ws,
+                      float* out_color, int* is_used) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || W <= 0 || H <= 0 || !background || !out_color || !image_ws) return GS_ERR_ARG;
+    if (P > 0 && (!geom_ws || !binning_ws || !radii || !is_used)) return GS_ERR_ARG;
+    if (R >= (1u << 30)) return GS_ERR_ARG;
+    uint2 grid;
+    const uint32_t tiles = tiles_of(W, H, &grid);
+    const int passes = sort_passes(tiles);
+    ImageWS img = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
+    GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
+    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, passes);
+    if (P == 0) R = 0;
+
+    int rc = GS_OK;
+    const uint64_t* keys_sorted = (passes & 1) ? b.keys_b : b.keys_a;
+    const uint32_t* vals_sorted = (passes & 1) ? b.vals_b : b.vals_a;
+    if (R > 0) {
+        GS_CUDA_TRY(cudaMemsetAsync(b.error_flag, 0, 16, stream));
+        rc = launch_duplicate_keys(P, g.means2D, g.depths, g.point_offsets, radii, grid, b.keys_a, b.vals_a, stream);
+        if (rc) return rc;
+        rc = launch_radix_sort(b.keys_a, b.keys_b, b.vals_a, b.vals_b, R, passes, b.sort_scratch, b.error_flag, stream);
+        if (rc) return rc;
+    }
+    const float* colors = colors_precomp ? colors_precomp : g.rgb;
+    rc = launch_ranges_and_pack(R, keys_sorted, vals_sorted, g.means2D, g.conic_opacity, colors, img.ranges, tiles, b.packed, stream);
+    if (rc) return rc;
+
+    RenderFwdParams rp;
+    rp.ranges = img.ranges; rp.packed = b.packed; rp.W = W; rp.H = H; rp.tiles_x = (int)grid.x; rp.bg = background;
+    rp.final_T = img.final_T; rp.n_contrib = img.n_contrib; rp.out_color = out_color; rp.is_used = is_used;
+    rp.tile_max_contrib = img.tile_max_contrib;
+    return launch_render_fwd(rp, (int)tiles, stream);
+}
+
+int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H, const float* background,
+                const float* means3D, const float* shs, const float* colors_precomp, const float* scales,
+                float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                const void* geom_ws, const void* binning_ws, const void* image_ws, const float* dL_dpix, void* scratch,
+                float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                float* dL_dsh, float* dL_dscales, float* dL_drotations) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return GS_ERR_ARG;
+    if (P == 0) return GS_OK;
+    if (!means3D || !radii || !geom_ws || !binning_ws || !image_ws || !dL_dpix || !scratch || !background ||
+        !viewmatrix || !projmatrix)
+        return GS_ERR_ARG;
+    if (!dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || !dL_dscales || !dL_drotations)
+        return GS_ERR_ARG;
+    if (shs && (!dL_dsh || !campos)) return GS_ERR_ARG;
+    uint2 grid;
+    const uint32_t tiles = tiles_of(W, H, &grid);
+    const int passes = sort_passes(tiles);
+    ImageWS img = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
+    GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
+    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, passes);
+    BwdScratch sc = BwdScratch::carve(aligned_base(scratch), (size_t)P);
+    GS_CUDA_TRY(cudaMemsetAsync(sc.acc_color_opacity, 0, sc.bytes, stream));
+
+    int rc = GS_OK;
+    if (R > 0) {
+        RenderBwdParams rb;
+        rb.ranges = img.ranges; rb.packed = b.packed; rb.tile_max_contrib = img.tile_max_contrib;
+        rb.W = W; rb.H = H; rb.tiles_x = (int)grid.x; rb.bg = background; rb.final_T = img.final_T;
+        rb.n_contrib = img.n_contrib; rb.dL_dpix = dL_dpix;
+        rb.acc_color_opacity = sc.acc_color_opacity; rb.acc_mean_conic = sc.acc_mean_conic; rb.acc_conic_w = sc.acc_conic_w;
+        rc = launch_render_bwd(rb, (int)tiles, stream);
+        if (rc) return rc;
+    }
+    PreprocessBwdParams pb;
+    pb.P = P; pb.D = D; pb.M = M; pb.means3D = means3D; pb.radii = radii; pb.shs = shs; pb.clamped = g.clamped;
+    pb.scales = cov3D_precomp ? nullptr : scales; pb.rotations = rotations; pb.scale_modifier = scale_modifier;
+    pb.cov3D = cov3D_precomp ? cov3D_precomp : g.cov3D;
+    pb.viewmatrix = viewmatrix; pb.projmatrix = projmatrix; pb.campos = campos;
+    pb.focal_y = H / (2.0f * tan_fovy);
+    pb.focal_x = W / (2.0f * tan_fovx);
+    pb.tan_fovx = tan_fovx; pb.tan_fovy = tan_fovy;
+    pb.acc_color_opacity = sc.acc_color_opacity; pb.acc_mean_conic = sc.acc_mean_conic; pb.acc_conic_w = sc.acc_conic_w;
+    pb.dL_dmeans3D = dL_dmeans3D; pb.dL_dmeans2D = dL_dmeans2D; pb.dL_dcolors = dL_dcolors; pb.dL_dopacity = dL_dopacity;
+    pb.dL_dcov3D = dL_dcov3D; pb.dL_dsh = dL_dsh; pb.dL_dscales = dL_dscales; pb.dL_drots = dL_drotations;
+    return launch_preprocess_bwd(pb, stream);
+}
+
+int gs_mark_visible(void* stream_, int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                    unsigned char* present) {
+    (void)projmatrix;  // the reference's frustum test only uses the view-space depth
+    if (P < 0) return GS_ERR_ARG;
+    if (P > 0 && (!means3D || !viewmatrix || !present)) return GS_ERR_ARG;
+    return launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream_);
+}
+
+int gs_compute_relocation(void* stream_, int P, const float* opacity_old, const float* scale_old, const int* N,
+                          const float* binoms, int n_max, float* opacity_new, float* scale_new) {
+    if (P < 0 || n_max <= 0) return GS_ERR_ARG;
+    if (P > 0 && (!opacity_old || !scale_old || !N || !binoms || !opacity_new || !scale_new)) return GS_ERR_ARG;
+    return launch_compute_relocation(P, opacity_old, scale_old, N, binoms, n_max, opacity_new, scale_new, (cudaStream_t)stream_);
+}
+
+int gs_add_noise(void* stream_, int P, float* xyz, const float* scaling_raw, const float* rotation_raw,
+                 const float* opacity_raw, const float* noise, float lr_scale, unsigned long long seed,
+                 unsigned long long offset) {
+    if (P < 0) return GS_ERR_ARG;
+    if (P > 0 && (!xyz || !scaling_raw || !rotation_raw || !opacity_raw)) return GS_ERR_ARG;
+    return launch_add_noise(P, xyz, scaling_raw, rotation_raw, opacity_raw, noise, lr_scale, seed, offset, (cudaStream_t)stream_);
+}
+
+long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const void* geom_ws, const void* binning_ws,
+                         const void* image_ws, void* dst, size_t max_bytes) {
+    const void* src = nullptr;
+    size_t n = 0;
+    uint2 grid;
+    const uint32_t tiles = tiles_of(W, H, &grid);
+    const int passes = sort_passes(tiles);
+    const size_t Ps = (size_t)P, Rs = (size_t)R, Npix = (size_t)W * (size_t)H;
+    if (which < 10) {
+        if (!geom_ws) return -1;
+        GeomWS g = GeomWS::carve(aligned_base(geom_ws), Ps);
+        switch (which) {
+            case 0: src = g.depths; n = Ps * 4; break;
+            case 1: src = g.clamped; n = Ps; break;
+            case 3: src = g.means2D; n = Ps * 8; break;
+            case 4: src = g.cov3D; n = Ps * 24; break;
+            case 5: src = g.conic_opacity; n = Ps * 16; break;
+            case 6: src = g.rgb; n = Ps * 12; break;
+            case 7: src = g.tiles_touched; n = Ps * 4; break;
+            case 8: src = g.point_offsets; n = Ps * 4; break;
+            default: return -1;
+        }
+    } else if (which < 20 || which == 30) {
+        if (!binning_ws) return -1;
+        BinningWS b = BinningWS::carve(aligned_base(binning_ws), Rs, passes);
+        switch (which) {
+            case 10: src = (passes & 1) ? b.vals_b : b.vals_a; n = Rs * 4; break;
+            case 12: src = (passes & 1) ? b.keys_b : b.keys_a; n = Rs * 8; break;
+            case 14: src = b.packed; n = Rs * sizeof(SplatRec); break;
+            case 30: src = b.error_flag; n = 4; break;
+            default: return -1;
+        }
+    } else {
+        if (!image_ws) return -1;
+        ImageWS s = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
+        switch (which) {
+            case 20: src = s.final_T; n = Npix * 4; break;
+            case 21: src = s.n_contrib; n = Npix * 4; break;
+            case 22: src = s.ranges; n = (size_t)tiles * 8; break;
+            case 23: src = s.tile_max_contrib; n = (size_t)tiles * 4; break;
+            default: return -1;
+        }
+    }
+    if (dst && n > 0 && n <= max_bytes) {
+        if (cudaMemcpy(dst, src, n, cudaMemcpyDeviceToDevice) != cudaSuccess) return -1;
+    }
+    return (long long)n;
+}
+
+}  // extern "C"

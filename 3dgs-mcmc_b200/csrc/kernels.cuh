@@ -1,0 +1,112 @@
+// Internal launcher interface between api.cu and the kernel translation units.
+#pragma once
+#include "gs_common.cuh"
+#include "workspace.cuh"
+
+namespace gs {
+
+struct PreprocessParams {
+    int P, D, M;
+    const float* __restrict__ means3D;
+    const float* __restrict__ scales;
+    float scale_modifier;
+    const float* __restrict__ rotations;
+    const float* __restrict__ opacities;
+    const float* __restrict__ shs;
+    const float* __restrict__ cov3D_precomp;
+    const float* __restrict__ colors_precomp;
+    const float* __restrict__ viewmatrix;
+    const float* __restrict__ projmatrix;
+    const float* __restrict__ campos;
+    int W, H;
+    float tan_fovx, tan_fovy, focal_x, focal_y;
+    uint2 grid;
+    int prefiltered;
+    // outputs
+    int* __restrict__ radii;
+    int* __restrict__ is_used;
+    float2* __restrict__ means2D;
+    float* __restrict__ depths;
+    float* __restrict__ cov3D;
+    float* __restrict__ rgb;
+    float4* __restrict__ conic_opacity;
+    uint32_t* __restrict__ tiles_touched;
+    uint8_t* __restrict__ clamped;
+};
+
+struct RenderFwdParams {
+    const uint2* __restrict__ ranges;
+    const SplatRec* __restrict__ packed;
+    int W, H, tiles_x;
+    const float* __restrict__ bg;
+    float* __restrict__ final_T;
+    uint32_t* __restrict__ n_contrib;
+    float* __restrict__ out_color;
+    int* __restrict__ is_used;
+    uint32_t* __restrict__ tile_max_contrib;
+};
+
+struct RenderBwdParams {
+    const uint2* __restrict__ ranges;
+    const SplatRec* __restrict__ packed;
+    const uint32_t* __restrict__ tile_max_contrib;
+    int W, H, tiles_x;
+    const float* __restrict__ bg;
+    const float* __restrict__ final_T;
+    const uint32_t* __restrict__ n_contrib;
+    const float* __restrict__ dL_dpix;
+    float4* __restrict__ acc_color_opacity;  // [P] (dL/dr, dL/dg, dL/db, dL/dopacity)
+    float4* __restrict__ acc_mean_conic;     // [P] (dL/dmean2D.x, .y, dL/dconic.x, .y)
+    float* __restrict__ acc_conic_w;         // [P] dL/dconic.w
+};
+
+struct PreprocessBwdParams {
+    int P, D, M;
+    const float* __restrict__ means3D;
+    const int* __restrict__ radii;
+    const float* __restrict__ shs;        // null when colours were precomputed
+    const uint8_t* __restrict__ clamped;
+    const float* __restrict__ scales;     // null when cov3D was precomputed
+    const float* __restrict__ rotations;
+    float scale_modifier;
+    const float* __restrict__ cov3D;      // [6P] (precomputed or from the forward workspace)
+    const float* __restrict__ viewmatrix;
+    const float* __restrict__ projmatrix;
+    const float* __restrict__ campos;
+    float focal_x, focal_y, tan_fovx, tan_fovy;
+    // accumulators from render backward
+    const float4* __restrict__ acc_color_opacity;
+    const float4* __restrict__ acc_mean_conic;
+    const float* __restrict__ acc_conic_w;
+    // outputs (API layouts)
+    float* __restrict__ dL_dmeans3D;   // [P,3]
+    float* __restrict__ dL_dmeans2D;   // [P,3]
+    float* __restrict__ dL_dcolors;    // [P,3]
+    float* __restrict__ dL_dopacity;   // [P]
+    float* __restrict__ dL_dcov3D;     // [P,6]
+    float* __restrict__ dL_dsh;        // [P,M,3]
+    float* __restrict__ dL_dscales;    // [P,3]
+    float* __restrict__ dL_drots;      // [P,4]
+};
+
+int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream);
+int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
+int launch_inclusive_scan(const uint32_t* in, int n, uint32_t* out, uint32_t* block_sums, uint32_t* total_out,
+                          cudaStream_t stream);
+int launch_duplicate_keys(int P, const float2* means2D, const float* depths, const uint32_t* offsets,
+                          const int* radii, uint2 grid, uint64_t* keys, uint32_t* vals, cudaStream_t stream);
+int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t R, int passes,
+                      char* scratch, uint32_t* error_flag, cudaStream_t stream);
+int launch_ranges_and_pack(uint32_t R, const uint64_t* keys, const uint32_t* vals, const float2* means2D,
+                           const float4* conic_opacity, const float* colors, uint2* ranges, uint32_t tiles,
+                           SplatRec* packed, cudaStream_t stream);
+int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream);
+int launch_render_bwd(const RenderBwdParams& p, int tiles, cudaStream_t stream);
+int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream);
+int launch_compute_relocation(int P, const float* opacity_old, const float* scale_old, const int* N, const float* binoms,
+                              int n_max, float* opacity_new, float* scale_new, cudaStream_t stream);
+int launch_add_noise(int P, float* xyz, const float* scaling_raw, const float* rotation_raw, const float* opacity_raw,
+                     const float* noise, float lr_scale, unsigned long long seed, unsigned long long offset,
+                     cudaStream_t stream);
+
+}  // namespace gs

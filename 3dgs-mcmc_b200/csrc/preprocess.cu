@@ -1,0 +1,182 @@
+// Per-Gaussian forward preprocessing for sm_100a: frustum cull, clip-space projection, 3D covariance,
+// EWA 2D covariance, conic / radius / tile rectangle and degree-0..3 spherical-harmonics colour,
+// fused in one HBM-bound pass, plus the stand-alone frustum test.
+//
+// Behaviour follows the reference's preprocessCUDA and helpers
+// (cuda_rasterizer/forward.cu:155-256, :118-152, :74-113, :20-71; auxiliary.h:139-164) so that
+// radii / means2D / depths / conics come out bit-identical; the structure is ours: one thread per
+// Gaussian with 128-bit read-only loads of the SH block, output zero-fill of radii / is_used /
+// tiles_touched folded in (no separate memsets), 3 clamp flags packed in one byte.
+#include "gs_common.cuh"
+#include "kernels.cuh"
+#include "workspace.cuh"
+
+namespace gs {
+
+// Sigma = (S R)^T (S R), S = diag(mod * scale), R from the quaternion as given (not normalised).
+GS_DEV void cov3d_from_scale_rot(const V3 scale, float mod, const float4 rot, float* cov3D) {
+    const float sx = mod * scale.x, sy = mod * scale.y, sz = mod * scale.z;
+    const float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
+    const M3 R(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+               2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+               2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+    M3 S(sx, 0.f, 0.f, 0.f, sy, 0.f, 0.f, 0.f, sz);
+    const M3 Mx = S * R;
+    const M3 Sigma = transpose(Mx) * Mx;
+    cov3D[0] = Sigma[0][0];
+    cov3D[1] = Sigma[0][1];
+    cov3D[2] = Sigma[0][2];
+    cov3D[3] = Sigma[1][1];
+    cov3D[4] = Sigma[1][2];
+    cov3D[5] = Sigma[2][2];
+}
+
+// EWA splatting: cov2D = (W J)^T Vrk^T (W J) + 0.3 I (upper 2x2).
+GS_DEV float3 cov2d_ewa(const float3& mean, float focal_x, float focal_y, float tan_fovx, float tan_fovy,
+                        const float* cov3D, const float* __restrict__ view) {
+    float3 t = xform_point_4x3(mean, view);
+    const float limx = 1.3f * tan_fovx;
+    const float limy = 1.3f * tan_fovy;
+    const float txtz = t.x / t.z;
+    const float tytz = t.y / t.z;
+    t.x = min(limx, max(-limx, txtz)) * t.z;
+    t.y = min(limy, max(-limy, tytz)) * t.z;
+
+    const M3 J(focal_x / t.z, 0.0f, -(focal_x * t.x) / (t.z * t.z),
+               0.0f, focal_y / t.z, -(focal_y * t.y) / (t.z * t.z),
+               0.f, 0.f, 0.f);
+    const M3 Wm(view[0], view[4], view[8], view[1], view[5], view[9], view[2], view[6], view[10]);
+    const M3 T = Wm * J;
+    const M3 Vrk(cov3D[0], cov3D[1], cov3D[2], cov3D[1], cov3D[3], cov3D[4], cov3D[2], cov3D[4], cov3D[5]);
+    M3 cov = transpose(T) * transpose(Vrk) * T;
+    cov[0][0] += 0.3f;
+    cov[1][1] += 0.3f;
+    return {cov[0][0], cov[0][1], cov[1][1]};
+}
+
+// Evaluate SH colour. `sh` points at this Gaussian's [M][3] block.
+GS_DEV V3 sh_to_rgb(int deg, const V3 pos, const V3 campos, const float* __restrict__ sh, uint8_t& clamp_bits) {
+    V3 dir = pos - campos;
+    dir = dir / sqrt(dot3(dir, dir));
+    auto C = [&](int k) { return V3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]); };
+
+    V3 result = kSH0 * C(0);
+    if (deg > 0) {
+        const float x = dir.x, y = dir.y, z = dir.z;
+        result = result - kSH1 * y * C(1) + kSH1 * z * C(2) - kSH1 * x * C(3);
+        if (deg > 1) {
+            const float xx = x * x, yy = y * y, zz = z * z;
+            const float xy = x * y, yz = y * z, xz = x * z;
+            result = result + kSH2[0] * xy * C(4) + kSH2[1] * yz * C(5) + kSH2[2] * (2.0f * zz - xx - yy) * C(6) +
+                     kSH2[3] * xz * C(7) + kSH2[4] * (xx - yy) * C(8);
+            if (deg > 2) {
+                result = result + kSH3[0] * y * (3.0f * xx - yy) * C(9) + kSH3[1] * xy * z * C(10) +
+                         kSH3[2] * y * (4.0f * zz - xx - yy) * C(11) +
+                         kSH3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * C(12) +
+                         kSH3[4] * x * (4.0f * zz - xx - yy) * C(13) + kSH3[5] * z * (xx - yy) * C(14) +
+                         kSH3[6] * x * (xx - 3.0f * yy) * C(15);
+            }
+        }
+    }
+    result.x += 0.5f;
+    result.y += 0.5f;
+    result.z += 0.5f;
+    clamp_bits = (uint8_t)((result.x < 0 ? 1 : 0) | (result.y < 0 ? 2 : 0) | (result.z < 0 ? 4 : 0));
+    return V3(fmaxf(result.x, 0.0f), fmaxf(result.y, 0.0f), fmaxf(result.z, 0.0f));
+}
+
+__global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessParams p) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= p.P) return;
+
+    // Defaults for culled Gaussians (replaces three host-side fills).
+    int out_radius = 0;
+    uint32_t out_tiles = 0;
+    p.is_used[idx] = 0;
+
+    const float3 p_orig = {p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]};
+    const float4 p_hom = xform_point_4x4(p_orig, p.projmatrix);
+    const float p_w = 1.0f / (p_hom.w + 0.0000001f);
+    const float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+    const float3 p_view = xform_point_4x3(p_orig, p.viewmatrix);
+
+    bool alive = p_view.z > 0.2f;
+    if (!alive && p.prefiltered) {
+        printf("Point is filtered although prefiltered is set. This shouldn't happen!");
+        __trap();
+    }
+
+    if (alive) {
+        const float* cov3D;
+        float cov_local[6];
+        if (p.cov3D_precomp != nullptr) {
+            cov3D = p.cov3D_precomp + 6 * (size_t)idx;
+        } else {
+            const V3 s(p.scales[3 * idx], p.scales[3 * idx + 1], p.scales[3 * idx + 2]);
+            const float4 q = reinterpret_cast<const float4*>(p.rotations)[idx];
+            cov3d_from_scale_rot(s, p.scale_modifier, q, cov_local);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) p.cov3D[6 * (size_t)idx + i] = cov_local[i];
+            cov3D = cov_local;
+        }
+        const float3 cov = cov2d_ewa(p_orig, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, cov3D, p.viewmatrix);
+
+        const float det = (cov.x * cov.z - cov.y * cov.y);
+        if (det != 0.0f) {
+            const float det_inv = 1.f / det;
+            const float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+            const float mid = 0.5f * (cov.x + cov.z);
+            const float lambda1 = mid + sqrt(max(0.1f, mid * mid - det));
+            const float lambda2 = mid - sqrt(max(0.1f, mid * mid - det));
+            const float my_radius = ceil(3.f * sqrt(max(lambda1, lambda2)));
+            const float2 point_image = {ndc_to_pix(p_proj.x, p.W), ndc_to_pix(p_proj.y, p.H)};
+            uint2 rect_min, rect_max;
+            tile_rect(point_image, (int)my_radius, rect_min, rect_max, p.grid);
+            const uint32_t ntiles = (rect_max.x - rect_min.x) * (rect_max.y - rect_min.y);
+            if (ntiles != 0) {
+                if (p.colors_precomp == nullptr) {
+                    uint8_t cb;
+                    const V3 campos(p.campos[0], p.campos[1], p.campos[2]);
+                    const V3 c = sh_to_rgb(p.D, V3(p_orig.x, p_orig.y, p_orig.z), campos,
+                                           p.shs + (size_t)idx * p.M * 3, cb);
+                    p.rgb[3 * (size_t)idx + 0] = c.x;
+                    p.rgb[3 * (size_t)idx + 1] = c.y;
+                    p.rgb[3 * (size_t)idx + 2] = c.z;
+                    p.clamped[idx] = cb;
+                }
+                p.depths[idx] = p_view.z;
+                p.means2D[idx] = point_image;
+                p.conic_opacity[idx] = {conic.x, conic.y, conic.z, p.opacities[idx]};
+                out_radius = (int)my_radius;
+                out_tiles = ntiles;
+            }
+        }
+    }
+    p.radii[idx] = out_radius;
+    p.tiles_touched[idx] = out_tiles;
+}
+
+__global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* __restrict__ means3D,
+                                                           const float* __restrict__ view, uint8_t* __restrict__ present) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const float3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+    const float3 p_view = xform_point_4x3(p_orig, view);
+    present[idx] = p_view.z > 0.2f ? 1 : 0;
+}
+
+int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream) {
+    if (p.P <= 0) return GS_OK;
+    preprocess_fwd_kernel<<<(p.P + 255) / 256, 256, 0, stream>>>(p);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream) {
+    if (P <= 0) return GS_OK;
+    mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, view, present);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+}  // namespace gs

@@ -1,0 +1,269 @@
+// Per-Gaussian backward for sm_100a: conic -> 2D covariance -> (3D covariance, view-space mean),
+// screen-space mean -> 3D mean, colour -> SH coefficients and view direction, 3D covariance ->
+// scale / quaternion, fused into ONE pass over the Gaussians.
+//
+// The reference runs two kernels here (computeCov2DCUDA then preprocessCUDA,
+// cuda_rasterizer/backward.cu:144-274, :346-396 with helpers :20-139, :278-341) on gradient tensors
+// that the torch glue zero-fills first (rasterize_points.cu:154-162, 300 B per Gaussian). This kernel
+// reads the render-backward accumulators once and writes every output gradient for every Gaussian
+// (zeros for culled ones and for SH coefficients above the active degree), so the outputs need no
+// memset and dL_dmeans3D is never read back. Expressions follow the reference so results agree to
+// rounding; the three contributions to dL_dmeans3D are added in the reference's order
+// (covariance path, projection path, view-direction path).
+#include "gs_common.cuh"
+#include "kernels.cuh"
+#include "workspace.cuh"
+
+namespace gs {
+
+GS_DEV void store3(float* __restrict__ dst, size_t idx, float a, float b, float c) {
+    dst[3 * idx] = a;
+    dst[3 * idx + 1] = b;
+    dst[3 * idx + 2] = c;
+}
+
+// SH backward: writes dL_dsh for coefficients [0, (deg+1)^2) and returns dL/dmean through the view direction.
+GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* __restrict__ sh, uint8_t clamp_bits,
+                          V3 dL_dRGB, float* __restrict__ dL_dsh) {
+    const V3 dir_orig = pos - campos;
+    const V3 dir = dir_orig / sqrt(dot3(dir_orig, dir_orig));
+    auto C = [&](int k) { return V3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]); };
+    auto W = [&](int k, float basis) {
+        dL_dsh[3 * k] = basis * dL_dRGB.x;
+        dL_dsh[3 * k + 1] = basis * dL_dRGB.y;
+        dL_dsh[3 * k + 2] = basis * dL_dRGB.z;
+    };
+    // Clamped channels pass no gradient.
+    dL_dRGB.x *= (clamp_bits & 1) ? 0.f : 1.f;
+    dL_dRGB.y *= (clamp_bits & 2) ? 0.f : 1.f;
+    dL_dRGB.z *= (clamp_bits & 4) ? 0.f : 1.f;
+
+    V3 dRGBdx(0.f, 0.f, 0.f), dRGBdy(0.f, 0.f, 0.f), dRGBdz(0.f, 0.f, 0.f);
+    const float x = dir.x, y = dir.y, z = dir.z;
+
+    W(0, kSH0);
+    if (deg > 0) {
+        W(1, -kSH1 * y);
+        W(2, kSH1 * z);
+        W(3, -kSH1 * x);
+        dRGBdx = -kSH1 * C(3);
+        dRGBdy = -kSH1 * C(1);
+        dRGBdz = kSH1 * C(2);
+        if (deg > 1) {
+            const float xx = x * x, yy = y * y, zz = z * z;
+            const float xy = x * y, yz = y * z, xz = x * z;
+            W(4, kSH2[0] * xy);
+            W(5, kSH2[1] * yz);
+            W(6, kSH2[2] * (2.f * zz - xx - yy));
+            W(7, kSH2[3] * xz);
+            W(8, kSH2[4] * (xx - yy));
+            dRGBdx = dRGBdx + (kSH2[0] * y * C(4) + kSH2[2] * 2.f * -x * C(6) + kSH2[3] * z * C(7) + kSH2[4] * 2.f * x * C(8));
+            dRGBdy = dRGBdy + (kSH2[0] * x * C(4) + kSH2[1] * z * C(5) + kSH2[2] * 2.f * -y * C(6) + kSH2[4] * 2.f * -y * C(8));
+            dRGBdz = dRGBdz + (kSH2[1] * y * C(5) + kSH2[2] * 2.f * 2.f * z * C(6) + kSH2[3] * x * C(7));
+            if (deg > 2) {
+                W(9, kSH3[0] * y * (3.f * xx - yy));
+                W(10, kSH3[1] * xy * z);
+                W(11, kSH3[2] * y * (4.f * zz - xx - yy));
+                W(12, kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
+                W(13, kSH3[4] * x * (4.f * zz - xx - yy));
+                W(14, kSH3[5] * z * (xx - yy));
+                W(15, kSH3[6] * x * (xx - 3.f * yy));
+                dRGBdx = dRGBdx + (kSH3[0] * C(9) * 3.f * 2.f * xy + kSH3[1] * C(10) * yz + kSH3[2] * C(11) * -2.f * xy +
+                                   kSH3[3] * C(12) * -3.f * 2.f * xz + kSH3[4] * C(13) * (-3.f * xx + 4.f * zz - yy) +
+                                   kSH3[5] * C(14) * 2.f * xz + kSH3[6] * C(15) * 3.f * (xx - yy));
+                dRGBdy = dRGBdy + (kSH3[0] * C(9) * 3.f * (xx - yy) + kSH3[1] * C(10) * xz +
+                                   kSH3[2] * C(11) * (-3.f * yy + 4.f * zz - xx) + kSH3[3] * C(12) * -3.f * 2.f * yz +
+                                   kSH3[4] * C(13) * -2.f * xy + kSH3[5] * C(14) * -2.f * yz +
+                                   kSH3[6] * C(15) * -3.f * 2.f * xy);
+                dRGBdz = dRGBdz + (kSH3[1] * C(10) * xy + kSH3[2] * C(11) * 4.f * 2.f * yz +
+                                   kSH3[3] * C(12) * 3.f * (2.f * zz - xx - yy) + kSH3[4] * C(13) * 4.f * 2.f * xz +
+                                   kSH3[5] * C(14) * (xx - yy));
+            }
+        }
+    }
+    const float3 dL_ddir = {dot3(dRGBdx, dL_dRGB), dot3(dRGBdy, dL_dRGB), dot3(dRGBdz, dL_dRGB)};
+    return dnormvdv3(float3{dir_orig.x, dir_orig.y, dir_orig.z}, dL_ddir);
+}
+
+// Sigma = M^T M with M = S R: gradient w.r.t. scale and the (un-normalised) quaternion.
+GS_DEV void cov3d_backward(const V3 scale, float mod, const float4 rot, const float* dL_dcov3D, float* __restrict__ dL_dscale,
+                           float4* __restrict__ dL_drot) {
+    const float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
+    const M3 R(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+               2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+               2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+    const V3 s = mod * scale;
+    const M3 S(s.x, 0.f, 0.f, 0.f, s.y, 0.f, 0.f, 0.f, s.z);
+    const M3 Mx = S * R;
+    const M3 dL_dSigma(dL_dcov3D[0], 0.5f * dL_dcov3D[1], 0.5f * dL_dcov3D[2],
+                       0.5f * dL_dcov3D[1], dL_dcov3D[3], 0.5f * dL_dcov3D[4],
+                       0.5f * dL_dcov3D[2], 0.5f * dL_dcov3D[4], dL_dcov3D[5]);
+    const M3 dL_dM = (2.0f * Mx) * dL_dSigma;
+    const M3 Rt = transpose(R);
+    M3 dL_dMt = transpose(dL_dM);
+
+    dL_dscale[0] = dot3(Rt[0], dL_dMt[0]);
+    dL_dscale[1] = dot3(Rt[1], dL_dMt[1]);
+    dL_dscale[2] = dot3(Rt[2], dL_dMt[2]);
+
+    dL_dMt[0] = dL_dMt[0] * s.x;
+    dL_dMt[1] = dL_dMt[1] * s.y;
+    dL_dMt[2] = dL_dMt[2] * s.z;
+
+    float4 dq;
+    dq.x = 2 * z * (dL_dMt[0][1] - dL_dMt[1][0]) + 2 * y * (dL_dMt[2][0] - dL_dMt[0][2]) + 2 * x * (dL_dMt[1][2] - dL_dMt[2][1]);
+    dq.y = 2 * y * (dL_dMt[1][0] + dL_dMt[0][1]) + 2 * z * (dL_dMt[2][0] + dL_dMt[0][2]) + 2 * r * (dL_dMt[1][2] - dL_dMt[2][1]) -
+           4 * x * (dL_dMt[2][2] + dL_dMt[1][1]);
+    dq.z = 2 * x * (dL_dMt[1][0] + dL_dMt[0][1]) + 2 * r * (dL_dMt[2][0] - dL_dMt[0][2]) + 2 * z * (dL_dMt[1][2] + dL_dMt[2][1]) -
+           4 * y * (dL_dMt[2][2] + dL_dMt[0][0]);
+    dq.w = 2 * r * (dL_dMt[0][1] - dL_dMt[1][0]) + 2 * x * (dL_dMt[2][0] + dL_dMt[0][2]) + 2 * y * (dL_dMt[1][2] + dL_dMt[2][1]) -
+           4 * z * (dL_dMt[1][1] + dL_dMt[0][0]);
+    *dL_drot = dq;  // gradient w.r.t. the quaternion as given; normalisation is the caller's (PyTorch's) job
+}
+
+__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwdParams p) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= p.P) return;
+    const size_t i = (size_t)idx;
+    const bool visible = p.radii[idx] > 0;
+
+    float4 acc0 = make_float4(0.f, 0.f, 0.f, 0.f), acc1 = acc0;
+    float acc2 = 0.f;
+    if (visible) {
+        acc0 = p.acc_color_opacity[idx];
+        acc1 = p.acc_mean_conic[idx];
+        acc2 = p.acc_conic_w[idx];
+    }
+    // Pass-through outputs.
+    store3(p.dL_dmeans2D, i, acc1.x, acc1.y, 0.f);
+    store3(p.dL_dcolors, i, acc0.x, acc0.y, acc0.z);
+    p.dL_dopacity[idx] = acc0.w;
+
+    float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float3 dmean = {0.f, 0.f, 0.f};
+    float dscale[3] = {0.f, 0.f, 0.f};
+    float4 drot = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int ncoef = (p.D + 1) * (p.D + 1);
+    float* __restrict__ my_dsh = p.shs ? p.dL_dsh + i * p.M * 3 : nullptr;
+
+    if (visible) {
+        const float3 mean = {p.means3D[3 * i], p.means3D[3 * i + 1], p.means3D[3 * i + 2]};
+        const float* cov3D = p.cov3D + 6 * i;
+        const float* view = p.viewmatrix;
+        const float3 dL_dconic = {acc1.z, acc1.w, acc2};
+
+        // ---- conic -> cov2D -> cov3D and view-space mean ----
+        float3 t = xform_point_4x3(mean, view);
+        const float limx = 1.3f * p.tan_fovx;
+        const float limy = 1.3f * p.tan_fovy;
+        const float txtz = t.x / t.z;
+        const float tytz = t.y / t.z;
+        t.x = min(limx, max(-limx, txtz)) * t.z;
+        t.y = min(limy, max(-limy, tytz)) * t.z;
+        const float x_grad_mul = txtz < -limx || txtz > limx ? 0 : 1;
+        const float y_grad_mul = tytz < -limy || tytz > limy ? 0 : 1;
+        const float h_x = p.focal_x, h_y = p.focal_y;
+
+        const M3 J(h_x / t.z, 0.0f, -(h_x * t.x) / (t.z * t.z), 0.0f, h_y / t.z, -(h_y * t.y) / (t.z * t.z), 0.f, 0.f, 0.f);
+        const M3 Wm(view[0], view[4], view[8], view[1], view[5], view[9], view[2], view[6], view[10]);
+        const M3 Vrk(cov3D[0], cov3D[1], cov3D[2], cov3D[1], cov3D[3], cov3D[4], cov3D[2], cov3D[4], cov3D[5]);
+        const M3 T = Wm * J;
+        M3 cov2D = transpose(T) * transpose(Vrk) * T;
+
+        const float a = cov2D[0][0] += 0.3f;
+        const float b = cov2D[0][1];
+        const float c = cov2D[1][1] += 0.3f;
+        const float denom = a * c - b * b;
+        float dL_da = 0, dL_db = 0, dL_dc = 0;
+        const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+        if (denom2inv != 0) {
+            dL_da = denom2inv * (-c * c * dL_dconic.x + 2 * b * c * dL_dconic.y + (denom - a * c) * dL_dconic.z);
+            dL_dc = denom2inv * (-a * a * dL_dconic.z + 2 * a * b * dL_dconic.y + (denom - a * c) * dL_dconic.x);
+            dL_db = denom2inv * 2 * (b * c * dL_dconic.x - (denom + 2 * b * b) * dL_dconic.y + a * b * dL_dconic.z);
+
+            dcov[0] = (T[0][0] * T[0][0] * dL_da + T[0][0] * T[1][0] * dL_db + T[1][0] * T[1][0] * dL_dc);
+            dcov[3] = (T[0][1] * T[0][1] * dL_da + T[0][1] * T[1][1] * dL_db + T[1][1] * T[1][1] * dL_dc);
+            dcov[5] = (T[0][2] * T[0][2] * dL_da + T[0][2] * T[1][2] * dL_db + T[1][2] * T[1][2] * dL_dc);
+            // Off-diagonal entries appear twice in the symmetric matrix.
+            dcov[1] = 2 * T[0][0] * T[0][1] * dL_da + (T[0][0] * T[1][1] + T[0][1] * T[1][0]) * dL_db + 2 * T[1][0] * T[1][1] * dL_dc;
+            dcov[2] = 2 * T[0][0] * T[0][2] * dL_da + (T[0][0] * T[1][2] + T[0][2] * T[1][0]) * dL_db + 2 * T[1][0] * T[1][2] * dL_dc;
+            dcov[4] = 2 * T[0][2] * T[0][1] * dL_da + (T[0][1] * T[1][2] + T[0][2] * T[1][1]) * dL_db + 2 * T[1][1] * T[1][2] * dL_dc;
+        }
+
+        const float dL_dT00 = 2 * (T[0][0] * Vrk[0][0] + T[0][1] * Vrk[0][1] + T[0][2] * Vrk[0][2]) * dL_da +
+                              (T[1][0] * Vrk[0][0] + T[1][1] * Vrk[0][1] + T[1][2] * Vrk[0][2]) * dL_db;
+        const float dL_dT01 = 2 * (T[0][0] * Vrk[1][0] + T[0][1] * Vrk[1][1] + T[0][2] * Vrk[1][2]) * dL_da +
+                              (T[1][0] * Vrk[1][0] + T[1][1] * Vrk[1][1] + T[1][2] * Vrk[1][2]) * dL_db;
+        const float dL_dT02 = 2 * (T[0][0] * Vrk[2][0] + T[0][1] * Vrk[2][1] + T[0][2] * Vrk[2][2]) * dL_da +
+                              (T[1][0] * Vrk[2][0] + T[1][1] * Vrk[2][1] + T[1][2] * Vrk[2][2]) * dL_db;
+        const float dL_dT10 = 2 * (T[1][0] * Vrk[0][0] + T[1][1] * Vrk[0][1] + T[1][2] * Vrk[0][2]) * dL_dc +
+                              (T[0][0] * Vrk[0][0] + T[0][1] * Vrk[0][1] + T[0][2] * Vrk[0][2]) * dL_db;
+        const float dL_dT11 = 2 * (T[1][0] * Vrk[1][0] + T[1][1] * Vrk[1][1] + T[1][2] * Vrk[1][2]) * dL_dc +
+                              (T[0][0] * Vrk[1][0] + T[0][1] * Vrk[1][1] + T[0][2] * Vrk[1][2]) * dL_db;
+        const float dL_dT12 = 2 * (T[1][0] * Vrk[2][0] + T[1][1] * Vrk[2][1] + T[1][2] * Vrk[2][2]) * dL_dc +
+                              (T[0][0] * Vrk[2][0] + T[0][1] * Vrk[2][1] + T[0][2] * Vrk[2][2]) * dL_db;
+
+        const float dL_dJ00 = Wm[0][0] * dL_dT00 + Wm[0][1] * dL_dT01 + Wm[0][2] * dL_dT02;
+        const float dL_dJ02 = Wm[2][0] * dL_dT00 + Wm[2][1] * dL_dT01 + Wm[2][2] * dL_dT02;
+        const float dL_dJ11 = Wm[1][0] * dL_dT10 + Wm[1][1] * dL_dT11 + Wm[1][2] * dL_dT12;
+        const float dL_dJ12 = Wm[2][0] * dL_dT10 + Wm[2][1] * dL_dT11 + Wm[2][2] * dL_dT12;
+
+        const float tz = 1.f / t.z;
+        const float tz2 = tz * tz;
+        const float tz3 = tz2 * tz;
+        const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+        const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+        const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 + (2 * h_y * t.y) * tz3 * dL_dJ12;
+        dmean = xform_vec_4x3_T({dL_dtx, dL_dty, dL_dtz}, view);
+
+        // ---- screen-space mean -> 3D mean through the projection ----
+        const float* proj = p.projmatrix;
+        const float4 m_hom = xform_point_4x4(mean, proj);
+        const float m_w = 1.0f / (m_hom.w + 0.0000001f);
+        const float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+        const float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+        float3 dproj;
+        dproj.x = (proj[0] * m_w - proj[3] * mul1) * acc1.x + (proj[1] * m_w - proj[3] * mul2) * acc1.y;
+        dproj.y = (proj[4] * m_w - proj[7] * mul1) * acc1.x + (proj[5] * m_w - proj[7] * mul2) * acc1.y;
+        dproj.z = (proj[8] * m_w - proj[11] * mul1) * acc1.x + (proj[9] * m_w - proj[11] * mul2) * acc1.y;
+        dmean.x += dproj.x;
+        dmean.y += dproj.y;
+        dmean.z += dproj.z;
+
+        // ---- colour -> SH and view direction ----
+        if (p.shs) {
+            const V3 campos(p.campos[0], p.campos[1], p.campos[2]);
+            const float3 dsh_mean = sh_backward(p.D, V3(mean.x, mean.y, mean.z), campos, p.shs + i * p.M * 3,
+                                                p.clamped[idx], V3(acc0.x, acc0.y, acc0.z), my_dsh);
+            dmean.x += dsh_mean.x;
+            dmean.y += dsh_mean.y;
+            dmean.z += dsh_mean.z;
+        }
+        // ---- 3D covariance -> scale, rotation ----
+        if (p.scales) {
+            const V3 sc(p.scales[3 * i], p.scales[3 * i + 1], p.scales[3 * i + 2]);
+            const float4 q = reinterpret_cast<const float4*>(p.rotations)[idx];
+            cov3d_backward(sc, p.scale_modifier, q, dcov, dscale, &drot);
+        }
+    }
+
+    store3(p.dL_dmeans3D, i, dmean.x, dmean.y, dmean.z);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * i + k] = dcov[k];
+    store3(p.dL_dscales, i, dscale[0], dscale[1], dscale[2]);
+    reinterpret_cast<float4*>(p.dL_drots)[idx] = drot;
+    if (my_dsh) {
+        // Zero the coefficients the SH backward did not write (all of them for culled Gaussians).
+        const int first = visible ? 3 * ncoef : 0;
+        for (int k = first; k < 3 * p.M; ++k) my_dsh[k] = 0.f;
+    }
+}
+
+int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream) {
+    if (p.P <= 0) return GS_OK;
+    preprocess_bwd_kernel<<<(p.P + 255) / 256, 256, 0, stream>>>(p);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+}  // namespace gs

@@ -1,0 +1,189 @@
+// Backward tile renderer for sm_100a: back-to-front replay of the blend with warp-aggregated,
+// vectorised gradient reductions.
+//
+// Same CTA / warp / pixel mapping and the same bulk-copy shared-memory ring as the forward, streamed
+// in reverse and only up to the tile's last blended position (tile_max_contrib, recorded by the
+// forward) instead of the end of the tile's list. Per (pixel, splat) pair the recomputation of G and
+// alpha and every gradient expression follow the reference (cuda_rasterizer/backward.cu:399-557). The
+// reference issues 9 scalar float atomics per contributing pair; here each warp first reduces its 32
+// pixels with a multi-value butterfly (8 values folded 2:1 on the first exchange) and then issues two
+// 128-bit vector reductions (red.global.add.v4.f32) plus one scalar per (warp, splat) — and nothing at
+// all when no lane of the warp blended the splat. Accumulators are laid out [P] x (float4, float4,
+// float) for that purpose; summation order differs from the reference (as it does between two runs of
+// the reference), hence tolerance parity on gradients.
+#include "bulk_copy.cuh"
+#include "gs_common.cuh"
+#include "kernels.cuh"
+#include "workspace.cuh"
+
+namespace gs {
+
+constexpr int kBwdChunk = 128;
+constexpr int kBwdStages = 4;
+
+GS_DEV void red_add_v4(float4* addr, const float4 v) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+GS_DEV void red_add_f32(float* addr, const float v) {
+    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwdParams p) {
+    __shared__ __align__(128) SplatRec s_rec[kBwdStages][kBwdChunk];
+    __shared__ __align__(8) uint64_t s_full[kBwdStages];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x;
+    const int tile_x = tile % p.tiles_x, tile_y = tile / p.tiles_x;
+    const uint32_t px = tile_x * GS_TILE_X + (warp & 1) * 8 + (lane & 7);
+    const uint32_t py = tile_y * GS_TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+    const bool inside = px < (uint32_t)p.W && py < (uint32_t)p.H;
+    const uint32_t pix_id = (uint32_t)p.W * py + px;
+    const float2 pixf = {(float)px, (float)py};
+
+    const uint2 range = p.ranges[tile];
+    const int n_total = min((int)(range.y - range.x), (int)p.tile_max_contrib[tile]);
+    const int nchunks = (n_total + kBwdChunk - 1) / kBwdChunk;
+    if (nchunks == 0) return;
+    const SplatRec* __restrict__ src = p.packed + range.x;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < kBwdStages; ++s) mbar_init(&s_full[s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    // Chunk k of the reversed stream is list chunk c = nchunks-1-k.
+    int issued = 0;
+    auto issue = [&](int k) {
+        const int s = k % kBwdStages;
+        const int c = nchunks - 1 - k;
+        const int n = min(kBwdChunk, n_total - c * kBwdChunk);
+        const uint32_t bytes = (uint32_t)n * (uint32_t)sizeof(SplatRec);
+        mbar_arrive_expect_tx(&s_full[s], bytes);
+        bulk_copy_g2s(&s_rec[s][0], src + (size_t)c * kBwdChunk, bytes, &s_full[s]);
+    };
+    if (tid == 0) {
+        for (; issued < min(kBwdStages, nchunks); ++issued) issue(issued);
+    }
+
+    const size_t plane = (size_t)p.H * p.W;
+    const float T_final = inside ? p.final_T[pix_id] : 0.f;
+    float T = T_final;
+    const int last_contributor = inside ? (int)p.n_contrib[pix_id] : 0;
+    const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+    float dL_dpixel[3] = {0.f, 0.f, 0.f};
+    if (inside) {
+        dL_dpixel[0] = p.dL_dpix[0 * plane + pix_id];
+        dL_dpixel[1] = p.dL_dpix[1 * plane + pix_id];
+        dL_dpixel[2] = p.dL_dpix[2 * plane + pix_id];
+    }
+    float bg_dot_dpixel = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) bg_dot_dpixel += p.bg[i] * dL_dpixel[i];
+
+    float accum_rec[3] = {0.f, 0.f, 0.f};
+    float last_alpha = 0.f;
+    float last_color[3] = {0.f, 0.f, 0.f};
+    // Gradient of pixel coordinates w.r.t. normalised screen coordinates.
+    const float ddelx_dx = 0.5 * p.W;
+    const float ddely_dy = 0.5 * p.H;
+    const bool hi = (lane & 16) != 0;
+
+    for (int k = 0; k < nchunks; ++k) {
+        if (k > 0) {
+            __syncthreads();  // every warp is done with chunk k-1: its stage can be refilled
+            if (tid == 0 && issued < nchunks) { issue(issued); ++issued; }
+        }
+        const int s = k % kBwdStages;
+        const int c = nchunks - 1 - k;
+        const int n = min(kBwdChunk, n_total - c * kBwdChunk);
+        mbar_wait(&s_full[s], (uint32_t)((k / kBwdStages) & 1));
+        const float4* __restrict__ rec = reinterpret_cast<const float4*>(&s_rec[s][0]);
+        // Positions >= warp_last were blended by no pixel of this warp.
+        const int jstart = min(n - 1, warp_last - 1 - c * kBwdChunk);
+        for (int j = jstart; j >= 0; --j) {
+            const int pos = c * kBwdChunk + j;  // 0-based position in the tile list
+            const float4 q0 = rec[3 * j];       // x, y, A, B
+            const float4 q1 = rec[3 * j + 1];   // C, opacity, thr, id
+            const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+            const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+            bool act = pos < last_contributor && !(power > 0.0f) && !(power < q1.z);
+            if (!__any_sync(0xffffffffu, act)) continue;
+            const float G = exp(power);
+            const float alpha = min(0.99f, q1.y * G);
+            act = act && !(alpha < 1.0f / 255.0f);
+            if (!__any_sync(0xffffffffu, act)) continue;
+
+            float v[8];
+            float v8 = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = 0.f;
+            if (act) {
+                const float4 q2 = rec[3 * j + 2];  // r, g, b
+                const float col[3] = {q2.x, q2.y, q2.z};
+                T = T / (1.f - alpha);
+                const float dchannel_dcolor = alpha * T;
+                float dL_dalpha = 0.0f;
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                    const float cc = col[ch];
+                    accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                    last_color[ch] = cc;
+                    const float dL_dchannel = dL_dpixel[ch];
+                    dL_dalpha += (cc - accum_rec[ch]) * dL_dchannel;
+                    v[ch] = dchannel_dcolor * dL_dchannel;
+                }
+                dL_dalpha *= T;
+                last_alpha = alpha;
+                dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+
+                const float dL_dG = q1.y * dL_dalpha;
+                const float gdx = G * d.x;
+                const float gdy = G * d.y;
+                const float dG_ddelx = -gdx * q0.z - gdy * q0.w;
+                const float dG_ddely = -gdy * q1.x - gdx * q0.w;
+                v[3] = G * dL_dalpha;                    // opacity
+                v[4] = dL_dG * dG_ddelx * ddelx_dx;      // mean2D.x
+                v[5] = dL_dG * dG_ddely * ddely_dy;      // mean2D.y
+                v[6] = -0.5f * gdx * d.x * dL_dG;        // conic.x
+                v[7] = -0.5f * gdx * d.y * dL_dG;        // conic.y
+                v8 = -0.5f * gdy * d.y * dL_dG;          // conic.w
+            }
+            // Multi-value butterfly: first exchange folds 8 values to 4 per lane (lanes 0-15 keep
+            // v0..3, lanes 16-31 keep v4..7), then four full exchanges.
+            float r4[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float send = hi ? v[i] : v[i + 4];
+                const float keep = hi ? v[i + 4] : v[i];
+                r4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+            }
+#pragma unroll
+            for (int m = 8; m >= 1; m >>= 1) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) r4[i] += __shfl_xor_sync(0xffffffffu, r4[i], m);
+                v8 += __shfl_xor_sync(0xffffffffu, v8, m);
+            }
+            v8 += __shfl_xor_sync(0xffffffffu, v8, 16);
+            const int id = __float_as_int(q1.w);
+            if ((lane & 15) == 0) {
+                float4* dst = hi ? (p.acc_mean_conic + id) : (p.acc_color_opacity + id);
+                red_add_v4(dst, make_float4(r4[0], r4[1], r4[2], r4[3]));
+                if (!hi) red_add_f32(p.acc_conic_w + id, v8);
+            }
+        }
+    }
+    // All issued copies were consumed (no early exit in the backward), nothing to drain.
+}
+
+int launch_render_bwd(const RenderBwdParams& p, int tiles, cudaStream_t stream) {
+    if (tiles <= 0) return GS_OK;
+    render_bwd_kernel<<<tiles, GS_TILE_PIX, 0, stream>>>(p);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+}  // namespace gs

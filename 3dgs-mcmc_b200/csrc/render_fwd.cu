@@ -1,0 +1,142 @@
+// Forward tile renderer for sm_100a: per-tile front-to-back alpha blending.
+//
+// One CTA per 16x16 tile; each warp owns an 8x4 pixel patch (compact footprint -> whole-warp rejects
+// are frequent). The tile's splats arrive as 48-byte records from the tile-ordered packed stream
+// through a 4-stage shared-memory ring filled by 1-D bulk async copies (cp.async.bulk + mbarrier), so
+// no indirect gather sits on the blending critical path. A conservative per-splat log-threshold skips
+// expf for pairs that cannot reach alpha >= 1/255; every blend decision and every arithmetic
+// expression that reaches the output is the reference's (cuda_rasterizer/forward.cu:261-377), so the
+// image, final_T and n_contrib match it bit for bit. is_used flags are collected per stage in shared
+// memory and written once per (tile, splat) instead of once per (pixel, splat).
+#include "bulk_copy.cuh"
+#include "gs_common.cuh"
+#include "kernels.cuh"
+#include "workspace.cuh"
+
+namespace gs {
+
+constexpr int kFwdChunk = 128;
+constexpr int kFwdStages = 4;
+
+__global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwdParams p) {
+    __shared__ __align__(128) SplatRec s_rec[kFwdStages][kFwdChunk];
+    __shared__ __align__(8) uint64_t s_full[kFwdStages];
+    __shared__ int s_used[kFwdStages][kFwdChunk];  // id+1 of splats blended by some pixel, 0 otherwise
+    __shared__ uint32_t s_maxc;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x;
+    const int tile_x = tile % p.tiles_x, tile_y = tile / p.tiles_x;
+    const uint32_t px = tile_x * GS_TILE_X + (warp & 1) * 8 + (lane & 7);
+    const uint32_t py = tile_y * GS_TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+    const bool inside = px < (uint32_t)p.W && py < (uint32_t)p.H;
+    const uint32_t pix_id = (uint32_t)p.W * py + px;
+    const float2 pixf = {(float)px, (float)py};
+
+    const uint2 range = p.ranges[tile];
+    const int n_total = (int)(range.y - range.x);
+    const int nchunks = (n_total + kFwdChunk - 1) / kFwdChunk;
+    const SplatRec* __restrict__ src = p.packed + range.x;
+
+    for (int i = tid; i < kFwdStages * kFwdChunk; i += GS_TILE_PIX) (&s_used[0][0])[i] = 0;
+    if (tid == 0) {
+        s_maxc = 0;
+#pragma unroll
+        for (int s = 0; s < kFwdStages; ++s) mbar_init(&s_full[s], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    int issued = 0;  // meaningful in thread 0 only
+    auto issue = [&](int c) {
+        const int s = c % kFwdStages;
+        const int n = min(kFwdChunk, n_total - c * kFwdChunk);
+        const uint32_t bytes = (uint32_t)n * (uint32_t)sizeof(SplatRec);
+        mbar_arrive_expect_tx(&s_full[s], bytes);
+        bulk_copy_g2s(&s_rec[s][0], src + (size_t)c * kFwdChunk, bytes, &s_full[s]);
+    };
+    if (tid == 0) {
+        for (; issued < min(kFwdStages, nchunks); ++issued) issue(issued);
+    }
+    auto flush_used = [&](int c) {
+        const int s = c % kFwdStages;
+        if (tid < kFwdChunk) {
+            const int u = s_used[s][tid];
+            if (u) {
+                p.is_used[u - 1] = 1;
+                s_used[s][tid] = 0;
+            }
+        }
+    };
+
+    float T = 1.0f;
+    uint32_t contributor = 0, last_contributor = 0;
+    float C[3] = {0.f, 0.f, 0.f};
+    bool done = !inside;
+
+    int c = 0;
+    for (; c < nchunks; ++c) {
+        const int ndone = __syncthreads_count(done);
+        if (c > 0) flush_used(c - 1);
+        if (ndone == GS_TILE_PIX) break;
+        if (tid == 0 && c > 0 && issued < nchunks) { issue(issued); ++issued; }
+
+        const int s = c % kFwdStages;
+        const int n = min(kFwdChunk, n_total - c * kFwdChunk);
+        mbar_wait(&s_full[s], (uint32_t)((c / kFwdStages) & 1));
+        if (!done) {
+            const float4* __restrict__ rec = reinterpret_cast<const float4*>(&s_rec[s][0]);
+            for (int j = 0; j < n; ++j) {
+                contributor++;
+                const float4 q0 = rec[3 * j];      // x, y, A, B
+                const float4 q1 = rec[3 * j + 1];  // C, opacity, thr, id
+                const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+                const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+                if (power > 0.0f) continue;
+                if (power < q1.z) continue;  // cannot reach alpha >= 1/255 (see ranges_and_pack_kernel)
+                const float alpha = min(0.99f, q1.y * exp(power));
+                if (alpha < 1.0f / 255.0f) continue;
+                const float test_T = T * (1 - alpha);
+                if (test_T < 0.0001f) {
+                    done = true;
+                    break;
+                }
+                const float4 q2 = rec[3 * j + 2];  // r, g, b
+                C[0] += q2.x * alpha * T;
+                C[1] += q2.y * alpha * T;
+                C[2] += q2.z * alpha * T;
+                T = test_T;
+                last_contributor = contributor;
+                s_used[s][j] = __float_as_int(q1.w) + 1;
+            }
+        }
+    }
+    __syncthreads();
+    if (c == nchunks && nchunks > 0) flush_used(nchunks - 1);
+    // Drain bulk copies that were issued but never consumed (early exit) before the CTA retires.
+    if (tid == 0) {
+        for (int q = c; q < issued; ++q) mbar_wait(&s_full[q % kFwdStages], (uint32_t)((q / kFwdStages) & 1));
+    }
+
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (lane == 0 && wmax) atomicMax(&s_maxc, wmax);
+    if (inside) {
+        p.final_T[pix_id] = T;
+        p.n_contrib[pix_id] = last_contributor;
+        const size_t plane = (size_t)p.H * p.W;
+        p.out_color[0 * plane + pix_id] = C[0] + T * p.bg[0];
+        p.out_color[1 * plane + pix_id] = C[1] + T * p.bg[1];
+        p.out_color[2 * plane + pix_id] = C[2] + T * p.bg[2];
+    }
+    __syncthreads();
+    if (tid == 0) p.tile_max_contrib[tile] = s_maxc;
+}
+
+int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream) {
+    if (tiles <= 0) return GS_OK;
+    render_fwd_kernel<<<tiles, GS_TILE_PIX, 0, stream>>>(p);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+}  // namespace gs

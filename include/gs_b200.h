@@ -1,0 +1,120 @@
+/*
+ * gs_b200.h — C ABI of lib3dgs_mcmc_b200.so: the B200 (sm_100a) Gaussian-splatting rasterizer and
+ * MCMC update kernels.
+ *
+ * This is the drop-in boundary for the hot path of NeutrinoLiu/3dgs-mcmc. Every entry point takes
+ * plain device pointers, sizes, scalars and a CUDA stream (as void*); no torch types. Each one
+ * replaces one native entry of the reference's pybind module `_C`
+ * (submodules/diff-gaussian-rasterization/ext.cpp:15-20):
+ *
+ *   gs_forward_preprocess + gs_forward_render  <-  rasterize_gaussians
+ *        = RasterizeGaussiansCUDA (rasterize_points.cu:36-118) -> CudaRasterizer::Rasterizer::forward
+ *          (cuda_rasterizer/rasterizer.h:33-58, rasterizer_impl.cu:198-338). The reference sizes its
+ *          binning buffer from a std::function callback after a blocking D2H copy of the instance count
+ *          (rasterizer_impl.cu:282-286); a C ABI has no callbacks, so the forward is two calls: the
+ *          first ends by copying R to a pinned host word, the caller allocates gs_binning_bytes(R).
+ *   gs_backward            <-  rasterize_gaussians_backward
+ *        = RasterizeGaussiansBackwardCUDA (rasterize_points.cu:120-199) -> Rasterizer::backward
+ *          (rasterizer.h:60-86, rasterizer_impl.cu:342-436)
+ *   gs_mark_visible        <-  mark_visible (rasterize_points.cu:201-220, rasterizer_impl.cu:141-153)
+ *   gs_compute_relocation  <-  compute_relocation (rasterize_points.cu:222-248, utils.h:8-19, utils.cu:6-51)
+ *   gs_add_noise           additive: fuses the inline torch code of train_static.py:132-140
+ *
+ * Conventions (same as the reference): all float data FP32, row-contiguous; an absent
+ * optional input is a NULL pointer; viewmatrix / projmatrix are 16 floats, element [4*i+j] of the
+ * transposed matrix; quaternions are (w,x,y,z); SH is [P][M][3]; the image is CHW; radii==0 means
+ * culled. Workspaces are opaque byte buffers owned by the caller; the library keeps no state.
+ * Every function returns 0 on success, a positive cudaError_t value if a CUDA call failed, or a
+ * negative GS_ERR_* code for bad arguments. Work is enqueued on `stream`; nothing synchronises
+ * except where stated.
+ */
+#ifndef GS_B200_H_INCLUDED
+#define GS_B200_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GS_B200_OK 0
+#define GS_B200_ERR_ARG (-1)
+#define GS_B200_ERR_WORKSPACE (-2)
+
+/* Library / ABI version (major*100 + minor). */
+int gs_abi_version(void);
+
+/* Human-readable text for a return code of this library. */
+const char* gs_error_string(int code);
+
+/* ---- workspace sizes (bytes). Replace required<GeometryState/ImageState/BinningState>()
+ *      (cuda_rasterizer/rasterizer_impl.h:65-72). ---- */
+size_t gs_geom_bytes(int P);
+size_t gs_image_bytes(int W, int H);
+size_t gs_binning_bytes(unsigned int R, int W, int H);
+size_t gs_backward_scratch_bytes(int P);
+
+/* Forward, stage 1: preprocess (cull, project, covariance, conic, radius, SH colour) + inclusive scan of
+ * tiles_touched. Writes radii[P] and zero-fills is_used[P]. If num_rendered_host != NULL (must be pinned
+ * host memory) the instance count R is copied there asynchronously on `stream`; synchronise the stream
+ * before reading it. */
+int gs_forward_preprocess(void* stream, int P, int D, int M,
+                          const float* means3D, const float* shs, const float* colors_precomp,
+                          const float* opacities, const float* scales, float scale_modifier,
+                          const float* rotations, const float* cov3D_precomp,
+                          const float* viewmatrix, const float* projmatrix, const float* campos,
+                          int W, int H, float tan_fovx, float tan_fovy, int prefiltered,
+                          int* radii, int* is_used, void* geom_ws, unsigned int* num_rendered_host);
+
+/* Forward, stage 2: tile-key duplication, radix sort, tile ranges, packed splat stream, tile render.
+ * Writes out_color[3][H][W] and sets is_used[id]=1 for every blended Gaussian. */
+int gs_forward_render(void* stream, int P, unsigned int R, int W, int H,
+                      const float* background, const float* colors_precomp, const int* radii,
+                      void* geom_ws, void* binning_ws, void* image_ws,
+                      float* out_color, int* is_used);
+
+/* Backward of the whole rasterizer. Every output is fully written (no pre-zeroing needed):
+ * dL_dmeans2D[P][3], dL_dcolors[P][3], dL_dopacity[P], dL_dmeans3D[P][3], dL_dcov3D[P][6],
+ * dL_dsh[P][M][3] (may be NULL when shs is NULL), dL_dscales[P][3], dL_drotations[P][4]. */
+int gs_backward(void* stream, int P, int D, int M, unsigned int R, int W, int H,
+                const float* background, const float* means3D, const float* shs, const float* colors_precomp,
+                const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                const float* viewmatrix, const float* projmatrix, const float* campos,
+                float tan_fovx, float tan_fovy, const int* radii,
+                const void* geom_ws, const void* binning_ws, const void* image_ws,
+                const float* dL_dpix, void* scratch,
+                float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+                float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations);
+
+/* present[i] = (view * means3D[i]).z > 0.2 ; one byte per Gaussian (bool). */
+int gs_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix,
+                    const float* projmatrix, unsigned char* present);
+
+/* MCMC relocation (Eq. 9): opacity_new[P], scale_new[3P]. N holds int32 counts (caller clamps to [1, n_max-1]). */
+int gs_compute_relocation(void* stream, int P, const float* opacity_old, const float* scale_old,
+                          const int* N, const float* binoms, int n_max,
+                          float* opacity_new, float* scale_new);
+
+/* xyz[P][3] += Sigma(scaling_raw, rotation_raw) * (n * gate(opacity_raw) * lr_scale), lr_scale = noise_lr * xyz_lr.
+ * noise[P][3] supplies the standard-normal deviates n; if NULL they are generated in-kernel from (seed, offset). */
+int gs_add_noise(void* stream, int P, float* xyz, const float* scaling_raw, const float* rotation_raw,
+                 const float* opacity_raw, const float* noise, float lr_scale,
+                 unsigned long long seed, unsigned long long offset);
+
+/* Test / debug hook: copy one internal array of the workspaces into dst (device memory). `which` uses the
+ * numbering of the reference's state structs so parity tests can compare array by array:
+ *   0 depths f32[P] | 1 clamped u8[P] (bit c = channel c) | 3 means2D f32[2P] | 4 cov3D f32[6P]
+ *   5 conic_opacity f32[4P] | 6 rgb f32[3P] | 7 tiles_touched u32[P] | 8 point_offsets u32[P]
+ *   10 sorted gaussian ids u32[R] | 12 sorted keys u64[R] | 14 packed splat records 48 B x R
+ *   20 final_T f32[WH] | 21 n_contrib u32[WH] | 22 ranges u32[2*tiles] | 23 tile_max_contrib u32[tiles]
+ *   30 sort error flag u32[1]
+ * Returns the array's size in bytes (copied only when it fits in max_bytes), or -1. Synchronous. */
+long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H,
+                         const void* geom_ws, const void* binning_ws, const void* image_ws,
+                         void* dst, size_t max_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GS_B200_H_INCLUDED */
