@@ -1,0 +1,285 @@
+"""ctypes binding of lib3dgs_mcmc_b200.so (C ABI: include/gs_b200.h).
+
+This module plays the role of the reference's pybind extension ``diff_gaussian_rasterization._C``
+(submodules/diff-gaussian-rasterization/ext.cpp:15-20): it exposes the same four callables with the
+same positional arguments and return tuples as ``RasterizeGaussiansCUDA``,
+``RasterizeGaussiansBackwardCUDA``, ``markVisible`` and ``ComputeRelocationCUDA``
+(rasterize_points.cu:36-248), plus the additive ``add_noise``. Torch is used for device memory and
+the current stream only; all compute is in the CUDA library. There is no CPU or eager fallback: a
+missing library or a non-CUDA tensor raises.
+"""
+import ctypes
+import os
+
+import torch
+
+_LIB_NAME = "lib3dgs_mcmc_b200.so"
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), _LIB_NAME)
+
+_c_void_p = ctypes.c_void_p
+_c_int = ctypes.c_int
+_c_uint = ctypes.c_uint
+_c_float = ctypes.c_float
+_c_size_t = ctypes.c_size_t
+_c_ull = ctypes.c_ulonglong
+
+# name -> (restype, argtypes); must list every symbol include/gs_b200.h declares.
+SIGNATURES = {
+    "gs_abi_version": (_c_int, []),
+    "gs_error_string": (ctypes.c_char_p, [_c_int]),
+    "gs_geom_bytes": (_c_size_t, [_c_int]),
+    "gs_image_bytes": (_c_size_t, [_c_int, _c_int]),
+    "gs_binning_bytes": (_c_size_t, [_c_uint, _c_int, _c_int]),
+    "gs_backward_scratch_bytes": (_c_size_t, [_c_int]),
+    "gs_forward_preprocess": (_c_int, [_c_void_p, _c_int, _c_int, _c_int] + [_c_void_p] * 5 + [_c_float]
+                              + [_c_void_p] * 5 + [_c_int, _c_int, _c_float, _c_float, _c_int]
+                              + [_c_void_p] * 4),
+    "gs_forward_render": (_c_int, [_c_void_p, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 8),
+    "gs_backward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 5
+                    + [_c_float] + [_c_void_p] * 5 + [_c_float, _c_float] + [_c_void_p] * 14),
+    "gs_mark_visible": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4),
+    "gs_compute_relocation": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 2),
+    "gs_add_noise": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 5 + [_c_float, _c_ull, _c_ull]),
+    "gs_debug_fetch": (ctypes.c_longlong, [_c_int, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 4 + [_c_size_t]),
+}
+
+
+def load_library(path=_LIB_PATH):
+    """Load the CUDA library and attach prototypes. Fails loudly when it has not been built."""
+    if not os.path.exists(path):
+        raise ImportError(
+            f"{_LIB_NAME} not found at {path}. Build it with `bash 3dgs-mcmc_b200/build.sh` "
+            "(or `python -c 'import __graft_entry__ as g; g.build()'`). There is no CPU fallback.")
+    lib = ctypes.CDLL(path)
+    for name, (restype, argtypes) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype = restype
+        fn.argtypes = argtypes
+    return lib
+
+
+_lib = load_library()
+_pinned_counts = {}
+
+
+def _check(rc, what):
+    if rc != 0:
+        msg = _lib.gs_error_string(rc)
+        raise RuntimeError(f"{what} failed: {msg.decode() if msg else rc} (code {rc})")
+
+
+def _ptr(t):
+    """Device pointer of a tensor, or NULL for an absent optional (empty tensor), as in the reference where
+    empty CPU tensors yield null data pointers (rasterize_points.cu:86,149; forward.cu:205,241)."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _f32_cuda(t, name, device):
+    if t is None or t.numel() == 0:
+        return t
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (no CPU path exists)")
+    if t.device != device:
+        raise RuntimeError(f"{name} is on {t.device}, expected {device}")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32, got {t.dtype}")
+    return t.contiguous()
+
+
+def _stream(device):
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _pinned_count(device):
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    buf = _pinned_counts.get(key)
+    if buf is None:
+        buf = torch.zeros(1, dtype=torch.int32, pin_memory=True)
+        _pinned_counts[key] = buf
+    return buf
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                        prefiltered, debug):
+    """Same contract as RasterizeGaussiansCUDA (rasterize_points.cu:36-118): returns
+    (num_rendered, out_color[3,H,W], radii[P] i32, geomBuffer, binningBuffer, imgBuffer, is_used[P] i32)."""
+    if means3D.ndimension() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D must be a CUDA tensor (no CPU path exists)")
+    device = means3D.device
+    P, H, W = int(means3D.size(0)), int(image_height), int(image_width)
+    byte_opts = dict(dtype=torch.uint8, device=device)
+    if P == 0:
+        z = torch.zeros
+        return (0, z((3, H, W), dtype=torch.float32, device=device), z((0,), dtype=torch.int32, device=device),
+                torch.empty(0, **byte_opts), torch.empty(0, **byte_opts), torch.empty(0, **byte_opts),
+                z((0,), dtype=torch.int32, device=device))
+
+    background = _f32_cuda(background, "bg", device)
+    means3D = _f32_cuda(means3D, "means3D", device)
+    colors = _f32_cuda(colors, "colors_precomp", device)
+    opacity = _f32_cuda(opacity, "opacities", device)
+    scales = _f32_cuda(scales, "scales", device)
+    rotations = _f32_cuda(rotations, "rotations", device)
+    cov3D_precomp = _f32_cuda(cov3D_precomp, "cov3D_precomp", device)
+    viewmatrix = _f32_cuda(viewmatrix, "viewmatrix", device)
+    projmatrix = _f32_cuda(projmatrix, "projmatrix", device)
+    sh = _f32_cuda(sh, "sh", device)
+    campos = _f32_cuda(campos, "campos", device)
+    M = int(sh.size(1)) if sh is not None and sh.numel() != 0 else 0
+
+    with torch.cuda.device(device):
+        stream = _stream(device)
+        out_color = torch.empty((3, H, W), dtype=torch.float32, device=device)
+        radii = torch.empty((P,), dtype=torch.int32, device=device)
+        is_used = torch.empty((P,), dtype=torch.int32, device=device)
+        geom = torch.empty(_lib.gs_geom_bytes(P), **byte_opts)
+        img = torch.empty(_lib.gs_image_bytes(W, H), **byte_opts)
+        count = _pinned_count(device)
+
+        _check(_lib.gs_forward_preprocess(
+            stream, P, int(degree), M, _ptr(means3D), _ptr(sh), _ptr(colors), _ptr(opacity), _ptr(scales),
+            float(scale_modifier), _ptr(rotations), _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix),
+            _ptr(campos), W, H, float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
+            radii.data_ptr(), is_used.data_ptr(), geom.data_ptr(), count.data_ptr()), "gs_forward_preprocess")
+        # The one host sync of the forward (the reference has the same one, rasterizer_impl.cu:282):
+        # the binning workspace is sized from the instance count.
+        torch.cuda.current_stream(device).synchronize()
+        rendered = int(count.item())
+        if debug:
+            _debug_sync("preprocess")
+
+        binning = torch.empty(_lib.gs_binning_bytes(rendered, W, H), **byte_opts)
+        _check(_lib.gs_forward_render(
+            stream, P, rendered, W, H, _ptr(background), _ptr(colors), radii.data_ptr(), geom.data_ptr(),
+            binning.data_ptr(), img.data_ptr(), out_color.data_ptr(), is_used.data_ptr()), "gs_forward_render")
+        if debug:
+            _debug_sync("render")
+            flag = torch.zeros(1, dtype=torch.int32, device=device)
+            _lib.gs_debug_fetch(30, P, rendered, W, H, geom.data_ptr(), binning.data_ptr(), img.data_ptr(),
+                                flag.data_ptr(), 4)
+            if int(flag.item()) != 0:
+                raise RuntimeError("radix sort look-back timed out")
+    return rendered, out_color, radii, geom, binning, img, is_used
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                                 viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
+                                 geomBuffer, R, binningBuffer, imageBuffer, debug):
+    """Same contract as RasterizeGaussiansBackwardCUDA (rasterize_points.cu:120-199): returns
+    (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)."""
+    device = means3D.device
+    P = int(means3D.size(0))
+    H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
+    M = int(sh.size(1)) if sh is not None and sh.numel() != 0 else 0
+    opts = dict(dtype=torch.float32, device=device)
+    shapes = [(P, 3), (P, 3), (P, 1), (P, 3), (P, 6), (P, M, 3), (P, 3), (P, 4)]
+    if P == 0:
+        return tuple(torch.zeros(s, **opts) for s in shapes)
+
+    background = _f32_cuda(background, "bg", device)
+    means3D = _f32_cuda(means3D, "means3D", device)
+    colors = _f32_cuda(colors, "colors_precomp", device)
+    scales = _f32_cuda(scales, "scales", device)
+    rotations = _f32_cuda(rotations, "rotations", device)
+    cov3D_precomp = _f32_cuda(cov3D_precomp, "cov3D_precomp", device)
+    viewmatrix = _f32_cuda(viewmatrix, "viewmatrix", device)
+    projmatrix = _f32_cuda(projmatrix, "projmatrix", device)
+    dL_dout_color = _f32_cuda(dL_dout_color, "dL_dout_color", device)
+    sh = _f32_cuda(sh, "sh", device)
+    campos = _f32_cuda(campos, "campos", device)
+    radii = radii.contiguous()
+
+    with torch.cuda.device(device):
+        # Every output is fully written by the fused backward kernel: no zero fill.
+        dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations = (
+            torch.empty(s, **opts) for s in shapes)
+        scratch = torch.empty(_lib.gs_backward_scratch_bytes(P), dtype=torch.uint8, device=device)
+        _check(_lib.gs_backward(
+            _stream(device), P, int(degree), M, int(R), W, H, _ptr(background), _ptr(means3D), _ptr(sh), _ptr(colors),
+            _ptr(scales), float(scale_modifier), _ptr(rotations), _ptr(cov3D_precomp), _ptr(viewmatrix),
+            _ptr(projmatrix), _ptr(campos), float(tan_fovx), float(tan_fovy), radii.data_ptr(),
+            geomBuffer.data_ptr(), binningBuffer.data_ptr(), imageBuffer.data_ptr(), dL_dout_color.data_ptr(),
+            scratch.data_ptr(), dL_dmeans2D.data_ptr(), dL_dcolors.data_ptr(), dL_dopacity.data_ptr(),
+            dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(), _ptr(dL_dsh), dL_dscales.data_ptr(),
+            dL_drotations.data_ptr()), "gs_backward")
+        if debug:
+            _debug_sync("backward")
+    return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """present[i] = view-space depth of means3D[i] > 0.2 (rasterize_points.cu:201-220)."""
+    device = means3D.device
+    P = int(means3D.size(0))
+    present = torch.zeros((P,), dtype=torch.bool, device=device)
+    if P != 0:
+        means3D = _f32_cuda(means3D, "means3D", device)
+        viewmatrix = _f32_cuda(viewmatrix, "viewmatrix", device)
+        projmatrix = _f32_cuda(projmatrix, "projmatrix", device)
+        with torch.cuda.device(device):
+            _check(_lib.gs_mark_visible(_stream(device), P, _ptr(means3D), _ptr(viewmatrix), _ptr(projmatrix),
+                                        present.data_ptr()), "gs_mark_visible")
+    return present
+
+
+def compute_relocation(opacity_old, scale_old, N, binoms, n_max):
+    """(final_opacity[P], final_scale[3P]) as ComputeRelocationCUDA (rasterize_points.cu:222-248)."""
+    device = opacity_old.device
+    P = int(opacity_old.size(0))
+    final_opacity = torch.zeros((P,), dtype=torch.float32, device=device)
+    final_scale = torch.zeros((3 * P,), dtype=torch.float32, device=device)
+    if P != 0:
+        opacity_old = _f32_cuda(opacity_old, "opacity_old", device)
+        scale_old = _f32_cuda(scale_old, "scale_old", device)
+        binoms = _f32_cuda(binoms, "binoms", device)
+        if N.dtype != torch.int32 or not N.is_cuda:
+            raise RuntimeError("N must be an int32 CUDA tensor")
+        N = N.contiguous()
+        with torch.cuda.device(device):
+            _check(_lib.gs_compute_relocation(_stream(device), P, _ptr(opacity_old), _ptr(scale_old), N.data_ptr(),
+                                              _ptr(binoms), int(n_max), final_opacity.data_ptr(),
+                                              final_scale.data_ptr()), "gs_compute_relocation")
+    return final_opacity, final_scale
+
+
+def add_noise(xyz, scaling_raw, rotation_raw, opacity_raw, lr_scale, noise=None, seed=0, offset=0):
+    """In place: xyz += Sigma * (n * gate(opacity) * lr_scale). See gs_add_noise in include/gs_b200.h."""
+    device = xyz.device
+    P = int(xyz.size(0))
+    if P == 0:
+        return xyz
+    if not (xyz.is_cuda and xyz.dtype == torch.float32 and xyz.is_contiguous()):
+        raise RuntimeError("xyz must be a contiguous float32 CUDA tensor (updated in place)")
+    scaling_raw = _f32_cuda(scaling_raw, "scaling", device)
+    rotation_raw = _f32_cuda(rotation_raw, "rotation", device)
+    opacity_raw = _f32_cuda(opacity_raw, "opacity", device)
+    noise = _f32_cuda(noise, "noise", device)
+    with torch.cuda.device(device):
+        _check(_lib.gs_add_noise(_stream(device), P, xyz.data_ptr(), _ptr(scaling_raw), _ptr(rotation_raw),
+                                 _ptr(opacity_raw), _ptr(noise), float(lr_scale), int(seed), int(offset)),
+               "gs_add_noise")
+    return xyz
+
+
+def debug_fetch(which, P, R, W, H, geom, binning, img, dtype):
+    """Copy one internal workspace array into a fresh tensor (tests only; numbering in gs_b200.h)."""
+    nbytes = _lib.gs_debug_fetch(which, P, R, W, H, _ptr(geom), _ptr(binning), _ptr(img), None, 0)
+    if nbytes < 0:
+        raise RuntimeError(f"gs_debug_fetch({which}) failed")
+    out = torch.empty(nbytes, dtype=torch.uint8, device=geom.device if geom.numel() else img.device)
+    if nbytes:
+        _lib.gs_debug_fetch(which, P, R, W, H, _ptr(geom), _ptr(binning), _ptr(img), out.data_ptr(), nbytes)
+    return out.view(dtype)
+
+
+def _debug_sync(stage):
+    # debug=True in the reference syncs and throws after every stage (auxiliary.h:166-173).
+    try:
+        torch.cuda.synchronize()
+    except RuntimeError as ex:
+        raise RuntimeError(f"[CUDA ERROR] in rasterizer stage '{stage}': {ex}") from ex
