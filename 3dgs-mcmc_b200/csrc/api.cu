@@ -3,6 +3,7 @@
 #include "../../include/gs_b200.h"
 
 #include <cstdio>
+#include <vector>
 
 #include "kernels.cuh"
 
@@ -32,6 +33,31 @@ struct BwdScratch {
     }
 };
 
+
+// ---- optional per-stage timing (CUDA events on the caller's stream) and a kernel-launch counter ----
+enum Stage {
+    ST_PREPROCESS = 0, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_PACK, ST_RENDER_FWD, ST_BWD_ZERO, ST_RENDER_BWD,
+    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_COUNT
+};
+const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "scan", "duplicate_keys", "radix_sort", "ranges_pack",
+                                           "render_fwd", "bwd_zero", "render_bwd", "preprocess_bwd",
+                                           "compute_relocation", "add_noise"};
+struct Profiler {
+    bool on = false;
+    std::vector<cudaEvent_t> ev;
+    std::vector<int> stage;   // stage[i] = what ran between ev[i-1] and ev[i]; -1 = region start
+    size_t n = 0;
+    unsigned long long launches = 0;
+} g_prof;
+
+inline void prof_mark(cudaStream_t stream, int stage) {
+    if (!g_prof.on || g_prof.n >= g_prof.ev.size()) return;
+    cudaEventRecord(g_prof.ev[g_prof.n], stream);
+    g_prof.stage[g_prof.n] = stage;
+    ++g_prof.n;
+}
+inline void count_launches(int k) { g_prof.launches += (unsigned long long)k; }
+
 }  // namespace
 
 extern "C" {
@@ -45,6 +71,38 @@ const char* gs_error_string(int code) {
     if (code > 0) return cudaGetErrorString((cudaError_t)code);
     return "gs_b200: unknown error";
 }
+
+
+int gs_profile_enable(int max_marks) {
+    for (cudaEvent_t e : g_prof.ev) cudaEventDestroy(e);
+    g_prof.ev.clear(); g_prof.stage.clear(); g_prof.n = 0; g_prof.on = false;
+    if (max_marks <= 0) return GS_OK;
+    g_prof.ev.resize((size_t)max_marks);
+    g_prof.stage.assign((size_t)max_marks, -1);
+    for (auto& e : g_prof.ev) GS_CUDA_TRY(cudaEventCreate(&e));
+    g_prof.on = true;
+    return GS_OK;
+}
+
+int gs_profile_collect(float* ms_sum, int* calls) {
+    for (int i = 0; i < ST_COUNT; ++i) { ms_sum[i] = 0.f; calls[i] = 0; }
+    if (g_prof.n == 0) return GS_OK;
+    GS_CUDA_TRY(cudaEventSynchronize(g_prof.ev[g_prof.n - 1]));
+    for (size_t i = 1; i < g_prof.n; ++i) {
+        const int st = g_prof.stage[i];
+        if (st < 0) continue;
+        float ms = 0.f;
+        GS_CUDA_TRY(cudaEventElapsedTime(&ms, g_prof.ev[i - 1], g_prof.ev[i]));
+        ms_sum[st] += ms;
+        calls[st] += 1;
+    }
+    g_prof.n = 0;
+    return GS_OK;
+}
+
+int gs_stage_count(void) { return ST_COUNT; }
+const char* gs_stage_name(int stage) { return (stage >= 0 && stage < ST_COUNT) ? kStageNames[stage] : "?"; }
+unsigned long long gs_launch_count(void) { return g_prof.launches; }
 
 size_t gs_geom_bytes(int P) { return GeomWS::carve(nullptr, (size_t)(P > 0 ? P : 0)).bytes + kAlign; }
 size_t gs_image_bytes(int W, int H) { return ImageWS::carve(nullptr, (size_t)W, (size_t)H).bytes + kAlign; }
@@ -86,10 +144,14 @@ int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means
     pp.prefiltered = prefiltered;
     pp.radii = radii; pp.is_used = is_used; pp.means2D = g.means2D; pp.depths = g.depths; pp.cov3D = g.cov3D;
     pp.rgb = g.rgb; pp.conic_opacity = g.conic_opacity; pp.tiles_touched = g.tiles_touched; pp.clamped = g.clamped;
+    prof_mark(stream, -1);
     int rc = launch_preprocess_fwd(pp, stream);
     if (rc) return rc;
+    prof_mark(stream, ST_PREPROCESS);
     rc = launch_inclusive_scan(g.tiles_touched, P, g.point_offsets, g.scan_block_sums, g.num_rendered, stream);
     if (rc) return rc;
+    prof_mark(stream, ST_SCAN);
+    count_launches(4);
     if (num_rendered_host)
         GS_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, g.num_rendered, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
     return GS_OK;
@@ -113,22 +175,30 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
     int rc = GS_OK;
     const uint64_t* keys_sorted = (passes & 1) ? b.keys_b : b.keys_a;
     const uint32_t* vals_sorted = (passes & 1) ? b.vals_b : b.vals_a;
+    prof_mark(stream, -1);
+    if (P > 0) GS_CUDA_TRY(cudaMemsetAsync(b.error_flag, 0, 16, stream));
     if (R > 0) {
-        GS_CUDA_TRY(cudaMemsetAsync(b.error_flag, 0, 16, stream));
         rc = launch_duplicate_keys(P, g.means2D, g.depths, g.point_offsets, radii, grid, b.keys_a, b.vals_a, stream);
         if (rc) return rc;
+        prof_mark(stream, ST_DUPLICATE);
         rc = launch_radix_sort(b.keys_a, b.keys_b, b.vals_a, b.vals_b, R, passes, b.sort_scratch, b.error_flag, stream);
         if (rc) return rc;
+        prof_mark(stream, ST_SORT);
+        count_launches(3 + passes);
     }
     const float* colors = colors_precomp ? colors_precomp : g.rgb;
     rc = launch_ranges_and_pack(R, keys_sorted, vals_sorted, g.means2D, g.conic_opacity, colors, img.ranges, tiles, b.packed, stream);
     if (rc) return rc;
+    prof_mark(stream, ST_PACK);
+    count_launches(R > 0 ? 2 : 1);
 
     RenderFwdParams rp;
     rp.ranges = img.ranges; rp.packed = b.packed; rp.W = W; rp.H = H; rp.tiles_x = (int)grid.x; rp.bg = background;
     rp.final_T = img.final_T; rp.n_contrib = img.n_contrib; rp.out_color = out_color; rp.is_used = is_used;
     rp.tile_max_contrib = img.tile_max_contrib;
-    return launch_render_fwd(rp, (int)tiles, stream);
+    rc = launch_render_fwd(rp, (int)tiles, stream);
+    prof_mark(stream, ST_RENDER_FWD);
+    return rc;
 }
 
 int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H, const float* background,
@@ -154,7 +224,9 @@ int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
     BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, passes);
     BwdScratch sc = BwdScratch::carve(aligned_base(scratch), (size_t)P);
+    prof_mark(stream, -1);
     GS_CUDA_TRY(cudaMemsetAsync(sc.acc_color_opacity, 0, sc.bytes, stream));
+    prof_mark(stream, ST_BWD_ZERO);
 
     int rc = GS_OK;
     if (R > 0) {
@@ -165,6 +237,8 @@ int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H
         rb.acc_color_opacity = sc.acc_color_opacity; rb.acc_mean_conic = sc.acc_mean_conic; rb.acc_conic_w = sc.acc_conic_w;
         rc = launch_render_bwd(rb, (int)tiles, stream);
         if (rc) return rc;
+        prof_mark(stream, ST_RENDER_BWD);
+        count_launches(1);
     }
     PreprocessBwdParams pb;
     pb.P = P; pb.D = D; pb.M = M; pb.means3D = means3D; pb.radii = radii; pb.shs = shs; pb.clamped = g.clamped;
@@ -177,7 +251,10 @@ int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H
     pb.acc_color_opacity = sc.acc_color_opacity; pb.acc_mean_conic = sc.acc_mean_conic; pb.acc_conic_w = sc.acc_conic_w;
     pb.dL_dmeans3D = dL_dmeans3D; pb.dL_dmeans2D = dL_dmeans2D; pb.dL_dcolors = dL_dcolors; pb.dL_dopacity = dL_dopacity;
     pb.dL_dcov3D = dL_dcov3D; pb.dL_dsh = dL_dsh; pb.dL_dscales = dL_dscales; pb.dL_drots = dL_drotations;
-    return launch_preprocess_bwd(pb, stream);
+    rc = launch_preprocess_bwd(pb, stream);
+    prof_mark(stream, ST_PREPROCESS_BWD);
+    count_launches(1);
+    return rc;
 }
 
 int gs_mark_visible(void* stream_, int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -192,7 +269,11 @@ int gs_compute_relocation(void* stream_, int P, const float* opacity_old, const 
                           const float* binoms, int n_max, float* opacity_new, float* scale_new) {
     if (P < 0 || n_max <= 0) return GS_ERR_ARG;
     if (P > 0 && (!opacity_old || !scale_old || !N || !binoms || !opacity_new || !scale_new)) return GS_ERR_ARG;
-    return launch_compute_relocation(P, opacity_old, scale_old, N, binoms, n_max, opacity_new, scale_new, (cudaStream_t)stream_);
+    prof_mark((cudaStream_t)stream_, -1);
+    int rc = launch_compute_relocation(P, opacity_old, scale_old, N, binoms, n_max, opacity_new, scale_new, (cudaStream_t)stream_);
+    prof_mark((cudaStream_t)stream_, ST_RELOCATION);
+    count_launches(P > 0 ? 1 : 0);
+    return rc;
 }
 
 int gs_add_noise(void* stream_, int P, float* xyz, const float* scaling_raw, const float* rotation_raw,
@@ -200,7 +281,11 @@ int gs_add_noise(void* stream_, int P, float* xyz, const float* scaling_raw, con
                  unsigned long long offset) {
     if (P < 0) return GS_ERR_ARG;
     if (P > 0 && (!xyz || !scaling_raw || !rotation_raw || !opacity_raw)) return GS_ERR_ARG;
-    return launch_add_noise(P, xyz, scaling_raw, rotation_raw, opacity_raw, noise, lr_scale, seed, offset, (cudaStream_t)stream_);
+    prof_mark((cudaStream_t)stream_, -1);
+    int rc = launch_add_noise(P, xyz, scaling_raw, rotation_raw, opacity_raw, noise, lr_scale, seed, offset, (cudaStream_t)stream_);
+    prof_mark((cudaStream_t)stream_, ST_ADD_NOISE);
+    count_launches(P > 0 ? 1 : 0);
+    return rc;
 }
 
 long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const void* geom_ws, const void* binning_ws,

@@ -40,6 +40,11 @@ SIGNATURES = {
     "gs_mark_visible": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4),
     "gs_compute_relocation": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 2),
     "gs_add_noise": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 5 + [_c_float, _c_ull, _c_ull]),
+    "gs_profile_enable": (_c_int, [_c_int]),
+    "gs_profile_collect": (_c_int, [_c_void_p, _c_void_p]),
+    "gs_stage_count": (_c_int, []),
+    "gs_stage_name": (ctypes.c_char_p, [_c_int]),
+    "gs_launch_count": (_c_ull, []),
     "gs_debug_fetch": (ctypes.c_longlong, [_c_int, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 4 + [_c_size_t]),
 }
 
@@ -169,9 +174,11 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
-                                 geomBuffer, R, binningBuffer, imageBuffer, debug):
+                                 geomBuffer, R, binningBuffer, imageBuffer, debug, out_buffers=None):
     """Same contract as RasterizeGaussiansBackwardCUDA (rasterize_points.cu:120-199): returns
-    (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)."""
+    (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
+    Additive: out_buffers (dict name -> preallocated contiguous tensor, names means2D/colors/opacity/means3D/cov3D/
+    sh/scales/rotations) lets the caller supply the outputs, e.g. views of one all-reduce arena (dp.GradientArena)."""
     device = means3D.device
     P = int(means3D.size(0))
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
@@ -196,8 +203,16 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
 
     with torch.cuda.device(device):
         # Every output is fully written by the fused backward kernel: no zero fill.
-        dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations = (
-            torch.empty(s, **opts) for s in shapes)
+        names = ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")
+        outs = []
+        for name, shape in zip(names, shapes):
+            t = out_buffers.get(name) if out_buffers else None
+            if t is None:
+                t = torch.empty(shape, **opts)
+            elif tuple(t.shape) != shape or t.dtype != torch.float32 or not t.is_contiguous() or t.device != device:
+                raise RuntimeError(f"out_buffers['{name}'] must be a contiguous float32 {shape} tensor on {device}")
+            outs.append(t)
+        dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations = outs
         scratch = torch.empty(_lib.gs_backward_scratch_bytes(P), dtype=torch.uint8, device=device)
         _check(_lib.gs_backward(
             _stream(device), P, int(degree), M, int(R), W, H, _ptr(background), _ptr(means3D), _ptr(sh), _ptr(colors),
@@ -283,3 +298,21 @@ def _debug_sync(stage):
         torch.cuda.synchronize()
     except RuntimeError as ex:
         raise RuntimeError(f"[CUDA ERROR] in rasterizer stage '{stage}': {ex}") from ex
+
+
+def profile_enable(max_marks):
+    """Arm (or, with 0, disarm) the library's per-stage CUDA-event timing. Measurement only."""
+    _check(_lib.gs_profile_enable(int(max_marks)), "gs_profile_enable")
+
+
+def profile_collect():
+    """-> {stage_name: (ms_sum, calls)} since the last collect; synchronises on the last recorded mark."""
+    n = _lib.gs_stage_count()
+    ms = (ctypes.c_float * n)()
+    calls = (ctypes.c_int * n)()
+    _check(_lib.gs_profile_collect(ctypes.cast(ms, _c_void_p), ctypes.cast(calls, _c_void_p)), "gs_profile_collect")
+    return {_lib.gs_stage_name(i).decode(): (float(ms[i]), int(calls[i])) for i in range(n)}
+
+
+def launch_count():
+    return int(_lib.gs_launch_count())

@@ -1,0 +1,446 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 Gaussian-splatting hot path.
+
+Metric (BASELINE.json): fwd+bwd rasterize ms/iter at 3M Gaussians / 1080p, reported as training views/s
+(1 view per GPU per step; `ms_per_step` is the fwd+bwd ms/iter). One step = one forward + one backward of the
+rasterizer on one camera view of a seeded synthetic "garden" scene (no datasets on the box); with N > 1 GPUs each
+rank renders its own view against replicated Gaussians and the 59-float-per-Gaussian gradient arena is
+all-reduced over NCCL (weak scaling: per-GPU work fixed).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # this implementation
+    python bench.py --impl reference [--gpus N] --steps K --warmup W  # the reference path on the host CPU cores
+
+JSON keys follow the driver contract; see DESIGN.md §Measurement for how each number is obtained.
+`oracle/` is used here only for the cpu_baseline / --impl reference / ref_cuda baseline legs.
+"""
+import argparse
+import json
+import math
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "3dgs-mcmc_b200"))
+
+import numpy as np  # noqa: E402
+
+SCENE = dict(kind="garden", seed=0, fovx=1.2, cam_radius=6.0, elevation=20.0, ncams=16)
+METRIC = "train views/s (fwd+bwd rasterize, 3M Gaussians, 1920x1080, SH deg 3)"
+FLOPS_PER_PAIR_FWD = 16   # ~16 FP32 ops + 1 exp per evaluated (pixel, splat) pair
+FLOPS_PER_PAIR_BWD = 45   # ~45 FP32 ops + 1 exp + 1 div per evaluated pair
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--P", type=int, default=3_000_000)
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--skip-baselines", action="store_true", help="skip the cpu_baseline and ref_cuda legs")
+    return ap.parse_args()
+
+
+def build_scene(P, W, H):
+    import gs_synth
+    scene = gs_synth.scene_garden(P, SCENE["seed"])
+    cams = gs_synth.orbit_cameras(SCENE["ncams"], SCENE["cam_radius"], W, H, SCENE["fovx"], SCENE["elevation"])
+    return scene, cams
+
+
+def workload_config(P, W, H, n_gpus):
+    return {"workload": f"synthetic garden scene (gs_synth.scene_garden seed 0): P={P} Gaussians, SH degree 3, "
+                        f"{W}x{H}, orbit cameras r=6 fovx=1.2; BASELINE.json config 3/4 shape at the headline size",
+            "gaussians": P, "width": W, "height": H, "views_per_step": n_gpus,
+            "parallelism": f"view-sharded dp{n_gpus}, replicated Gaussians" + (", NCCL all-reduce of the 59*P-float gradient arena" if n_gpus > 1 else ""),
+            "l2_policy": "inputs (708 MB of parameters, ~1.5 GB of instance records) exceed the 126 MB L2; no explicit flush"}
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# CPU port (oracle) timing — used by cpu_baseline and by --impl reference
+# ------------------------------------------------------------------------------------------------------------------
+def cpu_port_step(scene, cam, dL, tile_step):
+    """One fwd+bwd of the CPU oracle with the render stages run on every `tile_step`-th tile.
+    Returns (estimated full-step seconds, measured seconds, breakdown)."""
+    from oracle import oracle
+    W, H = cam["image_width"], cam["image_height"]
+    P = scene["means3D"].shape[0]
+    t = {}
+    t0 = time.perf_counter()
+    pre = oracle.preprocess(scene["means3D"], scene["scales"], scene["rotations"], scene["opacities"], scene["shs"],
+                            cam["viewmatrix"], cam["projmatrix"], cam["campos"], W, H, cam["tanfovx"], cam["tanfovy"], 3, 1.0)
+    t["preprocess"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    b = oracle.bin(pre["means2D"], pre["depths"], pre["radii"], pre["tiles_touched"], W, H)
+    t["bin"] = time.perf_counter() - t0
+    bg = np.zeros(3, np.float32)
+    t0 = time.perf_counter()
+    r = oracle.render_fwd(W, H, b["ranges"], b["point_list"], pre["means2D"], pre["conic_opacity"], pre["rgb"], bg, P, tile_step)
+    t["render_fwd_sample"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    rb = oracle.render_bwd(W, H, b["ranges"], b["point_list"], bg, pre["means2D"], pre["conic_opacity"], pre["rgb"],
+                           r["final_T"], r["n_contrib"], dL, P, tile_step)
+    t["render_bwd_sample"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    oracle.preprocess_bwd(scene["means3D"], pre["radii"], scene["shs"], pre["clamped"], scene["scales"], scene["rotations"],
+                          1.0, pre["cov3D"], cam["viewmatrix"], cam["projmatrix"], cam["campos"], W, H, cam["tanfovx"],
+                          cam["tanfovy"], 3, rb["dL_dmean2D"], rb["dL_dconic"], rb["dL_dcolors"])
+    t["preprocess_bwd"] = time.perf_counter() - t0
+    measured = sum(t.values())
+    est = t["preprocess"] + t["bin"] + t["preprocess_bwd"] + tile_step * (t["render_fwd_sample"] + t["render_bwd_sample"])
+    return est, measured, t
+
+
+def cpu_baseline_leg(scene, cam, W, H, tile_step=64):
+    from oracle import oracle
+    dL = np.random.default_rng(3).standard_normal((3, H, W)).astype(np.float32)
+    est, measured, t = cpu_port_step(scene, cam, dL, tile_step)
+    return {"value": 1.0 / est, "unit": "views/s", "cores": oracle.num_threads(), "kind": "port",
+            "sample": f"one view: preprocess + binning + preprocess-backward on all {scene['means3D'].shape[0]} Gaussians, "
+                      f"render fwd+bwd on every {tile_step}th tile scaled x{tile_step}; {measured:.1f} s of CPU work, "
+                      f"estimated full step {est:.1f} s",
+            "note": "the reference has no CPU implementation of this path; this is the plain-C restatement (oracle/oracle_cpu.c) with OpenMP"}
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference path on the host cores. The reference's own implementation is CUDA-only, so
+    this times the CPU port (kind 'port'). Rank 0 alone works; other ranks exit."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    from oracle import oracle
+    W, H, P = args.width, args.height, args.P
+    scene, cams = build_scene(P, W, H)
+    dL = np.random.default_rng(3).standard_normal((3, H, W)).astype(np.float32)
+    tile_step = 64
+    ests = []
+    for i in range(args.warmup + args.steps):
+        est, measured, _ = cpu_port_step(scene, cams[i % len(cams)], dL, tile_step)
+        if i >= args.warmup:
+            ests.append(est)
+        # keep the whole run within a few minutes
+        if i == 0 and measured * (args.warmup + args.steps) > 240.0:
+            tile_step *= 4
+    sec = sum(ests) / len(ests)
+    value = args.gpus * 0 + 1.0 / sec  # one host, one view at a time
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "views/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(P, W, H, args.gpus),
+            "cpu_baseline": {"value": value, "unit": "views/s", "cores": oracle.num_threads(), "kind": "port",
+                             "sample": f"each step: full preprocess/binning/preprocess-backward, render fwd+bwd on every "
+                                       f"{tile_step}th tile scaled x{tile_step}"},
+            "e2e": {"value": value, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# clocks sampling
+# ------------------------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        while self.ok and not self._stop_evt.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                try:
+                    mask = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    mask = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# this implementation
+# ------------------------------------------------------------------------------------------------------------------
+def run_b200_arm(args):
+    import torch
+    import torch.distributed as dist
+    import gs_synth
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, _native as C
+    from diff_gaussian_rasterization import dp
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this implementation has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    n_gpus = world
+    W, H, P = args.width, args.height, args.P
+    K, Wm = args.steps, args.warmup
+
+    scene_np, cams_np = build_scene(P, W, H)
+    s = gs_synth.to_torch(scene_np, dev)
+    cams = [gs_synth.to_torch(c, dev) for c in cams_np]
+    bg = torch.zeros(3, dtype=torch.float32, device=dev)
+    gen = torch.Generator(device="cpu").manual_seed(5)
+    dL = (torch.randn((3, H, W), generator=gen) / (3 * H * W)).to(dev)
+    e = torch.empty(0)
+    arena = dp.GradientArena(P, 16, dev)
+
+    def cam_for(step):
+        return cams[(step * n_gpus + rank) % len(cams)]
+
+    state = {}
+
+    def device_step(step):
+        c = cam_for(step)
+        R, color, radii, geom, binning, img, is_used = C.rasterize_gaussians(
+            bg, s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+            c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3, c["campos"], False, False)
+        C.rasterize_gaussians_backward(
+            bg, s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+            c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], geom, R, binning, img, False,
+            out_buffers=arena.backward_buffers())
+        if n_gpus > 1:
+            arena.all_reduce()
+        state.update(R=R, radii=radii, img=img, geom=geom, binning=binning)
+
+    def barrier():
+        if n_gpus > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(Wm):
+        device_step(i)
+    barrier()
+    marks = K * 16 + 8
+    C.profile_enable(marks)
+    launches0 = C.launch_count()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for i in range(K):
+        device_step(Wm + i)
+    ev1.record()
+    barrier()
+    clocks = sampler.stop()
+    total_ms = ev0.elapsed_time(ev1)
+    launches = C.launch_count() - launches0
+    stages = C.profile_collect()
+    C.profile_enable(0)
+    if n_gpus > 1:
+        t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    ms_per_step = total_ms / K
+    value = n_gpus * 1000.0 / ms_per_step
+
+    # ---- workload statistics for the roofline (from the last step's state; outside the timed region) ----
+    R = state["R"]
+    radii = state["radii"]
+    visible = int((radii > 0).sum().item())
+    n_contrib = C.debug_fetch(21, P, R, W, H, state["geom"], state["binning"], state["img"], torch.int32)
+    tmax = C.debug_fetch(23, P, R, W, H, state["geom"], state["binning"], state["img"], torch.int32)
+    ranges = C.debug_fetch(22, P, R, W, H, state["geom"], state["binning"], state["img"], torch.int32).view(-1, 2)
+    # backward evaluates, per warp (8x4 pixel patch), every list position below the patch's max n_contrib
+    Hp, Wp = (H + 15) // 16 * 16, (W + 15) // 16 * 16
+    nc = torch.zeros((Hp, Wp), dtype=torch.int32, device=dev)
+    nc[:H, :W] = n_contrib.view(H, W)
+    patch_max = nc.view(Hp // 4, 4, Wp // 8, 8).amax(dim=(1, 3)).long()
+    pairs_bwd = int(patch_max.sum().item()) * 32
+    # forward evaluates every position up to the tile's termination; bounded below by n_contrib, above by list length
+    pairs_fwd_lower = int(n_contrib.long().sum().item())
+    tile_len = (ranges[:, 1] - ranges[:, 0]).long()
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+    sm_max_mhz = float(clocks.get("sm_max_mhz") or peaks.get("sm_max_mhz", 1965.0))
+    fp32_peak_tflops = sm_count * 128 * 2 * sm_max_mhz * 1e6 / 1e12
+
+    def stage_ms(name):
+        ms, calls = stages.get(name, (0.0, 0))
+        return ms / calls if calls else None
+
+    M = 16
+    alg_bytes = {  # SURVEY.md §8(d) per-unit figures x units of this launch
+        "preprocess_fwd": visible * (44 + 12 * M + 75) + (P - visible) * 52,
+        "scan": P * 8,
+        "duplicate_keys": P * 20 + R * 12,
+        "radix_sort": R * 24,
+        "ranges_pack": R * (12 + 40 + 48) + len(tile_len) * 8,
+        "render_fwd": R * 48 + W * H * 20,
+        "render_bwd": int(tmax.long().sum().item()) * 48 + W * H * 20 + visible * 36,
+        "preprocess_bwd": visible * (107 + 12 * M + 40 + 12 * M) + (P - visible) * (4 + 300),
+        "bwd_zero": P * 36,
+    }
+    stage_report = {}
+    for name, b in alg_bytes.items():
+        ms = stage_ms(name)
+        if ms:
+            stage_report[name] = {"ms": round(ms, 4), "alg_GBps": round(b / ms / 1e6, 1), "hbm_frac": round(b / ms / 1e6 / hbm_peak, 4)}
+    dom = max(("render_bwd", "render_fwd", "radix_sort", "preprocess_bwd", "preprocess_fwd", "ranges_pack"),
+              key=lambda n: stage_ms(n) or 0.0)
+    dom_ms = stage_ms(dom)
+    if dom in ("render_bwd", "render_fwd"):
+        pairs = pairs_bwd if dom == "render_bwd" else pairs_fwd_lower
+        fl = pairs * (FLOPS_PER_PAIR_BWD if dom == "render_bwd" else FLOPS_PER_PAIR_FWD)
+        achieved = fl / (dom_ms * 1e-3) / 1e12
+        roofline = {"kernel": dom, "bound": "fp32", "achieved": round(achieved, 3), "peak": round(fp32_peak_tflops, 2),
+                    "unit": "TFLOP/s", "frac": round(achieved / fp32_peak_tflops, 4), "traffic": None,
+                    "ms": round(dom_ms, 4), "evaluated_pairs": pairs,
+                    "note": "FP32-SIMT bound (no tensor-core work on this path): algorithmic flops = evaluated (pixel, splat) pairs x "
+                            f"{FLOPS_PER_PAIR_BWD if dom == 'render_bwd' else FLOPS_PER_PAIR_FWD} (SURVEY.md 8d); peak = SMs x 128 lanes x 2 x max SM clock; "
+                            f"hbm view of the same launch: {stage_report.get(dom)}"}
+    else:
+        achieved = alg_bytes[dom] / (dom_ms * 1e-3) / 1e9
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s",
+                    "frac": round(achieved / hbm_peak, 4), "traffic": None, "ms": round(dom_ms, 4), "peak_source": peak_src}
+
+    # ---- e2e: public API, host buffers in, loss out ----
+    params = {k: s[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    gt_host = [torch.rand((3, H, W), generator=gen).pin_memory() for _ in range(2)]
+    cam_host = [{k: (torch.from_numpy(np.ascontiguousarray(v)).pin_memory() if isinstance(v, np.ndarray) else v)
+                 for k, v in c.items()} for c in cams_np]
+    gt_dev = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    view_dev = torch.empty((4, 4), dtype=torch.float32, device=dev)
+    proj_dev = torch.empty((4, 4), dtype=torch.float32, device=dev)
+    campos_dev = torch.empty((3,), dtype=torch.float32, device=dev)
+    h2d = gt_dev.numel() * 4 + (16 + 16 + 3) * 4
+    losses = []
+
+    def e2e_step(step):
+        ch = cam_host[(step * n_gpus + rank) % len(cam_host)]
+        gt_dev.copy_(gt_host[step % 2], non_blocking=True)
+        view_dev.copy_(ch["viewmatrix"], non_blocking=True)
+        proj_dev.copy_(ch["projmatrix"], non_blocking=True)
+        campos_dev.copy_(ch["campos"], non_blocking=True)
+        settings = GaussianRasterizationSettings(H, W, ch["tanfovx"], ch["tanfovy"], bg, 1.0, view_dev, proj_dev, 3,
+                                                 campos_dev, False, False)
+        means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+        image, radii_, used_ = GaussianRasterizer(settings)(
+            means3D=params["means3D"], means2D=means2D, shs=params["shs"], opacities=params["opacities"],
+            scales=params["scales"], rotations=params["rotations"])
+        loss = (image - gt_dev).abs().mean()
+        loss.backward()
+        if n_gpus > 1:
+            for p_ in params.values():
+                dist.all_reduce(p_.grad)
+        losses.append(float(loss.item()))  # the step's D2H result read
+        for p_ in params.values():
+            p_.grad = None
+
+    for i in range(min(Wm, 3)):
+        e2e_step(i)
+    barrier()
+    ev0.record()
+    for i in range(K):
+        e2e_step(Wm + i)
+    ev1.record()
+    barrier()
+    e2e_ms = ev0.elapsed_time(ev1)
+    if n_gpus > 1:
+        t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    e2e = {"value": n_gpus * 1000.0 * K / e2e_ms, "unit": "views/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+           "ms_per_step": e2e_ms / K, "api": "GaussianRasterizer.forward + L1 loss + loss.backward(); pinned gt image and camera in, loss out"}
+
+    if rank != 0:
+        if n_gpus > 1:
+            dist.destroy_process_group()
+        return
+
+    line = {"metric": METRIC, "value": value, "unit": "views/s", "n_gpus": n_gpus, "steps": K, "warmup": Wm,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": workload_config(P, W, H, n_gpus), "clocks": clocks, "e2e": e2e,
+            "gpu_launches": launches, "roofline": roofline, "stages": stage_report,
+            "scene_stats": {"num_rendered": R, "visible": visible, "instances_per_visible": round(R / max(visible, 1), 2),
+                            "tile_list_mean": float(tile_len.float().mean().item()), "tile_list_p99": float(torch.quantile(tile_len.float(), 0.99).item()),
+                            "pairs_bwd": pairs_bwd, "pairs_fwd_lower_bound": pairs_fwd_lower,
+                            "mpix_per_s": W * H / ms_per_step / 1e3}}
+
+    # ---- baseline legs (rank 0, N=1 only): reference CUDA on the same box, CPU port on the host cores ----
+    if n_gpus == 1 and not args.skip_baselines:
+        try:
+            from oracle import ref_cuda
+            if ref_cuda.available():
+                c = cams[0]
+
+                def ref_step():
+                    Rr, col, rad, used = ref_cuda.forward(bg, s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e,
+                                                          c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, s["shs"],
+                                                          3, c["campos"])
+                    ref_cuda.backward(bg, s["means3D"], rad, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+                                      c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], Rr)
+                for _ in range(3):
+                    ref_step()
+                torch.cuda.synchronize()
+                ev0.record()
+                kk = max(3, min(K, 10))
+                for _ in range(kk):
+                    ref_step()
+                ev1.record()
+                torch.cuda.synchronize()
+                rms = ev0.elapsed_time(ev1) / kk
+                line["ref_cuda"] = {"ms_per_step": rms, "value": 1000.0 / rms, "unit": "views/s", "steps": kk,
+                                    "what": "the reference's own cuda_rasterizer compiled for sm_100 (oracle/_ref), same tensors, same box",
+                                    "speedup_device": rms / ms_per_step}
+        except Exception as ex:  # baseline only; never fail the bench on it
+            line["ref_cuda"] = {"unavailable": repr(ex)[:200]}
+        try:
+            line["cpu_baseline"] = cpu_baseline_leg(scene_np, cams_np[0], W, H)
+        except Exception as ex:
+            line["cpu_baseline"] = {"unavailable": repr(ex)[:200]}
+    print(json.dumps(line), flush=True)
+    if n_gpus > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -102,6 +102,16 @@ int gs_add_noise(void* stream, int P, float* xyz, const float* scaling_raw, cons
                  const float* opacity_raw, const float* noise, float lr_scale,
                  unsigned long long seed, unsigned long long offset);
 
+/* ---- measurement hooks (bench.py): per-stage timing with CUDA events recorded on the caller's stream between
+ *      the stages of each call, and a counter of kernel launches made by this library. Process-global; not used
+ *      by the compute path. gs_profile_enable(n) arms n event marks (0 disables); gs_profile_collect() waits for
+ *      the last mark, writes per-stage summed milliseconds and call counts ([gs_stage_count()] each) and rearms. ---- */
+int gs_profile_enable(int max_marks);
+int gs_profile_collect(float* ms_sum, int* calls);
+int gs_stage_count(void);
+const char* gs_stage_name(int stage);
+unsigned long long gs_launch_count(void);
+
 /* Test / debug hook: copy one internal array of the workspaces into dst (device memory). `which` uses the
  * numbering of the reference's state structs so parity tests can compare array by array:
  *   0 depths f32[P] | 1 clamped u8[P] (bit c = channel c) | 3 means2D f32[2P] | 4 cov3D f32[6P]

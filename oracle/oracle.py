@@ -1,0 +1,218 @@
+"""numpy front-end of the plain-C CPU oracle (oracle/oracle_cpu.c -> liboracle_cpu.so).
+
+TEST INFRASTRUCTURE ONLY — the checker, never the product. Only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs may import this module. See oracle_cpu.c for the reference file:line each
+function follows and for the parity-pin status.
+
+The stages are separate on purpose so that integer stages can be checked bit-exactly on identical float inputs:
+  preprocess() -> bin() -> render_fwd() -> render_bwd() -> preprocess_bwd()
+``forward()`` / ``backward()`` chain them the way Rasterizer::forward / ::backward do
+(cuda_rasterizer/rasterizer_impl.cu:198-338, :342-436).
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_DIR = os.path.dirname(os.path.abspath(__file__))
+_PATH = os.path.join(_DIR, "liboracle_cpu.so")
+_lib = None
+
+_fp = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
+_ip = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+_up = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
+_bp = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+_kp = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
+_vp, _i, _f = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
+
+
+def build():
+    subprocess.check_call(["make", "-C", _DIR, "liboracle_cpu.so"], stdout=subprocess.DEVNULL)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_PATH):
+            build()
+        L = ctypes.CDLL(_PATH)
+        L.orc_preprocess.argtypes = [_i, _i, _i, _fp, _vp, _f, _vp, _fp, _vp, _vp, _vp, _fp, _fp, _vp, _i, _i, _f, _f,
+                                     _ip, _fp, _fp, _fp, _fp, _fp, _up, _bp]
+        L.orc_mark_visible.argtypes = [_i, _fp, _fp, _bp]
+        L.orc_bin.argtypes = [_i, _i, _i, _fp, _fp, _ip, _up, ctypes.c_uint32, _kp, _up, _up]
+        L.orc_render_fwd.argtypes = [_i, _i, _up, _up, _fp, _fp, _fp, _fp, _fp, _fp, _up, _ip, _i]
+        L.orc_render_bwd.argtypes = [_i, _i, _up, _up, _fp, _fp, _fp, _fp, _fp, _up, _fp, _fp, _fp, _fp, _fp, _i]
+        L.orc_preprocess_bwd.argtypes = [_i, _i, _i, _fp, _ip, _vp, _bp, _vp, _vp, _f, _fp, _fp, _fp, _vp, _i, _i, _f, _f,
+                                         _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp]
+        L.orc_compute_relocation.argtypes = [_i, _fp, _fp, _ip, _fp, _i, _fp, _fp]
+        L.orc_add_noise.argtypes = [_i, _fp, _fp, _fp, _fp, _fp, _f]
+        L.orc_num_threads.restype = _i
+        for n in ("orc_preprocess", "orc_mark_visible", "orc_bin", "orc_render_fwd", "orc_render_bwd",
+                  "orc_preprocess_bwd", "orc_compute_relocation", "orc_add_noise"):
+            getattr(L, n).restype = None
+        _lib = L
+    return _lib
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _opt(a):
+    """Optional float array -> void* (NULL when absent)."""
+    if a is None or a.size == 0:
+        return None, None
+    a = _f32(a)
+    return a, a.ctypes.data_as(ctypes.c_void_p)
+
+
+def num_threads():
+    return int(lib().orc_num_threads())
+
+
+def preprocess(means3D, scales, rotations, opacities, shs, view, proj, campos, W, H, tanfovx, tanfovy, degree=3,
+               scale_modifier=1.0, cov3D_precomp=None, colors_precomp=None):
+    means3D = _f32(means3D)
+    P = means3D.shape[0]
+    k_sc, p_sc = _opt(scales)
+    k_ro, p_ro = _opt(rotations)
+    k_sh, p_sh = _opt(shs)
+    k_c3, p_c3 = _opt(cov3D_precomp)
+    k_cp, p_cp = _opt(colors_precomp)
+    k_cam, p_cam = _opt(campos)
+    M = k_sh.shape[1] if k_sh is not None else 0
+    out = dict(radii=np.zeros(P, np.int32), means2D=np.zeros((P, 2), np.float32), depths=np.zeros(P, np.float32),
+               cov3D=np.zeros((P, 6), np.float32), rgb=np.zeros((P, 3), np.float32),
+               conic_opacity=np.zeros((P, 4), np.float32), tiles_touched=np.zeros(P, np.uint32),
+               clamped=np.zeros((P, 3), np.uint8))
+    lib().orc_preprocess(P, degree, M, means3D, p_sc, scale_modifier, p_ro, _f32(opacities).reshape(-1), p_sh, p_c3, p_cp,
+                         _f32(view).reshape(-1), _f32(proj).reshape(-1), p_cam, W, H, tanfovx, tanfovy, out["radii"],
+                         out["means2D"], out["depths"], out["cov3D"], out["rgb"], out["conic_opacity"],
+                         out["tiles_touched"], out["clamped"])
+    return out
+
+
+def mark_visible(means3D, view):
+    means3D = _f32(means3D)
+    present = np.zeros(means3D.shape[0], np.uint8)
+    lib().orc_mark_visible(means3D.shape[0], means3D, _f32(view).reshape(-1), present)
+    return present.astype(bool)
+
+
+def bin(means2D, depths, radii, tiles_touched, W, H):
+    """-> dict(point_offsets, keys (sorted u64), point_list (sorted ids u32), ranges [tiles,2], R)."""
+    P = radii.shape[0]
+    offsets = np.cumsum(tiles_touched.astype(np.uint64)).astype(np.uint32)
+    R = int(offsets[-1]) if P else 0
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    keys = np.zeros(max(R, 1), np.uint64)
+    vals = np.zeros(max(R, 1), np.uint32)
+    ranges = np.zeros((tiles, 2), np.uint32)
+    lib().orc_bin(P, W, H, _f32(means2D), _f32(depths), np.ascontiguousarray(radii, np.int32), offsets, R, keys, vals,
+                  ranges.reshape(-1))
+    return dict(point_offsets=offsets, keys=keys[:R], point_list=vals[:R], ranges=ranges, R=R)
+
+
+def render_fwd(W, H, ranges, point_list, means2D, conic_opacity, colors, bg, P, tile_step=1):
+    out_color = np.zeros((3, H, W), np.float32)
+    final_T = np.zeros(H * W, np.float32)
+    n_contrib = np.zeros(H * W, np.uint32)
+    is_used = np.zeros(P, np.int32)
+    pl = np.ascontiguousarray(point_list, np.uint32) if len(point_list) else np.zeros(1, np.uint32)
+    lib().orc_render_fwd(W, H, np.ascontiguousarray(ranges, np.uint32).reshape(-1), pl, _f32(means2D), _f32(conic_opacity),
+                         _f32(colors), _f32(bg), out_color.reshape(-1), final_T, n_contrib, is_used, tile_step)
+    return dict(color=out_color, final_T=final_T, n_contrib=n_contrib, is_used=is_used)
+
+
+def render_bwd(W, H, ranges, point_list, bg, means2D, conic_opacity, colors, final_T, n_contrib, dL_dpix, P, tile_step=1):
+    g = dict(dL_dmean2D=np.zeros((P, 3), np.float32), dL_dconic=np.zeros((P, 4), np.float32),
+             dL_dopacity=np.zeros(P, np.float32), dL_dcolors=np.zeros((P, 3), np.float32))
+    pl = np.ascontiguousarray(point_list, np.uint32) if len(point_list) else np.zeros(1, np.uint32)
+    lib().orc_render_bwd(W, H, np.ascontiguousarray(ranges, np.uint32).reshape(-1), pl, _f32(bg), _f32(means2D),
+                         _f32(conic_opacity), _f32(colors), _f32(final_T), np.ascontiguousarray(n_contrib, np.uint32),
+                         _f32(dL_dpix).reshape(-1), g["dL_dmean2D"], g["dL_dconic"], g["dL_dopacity"], g["dL_dcolors"],
+                         tile_step)
+    return g
+
+
+def preprocess_bwd(means3D, radii, shs, clamped, scales, rotations, scale_modifier, cov3D, view, proj, campos, W, H,
+                   tanfovx, tanfovy, degree, dL_dmean2D, dL_dconic, dL_dcolors):
+    means3D = _f32(means3D)
+    P = means3D.shape[0]
+    k_sh, p_sh = _opt(shs)
+    k_sc, p_sc = _opt(scales)
+    k_ro, p_ro = _opt(rotations)
+    k_cam, p_cam = _opt(campos)
+    M = k_sh.shape[1] if k_sh is not None else 0
+    g = dict(dL_dmeans3D=np.zeros((P, 3), np.float32), dL_dcov3D=np.zeros((P, 6), np.float32),
+             dL_dsh=np.zeros((P, max(M, 1), 3), np.float32), dL_dscales=np.zeros((P, 3), np.float32),
+             dL_drots=np.zeros((P, 4), np.float32))
+    lib().orc_preprocess_bwd(P, degree, M, means3D, np.ascontiguousarray(radii, np.int32), p_sh,
+                             np.ascontiguousarray(clamped, np.uint8).reshape(-1), p_sc, p_ro, scale_modifier, _f32(cov3D),
+                             _f32(view).reshape(-1), _f32(proj).reshape(-1), p_cam, W, H, tanfovx, tanfovy,
+                             _f32(dL_dmean2D), _f32(dL_dconic), _f32(dL_dcolors), g["dL_dmeans3D"], g["dL_dcov3D"],
+                             g["dL_dsh"].reshape(-1), g["dL_dscales"], g["dL_drots"])
+    if M == 0:
+        g["dL_dsh"] = np.zeros((P, 0, 3), np.float32)
+    return g
+
+
+def forward(scene, cam, bg=(0.0, 0.0, 0.0), degree=3, scale_modifier=1.0, tile_step=1):
+    """Whole forward on numpy inputs (scene/cam dicts as produced by gs_synth). Returns a dict with every stage's
+    arrays (the CPU analogue of geomBuffer / binningBuffer / imgBuffer) plus color, radii, is_used."""
+    W, H = cam["image_width"], cam["image_height"]
+    P = scene["means3D"].shape[0]
+    pre = preprocess(scene["means3D"], scene["scales"], scene["rotations"], scene["opacities"], scene["shs"],
+                     cam["viewmatrix"], cam["projmatrix"], cam["campos"], W, H, cam["tanfovx"], cam["tanfovy"], degree,
+                     scale_modifier)
+    b = bin(pre["means2D"], pre["depths"], pre["radii"], pre["tiles_touched"], W, H)
+    bg = np.asarray(bg, np.float32)
+    r = render_fwd(W, H, b["ranges"], b["point_list"], pre["means2D"], pre["conic_opacity"], pre["rgb"], bg, P, tile_step)
+    st = dict(pre)
+    st.update(b)
+    st.update(r)
+    st["bg"] = bg
+    return st
+
+
+def backward(scene, cam, st, dL_dpix, degree=3, scale_modifier=1.0, tile_step=1):
+    """Whole backward from the state of forward(). Returns the 8 API gradients (reference order of
+    rasterize_points.cu:198) in a dict."""
+    W, H = cam["image_width"], cam["image_height"]
+    P = scene["means3D"].shape[0]
+    rb = render_bwd(W, H, st["ranges"], st["point_list"], st["bg"], st["means2D"], st["conic_opacity"], st["rgb"],
+                    st["final_T"], st["n_contrib"], dL_dpix, P, tile_step)
+    pb = preprocess_bwd(scene["means3D"], st["radii"], scene["shs"], st["clamped"], scene["scales"], scene["rotations"],
+                        scale_modifier, st["cov3D"], cam["viewmatrix"], cam["projmatrix"], cam["campos"], W, H,
+                        cam["tanfovx"], cam["tanfovy"], degree, rb["dL_dmean2D"], rb["dL_dconic"], rb["dL_dcolors"])
+    return dict(means2D=rb["dL_dmean2D"], colors=rb["dL_dcolors"], opacity=rb["dL_dopacity"].reshape(P, 1),
+                means3D=pb["dL_dmeans3D"], cov3D=pb["dL_dcov3D"], sh=pb["dL_dsh"], scales=pb["dL_dscales"],
+                rotations=pb["dL_drots"], conic=rb["dL_dconic"])
+
+
+def compute_relocation(opacity_old, scale_old, N, binoms, n_max):
+    o = _f32(opacity_old).reshape(-1)
+    P = o.shape[0]
+    new_o = np.zeros(P, np.float32)
+    new_s = np.zeros(3 * P, np.float32)
+    lib().orc_compute_relocation(P, o, _f32(scale_old).reshape(-1), np.ascontiguousarray(N, np.int32), _f32(binoms).reshape(-1),
+                                 n_max, new_o, new_s)
+    return new_o, new_s
+
+
+def add_noise(xyz, scaling_raw, rotation_raw, opacity_raw, noise, lr_scale):
+    out = _f32(xyz).copy()
+    lib().orc_add_noise(out.shape[0], out, _f32(scaling_raw), _f32(rotation_raw), _f32(opacity_raw).reshape(-1), _f32(noise),
+                        lr_scale)
+    return out
+
+
+def binoms_table(n_max=51):
+    """C(n,k) as float32, the table utils/reloc_utils.py:7-11 builds with scipy.special.comb."""
+    from scipy.special import comb
+    t = np.zeros((n_max, n_max), np.float32)
+    for n in range(n_max):
+        for k in range(n + 1):
+            t[n, k] = comb(n, k)
+    return t

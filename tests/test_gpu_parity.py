@@ -1,0 +1,473 @@
+"""GPU parity tests (run on the B200 box with -m gpu). Everything goes through the reference-facing Python API /
+the C ABI of lib3dgs_mcmc_b200.so and is compared with
+
+  * the reference's own CUDA rasterizer (oracle/_ref/libref_dgr.so — the golden implementation): bit-exact tile
+    keys, sort order, tile ranges, radii, per-Gaussian state, n_contrib, final_T and image; gradients to the
+    north-star tolerance (relative L2 <= 1e-3; atomics reorder sums),
+  * the committed golden vectors generated from that reference (tests/golden),
+  * the CPU oracle (oracle/oracle_cpu.c) on the same seeded inputs,
+  * size-independent properties at BASELINE.json's full size (3M Gaussians, 1920x1080).
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import helpers
+import gs_synth
+
+pytestmark = pytest.mark.gpu
+
+GRAD_TOL = 1e-3       # north_star: gradient relative L2 <= 1e-3
+PIX_TOL = 1e-4        # north_star: max abs pixel error <= 1e-4
+GRAD_NAMES = ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def native():
+    from diff_gaussian_rasterization import _native
+    return _native
+
+
+def ref():
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        pytest.fail("oracle/_ref/libref_dgr.so did not travel with the snapshot (build it with `make -C oracle ref`)")
+    return ref_cuda
+
+
+def assert_forward_bit_exact(rep):
+    bad = {k: v for k, v in rep.items() if k.endswith("mismatch") and v}
+    assert not bad, bad
+    assert rep["R"] == rep["R_ref"]
+    assert rep["image_max_abs"] == 0.0
+    assert rep["sort_error_flag"] == 0
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# vs the reference CUDA implementation
+# --------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kind,P,W,H,rad,fovx", [
+    ("cube", 2000, 64, 48, 4.03, 0.6911),          # tiny, image not a multiple of 16 in y
+    ("cube", 20000, 250, 130, 4.03, 0.6911),       # ragged in both directions
+    ("cube", 100000, 800, 800, 4.03, 0.6911),      # BASELINE config 1 shape
+    ("garden", 300000, 1297, 840, 6.0, 1.2),       # BASELINE config 3 image size
+])
+def test_forward_bit_exact_and_gradients_vs_reference(kind, P, W, H, rad, fovx):
+    ref()
+    scene, cam = helpers.make_case(kind, P, W, H, seed=0, cam_radius=rad, fovx=fovx)
+    rep = helpers.compare_with_reference(scene, cam)
+    assert_forward_bit_exact(rep)
+    for n in GRAD_NAMES:
+        assert rep[f"grad_{n}_finite"]
+        assert rep[f"grad_{n}_rel_l2"] < GRAD_TOL, (n, rep[f"grad_{n}_rel_l2"])
+
+
+@pytest.mark.parametrize("degree", [0, 1, 2])
+def test_lower_sh_degrees_vs_reference(degree):
+    ref()
+    scene, cam = helpers.make_case("cube", 5000, 128, 96, seed=degree + 10)
+    scene["scales"] = (scene["scales"] * 5).astype(np.float32)
+    rep = helpers.compare_with_reference(scene, cam, degree=degree, bg=(1.0, 0.5, 0.25))
+    assert_forward_bit_exact(rep)
+    for n in GRAD_NAMES:
+        assert rep[f"grad_{n}_rel_l2"] < GRAD_TOL, n
+
+
+def _run_pair(args, bwd_builder):
+    """Run ours and the reference with identical positional args; return (ours_fwd, ref_fwd, ours_grads, ref_grads)."""
+    C, R_ = native(), ref()
+    R, color, radii, geom, binning, img, is_used = C.rasterize_gaussians(*args)
+    torch.cuda.synchronize()
+    Rr, color_r, radii_r, used_r = R_.forward(*args)
+    torch.cuda.synchronize()
+    ours = C.rasterize_gaussians_backward(*bwd_builder(radii, geom, R, binning, img))
+    b = bwd_builder(radii_r, None, Rr, None, None)
+    theirs = R_.backward(*b[:16], Rr)
+    torch.cuda.synchronize()
+    return (R, color, radii, is_used), (Rr, color_r, radii_r, used_r), dict(zip(GRAD_NAMES, ours)), theirs
+
+
+def test_precomputed_colors_and_covariance_paths_vs_reference():
+    scene, cam = helpers.make_case("cube", 6000, 160, 120, seed=21)
+    scene["scales"] = (scene["scales"] * 5).astype(np.float32)
+    s, c = helpers.torch_inputs(scene, cam, dev(), (0.2, 0.1, 0.0))
+    g = torch.Generator(device="cpu").manual_seed(3)
+    colors = torch.rand((6000, 3), generator=g).to(dev())
+    # covariance from the reference's python path: Sigma = (R S)(R S)^T, upper triangle
+    q = s["rotations"]
+    w, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    Rm = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y), 2 * (x * y + w * z),
+                      1 - 2 * (x * x + z * z), 2 * (y * z - w * x), 2 * (x * z - w * y), 2 * (y * z + w * x),
+                      1 - 2 * (x * x + y * y)], 1).view(-1, 3, 3)
+    L = Rm @ torch.diag_embed(s["scales"])
+    Sig = L @ L.transpose(1, 2)
+    cov = torch.stack([Sig[:, 0, 0], Sig[:, 0, 1], Sig[:, 0, 2], Sig[:, 1, 1], Sig[:, 1, 2], Sig[:, 2, 2]], 1).contiguous()
+    args = helpers.native_forward_args(s, c, 3, colors_precomp=colors, cov3D_precomp=cov)
+    dL = torch.randn((3, 120, 160), generator=g).to(dev())
+    e = torch.empty(0)
+
+    def bwd(radii, geom, R, binning, img):
+        return (c["bg"], s["means3D"], radii, colors, e, e, 1.0, cov, c["viewmatrix"], c["projmatrix"], c["tanfovx"],
+                c["tanfovy"], dL, e, 3, c["campos"], geom, R, binning, img, False)
+    o, r, go, gr = _run_pair(args, bwd)
+    assert o[0] == r[0] and torch.equal(o[2], r[2]) and torch.equal(o[3], r[3])
+    assert torch.equal(o[1], r[1])
+    for n in ("means2D", "colors", "opacity", "means3D", "cov3D"):
+        assert helpers.rel_l2(go[n], gr[n]) < GRAD_TOL, n
+    assert go["sh"].shape == (6000, 0, 3)
+    assert float(go["scales"].abs().max()) == 0.0 and float(go["rotations"].abs().max()) == 0.0
+
+
+def test_scale_modifier_and_nonunit_quaternions_vs_reference():
+    scene, cam = helpers.make_case("cube", 4000, 96, 96, seed=33)
+    scene["scales"] = (scene["scales"] * 4).astype(np.float32)
+    scene["rotations"] = (scene["rotations"] * np.linspace(0.5, 1.5, 4000, dtype=np.float32)[:, None]).astype(np.float32)
+    s, c = helpers.torch_inputs(scene, cam, dev())
+    args = helpers.native_forward_args(s, c, 3, scale_modifier=1.7)
+    g = torch.Generator(device="cpu").manual_seed(4)
+    dL = torch.randn((3, 96, 96), generator=g).to(dev())
+    e = torch.empty(0)
+
+    def bwd(radii, geom, R, binning, img):
+        return (c["bg"], s["means3D"], radii, e, s["scales"], s["rotations"], 1.7, e, c["viewmatrix"], c["projmatrix"],
+                c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], geom, R, binning, img, False)
+    o, r, go, gr = _run_pair(args, bwd)
+    assert o[0] == r[0] and torch.equal(o[1], r[1]) and torch.equal(o[2], r[2])
+    for n in GRAD_NAMES:
+        assert helpers.rel_l2(go[n], gr[n]) < GRAD_TOL, n
+
+
+def test_duplicate_gaussians_keep_index_order_like_reference():
+    """MCMC relocation copies positions exactly, so equal (tile, depth) keys are common; the stable sort must keep
+    Gaussian-index order for them (bit-exact sorted ids)."""
+    ref()
+    scene, cam = helpers.make_case("cube", 3000, 96, 64, seed=5)
+    scene["scales"] = (scene["scales"] * 5).astype(np.float32)
+    for k in ("means3D",):
+        scene[k][1500:] = scene[k][:1500]        # every position appears twice
+    rep = helpers.compare_with_reference(scene, cam)
+    assert_forward_bit_exact(rep)
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# edge cases
+# --------------------------------------------------------------------------------------------------------------------
+def test_empty_input():
+    C = native()
+    cam = gs_synth.to_torch(gs_synth.orbit_cameras(1, 4.0, 40, 24, 0.7)[0], dev())
+    e = torch.empty(0)
+    z3 = torch.zeros((0, 3), device=dev())
+    out = C.rasterize_gaussians(torch.ones(3, device=dev()), z3, e, torch.zeros((0, 1), device=dev()), z3,
+                                torch.zeros((0, 4), device=dev()), 1.0, e, cam["viewmatrix"], cam["projmatrix"],
+                                cam["tanfovx"], cam["tanfovy"], 24, 40, torch.zeros((0, 16, 3), device=dev()), 3,
+                                cam["campos"], False, False)
+    assert out[0] == 0 and out[1].shape == (3, 24, 40) and float(out[1].abs().max()) == 0.0   # zeros like the reference
+    assert out[2].numel() == 0 and out[6].numel() == 0
+
+
+def test_all_culled_renders_background():
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    scene, cam = helpers.make_case("cube", 500, 50, 34, seed=8)
+    scene["means3D"][:, :] = np.array(cam["campos"]) * 3.0     # far behind the camera
+    s, c = helpers.torch_inputs(scene, cam, dev(), (0.3, 0.6, 0.9))
+    st = GaussianRasterizationSettings(34, 50, c["tanfovx"], c["tanfovy"], c["bg"], 1.0, c["viewmatrix"], c["projmatrix"], 3,
+                                       c["campos"], False, True)   # debug=True exercises the sync path
+    m = s["means3D"].clone().requires_grad_(True)
+    img, radii, used = GaussianRasterizer(st)(m, torch.zeros_like(m, requires_grad=True), s["opacities"], shs=s["shs"],
+                                              scales=s["scales"], rotations=s["rotations"])
+    assert int(radii.abs().sum()) == 0 and int(used.sum()) == 0
+    assert torch.allclose(img, c["bg"][:, None, None].expand(3, 34, 50))
+    img.sum().backward()
+    assert float(m.grad.abs().max()) == 0.0
+
+
+def test_single_isotropic_splat_known_answer():
+    """One isotropic Gaussian on the optical axis: the centre pixel gets alpha = min(0.99, o * exp(-0.5 d^2 / s2))."""
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    W = H = 33
+    cam = gs_synth.look_at_camera((0, 0, -4.0), (0, 0, 0), W, H, 0.8)
+    c = gs_synth.to_torch(cam, dev())
+    sigma, opac = 0.05, 0.7
+    m = torch.zeros((1, 3), device=dev())
+    sh = torch.zeros((1, 16, 3), device=dev())
+    sh[0, 0] = torch.tensor([0.5, -0.2, 1.0]) / 0.28209479177387814      # rgb = sh*C0 + 0.5 -> (1.0, 0.3, 1.5)
+    st = GaussianRasterizationSettings(H, W, c["tanfovx"], c["tanfovy"], torch.zeros(3, device=dev()), 1.0, c["viewmatrix"],
+                                       c["projmatrix"], 0, c["campos"], False, False)
+    img, radii, used = GaussianRasterizer(st)(m, torch.zeros_like(m), torch.full((1, 1), opac, device=dev()), shs=sh,
+                                              scales=torch.full((1, 3), sigma, device=dev()),
+                                              rotations=torch.tensor([[1.0, 0, 0, 0]], device=dev()))
+    focal = W / (2 * cam["tanfovx"])
+    var_px = (sigma * focal / 4.0) ** 2 + 0.3
+    # projected mean: ((0 + 1) * W - 1) / 2 = 16 -> pixel (16,16) sits exactly on it
+    # isotropic: both eigenvalues are var_px, and the reference floors the discriminant at 0.1
+    assert int(radii[0]) == int(np.ceil(3 * np.sqrt(var_px + np.sqrt(0.1)))) and int(used[0]) == 1
+    assert torch.allclose(img[:, 16, 16], torch.tensor([1.0, 0.3, 1.5], device=dev()) * opac, rtol=1e-5)
+    a1 = opac * np.exp(-0.5 / var_px)
+    assert abs(float(img[0, 16, 17]) - a1) < 1e-5 and abs(float(img[0, 17, 16]) - a1) < 1e-5
+
+
+def test_saturating_stack_early_termination_matches_reference():
+    ref()
+    scene, cam = helpers.make_case("cube", 4000, 48, 48, seed=13, fovx=0.25)
+    scene["scales"] = (scene["scales"] * 12).astype(np.float32)
+    scene["opacities"] = np.clip(scene["opacities"] * 1.6, 0, 0.999).astype(np.float32)
+    rep = helpers.compare_with_reference(scene, cam)
+    assert_forward_bit_exact(rep)
+    for n in GRAD_NAMES:
+        assert rep[f"grad_{n}_rel_l2"] < GRAD_TOL, n
+
+
+def test_non_default_stream_and_determinism():
+    C = native()
+    scene, cam = helpers.make_case("cube", 30000, 320, 200, seed=17)
+    scene["scales"] = (scene["scales"] * 3).astype(np.float32)
+    s, c = helpers.torch_inputs(scene, cam, dev())
+    args = helpers.native_forward_args(s, c, 3)
+    a = C.rasterize_gaussians(*args)
+    torch.cuda.synchronize()
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        b = C.rasterize_gaussians(*args)
+    st.synchronize()
+    assert a[0] == b[0] and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]) and torch.equal(a[6], b[6])
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# golden vectors (from the reference) and the CPU oracle
+# --------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("path", sorted(p for p in glob.glob(os.path.join(GOLD, "*.npz")) if "relocation" not in p))
+def test_against_golden_vectors(path):
+    C = native()
+    z = np.load(path)
+    scene = {k[3:]: z[k] for k in z.files if k.startswith("in_")}
+    cam = {k[4:]: (z[k] if z[k].ndim else z[k].item()) for k in z.files if k.startswith("cam_")}
+    deg = int(z["degree"])
+    s, c = helpers.torch_inputs(scene, cam, dev(), tuple(z["bg"].tolist()))
+    R, color, radii, geom, binning, img, is_used = C.rasterize_gaussians(*helpers.native_forward_args(s, c, deg))
+    P, W, H = scene["means3D"].shape[0], cam["image_width"], cam["image_height"]
+    assert R == int(z["R"])
+    assert np.array_equal(radii.cpu().numpy(), z["radii"]) and np.array_equal(is_used.cpu().numpy(), z["is_used"])
+    assert np.array_equal(color.cpu().numpy(), z["color"])
+    f = lambda w, dt: C.debug_fetch(w, P, R, W, H, geom, binning, img, dt).cpu().numpy()
+    assert np.array_equal(f(12, torch.int64), z["st_keys"]) and np.array_equal(f(10, torch.int32), z["st_point_list"])
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    assert np.array_equal(f(22, torch.int32).reshape(-1, 2)[:tiles], z["st_ranges"][:tiles])
+    assert np.array_equal(f(21, torch.int32), z["st_n_contrib"])
+    dL = torch.from_numpy(z["dL_dpix"]).to(dev())
+    e = torch.empty(0)
+    grads = C.rasterize_gaussians_backward(c["bg"], s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e,
+                                           c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], dL, s["shs"], deg,
+                                           c["campos"], geom, R, binning, img, False)
+    for n, gten in zip(GRAD_NAMES, grads):
+        assert helpers.rel_l2(gten, torch.from_numpy(z[f"grad_{n}"]).to(dev())) < GRAD_TOL, n
+
+
+def test_against_cpu_oracle():
+    from oracle import oracle
+    C = native()
+    scene, cam = helpers.make_case("garden", 40000, 400, 256, seed=9, cam_radius=6.0, fovx=1.2)
+    s, c = helpers.torch_inputs(scene, cam, dev(), (0.1, 0.2, 0.3))
+    P, W, H = 40000, 400, 256
+    R, color, radii, geom, binning, img, is_used = C.rasterize_gaussians(*helpers.native_forward_args(s, c, 3))
+    f = lambda w, dt: C.debug_fetch(w, P, R, W, H, geom, binning, img, dt).cpu().numpy()
+    # binning on OUR float outputs must be bit-exact in the oracle
+    b = oracle.bin(f(3, torch.float32).reshape(P, 2), f(0, torch.float32), radii.cpu().numpy(), f(7, torch.int32).astype(np.uint32), W, H)
+    assert b["R"] == R
+    assert np.array_equal(b["keys"], f(12, torch.int64).astype(np.uint64))
+    assert np.array_equal(b["point_list"], f(10, torch.int32).astype(np.uint32))
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    assert np.array_equal(b["ranges"], f(22, torch.int32).reshape(-1, 2)[:tiles].astype(np.uint32))
+    # whole pipeline in the oracle vs ours
+    st = oracle.forward(scene, cam, bg=(0.1, 0.2, 0.3))
+    assert int((st["radii"] != radii.cpu().numpy()).sum()) <= P // 1000
+    err = np.abs(st["color"] - color.cpu().numpy())
+    assert int((err > PIX_TOL).sum()) <= W * H // 500, float(err.max())
+    dLn = np.random.default_rng(1).standard_normal((3, H, W)).astype(np.float32)
+    og = oracle.backward(scene, cam, st, dLn)
+    e = torch.empty(0)
+    grads = C.rasterize_gaussians_backward(c["bg"], s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e,
+                                           c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"],
+                                           torch.from_numpy(dLn).to(dev()), s["shs"], 3, c["campos"], geom, R, binning, img, False)
+    for n, gten in zip(GRAD_NAMES, grads):
+        # the oracle's forward state differs by a few threshold flips, so this is looser than vs the reference
+        assert helpers.rel_l2(gten, torch.from_numpy(og[n]).to(dev())) < 2e-2, n
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# public autograd API
+# --------------------------------------------------------------------------------------------------------------------
+def test_autograd_api_returns_all_gradients():
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    C = native()
+    scene, cam = helpers.make_case("cube", 8000, 128, 128, seed=2)
+    scene["scales"] = (scene["scales"] * 4).astype(np.float32)
+    s, c = helpers.torch_inputs(scene, cam, dev())
+    p = {k: s[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    m2d = torch.zeros_like(p["means3D"], requires_grad=True)
+    st = GaussianRasterizationSettings(128, 128, c["tanfovx"], c["tanfovy"], c["bg"], 1.0, c["viewmatrix"], c["projmatrix"], 3,
+                                       c["campos"], False, False)
+    rast = GaussianRasterizer(st)
+    img, radii, used = rast(means3D=p["means3D"], means2D=m2d, shs=p["shs"], opacities=p["opacities"], scales=p["scales"],
+                            rotations=p["rotations"])
+    assert img.shape == (3, 128, 128) and radii.dtype == torch.int32 and used.dtype == torch.int32
+    g = torch.Generator(device="cpu").manual_seed(1)
+    dL = torch.randn((3, 128, 128), generator=g).to(dev())
+    (img * dL).sum().backward()
+    R, color, radii2, geom, binning, im, used2 = C.rasterize_gaussians(*helpers.native_forward_args(s, c, 3))
+    e = torch.empty(0)
+    raw = dict(zip(GRAD_NAMES, C.rasterize_gaussians_backward(
+        c["bg"], s["means3D"], radii2, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"], c["tanfovx"],
+        c["tanfovy"], dL, s["shs"], 3, c["campos"], geom, R, binning, im, False)))
+    assert torch.equal(img.detach(), color)
+    for a, n in ((p["means3D"].grad, "means3D"), (m2d.grad, "means2D"), (p["shs"].grad, "sh"), (p["opacities"].grad, "opacity"),
+                 (p["scales"].grad, "scales"), (p["rotations"].grad, "rotations")):
+        assert a is not None and helpers.rel_l2(a, raw[n]) < 1e-4, n
+    vis = rast.markVisible(s["means3D"])
+    assert vis.dtype == torch.bool and torch.equal(vis, ref().mark_visible(s["means3D"], c["viewmatrix"], c["projmatrix"]))
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# MCMC update kernels
+# --------------------------------------------------------------------------------------------------------------------
+def test_compute_relocation_bit_exact_vs_reference_and_golden():
+    from diff_gaussian_rasterization import compute_relocation
+    z = np.load(os.path.join(GOLD, "relocation.npz"))
+    t = lambda a: torch.from_numpy(a).to(dev())
+    o, s = compute_relocation(t(z["opacity_old"]), t(z["scale_old"]), t(z["N"]).long(), t(z["binoms"]), 51)
+    assert np.array_equal(o.cpu().numpy(), z["opacity_new"]) and np.array_equal(s.cpu().numpy(), z["scale_new"])
+    # larger random batch against the live reference kernel, every N including the clamp edges 1 and 50
+    rng = np.random.default_rng(3)
+    K = 20000
+    op = t(rng.uniform(0.005, 0.999, K).astype(np.float32))
+    sc = t(np.exp(rng.normal(-4, 1, (K, 3))).astype(np.float32))
+    N = t(rng.integers(1, 51, K).astype(np.int32))
+    o1, s1 = compute_relocation(op, sc, N, t(z["binoms"]), 51)
+    o2, s2 = ref().compute_relocation(op, sc, N, t(z["binoms"]), 51)
+    torch.cuda.synchronize()
+    assert torch.equal(o1, o2) and torch.equal(s1, s2)
+    assert s1.shape == (3 * K,)
+
+
+def test_reloc_utils_call_pattern():
+    """utils/reloc_utils.py:13-15: clamp N in place to [1, 50], pass an int64 tensor, reshape the flat scale."""
+    from diff_gaussian_rasterization import compute_relocation
+    from oracle import oracle
+    binoms = torch.from_numpy(oracle.binoms_table(51)).to(dev())
+    N = torch.tensor([0, 1, 7, 50, 400], device=dev())
+    N.clamp_(min=1, max=50)
+    op = torch.tensor([0.5, 0.5, 0.2, 0.9, 0.9], device=dev())
+    sc = torch.full((5, 3), 0.01, device=dev())
+    o, s = compute_relocation(op, sc, N, binoms, 51)
+    oo, so = oracle.compute_relocation(op.cpu().numpy(), sc.cpu().numpy(), N.cpu().numpy().astype(np.int32), binoms.cpu().numpy(), 51)
+    assert np.allclose(o.cpu().numpy(), oo, rtol=2e-6, atol=2e-7) and np.allclose(s.reshape(-1, 3).cpu().numpy(), so.reshape(-1, 3), rtol=2e-5)
+    assert float(o[0]) == float(o[1]) == 0.5
+
+
+def test_add_noise_vs_oracle_and_inline_torch():
+    from diff_gaussian_rasterization import add_noise
+    from oracle import oracle
+    rng = np.random.default_rng(5)
+    P = 100003
+    xyz = rng.standard_normal((P, 3)).astype(np.float32)
+    sc = rng.normal(-3, 0.7, (P, 3)).astype(np.float32)
+    rot = rng.standard_normal((P, 4)).astype(np.float32)
+    op = rng.normal(-4, 3, (P, 1)).astype(np.float32)
+    noise = rng.standard_normal((P, 3)).astype(np.float32)
+    lr = 5e4 * 1.6e-4
+    t = lambda a: torch.from_numpy(a).to(dev())
+    got = add_noise(t(xyz), t(sc), t(rot), t(op), lr, noise=t(noise)).cpu().numpy()
+    want = oracle.add_noise(xyz, sc, rot, op, noise, lr)
+    assert np.allclose(got, want, rtol=2e-5, atol=1e-6)
+    # the reference's inline torch code on the GPU (train_static.py:132-140)
+    r = t(rot)
+    q = r / torch.sqrt((r * r).sum(1))[:, None]
+    w, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    Rm = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y), 2 * (x * y + w * z),
+                      1 - 2 * (x * x + z * z), 2 * (y * z - w * x), 2 * (x * z - w * y), 2 * (y * z + w * x),
+                      1 - 2 * (x * x + y * y)], 1).view(P, 3, 3)
+    L = Rm @ torch.diag_embed(torch.exp(t(sc)))
+    cov = L @ L.transpose(1, 2)
+    gate = 1 / (1 + torch.exp(-100 * ((1 - torch.sigmoid(t(op))) - 0.995)))
+    inline = t(xyz) + torch.bmm(cov, (t(noise) * gate * lr).unsqueeze(-1)).squeeze(-1)
+    assert np.allclose(got, inline.cpu().numpy(), rtol=1e-4, atol=1e-5)
+
+
+def test_add_noise_in_kernel_generator_statistics():
+    from diff_gaussian_rasterization import add_noise
+    P = 400000
+    xyz = torch.zeros((P, 3), device=dev())
+    sc = torch.zeros((P, 3), device=dev())                      # exp(0) = 1 -> Sigma = I
+    rot = torch.tensor([[1.0, 0, 0, 0]], device=dev()).repeat(P, 1)
+    op = torch.full((P, 1), -20.0, device=dev())                # gate -> sigmoid(0.5) = 0.622
+    add_noise(xyz, sc, rot, op, 1.0, noise=None, seed=1234, offset=0)
+    gate = 1 / (1 + np.exp(-100 * ((1 - 1 / (1 + np.exp(20.0))) - 0.995)))
+    n = (xyz / gate).cpu().numpy()
+    assert abs(n.mean()) < 0.01 and abs(n.std() - 1.0) < 0.01 and abs(np.corrcoef(n[:, 0], n[:, 1])[0, 1]) < 0.01
+    xyz2 = torch.zeros((P, 3), device=dev())
+    add_noise(xyz2, sc, rot, op, 1.0, noise=None, seed=1234, offset=0)
+    assert torch.equal(xyz, xyz2)                                # counter-based: reproducible
+    add_noise(xyz2, sc, rot, op, 1.0, noise=None, seed=1234, offset=1)
+    assert not torch.equal(xyz * 2, xyz2)
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# size-independent properties at BASELINE's full size
+# --------------------------------------------------------------------------------------------------------------------
+def test_full_size_properties_3M_1080p():
+    C = native()
+    P, W, H = 3_000_000, 1920, 1080
+    scene, cam = helpers.make_case("garden", P, W, H, seed=0, cam_radius=6.0, fovx=1.2, ncams=16)
+    s, c = helpers.torch_inputs(scene, cam, dev())
+    args = helpers.native_forward_args(s, c, 3)
+    R, color, radii, geom, binning, img, is_used = C.rasterize_gaussians(*args)
+    f = lambda w, dt: C.debug_fetch(w, P, R, W, H, geom, binning, img, dt)
+    assert int(f(30, torch.int32)[0]) == 0
+    tiles_touched, offsets = f(7, torch.int32).long(), f(8, torch.int32).long()
+    assert int(tiles_touched.sum()) == R and int(offsets[-1]) == R
+    assert torch.equal(torch.cumsum(tiles_touched, 0), offsets)
+    keys, ids = f(12, torch.int64), f(10, torch.int32).long()
+    assert bool((keys[1:] >= keys[:-1]).all())                      # sortedness
+    assert bool(((keys[1:] != keys[:-1]) | (ids[1:] > ids[:-1])).all())   # stability: ties keep index order
+    # the sorted list is a permutation of the emitted instances: per-Gaussian multiplicities match tiles_touched
+    assert torch.equal(torch.bincount(ids, minlength=P), tiles_touched)
+    depth_bits = f(0, torch.float32).view(torch.int32).long()
+    assert torch.equal(keys & 0xFFFFFFFF, depth_bits[ids] & 0xFFFFFFFF)
+    tile_of = keys >> 32
+    ntiles = ((W + 15) // 16) * ((H + 15) // 16)
+    ranges = f(22, torch.int32).view(-1, 2)[:ntiles].long()
+    cnt = torch.bincount(tile_of, minlength=ntiles)
+    assert torch.equal(ranges[:, 1] - ranges[:, 0], cnt)             # ranges partition the list by tile
+    nz = cnt > 0
+    assert torch.equal(tile_of[ranges[nz, 0]], torch.nonzero(nz).flatten())
+    assert bool((is_used <= (radii > 0).int()).all())
+    assert bool(torch.isfinite(color).all()) and float(color.min()) >= 0.0
+    n_contrib = f(21, torch.int32).view(H, W).long()
+    tile_len = torch.zeros((H + 15) // 16 * 16, (W + 15) // 16 * 16, dtype=torch.long, device=dev())
+    tl = cnt.view((H + 15) // 16, (W + 15) // 16)
+    tile_len = tl.repeat_interleave(16, 0).repeat_interleave(16, 1)[:H, :W]
+    assert bool((n_contrib <= tile_len).all())
+    # determinism of the forward (no atomics on the image path): second run is bit-identical
+    R2, color2, radii2, *_ = C.rasterize_gaussians(*args)
+    assert R2 == R and torch.equal(color, color2) and torch.equal(radii, radii2)
+    # backward is linear in dL/dpix
+    g = torch.Generator(device="cpu").manual_seed(2)
+    dL = torch.randn((3, H, W), generator=g).to(dev())
+    e = torch.empty(0)
+    bargs = lambda d: (c["bg"], s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+                       c["tanfovx"], c["tanfovy"], d, s["shs"], 3, c["campos"], geom, R, binning, img, False)
+    g1 = C.rasterize_gaussians_backward(*bargs(dL))
+    g2 = C.rasterize_gaussians_backward(*bargs(dL * 2))
+    for n, a, b in zip(GRAD_NAMES, g1, g2):
+        assert bool(torch.isfinite(a).all()), n
+        assert helpers.rel_l2(b, a * 2) < 1e-4, n
+    # culled Gaussians receive exactly zero gradient everywhere
+    culled = radii == 0
+    for a in g1:
+        assert float(a[culled].abs().max()) == 0.0

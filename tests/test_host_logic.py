@@ -1,0 +1,143 @@
+"""Host-side behaviour of the drop-in Python API (no GPU): argument validation mirrors the reference wrapper
+(diff_gaussian_rasterization/__init__.py:171-220), there is no CPU fallback, the DP gradient arena and the
+synthetic camera conventions are what the rest of the suite assumes."""
+import math
+import os
+import socket
+import subprocess
+import sys
+import textwrap
+
+import numpy as np
+import pytest
+import torch
+
+import gs_synth
+from diff_gaussian_rasterization import (GaussianRasterizationSettings, GaussianRasterizer, compute_relocation,
+                                         rasterize_gaussians)
+from diff_gaussian_rasterization import _native, dp
+
+
+def settings(W=32, H=16):
+    cam = gs_synth.orbit_cameras(1, 4.0, W, H, 0.7)[0]
+    return GaussianRasterizationSettings(H, W, cam["tanfovx"], cam["tanfovy"], torch.zeros(3), 1.0,
+                                         torch.from_numpy(cam["viewmatrix"]), torch.from_numpy(cam["projmatrix"]), 3,
+                                         torch.from_numpy(cam["campos"]), False, False)
+
+
+def test_settings_fields_match_reference_order():
+    assert GaussianRasterizationSettings._fields == (
+        "image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix", "projmatrix",
+        "sh_degree", "campos", "prefiltered", "debug")
+
+
+def test_exactly_one_colour_source_and_one_covariance_source():
+    r = GaussianRasterizer(settings())
+    P = 4
+    m, o = torch.zeros(P, 3), torch.ones(P, 1)
+    sh, col = torch.zeros(P, 16, 3), torch.zeros(P, 3)
+    sc, rot, cov = torch.ones(P, 3), torch.ones(P, 4), torch.zeros(P, 6)
+    with pytest.raises(Exception, match="SHs or precomputed colors"):
+        r(m, m, o, shs=None, colors_precomp=None, scales=sc, rotations=rot)
+    with pytest.raises(Exception, match="SHs or precomputed colors"):
+        r(m, m, o, shs=sh, colors_precomp=col, scales=sc, rotations=rot)
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed 3D covariance"):
+        r(m, m, o, shs=sh, scales=sc, rotations=None)
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed 3D covariance"):
+        r(m, m, o, shs=sh, scales=sc, rotations=rot, cov3D_precomp=cov)
+
+
+def test_no_cpu_fallback():
+    r = GaussianRasterizer(settings())
+    P = 4
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        r(torch.zeros(P, 3), torch.zeros(P, 3), torch.ones(P, 1), shs=torch.zeros(P, 16, 3), scales=torch.ones(P, 3),
+          rotations=torch.ones(P, 4))
+    with pytest.raises(RuntimeError, match="num_points, 3"):
+        rasterize_gaussians(torch.zeros(P, 4), torch.zeros(P, 3), torch.zeros(P, 16, 3), torch.Tensor([]), torch.ones(P, 1),
+                            torch.ones(P, 3), torch.ones(P, 4), torch.Tensor([]), settings())
+
+
+def test_compute_relocation_empty_is_a_noop_without_gpu():
+    o, s = compute_relocation(torch.zeros(0), torch.zeros(0, 3), torch.zeros(0, dtype=torch.int64), torch.zeros(51, 51), 51)
+    assert o.shape == (0,) and s.shape == (0,)
+
+
+def test_gradient_arena_layout():
+    a = dp.GradientArena(7, 16, "cpu")
+    assert a.floats_per_gaussian() == 59
+    bufs = a.backward_buffers()
+    assert set(bufs) == {"means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations"}
+    for name in ("means3D", "sh", "opacity", "scales", "rotations"):
+        assert bufs[name].is_contiguous()
+        bufs[name].fill_(1.0)
+    assert float(a.flat.sum()) == 7 * 59          # the five parameter gradients tile the arena exactly
+    assert dp.shard_views(8, 1, 4) == [1, 5]
+    assert a.all_reduce() is a.flat                # no process group: no-op
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def test_arena_all_reduce_world_size_2_gloo(tmp_path):
+    """The N>1 exchange step on CPU: two gloo ranks fill their arenas differently; after all_reduce both hold the sum."""
+    script = tmp_path / "worker.py"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script.write_text(textwrap.dedent(f"""
+        import os, sys
+        sys.path.insert(0, {os.path.join(root, '3dgs-mcmc_b200')!r})
+        import torch, torch.distributed as dist
+        from diff_gaussian_rasterization import dp
+        dist.init_process_group("gloo")
+        r = dist.get_rank()
+        a = dp.GradientArena(11, 16, "cpu")
+        for i, (name, v) in enumerate(sorted(a.views.items())):
+            v.fill_(float((r + 1) * (i + 1)))
+        a.all_reduce()
+        for i, (name, v) in enumerate(sorted(a.views.items())):
+            assert torch.all(v == 3.0 * (i + 1)), name
+        a.all_reduce(average=True)
+        for i, (name, v) in enumerate(sorted(a.views.items())):
+            assert torch.all(v == 3.0 * (i + 1)), name
+        assert dp.shard_views(6, r, 2) == [r, r + 2, r + 4]
+        dist.destroy_process_group()
+        print("rank", r, "ok")
+    """))
+    port = _free_port()
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
+                         capture_output=True, text=True, timeout=240)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "rank 0 ok" in out.stdout and "rank 1 ok" in out.stdout
+
+
+def test_camera_conventions():
+    cam = gs_synth.look_at_camera((0.0, 0.0, -4.0), (0.0, 0.0, 0.0), 64, 48, 0.8)
+    V = cam["viewmatrix"]            # transposed storage: element [4*i+j] of the transposed matrix
+    m = V.reshape(-1)
+    p = np.array([0.1, -0.2, 0.3], np.float32)
+    view = np.array([m[0] * p[0] + m[4] * p[1] + m[8] * p[2] + m[12],
+                     m[1] * p[0] + m[5] * p[1] + m[9] * p[2] + m[13],
+                     m[2] * p[0] + m[6] * p[1] + m[10] * p[2] + m[14]])
+    assert abs(view[2] - 4.3) < 1e-5            # +z is forward
+    assert np.allclose(cam["campos"], [0, 0, -4], atol=1e-6)
+    assert np.allclose(cam["projmatrix"], V @ (np.linalg.inv(V) @ cam["projmatrix"]), atol=1e-5)
+    assert math.isclose(cam["tanfovx"], math.tan(0.4), rel_tol=1e-6)
+    # aspect: tanfovy / tanfovx = H / W
+    assert math.isclose(cam["tanfovy"] / cam["tanfovx"], 48 / 64, rel_tol=1e-6)
+
+
+def test_scene_generators_are_deterministic_and_well_formed():
+    a, b = gs_synth.scene_garden(2000, seed=4), gs_synth.scene_garden(2000, seed=4)
+    for k in a:
+        assert np.array_equal(a[k], b[k]) and a[k].dtype == np.float32
+    assert a["shs"].shape == (2000, 16, 3) and a["opacities"].shape == (2000, 1)
+    assert np.allclose(np.linalg.norm(a["rotations"], axis=1), 1.0, atol=1e-5)
+    assert (a["scales"] > 0).all() and (a["opacities"] >= 0.005).all() and (a["opacities"] <= 0.99).all()
+    c = gs_synth.scene_cube(1000, seed=1)
+    assert np.abs(c["means3D"]).max() <= 1.3
