@@ -36,10 +36,10 @@ struct BwdScratch {
 
 // ---- optional per-stage timing (CUDA events on the caller's stream) and a kernel-launch counter ----
 enum Stage {
-    ST_PREPROCESS = 0, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_PACK, ST_RENDER_FWD, ST_BWD_ZERO, ST_RENDER_BWD,
+    ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_PACK, ST_RENDER_FWD, ST_BWD_ZERO, ST_RENDER_BWD,
     ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_COUNT
 };
-const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "scan", "duplicate_keys", "radix_sort", "ranges_pack",
+const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "scan", "emit_instances", "tile_sort", "ranges_pack",
                                            "render_fwd", "bwd_zero", "render_bwd", "preprocess_bwd",
                                            "compute_relocation", "add_noise"};
 struct Profiler {
@@ -62,7 +62,7 @@ inline void count_launches(int k) { g_prof.launches += (unsigned long long)k; }
 
 extern "C" {
 
-int gs_abi_version(void) { return 100; }
+int gs_abi_version(void) { return 101; }
 
 const char* gs_error_string(int code) {
     if (code == GS_OK) return "ok";
@@ -120,7 +120,7 @@ int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means
                           float scale_modifier, const float* rotations, const float* cov3D_precomp,
                           const float* viewmatrix, const float* projmatrix, const float* campos, int W, int H,
                           float tan_fovx, float tan_fovy, int prefiltered, int* radii, int* is_used, void* geom_ws,
-                          unsigned int* num_rendered_host) {
+                          unsigned int* num_rendered_host, void* count_ready_event) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return GS_ERR_ARG;
     if (P > 0 && (!means3D || !opacities || !viewmatrix || !projmatrix || !radii || !is_used || !geom_ws)) return GS_ERR_ARG;
@@ -128,6 +128,7 @@ int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means
     if (P > 0 && !cov3D_precomp && (!scales || !rotations)) return GS_ERR_ARG;
     if (P == 0) {
         if (num_rendered_host) *num_rendered_host = 0;
+        if (count_ready_event) GS_CUDA_TRY(cudaEventRecord((cudaEvent_t)count_ready_event, stream));
         return GS_OK;
     }
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
@@ -144,16 +145,24 @@ int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means
     pp.prefiltered = prefiltered;
     pp.radii = radii; pp.is_used = is_used; pp.means2D = g.means2D; pp.depths = g.depths; pp.cov3D = g.cov3D;
     pp.rgb = g.rgb; pp.conic_opacity = g.conic_opacity; pp.tiles_touched = g.tiles_touched; pp.clamped = g.clamped;
+    pp.depth_keys = g.dkeys_a; pp.num_rendered = g.num_rendered;
     prof_mark(stream, -1);
+    GS_CUDA_TRY(cudaMemsetAsync(g.num_rendered, 0, 16, stream));
     int rc = launch_preprocess_fwd(pp, stream);
     if (rc) return rc;
     prof_mark(stream, ST_PREPROCESS);
-    rc = launch_inclusive_scan(g.tiles_touched, P, g.point_offsets, g.scan_block_sums, g.num_rendered, stream);
-    if (rc) return rc;
-    prof_mark(stream, ST_SCAN);
-    count_launches(4);
+    // The instance count is known here; the host can size the binning workspace while the depth sort runs.
     if (num_rendered_host)
         GS_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, g.num_rendered, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
+    if (count_ready_event) GS_CUDA_TRY(cudaEventRecord((cudaEvent_t)count_ready_event, stream));
+    // Depth order of the Gaussians: stable sort of (depth_bits << 32 | idx) on the depth field.
+    rc = launch_radix_sort(g.dkeys_a, g.dkeys_b, (uint32_t)P, 32, kDepthSortPasses, g.dsort_scratch, g.num_rendered + 1, stream);
+    if (rc) return rc;
+    prof_mark(stream, ST_DEPTH_SORT);
+    rc = launch_inclusive_scan(g.tiles_touched, g.dkeys_a, P, g.point_offsets, g.scan_block_sums, stream);
+    if (rc) return rc;
+    prof_mark(stream, ST_SCAN);
+    count_launches(1 + 2 + kDepthSortPasses + 3);
     return GS_OK;
 }
 
@@ -173,21 +182,19 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
     if (P == 0) R = 0;
 
     int rc = GS_OK;
-    const uint64_t* keys_sorted = (passes & 1) ? b.keys_b : b.keys_a;
-    const uint32_t* vals_sorted = (passes & 1) ? b.vals_b : b.vals_a;
     prof_mark(stream, -1);
     if (P > 0) GS_CUDA_TRY(cudaMemsetAsync(b.error_flag, 0, 16, stream));
     if (R > 0) {
-        rc = launch_duplicate_keys(P, g.means2D, g.depths, g.point_offsets, radii, grid, b.keys_a, b.vals_a, stream);
+        rc = launch_emit_instances(P, g.dkeys_a, g.means2D, g.point_offsets, radii, grid, b.inst_a, stream);
         if (rc) return rc;
         prof_mark(stream, ST_DUPLICATE);
-        rc = launch_radix_sort(b.keys_a, b.keys_b, b.vals_a, b.vals_b, R, passes, b.sort_scratch, b.error_flag, stream);
+        rc = launch_radix_sort(b.inst_a, b.inst_b, R, 32, passes, b.sort_scratch, b.error_flag, stream);
         if (rc) return rc;
         prof_mark(stream, ST_SORT);
         count_launches(3 + passes);
     }
     const float* colors = colors_precomp ? colors_precomp : g.rgb;
-    rc = launch_ranges_and_pack(R, keys_sorted, vals_sorted, g.means2D, g.conic_opacity, colors, img.ranges, tiles, b.packed, stream);
+    rc = launch_ranges_and_pack(R, b.sorted(passes), g.means2D, g.conic_opacity, colors, img.ranges, tiles, b.packed, stream);
     if (rc) return rc;
     prof_mark(stream, ST_PACK);
     count_launches(R > 0 ? 2 : 1);
@@ -257,6 +264,22 @@ int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H
     return rc;
 }
 
+void* gs_host_event_create(void) {
+    cudaEvent_t ev = nullptr;
+    if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    return (void*)ev;
+}
+int gs_host_event_wait(void* event) {
+    if (!event) return GS_ERR_ARG;
+    GS_CUDA_TRY(cudaEventSynchronize((cudaEvent_t)event));
+    return GS_OK;
+}
+int gs_host_event_destroy(void* event) {
+    if (!event) return GS_OK;
+    GS_CUDA_TRY(cudaEventDestroy((cudaEvent_t)event));
+    return GS_OK;
+}
+
 int gs_mark_visible(void* stream_, int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                     unsigned char* present) {
     (void)projmatrix;  // the reference's frustum test only uses the view-space depth
@@ -296,10 +319,11 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const v
     const uint32_t tiles = tiles_of(W, H, &grid);
     const int passes = sort_passes(tiles);
     const size_t Ps = (size_t)P, Rs = (size_t)R, Npix = (size_t)W * (size_t)H;
-    if (which < 10) {
+    if (which < 10 || which == 31) {
         if (!geom_ws) return -1;
         GeomWS g = GeomWS::carve(aligned_base(geom_ws), Ps);
         switch (which) {
+            case 31: src = g.num_rendered + 1; n = 4; break;
             case 0: src = g.depths; n = Ps * 4; break;
             case 1: src = g.clamped; n = Ps; break;
             case 3: src = g.means2D; n = Ps * 8; break;
@@ -308,14 +332,33 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const v
             case 6: src = g.rgb; n = Ps * 12; break;
             case 7: src = g.tiles_touched; n = Ps * 4; break;
             case 8: src = g.point_offsets; n = Ps * 4; break;
+            case 9:  // Gaussian indices in (depth, index) order; culled ones last
+                n = Ps * 4;
+                if (dst && n > 0 && n <= max_bytes) {
+                    if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+                    if (launch_debug_low32((uint32_t)P, g.dkeys_a, (uint32_t*)dst)) return -1;
+                }
+                return (long long)n;
             default: return -1;
         }
     } else if (which < 20 || which == 30) {
         if (!binning_ws) return -1;
         BinningWS b = BinningWS::carve(aligned_base(binning_ws), Rs, passes);
+        if (which == 10 || which == 12) {
+            // Views of the sorted instance list in the reference's formats: Gaussian ids / (tile << 32 | depth_bits).
+            n = Rs * (which == 10 ? 4 : 8);
+            if (dst && n > 0 && n <= max_bytes) {
+                if (!geom_ws) return -1;
+                GeomWS g = GeomWS::carve(aligned_base(geom_ws), Ps);
+                if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+                if (launch_debug_expand(R, b.sorted(passes), g.depths, which == 12 ? (uint64_t*)dst : nullptr,
+                                        which == 10 ? (uint32_t*)dst : nullptr))
+                    return -1;
+            }
+            return (long long)n;
+        }
         switch (which) {
-            case 10: src = (passes & 1) ? b.vals_b : b.vals_a; n = Rs * 4; break;
-            case 12: src = (passes & 1) ? b.keys_b : b.keys_a; n = Rs * 8; break;
+            case 13: src = b.sorted(passes); n = Rs * 8; break;  // raw sorted instances (tile << 32 | idx)
             case 14: src = b.packed; n = Rs * sizeof(SplatRec); break;
             case 30: src = b.error_flag; n = 4; break;
             default: return -1;

@@ -32,6 +32,8 @@ struct PreprocessParams {
     float4* __restrict__ conic_opacity;
     uint32_t* __restrict__ tiles_touched;
     uint8_t* __restrict__ clamped;
+    uint64_t* __restrict__ depth_keys;   // [P] (depth_bits << 32 | idx); depth_bits = ~0 when culled
+    uint32_t* __restrict__ num_rendered; // [1] += sum of tiles_touched (zeroed by the caller)
 };
 
 struct RenderFwdParams {
@@ -91,15 +93,16 @@ struct PreprocessBwdParams {
 
 int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
-int launch_inclusive_scan(const uint32_t* in, int n, uint32_t* out, uint32_t* block_sums, uint32_t* total_out,
+int launch_inclusive_scan(const uint32_t* in, const uint64_t* order, int n, uint32_t* out, uint32_t* block_sums,
                           cudaStream_t stream);
-int launch_duplicate_keys(int P, const float2* means2D, const float* depths, const uint32_t* offsets,
-                          const int* radii, uint2 grid, uint64_t* keys, uint32_t* vals, cudaStream_t stream);
-int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, uint32_t R, int passes,
-                      char* scratch, uint32_t* error_flag, cudaStream_t stream);
-int launch_ranges_and_pack(uint32_t R, const uint64_t* keys, const uint32_t* vals, const float2* means2D,
-                           const float4* conic_opacity, const float* colors, uint2* ranges, uint32_t tiles,
-                           SplatRec* packed, cudaStream_t stream);
+int launch_emit_instances(int P, const uint64_t* depth_order, const float2* means2D, const uint32_t* offsets,
+                          const int* radii, uint2 grid, uint64_t* inst, cudaStream_t stream);
+int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, int first_bit, int passes, char* scratch,
+                      uint32_t* error_flag, cudaStream_t stream);
+int launch_ranges_and_pack(uint32_t R, const uint64_t* inst, const float2* means2D, const float4* conic_opacity,
+                           const float* colors, uint2* ranges, uint32_t tiles, SplatRec* packed, cudaStream_t stream);
+int launch_debug_expand(uint32_t R, const uint64_t* inst, const float* depths, uint64_t* keys, uint32_t* ids);
+int launch_debug_low32(uint32_t n, const uint64_t* in, uint32_t* out);
 int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream);
 int launch_render_bwd(const RenderBwdParams& p, int tiles, cudaStream_t stream);
 int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream);

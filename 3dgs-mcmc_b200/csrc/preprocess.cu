@@ -85,13 +85,12 @@ GS_DEV V3 sh_to_rgb(int deg, const V3 pos, const V3 campos, const float* __restr
     return V3(fmaxf(result.x, 0.0f), fmaxf(result.y, 0.0f), fmaxf(result.z, 0.0f));
 }
 
-__global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessParams p) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= p.P) return;
-
-    // Defaults for culled Gaussians (replaces three host-side fills).
+// One Gaussian: writes every per-Gaussian output (defaults for culled ones, replacing three host-side fills)
+// and returns tiles_touched.
+GS_DEV uint32_t preprocess_one(const PreprocessParams& p, const int idx) {
     int out_radius = 0;
     uint32_t out_tiles = 0;
+    uint32_t depth_bits = 0xffffffffu;  // culled Gaussians sort behind every visible one
     p.is_used[idx] = 0;
 
     const float3 p_orig = {p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]};
@@ -149,11 +148,28 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessPar
                 p.conic_opacity[idx] = {conic.x, conic.y, conic.z, p.opacities[idx]};
                 out_radius = (int)my_radius;
                 out_tiles = ntiles;
+                depth_bits = __float_as_uint(p_view.z);
             }
         }
     }
     p.radii[idx] = out_radius;
     p.tiles_touched[idx] = out_tiles;
+    p.depth_keys[idx] = ((uint64_t)depth_bits << 32) | (uint32_t)idx;
+    return out_tiles;
+}
+
+__global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessParams p) {
+    __shared__ uint32_t s_tiles;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (threadIdx.x == 0) s_tiles = 0;
+    __syncthreads();
+    uint32_t out_tiles = 0;
+    if (idx < p.P) out_tiles = preprocess_one(p, idx);
+    // Instance count R = sum of tiles_touched: one atomic per warp into shared memory, one per block to global.
+    const uint32_t wsum = __reduce_add_sync(0xffffffffu, out_tiles);
+    if ((threadIdx.x & 31) == 0 && wsum) atomicAdd(&s_tiles, wsum);
+    __syncthreads();
+    if (threadIdx.x == 0 && s_tiles) atomicAdd(p.num_rendered, s_tiles);
 }
 
 __global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* __restrict__ means3D,

@@ -11,6 +11,17 @@ namespace gs {
 
 constexpr size_t kAlign = 256;
 constexpr int kScanBlock = 2048;  // items per scan block (256 threads x 8)
+constexpr int kRadixBits = 8;
+constexpr int kRadixBins = 1 << kRadixBits;
+constexpr int kSortTile = 256 * 16;   // keys per sort block (256 threads x 16 keys)
+constexpr int kDepthSortPasses = 4;   // 32 depth bits, 8 per pass
+
+// Scratch of one radix sort of n keys: per-pass digit histograms, tile tickets, look-back status words.
+__host__ inline size_t radix_scratch_bytes(size_t n, int passes) {
+    const size_t ntiles = (n + kSortTile - 1) / kSortTile;
+    return align_up((size_t)passes * kRadixBins * 4, kAlign) + align_up((size_t)passes * 4 + 16, kAlign) +
+           (size_t)passes * ntiles * kRadixBins * 4 + kAlign;
+}
 
 struct Carver {
     char* base;
@@ -34,9 +45,13 @@ struct GeomWS {
     float* cov3D;             // [6P]  upper triangle of Sigma
     uint8_t* clamped;         // [P]   bit c set when channel c was clamped to 0
     uint32_t* tiles_touched;  // [P]
-    uint32_t* point_offsets;  // [P]   inclusive scan of tiles_touched
+    uint32_t* point_offsets;  // [P]   inclusive scan of tiles_touched taken in depth order
     uint32_t* scan_block_sums;  // [ceil(P/kScanBlock)+1]
-    uint32_t* num_rendered;   // [1]   device copy of R
+    uint32_t* num_rendered;   // [0] device copy of R, [1] depth-sort error flag
+    uint64_t* dkeys_a;        // [P]   (depth_bits << 32 | idx), culled Gaussians carry depth_bits = ~0; sorted in place
+    uint64_t* dkeys_b;        // [P]   ping-pong partner (4 passes: the sorted keys end up in dkeys_a)
+    char* dsort_scratch;      // radix-sort histograms / tickets / look-back status for the depth sort
+    size_t dsort_scratch_bytes;
     size_t bytes;
 
     __host__ static GeomWS carve(char* base, size_t P) {
@@ -52,6 +67,10 @@ struct GeomWS {
         g.point_offsets = c.take<uint32_t>(P);
         g.scan_block_sums = c.take<uint32_t>((P + kScanBlock - 1) / kScanBlock + 1);
         g.num_rendered = c.take<uint32_t>(4);
+        g.dkeys_a = c.take<uint64_t>(P);
+        g.dkeys_b = c.take<uint64_t>(P);
+        g.dsort_scratch_bytes = radix_scratch_bytes(P, kDepthSortPasses);
+        g.dsort_scratch = c.take<char>(g.dsort_scratch_bytes);
         g.bytes = align_up(c.off, kAlign);
         return g;
     }
@@ -87,46 +106,37 @@ struct __align__(16) SplatRec {
 };
 static_assert(sizeof(SplatRec) == 48, "SplatRec must be 48 bytes");
 
-constexpr int kRadixBits = 8;
-constexpr int kRadixBins = 1 << kRadixBits;
-constexpr int kSortTile = 256 * 16;  // keys per sort block (256 threads x 16 keys)
-
 struct BinningWS {
-    uint64_t* keys_a;   // [R] unsorted keys; ping-pong partner of keys_b
-    uint64_t* keys_b;   // [R]
-    uint32_t* vals_a;   // [R]
-    uint32_t* vals_b;   // [R]
+    uint64_t* inst_a;   // [R] instances (tile << 32 | gaussian_idx) in emission (depth) order; ping-pong partner of inst_b
+    uint64_t* inst_b;   // [R]
     SplatRec* packed;   // [R] tile-ordered records (what render fwd/bwd stream)
     uint32_t* error_flag;  // [1] set by the sort if a look-back spin ran out
     char* sort_scratch; // histograms, tile tickets, look-back status words
     size_t sort_scratch_bytes;
     size_t bytes;
-    // After the sort the sorted pairs are in (keys_a, vals_a) when `passes` is even, else (keys_b, vals_b).
+    // After the sort the instances are in inst_a when `passes` is even, else in inst_b.
     __host__ static BinningWS carve(char* base, size_t R, int passes) {
         const size_t Rp = R > 0 ? R : 1;
-        const size_t sort_tiles = (Rp + kSortTile - 1) / kSortTile;
         Carver c(base);
         BinningWS b;
         b.packed = c.take<SplatRec>(Rp);
-        b.keys_a = c.take<uint64_t>(Rp);
-        b.keys_b = c.take<uint64_t>(Rp);
-        b.vals_a = c.take<uint32_t>(Rp);
-        b.vals_b = c.take<uint32_t>(Rp);
+        b.inst_a = c.take<uint64_t>(Rp);
+        b.inst_b = c.take<uint64_t>(Rp);
         b.error_flag = c.take<uint32_t>(4);
-        b.sort_scratch_bytes = align_up((size_t)passes * kRadixBins * 4, kAlign) + align_up((size_t)passes * 4 + 16, kAlign) +
-                               (size_t)passes * sort_tiles * kRadixBins * 4 + kAlign;
+        b.sort_scratch_bytes = radix_scratch_bytes(Rp, passes);
         b.sort_scratch = c.take<char>(b.sort_scratch_bytes);
         b.bytes = align_up(c.off, kAlign);
         return b;
     }
+    __host__ const uint64_t* sorted(int passes) const { return (passes & 1) ? inst_b : inst_a; }
 };
 
-// Number of 8-bit radix passes needed for keys (tile << 32 | depth_bits) with `tiles` tiles.
+// Number of 8-bit radix passes that cover the tile field of the instances for `tiles` tiles.
 __host__ inline int sort_passes(uint32_t tiles) {
     int bits = 0;
     while ((1u << bits) < tiles && bits < 31) ++bits;   // tile ids fit in `bits` bits
     if (bits == 0) bits = 1;
-    return (32 + bits + kRadixBits - 1) / kRadixBits;
+    return (bits + kRadixBits - 1) / kRadixBits;
 }
 
 }  // namespace gs

@@ -33,7 +33,10 @@ SIGNATURES = {
     "gs_backward_scratch_bytes": (_c_size_t, [_c_int]),
     "gs_forward_preprocess": (_c_int, [_c_void_p, _c_int, _c_int, _c_int] + [_c_void_p] * 5 + [_c_float]
                               + [_c_void_p] * 5 + [_c_int, _c_int, _c_float, _c_float, _c_int]
-                              + [_c_void_p] * 4),
+                              + [_c_void_p] * 5),
+    "gs_host_event_create": (_c_void_p, []),
+    "gs_host_event_wait": (_c_int, [_c_void_p]),
+    "gs_host_event_destroy": (_c_int, [_c_void_p]),
     "gs_forward_render": (_c_int, [_c_void_p, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 8),
     "gs_backward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 5
                     + [_c_float] + [_c_void_p] * 5 + [_c_float, _c_float] + [_c_void_p] * 14),
@@ -65,6 +68,7 @@ def load_library(path=_LIB_PATH):
 
 _lib = load_library()
 _pinned_counts = {}
+_count_events = {}
 
 
 def _check(rc, what):
@@ -106,6 +110,17 @@ def _pinned_count(device):
     return buf
 
 
+def _count_event(device):
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    ev = _count_events.get(key)
+    if ev is None:
+        ev = _lib.gs_host_event_create()
+        if not ev:
+            raise RuntimeError("gs_host_event_create failed")
+        _count_events[key] = ev
+    return ev
+
+
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
                         prefiltered, debug):
@@ -145,16 +160,19 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         geom = torch.empty(_lib.gs_geom_bytes(P), **byte_opts)
         img = torch.empty(_lib.gs_image_bytes(W, H), **byte_opts)
         count = _pinned_count(device)
+        count_ev = _count_event(device)
 
         _check(_lib.gs_forward_preprocess(
             stream, P, int(degree), M, _ptr(means3D), _ptr(sh), _ptr(colors), _ptr(opacity), _ptr(scales),
             float(scale_modifier), _ptr(rotations), _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix),
             _ptr(campos), W, H, float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
-            radii.data_ptr(), is_used.data_ptr(), geom.data_ptr(), count.data_ptr()), "gs_forward_preprocess")
-        # The one host sync of the forward (the reference has the same one, rasterizer_impl.cu:282):
-        # the binning workspace is sized from the instance count.
-        torch.cuda.current_stream(device).synchronize()
-        rendered = int(count.item())
+            radii.data_ptr(), is_used.data_ptr(), geom.data_ptr(), count.data_ptr(), count_ev),
+            "gs_forward_preprocess")
+        # The one host wait of the forward (the reference blocks the stream here, rasterizer_impl.cu:282): the
+        # binning workspace is sized from the instance count. Only the preprocess kernel is waited for; the depth
+        # sort and scan enqueued behind it keep the GPU busy meanwhile.
+        _check(_lib.gs_host_event_wait(count_ev), "gs_host_event_wait")
+        rendered = int(count[0])
         if debug:
             _debug_sync("preprocess")
 

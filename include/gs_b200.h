@@ -55,19 +55,30 @@ size_t gs_image_bytes(int W, int H);
 size_t gs_binning_bytes(unsigned int R, int W, int H);
 size_t gs_backward_scratch_bytes(int P);
 
-/* Forward, stage 1: preprocess (cull, project, covariance, conic, radius, SH colour) + inclusive scan of
- * tiles_touched. Writes radii[P] and zero-fills is_used[P]. If num_rendered_host != NULL (must be pinned
- * host memory) the instance count R is copied there asynchronously on `stream`; synchronise the stream
- * before reading it. */
+/* Forward, stage 1: preprocess (cull, project, covariance, conic, radius, SH colour), then the depth order of
+ * the Gaussians (radix sort of depth_bits|index) and the inclusive scan of tiles_touched in that order.
+ * Writes radii[P] and zero-fills is_used[P]. If num_rendered_host != NULL (must be pinned host memory) the
+ * instance count R is copied there asynchronously on `stream` right after the preprocess kernel; if
+ * count_ready_event != NULL (a handle from gs_host_event_create) it is recorded after that copy, so the host can
+ * gs_host_event_wait() for R and size the binning workspace while the depth sort is still running. Without
+ * an event, synchronise the stream before reading R. */
 int gs_forward_preprocess(void* stream, int P, int D, int M,
                           const float* means3D, const float* shs, const float* colors_precomp,
                           const float* opacities, const float* scales, float scale_modifier,
                           const float* rotations, const float* cov3D_precomp,
                           const float* viewmatrix, const float* projmatrix, const float* campos,
                           int W, int H, float tan_fovx, float tan_fovy, int prefiltered,
-                          int* radii, int* is_used, void* geom_ws, unsigned int* num_rendered_host);
+                          int* radii, int* is_used, void* geom_ws, unsigned int* num_rendered_host,
+                          void* count_ready_event);
 
-/* Forward, stage 2: tile-key duplication, radix sort, tile ranges, packed splat stream, tile render.
+/* Host-side wait handle for the instance count (a CUDA event without timing). The reference blocks the whole
+ * stream with a synchronous cudaMemcpy at this point (rasterizer_impl.cu:282). */
+void* gs_host_event_create(void);
+int gs_host_event_wait(void* event);
+int gs_host_event_destroy(void* event);
+
+/* Forward, stage 2: tile-instance emission in depth order, stable radix sort by tile, tile ranges, packed splat
+ * stream, tile render. The resulting per-tile lists equal the reference's (tile|depth)-sorted lists exactly.
  * Writes out_color[3][H][W] and sets is_used[id]=1 for every blended Gaussian. */
 int gs_forward_render(void* stream, int P, unsigned int R, int W, int H,
                       const float* background, const float* colors_precomp, const int* radii,
@@ -115,10 +126,12 @@ unsigned long long gs_launch_count(void);
 /* Test / debug hook: copy one internal array of the workspaces into dst (device memory). `which` uses the
  * numbering of the reference's state structs so parity tests can compare array by array:
  *   0 depths f32[P] | 1 clamped u8[P] (bit c = channel c) | 3 means2D f32[2P] | 4 cov3D f32[6P]
- *   5 conic_opacity f32[4P] | 6 rgb f32[3P] | 7 tiles_touched u32[P] | 8 point_offsets u32[P]
- *   10 sorted gaussian ids u32[R] | 12 sorted keys u64[R] | 14 packed splat records 48 B x R
+ *   5 conic_opacity f32[4P] | 6 rgb f32[3P] | 7 tiles_touched u32[P]
+ *   8 inclusive scan of tiles_touched in depth order u32[P] | 9 gaussian ids in (depth, index) order u32[P]
+ *   10 sorted gaussian ids u32[R] | 12 sorted keys (tile << 32 | depth_bits) u64[R], both in the reference's format
+ *   13 raw sorted instances (tile << 32 | id) u64[R] | 14 packed splat records 48 B x R
  *   20 final_T f32[WH] | 21 n_contrib u32[WH] | 22 ranges u32[2*tiles] | 23 tile_max_contrib u32[tiles]
- *   30 sort error flag u32[1]
+ *   30 tile-sort error flag u32[1] | 31 depth-sort error flag u32[1]
  * Returns the array's size in bytes (copied only when it fits in max_bytes), or -1. Synchronous. */
 long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H,
                          const void* geom_ws, const void* binning_ws, const void* image_ws,

@@ -98,7 +98,16 @@ def compare_with_reference(scene, cam, degree=3, bg=(0.0, 0.0, 0.0), seed=1, do_
         rep[f"{name}_bit_mismatch"] = bits_equal_count(a, b)
         rep[f"{name}_max_abs"] = float((a - b).abs().max().item()) if a.numel() else 0.0
     rep["tiles_touched_mismatch"] = int((mine(7, i32) != ref(7, i32)).sum().item())
-    rep["point_offsets_mismatch"] = int((mine(8, i32) != ref(8, i32)).sum().item())
+    # ours scans tiles_touched in depth order (the reference in index order): same total, and the scan must be the
+    # running sum over our depth order, which must itself be the stable (depth, index) order of the visible set
+    order = mine(9, i32).long()
+    tt = mine(7, i32).long()
+    rep["point_offsets_mismatch"] = int((torch.cumsum(tt[order], 0) != mine(8, i32).long()).sum().item())
+    rep["point_offsets_mismatch"] += int(ref(8, i32)[-1].item() != R) if P else 0
+    dbits = mine(0, f32).view(i32).long()
+    dkey = torch.where(tt > 0, dbits, torch.full_like(dbits, 0xFFFFFFFF))
+    composite = (dkey[order] << 32) | order
+    rep["depth_order_mismatch"] = int((composite[1:] <= composite[:-1]).sum().item()) + int(order.unique().numel() != P)
     cl_m = mine(1, u8)[both_vis]
     cl_r = ref(1, u8).view(P, 3)[both_vis]
     cl_r_bits = (cl_r[:, 0] | (cl_r[:, 1] << 1) | (cl_r[:, 2] << 2)).to(u8)
@@ -114,7 +123,7 @@ def compare_with_reference(scene, cam, degree=3, bg=(0.0, 0.0, 0.0), seed=1, do_
     rep["image_bit_mismatch"] = bits_equal_count(color, color_r)
     rep["image_max_abs"] = float((color - color_r).abs().max().item())
     rep["is_used_mismatch"] = int((is_used != is_used_r).sum().item())
-    rep["sort_error_flag"] = int(mine(30, i32)[0].item()) if R > 0 else 0
+    rep["sort_error_flag"] = (int(mine(30, i32)[0].item()) if R > 0 else 0) + int(mine(31, i32)[0].item())
 
     if do_backward:
         g = torch.Generator(device="cpu").manual_seed(seed)

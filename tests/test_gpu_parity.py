@@ -428,10 +428,14 @@ def test_full_size_properties_3M_1080p():
     args = helpers.native_forward_args(s, c, 3)
     R, color, radii, geom, binning, img, is_used = C.rasterize_gaussians(*args)
     f = lambda w, dt: C.debug_fetch(w, P, R, W, H, geom, binning, img, dt)
-    assert int(f(30, torch.int32)[0]) == 0
-    tiles_touched, offsets = f(7, torch.int32).long(), f(8, torch.int32).long()
+    assert int(f(30, torch.int32)[0]) == 0 and int(f(31, torch.int32)[0]) == 0
+    tiles_touched, offsets, order = f(7, torch.int32).long(), f(8, torch.int32).long(), f(9, torch.int32).long()
     assert int(tiles_touched.sum()) == R and int(offsets[-1]) == R
-    assert torch.equal(torch.cumsum(tiles_touched, 0), offsets)
+    assert torch.equal(torch.cumsum(tiles_touched[order], 0), offsets)      # scan runs in depth order
+    assert torch.equal(torch.sort(order).values, torch.arange(P, device=dev()))   # a permutation
+    dkey = torch.where(tiles_touched > 0, f(0, torch.float32).view(torch.int32).long(), torch.full_like(order, 0xFFFFFFFF))
+    comp = (dkey[order] << 32) | order
+    assert bool((comp[1:] > comp[:-1]).all())                                # stable (depth, index) order
     keys, ids = f(12, torch.int64), f(10, torch.int32).long()
     assert bool((keys[1:] >= keys[:-1]).all())                      # sortedness
     assert bool(((keys[1:] != keys[:-1]) | (ids[1:] > ids[:-1])).all())   # stability: ties keep index order
