@@ -105,7 +105,7 @@ def compare_with_reference(scene, cam, degree=3, bg=(0.0, 0.0, 0.0), seed=1, do_
     rep["point_offsets_mismatch"] = int((torch.cumsum(tt[order], 0) != mine(8, i32).long()).sum().item())
     rep["point_offsets_mismatch"] += int(ref(8, i32)[-1].item() != R) if P else 0
     dbits = mine(0, f32).view(i32).long()
-    dkey = torch.where(tt > 0, dbits, torch.full_like(dbits, 0xFFFFFFFF))
+    dkey = torch.where(tt > 0, dbits, torch.full_like(dbits, 0x7FFFFFFF))
     composite = (dkey[order] << 32) | order
     rep["depth_order_mismatch"] = int((composite[1:] <= composite[:-1]).sum().item()) + int(order.unique().numel() != P)
     cl_m = mine(1, u8)[both_vis]

@@ -47,7 +47,7 @@ def test_sizes_and_errors_without_gpu():
     assert lib.gs_stage_count() >= 9 and lib.gs_stage_name(0) == b"preprocess_fwd"
     # bad arguments are rejected with GS_ERR_ARG before touching the device
     rc = lib.gs_forward_preprocess(None, 10, 3, 16, None, None, None, None, None, 1.0, None, None, None, None, None,
-                                   0, 0, 1.0, 1.0, 0, None, None, None, None)
+                                   0, 0, 1.0, 1.0, 0, None, None, None, None, None)
     assert rc == -1
     rc = lib.gs_compute_relocation(None, 5, None, None, None, None, 51, None, None)
     assert rc == -1

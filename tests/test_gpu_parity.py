@@ -433,7 +433,7 @@ def test_full_size_properties_3M_1080p():
     assert int(tiles_touched.sum()) == R and int(offsets[-1]) == R
     assert torch.equal(torch.cumsum(tiles_touched[order], 0), offsets)      # scan runs in depth order
     assert torch.equal(torch.sort(order).values, torch.arange(P, device=dev()))   # a permutation
-    dkey = torch.where(tiles_touched > 0, f(0, torch.float32).view(torch.int32).long(), torch.full_like(order, 0xFFFFFFFF))
+    dkey = torch.where(tiles_touched > 0, f(0, torch.float32).view(torch.int32).long(), torch.full_like(order, 0x7FFFFFFF))
     comp = (dkey[order] << 32) | order
     assert bool((comp[1:] > comp[:-1]).all())                                # stable (depth, index) order
     keys, ids = f(12, torch.int64), f(10, torch.int32).long()
