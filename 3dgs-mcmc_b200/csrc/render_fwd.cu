@@ -11,6 +11,7 @@
 #include "bulk_copy.cuh"
 #include "gs_common.cuh"
 #include "kernels.cuh"
+#include "render_common.cuh"
 #include "workspace.cuh"
 
 namespace gs {
@@ -32,6 +33,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
     const bool inside = px < (uint32_t)p.W && py < (uint32_t)p.H;
     const uint32_t pix_id = (uint32_t)p.W * py + px;
     const float2 pixf = {(float)px, (float)py};
+    const float patch_x0 = (float)(tile_x * GS_TILE_X + (warp & 1) * 8), patch_y0 = (float)(tile_y * GS_TILE_Y + (warp >> 1) * 4);
 
     const uint2 range = p.ranges[tile];
     const int n_total = (int)(range.y - range.x);
@@ -70,7 +72,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
     };
 
     float T = 1.0f;
-    uint32_t contributor = 0, last_contributor = 0;
+    uint32_t last_contributor = 0;
     float C[3] = {0.f, 0.f, 0.f};
     bool done = !inside;
 
@@ -84,30 +86,44 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
         const int s = c % kFwdStages;
         const int n = min(kFwdChunk, n_total - c * kFwdChunk);
         mbar_wait(&s_full[s], (uint32_t)((c / kFwdStages) & 1));
-        if (!done) {
+        // Lane-parallel patch cull: lane l tests splat base+l against this warp's 8x4 patch; only the survivors
+        // are evaluated per pixel. Positions keep their list index, so n_contrib is unchanged.
+        if (!__all_sync(0xffffffffu, done)) {
             const float4* __restrict__ rec = reinterpret_cast<const float4*>(&s_rec[s][0]);
-            for (int j = 0; j < n; ++j) {
-                contributor++;
-                const float4 q0 = rec[3 * j];      // x, y, A, B
-                const float4 q1 = rec[3 * j + 1];  // C, opacity, thr, id
-                const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
-                const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-                if (power > 0.0f) continue;
-                if (power < q1.z) continue;  // cannot reach alpha >= 1/255 (see ranges_and_pack_kernel)
-                const float alpha = min(0.99f, q1.y * exp(power));
-                if (alpha < 1.0f / 255.0f) continue;
-                const float test_T = T * (1 - alpha);
-                if (test_T < 0.0001f) {
-                    done = true;
-                    break;
+            for (int base = 0; base < n; base += 32) {
+                if (__all_sync(0xffffffffu, done)) break;
+                const int jt = base + lane;
+                bool may = false;
+                if (jt < n) {
+                    const float4 t0 = rec[3 * jt], t1 = rec[3 * jt + 1];
+                    may = patch_may_contribute(t0.x, t0.y, t0.z, t0.w, t1.x, t1.z, patch_x0, patch_y0);
                 }
-                const float4 q2 = rec[3 * j + 2];  // r, g, b
-                C[0] += q2.x * alpha * T;
-                C[1] += q2.y * alpha * T;
-                C[2] += q2.z * alpha * T;
-                T = test_T;
-                last_contributor = contributor;
-                s_used[s][j] = __float_as_int(q1.w) + 1;
+                uint32_t m = __ballot_sync(0xffffffffu, may);
+                while (m) {
+                    const int j = base + __ffs(m) - 1;
+                    m &= m - 1;
+                    if (done) continue;
+                    const float4 q0 = rec[3 * j];      // x, y, A, B
+                    const float4 q1 = rec[3 * j + 1];  // C, opacity, thr, id
+                    const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+                    const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+                    if (power > 0.0f) continue;
+                    if (power < q1.z) continue;  // cannot reach alpha >= 1/255 (see ranges_and_pack_kernel)
+                    const float alpha = min(0.99f, q1.y * exp(power));
+                    if (alpha < 1.0f / 255.0f) continue;
+                    const float test_T = T * (1 - alpha);
+                    if (test_T < 0.0001f) {
+                        done = true;
+                        continue;
+                    }
+                    const float4 q2 = rec[3 * j + 2];  // r, g, b
+                    C[0] += q2.x * alpha * T;
+                    C[1] += q2.y * alpha * T;
+                    C[2] += q2.z * alpha * T;
+                    T = test_T;
+                    last_contributor = (uint32_t)(c * kFwdChunk + j + 1);
+                    s_used[s][j] = __float_as_int(q1.w) + 1;
+                }
             }
         }
     }
