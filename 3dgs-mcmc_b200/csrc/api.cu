@@ -39,7 +39,7 @@ enum Stage {
     ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_PACK, ST_RENDER_FWD, ST_BWD_ZERO, ST_RENDER_BWD,
     ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_COUNT
 };
-const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "scan", "emit_instances", "tile_sort", "ranges_pack",
+const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "scan", "emit_instances", "tile_sort", "tile_ranges",
                                            "render_fwd", "bwd_zero", "render_bwd", "preprocess_bwd",
                                            "compute_relocation", "add_noise"};
 struct Profiler {
@@ -145,7 +145,7 @@ int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means
     pp.prefiltered = prefiltered;
     pp.radii = radii; pp.is_used = is_used; pp.means2D = g.means2D; pp.depths = g.depths; pp.cov3D = g.cov3D;
     pp.rgb = g.rgb; pp.conic_opacity = g.conic_opacity; pp.tiles_touched = g.tiles_touched; pp.clamped = g.clamped;
-    pp.depth_keys = g.dkeys_a; pp.num_rendered = g.num_rendered;
+    pp.rec = g.rec; pp.depth_keys = g.dkeys_a; pp.num_rendered = g.num_rendered;
     prof_mark(stream, -1);
     GS_CUDA_TRY(cudaMemsetAsync(g.num_rendered, 0, 16, stream));
     int rc = launch_preprocess_fwd(pp, stream);
@@ -193,14 +193,14 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
         prof_mark(stream, ST_SORT);
         count_launches(3 + passes);
     }
-    const float* colors = colors_precomp ? colors_precomp : g.rgb;
-    rc = launch_ranges_and_pack(R, b.sorted(passes), g.means2D, g.conic_opacity, colors, img.ranges, tiles, b.packed, stream);
+    (void)colors_precomp;  // already folded into the render records by the preprocess stage
+    rc = launch_tile_ranges(R, b.sorted(passes), img.ranges, tiles, stream);
     if (rc) return rc;
     prof_mark(stream, ST_PACK);
     count_launches(R > 0 ? 2 : 1);
 
     RenderFwdParams rp;
-    rp.ranges = img.ranges; rp.packed = b.packed; rp.W = W; rp.H = H; rp.tiles_x = (int)grid.x; rp.bg = background;
+    rp.ranges = img.ranges; rp.inst = b.sorted(passes); rp.rec = g.rec; rp.W = W; rp.H = H; rp.tiles_x = (int)grid.x; rp.bg = background;
     rp.final_T = img.final_T; rp.n_contrib = img.n_contrib; rp.out_color = out_color; rp.is_used = is_used;
     rp.tile_max_contrib = img.tile_max_contrib;
     rc = launch_render_fwd(rp, (int)tiles, stream);
@@ -238,7 +238,7 @@ int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H
     int rc = GS_OK;
     if (R > 0) {
         RenderBwdParams rb;
-        rb.ranges = img.ranges; rb.packed = b.packed; rb.tile_max_contrib = img.tile_max_contrib;
+        rb.ranges = img.ranges; rb.inst = b.sorted(passes); rb.rec = g.rec; rb.tile_max_contrib = img.tile_max_contrib;
         rb.W = W; rb.H = H; rb.tiles_x = (int)grid.x; rb.bg = background; rb.final_T = img.final_T;
         rb.n_contrib = img.n_contrib; rb.dL_dpix = dL_dpix;
         rb.acc_color_opacity = sc.acc_color_opacity; rb.acc_mean_conic = sc.acc_mean_conic; rb.acc_conic_w = sc.acc_conic_w;
@@ -332,6 +332,7 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const v
             case 6: src = g.rgb; n = Ps * 12; break;
             case 7: src = g.tiles_touched; n = Ps * 4; break;
             case 8: src = g.point_offsets; n = Ps * 4; break;
+            case 2: src = g.rec; n = Ps * sizeof(SplatRec); break;
             case 9:  // Gaussian indices in (depth, index) order; culled ones last
                 n = Ps * 4;
                 if (dst && n > 0 && n <= max_bytes) {
@@ -359,7 +360,6 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const v
         }
         switch (which) {
             case 13: src = b.sorted(passes); n = Rs * 8; break;  // raw sorted instances (tile << 32 | idx)
-            case 14: src = b.packed; n = Rs * sizeof(SplatRec); break;
             case 30: src = b.error_flag; n = 4; break;
             default: return -1;
         }

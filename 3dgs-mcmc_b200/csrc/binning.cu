@@ -1,6 +1,6 @@
 // Binning for sm_100a: depth ordering of the Gaussians, tile-instance emission, a stable onesweep
-// radix sort of the instances by tile, tile ranges and the tile-ordered packed splat stream the
-// render kernels consume.
+// radix sort of the instances by tile, tile ranges and the per-tile ranges of the sorted list
+// the render kernels walk.
 //
 // The reference sorts R instance pairs (tile << 32 | depth_bits, gaussian_idx) with a 6-pass CUB radix
 // sort over 44-45 significant bits (cuda_rasterizer/rasterizer_impl.cu:70-138, :278-318; ~152 B of
@@ -407,17 +407,13 @@ int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, int first_
 }
 
 // ------------------------------------------------------------------------------------------------
-// Tile ranges + packed splat stream, one thread per sorted instance.
+// Tile ranges, one thread per sorted instance (identifyTileRanges, rasterizer_impl.cu:116-138).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) ranges_and_pack_kernel(uint32_t R, const uint64_t* __restrict__ inst,
-                                                              const float2* __restrict__ means2D,
-                                                              const float4* __restrict__ conic_opacity,
-                                                              const float* __restrict__ colors /*[3P]*/,
-                                                              uint2* __restrict__ ranges, SplatRec* __restrict__ packed) {
+__global__ void __launch_bounds__(256) tile_ranges_kernel(uint32_t R, const uint64_t* __restrict__ inst,
+                                                          uint2* __restrict__ ranges) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= R) return;
-    const uint64_t k = inst[i];
-    const uint32_t tile = (uint32_t)(k >> 32);
+    const uint32_t tile = (uint32_t)(inst[i] >> 32);
     if (i == 0) {
         ranges[tile].x = 0;
     } else {
@@ -428,36 +424,12 @@ __global__ void __launch_bounds__(256) ranges_and_pack_kernel(uint32_t R, const 
         }
     }
     if (i == R - 1) ranges[tile].y = R;
-
-    const uint32_t id = (uint32_t)k;
-    const float2 xy = means2D[id];
-    const float4 co = conic_opacity[id];
-    // Conservative reject threshold: power < thr  ==>  opacity * expf(power) < 1/255 (with 1e-3 slack
-    // in the exponent, far above the expf / logf / product rounding errors), so the render kernels can
-    // skip expf for such pairs without changing any decision.
-    float thr;
-    if (co.w > 0.0f) {
-        const float lt = logf(1.0f / (255.0f * co.w));
-        thr = lt - 0.001f - 1e-6f * fabsf(lt);
-    } else {
-        thr = co.w == co.w ? 1.0f : -INFINITY;  // non-positive opacity never passes; NaN takes the exact path
-    }
-    SplatRec rec;
-    rec.x = xy.x; rec.y = xy.y; rec.A = co.x; rec.B = co.y;
-    rec.C = co.z; rec.opacity = co.w; rec.thr = thr; rec.id = (int)id;
-    rec.r = colors[3 * (size_t)id]; rec.g = colors[3 * (size_t)id + 1]; rec.b = colors[3 * (size_t)id + 2]; rec.pad = 0.f;
-    float4* dst = reinterpret_cast<float4*>(packed + i);
-    const float4* src = reinterpret_cast<const float4*>(&rec);
-    dst[0] = src[0];
-    dst[1] = src[1];
-    dst[2] = src[2];
 }
 
-int launch_ranges_and_pack(uint32_t R, const uint64_t* inst, const float2* means2D, const float4* conic_opacity,
-                           const float* colors, uint2* ranges, uint32_t tiles, SplatRec* packed, cudaStream_t stream) {
+int launch_tile_ranges(uint32_t R, const uint64_t* inst, uint2* ranges, uint32_t tiles, cudaStream_t stream) {
     GS_CUDA_TRY(cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), stream));
     if (R == 0) return GS_OK;
-    ranges_and_pack_kernel<<<(R + 255) / 256, 256, 0, stream>>>(R, inst, means2D, conic_opacity, colors, ranges, packed);
+    tile_ranges_kernel<<<(R + 255) / 256, 256, 0, stream>>>(R, inst, ranges);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

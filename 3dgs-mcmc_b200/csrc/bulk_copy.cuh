@@ -1,7 +1,9 @@
-// mbarrier + 1-D bulk async copy (TMA engine, `cp.async.bulk`, SASS UBLKCP) helpers for sm_100a.
-// The render kernels stream 48-byte splat records from the tile-ordered packed list into shared
-// memory through a small ring of stages; one elected thread issues the copies, every thread waits on
-// the stage's mbarrier phase.
+// mbarrier + async-copy helpers for sm_100a.
+//   * 1-D bulk copies (TMA engine, `cp.async.bulk`, SASS UBLKCP): the render kernels stream each tile's slice of
+//     the sorted instance list into shared memory through a small ring; one elected thread issues, every
+//     thread waits on the stage's mbarrier phase.
+//   * 16-byte `cp.async.cg` gathers (SASS LDGSTS) of the per-Gaussian 48-byte records those instances name,
+//     whose completion is tracked by an mbarrier too (`cp.async.mbarrier.arrive.noinc`).
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -50,5 +52,18 @@ __device__ __forceinline__ void bulk_copy_g2s(void* smem_dst, const void* gmem_s
         "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
         : "memory");
 }
+
+// 16-byte global -> shared asynchronous copy (L2 only), no register staging.
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+
+// The barrier receives one arrival from this thread once all of the thread's earlier cp.async copies have landed
+// (the pending count is not incremented: initialise the barrier with the number of arriving threads).
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint64_t* bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 }  // namespace gs

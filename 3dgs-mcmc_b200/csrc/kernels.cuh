@@ -32,13 +32,15 @@ struct PreprocessParams {
     float4* __restrict__ conic_opacity;
     uint32_t* __restrict__ tiles_touched;
     uint8_t* __restrict__ clamped;
+    SplatRec* __restrict__ rec;          // [P] render records (visible Gaussians only)
     uint64_t* __restrict__ depth_keys;   // [P] (depth_bits << 32 | idx); depth_bits = ~0 when culled
     uint32_t* __restrict__ num_rendered; // [1] += sum of tiles_touched (zeroed by the caller)
 };
 
 struct RenderFwdParams {
     const uint2* __restrict__ ranges;
-    const SplatRec* __restrict__ packed;
+    const uint64_t* __restrict__ inst;   // sorted instances (tile << 32 | gaussian idx), padded by 2 entries
+    const SplatRec* __restrict__ rec;    // per-Gaussian render records
     int W, H, tiles_x;
     const float* __restrict__ bg;
     float* __restrict__ final_T;
@@ -50,7 +52,8 @@ struct RenderFwdParams {
 
 struct RenderBwdParams {
     const uint2* __restrict__ ranges;
-    const SplatRec* __restrict__ packed;
+    const uint64_t* __restrict__ inst;
+    const SplatRec* __restrict__ rec;
     const uint32_t* __restrict__ tile_max_contrib;
     int W, H, tiles_x;
     const float* __restrict__ bg;
@@ -99,8 +102,7 @@ int launch_emit_instances(int P, const uint64_t* depth_order, const float2* mean
                           const int* radii, uint2 grid, uint64_t* inst, cudaStream_t stream);
 int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, int first_bit, int passes, char* scratch,
                       uint32_t* error_flag, cudaStream_t stream);
-int launch_ranges_and_pack(uint32_t R, const uint64_t* inst, const float2* means2D, const float4* conic_opacity,
-                           const float* colors, uint2* ranges, uint32_t tiles, SplatRec* packed, cudaStream_t stream);
+int launch_tile_ranges(uint32_t R, const uint64_t* inst, uint2* ranges, uint32_t tiles, cudaStream_t stream);
 int launch_debug_expand(uint32_t R, const uint64_t* inst, const float* depths, uint64_t* keys, uint32_t* ids);
 int launch_debug_low32(uint32_t n, const uint64_t* in, uint32_t* out);
 int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream);

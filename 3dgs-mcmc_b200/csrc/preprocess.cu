@@ -55,7 +55,9 @@ GS_DEV float3 cov2d_ewa(const float3& mean, float focal_x, float focal_y, float 
 }
 
 // Evaluate SH colour. `sh` points at this Gaussian's [M][3] block.
-GS_DEV V3 sh_to_rgb(int deg, const V3 pos, const V3 campos, const float* __restrict__ sh, uint8_t& clamp_bits) {
+// Not inlined on purpose: bit-exact parity of the colours depends on which multiplies the compiler contracts
+// into FMAs, and that choice must not drift with edits to the caller.
+__device__ __noinline__ V3 sh_to_rgb(int deg, const V3 pos, const V3 campos, const float* __restrict__ sh, uint8_t& clamp_bits) {
     V3 dir = pos - campos;
     dir = dir / sqrt(dot3(dir, dir));
     auto C = [&](int k) { return V3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]); };
@@ -133,6 +135,7 @@ GS_DEV uint32_t preprocess_one(const PreprocessParams& p, const int idx) {
             tile_rect(point_image, (int)my_radius, rect_min, rect_max, p.grid);
             const uint32_t ntiles = (rect_max.x - rect_min.x) * (rect_max.y - rect_min.y);
             if (ntiles != 0) {
+                float3 col;
                 if (p.colors_precomp == nullptr) {
                     uint8_t cb;
                     const V3 campos(p.campos[0], p.campos[1], p.campos[2]);
@@ -142,10 +145,29 @@ GS_DEV uint32_t preprocess_one(const PreprocessParams& p, const int idx) {
                     p.rgb[3 * (size_t)idx + 1] = c.y;
                     p.rgb[3 * (size_t)idx + 2] = c.z;
                     p.clamped[idx] = cb;
+                    col = make_float3(c.x, c.y, c.z);
+                } else {
+                    col = make_float3(p.colors_precomp[3 * (size_t)idx], p.colors_precomp[3 * (size_t)idx + 1],
+                                      p.colors_precomp[3 * (size_t)idx + 2]);
                 }
+                const float opacity = p.opacities[idx];
                 p.depths[idx] = p_view.z;
                 p.means2D[idx] = point_image;
-                p.conic_opacity[idx] = {conic.x, conic.y, conic.z, p.opacities[idx]};
+                p.conic_opacity[idx] = {conic.x, conic.y, conic.z, opacity};
+                // Render record. thr is a conservative reject threshold: power < thr  ==>  opacity * expf(power) < 1/255
+                // (1e-3 slack in the exponent, far above the expf / logf / product rounding errors), so the renderers can
+                // skip expf — and whole pixel patches — for such pairs without changing any decision.
+                float thr;
+                if (opacity > 0.0f) {
+                    const float lt = logf(1.0f / (255.0f * opacity));
+                    thr = lt - 0.001f - 1e-6f * fabsf(lt);
+                } else {
+                    thr = opacity == opacity ? 1.0f : -INFINITY;  // non-positive opacity never passes; NaN takes the exact path
+                }
+                float4* dst = reinterpret_cast<float4*>(p.rec + idx);
+                dst[0] = make_float4(point_image.x, point_image.y, conic.x, conic.y);
+                dst[1] = make_float4(conic.z, opacity, thr, __int_as_float(idx));
+                dst[2] = make_float4(col.x, col.y, col.z, p_view.z);
                 out_radius = (int)my_radius;
                 out_tiles = ntiles;
                 depth_bits = __float_as_uint(p_view.z);

@@ -1,16 +1,16 @@
-// Backward tile renderer for sm_100a: back-to-front replay of the blend with warp-aggregated,
-// vectorised gradient reductions.
+// Backward tile renderer for sm_100a: back-to-front replay of the blend with warp-aggregated gradient
+// reductions.
 //
-// Same CTA / warp / pixel mapping and the same bulk-copy shared-memory ring as the forward, streamed
-// in reverse and only up to the tile's last blended position (tile_max_contrib, recorded by the
-// forward) instead of the end of the tile's list. Per (pixel, splat) pair the recomputation of G and
-// alpha and every gradient expression follow the reference (cuda_rasterizer/backward.cu:399-557). The
-// reference issues 9 scalar float atomics per contributing pair; here each warp first reduces its 32
-// pixels with a multi-value butterfly (8 values folded 2:1 on the first exchange) and then issues two
-// 128-bit vector reductions (red.global.add.v4.f32) plus one scalar per (warp, splat) — and nothing at
-// all when no lane of the warp blended the splat. Accumulators are laid out [P] x (float4, float4,
-// float) for that purpose; summation order differs from the reference (as it does between two runs of
-// the reference), hence tolerance parity on gradients.
+// Same CTA / warp / pixel mapping and the same staging as the forward (bulk-copied instance slices,
+// cp.async-gathered 48-byte records, see render_common.cuh), streamed in reverse and only up to the
+// tile's last blended position (tile_max_contrib, recorded by the forward) instead of the end of the
+// tile's list. Per (pixel, splat) pair the recomputation of G and alpha and every gradient expression
+// follow the reference (cuda_rasterizer/backward.cu:399-557). The reference issues 9 scalar float
+// atomics per contributing pair; here each warp culls splats that cannot touch its 8x4 patch, reduces the
+// nine per-pair terms over its 32 pixels with a fold tree (14 shuffles) and issues one predicated
+// red.global.add.f32 from nine lanes per (warp, splat) — and nothing at all when no lane of the warp
+// blended the splat. Summation order differs from the reference (as it does between two runs of the
+// reference), hence tolerance parity on gradients.
 #include "bulk_copy.cuh"
 #include "gs_common.cuh"
 #include "kernels.cuh"
@@ -19,20 +19,15 @@
 
 namespace gs {
 
-constexpr int kBwdChunk = 128;
-constexpr int kBwdStages = 4;
-
-GS_DEV void red_add_v4(float4* addr, const float4 v) {
-    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
-                 : "memory");
-}
 GS_DEV void red_add_f32(float* addr, const float v) {
     asm volatile("red.global.add.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
 }
 
 __global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwdParams p) {
-    __shared__ __align__(128) SplatRec s_rec[kBwdStages][kBwdChunk];
-    __shared__ __align__(8) uint64_t s_full[kBwdStages];
+    __shared__ __align__(128) SplatRec s_rec[kRecStages][kChunk];
+    __shared__ __align__(16) uint64_t s_inst[kInstStages][kChunk + 2];
+    __shared__ __align__(8) uint64_t s_inst_full[kInstStages];
+    __shared__ __align__(8) uint64_t s_rec_full[kRecStages];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x;
@@ -46,30 +41,14 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwd
 
     const uint2 range = p.ranges[tile];
     const int n_total = min((int)(range.y - range.x), (int)p.tile_max_contrib[tile]);
-    const int nchunks = (n_total + kBwdChunk - 1) / kBwdChunk;
+    const int nchunks = (n_total + kChunk - 1) / kChunk;
     if (nchunks == 0) return;
-    const SplatRec* __restrict__ src = p.packed + range.x;
 
-    if (tid == 0) {
-#pragma unroll
-        for (int s = 0; s < kBwdStages; ++s) mbar_init(&s_full[s], 1);
-        mbar_fence_init();
-    }
+    if (tid == 0) stager_init(s_inst_full, s_rec_full);
     __syncthreads();
-
-    // Chunk k of the reversed stream is list chunk c = nchunks-1-k.
-    int issued = 0;
-    auto issue = [&](int k) {
-        const int s = k % kBwdStages;
-        const int c = nchunks - 1 - k;
-        const int n = min(kBwdChunk, n_total - c * kBwdChunk);
-        const uint32_t bytes = (uint32_t)n * (uint32_t)sizeof(SplatRec);
-        mbar_arrive_expect_tx(&s_full[s], bytes);
-        bulk_copy_g2s(&s_rec[s][0], src + (size_t)c * kBwdChunk, bytes, &s_full[s]);
-    };
-    if (tid == 0) {
-        for (; issued < min(kBwdStages, nchunks); ++issued) issue(issued);
-    }
+    // Stream chunk k is list chunk c = nchunks-1-k.
+    Stager st(p.inst, p.rec, range.x, n_total, nchunks, /*reversed=*/true, &s_inst[0][0], s_inst_full, &s_rec[0][0], s_rec_full);
+    st.prologue(tid);
 
     const size_t plane = (size_t)p.H * p.W;
     const float T_final = inside ? p.final_T[pix_id] : 0.f;
@@ -95,17 +74,15 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwd
     const bool b4 = (lane & 16) != 0, b3 = (lane & 8) != 0, b2 = (lane & 4) != 0;
 
     for (int k = 0; k < nchunks; ++k) {
-        if (k > 0) {
-            __syncthreads();  // every warp is done with chunk k-1: its stage can be refilled
-            if (tid == 0 && issued < nchunks) { issue(issued); ++issued; }
-        }
-        const int s = k % kBwdStages;
+        if (k > 0) __syncthreads();  // every warp is done with chunk k-1: its stages can be refilled
+        st.advance(tid, k);
+        const int s = k % kRecStages;
         const int c = nchunks - 1 - k;
-        const int n = min(kBwdChunk, n_total - c * kBwdChunk);
-        mbar_wait(&s_full[s], (uint32_t)((k / kBwdStages) & 1));
+        const int n = min(kChunk, n_total - c * kChunk);
+        mbar_wait(&s_rec_full[s], (uint32_t)((k / kRecStages) & 1));
         const float4* __restrict__ rec = reinterpret_cast<const float4*>(&s_rec[s][0]);
         // Positions >= warp_last were blended by no pixel of this warp.
-        const int jstart = min(n - 1, warp_last - 1 - c * kBwdChunk);
+        const int jstart = min(n - 1, warp_last - 1 - c * kChunk);
         // Lane-parallel patch cull (see render_common.cuh), 32 list positions at a time, walked back to front.
         for (int base = jstart & ~31; base >= 0; base -= 32) {
             const int jt = base + lane;
@@ -119,7 +96,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwd
                 const int b = 31 - __clz(m);
                 m &= ~(1u << b);
                 const int j = base + b;
-                const int pos = c * kBwdChunk + j;  // 0-based position in the tile list
+                const int pos = c * kChunk + j;  // 0-based position in the tile list
                 const float4 q0 = rec[3 * j];       // x, y, A, B
                 const float4 q1 = rec[3 * j + 1];   // C, opacity, thr, id
                 const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
@@ -206,7 +183,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwd
             }
         }
     }
-    // All issued copies were consumed (no early exit in the backward), nothing to drain.
+    st.drain(tid);  // every copy was consumed (no early exit); this only retires the cp.async groups
 }
 
 int launch_render_bwd(const RenderBwdParams& p, int tiles, cudaStream_t stream) {

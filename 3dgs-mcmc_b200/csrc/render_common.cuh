@@ -1,6 +1,8 @@
 // Shared pieces of the forward / backward tile renderers.
 #pragma once
+#include "bulk_copy.cuh"
 #include "gs_common.cuh"
+#include "workspace.cuh"
 
 namespace gs {
 
@@ -44,5 +46,106 @@ GS_DEV bool patch_may_contribute(const float mx, const float my, const float A, 
     const float pmax = inside ? 0.0f : -0.5f * qmin;
     return !(pmax + 4e-6f * mag + 1e-4f < thr);
 }
+
+// ------------------------------------------------------------------------------------------------
+// Shared-memory staging of one tile's splats, used by both renderers.
+//   instance ring : kInstStages x (kChunk + 2) u64, filled by 1-D bulk copies (one issuing thread);
+//   record ring   : kRecStages x kChunk SplatRec, filled by 16-byte cp.async gathers (threads 0..kChunk-1,
+//                   one record each), two stream chunks ahead of the consumer.
+// "Stream chunk" k is list chunk k for the forward and nchunks-1-k for the backward (reversed).
+// Barrier protocol: chunk k's instances complete phase (k / kInstStages) & 1 of inst_full[k % kInstStages]
+// (armed with the byte count by the issuing thread); its records complete phase (k / kRecStages) & 1 of
+// rec_full[k % kRecStages] after kChunk thread arrivals, each triggered when that thread's copies have landed.
+// A stage is refilled only after a CTA-wide barrier that follows its last reader, so phases never alias.
+// ------------------------------------------------------------------------------------------------
+constexpr int kChunk = 128;
+constexpr int kRecStages = 3;
+constexpr int kInstStages = 4;
+constexpr int kGatherAhead = 2;
+static_assert(kChunk % 2 == 0, "chunk starts must keep the parity of the tile's first instance");
+
+GS_DEV void stager_init(uint64_t* inst_full, uint64_t* rec_full) {
+#pragma unroll
+    for (int s = 0; s < kInstStages; ++s) mbar_init(&inst_full[s], 1);
+#pragma unroll
+    for (int s = 0; s < kRecStages; ++s) mbar_init(&rec_full[s], kChunk);
+    mbar_fence_init();
+}
+
+struct Stager {
+    const uint64_t* __restrict__ inst;
+    const SplatRec* __restrict__ rec;
+    uint32_t first;
+    int n_total, nchunks;
+    bool reversed;
+    uint64_t* s_inst;
+    uint64_t* inst_full;
+    SplatRec* s_rec;
+    uint64_t* rec_full;
+    int odd;
+    int inst_issued;  // meaningful in thread 0
+    int gathered;     // uniform
+
+    GS_DEV Stager(const uint64_t* inst_, const SplatRec* rec_, uint32_t first_, int n_total_, int nchunks_, bool reversed_,
+                  uint64_t* s_inst_, uint64_t* inst_full_, SplatRec* s_rec_, uint64_t* rec_full_)
+        : inst(inst_), rec(rec_), first(first_), n_total(n_total_), nchunks(nchunks_), reversed(reversed_), s_inst(s_inst_),
+          inst_full(inst_full_), s_rec(s_rec_), rec_full(rec_full_), odd((int)(first_ & 1u)), inst_issued(0), gathered(0) {}
+
+    GS_DEV int list_chunk(int k) const { return reversed ? nchunks - 1 - k : k; }
+    GS_DEV int chunk_n(int lc) const { return min(kChunk, n_total - lc * kChunk); }
+
+    // Thread 0: bulk-copy the instance slice of stream chunk k. Bulk copies move 16-byte units from 16-byte
+    // aligned addresses, so the copy starts one entry early when the slice starts at an odd index and may
+    // run one entry past its end (the instance arrays are padded for that).
+    GS_DEV void issue_inst(int k) {
+        const int lc = list_chunk(k), n = chunk_n(lc), s = k % kInstStages;
+        const size_t start = (size_t)first + (size_t)lc * kChunk;
+        const uint32_t bytes = (uint32_t)((n + odd + 1) & ~1) * 8u;
+        mbar_arrive_expect_tx(&inst_full[s], bytes);
+        bulk_copy_g2s(s_inst + s * (kChunk + 2), inst + (start - odd), bytes, &inst_full[s]);
+    }
+
+    // Threads 0..kChunk-1: gather the records of stream chunk k (its instances must have been issued).
+    GS_DEV void gather(int tid, int k) {
+        if (tid < kChunk) {
+            const int lc = list_chunk(k), n = chunk_n(lc), si = k % kInstStages, sr = k % kRecStages;
+            mbar_wait(&inst_full[si], (uint32_t)((k / kInstStages) & 1));
+            if (tid < n) {
+                const uint32_t id = (uint32_t)s_inst[si * (kChunk + 2) + odd + tid];
+                const float4* src = reinterpret_cast<const float4*>(rec + id);
+                float4* dst = reinterpret_cast<float4*>(s_rec + sr * kChunk + tid);
+                cp_async_16(dst, src);
+                cp_async_16(dst + 1, src + 1);
+                cp_async_16(dst + 2, src + 2);
+            }
+            cp_async_mbar_arrive_noinc(&rec_full[sr]);
+        }
+    }
+
+    GS_DEV void prologue(int tid) {
+        if (tid == 0)
+            for (; inst_issued < min(kInstStages, nchunks); ++inst_issued) issue_inst(inst_issued);
+        for (; gathered < min(kGatherAhead, nchunks); ++gathered) gather(tid, gathered);
+    }
+
+    // Call at iteration c (consumer about to read stream chunk c), after the CTA-wide barrier at the loop top.
+    GS_DEV void advance(int tid, int c) {
+        if (c + kGatherAhead < nchunks) {
+            gather(tid, c + kGatherAhead);
+            gathered = c + kGatherAhead + 1;
+        }
+        if (tid == 0 && c + kInstStages < nchunks) {
+            issue_inst(c + kInstStages);
+            inst_issued = c + kInstStages + 1;
+        }
+    }
+
+    // Before the CTA retires: every asynchronous copy aimed at its shared memory must have landed.
+    GS_DEV void drain(int tid) {
+        cp_async_wait_all();
+        if (tid == 0)
+            for (int k = gathered; k < inst_issued; ++k) mbar_wait(&inst_full[k % kInstStages], (uint32_t)((k / kInstStages) & 1));
+    }
+};
 
 }  // namespace gs

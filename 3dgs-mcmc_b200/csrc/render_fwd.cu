@@ -1,13 +1,17 @@
 // Forward tile renderer for sm_100a: per-tile front-to-back alpha blending.
 //
 // One CTA per 16x16 tile; each warp owns an 8x4 pixel patch (compact footprint -> whole-warp rejects
-// are frequent). The tile's splats arrive as 48-byte records from the tile-ordered packed stream
-// through a 4-stage shared-memory ring filled by 1-D bulk async copies (cp.async.bulk + mbarrier), so
-// no indirect gather sits on the blending critical path. A conservative per-splat log-threshold skips
-// expf for pairs that cannot reach alpha >= 1/255; every blend decision and every arithmetic
-// expression that reaches the output is the reference's (cuda_rasterizer/forward.cu:261-377), so the
-// image, final_T and n_contrib match it bit for bit. is_used flags are collected per stage in shared
-// memory and written once per (tile, splat) instead of once per (pixel, splat).
+// are frequent). The tile's slice of the sorted instance list is streamed into shared memory by 1-D bulk
+// async copies (cp.async.bulk + mbarrier, 4-deep ring, one issuing thread); the 48-byte render records
+// those instances name are then gathered straight into a 3-deep shared-memory ring with 16-byte
+// cp.async copies (no registers, completion tracked by an mbarrier), two chunks ahead of the blending,
+// so no indirect load sits on the blending critical path and no tile-ordered copy of the records is ever
+// written to HBM (the reference gathers with plain loads inside the loop, forward.cu:318-321).
+// Per 32 records each lane runs a conservative patch cull for one record (render_common.cuh); only the
+// survivors are evaluated per pixel. Every blend decision and every arithmetic expression that reaches
+// the output is the reference's (cuda_rasterizer/forward.cu:261-377), so the image, final_T and n_contrib
+// match it bit for bit. is_used flags are collected per stage in shared memory and written once per
+// (tile, splat) instead of once per (pixel, splat).
 #include "bulk_copy.cuh"
 #include "gs_common.cuh"
 #include "kernels.cuh"
@@ -16,13 +20,12 @@
 
 namespace gs {
 
-constexpr int kFwdChunk = 128;
-constexpr int kFwdStages = 4;
-
 __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwdParams p) {
-    __shared__ __align__(128) SplatRec s_rec[kFwdStages][kFwdChunk];
-    __shared__ __align__(8) uint64_t s_full[kFwdStages];
-    __shared__ int s_used[kFwdStages][kFwdChunk];  // id+1 of splats blended by some pixel, 0 otherwise
+    __shared__ __align__(128) SplatRec s_rec[kRecStages][kChunk];
+    __shared__ __align__(16) uint64_t s_inst[kInstStages][kChunk + 2];
+    __shared__ __align__(8) uint64_t s_inst_full[kInstStages];
+    __shared__ __align__(8) uint64_t s_rec_full[kRecStages];
+    __shared__ int s_used[kRecStages][kChunk];  // id+1 of splats blended by some pixel, 0 otherwise
     __shared__ uint32_t s_maxc;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -37,32 +40,22 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
 
     const uint2 range = p.ranges[tile];
     const int n_total = (int)(range.y - range.x);
-    const int nchunks = (n_total + kFwdChunk - 1) / kFwdChunk;
-    const SplatRec* __restrict__ src = p.packed + range.x;
+    const int nchunks = (n_total + kChunk - 1) / kChunk;
 
-    for (int i = tid; i < kFwdStages * kFwdChunk; i += GS_TILE_PIX) (&s_used[0][0])[i] = 0;
+    for (int i = tid; i < kRecStages * kChunk; i += GS_TILE_PIX) (&s_used[0][0])[i] = 0;
     if (tid == 0) {
         s_maxc = 0;
-#pragma unroll
-        for (int s = 0; s < kFwdStages; ++s) mbar_init(&s_full[s], 1);
-        mbar_fence_init();
+        stager_init(s_inst_full, s_rec_full);
     }
     __syncthreads();
 
-    int issued = 0;  // meaningful in thread 0 only
-    auto issue = [&](int c) {
-        const int s = c % kFwdStages;
-        const int n = min(kFwdChunk, n_total - c * kFwdChunk);
-        const uint32_t bytes = (uint32_t)n * (uint32_t)sizeof(SplatRec);
-        mbar_arrive_expect_tx(&s_full[s], bytes);
-        bulk_copy_g2s(&s_rec[s][0], src + (size_t)c * kFwdChunk, bytes, &s_full[s]);
-    };
-    if (tid == 0) {
-        for (; issued < min(kFwdStages, nchunks); ++issued) issue(issued);
-    }
+    // List chunk c covers positions [c*kChunk, c*kChunk + n) of the tile's list.
+    Stager st(p.inst, p.rec, range.x, n_total, nchunks, /*reversed=*/false, &s_inst[0][0], s_inst_full, &s_rec[0][0], s_rec_full);
+    st.prologue(tid);
+
     auto flush_used = [&](int c) {
-        const int s = c % kFwdStages;
-        if (tid < kFwdChunk) {
+        const int s = c % kRecStages;
+        if (tid < kChunk) {
             const int u = s_used[s][tid];
             if (u) {
                 p.is_used[u - 1] = 1;
@@ -81,11 +74,11 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
         const int ndone = __syncthreads_count(done);
         if (c > 0) flush_used(c - 1);
         if (ndone == GS_TILE_PIX) break;
-        if (tid == 0 && c > 0 && issued < nchunks) { issue(issued); ++issued; }
+        st.advance(tid, c);
 
-        const int s = c % kFwdStages;
-        const int n = min(kFwdChunk, n_total - c * kFwdChunk);
-        mbar_wait(&s_full[s], (uint32_t)((c / kFwdStages) & 1));
+        const int s = c % kRecStages;
+        const int n = min(kChunk, n_total - c * kChunk);
+        mbar_wait(&s_rec_full[s], (uint32_t)((c / kRecStages) & 1));
         // Lane-parallel patch cull: lane l tests splat base+l against this warp's 8x4 patch; only the survivors
         // are evaluated per pixel. Positions keep their list index, so n_contrib is unchanged.
         if (!__all_sync(0xffffffffu, done)) {
@@ -108,7 +101,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
                     const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
                     const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
                     if (power > 0.0f) continue;
-                    if (power < q1.z) continue;  // cannot reach alpha >= 1/255 (see ranges_and_pack_kernel)
+                    if (power < q1.z) continue;  // cannot reach alpha >= 1/255 (see preprocess_one)
                     const float alpha = min(0.99f, q1.y * exp(power));
                     if (alpha < 1.0f / 255.0f) continue;
                     const float test_T = T * (1 - alpha);
@@ -121,7 +114,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
                     C[1] += q2.y * alpha * T;
                     C[2] += q2.z * alpha * T;
                     T = test_T;
-                    last_contributor = (uint32_t)(c * kFwdChunk + j + 1);
+                    last_contributor = (uint32_t)(c * kChunk + j + 1);
                     s_used[s][j] = __float_as_int(q1.w) + 1;
                 }
             }
@@ -129,10 +122,8 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
     }
     __syncthreads();
     if (c == nchunks && nchunks > 0) flush_used(nchunks - 1);
-    // Drain bulk copies that were issued but never consumed (early exit) before the CTA retires.
-    if (tid == 0) {
-        for (int q = c; q < issued; ++q) mbar_wait(&s_full[q % kFwdStages], (uint32_t)((q / kFwdStages) & 1));
-    }
+    // Copies that were issued but never consumed (early exit) must land before the CTA retires.
+    st.drain(tid);
 
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, last_contributor);
     if (lane == 0 && wmax) atomicMax(&s_maxc, wmax);

@@ -36,6 +36,15 @@ struct Carver {
     }
 };
 
+// One 48-byte record per visible Gaussian: everything the tile renderers need about a splat.
+struct __align__(16) SplatRec {
+    float x, y, A, B;        // q0: pixel mean, conic.x, conic.y
+    float C, opacity, thr;   // q1: conic.z, opacity, conservative log-threshold for alpha >= 1/255
+    int id;                  //     Gaussian index
+    float r, g, b, depth;    // q2: colour, view-space depth
+};
+static_assert(sizeof(SplatRec) == 48, "SplatRec must be 48 bytes");
+
 // Per-Gaussian state written by preprocess, read by binning / render / backward.
 struct GeomWS {
     float* depths;            // [P]   view-space z
@@ -43,6 +52,7 @@ struct GeomWS {
     float4* conic_opacity;    // [P]   (A, B, C, opacity)
     float* rgb;               // [3P]  clamped SH colour
     float* cov3D;             // [6P]  upper triangle of Sigma
+    SplatRec* rec;            // [P]   48-byte render record of every visible Gaussian (what the tile renderers gather)
     uint8_t* clamped;         // [P]   bit c set when channel c was clamped to 0
     uint32_t* tiles_touched;  // [P]
     uint32_t* point_offsets;  // [P]   inclusive scan of tiles_touched taken in depth order
@@ -62,6 +72,7 @@ struct GeomWS {
         g.conic_opacity = c.take<float4>(P);
         g.rgb = c.take<float>(3 * P);
         g.cov3D = c.take<float>(6 * P);
+        g.rec = c.take<SplatRec>(P);
         g.clamped = c.take<uint8_t>(P);
         g.tiles_touched = c.take<uint32_t>(P);
         g.point_offsets = c.take<uint32_t>(P);
@@ -97,19 +108,10 @@ struct ImageWS {
     }
 };
 
-// One 48-byte record per (tile, splat) instance, in sorted order.
-struct __align__(16) SplatRec {
-    float x, y, A, B;        // q0: pixel mean, conic.x, conic.y
-    float C, opacity, thr;   // q1: conic.z, opacity, conservative log-threshold for alpha >= 1/255
-    int id;                  //     Gaussian index
-    float r, g, b, pad;      // q2: colour
-};
-static_assert(sizeof(SplatRec) == 48, "SplatRec must be 48 bytes");
 
 struct BinningWS {
     uint64_t* inst_a;   // [R] instances (tile << 32 | gaussian_idx) in emission (depth) order; ping-pong partner of inst_b
     uint64_t* inst_b;   // [R]
-    SplatRec* packed;   // [R] tile-ordered records (what render fwd/bwd stream)
     uint32_t* error_flag;  // [1] set by the sort if a look-back spin ran out
     char* sort_scratch; // histograms, tile tickets, look-back status words
     size_t sort_scratch_bytes;
@@ -119,9 +121,8 @@ struct BinningWS {
         const size_t Rp = R > 0 ? R : 1;
         Carver c(base);
         BinningWS b;
-        b.packed = c.take<SplatRec>(Rp);
-        b.inst_a = c.take<uint64_t>(Rp);
-        b.inst_b = c.take<uint64_t>(Rp);
+        b.inst_a = c.take<uint64_t>(Rp + 2);   // +2: the renderers' 16-byte-aligned bulk copies may read one entry past the end
+        b.inst_b = c.take<uint64_t>(Rp + 2);
         b.error_flag = c.take<uint32_t>(4);
         b.sort_scratch_bytes = radix_scratch_bytes(Rp, passes);
         b.sort_scratch = c.take<char>(b.sort_scratch_bytes);

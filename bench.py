@@ -301,14 +301,14 @@ def run_b200_arm(args):
 
     M = 16
     alg_bytes = {  # SURVEY.md §8(d) per-unit figures x units of this launch
-        "preprocess_fwd": visible * (44 + 12 * M + 75) + (P - visible) * 52,
+        "preprocess_fwd": visible * (44 + 12 * M + 75 + 48 + 8) + (P - visible) * 60,
         "depth_sort": P * 16,                       # read + write one u64 key per Gaussian (algorithmic minimum)
         "scan": P * 16,
         "emit_instances": P * 24 + R * 8,
         "tile_sort": R * 16,                         # read + write one u64 instance (algorithmic minimum; 2 passes move 40 B)
-        "ranges_pack": R * (8 + 40 + 48) + len(tile_len) * 8,
-        "render_fwd": R * 48 + W * H * 20,
-        "render_bwd": int(tmax.long().sum().item()) * 48 + W * H * 20 + visible * 36,
+        "tile_ranges": R * 8 + len(tile_len) * 8,
+        "render_fwd": R * (8 + 48) + W * H * 20,      # instance list streamed; 48-B records gathered (mostly L2 hits)
+        "render_bwd": int(tmax.long().sum().item()) * (8 + 48) + W * H * 20 + visible * 36,
         "preprocess_bwd": visible * (107 + 12 * M + 40 + 12 * M) + (P - visible) * (4 + 300),
         "bwd_zero": P * 36,
     }
@@ -317,7 +317,7 @@ def run_b200_arm(args):
         ms = stage_ms(name)
         if ms:
             stage_report[name] = {"ms": round(ms, 4), "alg_GBps": round(b / ms / 1e6, 1), "hbm_frac": round(b / ms / 1e6 / hbm_peak, 4)}
-    dom = max(("render_bwd", "render_fwd", "tile_sort", "preprocess_bwd", "preprocess_fwd", "ranges_pack"),
+    dom = max(("render_bwd", "render_fwd", "tile_sort", "preprocess_bwd", "preprocess_fwd", "emit_instances"),
               key=lambda n: stage_ms(n) or 0.0)
     dom_ms = stage_ms(dom)
     if dom in ("render_bwd", "render_fwd"):
