@@ -106,14 +106,14 @@ def test_arena_all_reduce_world_size_2_gloo(tmp_path):
             assert torch.all(v == 3.0 * (i + 1)), name
         assert dp.shard_views(6, r, 2) == [r, r + 2, r + 4]
         dist.destroy_process_group()
-        print("rank", r, "ok")
+        open(os.path.join({str(tmp_path)!r}, f"ok{{r}}"), "w").write("ok")
     """))
     port = _free_port()
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                           "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
                          capture_output=True, text=True, timeout=240)
     assert out.returncode == 0, out.stdout + out.stderr
-    assert "rank 0 ok" in out.stdout and "rank 1 ok" in out.stdout
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
 
 
 def test_camera_conventions():
