@@ -10,6 +10,7 @@
 // memset and dL_dmeans3D is never read back. Expressions follow the reference so results agree to
 // rounding; the three contributions to dL_dmeans3D are added in the reference's order
 // (covariance path, projection path, view-direction path).
+#include "bulk_copy.cuh"
 #include "gs_common.cuh"
 #include "kernels.cuh"
 #include "workspace.cuh"
@@ -22,17 +23,14 @@ GS_DEV void store3(float* __restrict__ dst, size_t idx, float a, float b, float 
     dst[3 * idx + 2] = c;
 }
 
-// SH backward: writes dL_dsh for coefficients [0, (deg+1)^2) and returns dL/dmean through the view direction.
-GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* __restrict__ sh, uint8_t clamp_bits,
-                          V3 dL_dRGB, float* __restrict__ dL_dsh) {
+// SH backward: returns dL/dmean through the view direction and writes dL_dsh for coefficients [0, (deg+1)^2).
+// `sh` and `dL_dsh` may be the same shared-memory row (see the kernel): every read of `sh` happens before the
+// first write of `dL_dsh`.
+GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* sh, uint8_t clamp_bits, V3 dL_dRGB,
+                          float* dL_dsh) {
     const V3 dir_orig = pos - campos;
     const V3 dir = dir_orig / sqrt(dot3(dir_orig, dir_orig));
     auto C = [&](int k) { return V3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]); };
-    auto W = [&](int k, float basis) {
-        dL_dsh[3 * k] = basis * dL_dRGB.x;
-        dL_dsh[3 * k + 1] = basis * dL_dRGB.y;
-        dL_dsh[3 * k + 2] = basis * dL_dRGB.z;
-    };
     // Clamped channels pass no gradient.
     dL_dRGB.x *= (clamp_bits & 1) ? 0.f : 1.f;
     dL_dRGB.y *= (clamp_bits & 2) ? 0.f : 1.f;
@@ -40,34 +38,18 @@ GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* _
 
     V3 dRGBdx(0.f, 0.f, 0.f), dRGBdy(0.f, 0.f, 0.f), dRGBdz(0.f, 0.f, 0.f);
     const float x = dir.x, y = dir.y, z = dir.z;
-
-    W(0, kSH0);
+    const float xx = x * x, yy = y * y, zz = z * z;
+    const float xy = x * y, yz = y * z, xz = x * z;
+    // ---- phase 1: derivative of the colour w.r.t. the view direction (reads the coefficients) ----
     if (deg > 0) {
-        W(1, -kSH1 * y);
-        W(2, kSH1 * z);
-        W(3, -kSH1 * x);
         dRGBdx = -kSH1 * C(3);
         dRGBdy = -kSH1 * C(1);
         dRGBdz = kSH1 * C(2);
         if (deg > 1) {
-            const float xx = x * x, yy = y * y, zz = z * z;
-            const float xy = x * y, yz = y * z, xz = x * z;
-            W(4, kSH2[0] * xy);
-            W(5, kSH2[1] * yz);
-            W(6, kSH2[2] * (2.f * zz - xx - yy));
-            W(7, kSH2[3] * xz);
-            W(8, kSH2[4] * (xx - yy));
             dRGBdx = dRGBdx + (kSH2[0] * y * C(4) + kSH2[2] * 2.f * -x * C(6) + kSH2[3] * z * C(7) + kSH2[4] * 2.f * x * C(8));
             dRGBdy = dRGBdy + (kSH2[0] * x * C(4) + kSH2[1] * z * C(5) + kSH2[2] * 2.f * -y * C(6) + kSH2[4] * 2.f * -y * C(8));
             dRGBdz = dRGBdz + (kSH2[1] * y * C(5) + kSH2[2] * 2.f * 2.f * z * C(6) + kSH2[3] * x * C(7));
             if (deg > 2) {
-                W(9, kSH3[0] * y * (3.f * xx - yy));
-                W(10, kSH3[1] * xy * z);
-                W(11, kSH3[2] * y * (4.f * zz - xx - yy));
-                W(12, kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
-                W(13, kSH3[4] * x * (4.f * zz - xx - yy));
-                W(14, kSH3[5] * z * (xx - yy));
-                W(15, kSH3[6] * x * (xx - 3.f * yy));
                 dRGBdx = dRGBdx + (kSH3[0] * C(9) * 3.f * 2.f * xy + kSH3[1] * C(10) * yz + kSH3[2] * C(11) * -2.f * xy +
                                    kSH3[3] * C(12) * -3.f * 2.f * xz + kSH3[4] * C(13) * (-3.f * xx + 4.f * zz - yy) +
                                    kSH3[5] * C(14) * 2.f * xz + kSH3[6] * C(15) * 3.f * (xx - yy));
@@ -82,7 +64,36 @@ GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* _
         }
     }
     const float3 dL_ddir = {dot3(dRGBdx, dL_dRGB), dot3(dRGBdy, dL_dRGB), dot3(dRGBdz, dL_dRGB)};
-    return dnormvdv3(float3{dir_orig.x, dir_orig.y, dir_orig.z}, dL_ddir);
+    const float3 dmean = dnormvdv3(float3{dir_orig.x, dir_orig.y, dir_orig.z}, dL_ddir);
+    // ---- phase 2: dL/dsh[k] = basis_k(dir) * dL/dRGB ----
+    auto W = [&](int k, float basis) {
+        dL_dsh[3 * k] = basis * dL_dRGB.x;
+        dL_dsh[3 * k + 1] = basis * dL_dRGB.y;
+        dL_dsh[3 * k + 2] = basis * dL_dRGB.z;
+    };
+    W(0, kSH0);
+    if (deg > 0) {
+        W(1, -kSH1 * y);
+        W(2, kSH1 * z);
+        W(3, -kSH1 * x);
+        if (deg > 1) {
+            W(4, kSH2[0] * xy);
+            W(5, kSH2[1] * yz);
+            W(6, kSH2[2] * (2.f * zz - xx - yy));
+            W(7, kSH2[3] * xz);
+            W(8, kSH2[4] * (xx - yy));
+            if (deg > 2) {
+                W(9, kSH3[0] * y * (3.f * xx - yy));
+                W(10, kSH3[1] * xy * z);
+                W(11, kSH3[2] * y * (4.f * zz - xx - yy));
+                W(12, kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
+                W(13, kSH3[4] * x * (4.f * zz - xx - yy));
+                W(14, kSH3[5] * z * (xx - yy));
+                W(15, kSH3[6] * x * (xx - 3.f * yy));
+            }
+        }
+    }
+    return dmean;
 }
 
 // Sigma = M^T M with M = S R: gradient w.r.t. scale and the (un-normalised) quaternion.
@@ -121,11 +132,76 @@ GS_DEV void cov3d_backward(const V3 scale, float mod, const float4 rot, const fl
     *dL_drot = dq;  // gradient w.r.t. the quaternion as given; normalisation is the caller's (PyTorch's) job
 }
 
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwdParams p) {
+constexpr int kPbThreads = 128;
+constexpr int kShMaxRow = 48;  // floats per SH row that the shared staging supports (M <= 16)
+
+// Coalesced staging of the warp's 32 SH rows (row r = Gaussian warp_first + r) between global memory and a
+// [32][row_stride] shared tile whose odd stride makes both the warp-wide copies and the per-thread row walks
+// bank-conflict free. A thread reading / writing its own 192-byte row straight from global memory touches 32
+// different lines per warp instruction; this way every warp instruction moves whole 128-byte lines.
+// kMrow > 0: compile-time row length (fully unrolled, loads issued as cp.async so that all of them are in flight
+// at once); kMrow == 0: run-time row length.
+template <bool kLoad, int kMrow>
+GS_DEV void stage_sh_rows(float* tile, int row_stride, float* gmem /* first row of the warp */, int Mrow_rt, int rows_valid,
+                          uint32_t row_mask, int ncoef3, int lane) {
+    const int Mrow = kMrow > 0 ? kMrow : Mrow_rt;
+    if (kMrow > 0) {
+#pragma unroll 12
+        for (int it = 0; it < kMrow; ++it) {
+            const int f = it * 32 + lane;
+            const int row = f / (kMrow > 0 ? kMrow : 1), col = f - row * Mrow;
+            if (row < rows_valid) {
+                const bool on = (row_mask >> row) & 1u;
+                if (kLoad) {
+                    if (on)
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(tile + row * row_stride + col)),
+                                     "l"(gmem + (size_t)row * Mrow + col)
+                                     : "memory");
+                } else {
+                    gmem[(size_t)row * Mrow + col] = (on && col < ncoef3) ? tile[row * row_stride + col] : 0.f;
+                }
+            }
+        }
+        return;  // loads: the caller waits (cp_async_wait_all) before reading the tile
+    }
+    int row = 0, col = lane;
+    while (col >= Mrow) { col -= Mrow; ++row; }
+    for (int it = 0; it < Mrow; ++it) {
+        if (row < rows_valid) {
+            const bool on = (row_mask >> row) & 1u;
+            if (kLoad) {
+                if (on) tile[row * row_stride + col] = gmem[(size_t)row * Mrow + col];
+            } else {
+                // rows of culled Gaussians and coefficients above the active degree are zero
+                gmem[(size_t)row * Mrow + col] = (on && col < ncoef3) ? tile[row * row_stride + col] : 0.f;
+            }
+        }
+        col += 32;
+        while (col >= Mrow) { col -= Mrow; ++row; }
+    }
+}
+
+__global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PreprocessBwdParams p) {
+    __shared__ float s_sh[kPbThreads / 32][32 * (kShMaxRow + 1)];
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= p.P) return;
-    const size_t i = (size_t)idx;
-    const bool visible = p.radii[idx] > 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool valid = idx < p.P;
+    const size_t i = (size_t)(valid ? idx : 0);
+    const bool visible = valid && p.radii[i] > 0;
+    // ---- SH rows in: one coalesced sweep per warp ----
+    const int Mrow = 3 * p.M;
+    const bool staged = p.shs != nullptr && Mrow <= kShMaxRow;
+    const int row_stride = Mrow | 1;
+    const int warp_first = idx - lane;
+    const int rows_valid = min(32, p.P - warp_first);
+    const uint32_t vis_mask = __ballot_sync(0xffffffffu, visible);
+    float* tile = &s_sh[warp][0];
+    if (staged && rows_valid > 0) {
+        float* src = const_cast<float*>(p.shs) + (size_t)warp_first * Mrow;
+        if (Mrow == 48) stage_sh_rows<true, 48>(tile, row_stride, src, Mrow, rows_valid, vis_mask, 0, lane);
+        else stage_sh_rows<true, 0>(tile, row_stride, src, Mrow, rows_valid, vis_mask, 0, lane);
+        // not waited for yet: the covariance / projection part below runs while the rows arrive
+    }
 
     float4 acc0 = make_float4(0.f, 0.f, 0.f, 0.f), acc1 = acc0;
     float acc2 = 0.f;
@@ -135,16 +211,19 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwd
         acc2 = p.acc_conic_w[idx];
     }
     // Pass-through outputs.
-    store3(p.dL_dmeans2D, i, acc1.x, acc1.y, 0.f);
-    store3(p.dL_dcolors, i, acc0.x, acc0.y, acc0.z);
-    p.dL_dopacity[idx] = acc0.w;
+    if (valid) {
+        store3(p.dL_dmeans2D, i, acc1.x, acc1.y, 0.f);
+        store3(p.dL_dcolors, i, acc0.x, acc0.y, acc0.z);
+        p.dL_dopacity[idx] = acc0.w;
+    }
 
     float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float3 dmean = {0.f, 0.f, 0.f};
     float dscale[3] = {0.f, 0.f, 0.f};
     float4 drot = make_float4(0.f, 0.f, 0.f, 0.f);
     const int ncoef = (p.D + 1) * (p.D + 1);
-    float* __restrict__ my_dsh = p.shs ? p.dL_dsh + i * p.M * 3 : nullptr;
+    float* my_dsh = p.shs ? (staged ? tile + lane * row_stride : p.dL_dsh + i * Mrow) : nullptr;
+    const float* my_sh = p.shs ? (staged ? tile + lane * row_stride : p.shs + i * Mrow) : nullptr;
 
     if (visible) {
         const float3 mean = {p.means3D[3 * i], p.means3D[3 * i + 1], p.means3D[3 * i + 2]};
@@ -230,10 +309,15 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwd
         dmean.y += dproj.y;
         dmean.z += dproj.z;
 
+    }
+    cp_async_wait_all();
+    __syncwarp();
+    if (visible) {
+        const float3 mean = {p.means3D[3 * i], p.means3D[3 * i + 1], p.means3D[3 * i + 2]};
         // ---- colour -> SH and view direction ----
         if (p.shs) {
             const V3 campos(p.campos[0], p.campos[1], p.campos[2]);
-            const float3 dsh_mean = sh_backward(p.D, V3(mean.x, mean.y, mean.z), campos, p.shs + i * p.M * 3,
+            const float3 dsh_mean = sh_backward(p.D, V3(mean.x, mean.y, mean.z), campos, my_sh,
                                                 p.clamped[idx], V3(acc0.x, acc0.y, acc0.z), my_dsh);
             dmean.x += dsh_mean.x;
             dmean.y += dsh_mean.y;
@@ -247,21 +331,31 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreprocessBwd
         }
     }
 
-    store3(p.dL_dmeans3D, i, dmean.x, dmean.y, dmean.z);
+    if (valid) {
+        store3(p.dL_dmeans3D, i, dmean.x, dmean.y, dmean.z);
 #pragma unroll
-    for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * i + k] = dcov[k];
-    store3(p.dL_dscales, i, dscale[0], dscale[1], dscale[2]);
-    reinterpret_cast<float4*>(p.dL_drots)[idx] = drot;
-    if (my_dsh) {
+        for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * i + k] = dcov[k];
+        store3(p.dL_dscales, i, dscale[0], dscale[1], dscale[2]);
+        reinterpret_cast<float4*>(p.dL_drots)[idx] = drot;
+    }
+    if (staged) {
+        // ---- SH gradient rows out: coalesced, zeros for culled Gaussians and unused coefficients ----
+        __syncwarp();
+        if (rows_valid > 0) {
+            float* dst = p.dL_dsh + (size_t)warp_first * Mrow;
+            if (Mrow == 48) stage_sh_rows<false, 48>(tile, row_stride, dst, Mrow, rows_valid, vis_mask, 3 * ncoef, lane);
+            else stage_sh_rows<false, 0>(tile, row_stride, dst, Mrow, rows_valid, vis_mask, 3 * ncoef, lane);
+        }
+    } else if (my_dsh && valid) {
         // Zero the coefficients the SH backward did not write (all of them for culled Gaussians).
         const int first = visible ? 3 * ncoef : 0;
-        for (int k = first; k < 3 * p.M; ++k) my_dsh[k] = 0.f;
+        for (int k = first; k < Mrow; ++k) my_dsh[k] = 0.f;
     }
 }
 
 int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream) {
     if (p.P <= 0) return GS_OK;
-    preprocess_bwd_kernel<<<(p.P + 255) / 256, 256, 0, stream>>>(p);
+    preprocess_bwd_kernel<<<(p.P + kPbThreads - 1) / kPbThreads, kPbThreads, 0, stream>>>(p);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
