@@ -1,33 +1,178 @@
-// Backward tile renderer for sm_100a: back-to-front replay of the blend with warp-aggregated gradient
-// reductions.
+// Backward tile renderer for sm_100a: back-to-front replay of the blend with deferred, moment-based
+// gradient reductions.
 //
 // Same CTA / warp / pixel mapping and the same staging as the forward (bulk-copied instance slices,
 // cp.async-gathered 48-byte records, see render_common.cuh), streamed in reverse and only up to the
 // tile's last blended position (tile_max_contrib, recorded by the forward) instead of the end of the
-// tile's list. Per (pixel, splat) pair the recomputation of G and alpha and every gradient expression
-// follow the reference (cuda_rasterizer/backward.cu:399-557). The reference issues 9 scalar float
-// atomics per contributing pair; here each warp culls splats that cannot touch its 8x4 patch, reduces the
-// nine per-pair terms over its 32 pixels with a fold tree (14 shuffles) and issues one predicated
-// red.global.add.f32 from nine lanes per (warp, splat) — and nothing at all when no lane of the warp
-// blended the splat. Summation order differs from the reference (as it does between two runs of the
-// reference), hence tolerance parity on gradients.
+// tile's list. Per (pixel, splat) pair the recomputation of G and alpha and the expression for dL/dalpha
+// follow the reference (cuda_rasterizer/backward.cu:399-557).
+//
+// The reference issues 9 scalar float atomics per contributing pair (backward.cu:523-554). All nine sums
+// over the pixels of a warp's 8x4 patch are linear in just two per-pixel scalars,
+//     u = alpha * T                     (colour:   dL/dc_ch  = sum_pix u * dL/dpix_ch)
+//     w = G * dL/dalpha                 (opacity:  dL/do     = sum_pix w)
+// because with d = (X - px, Y - py), px = patch_x0 + lx, py = patch_y0 + ly (lx 0..7, ly 0..3 are lane constants)
+//     dL/dmean2D, dL/dconic  are  o * {A, B, C}-weighted combinations of  sum w*dx, sum w*dy, sum w*dx^2,
+//     sum w*dx*dy, sum w*dy^2,  and those follow from the six moments  sum w * {1, lx, ly, lx^2, lx*ly, ly^2}.
+// So each warp appends (u, w) of every splat it blended as one 32-float row pair to a small shared-memory
+// buffer (two STS per splat instead of a 14-shuffle fold tree) and, every ROWS splats, reduces the rows
+// as a tiny dense product against lane-constant coefficients: lane (row r, column group g) sums its
+// columns with immediates for lx / ly, the groups combine with one or two butterfly steps, and the row's
+// owner issues three reductions (two 16-byte `red.global.add.v4.f32`, one scalar) for the whole patch.
+// Summation order differs from the reference (as it does between two runs of the reference), hence
+// tolerance parity on gradients.
 #include "bulk_copy.cuh"
 #include "gs_common.cuh"
 #include "kernels.cuh"
 #include "render_common.cuh"
 #include "workspace.cuh"
 
+#include <cstdlib>
+
 namespace gs {
 
 GS_DEV void red_add_f32(float* addr, const float v) {
     asm volatile("red.global.add.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
 }
+GS_DEV void red_add_f32x4(float4* addr, const float a, const float b, const float c, const float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 
-__global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwdParams p) {
-    __shared__ __align__(128) SplatRec s_rec[kRecStages][kChunk];
-    __shared__ __align__(16) uint64_t s_inst[kInstStages][kChunk + 2];
-    __shared__ __align__(8) uint64_t s_inst_full[kInstStages];
-    __shared__ __align__(8) uint64_t s_rec_full[kRecStages];
+constexpr int kBwdWarps = GS_TILE_PIX / 32;
+
+// Dynamic shared-memory layout of render_bwd_kernel<CH, ROWS>.
+template <int CH, int ROWS>
+struct BwdSmem {
+    static constexpr size_t kRec = 0;
+    static constexpr size_t kInst = kRec + sizeof(SplatRec) * kRecStages * CH;
+    static constexpr size_t kInstFull = kInst + sizeof(uint64_t) * kInstStages * (CH + 2);
+    static constexpr size_t kRecFull = kInstFull + sizeof(uint64_t) * kInstStages;
+    static constexpr size_t kRows = (kRecFull + sizeof(uint64_t) * kRecStages + 127) / 128 * 128;
+    static constexpr size_t kDpix = kRows + sizeof(float) * kBwdWarps * 2 * ROWS * 32;
+    static constexpr size_t kBytes = kDpix + sizeof(float4) * kBwdWarps * 32;
+};
+
+// Reduce the pending rows of one warp and add them to the per-Gaussian accumulators.
+// U, W: [ROWS][32] floats, element (row, lane) at row*32 + (lane ^ ((row & 7) << 2)) (16-byte chunks XOR-swizzled by
+// the row so that both the row-wise appends and the row-per-lane float4 reads are bank-conflict free).
+template <int ROWS>
+GS_DEV void flush_rows(const RenderBwdParams& p, const float* __restrict__ U, const float* __restrict__ W,
+                                        const float4* __restrict__ dpix, const int nrows, const int myid, const int lane,
+                                        const float patch_x0, const float patch_y0) {
+    constexpr int GROUPS = 32 / ROWS;        // column groups per row (2 or 4)
+    constexpr int COLS = 32 / GROUPS;        // columns per lane (16 or 8)
+    const int r = lane & (ROWS - 1), g = lane / ROWS;
+    const bool valid = r < nrows;
+    float4 m0 = {0.f, 0.f, 0.f, 0.f}, m1 = {0.f, 0.f, 0.f, 0.f};
+    if (valid) {  // x, y, A, B | C, opacity, thr, id of the row's splat (L2-resident: this CTA gathered it moments ago)
+        const float4* rp = reinterpret_cast<const float4*>(p.rec + myid);
+        m0 = __ldg(rp);
+        m1 = __ldg(rp + 1);
+    }
+    const float4* Ur = reinterpret_cast<const float4*>(U + r * 32);
+    const float4* Wr = reinterpret_cast<const float4*>(W + r * 32);
+    const float4* dp = dpix + COLS * g;
+    const int sw = r & 7;
+    float cr = 0.f, cg = 0.f, cb = 0.f;
+    float wv[COLS];
+#pragma unroll
+    for (int q = 0; q < COLS / 4; ++q) {
+        const int chunk = ((COLS / 4) * g + q) ^ sw;
+        const float4 u4 = Ur[chunk], w4 = Wr[chunk];
+        wv[4 * q + 0] = w4.x; wv[4 * q + 1] = w4.y; wv[4 * q + 2] = w4.z; wv[4 * q + 3] = w4.w;
+        const float uu[4] = {u4.x, u4.y, u4.z, u4.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float4 d = dp[4 * q + e];
+            cr = fmaf(uu[e], d.x, cr);
+            cg = fmaf(uu[e], d.y, cg);
+            cb = fmaf(uu[e], d.z, cb);
+        }
+    }
+    // Moments of w over this lane's columns; column c of the warp is pixel (lx, ly) = (c & 7, c >> 3).
+    float S0, Sx, Sy, Sxx, Sxy, Syy;
+    if constexpr (ROWS == 16) {
+        // columns 16g .. 16g+15: ly = 2g + (k >> 3), lx = k & 7
+        float c8[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) c8[k] = wv[k] + wv[8 + k];
+        S0 = c8[0]; Sx = 0.f; Sxx = 0.f;
+        float Sy1 = wv[8], Sxy1 = 0.f;
+#pragma unroll
+        for (int k = 1; k < 8; ++k) {
+            S0 += c8[k];
+            Sx = fmaf((float)k, c8[k], Sx);
+            Sxx = fmaf((float)(k * k), c8[k], Sxx);
+            Sy1 += wv[8 + k];
+            Sxy1 = fmaf((float)k, wv[8 + k], Sxy1);
+        }
+        const float hf = (float)(2 * g);  // ly = ly' + hf with ly' in {0, 1}: ly^2 = ly' + 2 hf ly' + hf^2
+        Sy = fmaf(hf, S0, Sy1);
+        Sxy = fmaf(hf, Sx, Sxy1);
+        Syy = fmaf(hf, fmaf(hf, S0, 2.f * Sy1), Sy1);
+    } else {
+        // columns 8g .. 8g+7: ly = g, lx = k
+        S0 = wv[0]; Sx = 0.f; Sxx = 0.f;
+#pragma unroll
+        for (int k = 1; k < 8; ++k) {
+            S0 += wv[k];
+            Sx = fmaf((float)k, wv[k], Sx);
+            Sxx = fmaf((float)(k * k), wv[k], Sxx);
+        }
+        const float gf = (float)g;
+        Sy = gf * S0;
+        Sxy = gf * Sx;
+        Syy = gf * Sy;
+    }
+#pragma unroll
+    for (int msk = 16; msk >= ROWS; msk >>= 1) {
+        cr += __shfl_xor_sync(0xffffffffu, cr, msk);
+        cg += __shfl_xor_sync(0xffffffffu, cg, msk);
+        cb += __shfl_xor_sync(0xffffffffu, cb, msk);
+        S0 += __shfl_xor_sync(0xffffffffu, S0, msk);
+        Sx += __shfl_xor_sync(0xffffffffu, Sx, msk);
+        Sy += __shfl_xor_sync(0xffffffffu, Sy, msk);
+        Sxx += __shfl_xor_sync(0xffffffffu, Sxx, msk);
+        Sxy += __shfl_xor_sync(0xffffffffu, Sxy, msk);
+        Syy += __shfl_xor_sync(0xffffffffu, Syy, msk);
+    }
+    if (valid) {
+        if (g == 0) {
+            red_add_f32x4(p.acc_color_opacity + myid, cr, cg, cb, S0);
+        } else {
+            // d = (Xp - lx, Yp - ly): sum w dx = Xp S0 - Sx, sum w dx^2 = Xp (Xp S0 - Sx) - (Xp Sx - Sxx), ...
+            const float Xp = m0.x - patch_x0, Yp = m0.y - patch_y0;
+            const float A = m0.z, B = m0.w, C = m1.x, o = m1.y;
+            const float Mx = fmaf(Xp, S0, -Sx), My = fmaf(Yp, S0, -Sy);
+            if (g == 1) {
+                const float Mxx = fmaf(Xp, Mx, -fmaf(Xp, Sx, -Sxx));
+                const float Mxy = fmaf(Xp, My, -fmaf(Yp, Sx, -Sxy));
+                // Gradient of pixel coordinates w.r.t. normalised screen coordinates (reference backward.cu:460-461).
+                const float ddelx_dx = 0.5f * p.W, ddely_dy = 0.5f * p.H;
+                const float ho = -0.5f * o;
+                red_add_f32x4(p.acc_mean_conic + myid, o * (-A * Mx - B * My) * ddelx_dx, o * (-C * My - B * Mx) * ddely_dy,
+                              ho * Mxx, ho * Mxy);
+                if constexpr (GROUPS == 2) {
+                    const float Myy = fmaf(Yp, My, -fmaf(Yp, Sy, -Syy));
+                    red_add_f32(p.acc_conic_w + myid, ho * Myy);
+                }
+            } else if (GROUPS > 2 && g == 2) {
+                const float Myy = fmaf(Yp, My, -fmaf(Yp, Sy, -Syy));
+                red_add_f32(p.acc_conic_w + myid, -0.5f * o * Myy);
+            }
+        }
+    }
+    __syncwarp();  // the rows may be overwritten once every lane has read them
+}
+
+template <int CH, int ROWS, int MIN_CTAS>
+__global__ void __launch_bounds__(GS_TILE_PIX, MIN_CTAS) render_bwd_kernel(const RenderBwdParams p) {
+    using L = BwdSmem<CH, ROWS>;
+    extern __shared__ __align__(128) unsigned char smem[];
+    SplatRec* s_rec = reinterpret_cast<SplatRec*>(smem + L::kRec);
+    uint64_t* s_inst = reinterpret_cast<uint64_t*>(smem + L::kInst);
+    uint64_t* s_inst_full = reinterpret_cast<uint64_t*>(smem + L::kInstFull);
+    uint64_t* s_rec_full = reinterpret_cast<uint64_t*>(smem + L::kRecFull);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x;
@@ -41,14 +186,18 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwd
 
     const uint2 range = p.ranges[tile];
     const int n_total = min((int)(range.y - range.x), (int)p.tile_max_contrib[tile]);
-    const int nchunks = (n_total + kChunk - 1) / kChunk;
+    const int nchunks = (n_total + CH - 1) / CH;
     if (nchunks == 0) return;
 
-    if (tid == 0) stager_init(s_inst_full, s_rec_full);
+    if (tid == 0) stager_init<CH>(s_inst_full, s_rec_full);
     __syncthreads();
     // Stream chunk k is list chunk c = nchunks-1-k.
-    Stager st(p.inst, p.rec, range.x, n_total, nchunks, /*reversed=*/true, &s_inst[0][0], s_inst_full, &s_rec[0][0], s_rec_full);
+    Stager<CH> st(p.inst, p.rec, range.x, n_total, nchunks, /*reversed=*/true, s_inst, s_inst_full, s_rec, s_rec_full);
     st.prologue(tid);
+
+    float* const U = reinterpret_cast<float*>(smem + L::kRows) + warp * (2 * ROWS * 32);
+    float* const W = U + ROWS * 32;
+    float4* const dpix = reinterpret_cast<float4*>(smem + L::kDpix) + warp * 32;
 
     const size_t plane = (size_t)p.H * p.W;
     const float T_final = inside ? p.final_T[pix_id] : 0.f;
@@ -61,6 +210,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwd
         dL_dpixel[1] = p.dL_dpix[1 * plane + pix_id];
         dL_dpixel[2] = p.dL_dpix[2 * plane + pix_id];
     }
+    dpix[lane] = make_float4(dL_dpixel[0], dL_dpixel[1], dL_dpixel[2], 0.f);
     float bg_dot_dpixel = 0.f;
 #pragma unroll
     for (int i = 0; i < 3; ++i) bg_dot_dpixel += p.bg[i] * dL_dpixel[i];
@@ -68,21 +218,20 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwd
     float accum_rec[3] = {0.f, 0.f, 0.f};
     float last_alpha = 0.f;
     float last_color[3] = {0.f, 0.f, 0.f};
-    // Gradient of pixel coordinates w.r.t. normalised screen coordinates.
-    const float ddelx_dx = 0.5 * p.W;
-    const float ddely_dy = 0.5 * p.H;
-    const bool b4 = (lane & 16) != 0, b3 = (lane & 8) != 0, b2 = (lane & 4) != 0;
+    int nrows = 0;   // pending rows of this warp (uniform)
+    int myid = 0;    // Gaussian index of pending row (lane & (ROWS-1))
+    __syncwarp();
 
     for (int k = 0; k < nchunks; ++k) {
         if (k > 0) __syncthreads();  // every warp is done with chunk k-1: its stages can be refilled
         st.advance(tid, k);
         const int s = k % kRecStages;
         const int c = nchunks - 1 - k;
-        const int n = min(kChunk, n_total - c * kChunk);
+        const int n = min(CH, n_total - c * CH);
         mbar_wait(&s_rec_full[s], (uint32_t)((k / kRecStages) & 1));
-        const float4* __restrict__ rec = reinterpret_cast<const float4*>(&s_rec[s][0]);
+        const float4* __restrict__ rec = reinterpret_cast<const float4*>(s_rec + s * CH);
         // Positions >= warp_last were blended by no pixel of this warp.
-        const int jstart = min(n - 1, warp_last - 1 - c * kChunk);
+        const int jstart = min(n - 1, warp_last - 1 - c * CH);
         // Lane-parallel patch cull (see render_common.cuh), 32 list positions at a time, walked back to front.
         for (int base = jstart & ~31; base >= 0; base -= 32) {
             const int jt = base + lane;
@@ -96,7 +245,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwd
                 const int b = 31 - __clz(m);
                 m &= ~(1u << b);
                 const int j = base + b;
-                const int pos = c * kChunk + j;  // 0-based position in the tile list
+                const int pos = c * CH + j;  // 0-based position in the tile list
                 const float4 q0 = rec[3 * j];       // x, y, A, B
                 const float4 q1 = rec[3 * j + 1];   // C, opacity, thr, id
                 const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
@@ -108,10 +257,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwd
                 act = act && !(alpha < 1.0f / 255.0f);
                 if (!__any_sync(0xffffffffu, act)) continue;
 
-                float v[8];
-                float v8 = 0.f;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = 0.f;
+                float u = 0.f, w = 0.f;
                 if (act) {
                     const float4 q2 = rec[3 * j + 2];  // r, g, b
                     const float col[3] = {q2.x, q2.y, q2.z};
@@ -119,78 +265,58 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_bwd_kernel(const RenderBwd
                     // divisions; the difference is far inside the gradient tolerance.
                     const float inv_1ma = __fdividef(1.0f, 1.f - alpha);
                     T = T * inv_1ma;
-                    const float dchannel_dcolor = alpha * T;
+                    u = alpha * T;
                     float dL_dalpha = 0.0f;
 #pragma unroll
                     for (int ch = 0; ch < 3; ++ch) {
                         const float cc = col[ch];
                         accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
                         last_color[ch] = cc;
-                        const float dL_dchannel = dL_dpixel[ch];
-                        dL_dalpha += (cc - accum_rec[ch]) * dL_dchannel;
-                        v[ch] = dchannel_dcolor * dL_dchannel;
+                        dL_dalpha += (cc - accum_rec[ch]) * dL_dpixel[ch];
                     }
                     dL_dalpha *= T;
                     last_alpha = alpha;
                     dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
-
-                    const float dL_dG = q1.y * dL_dalpha;
-                    const float gdx = G * d.x;
-                    const float gdy = G * d.y;
-                    const float dG_ddelx = -gdx * q0.z - gdy * q0.w;
-                    const float dG_ddely = -gdy * q1.x - gdx * q0.w;
-                    v[3] = G * dL_dalpha;                    // opacity
-                    v[4] = dL_dG * dG_ddelx * ddelx_dx;      // mean2D.x
-                    v[5] = dL_dG * dG_ddely * ddely_dy;      // mean2D.y
-                    v[6] = -0.5f * gdx * d.x * dL_dG;        // conic.x
-                    v[7] = -0.5f * gdx * d.y * dL_dG;        // conic.y
-                    v8 = -0.5f * gdy * d.y * dL_dG;          // conic.w
+                    w = G * dL_dalpha;
                 }
-                // Fold tree: 8 values -> 4 -> 2 -> 1 per lane over lane bits 4, 3, 2 (7 shuffles), then two plain
-                // exchanges over bits 1, 0: lane 4k ends with the warp total of v[k]. v8 takes a 5-step butterfly.
-                float r4[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float send = b4 ? v[i] : v[i + 4];
-                    const float keep = b4 ? v[i + 4] : v[i];
-                    r4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-                }
-                float r2[2];
-#pragma unroll
-                for (int i = 0; i < 2; ++i) {
-                    const float send = b3 ? r4[i] : r4[i + 2];
-                    const float keep = b3 ? r4[i + 2] : r4[i];
-                    r2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-                }
-                float r1;
-                {
-                    const float send = b2 ? r2[0] : r2[1];
-                    const float keep = b2 ? r2[1] : r2[0];
-                    r1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-                }
-                r1 += __shfl_xor_sync(0xffffffffu, r1, 2);
-                r1 += __shfl_xor_sync(0xffffffffu, r1, 1);
-#pragma unroll
-                for (int msk = 16; msk >= 1; msk >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, msk);
-                const int id = __float_as_int(q1.w);
-                // lane 4k adds v[k] (k < 4: colour.rgb, opacity; k >= 4: mean2D.xy, conic.xy); lane 1 adds conic.w
-                if ((lane & 3) == 0) {
-                    float* dst = reinterpret_cast<float*>((lane & 16 ? p.acc_mean_conic : p.acc_color_opacity) + id) + ((lane >> 2) & 3);
-                    red_add_f32(dst, r1);
-                } else if (lane == 1) {
-                    red_add_f32(p.acc_conic_w + id, v8);
+                // Append the splat's row: lane l holds pixel l's (u, w).
+                const int col_sw = lane ^ ((nrows & 7) << 2);
+                U[nrows * 32 + col_sw] = u;
+                W[nrows * 32 + col_sw] = w;
+                if ((lane & (ROWS - 1)) == nrows) myid = __float_as_int(q1.w);
+                if (++nrows == ROWS) {
+                    __syncwarp();
+                    flush_rows<ROWS>(p, U, W, dpix, ROWS, myid, lane, patch_x0, patch_y0);
+                    nrows = 0;
                 }
             }
         }
     }
+    if (nrows > 0) {
+        __syncwarp();
+        flush_rows<ROWS>(p, U, W, dpix, nrows, myid, lane, patch_x0, patch_y0);
+    }
     st.drain(tid);  // every copy was consumed (no early exit); this only retires the cp.async groups
+}
+
+template <int CH, int ROWS, int MIN_CTAS>
+static int launch_variant(const RenderBwdParams& p, int tiles, cudaStream_t stream) {
+    auto kern = render_bwd_kernel<CH, ROWS, MIN_CTAS>;
+    constexpr size_t bytes = BwdSmem<CH, ROWS>::kBytes;
+    GS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    kern<<<tiles, GS_TILE_PIX, bytes, stream>>>(p);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
 }
 
 int launch_render_bwd(const RenderBwdParams& p, int tiles, cudaStream_t stream) {
     if (tiles <= 0) return GS_OK;
-    render_bwd_kernel<<<tiles, GS_TILE_PIX, 0, stream>>>(p);
-    GS_LAUNCH_CHECK();
-    return GS_OK;
+    static const int variant = [] { const char* e = getenv("GS_BWD_VARIANT"); return e ? atoi(e) : 0; }();
+    switch (variant) {
+        case 1: return launch_variant<64, 16, 4>(p, tiles, stream);
+        case 2: return launch_variant<128, 8, 4>(p, tiles, stream);
+        default: return launch_variant<128, 16, 3>(p, tiles, stream);
+    }
 }
 
 }  // namespace gs

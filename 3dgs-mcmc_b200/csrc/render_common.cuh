@@ -64,15 +64,19 @@ constexpr int kInstStages = 4;
 constexpr int kGatherAhead = 2;
 static_assert(kChunk % 2 == 0, "chunk starts must keep the parity of the tile's first instance");
 
+template <int CH = kChunk>
 GS_DEV void stager_init(uint64_t* inst_full, uint64_t* rec_full) {
 #pragma unroll
     for (int s = 0; s < kInstStages; ++s) mbar_init(&inst_full[s], 1);
 #pragma unroll
-    for (int s = 0; s < kRecStages; ++s) mbar_init(&rec_full[s], kChunk);
+    for (int s = 0; s < kRecStages; ++s) mbar_init(&rec_full[s], CH);
     mbar_fence_init();
 }
 
+// CH = records per chunk (the forward uses kChunk; the backward picks its own to fit its shared-memory budget).
+template <int CH = kChunk>
 struct Stager {
+    static_assert(CH % 2 == 0 && CH <= GS_TILE_PIX, "chunk starts must keep the parity of the tile's first instance");
     const uint64_t* __restrict__ inst;
     const SplatRec* __restrict__ rec;
     uint32_t first;
@@ -92,28 +96,28 @@ struct Stager {
           inst_full(inst_full_), s_rec(s_rec_), rec_full(rec_full_), odd((int)(first_ & 1u)), inst_issued(0), gathered(0) {}
 
     GS_DEV int list_chunk(int k) const { return reversed ? nchunks - 1 - k : k; }
-    GS_DEV int chunk_n(int lc) const { return min(kChunk, n_total - lc * kChunk); }
+    GS_DEV int chunk_n(int lc) const { return min(CH, n_total - lc * CH); }
 
     // Thread 0: bulk-copy the instance slice of stream chunk k. Bulk copies move 16-byte units from 16-byte
     // aligned addresses, so the copy starts one entry early when the slice starts at an odd index and may
     // run one entry past its end (the instance arrays are padded for that).
     GS_DEV void issue_inst(int k) {
         const int lc = list_chunk(k), n = chunk_n(lc), s = k % kInstStages;
-        const size_t start = (size_t)first + (size_t)lc * kChunk;
+        const size_t start = (size_t)first + (size_t)lc * CH;
         const uint32_t bytes = (uint32_t)((n + odd + 1) & ~1) * 8u;
         mbar_arrive_expect_tx(&inst_full[s], bytes);
-        bulk_copy_g2s(s_inst + s * (kChunk + 2), inst + (start - odd), bytes, &inst_full[s]);
+        bulk_copy_g2s(s_inst + s * (CH + 2), inst + (start - odd), bytes, &inst_full[s]);
     }
 
-    // Threads 0..kChunk-1: gather the records of stream chunk k (its instances must have been issued).
+    // Threads 0..CH-1: gather the records of stream chunk k (its instances must have been issued).
     GS_DEV void gather(int tid, int k) {
-        if (tid < kChunk) {
+        if (tid < CH) {
             const int lc = list_chunk(k), n = chunk_n(lc), si = k % kInstStages, sr = k % kRecStages;
             mbar_wait(&inst_full[si], (uint32_t)((k / kInstStages) & 1));
             if (tid < n) {
-                const uint32_t id = (uint32_t)s_inst[si * (kChunk + 2) + odd + tid];
+                const uint32_t id = (uint32_t)s_inst[si * (CH + 2) + odd + tid];
                 const float4* src = reinterpret_cast<const float4*>(rec + id);
-                float4* dst = reinterpret_cast<float4*>(s_rec + sr * kChunk + tid);
+                float4* dst = reinterpret_cast<float4*>(s_rec + sr * CH + tid);
                 cp_async_16(dst, src);
                 cp_async_16(dst + 1, src + 1);
                 cp_async_16(dst + 2, src + 2);

@@ -45,12 +45,12 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
     for (int i = tid; i < kRecStages * kChunk; i += GS_TILE_PIX) (&s_used[0][0])[i] = 0;
     if (tid == 0) {
         s_maxc = 0;
-        stager_init(s_inst_full, s_rec_full);
+        stager_init<kChunk>(s_inst_full, s_rec_full);
     }
     __syncthreads();
 
     // List chunk c covers positions [c*kChunk, c*kChunk + n) of the tile's list.
-    Stager st(p.inst, p.rec, range.x, n_total, nchunks, /*reversed=*/false, &s_inst[0][0], s_inst_full, &s_rec[0][0], s_rec_full);
+    Stager<kChunk> st(p.inst, p.rec, range.x, n_total, nchunks, /*reversed=*/false, &s_inst[0][0], s_inst_full, &s_rec[0][0], s_rec_full);
     st.prologue(tid);
 
     auto flush_used = [&](int c) {
