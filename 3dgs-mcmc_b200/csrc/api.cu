@@ -62,7 +62,7 @@ inline void count_launches(int k) { g_prof.launches += (unsigned long long)k; }
 
 extern "C" {
 
-int gs_abi_version(void) { return 101; }
+int gs_abi_version(void) { return 102; }
 
 const char* gs_error_string(int code) {
     if (code == GS_OK) return "ok";
@@ -107,7 +107,7 @@ unsigned long long gs_launch_count(void) { return g_prof.launches; }
 size_t gs_geom_bytes(int P) { return GeomWS::carve(nullptr, (size_t)(P > 0 ? P : 0)).bytes + kAlign; }
 size_t gs_image_bytes(int W, int H) { return ImageWS::carve(nullptr, (size_t)W, (size_t)H).bytes + kAlign; }
 size_t gs_binning_bytes(unsigned int R, int W, int H) {
-    return BinningWS::carve(nullptr, R, sort_passes(tiles_of(W, H, nullptr))).bytes + kAlign;
+    return BinningWS::carve(nullptr, R, tiles_of(W, H, nullptr)).bytes + kAlign;
 }
 size_t gs_backward_scratch_bytes(int P) { return BwdScratch::carve(nullptr, (size_t)(P > 0 ? P : 0)).bytes + kAlign; }
 
@@ -146,6 +146,7 @@ int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means
     pp.radii = radii; pp.is_used = is_used; pp.means2D = g.means2D; pp.depths = g.depths; pp.cov3D = g.cov3D;
     pp.rgb = g.rgb; pp.conic_opacity = g.conic_opacity; pp.tiles_touched = g.tiles_touched; pp.clamped = g.clamped;
     pp.rec = g.rec; pp.depth_keys = g.dkeys_a; pp.num_rendered = g.num_rendered;
+    pp.rect = g.rect;
     prof_mark(stream, -1);
     GS_CUDA_TRY(cudaMemsetAsync(g.num_rendered, 0, 16, stream));
     int rc = launch_preprocess_fwd(pp, stream);
@@ -159,7 +160,7 @@ int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means
     rc = launch_radix_sort(g.dkeys_a, g.dkeys_b, (uint32_t)P, 32, kDepthSortPasses, g.dsort_scratch, g.num_rendered + 1, stream);
     if (rc) return rc;
     prof_mark(stream, ST_DEPTH_SORT);
-    rc = launch_inclusive_scan(g.tiles_touched, g.dkeys_a, P, g.point_offsets, g.scan_block_sums, stream);
+    rc = launch_inclusive_scan(g.rect, g.dkeys_a, P, g.point_offsets, g.emit, g.scan_block_sums, stream);
     if (rc) return rc;
     prof_mark(stream, ST_SCAN);
     count_launches(1 + 2 + kDepthSortPasses + 3);
@@ -175,36 +176,50 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
     if (R >= (1u << 30)) return GS_ERR_ARG;
     uint2 grid;
     const uint32_t tiles = tiles_of(W, H, &grid);
-    const int passes = sort_passes(tiles);
     ImageWS img = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
-    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, passes);
+    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, tiles);
     if (P == 0) R = 0;
 
     int rc = GS_OK;
     prof_mark(stream, -1);
     if (P > 0) GS_CUDA_TRY(cudaMemsetAsync(b.error_flag, 0, 16, stream));
-    if (R > 0) {
-        rc = launch_emit_instances(P, g.dkeys_a, g.means2D, g.point_offsets, radii, grid, b.inst_a, stream);
-        if (rc) return rc;
-        prof_mark(stream, ST_DUPLICATE);
-        rc = launch_radix_sort(b.inst_a, b.inst_b, R, 32, passes, b.sort_scratch, b.error_flag, stream);
+    if (P > 0 && bin_fast_path(tiles)) {
+        // Two fused binning passes (count -> scan -> scatter each); the tile ranges fall out of the second count.
+        int bits1, bits2;
+        bin_digit_bits(tiles, &bits1, &bits2);
+        rc = launch_fast_binning(P, R, grid, tiles, bits1, bits2, g.emit, g.point_offsets, b, img.ranges, stream);
         if (rc) return rc;
         prof_mark(stream, ST_SORT);
-        count_launches(3 + passes);
+        count_launches(R > 0 ? 7 : 0);
+    } else {
+        // Generic path (tile ids wider than two binning digits): emission, multi-pass radix sort, range detection.
+        const int passes = sort_passes(tiles);
+        if (R > 0) {
+            rc = launch_emit_instances(P, g.dkeys_a, g.means2D, g.point_offsets, radii, grid, b.inst_a, stream);
+            if (rc) return rc;
+            prof_mark(stream, ST_DUPLICATE);
+            rc = launch_radix_sort(b.inst_a, b.inst_b, R, 32, passes, b.sort_scratch, b.error_flag, stream);
+            if (rc) return rc;
+            rc = launch_strip_ids(R, b.sorted(passes), b.ids, stream);
+            if (rc) return rc;
+            prof_mark(stream, ST_SORT);
+            count_launches(4 + passes);
+        }
+        rc = launch_tile_ranges(R, b.sorted(passes), img.ranges, tiles, stream);
+        if (rc) return rc;
+        prof_mark(stream, ST_PACK);
+        count_launches(1);
     }
     (void)colors_precomp;  // already folded into the render records by the preprocess stage
-    rc = launch_tile_ranges(R, b.sorted(passes), img.ranges, tiles, stream);
-    if (rc) return rc;
-    prof_mark(stream, ST_PACK);
-    count_launches(R > 0 ? 2 : 1);
 
     RenderFwdParams rp;
-    rp.ranges = img.ranges; rp.inst = b.sorted(passes); rp.rec = g.rec; rp.W = W; rp.H = H; rp.tiles_x = (int)grid.x; rp.bg = background;
+    rp.ranges = img.ranges; rp.ids = b.ids; rp.rec = g.rec; rp.W = W; rp.H = H; rp.tiles_x = (int)grid.x; rp.bg = background;
     rp.final_T = img.final_T; rp.n_contrib = img.n_contrib; rp.out_color = out_color; rp.is_used = is_used;
     rp.tile_max_contrib = img.tile_max_contrib;
     rc = launch_render_fwd(rp, (int)tiles, stream);
     prof_mark(stream, ST_RENDER_FWD);
+    count_launches(1);
     return rc;
 }
 
@@ -226,10 +241,9 @@ int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H
     if (shs && (!dL_dsh || !campos)) return GS_ERR_ARG;
     uint2 grid;
     const uint32_t tiles = tiles_of(W, H, &grid);
-    const int passes = sort_passes(tiles);
     ImageWS img = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
-    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, passes);
+    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, tiles);
     BwdScratch sc = BwdScratch::carve(aligned_base(scratch), (size_t)P);
     prof_mark(stream, -1);
     GS_CUDA_TRY(cudaMemsetAsync(sc.acc_color_opacity, 0, sc.bytes, stream));
@@ -238,7 +252,7 @@ int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H
     int rc = GS_OK;
     if (R > 0) {
         RenderBwdParams rb;
-        rb.ranges = img.ranges; rb.inst = b.sorted(passes); rb.rec = g.rec; rb.tile_max_contrib = img.tile_max_contrib;
+        rb.ranges = img.ranges; rb.ids = b.ids; rb.rec = g.rec; rb.tile_max_contrib = img.tile_max_contrib;
         rb.W = W; rb.H = H; rb.tiles_x = (int)grid.x; rb.bg = background; rb.final_T = img.final_T;
         rb.n_contrib = img.n_contrib; rb.dL_dpix = dL_dpix;
         rb.acc_color_opacity = sc.acc_color_opacity; rb.acc_mean_conic = sc.acc_mean_conic; rb.acc_conic_w = sc.acc_conic_w;
@@ -317,7 +331,6 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const v
     size_t n = 0;
     uint2 grid;
     const uint32_t tiles = tiles_of(W, H, &grid);
-    const int passes = sort_passes(tiles);
     const size_t Ps = (size_t)P, Rs = (size_t)R, Npix = (size_t)W * (size_t)H;
     if (which < 10 || which == 31) {
         if (!geom_ws) return -1;
@@ -344,22 +357,24 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const v
         }
     } else if (which < 20 || which == 30) {
         if (!binning_ws) return -1;
-        BinningWS b = BinningWS::carve(aligned_base(binning_ws), Rs, passes);
-        if (which == 10 || which == 12) {
-            // Views of the sorted instance list in the reference's formats: Gaussian ids / (tile << 32 | depth_bits).
-            n = Rs * (which == 10 ? 4 : 8);
+        BinningWS b = BinningWS::carve(aligned_base(binning_ws), Rs, tiles);
+        if (which == 12 || which == 13) {
+            // Views of the sorted list in the reference's key format (tile << 32 | depth_bits) / as raw instances
+            // (tile << 32 | idx), rebuilt from the tile ranges and the sorted ids.
+            n = Rs * 8;
             if (dst && n > 0 && n <= max_bytes) {
-                if (!geom_ws) return -1;
+                if (!geom_ws || !image_ws) return -1;
                 GeomWS g = GeomWS::carve(aligned_base(geom_ws), Ps);
+                ImageWS im = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
                 if (cudaDeviceSynchronize() != cudaSuccess) return -1;
-                if (launch_debug_expand(R, b.sorted(passes), g.depths, which == 12 ? (uint64_t*)dst : nullptr,
-                                        which == 10 ? (uint32_t*)dst : nullptr))
+                if (launch_debug_expand(tiles, im.ranges, b.ids, g.depths, which == 12 ? (uint64_t*)dst : nullptr,
+                                        which == 13 ? (uint64_t*)dst : nullptr))
                     return -1;
             }
             return (long long)n;
         }
         switch (which) {
-            case 13: src = b.sorted(passes); n = Rs * 8; break;  // raw sorted instances (tile << 32 | idx)
+            case 10: src = b.ids; n = Rs * 4; break;   // sorted Gaussian ids (the reference's point_list)
             case 30: src = b.error_flag; n = 4; break;
             default: return -1;
         }

@@ -58,14 +58,14 @@ GS_DEV uint32_t block_excl_scan(uint32_t v, uint32_t* smem_warp, uint32_t* total
 }
 
 // ------------------------------------------------------------------------------------------------
-// Inclusive scan of tiles_touched taken in depth order: out[r] = sum_{r' <= r} in[order[r'] & 0xffffffff].
-// Three small kernels: block sums -> scan of block sums -> apply. `order` may be null (identity).
+// Inclusive scan of the per-Gaussian tile counts taken in depth order:
+//     out[r] = sum_{r' <= r} tiles(order[r'] & 0xffffffff),  tiles = w * h of the Gaussian's tile rectangle.
+// Three small kernels: block sums -> scan of block sums -> apply. The apply kernel also writes the
+// depth-ordered emission table the first binning pass expands: (idx, x0 | y0 << 16, w | h << 16, first slot).
 // ------------------------------------------------------------------------------------------------
-GS_DEV uint32_t scan_load(const uint32_t* __restrict__ in, const uint64_t* __restrict__ order, size_t k) {
-    return order ? in[(uint32_t)order[k]] : in[k];
-}
+GS_DEV uint32_t rect_tiles(const uint2 rc) { return (rc.y & 0xffffu) * (rc.y >> 16); }
 
-__global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uint32_t* __restrict__ in,
+__global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uint2* __restrict__ rect,
                                                                        const uint64_t* __restrict__ order, int n,
                                                                        uint32_t* __restrict__ block_sums) {
     __shared__ uint32_t sw[33];
@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uin
 #pragma unroll
     for (int i = 0; i < kScanItems; ++i) {
         const size_t k = base + (size_t)i * kScanThreads + threadIdx.x;
-        if (k < (size_t)n) s += scan_load(in, order, k);
+        if (k < (size_t)n) s += rect_tiles(rect[(uint32_t)order[k]]);
     }
     uint32_t total;
     block_excl_scan(s, sw, &total);
@@ -95,36 +95,46 @@ __global__ void __launch_bounds__(1024) scan_spine_kernel(uint32_t* __restrict__
     }
 }
 
-__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(const uint32_t* __restrict__ in,
+__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(const uint2* __restrict__ rect,
                                                                   const uint64_t* __restrict__ order, int n,
                                                                   const uint32_t* __restrict__ block_offsets,
-                                                                  uint32_t* __restrict__ out) {
+                                                                  uint32_t* __restrict__ out, uint4* __restrict__ emit) {
     __shared__ uint32_t sw[33];
     // Blocked arrangement: thread t owns items [t*8, t*8+8) of the block so the scan order is the list order.
     const size_t base = (size_t)blockIdx.x * kScanBlock + (size_t)threadIdx.x * kScanItems;
-    uint32_t v[kScanItems];
+    uint32_t v[kScanItems], idx[kScanItems];
+    uint2 rc[kScanItems];
     uint32_t s = 0;
 #pragma unroll
     for (int i = 0; i < kScanItems; ++i) {
-        v[i] = (base + i < (size_t)n) ? scan_load(in, order, base + i) : 0;
+        idx[i] = 0;
+        rc[i] = make_uint2(0u, 0u);
+        if (base + i < (size_t)n) {
+            idx[i] = (uint32_t)order[base + i];
+            rc[i] = rect[idx[i]];
+        }
+        v[i] = rect_tiles(rc[i]);
         s += v[i];
     }
     uint32_t total;
     uint32_t run = block_excl_scan(s, sw, &total) + block_offsets[blockIdx.x];
 #pragma unroll
     for (int i = 0; i < kScanItems; ++i) {
+        if (base + i < (size_t)n) {
+            emit[base + i] = make_uint4(idx[i], rc[i].x, rc[i].y, run);
+            out[base + i] = run + v[i];
+        }
         run += v[i];
-        if (base + i < (size_t)n) out[base + i] = run;
     }
 }
 
-int launch_inclusive_scan(const uint32_t* in, const uint64_t* order, int n, uint32_t* out, uint32_t* block_sums,
+int launch_inclusive_scan(const uint2* rect, const uint64_t* order, int n, uint32_t* out, uint4* emit, uint32_t* block_sums,
                           cudaStream_t stream) {
     if (n <= 0) return GS_OK;
     const int nb = (n + kScanBlock - 1) / kScanBlock;
-    scan_block_sums_kernel<<<nb, kScanThreads, 0, stream>>>(in, order, n, block_sums);
+    scan_block_sums_kernel<<<nb, kScanThreads, 0, stream>>>(rect, order, n, block_sums);
     scan_spine_kernel<<<1, 1024, 0, stream>>>(block_sums, nb);
-    scan_apply_kernel<<<nb, kScanThreads, 0, stream>>>(in, order, n, block_sums, out);
+    scan_apply_kernel<<<nb, kScanThreads, 0, stream>>>(rect, order, n, block_sums, out, emit);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
@@ -434,24 +444,398 @@ int launch_tile_ranges(uint32_t R, const uint64_t* inst, uint2* ranges, uint32_t
     return GS_OK;
 }
 
-// ------------------------------------------------------------------------------------------------
-// Debug / parity views of the sorted instance list in the reference's formats (gs_debug_fetch):
-// keys (tile << 32 | depth_bits) and the Gaussian index list.
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) debug_expand_kernel(uint32_t R, const uint64_t* __restrict__ inst,
-                                                           const float* __restrict__ depths, uint64_t* __restrict__ keys,
-                                                           uint32_t* __restrict__ ids) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= R) return;
-    const uint64_t k = inst[i];
-    const uint32_t id = (uint32_t)k;
-    if (keys) keys[i] = (k & 0xffffffff00000000ull) | __float_as_uint(depths[id]);
-    if (ids) ids[i] = id;
+// ================================================================================================
+// Fast path: two fused, lookback-free binning passes (count -> scan -> scatter each).
+//
+//   pass 1: block b owns emission slots [b*kBinTile, (b+1)*kBinTile) of the depth-ordered emission (no instance
+//           list is ever written in emission order: the slots are expanded in registers from the emission table).
+//           bin_count1_kernel  - digit histogram of every block, ANALYTICALLY from the tile rectangles (a row of a
+//                                rectangle is a run of consecutive tile ids = a circular run of low digits: two
+//                                shared-memory atomics per row on a difference array);
+//           bin_scan_kernel    - exclusive scan over blocks for every digit (one CTA per digit) + digit totals;
+//           bin_scatter_kernel<1> - expands, ranks by the low tile digit, scatters u64 keys (tile << 32 | idx).
+//   pass 2: bin_count2_kernel  - high-digit histogram of every block of those keys, and the per-tile instance
+//                                counts (shared-memory aggregated) from which the tile ranges follow by one scan
+//                                (identifyTileRanges, rasterizer_impl.cu:116-138, without a pass over the list);
+//           bin_scan_kernel    - as above (+ one extra CTA: tile counts -> ranges);
+//           bin_scatter_kernel<2> - ranks by the high digit, scatters the Gaussian ids (u32).
+// Both passes are stable, so every tile's list ends up in (depth, index) order: the reference's order. There is no
+// inter-block dependency inside any kernel (no tickets, flags, spins or fences).
+// ================================================================================================
+constexpr int kBinThreads = 256;
+constexpr int kBinItems = kBinTile / kBinThreads;  // 16
+constexpr int kTileSpan = 8;                        // low digits per block that bin_count2_kernel aggregates in shared memory
+static_assert(kBinItems == 16 && kBinThreads == 256, "the binning kernels are written for 256 threads x 16 slots");
+
+// Depth rank of the Gaussian owning the first / last emission slot of every pass-1 block.
+__global__ void __launch_bounds__(256) block_bounds_kernel(int P, const uint32_t* __restrict__ offsets, uint32_t R,
+                                                            uint32_t* __restrict__ first, uint32_t* __restrict__ last) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= P) return;
+    const uint32_t s1 = offsets[r], s0 = r ? offsets[r - 1] : 0u;
+    if (s1 <= s0) return;
+    for (uint32_t b = s0 / kBinTile; b <= (s1 - 1) / kBinTile; ++b) {
+        if (b * (uint32_t)kBinTile >= s0) first[b] = (uint32_t)r;
+        const uint32_t e = min((b + 1) * (uint32_t)kBinTile, R) - 1u;
+        if (e < s1) last[b] = (uint32_t)r;
+    }
 }
 
-int launch_debug_expand(uint32_t R, const uint64_t* inst, const float* depths, uint64_t* keys, uint32_t* ids) {
-    if (R == 0) return GS_OK;
-    debug_expand_kernel<<<(R + 255) / 256, 256>>>(R, inst, depths, keys, ids);
+// t / w and t % w for t < 65536 * w... in practice t < number of tiles <= 65536: the float product is at least
+// 0.5 / w away from an integer, far above its rounding error.
+GS_DEV uint32_t div_small(uint32_t t, uint32_t w, float rw) { (void)w; return (uint32_t)(((float)t + 0.5f) * rw); }
+
+// hist[d][b] = number of slots of block b whose tile id has low digit d, from the rectangles alone.
+__global__ void __launch_bounds__(kBinThreads) bin_count1_kernel(const uint4* __restrict__ emit, const uint32_t* __restrict__ block_first,
+                                                                  const uint32_t* __restrict__ block_last, uint32_t R, uint32_t grid_x,
+                                                                  int bits, uint32_t* __restrict__ hist, uint32_t nb) {
+    __shared__ int s_diff[256];
+    __shared__ int s_all;
+    __shared__ uint32_t s_scan[33];
+    const int tid = threadIdx.x;
+    const uint32_t b = blockIdx.x;
+    const int bins = 1 << bits;
+    const uint32_t mask = (uint32_t)bins - 1u;
+    s_diff[tid] = 0;
+    if (tid == 0) s_all = 0;
+    __syncthreads();
+    const uint32_t slot_begin = b * (uint32_t)kBinTile, slot_end = min(R, slot_begin + (uint32_t)kBinTile);
+    const uint32_t r0 = block_first[b], ng = block_last[b] - r0 + 1u;
+    for (uint32_t i = tid; i < ng; i += kBinThreads) {
+        const uint4 E = __ldg(emit + r0 + i);
+        const uint32_t w = E.z & 0xffffu, h = E.z >> 16, x0 = E.y & 0xffffu, y0 = E.y >> 16;
+        // clip the Gaussian's slots [E.w, E.w + w h) to the block: local positions [ta, tb)
+        const uint32_t ta = max(slot_begin, E.w) - E.w, tb = min(slot_end, E.w + w * h) - E.w;
+        const float rw = __frcp_rn((float)w);
+        const uint32_t ya = div_small(ta, w, rw), yb = div_small(tb - 1, w, rw);
+        const uint32_t xa = ta - ya * w, xb = tb - 1 - yb * w + 1;
+        for (uint32_t y = ya; y <= yb; ++y) {
+            const uint32_t xs = y == ya ? xa : 0u, xe = y == yb ? xb : w;
+            const uint32_t len = xe - xs;
+            const uint32_t s0 = ((y0 + y) * grid_x + x0 + xs) & mask;   // digit of the first tile of this row segment
+            const uint32_t full = len >> bits, rem = len & mask;       // a run of `len` consecutive digits (mod bins)
+            if (full) atomicAdd(&s_all, (int)full);
+            if (rem) {
+                atomicAdd(&s_diff[s0], 1);
+                const uint32_t e = s0 + rem;
+                if (e < (uint32_t)bins) {
+                    atomicAdd(&s_diff[e], -1);
+                } else if (e > (uint32_t)bins) {
+                    atomicAdd(&s_diff[0], 1);
+                    atomicAdd(&s_diff[e - bins], -1);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const uint32_t v = (uint32_t)s_diff[tid];
+    uint32_t total;
+    const uint32_t ex = block_excl_scan(v, s_scan, &total);   // wrap-around arithmetic: the partial sums are >= 0
+    if (tid < bins) hist[(size_t)tid * nb + b] = ex + v + (uint32_t)s_all;
+}
+
+// CTA d < bins: in-place exclusive scan of hist[d][0..nb) and totals[d]. CTA `bins` (launched only for pass 2):
+// ranges[t] = [start, start + count) from the per-tile counts ((0, 0) for an empty tile, as the reference leaves them).
+constexpr int kScanPer = 8;
+__global__ void __launch_bounds__(1024) bin_scan_kernel(uint32_t* __restrict__ hist, uint32_t nb, int bins, uint32_t* __restrict__ totals,
+                                                         const uint32_t* __restrict__ tile_counts, uint32_t tiles, uint2* __restrict__ ranges) {
+    __shared__ uint32_t sw[33];
+    const int tid = threadIdx.x;
+    const bool do_ranges = (int)blockIdx.x == bins;
+    const uint32_t n = do_ranges ? tiles : nb;
+    uint32_t* row = do_ranges ? nullptr : hist + (size_t)blockIdx.x * nb;
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < n; base += 1024 * kScanPer) {
+        uint32_t v[kScanPer], s = 0;
+#pragma unroll
+        for (int i = 0; i < kScanPer; ++i) {
+            const uint32_t k = base + tid * kScanPer + i;
+            v[i] = k < n ? (do_ranges ? tile_counts[k] : row[k]) : 0u;
+            s += v[i];
+        }
+        uint32_t total;
+        uint32_t run = carry + block_excl_scan(s, sw, &total);
+#pragma unroll
+        for (int i = 0; i < kScanPer; ++i) {
+            const uint32_t k = base + tid * kScanPer + i;
+            if (k < n) {
+                if (do_ranges) ranges[k] = v[i] ? make_uint2(run, run + v[i]) : make_uint2(0u, 0u);
+                else row[k] = run;
+            }
+            run += v[i];
+        }
+        carry += total;
+    }
+    if (!do_ranges && tid == 0) totals[blockIdx.x] = carry;
+}
+
+// hist[d][b] = number of keys of block b with high digit d; tile_counts[tile] += per-tile counts of the block.
+__global__ void __launch_bounds__(kBinThreads) bin_count2_kernel(const uint64_t* __restrict__ keys, uint32_t R, int bits1, int bits2,
+                                                                  uint32_t* __restrict__ hist, uint32_t nb,
+                                                                  uint32_t* __restrict__ tile_counts) {
+    __shared__ uint32_t s_t[kTileSpan][256];
+    __shared__ uint32_t s_lo[2];
+    const int tid = threadIdx.x;
+    const uint32_t b = blockIdx.x;
+    const uint32_t slot_begin = b * (uint32_t)kBinTile, n = min((uint32_t)kBinTile, R - slot_begin);
+    const uint32_t mask1 = (1u << bits1) - 1u;
+    for (int i = tid; i < kTileSpan * 256; i += kBinThreads) (&s_t[0][0])[i] = 0;
+    if (tid < 2) s_lo[tid] = (uint32_t)(keys[(size_t)slot_begin + (tid ? n - 1 : 0)] >> 32) & mask1;
+    __syncthreads();
+    // The keys are sorted by the low digit: the block holds low digits lmin..lmax only.
+    const uint32_t lmin = s_lo[0], span = s_lo[1] - lmin + 1u;
+    const bool compact = span <= (uint32_t)kTileSpan;
+#pragma unroll 4
+    for (int i = 0; i < kBinItems; ++i) {
+        const uint32_t e = i * kBinThreads + tid;
+        if (e < n) {
+            const uint32_t tile = (uint32_t)(keys[(size_t)slot_begin + e] >> 32);
+            const uint32_t hi = tile >> bits1;
+            if (compact) {
+                atomicAdd(&s_t[(tile & mask1) - lmin][hi], 1u);
+            } else {
+                atomicAdd(&s_t[0][hi], 1u);
+                atomicAdd(tile_counts + tile, 1u);
+            }
+        }
+    }
+    __syncthreads();
+    const int bins2 = 1 << bits2;
+    if (tid < bins2) {
+        uint32_t c = 0;
+        const int rows = compact ? (int)span : 1;
+        for (int l = 0; l < rows; ++l) {
+            const uint32_t t = s_t[l][tid];
+            c += t;
+            if (compact && t) atomicAdd(tile_counts + (((uint32_t)tid << bits1) | (lmin + l)), t);
+        }
+        hist[(size_t)tid * nb + b] = c;
+    }
+}
+
+struct BinScatterParams {
+    // pass 1 input
+    const uint4* __restrict__ emit;          // [P] depth-ordered (idx, x0 | y0 << 16, w | h << 16, first slot)
+    const uint32_t* __restrict__ offsets;    // [P] inclusive scan (first slot of rank r+1)
+    const uint32_t* __restrict__ block_first;
+    const uint32_t* __restrict__ block_last;
+    uint32_t grid_x;
+    // pass 2 input
+    const uint64_t* __restrict__ keys_in;
+    // outputs
+    uint64_t* __restrict__ keys_out;         // pass 1
+    uint32_t* __restrict__ ids_out;          // pass 2
+    uint32_t n;                              // R
+    uint32_t nb;
+    int shift, bits;                         // digit = (tile >> shift) & (2^bits - 1)
+    const uint32_t* __restrict__ scanned;    // [2^bits][nb] exclusive scan over blocks (bin_scan_kernel)
+    const uint32_t* __restrict__ totals;     // [2^bits] digit totals
+};
+
+template <int PASS>
+__global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinScatterParams p) {
+    __shared__ __align__(16) uint64_t s_keys[kBinTile];              // 32 KB (pass 1 first uses it as u16 owner[kBinTile])
+    __shared__ uint32_t s_hist[kBinThreads / 32][256];               // per-warp digit counts -> block positions
+    __shared__ uint32_t s_gbase[256];                                // global position of slot 0 of each digit's run
+    __shared__ uint32_t s_scan[33];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bins = 1 << p.bits;
+    for (int i = tid; i < (kBinThreads / 32) * 256; i += kBinThreads) (&s_hist[0][0])[i] = 0;
+    if (PASS == 1)
+        for (int i = tid; i < kBinTile / 8; i += kBinThreads) reinterpret_cast<uint4*>(s_keys)[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();
+    const uint32_t tile = blockIdx.x;
+    const uint32_t slot_begin = tile * (uint32_t)kBinTile;
+    const uint32_t tile_n = min((uint32_t)kBinTile, p.n - slot_begin);
+    const uint32_t warp_base = warp * (32 * kBinItems) + lane;   // item i of this thread is slot warp_base + 32 i
+
+    // ---- 1. keys into registers, warp-striped ----
+    uint64_t key[kBinItems];
+    if (PASS == 1) {
+        uint16_t* s_owner = reinterpret_cast<uint16_t*>(s_keys);
+        const uint32_t r0 = p.block_first[tile];
+        const uint32_t ng = p.block_last[tile] - r0 + 1u;   // Gaussians whose slots intersect this block (<= kBinTile + 1)
+        // head flags: local Gaussian i > 0 starts at slot offsets[r0 + i - 1] (>= slot_begin); Gaussian 0 owns slot 0
+        for (uint32_t i = 1 + tid; i < ng; i += kBinThreads) s_owner[p.offsets[r0 + i - 1] - slot_begin] = (uint16_t)i;
+        __syncthreads();
+        // inclusive max-scan in a blocked arrangement: thread t owns slots [16 t, 16 t + 16)
+        uint4 q[2];
+        q[0] = reinterpret_cast<uint4*>(s_owner)[2 * tid];
+        q[1] = reinterpret_cast<uint4*>(s_owner)[2 * tid + 1];
+        uint32_t* qw = reinterpret_cast<uint32_t*>(q);
+        uint32_t v[16];
+        uint32_t m = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            m = max(m, qw[j] & 0xffffu); v[2 * j] = m;
+            m = max(m, qw[j] >> 16);     v[2 * j + 1] = m;
+        }
+        uint32_t inc = m;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc = max(inc, up);
+        }
+        if (lane == 31) s_scan[warp] = inc;
+        __syncthreads();
+        uint32_t carry = __shfl_up_sync(0xffffffffu, inc, 1);
+        if (lane == 0) carry = 0;
+        for (int w = 0; w < warp; ++w) carry = max(carry, s_scan[w]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) qw[j] = max(v[2 * j], carry) | (max(v[2 * j + 1], carry) << 16);
+        reinterpret_cast<uint4*>(s_owner)[2 * tid] = q[0];
+        reinterpret_cast<uint4*>(s_owner)[2 * tid + 1] = q[1];
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < kBinItems; ++i) {
+            const uint32_t e = warp_base + i * 32;
+            key[i] = ~0ull;
+            if (e < tile_n) {
+                const uint4 E = __ldg(p.emit + r0 + s_owner[e]);
+                const uint32_t t = slot_begin + e - E.w, w = E.z & 0xffffu;
+                const uint32_t ty = div_small(t, w, __frcp_rn((float)w));
+                const uint32_t tx = t - ty * w;
+                const uint32_t tl = ((E.y >> 16) + ty) * p.grid_x + (E.y & 0xffffu) + tx;
+                key[i] = ((uint64_t)tl << 32) | E.x;
+            }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < kBinItems; ++i) {
+            const uint32_t e = warp_base + i * 32;
+            key[i] = e < tile_n ? p.keys_in[(size_t)slot_begin + e] : ~0ull;
+        }
+    }
+
+    // ---- 2. stable rank inside the warp: peer masks first (independent MATCH instructions), then the counter chain ----
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t dmask = (uint32_t)bins - 1u;
+    const int dshift = 32 + p.shift;
+    uint16_t rank[kBinItems];
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        uint32_t peers[kBinItems / 2];
+#pragma unroll
+        for (int i = 0; i < kBinItems / 2; ++i) {
+            const int k = half * (kBinItems / 2) + i;
+            const bool valid = warp_base + k * 32 < tile_n;
+            const uint32_t d = valid ? (uint32_t)(key[k] >> dshift) & dmask : 0xffffffffu;
+            peers[i] = __match_any_sync(0xffffffffu, d);
+        }
+#pragma unroll
+        for (int i = 0; i < kBinItems / 2; ++i) {
+            const int k = half * (kBinItems / 2) + i;
+            const bool valid = warp_base + k * 32 < tile_n;
+            const int leader = __ffs(peers[i]) - 1;
+            uint32_t old = 0;
+            if (valid && lane == leader) old = atomicAdd(&s_hist[warp][(uint32_t)(key[k] >> dshift) & dmask], (uint32_t)__popc(peers[i]));
+            old = __shfl_sync(0xffffffffu, old, leader);
+            rank[k] = (uint16_t)(old + __popc(peers[i] & lt_mask));
+        }
+    }
+    __syncthreads();   // (also: every read of s_owner is done, s_keys may be overwritten)
+
+    // ---- 3. thread d owns digit d: position of each warp's group inside the block, global base of the digit's run ----
+    uint32_t count = 0, tot_d = 0;
+    if (tid < bins) {
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < kBinThreads / 32; ++w) {
+            const uint32_t t = s_hist[w][tid];
+            s_hist[w][tid] = run;
+            run += t;
+        }
+        count = run;
+        tot_d = p.totals[tid];
+    }
+    uint32_t total;
+    const uint32_t lbase = block_excl_scan(count, s_scan, &total);   // start of digit d's run inside the block
+    const uint32_t dbase = block_excl_scan(tot_d, s_scan, &total);   // start of digit d in the output
+    if (tid < bins) {
+#pragma unroll
+        for (int w = 0; w < kBinThreads / 32; ++w) s_hist[w][tid] += lbase;
+        s_gbase[tid] = dbase + p.scanned[(size_t)tid * p.nb + tile] - lbase;
+    }
+    __syncthreads();
+
+    // ---- 4. scatter into shared memory in sorted order, then write out: consecutive threads write consecutive slots ----
+#pragma unroll
+    for (int i = 0; i < kBinItems; ++i) {
+        const uint32_t e = warp_base + i * 32;
+        if (e < tile_n) s_keys[s_hist[warp][(uint32_t)(key[i] >> dshift) & dmask] + rank[i]] = key[i];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < kBinItems; ++i) {
+        const uint32_t s = i * kBinThreads + tid;
+        if (s < tile_n) {
+            const uint64_t k = s_keys[s];
+            const uint32_t pos = s_gbase[(uint32_t)(k >> dshift) & dmask] + s;
+            if (PASS == 1) p.keys_out[pos] = k; else p.ids_out[pos] = (uint32_t)k;
+        }
+    }
+}
+
+int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1, int bits2, const uint4* emit,
+                        const uint32_t* offsets, const BinningWS& b, uint2* ranges, cudaStream_t stream) {
+    GS_CUDA_TRY(cudaMemsetAsync(b.tile_counts, 0, (size_t)tiles * sizeof(uint32_t), stream));
+    if (R == 0 || P <= 0) {
+        GS_CUDA_TRY(cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), stream));
+        return GS_OK;
+    }
+    const uint32_t nb = (R + kBinTile - 1) / kBinTile;
+    const int bins1 = 1 << bits1, bins2 = 1 << bits2;
+    block_bounds_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, offsets, R, b.block_first, b.block_last);
+    bin_count1_kernel<<<nb, kBinThreads, 0, stream>>>(emit, b.block_first, b.block_last, R, grid.x, bits1, b.hist1, nb);
+    bin_scan_kernel<<<bins1, 1024, 0, stream>>>(b.hist1, nb, bins1, b.totals, nullptr, 0, nullptr);
+    BinScatterParams sp;
+    sp.emit = emit; sp.offsets = offsets; sp.block_first = b.block_first; sp.block_last = b.block_last; sp.grid_x = grid.x;
+    sp.keys_in = nullptr; sp.keys_out = b.keys1; sp.ids_out = nullptr; sp.n = R; sp.nb = nb;
+    sp.shift = 0; sp.bits = bits1; sp.scanned = b.hist1; sp.totals = b.totals;
+    bin_scatter_kernel<1><<<nb, kBinThreads, 0, stream>>>(sp);
+    bin_count2_kernel<<<nb, kBinThreads, 0, stream>>>(b.keys1, R, bits1, bits2, b.hist2, nb, b.tile_counts);
+    bin_scan_kernel<<<bins2 + 1, 1024, 0, stream>>>(b.hist2, nb, bins2, b.totals + 256, b.tile_counts, tiles, ranges);
+    sp.keys_in = b.keys1; sp.keys_out = nullptr; sp.ids_out = b.ids;
+    sp.shift = bits1; sp.bits = bits2; sp.scanned = b.hist2; sp.totals = b.totals + 256;
+    bin_scatter_kernel<2><<<nb, kBinThreads, 0, stream>>>(sp);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+// Generic path tail: keep only the Gaussian index of every sorted instance.
+__global__ void __launch_bounds__(256) strip_ids_kernel(uint32_t n, const uint64_t* __restrict__ in, uint32_t* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (uint32_t)in[i];
+}
+
+int launch_strip_ids(uint32_t n, const uint64_t* in, uint32_t* out, cudaStream_t stream) {
+    if (n == 0) return GS_OK;
+    strip_ids_kernel<<<(n + 255) / 256, 256, 0, stream>>>(n, in, out);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Debug / parity views of the sorted instance list in the reference's formats (gs_debug_fetch):
+// keys (tile << 32 | depth_bits) and raw instances (tile << 32 | idx), rebuilt from the ranges and the ids.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) debug_expand_kernel(uint32_t tiles, const uint2* __restrict__ ranges,
+                                                           const uint32_t* __restrict__ ids, const float* __restrict__ depths,
+                                                           uint64_t* __restrict__ keys, uint64_t* __restrict__ raw) {
+    const uint32_t tile = blockIdx.x;
+    if (tile >= tiles) return;
+    const uint2 rg = ranges[tile];
+    for (uint32_t i = rg.x + threadIdx.x; i < rg.y; i += blockDim.x) {
+        const uint32_t id = ids[i];
+        if (keys) keys[i] = ((uint64_t)tile << 32) | __float_as_uint(depths[id]);
+        if (raw) raw[i] = ((uint64_t)tile << 32) | id;
+    }
+}
+
+int launch_debug_expand(uint32_t tiles, const uint2* ranges, const uint32_t* ids, const float* depths, uint64_t* keys, uint64_t* raw) {
+    if (tiles == 0) return GS_OK;
+    debug_expand_kernel<<<tiles, 256>>>(tiles, ranges, ids, depths, keys, raw);
     GS_LAUNCH_CHECK();
     GS_CUDA_TRY(cudaDeviceSynchronize());
     return GS_OK;

@@ -34,12 +34,13 @@ struct PreprocessParams {
     uint8_t* __restrict__ clamped;
     SplatRec* __restrict__ rec;          // [P] render records (visible Gaussians only)
     uint64_t* __restrict__ depth_keys;   // [P] (depth_bits << 32 | idx); depth_bits = ~0 when culled
+    uint2* __restrict__ rect;            // [P] (x0 | y0 << 16, w | h << 16) tile rectangle, zero when culled
     uint32_t* __restrict__ num_rendered; // [1] += sum of tiles_touched (zeroed by the caller)
 };
 
 struct RenderFwdParams {
     const uint2* __restrict__ ranges;
-    const uint64_t* __restrict__ inst;   // sorted instances (tile << 32 | gaussian idx), padded by 2 entries
+    const uint32_t* __restrict__ ids;    // Gaussian index of every instance in (tile, depth, index) order, padded
     const SplatRec* __restrict__ rec;    // per-Gaussian render records
     int W, H, tiles_x;
     const float* __restrict__ bg;
@@ -52,7 +53,7 @@ struct RenderFwdParams {
 
 struct RenderBwdParams {
     const uint2* __restrict__ ranges;
-    const uint64_t* __restrict__ inst;
+    const uint32_t* __restrict__ ids;
     const SplatRec* __restrict__ rec;
     const uint32_t* __restrict__ tile_max_contrib;
     int W, H, tiles_x;
@@ -96,14 +97,17 @@ struct PreprocessBwdParams {
 
 int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
-int launch_inclusive_scan(const uint32_t* in, const uint64_t* order, int n, uint32_t* out, uint32_t* block_sums,
+int launch_inclusive_scan(const uint2* rect, const uint64_t* order, int n, uint32_t* out, uint4* emit, uint32_t* block_sums,
                           cudaStream_t stream);
+int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1, int bits2, const uint4* emit,
+                        const uint32_t* offsets, const BinningWS& b, uint2* ranges, cudaStream_t stream);
+int launch_strip_ids(uint32_t n, const uint64_t* in, uint32_t* out, cudaStream_t stream);
 int launch_emit_instances(int P, const uint64_t* depth_order, const float2* means2D, const uint32_t* offsets,
                           const int* radii, uint2 grid, uint64_t* inst, cudaStream_t stream);
 int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, int first_bit, int passes, char* scratch,
                       uint32_t* error_flag, cudaStream_t stream);
 int launch_tile_ranges(uint32_t R, const uint64_t* inst, uint2* ranges, uint32_t tiles, cudaStream_t stream);
-int launch_debug_expand(uint32_t R, const uint64_t* inst, const float* depths, uint64_t* keys, uint32_t* ids);
+int launch_debug_expand(uint32_t tiles, const uint2* ranges, const uint32_t* ids, const float* depths, uint64_t* keys, uint64_t* raw);
 int launch_debug_low32(uint32_t n, const uint64_t* in, uint32_t* out);
 int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream);
 int launch_render_bwd(const RenderBwdParams& p, int tiles, cudaStream_t stream);

@@ -92,6 +92,7 @@ __device__ __noinline__ V3 sh_to_rgb(int deg, const V3 pos, const V3 campos, con
 GS_DEV uint32_t preprocess_one(const PreprocessParams& p, const int idx) {
     int out_radius = 0;
     uint32_t out_tiles = 0;
+    uint2 out_rect = {0u, 0u};
     uint32_t depth_bits = 0xffffffffu;  // culled Gaussians sort behind every visible one
     p.is_used[idx] = 0;
 
@@ -170,12 +171,14 @@ GS_DEV uint32_t preprocess_one(const PreprocessParams& p, const int idx) {
                 dst[2] = make_float4(col.x, col.y, col.z, p_view.z);
                 out_radius = (int)my_radius;
                 out_tiles = ntiles;
+                out_rect = make_uint2(rect_min.x | (rect_min.y << 16), (rect_max.x - rect_min.x) | ((rect_max.y - rect_min.y) << 16));
                 depth_bits = __float_as_uint(p_view.z);
             }
         }
     }
     p.radii[idx] = out_radius;
     p.tiles_touched[idx] = out_tiles;
+    p.rect[idx] = out_rect;
     p.depth_keys[idx] = ((uint64_t)depth_bits << 32) | (uint32_t)idx;
     return out_tiles;
 }

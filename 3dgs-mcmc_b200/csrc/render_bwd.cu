@@ -45,7 +45,7 @@ template <int CH, int ROWS>
 struct BwdSmem {
     static constexpr size_t kRec = 0;
     static constexpr size_t kInst = kRec + sizeof(SplatRec) * kRecStages * CH;
-    static constexpr size_t kInstFull = kInst + sizeof(uint64_t) * kInstStages * (CH + 2);
+    static constexpr size_t kInstFull = kInst + sizeof(uint32_t) * kInstStages * (CH + kInstPad);
     static constexpr size_t kRecFull = kInstFull + sizeof(uint64_t) * kInstStages;
     static constexpr size_t kRows = (kRecFull + sizeof(uint64_t) * kRecStages + 127) / 128 * 128;
     static constexpr size_t kDpix = kRows + sizeof(float) * kBwdWarps * 2 * ROWS * 32;
@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX, MIN_CTAS) render_bwd_kernel(const
     using L = BwdSmem<CH, ROWS>;
     extern __shared__ __align__(128) unsigned char smem[];
     SplatRec* s_rec = reinterpret_cast<SplatRec*>(smem + L::kRec);
-    uint64_t* s_inst = reinterpret_cast<uint64_t*>(smem + L::kInst);
+    uint32_t* s_inst = reinterpret_cast<uint32_t*>(smem + L::kInst);
     uint64_t* s_inst_full = reinterpret_cast<uint64_t*>(smem + L::kInstFull);
     uint64_t* s_rec_full = reinterpret_cast<uint64_t*>(smem + L::kRecFull);
 
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX, MIN_CTAS) render_bwd_kernel(const
     if (tid == 0) stager_init<CH>(s_inst_full, s_rec_full);
     __syncthreads();
     // Stream chunk k is list chunk c = nchunks-1-k.
-    Stager<CH> st(p.inst, p.rec, range.x, n_total, nchunks, /*reversed=*/true, s_inst, s_inst_full, s_rec, s_rec_full);
+    Stager<CH> st(p.ids, p.rec, range.x, n_total, nchunks, /*reversed=*/true, s_inst, s_inst_full, s_rec, s_rec_full);
     st.prologue(tid);
 
     float* const U = reinterpret_cast<float*>(smem + L::kRows) + warp * (2 * ROWS * 32);

@@ -49,20 +49,20 @@ GS_DEV bool patch_may_contribute(const float mx, const float my, const float A, 
 
 // ------------------------------------------------------------------------------------------------
 // Shared-memory staging of one tile's splats, used by both renderers.
-//   instance ring : kInstStages x (kChunk + 2) u64, filled by 1-D bulk copies (one issuing thread);
-//   record ring   : kRecStages x kChunk SplatRec, filled by 16-byte cp.async gathers (threads 0..kChunk-1,
-//                   one record each), two stream chunks ahead of the consumer.
+//   id ring     : kInstStages x (CH + 8) u32 Gaussian ids, filled by 1-D bulk copies (one issuing thread);
+//   record ring : kRecStages x CH SplatRec, filled by 16-byte cp.async gathers (threads 0..CH-1,
+//                 one record each), two stream chunks ahead of the consumer.
 // "Stream chunk" k is list chunk k for the forward and nchunks-1-k for the backward (reversed).
-// Barrier protocol: chunk k's instances complete phase (k / kInstStages) & 1 of inst_full[k % kInstStages]
+// Barrier protocol: chunk k's ids complete phase (k / kInstStages) & 1 of inst_full[k % kInstStages]
 // (armed with the byte count by the issuing thread); its records complete phase (k / kRecStages) & 1 of
-// rec_full[k % kRecStages] after kChunk thread arrivals, each triggered when that thread's copies have landed.
+// rec_full[k % kRecStages] after CH thread arrivals, each triggered when that thread's copies have landed.
 // A stage is refilled only after a CTA-wide barrier that follows its last reader, so phases never alias.
 // ------------------------------------------------------------------------------------------------
 constexpr int kChunk = 128;
 constexpr int kRecStages = 3;
 constexpr int kInstStages = 4;
 constexpr int kGatherAhead = 2;
-static_assert(kChunk % 2 == 0, "chunk starts must keep the parity of the tile's first instance");
+constexpr int kInstPad = 8;   // ring slots per stage beyond CH (16-byte alignment slack on both ends)
 
 template <int CH = kChunk>
 GS_DEV void stager_init(uint64_t* inst_full, uint64_t* rec_full) {
@@ -76,46 +76,46 @@ GS_DEV void stager_init(uint64_t* inst_full, uint64_t* rec_full) {
 // CH = records per chunk (the forward uses kChunk; the backward picks its own to fit its shared-memory budget).
 template <int CH = kChunk>
 struct Stager {
-    static_assert(CH % 2 == 0 && CH <= GS_TILE_PIX, "chunk starts must keep the parity of the tile's first instance");
-    const uint64_t* __restrict__ inst;
+    static_assert(CH % 4 == 0 && CH <= GS_TILE_PIX, "chunk starts must keep the 16-byte phase of the tile's first id");
+    const uint32_t* __restrict__ ids;
     const SplatRec* __restrict__ rec;
     uint32_t first;
     int n_total, nchunks;
     bool reversed;
-    uint64_t* s_inst;
+    uint32_t* s_inst;
     uint64_t* inst_full;
     SplatRec* s_rec;
     uint64_t* rec_full;
-    int odd;
+    int mis;          // first & 3: entries between the previous 16-byte boundary and the slice start
     int inst_issued;  // meaningful in thread 0
     int gathered;     // uniform
 
-    GS_DEV Stager(const uint64_t* inst_, const SplatRec* rec_, uint32_t first_, int n_total_, int nchunks_, bool reversed_,
-                  uint64_t* s_inst_, uint64_t* inst_full_, SplatRec* s_rec_, uint64_t* rec_full_)
-        : inst(inst_), rec(rec_), first(first_), n_total(n_total_), nchunks(nchunks_), reversed(reversed_), s_inst(s_inst_),
-          inst_full(inst_full_), s_rec(s_rec_), rec_full(rec_full_), odd((int)(first_ & 1u)), inst_issued(0), gathered(0) {}
+    GS_DEV Stager(const uint32_t* ids_, const SplatRec* rec_, uint32_t first_, int n_total_, int nchunks_, bool reversed_,
+                  uint32_t* s_inst_, uint64_t* inst_full_, SplatRec* s_rec_, uint64_t* rec_full_)
+        : ids(ids_), rec(rec_), first(first_), n_total(n_total_), nchunks(nchunks_), reversed(reversed_), s_inst(s_inst_),
+          inst_full(inst_full_), s_rec(s_rec_), rec_full(rec_full_), mis((int)(first_ & 3u)), inst_issued(0), gathered(0) {}
 
     GS_DEV int list_chunk(int k) const { return reversed ? nchunks - 1 - k : k; }
     GS_DEV int chunk_n(int lc) const { return min(CH, n_total - lc * CH); }
 
-    // Thread 0: bulk-copy the instance slice of stream chunk k. Bulk copies move 16-byte units from 16-byte
-    // aligned addresses, so the copy starts one entry early when the slice starts at an odd index and may
-    // run one entry past its end (the instance arrays are padded for that).
+    // Thread 0: bulk-copy the id slice of stream chunk k. Bulk copies move 16-byte units from 16-byte aligned
+    // addresses, so the copy starts up to three entries early and may run up to three entries past the slice's
+    // end (the id array is padded for that).
     GS_DEV void issue_inst(int k) {
         const int lc = list_chunk(k), n = chunk_n(lc), s = k % kInstStages;
         const size_t start = (size_t)first + (size_t)lc * CH;
-        const uint32_t bytes = (uint32_t)((n + odd + 1) & ~1) * 8u;
+        const uint32_t bytes = (uint32_t)((n + mis + 3) & ~3) * 4u;
         mbar_arrive_expect_tx(&inst_full[s], bytes);
-        bulk_copy_g2s(s_inst + s * (CH + 2), inst + (start - odd), bytes, &inst_full[s]);
+        bulk_copy_g2s(s_inst + s * (CH + kInstPad), ids + (start - mis), bytes, &inst_full[s]);
     }
 
-    // Threads 0..CH-1: gather the records of stream chunk k (its instances must have been issued).
+    // Threads 0..CH-1: gather the records of stream chunk k (its ids must have been issued).
     GS_DEV void gather(int tid, int k) {
         if (tid < CH) {
             const int lc = list_chunk(k), n = chunk_n(lc), si = k % kInstStages, sr = k % kRecStages;
             mbar_wait(&inst_full[si], (uint32_t)((k / kInstStages) & 1));
             if (tid < n) {
-                const uint32_t id = (uint32_t)s_inst[si * (CH + 2) + odd + tid];
+                const uint32_t id = s_inst[si * (CH + kInstPad) + mis + tid];
                 const float4* src = reinterpret_cast<const float4*>(rec + id);
                 float4* dst = reinterpret_cast<float4*>(s_rec + sr * CH + tid);
                 cp_async_16(dst, src);

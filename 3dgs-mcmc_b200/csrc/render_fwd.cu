@@ -22,7 +22,7 @@ namespace gs {
 
 __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwdParams p) {
     __shared__ __align__(128) SplatRec s_rec[kRecStages][kChunk];
-    __shared__ __align__(16) uint64_t s_inst[kInstStages][kChunk + 2];
+    __shared__ __align__(16) uint32_t s_inst[kInstStages][kChunk + kInstPad];
     __shared__ __align__(8) uint64_t s_inst_full[kInstStages];
     __shared__ __align__(8) uint64_t s_rec_full[kRecStages];
     __shared__ int s_used[kRecStages][kChunk];  // id+1 of splats blended by some pixel, 0 otherwise
@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
     __syncthreads();
 
     // List chunk c covers positions [c*kChunk, c*kChunk + n) of the tile's list.
-    Stager<kChunk> st(p.inst, p.rec, range.x, n_total, nchunks, /*reversed=*/false, &s_inst[0][0], s_inst_full, &s_rec[0][0], s_rec_full);
+    Stager<kChunk> st(p.ids, p.rec, range.x, n_total, nchunks, /*reversed=*/false, &s_inst[0][0], s_inst_full, &s_rec[0][0], s_rec_full);
     st.prologue(tid);
 
     auto flush_used = [&](int c) {

@@ -129,7 +129,7 @@ unsigned long long gs_launch_count(void);
  *   5 conic_opacity f32[4P] | 6 rgb f32[3P] | 7 tiles_touched u32[P]
  *   8 inclusive scan of tiles_touched in depth order u32[P] | 9 gaussian ids in (depth, index) order u32[P]
  *   10 sorted gaussian ids u32[R] | 12 sorted keys (tile << 32 | depth_bits) u64[R], both in the reference's format
- *   13 raw sorted instances (tile << 32 | id) u64[R] | 14 packed splat records 48 B x R
+ *   13 sorted instances as (tile << 32 | id) u64[R] | 2 per-Gaussian render records 48 B x P
  *   20 final_T f32[WH] | 21 n_contrib u32[WH] | 22 ranges u32[2*tiles] | 23 tile_max_contrib u32[tiles]
  *   30 tile-sort error flag u32[1] | 31 depth-sort error flag u32[1]
  * Returns the array's size in bytes (copied only when it fits in max_bytes), or -1. Synchronous. */
