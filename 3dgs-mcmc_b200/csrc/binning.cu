@@ -467,6 +467,23 @@ constexpr int kBinItems = kBinTile / kBinThreads;  // 16
 constexpr int kTileSpan = 8;                        // low digits per block that bin_count2_kernel aggregates in shared memory
 static_assert(kBinItems == 16 && kBinThreads == 256, "the binning kernels are written for 256 threads x 16 slots");
 
+
+// Lanes of the warp whose digit equals this lane's, from BITS ballots. (__match_any_sync is not used: on sm_100a MATCH.ANY
+// runs on one per-SM unit at ~3.5 cycles per DISTINCT value in the warp - measured with tools/microbench/match_vs_ballot.cu -
+// which bounded the binning passes at >100 cycles per warp-item; BITS ballots cost 4 issue slots each, spread over the
+// four schedulers.)
+template <int BITS>
+GS_DEV uint32_t peer_mask(const uint32_t d) {
+    uint32_t peers = 0xffffffffu;
+#pragma unroll
+    for (int k = 0; k < BITS; ++k) {
+        const bool bit = (d & (1u << k)) != 0u;
+        const uint32_t b = __ballot_sync(0xffffffffu, bit);
+        peers &= ~(b ^ (bit ? 0xffffffffu : 0u));
+    }
+    return peers;
+}
+
 // Depth rank of the Gaussian owning the first / last emission slot of every pass-1 block.
 __global__ void __launch_bounds__(256) block_bounds_kernel(int P, const uint32_t* __restrict__ offsets, uint32_t R,
                                                             uint32_t* __restrict__ first, uint32_t* __restrict__ last) {
@@ -632,7 +649,7 @@ struct BinScatterParams {
     const uint32_t* __restrict__ totals;     // [2^bits] digit totals
 };
 
-template <int PASS>
+template <int PASS, int BITS>
 __global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinScatterParams p) {
     __shared__ __align__(16) uint64_t s_keys[kBinTile];              // 32 KB (pass 1 first uses it as u16 owner[kBinTile])
     __shared__ uint32_t s_hist[kBinThreads / 32][256];               // per-warp digit counts -> block positions
@@ -640,7 +657,7 @@ __global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinSc
     __shared__ uint32_t s_scan[33];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int bins = 1 << p.bits;
+    constexpr int bins = 1 << BITS;
     for (int i = tid; i < (kBinThreads / 32) * 256; i += kBinThreads) (&s_hist[0][0])[i] = 0;
     if (PASS == 1)
         for (int i = tid; i < kBinTile / 8; i += kBinThreads) reinterpret_cast<uint4*>(s_keys)[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -708,31 +725,27 @@ __global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinSc
         }
     }
 
-    // ---- 2. stable rank inside the warp: peer masks first (independent MATCH instructions), then the counter chain ----
+    // ---- 2. stable rank inside the warp: peer mask per item from ballots, running per-warp digit counters kept by
+    //         one leader lane per distinct digit (plain LDS / STS; __syncwarp orders them between items) ----
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t dmask = (uint32_t)bins - 1u;
     const int dshift = 32 + p.shift;
     uint16_t rank[kBinItems];
+    uint32_t* const wh = s_hist[warp];
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
-        uint32_t peers[kBinItems / 2];
-#pragma unroll
-        for (int i = 0; i < kBinItems / 2; ++i) {
-            const int k = half * (kBinItems / 2) + i;
-            const bool valid = warp_base + k * 32 < tile_n;
-            const uint32_t d = valid ? (uint32_t)(key[k] >> dshift) & dmask : 0xffffffffu;
-            peers[i] = __match_any_sync(0xffffffffu, d);
+    for (int k = 0; k < kBinItems; ++k) {
+        const bool valid = warp_base + k * 32 < tile_n;
+        const uint32_t d = (uint32_t)(key[k] >> dshift) & dmask;   // invalid slots (all-ones key) are masked out below
+        const uint32_t peers = peer_mask<BITS>(d) & __ballot_sync(0xffffffffu, valid);
+        const int leader = __ffs(peers) - 1;
+        uint32_t old = 0;
+        if (valid && lane == leader) {
+            old = wh[d];
+            wh[d] = old + (uint32_t)__popc(peers);
         }
-#pragma unroll
-        for (int i = 0; i < kBinItems / 2; ++i) {
-            const int k = half * (kBinItems / 2) + i;
-            const bool valid = warp_base + k * 32 < tile_n;
-            const int leader = __ffs(peers[i]) - 1;
-            uint32_t old = 0;
-            if (valid && lane == leader) old = atomicAdd(&s_hist[warp][(uint32_t)(key[k] >> dshift) & dmask], (uint32_t)__popc(peers[i]));
-            old = __shfl_sync(0xffffffffu, old, leader);
-            rank[k] = (uint16_t)(old + __popc(peers[i] & lt_mask));
-        }
+        old = __shfl_sync(0xffffffffu, old, leader & 31);
+        rank[k] = (uint16_t)(old + __popc(peers & lt_mask));
+        __syncwarp();
     }
     __syncthreads();   // (also: every read of s_owner is done, s_keys may be overwritten)
 
@@ -777,6 +790,25 @@ __global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinSc
     }
 }
 
+template <int PASS, int BITS>
+static void launch_scatter(const BinScatterParams& sp, uint32_t nb, cudaStream_t stream) {
+    bin_scatter_kernel<PASS, BITS><<<nb, kBinThreads, 0, stream>>>(sp);
+}
+template <int PASS>
+static int dispatch_scatter(int bits, const BinScatterParams& sp, uint32_t nb, cudaStream_t stream) {
+    switch (bits) {
+        case 1: launch_scatter<PASS, 1>(sp, nb, stream); break;
+        case 2: launch_scatter<PASS, 2>(sp, nb, stream); break;
+        case 3: launch_scatter<PASS, 3>(sp, nb, stream); break;
+        case 4: launch_scatter<PASS, 4>(sp, nb, stream); break;
+        case 5: launch_scatter<PASS, 5>(sp, nb, stream); break;
+        case 6: launch_scatter<PASS, 6>(sp, nb, stream); break;
+        case 7: launch_scatter<PASS, 7>(sp, nb, stream); break;
+        case 8: launch_scatter<PASS, 8>(sp, nb, stream); break;
+        default: return GS_ERR_ARG;
+    }
+    return GS_OK;
+}
 int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1, int bits2, const uint4* emit,
                         const uint32_t* offsets, const BinningWS& b, uint2* ranges, cudaStream_t stream) {
     GS_CUDA_TRY(cudaMemsetAsync(b.tile_counts, 0, (size_t)tiles * sizeof(uint32_t), stream));
@@ -793,12 +825,14 @@ int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1
     sp.emit = emit; sp.offsets = offsets; sp.block_first = b.block_first; sp.block_last = b.block_last; sp.grid_x = grid.x;
     sp.keys_in = nullptr; sp.keys_out = b.keys1; sp.ids_out = nullptr; sp.n = R; sp.nb = nb;
     sp.shift = 0; sp.bits = bits1; sp.scanned = b.hist1; sp.totals = b.totals;
-    bin_scatter_kernel<1><<<nb, kBinThreads, 0, stream>>>(sp);
+    int rc = dispatch_scatter<1>(bits1, sp, nb, stream);
+    if (rc) return rc;
     bin_count2_kernel<<<nb, kBinThreads, 0, stream>>>(b.keys1, R, bits1, bits2, b.hist2, nb, b.tile_counts);
     bin_scan_kernel<<<bins2 + 1, 1024, 0, stream>>>(b.hist2, nb, bins2, b.totals + 256, b.tile_counts, tiles, ranges);
     sp.keys_in = b.keys1; sp.keys_out = nullptr; sp.ids_out = b.ids;
     sp.shift = bits1; sp.bits = bits2; sp.scanned = b.hist2; sp.totals = b.totals + 256;
-    bin_scatter_kernel<2><<<nb, kBinThreads, 0, stream>>>(sp);
+    rc = dispatch_scatter<2>(bits2, sp, nb, stream);
+    if (rc) return rc;
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

@@ -121,6 +121,16 @@ def _count_event(device):
     return ev
 
 
+def _stable_size(nbytes):
+    """Round a workspace size up to 1/8-octave steps. The instance count changes with every camera; rounding makes the
+    binning workspace fall into a handful of size classes, so torch's caching allocator can hand back the block the
+    previous step released instead of calling cudaMalloc (a device-wide sync) whenever a slightly larger view shows up."""
+    if nbytes <= (1 << 20):
+        return nbytes
+    step = 1 << (nbytes.bit_length() - 4)
+    return (nbytes + step - 1) // step * step
+
+
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
                         prefiltered, debug):
@@ -176,7 +186,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         if debug:
             _debug_sync("preprocess")
 
-        binning = torch.empty(_lib.gs_binning_bytes(rendered, W, H), **byte_opts)
+        binning = torch.empty(_stable_size(_lib.gs_binning_bytes(rendered, W, H)), **byte_opts)
         _check(_lib.gs_forward_render(
             stream, P, rendered, W, H, _ptr(background), _ptr(colors), radii.data_ptr(), geom.data_ptr(),
             binning.data_ptr(), img.data_ptr(), out_color.data_ptr(), is_used.data_ptr()), "gs_forward_render")
