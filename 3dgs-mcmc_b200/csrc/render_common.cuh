@@ -19,13 +19,21 @@ constexpr float kPatchH = 3.0f;  // and in y (4 pixels)
 // and compares -0.5 q_min, widened by a rounding allowance proportional to the largest term either evaluation can
 // see, with thr. Anything odd (non-positive-definite conic, NaN) answers true and takes the exact per-pixel path,
 // so no blend decision ever changes.
+GS_DEV float rcp_approx(const float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 GS_DEV bool patch_may_contribute(const float mx, const float my, const float A, const float B, const float C,
                                  const float thr, const float X0, const float Y0) {
-    if (!(A > 0.0f) || !(C > 0.0f)) return true;
+    if (!(A > 1e-30f) || !(C > 1e-30f)) return true;   // (also keeps the bare reciprocals below in range)
     const float hx = (mx - X0) + 1e-3f, lx = (mx - X0) - (kPatchW + 1e-3f);
     const float hy = (my - Y0) + 1e-3f, ly = (my - Y0) - (kPatchH + 1e-3f);
     const bool inside = (lx <= 0.0f) && (hx >= 0.0f) && (ly <= 0.0f) && (hy >= 0.0f);
-    const float nBrC = -__fdividef(B, C), nBrA = -__fdividef(B, A);
+    // The clamp points only have to be near the edge minima (q is stationary there: an error d in t costs C d^2,
+    // far below the allowance), so bare rcp.approx (no range-scaling guards) is enough.
+    const float nBrC = -B * rcp_approx(C), nBrA = -B * rcp_approx(A);
     const float B2 = 2.0f * B;
     // vertical edges dx = e: best dy = clamp(-B e / C)
     float t, q;
