@@ -729,7 +729,7 @@ __global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinSc
     //         one leader lane per distinct digit (plain LDS / STS; __syncwarp orders them between items) ----
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t dmask = (uint32_t)bins - 1u;
-    const int dshift = 32 + p.shift;
+    const int dshift = 32 + p.shift;   // digits live in the upper word of the key (tile id / depth bits)
     uint16_t rank[kBinItems];
     uint32_t* const wh = s_hist[warp];
 #pragma unroll
@@ -785,8 +785,33 @@ __global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinSc
         if (s < tile_n) {
             const uint64_t k = s_keys[s];
             const uint32_t pos = s_gbase[(uint32_t)(k >> dshift) & dmask] + s;
-            if (PASS == 1) p.keys_out[pos] = k; else p.ids_out[pos] = (uint32_t)k;
+            if (PASS == 2) p.ids_out[pos] = (uint32_t)k; else p.keys_out[pos] = k;
         }
+    }
+}
+
+// hist[d][b] = number of keys of block b whose digit (key >> shift) & (2^bits - 1) is d. Generic counterpart of
+// bin_count1/2 for plain u64 keys (the depth ordering of the Gaussians).
+__global__ void __launch_bounds__(kBinThreads) bin_count_kernel(const uint64_t* __restrict__ keys, uint32_t n, int shift, int bits,
+                                                                 uint32_t* __restrict__ hist, uint32_t nb) {
+    __shared__ uint32_t s_h[kBinThreads / 32][256];
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t b = blockIdx.x;
+    const uint32_t slot_begin = b * (uint32_t)kBinTile, cnt = min((uint32_t)kBinTile, n - slot_begin);
+    const uint32_t dmask = (1u << bits) - 1u;
+    for (int i = tid; i < (kBinThreads / 32) * 256; i += kBinThreads) (&s_h[0][0])[i] = 0;
+    __syncthreads();
+#pragma unroll 4
+    for (int i = 0; i < kBinItems; ++i) {
+        const uint32_t e = i * kBinThreads + tid;
+        if (e < cnt) atomicAdd(&s_h[warp][(uint32_t)(keys[(size_t)slot_begin + e] >> shift) & dmask], 1u);
+    }
+    __syncthreads();
+    if (tid < (1 << bits)) {
+        uint32_t c = 0;
+#pragma unroll
+        for (int w = 0; w < kBinThreads / 32; ++w) c += s_h[w][tid];
+        hist[(size_t)tid * nb + b] = c;
     }
 }
 
@@ -833,6 +858,27 @@ int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1
     sp.shift = bits1; sp.bits = bits2; sp.scanned = b.hist2; sp.totals = b.totals + 256;
     rc = dispatch_scatter<2>(bits2, sp, nb, stream);
     if (rc) return rc;
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+// Stable LSD sort of n u64 keys on the 32 bits [32, 64) in four 8-bit passes (count -> scan -> scatter each, no
+// look-back): the depth ordering of the Gaussians. The sorted keys end up in keys_a. scratch: (256 * nb + 256) u32.
+int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* scratch, cudaStream_t stream) {
+    if (n == 0) return GS_OK;
+    const uint32_t nb = (n + kBinTile - 1) / kBinTile;
+    uint32_t* hist = scratch;
+    uint32_t* totals = scratch + (size_t)256 * nb;
+    for (int pass = 0; pass < 4; ++pass) {
+        const uint64_t* in = (pass & 1) ? keys_b : keys_a;
+        uint64_t* out = (pass & 1) ? keys_a : keys_b;
+        bin_count_kernel<<<nb, kBinThreads, 0, stream>>>(in, n, 32 + 8 * pass, 8, hist, nb);
+        bin_scan_kernel<<<256, 1024, 0, stream>>>(hist, nb, 256, totals, nullptr, 0, nullptr);
+        BinScatterParams sp = {};
+        sp.keys_in = in; sp.keys_out = out; sp.n = n; sp.nb = nb; sp.shift = 8 * pass; sp.bits = 8;
+        sp.scanned = hist; sp.totals = totals;
+        launch_scatter<0, 8>(sp, nb, stream);
+    }
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

@@ -101,6 +101,7 @@ int launch_inclusive_scan(const uint2* rect, const uint64_t* order, int n, uint3
                           cudaStream_t stream);
 int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1, int bits2, const uint4* emit,
                         const uint32_t* offsets, const BinningWS& b, uint2* ranges, cudaStream_t stream);
+int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* scratch, cudaStream_t stream);
 int launch_strip_ids(uint32_t n, const uint64_t* in, uint32_t* out, cudaStream_t stream);
 int launch_emit_instances(int P, const uint64_t* depth_order, const float2* means2D, const uint32_t* offsets,
                           const int* radii, uint2 grid, uint64_t* inst, cudaStream_t stream);

@@ -107,7 +107,8 @@ struct GeomWS {
         g.emit = c.take<uint4>(P);
         g.dkeys_a = c.take<uint64_t>(P);
         g.dkeys_b = c.take<uint64_t>(P);
-        g.dsort_scratch_bytes = radix_scratch_bytes(P, kDepthSortPasses);
+        // depth sort (launch_depth_sort): [256][nb] block histograms + 256 digit totals
+        g.dsort_scratch_bytes = (256 * ((P + kBinTile - 1) / kBinTile) + 256) * sizeof(uint32_t) + kAlign;
         g.dsort_scratch = c.take<char>(g.dsort_scratch_bytes);
         g.bytes = align_up(c.off, kAlign);
         return g;
