@@ -9,6 +9,7 @@
 // tiles_touched folded in (no separate memsets), 3 clamp flags packed in one byte.
 #include "gs_common.cuh"
 #include "kernels.cuh"
+#include "sh_stage.cuh"
 #include "workspace.cuh"
 
 namespace gs {
@@ -87,38 +88,74 @@ __device__ __noinline__ V3 sh_to_rgb(int deg, const V3 pos, const V3 campos, con
     return V3(fmaxf(result.x, 0.0f), fmaxf(result.y, 0.0f), fmaxf(result.z, 0.0f));
 }
 
-// One Gaussian: writes every per-Gaussian output (defaults for culled ones, replacing three host-side fills)
-// and returns tiles_touched.
-GS_DEV uint32_t preprocess_one(const PreprocessParams& p, const int idx) {
+constexpr int kPfThreads = 128;
+
+// One thread per Gaussian, in two phases around the arrival of the SH rows:
+//   phase 1  cull, projection, covariance, conic, radius, tile rectangle (everything that does not need colour);
+//   phase 2  SH colour, per-Gaussian outputs and the 48-byte render record.
+// The warp's SH rows are copied to shared memory with coalesced cp.async sweeps (sh_stage.cuh) issued right after the
+// frustum test, so the copies overlap phase 1; a thread reading its own 192-byte row straight from global memory
+// would touch 32 different lines per load instruction (the reference's access pattern, forward.cu:29).
+// Every per-Gaussian output is written (defaults for culled ones, replacing three host-side fills).
+__global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const PreprocessParams p) {
+    __shared__ float s_sh[kPfThreads / 32][32 * (kShMaxRow + 1)];
+    __shared__ uint32_t s_tiles;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_tiles = 0;
+    __syncthreads();
+    const bool valid = idx < p.P;
+    const size_t i = (size_t)(valid ? idx : 0);
+
     int out_radius = 0;
     uint32_t out_tiles = 0;
     uint2 out_rect = {0u, 0u};
     uint32_t depth_bits = 0xffffffffu;  // culled Gaussians sort behind every visible one
-    p.is_used[idx] = 0;
 
-    const float3 p_orig = {p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]};
+    const float3 p_orig = {p.means3D[3 * i], p.means3D[3 * i + 1], p.means3D[3 * i + 2]};
     const float4 p_hom = xform_point_4x4(p_orig, p.projmatrix);
     const float p_w = 1.0f / (p_hom.w + 0.0000001f);
     const float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
     const float3 p_view = xform_point_4x3(p_orig, p.viewmatrix);
 
-    bool alive = p_view.z > 0.2f;
-    if (!alive && p.prefiltered) {
+    const bool alive = valid && p_view.z > 0.2f;
+    if (valid && !alive && p.prefiltered) {
         printf("Point is filtered although prefiltered is set. This shouldn't happen!");
         __trap();
     }
 
+    // ---- SH rows of the Gaussians that passed the frustum test: start the copies now ----
+    const int Mrow = 3 * p.M;
+    const bool use_sh = p.colors_precomp == nullptr;
+    const bool staged = use_sh && Mrow <= kShMaxRow;
+    const int row_stride = Mrow | 1;
+    const int warp_first = idx - lane;
+    const int rows_valid = min(32, p.P - warp_first);
+    const uint32_t alive_mask = __ballot_sync(0xffffffffu, alive);
+    float* tile = &s_sh[warp][0];
+    const int ncoef3 = 3 * (p.D + 1) * (p.D + 1);
+    if (staged && alive_mask) {
+        float* src = const_cast<float*>(p.shs) + (size_t)warp_first * Mrow;
+        if (Mrow == 48) stage_sh_rows<true, 48>(tile, row_stride, src, Mrow, rows_valid, alive_mask, ncoef3, lane);
+        else stage_sh_rows<true, 0>(tile, row_stride, src, Mrow, rows_valid, alive_mask, ncoef3, lane);
+    }
+
+    // ---- phase 1 ----
+    bool visible = false;
+    float3 conic = {0.f, 0.f, 0.f};
+    float2 point_image = {0.f, 0.f};
+    float my_radius = 0.f;
     if (alive) {
         const float* cov3D;
         float cov_local[6];
         if (p.cov3D_precomp != nullptr) {
-            cov3D = p.cov3D_precomp + 6 * (size_t)idx;
+            cov3D = p.cov3D_precomp + 6 * i;
         } else {
-            const V3 s(p.scales[3 * idx], p.scales[3 * idx + 1], p.scales[3 * idx + 2]);
+            const V3 s(p.scales[3 * i], p.scales[3 * i + 1], p.scales[3 * i + 2]);
             const float4 q = reinterpret_cast<const float4*>(p.rotations)[idx];
             cov3d_from_scale_rot(s, p.scale_modifier, q, cov_local);
 #pragma unroll
-            for (int i = 0; i < 6; ++i) p.cov3D[6 * (size_t)idx + i] = cov_local[i];
+            for (int k = 0; k < 6; ++k) p.cov3D[6 * i + k] = cov_local[k];
             cov3D = cov_local;
         }
         const float3 cov = cov2d_ewa(p_orig, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, cov3D, p.viewmatrix);
@@ -126,49 +163,17 @@ GS_DEV uint32_t preprocess_one(const PreprocessParams& p, const int idx) {
         const float det = (cov.x * cov.z - cov.y * cov.y);
         if (det != 0.0f) {
             const float det_inv = 1.f / det;
-            const float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+            conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
             const float mid = 0.5f * (cov.x + cov.z);
             const float lambda1 = mid + sqrt(max(0.1f, mid * mid - det));
             const float lambda2 = mid - sqrt(max(0.1f, mid * mid - det));
-            const float my_radius = ceil(3.f * sqrt(max(lambda1, lambda2)));
-            const float2 point_image = {ndc_to_pix(p_proj.x, p.W), ndc_to_pix(p_proj.y, p.H)};
+            my_radius = ceil(3.f * sqrt(max(lambda1, lambda2)));
+            point_image = {ndc_to_pix(p_proj.x, p.W), ndc_to_pix(p_proj.y, p.H)};
             uint2 rect_min, rect_max;
             tile_rect(point_image, (int)my_radius, rect_min, rect_max, p.grid);
             const uint32_t ntiles = (rect_max.x - rect_min.x) * (rect_max.y - rect_min.y);
             if (ntiles != 0) {
-                float3 col;
-                if (p.colors_precomp == nullptr) {
-                    uint8_t cb;
-                    const V3 campos(p.campos[0], p.campos[1], p.campos[2]);
-                    const V3 c = sh_to_rgb(p.D, V3(p_orig.x, p_orig.y, p_orig.z), campos,
-                                           p.shs + (size_t)idx * p.M * 3, cb);
-                    p.rgb[3 * (size_t)idx + 0] = c.x;
-                    p.rgb[3 * (size_t)idx + 1] = c.y;
-                    p.rgb[3 * (size_t)idx + 2] = c.z;
-                    p.clamped[idx] = cb;
-                    col = make_float3(c.x, c.y, c.z);
-                } else {
-                    col = make_float3(p.colors_precomp[3 * (size_t)idx], p.colors_precomp[3 * (size_t)idx + 1],
-                                      p.colors_precomp[3 * (size_t)idx + 2]);
-                }
-                const float opacity = p.opacities[idx];
-                p.depths[idx] = p_view.z;
-                p.means2D[idx] = point_image;
-                p.conic_opacity[idx] = {conic.x, conic.y, conic.z, opacity};
-                // Render record. thr is a conservative reject threshold: power < thr  ==>  opacity * expf(power) < 1/255
-                // (1e-3 slack in the exponent, far above the expf / logf / product rounding errors), so the renderers can
-                // skip expf — and whole pixel patches — for such pairs without changing any decision.
-                float thr;
-                if (opacity > 0.0f) {
-                    const float lt = logf(1.0f / (255.0f * opacity));
-                    thr = lt - 0.001f - 1e-6f * fabsf(lt);
-                } else {
-                    thr = opacity == opacity ? 1.0f : -INFINITY;  // non-positive opacity never passes; NaN takes the exact path
-                }
-                float4* dst = reinterpret_cast<float4*>(p.rec + idx);
-                dst[0] = make_float4(point_image.x, point_image.y, conic.x, conic.y);
-                dst[1] = make_float4(conic.z, opacity, thr, __int_as_float(idx));
-                dst[2] = make_float4(col.x, col.y, col.z, p_view.z);
+                visible = true;
                 out_radius = (int)my_radius;
                 out_tiles = ntiles;
                 out_rect = make_uint2(rect_min.x | (rect_min.y << 16), (rect_max.x - rect_min.x) | ((rect_max.y - rect_min.y) << 16));
@@ -176,23 +181,56 @@ GS_DEV uint32_t preprocess_one(const PreprocessParams& p, const int idx) {
             }
         }
     }
-    p.radii[idx] = out_radius;
-    p.tiles_touched[idx] = out_tiles;
-    p.rect[idx] = out_rect;
-    p.depth_keys[idx] = ((uint64_t)depth_bits << 32) | (uint32_t)idx;
-    return out_tiles;
-}
 
-__global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessParams p) {
-    __shared__ uint32_t s_tiles;
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (threadIdx.x == 0) s_tiles = 0;
-    __syncthreads();
-    uint32_t out_tiles = 0;
-    if (idx < p.P) out_tiles = preprocess_one(p, idx);
+    // ---- the SH rows have landed ----
+    cp_async_wait_all();
+    __syncwarp();
+
+    // ---- phase 2 ----
+    if (visible) {
+        float3 col;
+        if (use_sh) {
+            uint8_t cb;
+            const V3 campos(p.campos[0], p.campos[1], p.campos[2]);
+            const float* my_sh = staged ? tile + lane * row_stride : p.shs + i * Mrow;
+            const V3 c = sh_to_rgb(p.D, V3(p_orig.x, p_orig.y, p_orig.z), campos, my_sh, cb);
+            p.rgb[3 * i + 0] = c.x;
+            p.rgb[3 * i + 1] = c.y;
+            p.rgb[3 * i + 2] = c.z;
+            p.clamped[idx] = cb;
+            col = make_float3(c.x, c.y, c.z);
+        } else {
+            col = make_float3(p.colors_precomp[3 * i], p.colors_precomp[3 * i + 1], p.colors_precomp[3 * i + 2]);
+        }
+        const float opacity = p.opacities[idx];
+        p.depths[idx] = p_view.z;
+        p.means2D[idx] = point_image;
+        p.conic_opacity[idx] = {conic.x, conic.y, conic.z, opacity};
+        // Render record. thr is a conservative reject threshold: power < thr  ==>  opacity * expf(power) < 1/255
+        // (1e-3 slack in the exponent, far above the expf / logf / product rounding errors), so the renderers can
+        // skip expf — and whole pixel patches — for such pairs without changing any decision.
+        float thr;
+        if (opacity > 0.0f) {
+            const float lt = logf(1.0f / (255.0f * opacity));
+            thr = lt - 0.001f - 1e-6f * fabsf(lt);
+        } else {
+            thr = opacity == opacity ? 1.0f : -INFINITY;  // non-positive opacity never passes; NaN takes the exact path
+        }
+        float4* dst = reinterpret_cast<float4*>(p.rec + idx);
+        dst[0] = make_float4(point_image.x, point_image.y, conic.x, conic.y);
+        dst[1] = make_float4(conic.z, opacity, thr, __int_as_float(idx));
+        dst[2] = make_float4(col.x, col.y, col.z, p_view.z);
+    }
+    if (valid) {
+        p.is_used[idx] = 0;
+        p.radii[idx] = out_radius;
+        p.tiles_touched[idx] = out_tiles;
+        p.rect[idx] = out_rect;
+        p.depth_keys[idx] = ((uint64_t)depth_bits << 32) | (uint32_t)idx;
+    }
     // Instance count R = sum of tiles_touched: one atomic per warp into shared memory, one per block to global.
     const uint32_t wsum = __reduce_add_sync(0xffffffffu, out_tiles);
-    if ((threadIdx.x & 31) == 0 && wsum) atomicAdd(&s_tiles, wsum);
+    if (lane == 0 && wsum) atomicAdd(&s_tiles, wsum);
     __syncthreads();
     if (threadIdx.x == 0 && s_tiles) atomicAdd(p.num_rendered, s_tiles);
 }
@@ -208,7 +246,7 @@ __global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* _
 
 int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream) {
     if (p.P <= 0) return GS_OK;
-    preprocess_fwd_kernel<<<(p.P + 255) / 256, 256, 0, stream>>>(p);
+    preprocess_fwd_kernel<<<(p.P + kPfThreads - 1) / kPfThreads, kPfThreads, 0, stream>>>(p);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
