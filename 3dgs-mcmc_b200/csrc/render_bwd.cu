@@ -38,12 +38,6 @@ GS_DEV void red_add_f32x4(float4* addr, const float a, const float b, const floa
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-GS_DEV float ex2_approx(const float x) {
-    float y;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-}
-
 constexpr int kBwdWarps = GS_TILE_PIX / 32;
 
 // Dynamic shared-memory layout of render_bwd_kernel<CH, ROWS>.
@@ -256,10 +250,11 @@ __global__ void __launch_bounds__(GS_TILE_PIX, MIN_CTAS) render_bwd_kernel(const
                 const float4 q1 = rec[3 * j + 1];   // C, opacity, thr, id
                 const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
                 const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-                // ex2.approx (2 ulp) instead of the forward's expf: a pair whose alpha sits within ~1e-7 of the 1/255
-                // threshold may be classified differently than in the forward; the effect (one 0.4 % factor on a handful of
-                // pixels) is orders of magnitude inside the gradient tolerance.
-                const float G = ex2_approx(power * 1.4426950408889634f);
+                // The same expf as the forward, on purpose: the replay T <- T / (1 - alpha) only telescopes back to the
+                // forward's transmittances when alpha is reproduced bit for bit. With ex2.approx (7 instructions fewer
+                // per pair) the gradients drifted by ~3e-5 relative and dL/dopacity, a sum with heavy cancellation, by
+                // 1.1e-3 against the reference (tools/diag_grad_noise.py) - outside the 1e-3 tolerance.
+                const float G = exp(power);
                 const float alpha = min(0.99f, q1.y * G);
                 const bool act = pos < last_contributor && !(power > 0.0f) && !(power < q1.z) && !(alpha < 1.0f / 255.0f);
                 // No warp-wide early-outs here: 99 % of the splats that pass the patch cull are blended by some lane.

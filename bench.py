@@ -59,7 +59,7 @@ def workload_config(P, W, H, n_gpus):
                         f"{W}x{H}, orbit cameras r=6 fovx=1.2; BASELINE.json config 3/4 shape at the headline size",
             "gaussians": P, "width": W, "height": H, "views_per_step": n_gpus,
             "parallelism": f"view-sharded dp{n_gpus}, replicated Gaussians" + (", NCCL all-reduce of the 59*P-float gradient arena" if n_gpus > 1 else ""),
-            "l2_policy": "inputs (708 MB of parameters, ~1.5 GB of instance records) exceed the 126 MB L2; no explicit flush"}
+            "l2_policy": "inputs (708 MB of parameters, 0.9 GB of gradients, ~0.4 GB of instance keys/ids per step) exceed the 126 MB L2; no explicit flush"}
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -304,16 +304,17 @@ def run_b200_arm(args):
         return ms / calls if calls else None
 
     M = 16
-    alg_bytes = {  # SURVEY.md §8(d) per-unit figures x units of this launch
-        "preprocess_fwd": visible * (44 + 12 * M + 75 + 48 + 8) + (P - visible) * 60,
-        "depth_sort": P * 16,                       # read + write one u64 key per Gaussian (algorithmic minimum)
-        "scan": P * 16,
-        "emit_instances": P * 24 + R * 8,
-        "tile_sort": R * 16,                         # read + write one u64 instance (algorithmic minimum; 2 passes move 40 B)
-        "tile_ranges": R * 8 + len(tile_len) * 8,
-        "render_fwd": R * (8 + 48) + W * H * 20,      # instance list streamed; 48-B records gathered (mostly L2 hits)
-        "render_bwd": int(tmax.long().sum().item()) * (8 + 48) + W * H * 20 + visible * 36,
-        "preprocess_bwd": visible * (107 + 12 * M + 40 + 12 * M) + (P - visible) * (4 + 300),
+    tiles_n = len(tile_len)
+    # ALGORITHMIC bytes: SURVEY.md §8(d) per-unit figures (what the reference formulation of each stage has to move) x the
+    # units of this launch. Our fused stages are charged the sum of the reference stages they replace.
+    alg_bytes = {
+        "preprocess_fwd": visible * 311 + (P - visible) * 52,                 # 44 + 12(D+1)^2 read + 75 written | 44 + 8
+        "depth_sort": P * 16,                                                  # one u64 key per Gaussian in and out
+        "scan": P * 8,                                                         # InclusiveSum over tiles_touched
+        "tile_sort": visible * 20 + R * 12 + R * 24 + R * 8 + tiles_n * 8,     # duplicateWithKeys + SortPairs (minimum) + identifyTileRanges
+        "render_fwd": R * 28 + W * H * 20,
+        "render_bwd": R * 40 + W * H * 20 + visible * 36,
+        "preprocess_bwd": visible * 531 + (P - visible) * 304,                 # cov2D + preprocess backward; zero gradients of culled ones
         "bwd_zero": P * 36,
     }
     stage_report = {}
@@ -321,7 +322,11 @@ def run_b200_arm(args):
         ms = stage_ms(name)
         if ms:
             stage_report[name] = {"ms": round(ms, 4), "alg_GBps": round(b / ms / 1e6, 1), "hbm_frac": round(b / ms / 1e6 / hbm_peak, 4)}
-    dom = max(("render_bwd", "render_fwd", "tile_sort", "preprocess_bwd", "preprocess_fwd", "emit_instances"),
+    try:
+        ncu_traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+    except Exception:
+        ncu_traffic = {}
+    dom = max(("render_bwd", "render_fwd", "tile_sort", "preprocess_bwd", "preprocess_fwd"),
               key=lambda n: stage_ms(n) or 0.0)
     dom_ms = stage_ms(dom)
     if dom in ("render_bwd", "render_fwd"):
@@ -329,7 +334,8 @@ def run_b200_arm(args):
         fl = pairs * (FLOPS_PER_PAIR_BWD if dom == "render_bwd" else FLOPS_PER_PAIR_FWD)
         achieved = fl / (dom_ms * 1e-3) / 1e12
         roofline = {"kernel": dom, "bound": "fp32", "achieved": round(achieved, 3), "peak": round(fp32_peak_tflops, 2),
-                    "unit": "TFLOP/s", "frac": round(achieved / fp32_peak_tflops, 4), "traffic": None,
+                    "unit": "TFLOP/s", "frac": round(achieved / fp32_peak_tflops, 4),
+                    "traffic": (ncu_traffic.get(dom) or {}).get("bytes"), "traffic_source": (ncu_traffic.get(dom) or {}).get("capture"),
                     "ms": round(dom_ms, 4), "evaluated_pairs": pairs,
                     "note": "FP32-SIMT bound (no tensor-core work on this path): algorithmic flops = evaluated (pixel, splat) pairs x "
                             f"{FLOPS_PER_PAIR_BWD if dom == 'render_bwd' else FLOPS_PER_PAIR_FWD} (SURVEY.md 8d); peak = SMs x 128 lanes x 2 x max SM clock; "
@@ -337,7 +343,8 @@ def run_b200_arm(args):
     else:
         achieved = alg_bytes[dom] / (dom_ms * 1e-3) / 1e9
         roofline = {"kernel": dom, "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s",
-                    "frac": round(achieved / hbm_peak, 4), "traffic": None, "ms": round(dom_ms, 4), "peak_source": peak_src}
+                    "frac": round(achieved / hbm_peak, 4), "traffic": (ncu_traffic.get(dom) or {}).get("bytes"),
+                    "traffic_source": (ncu_traffic.get(dom) or {}).get("capture"), "ms": round(dom_ms, 4), "peak_source": peak_src}
 
     # ---- e2e: public API, host buffers in, loss out ----
     # Every step copies its own ground-truth image and camera from pinned host memory (inside the timed region) and

@@ -69,6 +69,33 @@ def test_forward_bit_exact_and_gradients_vs_reference(kind, P, W, H, rad, fovx):
         assert rep[f"grad_{n}_rel_l2"] < GRAD_TOL, (n, rep[f"grad_{n}_rel_l2"])
 
 
+def test_generic_binning_path():
+    """Images with more than 65536 tiles take the generic binning path (emission + multi-pass radix sort). The switch
+    is read once per process, so the same bit-exact comparison runs in a child process with the path forced."""
+    import subprocess
+    import sys
+    ref()
+    code = (
+        "import sys, json; sys.path[:0] = [%r, %r, %r]\n"
+        "import helpers\n"
+        "out = {}\n"
+        "for kind, P, W, H, rad, fovx in (('cube', 20000, 250, 130, 4.03, 0.6911), ('garden', 200000, 640, 360, 6.0, 1.2)):\n"
+        "    scene, cam = helpers.make_case(kind, P, W, H, seed=0, cam_radius=rad, fovx=fovx)\n"
+        "    out[kind] = helpers.compare_with_reference(scene, cam)\n"
+        "print('REPORT' + json.dumps(out))\n"
+    ) % (os.path.dirname(os.path.abspath(__file__)), os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "3dgs-mcmc_b200"),
+         os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+    env = dict(os.environ, GS_FORCE_GENERIC_BINNING="1")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    import json
+    line = [ln for ln in r.stdout.splitlines() if ln.startswith("REPORT")][-1]
+    for kind, rep in json.loads(line[len("REPORT"):]).items():
+        assert_forward_bit_exact(rep)
+        for n in GRAD_NAMES:
+            assert rep[f"grad_{n}_rel_l2"] < GRAD_TOL, (kind, n, rep[f"grad_{n}_rel_l2"])
+
+
 @pytest.mark.parametrize("degree", [0, 1, 2])
 def test_lower_sh_degrees_vs_reference(degree):
     ref()
