@@ -37,11 +37,12 @@ struct BwdScratch {
 // ---- optional per-stage timing (CUDA events on the caller's stream) and a kernel-launch counter ----
 enum Stage {
     ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_PACK, ST_RENDER_FWD, ST_BWD_ZERO, ST_RENDER_BWD,
-    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_COUNT
+    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_DP_PUSH, ST_DP_COMBINE, ST_DP_ALL_REDUCE, ST_COUNT
 };
 const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "scan", "emit_instances", "tile_sort", "tile_ranges",
                                            "render_fwd", "bwd_zero", "render_bwd", "preprocess_bwd",
-                                           "compute_relocation", "add_noise"};
+                                           "compute_relocation", "add_noise", "dp_color_grad_push", "dp_sh_grad_combine",
+                                           "dp_slab_all_reduce"};
 struct Profiler {
     bool on = false;
     std::vector<cudaEvent_t> ev;
@@ -62,7 +63,7 @@ inline void count_launches(int k) { g_prof.launches += (unsigned long long)k; }
 
 extern "C" {
 
-int gs_abi_version(void) { return 102; }
+int gs_abi_version(void) { return 103; }
 
 const char* gs_error_string(int code) {
     if (code == GS_OK) return "ok";
@@ -223,22 +224,12 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
     return rc;
 }
 
-int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H, const float* background,
-                const float* means3D, const float* shs, const float* colors_precomp, const float* scales,
-                float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
-                const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, const int* radii,
-                const void* geom_ws, const void* binning_ws, const void* image_ws, const float* dL_dpix, void* scratch,
-                float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
-                float* dL_dsh, float* dL_dscales, float* dL_drotations) {
+int gs_backward_render(void* stream_, int P, unsigned int R, int W, int H, const float* background, const void* geom_ws,
+                       const void* binning_ws, const void* image_ws, const float* dL_dpix, void* scratch) {
     cudaStream_t stream = (cudaStream_t)stream_;
-    if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return GS_ERR_ARG;
+    if (P < 0 || W <= 0 || H <= 0) return GS_ERR_ARG;
     if (P == 0) return GS_OK;
-    if (!means3D || !radii || !geom_ws || !binning_ws || !image_ws || !dL_dpix || !scratch || !background ||
-        !viewmatrix || !projmatrix)
-        return GS_ERR_ARG;
-    if (!dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || !dL_dscales || !dL_drotations)
-        return GS_ERR_ARG;
-    if (shs && (!dL_dsh || !campos)) return GS_ERR_ARG;
+    if (!geom_ws || !binning_ws || !image_ws || !dL_dpix || !scratch || !background) return GS_ERR_ARG;
     uint2 grid;
     const uint32_t tiles = tiles_of(W, H, &grid);
     ImageWS img = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
@@ -248,19 +239,37 @@ int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H
     prof_mark(stream, -1);
     GS_CUDA_TRY(cudaMemsetAsync(sc.acc_color_opacity, 0, sc.bytes, stream));
     prof_mark(stream, ST_BWD_ZERO);
-
-    int rc = GS_OK;
     if (R > 0) {
         RenderBwdParams rb;
         rb.ranges = img.ranges; rb.ids = b.ids; rb.rec = g.rec; rb.tile_max_contrib = img.tile_max_contrib;
         rb.W = W; rb.H = H; rb.tiles_x = (int)grid.x; rb.bg = background; rb.final_T = img.final_T;
         rb.n_contrib = img.n_contrib; rb.dL_dpix = dL_dpix;
         rb.acc_color_opacity = sc.acc_color_opacity; rb.acc_mean_conic = sc.acc_mean_conic; rb.acc_conic_w = sc.acc_conic_w;
-        rc = launch_render_bwd(rb, (int)tiles, stream);
+        const int rc = launch_render_bwd(rb, (int)tiles, stream);
         if (rc) return rc;
         prof_mark(stream, ST_RENDER_BWD);
         count_launches(1);
     }
+    return GS_OK;
+}
+
+int gs_backward_geometry(void* stream_, int P, int D, int M, int W, int H, const float* means3D, const float* shs,
+                         const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                         const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,
+                         float tan_fovy, const int* radii, const void* geom_ws, const void* scratch, float* dL_dmeans2D,
+                         float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                         float* dL_dscales, float* dL_drotations) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return GS_ERR_ARG;
+    if (P == 0) return GS_OK;
+    if (!means3D || !radii || !geom_ws || !scratch || !viewmatrix || !projmatrix) return GS_ERR_ARG;
+    if (!dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || !dL_dscales || !dL_drotations)
+        return GS_ERR_ARG;
+    if (shs && !campos) return GS_ERR_ARG;
+    if (shs && !dL_dsh && 3 * M > 48) return GS_ERR_ARG;   // factored mode needs the staged SH rows (sh_stage.cuh: kShMaxRow)
+    GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
+    BwdScratch sc = BwdScratch::carve(aligned_base(scratch), (size_t)P);
+    prof_mark(stream, -1);
     PreprocessBwdParams pb;
     pb.P = P; pb.D = D; pb.M = M; pb.means3D = means3D; pb.radii = radii; pb.shs = shs; pb.clamped = g.clamped;
     pb.scales = cov3D_precomp ? nullptr : scales; pb.rotations = rotations; pb.scale_modifier = scale_modifier;
@@ -272,8 +281,89 @@ int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H
     pb.acc_color_opacity = sc.acc_color_opacity; pb.acc_mean_conic = sc.acc_mean_conic; pb.acc_conic_w = sc.acc_conic_w;
     pb.dL_dmeans3D = dL_dmeans3D; pb.dL_dmeans2D = dL_dmeans2D; pb.dL_dcolors = dL_dcolors; pb.dL_dopacity = dL_dopacity;
     pb.dL_dcov3D = dL_dcov3D; pb.dL_dsh = dL_dsh; pb.dL_dscales = dL_dscales; pb.dL_drots = dL_drotations;
-    rc = launch_preprocess_bwd(pb, stream);
+    const int rc = launch_preprocess_bwd(pb, stream);
     prof_mark(stream, ST_PREPROCESS_BWD);
+    count_launches(1);
+    return rc;
+}
+
+int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H, const float* background,
+                const float* means3D, const float* shs, const float* colors_precomp, const float* scales,
+                float scale_modifier, const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                const void* geom_ws, const void* binning_ws, const void* image_ws, const float* dL_dpix, void* scratch,
+                float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                float* dL_dsh, float* dL_dscales, float* dL_drotations) {
+    (void)colors_precomp;
+    if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return GS_ERR_ARG;
+    if (P == 0) return GS_OK;
+    if (!means3D || !radii || !geom_ws || !binning_ws || !image_ws || !dL_dpix || !scratch || !background ||
+        !viewmatrix || !projmatrix)
+        return GS_ERR_ARG;
+    if (!dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || !dL_dscales || !dL_drotations)
+        return GS_ERR_ARG;
+    if (shs && (!dL_dsh || !campos)) return GS_ERR_ARG;
+    int rc = gs_backward_render(stream_, P, R, W, H, background, geom_ws, binning_ws, image_ws, dL_dpix, scratch);
+    if (rc) return rc;
+    return gs_backward_geometry(stream_, P, D, M, W, H, means3D, shs, scales, scale_modifier, rotations, cov3D_precomp,
+                                viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii, geom_ws, scratch, dL_dmeans2D,
+                                dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
+}
+
+static int fill_peers(DpPeers* peers, float* const* ptrs, int n) {
+    if (!ptrs || n < 1 || n > 8) return GS_ERR_ARG;
+    for (int r = 0; r < 8; ++r) peers->ptr[r] = r < n ? ptrs[r] : nullptr;
+    for (int r = 0; r < n; ++r)
+        if (!ptrs[r] || (reinterpret_cast<size_t>(ptrs[r]) & 15)) return GS_ERR_ARG;
+    peers->n = n;
+    return GS_OK;
+}
+
+int gs_dp_color_grad_push(void* stream_, int P, const int* radii, const void* geom_ws, const void* scratch,
+                          float* const* dst_ptrs, int n_dst, int multicast, size_t slot_offset) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || (slot_offset & 3)) return GS_ERR_ARG;
+    if (P == 0) return GS_OK;
+    if (!radii || !geom_ws || !scratch) return GS_ERR_ARG;
+    DpPeers peers;
+    int rc = fill_peers(&peers, dst_ptrs, n_dst);
+    if (rc) return rc;
+    if (multicast && n_dst != 1) return GS_ERR_ARG;
+    GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
+    BwdScratch sc = BwdScratch::carve(aligned_base(scratch), (size_t)P);
+    prof_mark(stream, -1);
+    rc = launch_color_grad_push(P, radii, g.clamped, sc.acc_color_opacity, peers, slot_offset, multicast != 0, stream);
+    prof_mark(stream, ST_DP_PUSH);
+    count_launches(1);
+    return rc;
+}
+
+int gs_dp_sh_grad_combine(void* stream_, int P, int D, int M, int V, const float* means3D, const float* campos_views,
+                          const float* color_grads, size_t slot_stride, float* dL_dsh) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || D < 0 || D > 3 || V < 1) return GS_ERR_ARG;
+    if (P == 0) return GS_OK;
+    if (!means3D || !campos_views || !color_grads || !dL_dsh || slot_stride < (size_t)3 * P) return GS_ERR_ARG;
+    prof_mark(stream, -1);
+    const int rc = launch_sh_grad_combine(P, D, M, V, means3D, campos_views, color_grads, slot_stride, dL_dsh, stream);
+    prof_mark(stream, ST_DP_COMBINE);
+    count_launches(1);
+    return rc;
+}
+
+int gs_dp_slab_all_reduce(void* stream_, float* const* slab_ptrs, int n_ptrs, int multicast, size_t n_floats, int rank,
+                          int world) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    DpPeers peers;
+    int rc = fill_peers(&peers, slab_ptrs, n_ptrs);
+    if (rc) return rc;
+    if (multicast ? n_ptrs != 1 : n_ptrs != world) return GS_ERR_ARG;
+    int dev = 0, sms = 0;
+    GS_CUDA_TRY(cudaGetDevice(&dev));
+    GS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    prof_mark(stream, -1);
+    rc = launch_slab_all_reduce(peers, multicast != 0, n_floats, rank, world, sms, stream);
+    prof_mark(stream, ST_DP_ALL_REDUCE);
     count_launches(1);
     return rc;
 }

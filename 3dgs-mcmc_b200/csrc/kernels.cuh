@@ -90,9 +90,16 @@ struct PreprocessBwdParams {
     float* __restrict__ dL_dcolors;    // [P,3]
     float* __restrict__ dL_dopacity;   // [P]
     float* __restrict__ dL_dcov3D;     // [P,6]
-    float* __restrict__ dL_dsh;        // [P,M,3]
+    float* __restrict__ dL_dsh;        // [P,M,3]; null with shs non-null = factored exchange (dp_exchange.cu): rows not written
     float* __restrict__ dL_dscales;    // [P,3]
     float* __restrict__ dL_drots;      // [P,4]
+};
+
+// Up to 8 device pointers to the same symmetric buffer on the ranks of one node (index = rank), or one NVSwitch
+// multicast pointer in ptr[0] with n == 1 (dp_exchange.cu).
+struct DpPeers {
+    float* ptr[8];
+    int n;
 };
 
 int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream);
@@ -118,5 +125,12 @@ int launch_compute_relocation(int P, const float* opacity_old, const float* scal
 int launch_add_noise(int P, float* xyz, const float* scaling_raw, const float* rotation_raw, const float* opacity_raw,
                      const float* noise, float lr_scale, unsigned long long seed, unsigned long long offset,
                      cudaStream_t stream);
+
+int launch_color_grad_push(int P, const int* radii, const uint8_t* clamped, const float4* acc, const DpPeers& dst,
+                           size_t slot_offset, bool multicast, cudaStream_t stream);
+int launch_sh_grad_combine(int P, int D, int M, int V, const float* means3D, const float* campos, const float* gathered,
+                           size_t slot_stride, float* dL_dsh, cudaStream_t stream);
+int launch_slab_all_reduce(const DpPeers& peers, bool multicast, size_t n_floats, int rank, int world, int sm_count,
+                           cudaStream_t stream);
 
 }  // namespace gs

@@ -176,7 +176,8 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
     float dscale[3] = {0.f, 0.f, 0.f};
     float4 drot = make_float4(0.f, 0.f, 0.f, 0.f);
     const int ncoef = (p.D + 1) * (p.D + 1);
-    float* my_dsh = p.shs ? (staged ? tile + lane * row_stride : p.dL_dsh + i * Mrow) : nullptr;
+    const bool write_dsh = p.dL_dsh != nullptr;   // false: the caller rebuilds dL_dsh from the colour gradients (dp_exchange.cu)
+    float* my_dsh = p.shs ? (staged ? tile + lane * row_stride : (write_dsh ? p.dL_dsh + i * Mrow : nullptr)) : nullptr;
     const float* my_sh = p.shs ? (staged ? tile + lane * row_stride : p.shs + i * Mrow) : nullptr;
 
     if (visible) {
@@ -295,7 +296,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
     if (staged) {
         // ---- SH gradient rows out: coalesced, zeros for culled Gaussians and unused coefficients ----
         __syncwarp();
-        if (rows_valid > 0) {
+        if (rows_valid > 0 && write_dsh) {
             float* dst = p.dL_dsh + (size_t)warp_first * Mrow;
             if (Mrow == 48) stage_sh_rows<false, 48>(tile, row_stride, dst, Mrow, rows_valid, vis_mask, 3 * ncoef, lane);
             else stage_sh_rows<false, 0>(tile, row_stride, dst, Mrow, rows_valid, vis_mask, 3 * ncoef, lane);

@@ -40,6 +40,14 @@ SIGNATURES = {
     "gs_forward_render": (_c_int, [_c_void_p, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 8),
     "gs_backward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 5
                     + [_c_float] + [_c_void_p] * 5 + [_c_float, _c_float] + [_c_void_p] * 14),
+    "gs_backward_render": (_c_int, [_c_void_p, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 6),
+    "gs_backward_geometry": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int] + [_c_void_p] * 3 + [_c_float]
+                             + [_c_void_p] * 5 + [_c_float, _c_float] + [_c_void_p] * 11),
+    "gs_dp_color_grad_push": (_c_int, [_c_void_p, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_int,
+                                       _c_size_t]),
+    "gs_dp_sh_grad_combine": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p,
+                                       _c_size_t, _c_void_p]),
+    "gs_dp_slab_all_reduce": (_c_int, [_c_void_p, _c_void_p, _c_int, _c_int, _c_size_t, _c_int, _c_int]),
     "gs_mark_visible": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4),
     "gs_compute_relocation": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 2),
     "gs_add_noise": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 5 + [_c_float, _c_ull, _c_ull]),
@@ -230,16 +238,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     radii = radii.contiguous()
 
     with torch.cuda.device(device):
-        # Every output is fully written by the fused backward kernel: no zero fill.
-        names = ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")
-        outs = []
-        for name, shape in zip(names, shapes):
-            t = out_buffers.get(name) if out_buffers else None
-            if t is None:
-                t = torch.empty(shape, **opts)
-            elif tuple(t.shape) != shape or t.dtype != torch.float32 or not t.is_contiguous() or t.device != device:
-                raise RuntimeError(f"out_buffers['{name}'] must be a contiguous float32 {shape} tensor on {device}")
-            outs.append(t)
+        outs = _backward_outputs(P, M, device, out_buffers, want_sh=True)
         dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations = outs
         scratch = torch.empty(_lib.gs_backward_scratch_bytes(P), dtype=torch.uint8, device=device)
         _check(_lib.gs_backward(
@@ -253,6 +252,122 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         if debug:
             _debug_sync("backward")
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
+
+
+_BWD_NAMES = ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")
+
+
+def _backward_outputs(P, M, device, out_buffers, want_sh):
+    """The eight gradient tensors of the backward, taken from out_buffers where given. Every one is fully written by
+    the kernels (no zero fill). want_sh=False leaves the SH slot None (factored exchange)."""
+    opts = dict(dtype=torch.float32, device=device)
+    shapes = [(P, 3), (P, 3), (P, 1), (P, 3), (P, 6), (P, M, 3), (P, 3), (P, 4)]
+    outs = []
+    for name, shape in zip(_BWD_NAMES, shapes):
+        if name == "sh" and not want_sh:
+            outs.append(None)
+            continue
+        t = out_buffers.get(name) if out_buffers else None
+        if t is None:
+            t = torch.empty(shape, **opts)
+        elif tuple(t.shape) != shape or t.dtype != torch.float32 or not t.is_contiguous() or t.device != device:
+            raise RuntimeError(f"out_buffers['{name}'] must be a contiguous float32 {shape} tensor on {device}")
+        outs.append(t)
+    return outs
+
+
+def backward_render(background, P, R, dL_dout_color, geomBuffer, binningBuffer, imageBuffer):
+    """First half of the backward (gs_backward_render): zero the per-Gaussian accumulators and run the tile kernel.
+    Returns the scratch tensor that backward_geometry / dp_color_grad_push read."""
+    device = dL_dout_color.device
+    H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
+    background = _f32_cuda(background, "bg", device)
+    dL_dout_color = _f32_cuda(dL_dout_color, "dL_dout_color", device)
+    with torch.cuda.device(device):
+        scratch = torch.empty(max(_lib.gs_backward_scratch_bytes(P), 16), dtype=torch.uint8, device=device)
+        _check(_lib.gs_backward_render(_stream(device), int(P), int(R), W, H, _ptr(background), geomBuffer.data_ptr(),
+                                       binningBuffer.data_ptr(), imageBuffer.data_ptr(), dL_dout_color.data_ptr(),
+                                       scratch.data_ptr()), "gs_backward_render")
+    return scratch
+
+
+def backward_geometry(means3D, radii, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx,
+                      tan_fovy, H, W, sh, degree, campos, geomBuffer, scratch, out_buffers=None, write_sh=True):
+    """Second half of the backward (gs_backward_geometry). write_sh=False: the SH gradient is not written (the caller
+    rebuilds the cross-view sum with dp_sh_grad_combine); the returned tuple has None in its place."""
+    device = means3D.device
+    P = int(means3D.size(0))
+    M = int(sh.size(1)) if sh is not None and sh.numel() != 0 else 0
+    means3D = _f32_cuda(means3D, "means3D", device)
+    scales = _f32_cuda(scales, "scales", device)
+    rotations = _f32_cuda(rotations, "rotations", device)
+    cov3D_precomp = _f32_cuda(cov3D_precomp, "cov3D_precomp", device)
+    viewmatrix = _f32_cuda(viewmatrix, "viewmatrix", device)
+    projmatrix = _f32_cuda(projmatrix, "projmatrix", device)
+    sh = _f32_cuda(sh, "sh", device)
+    campos = _f32_cuda(campos, "campos", device)
+    radii = radii.contiguous()
+    with torch.cuda.device(device):
+        outs = _backward_outputs(P, M, device, out_buffers, want_sh=write_sh)
+        dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations = outs
+        if P:
+            _check(_lib.gs_backward_geometry(
+                _stream(device), P, int(degree), M, int(W), int(H), _ptr(means3D), _ptr(sh), _ptr(scales),
+                float(scale_modifier), _ptr(rotations), _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix),
+                _ptr(campos), float(tan_fovx), float(tan_fovy), radii.data_ptr(), geomBuffer.data_ptr(),
+                scratch.data_ptr(), dL_dmeans2D.data_ptr(), dL_dcolors.data_ptr(), dL_dopacity.data_ptr(),
+                dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(), _ptr(dL_dsh), dL_dscales.data_ptr(),
+                dL_drotations.data_ptr()), "gs_backward_geometry")
+    return tuple(outs)
+
+
+def _ptr_array(ptrs):
+    arr = (ctypes.c_void_p * len(ptrs))(*[int(p) for p in ptrs])
+    return arr
+
+
+def dp_color_grad_push(P, radii, geomBuffer, scratch, dst_ptrs, slot_offset, multicast=False):
+    """Masked dL/dRGB of this rank's view -> float offset slot_offset of every buffer in dst_ptrs (raw device
+    pointers: this rank's own buffer and its peers', or one multicast pointer). gs_dp_color_grad_push."""
+    device = radii.device
+    arr = _ptr_array(dst_ptrs)
+    with torch.cuda.device(device):
+        _check(_lib.gs_dp_color_grad_push(_stream(device), int(P), radii.data_ptr(), geomBuffer.data_ptr(),
+                                          scratch.data_ptr(), ctypes.cast(arr, _c_void_p), len(dst_ptrs),
+                                          1 if multicast else 0, int(slot_offset)), "gs_dp_color_grad_push")
+
+
+def dp_sh_grad_combine(means3D, campos_views, color_grads, slot_stride, degree, M, out=None):
+    """dL_dsh[P, M, 3] summed over the V views whose masked colour gradients sit in color_grads[V, slot_stride]
+    (gs_dp_sh_grad_combine)."""
+    device = means3D.device
+    P = int(means3D.size(0))
+    V = int(campos_views.size(0))
+    means3D = _f32_cuda(means3D, "means3D", device)
+    campos_views = _f32_cuda(campos_views, "campos_views", device)
+    color_grads = _f32_cuda(color_grads, "color_grads", device)
+    if color_grads.numel() < V * slot_stride:
+        raise RuntimeError("color_grads is smaller than V * slot_stride floats")
+    if out is None:
+        out = torch.empty((P, M, 3), dtype=torch.float32, device=device)
+    elif tuple(out.shape) != (P, M, 3) or out.dtype != torch.float32 or not out.is_contiguous():
+        raise RuntimeError(f"out must be a contiguous float32 {(P, M, 3)} tensor")
+    if P:
+        with torch.cuda.device(device):
+            _check(_lib.gs_dp_sh_grad_combine(_stream(device), P, int(degree), int(M), V, means3D.data_ptr(),
+                                              campos_views.data_ptr(), color_grads.data_ptr(), int(slot_stride),
+                                              out.data_ptr()), "gs_dp_sh_grad_combine")
+    return out
+
+
+def dp_slab_all_reduce(device, slab_ptrs, n_floats, rank, world, multicast=False):
+    """In-place two-shot all-reduce of a symmetric slab over NVLink (gs_dp_slab_all_reduce); the caller brackets it
+    with cross-rank barriers."""
+    arr = _ptr_array(slab_ptrs)
+    with torch.cuda.device(device):
+        _check(_lib.gs_dp_slab_all_reduce(_stream(device), ctypes.cast(arr, _c_void_p), len(slab_ptrs),
+                                          1 if multicast else 0, int(n_floats), int(rank), int(world)),
+               "gs_dp_slab_all_reduce")
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

@@ -44,6 +44,10 @@ def parse():
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--skip-baselines", action="store_true", help="skip the cpu_baseline and ref_cuda legs")
+    ap.add_argument("--exchange", default="factored", choices=["factored", "allreduce"],
+                    help="N > 1: gradient exchange. factored = all-gather masked dL/dRGB + rebuild the SH gradient + all-reduce "
+                         "11 floats per Gaussian (dp.FactoredExchange); allreduce = NCCL all-reduce of the 59-float arena")
+    ap.add_argument("--transport", default="auto", choices=["auto", "symm", "nccl"])
     return ap.parse_args()
 
 
@@ -54,11 +58,11 @@ def build_scene(P, W, H):
     return scene, cams
 
 
-def workload_config(P, W, H, n_gpus):
+def workload_config(P, W, H, n_gpus, exchange=None):
     return {"workload": f"synthetic garden scene (gs_synth.scene_garden seed 0): P={P} Gaussians, SH degree 3, "
                         f"{W}x{H}, orbit cameras r=6 fovx=1.2; BASELINE.json config 3/4 shape at the headline size",
             "gaussians": P, "width": W, "height": H, "views_per_step": n_gpus,
-            "parallelism": f"view-sharded dp{n_gpus}, replicated Gaussians" + (", NCCL all-reduce of the 59*P-float gradient arena" if n_gpus > 1 else ""),
+            "parallelism": f"view-sharded dp{n_gpus}, replicated Gaussians" + (f", gradient exchange: {exchange}" if n_gpus > 1 else ""),
             "l2_policy": "inputs (708 MB of parameters, 0.9 GB of gradients, ~0.4 GB of instance keys/ids per step) exceed the 126 MB L2; no explicit flush"}
 
 
@@ -176,7 +180,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.005)
 
     def stop(self):
         self._stop_evt.set()
@@ -216,10 +220,24 @@ def run_b200_arm(args):
     gen = torch.Generator(device="cpu").manual_seed(5)
     dL = (torch.randn((3, H, W), generator=gen) / (3 * H * W)).to(dev)
     e = torch.empty(0)
-    arena = dp.GradientArena(P, 16, dev)
+    factored = n_gpus > 1 and args.exchange == "factored"
+    arena = None if factored else dp.GradientArena(P, 16, dev)
+    exchange = dp.FactoredExchange(P, 16, dev, transport=args.transport) if factored else None
+    if factored:
+        exchange_desc = (f"factored ({exchange.transport}" + (", NVSwitch multicast" if exchange._multicast else "") +
+                         "): all-gather of the masked dL/dRGB (12 B/Gaussian/view) fused into its producer kernel, summed SH "
+                         "gradient rebuilt per rank, two-shot all-reduce of the other 11 floats/Gaussian")
+    else:
+        exchange_desc = "NCCL all-reduce of the 59*P-float gradient arena"
 
     def cam_for(step):
         return cams[(step * n_gpus + rank) % len(cams)]
+
+    def campos_for(step):
+        """Camera positions of the step's views in rank order (every rank knows the step's view list)."""
+        return torch.stack([cams[(step * n_gpus + r) % len(cams)]["campos"] for r in range(n_gpus)])
+
+    campos_tables = [campos_for(i) for i in range(len(cams))] if factored else None
 
     state = {}
 
@@ -228,12 +246,17 @@ def run_b200_arm(args):
         R, color, radii, geom, binning, img, is_used = C.rasterize_gaussians(
             bg, s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
             c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3, c["campos"], False, False)
-        C.rasterize_gaussians_backward(
-            bg, s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
-            c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], geom, R, binning, img, False,
-            out_buffers=arena.backward_buffers())
-        if n_gpus > 1:
-            arena.all_reduce()
+        if factored:
+            exchange.backward(C, bg, s["means3D"], radii, s["scales"], s["rotations"], 1.0, c["viewmatrix"], c["projmatrix"],
+                              c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], campos_tables[step % len(cams)],
+                              geom, R, binning, img)
+        else:
+            C.rasterize_gaussians_backward(
+                bg, s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+                c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], geom, R, binning, img, False,
+                out_buffers=arena.backward_buffers())
+            if n_gpus > 1:
+                arena.all_reduce()
         state.update(R=R, radii=radii, img=img, geom=geom, binning=binning)
 
     def barrier():
@@ -314,9 +337,16 @@ def run_b200_arm(args):
         "tile_sort": visible * 20 + R * 12 + R * 24 + R * 8 + tiles_n * 8,     # duplicateWithKeys + SortPairs (minimum) + identifyTileRanges
         "render_fwd": R * 28 + W * H * 20,
         "render_bwd": R * 40 + W * H * 20 + visible * 36,
-        "preprocess_bwd": visible * 531 + (P - visible) * 304,                 # cov2D + preprocess backward; zero gradients of culled ones
+        # cov2D + preprocess backward; zero gradients of culled ones. Factored exchange: the 192 B SH gradient row is not
+        # written here (dp_sh_grad_combine writes the cross-view sum)
+        "preprocess_bwd": visible * (531 - (192 if factored else 0)) + (P - visible) * (304 - (192 if factored else 0)),
         "bwd_zero": P * 36,
     }
+    if factored:
+        # NVLink / HBM bytes of the exchange kernels per rank and step
+        alg_bytes["dp_color_grad_push"] = P * (21 + 12) + (n_gpus - 1) * P * 12   # read acc+clamp+radii, write own slot, receive the others
+        alg_bytes["dp_slab_all_reduce"] = 2 * P * 44                               # slab read + written once per rank (two-shot)
+        alg_bytes["dp_sh_grad_combine"] = P * (12 + 12 * n_gpus + 192)              # means + V colour triples in, 48 floats out
     stage_report = {}
     for name, b in alg_bytes.items():
         ms = stage_ms(name)
@@ -363,6 +393,17 @@ def run_b200_arm(args):
     campos_dev = torch.empty((3,), dtype=torch.float32, device=dev)
     h2d = gt_dev[0].numel() * 4 + (16 + 16 + 3) * 4
     losses = []
+    vp_raster = None
+    if factored:
+        # public multi-GPU API: a rasterizer whose backward returns gradients already summed over the ranks; it reuses the
+        # exchange (symmetric buffers) of the device-timed loop
+        vp_raster = dp.ViewParallelRasterizer.__new__(dp.ViewParallelRasterizer)
+        torch.nn.Module.__init__(vp_raster)
+        vp_raster.exchange = exchange
+        campos_views_host = [torch.stack([torch.as_tensor(cams_np[(i * n_gpus + r) % len(cams_np)]["campos"]) for r in range(n_gpus)]).pin_memory()
+                             for i in range(len(cams_np))]
+        campos_views_dev = torch.empty((n_gpus, 3), dtype=torch.float32, device=dev)
+        h2d += n_gpus * 3 * 4
 
     def prefetch_gt(step):
         slot = step % 2
@@ -386,14 +427,19 @@ def run_b200_arm(args):
         settings = GaussianRasterizationSettings(H, W, ch["tanfovx"], ch["tanfovy"], bg, 1.0, view_dev, proj_dev, 3,
                                                  campos_dev, False, False)
         means2D = torch.zeros_like(params["means3D"], requires_grad=True)
-        image, radii_, used_ = GaussianRasterizer(settings)(
-            means3D=params["means3D"], means2D=means2D, shs=params["shs"], opacities=params["opacities"],
-            scales=params["scales"], rotations=params["rotations"])
+        if vp_raster is not None:
+            campos_views_dev.copy_(campos_views_host[step % len(campos_views_host)], non_blocking=True)
+            image, radii_, used_ = vp_raster(settings, campos_views_dev, params["means3D"], means2D, params["opacities"],
+                                             params["shs"], params["scales"], params["rotations"])
+        else:
+            image, radii_, used_ = GaussianRasterizer(settings)(
+                means3D=params["means3D"], means2D=means2D, shs=params["shs"], opacities=params["opacities"],
+                scales=params["scales"], rotations=params["rotations"])
         torch.cuda.current_stream().wait_event(gt_ready[slot])
         loss = (image - gt_dev[slot]).abs().mean()
         loss.backward()
         gt_free[slot].record()
-        if n_gpus > 1:
+        if n_gpus > 1 and vp_raster is None:
             for p_ in params.values():
                 dist.all_reduce(p_.grad)
         losses.append(float(loss.item()))  # the step's D2H result read
@@ -417,7 +463,9 @@ def run_b200_arm(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
     e2e = {"value": n_gpus * 1000.0 * K / e2e_ms, "unit": "views/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-           "ms_per_step": e2e_ms / K, "api": "GaussianRasterizer.forward + L1 loss + loss.backward(); pinned gt image (copy stream, one step ahead) and camera in, loss out"}
+           "ms_per_step": e2e_ms / K, "api": ("dp.ViewParallelRasterizer" if factored else "GaussianRasterizer") + ".forward + L1 loss + loss.backward()" +
+                  ("" if n_gpus == 1 else " with the cross-rank gradient sum inside the backward" if factored else " + all_reduce of the 5 parameter gradients") +
+                  "; pinned gt image (copy stream, one step ahead) and camera in, loss out"}
 
     if rank != 0:
         if n_gpus > 1:
@@ -426,7 +474,7 @@ def run_b200_arm(args):
 
     line = {"metric": METRIC, "value": value, "unit": "views/s", "n_gpus": n_gpus, "steps": K, "warmup": Wm,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": workload_config(P, W, H, n_gpus), "clocks": clocks, "e2e": e2e,
+            "data": "synthetic", "config": workload_config(P, W, H, n_gpus, exchange_desc), "clocks": clocks, "e2e": e2e,
             "gpu_launches": launches, "roofline": roofline, "stages": stage_report,
             "step_ms": {"min": round(per_step[0], 4), "p50": round(per_step[len(per_step) // 2], 4), "max": round(per_step[-1], 4)},
             "scene_stats": {"num_rendered": R, "visible": visible, "instances_per_visible": round(R / max(visible, 1), 2),

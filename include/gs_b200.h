@@ -98,6 +98,47 @@ int gs_backward(void* stream, int P, int D, int M, unsigned int R, int W, int H,
                 float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
                 float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations);
 
+/* The two halves of gs_backward, for callers that overlap an inter-GPU exchange with the per-Gaussian half
+ * (Rasterizer::backward runs the same two groups back to back: BACKWARD::render, then BACKWARD::preprocess,
+ * rasterizer_impl.cu:391-435). gs_backward(...) == gs_backward_render(...) then gs_backward_geometry(...) on the
+ * same scratch. In gs_backward_geometry dL_dsh may be NULL while shs is not: the SH gradient rows are then not
+ * written (the caller rebuilds them with gs_dp_sh_grad_combine). */
+int gs_backward_render(void* stream, int P, unsigned int R, int W, int H, const float* background,
+                       const void* geom_ws, const void* binning_ws, const void* image_ws,
+                       const float* dL_dpix, void* scratch);
+int gs_backward_geometry(void* stream, int P, int D, int M, int W, int H,
+                         const float* means3D, const float* shs, const float* scales, float scale_modifier,
+                         const float* rotations, const float* cov3D_precomp,
+                         const float* viewmatrix, const float* projmatrix, const float* campos,
+                         float tan_fovx, float tan_fovy, const int* radii,
+                         const void* geom_ws, const void* scratch,
+                         float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+                         float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations);
+
+/* ---- view-sharded data parallelism (additive; the reference is single-GPU). One process per GPU,
+ *      Gaussians replicated, one camera view per rank. The SH gradient of one view is rank one,
+ *      dL_dsh[k][c] = basis_k(dir) * dL_dRGB[c] (cuda_rasterizer/backward.cu:20-139), so instead of all-reducing
+ *      3M floats per Gaussian the ranks all-gather the clamp-masked dL_dRGB (3 floats) and rebuild the sum. ----
+ *
+ * gs_dp_color_grad_push: after gs_backward_render, write this rank's masked dL_dRGB [P][3] at float offset
+ *   slot_offset (a multiple of 4) of every buffer in dst_ptrs[n_dst] (peer-mapped device pointers, one per rank,
+ *   16-byte aligned), or, with multicast != 0, through the single NVSwitch multicast pointer dst_ptrs[0]
+ *   (multimem.st). The kernel does not wait for anything; order it against the consumers with a barrier.
+ * gs_dp_sh_grad_combine: dL_dsh[P][M][3] = sum over views v (in order) of basis(dir(means3D, campos_views[v]))
+ *   (x) color_grads[v * slot_stride + 3 i ...]; products rounded separately, so the result equals adding the
+ *   per-view dL_dsh tensors in view order, on every rank bit for bit.
+ * gs_dp_slab_all_reduce: in-place sum of a float slab that every rank holds at the same symmetric address.
+ *   slab_ptrs[world] are the peer-mapped pointers in rank order (or one multicast pointer with multicast != 0);
+ *   this rank reduces slice `rank` of `world` and stores it to every rank. n_floats must be a multiple of 4.
+ *   The caller brackets the call with cross-rank barriers (all slabs written before; all slices landed after). */
+int gs_dp_color_grad_push(void* stream, int P, const int* radii, const void* geom_ws, const void* scratch,
+                          float* const* dst_ptrs, int n_dst, int multicast, size_t slot_offset);
+int gs_dp_sh_grad_combine(void* stream, int P, int D, int M, int V, const float* means3D,
+                          const float* campos_views, const float* color_grads, size_t slot_stride,
+                          float* dL_dsh);
+int gs_dp_slab_all_reduce(void* stream, float* const* slab_ptrs, int n_ptrs, int multicast, size_t n_floats,
+                          int rank, int world);
+
 /* present[i] = (view * means3D[i]).z > 0.2 ; one byte per Gaussian (bool). */
 int gs_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix,
                     const float* projmatrix, unsigned char* present);

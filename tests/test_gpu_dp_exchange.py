@@ -1,0 +1,166 @@
+"""GPU tests of the view-sharded gradient exchange (csrc/dp_exchange.cu, diff_gaussian_rasterization/dp.py) on ONE
+device: the views of a step are rendered one after the other and the factored exchange (masked dL/dRGB per view +
+rebuilt SH gradient + summed 11-float slab) is compared with the plain sum of the per-view gradients of the fused
+backward — which the other GPU tests compare with the reference CUDA rasterizer. The 2-GPU transports (NVLink
+symmetric memory and NCCL) are checked by tools/dp_check.py under torchrun on the GPU box.
+"""
+import pytest
+import torch
+
+import helpers
+import gs_synth
+
+pytestmark = pytest.mark.gpu
+
+NAMES = ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")
+
+
+def native():
+    from diff_gaussian_rasterization import _native
+    return _native
+
+
+def _views(kind, P, W, H, V, degree, rad, fovx, seed=0):
+    dev = torch.device("cuda:0")
+    scene = gs_synth.scene_cube(P, seed) if kind == "cube" else gs_synth.scene_garden(P, seed)
+    if degree < 3:
+        scene["shs"] = scene["shs"][:, : (degree + 1) ** 2].copy()
+    cams = gs_synth.orbit_cameras(max(V, 4), rad, W, H, fovx, 20.0)[:V]
+    s = gs_synth.to_torch(scene, dev)
+    cs = []
+    for cam in cams:
+        c = gs_synth.to_torch(cam, dev)
+        c["bg"] = torch.tensor((0.1, 0.0, 0.3), dtype=torch.float32, device=dev)
+        cs.append(c)
+    g = torch.Generator(device="cpu").manual_seed(7)
+    dLs = [torch.randn((3, H, W), generator=g).to(dev) for _ in range(V)]
+    return s, cs, dLs
+
+
+def _forward(C, s, c, degree):
+    return C.rasterize_gaussians(*helpers.native_forward_args(s, c, degree))
+
+
+def _fused_backward(C, s, c, degree, dL, fwd):
+    R, color, radii, geom, binning, img, is_used = fwd
+    e = torch.empty(0)
+    return dict(zip(NAMES, C.rasterize_gaussians_backward(
+        c["bg"], s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+        c["tanfovx"], c["tanfovy"], dL, s["shs"], degree, c["campos"], geom, R, binning, img, False)))
+
+
+@pytest.mark.parametrize("kind,P,W,H,rad,fovx", [("cube", 20000, 250, 130, 4.03, 0.6911),
+                                                  ("garden", 100003, 640, 360, 6.0, 1.2)])
+def test_split_backward_equals_fused_backward(kind, P, W, H, rad, fovx):
+    """gs_backward_render + gs_backward_geometry write the same bits as gs_backward."""
+    C = native()
+    s, cs, dLs = _views(kind, P, W, H, 1, 3, rad, fovx)
+    c, dL = cs[0], dLs[0]
+    fwd = _forward(C, s, c, 3)
+    R, _, radii, geom, binning, img, _ = fwd
+    fused = _fused_backward(C, s, c, 3, dL, fwd)
+    scratch = C.backward_render(c["bg"], P, R, dL, geom, binning, img)
+    e = torch.empty(0)
+    split = dict(zip(NAMES, C.backward_geometry(s["means3D"], radii, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"],
+                                                c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3,
+                                                c["campos"], geom, scratch)))
+    torch.cuda.synchronize()
+    for n in NAMES:
+        # float atomics in the tile backward reorder sums from run to run: compare to the run-to-run noise floor
+        assert helpers.rel_l2(split[n], fused[n]) < 2e-5, n
+    # without the SH rows: every other output unchanged, SH slot None
+    nosh = dict(zip(NAMES, C.backward_geometry(s["means3D"], radii, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"],
+                                               c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3,
+                                               c["campos"], geom, scratch, write_sh=False)))
+    torch.cuda.synchronize()
+    assert nosh["sh"] is None
+    for n in NAMES:
+        if n != "sh":
+            assert helpers.bits_equal_count(nosh[n], split[n]) == 0, n
+
+
+@pytest.mark.parametrize("kind,P,W,H,V,degree,rad,fovx", [
+    ("cube", 20001, 250, 130, 3, 3, 4.03, 0.6911),      # P not a multiple of 4: scalar tail of the push kernel
+    ("cube", 5000, 96, 64, 2, 1, 4.03, 0.6911),         # lower degree, M = 4 rows
+    ("cube", 5000, 96, 64, 2, 0, 4.03, 0.6911),
+    ("garden", 200000, 800, 450, 4, 3, 6.0, 1.2),
+])
+def test_factored_sh_gradient_equals_sum_of_per_view_gradients(kind, P, W, H, V, degree, rad, fovx):
+    """Masked dL/dRGB per view + gs_dp_sh_grad_combine == sum over views (in order) of the per-view dL_dsh that the
+    same scratch gives through the ordinary backward, bit for bit."""
+    C = native()
+    dev = torch.device("cuda:0")
+    s, cs, dLs = _views(kind, P, W, H, V, degree, rad, fovx)
+    M = s["shs"].shape[1]
+    slot_stride = (3 * P + 63) // 64 * 64
+    gathered = torch.full((V, slot_stride), float("nan"), device=dev)
+    e = torch.empty(0)
+    total = torch.zeros((P, M, 3), device=dev)
+    campos = torch.stack([c["campos"] for c in cs])
+    for v, (c, dL) in enumerate(zip(cs, dLs)):
+        R, _, radii, geom, binning, img, _ = _forward(C, s, c, degree)
+        scratch = C.backward_render(c["bg"], P, R, dL, geom, binning, img)
+        C.dp_color_grad_push(P, radii, geom, scratch, [gathered.data_ptr()], v * slot_stride, False)
+        outs = dict(zip(NAMES, C.backward_geometry(s["means3D"], radii, s["scales"], s["rotations"], 1.0, e,
+                                                   c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W,
+                                                   s["shs"], degree, c["campos"], geom, scratch)))
+        total = total + outs["sh"]
+        # the pushed colour gradient is the backward's dL_dcolors with the clamp mask applied
+        g = gathered[v, : 3 * P].view(P, 3)
+        assert torch.isfinite(g).all()
+        changed = g != outs["colors"]
+        assert bool(((g == 0) | ~changed).all())
+    sh = C.dp_sh_grad_combine(s["means3D"], campos, gathered, slot_stride, degree, M)
+    torch.cuda.synchronize()
+    assert sh.shape == total.shape
+    assert float(total.abs().max()) > 0
+    assert helpers.bits_equal_count(sh + 0.0, total + 0.0) == 0, helpers.rel_l2(sh, total)
+
+
+def test_factored_exchange_world_1_equals_fused_backward():
+    """dp.FactoredExchange without a process group: same gradients as the fused backward."""
+    from diff_gaussian_rasterization import dp
+    C = native()
+    P, W, H = 30000, 320, 200
+    s, cs, dLs = _views("cube", P, W, H, 1, 3, 4.03, 0.6911)
+    c, dL = cs[0], dLs[0]
+    fwd = _forward(C, s, c, 3)
+    R, _, radii, geom, binning, img, _ = fwd
+    fused = _fused_backward(C, s, c, 3, dL, fwd)
+    ex = dp.FactoredExchange(P, 16, torch.device("cuda:0"))
+    assert ex.world == 1
+    grads = ex.backward(C, c["bg"], s["means3D"], radii, s["scales"], s["rotations"], 1.0, c["viewmatrix"],
+                        c["projmatrix"], c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"],
+                        c["campos"].view(1, 3), geom, R, binning, img)
+    torch.cuda.synchronize()
+    for n in ("means3D", "sh", "opacity", "scales", "rotations"):
+        assert helpers.rel_l2(grads[n], fused[n]) < 2e-5, n
+
+
+def test_dp_entry_points_reject_bad_arguments():
+    C = native()
+    dev = torch.device("cuda:0")
+    x = torch.zeros(64, device=dev)
+    with pytest.raises(RuntimeError):
+        C.dp_slab_all_reduce(dev, [x.data_ptr()], 6, 0, 2)           # n_ptrs != world
+    with pytest.raises(RuntimeError):
+        C.dp_slab_all_reduce(dev, [x.data_ptr(), x.data_ptr()], 6, 0, 2)   # not a multiple of 4 floats
+    with pytest.raises(RuntimeError):
+        C.dp_sh_grad_combine(torch.zeros((8, 3), device=dev), torch.zeros((1, 3), device=dev), x, 8, 3, 16)  # stride < 3P
+
+
+def test_slab_all_reduce_single_device_two_buffers():
+    """The peer-pointer all-reduce kernel with both 'ranks' on one device: each call reduces one slice of two buffers."""
+    C = native()
+    dev = torch.device("cuda:0")
+    n = 4 * 1031
+    g = torch.Generator(device="cpu").manual_seed(1)
+    a = torch.randn(n, generator=g).to(dev)
+    b = torch.randn(n, generator=g).to(dev)
+    want = a + b
+    ptrs = [a.data_ptr(), b.data_ptr()]
+    C.dp_slab_all_reduce(dev, ptrs, n, 0, 2)
+    C.dp_slab_all_reduce(dev, ptrs, n, 1, 2)
+    torch.cuda.synchronize()
+    assert helpers.bits_equal_count(a, want) == 0
+    assert helpers.bits_equal_count(b, want) == 0

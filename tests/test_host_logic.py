@@ -116,6 +116,78 @@ def test_arena_all_reduce_world_size_2_gloo(tmp_path):
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
 
 
+def test_factored_exchange_world_size_2_gloo(tmp_path):
+    """dp.FactoredExchange over gloo (transport "nccl" = plain torch.distributed collectives) with the CUDA kernels
+    replaced by numpy stand-ins: after the exchange both ranks hold the summed 11-float slab and the SH gradient
+    sum_v basis(dir_v) (x) g_v rebuilt from the gathered colour gradients, bit-identical on both ranks."""
+    script = tmp_path / "worker.py"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script.write_text(textwrap.dedent(f"""
+        import ctypes, os, sys
+        import numpy as np
+        sys.path.insert(0, {os.path.join(root, '3dgs-mcmc_b200')!r})
+        import torch, torch.distributed as dist
+        from diff_gaussian_rasterization import dp
+        dist.init_process_group("gloo")
+        r, world = dist.get_rank(), dist.get_world_size()
+        P, M = 37, 4                                   # degree 1
+        rng = np.random.default_rng(5)
+        means = rng.normal(size=(P, 3)).astype(np.float32)
+        campos = np.array([[4.0, 0.5, 0.0], [-3.0, 1.0, 2.0]], np.float32)
+        g_all = rng.normal(size=(world, P, 3)).astype(np.float32)
+        g_all[1, ::3] = 0.0                            # Gaussians culled in view 1
+
+        def basis(d):                                  # degree-1 real SH basis of unit vectors d[P,3]
+            c0, c1 = 0.28209479177387814, 0.4886025119029199
+            return np.stack([np.full(len(d), c0, np.float32), -c1 * d[:, 1], c1 * d[:, 2], -c1 * d[:, 0]], 1).astype(np.float32)
+
+        class FakeNative:                              # stands in for _native on a box without a GPU (test only)
+            def dp_color_grad_push(self, P_, radii, geom, scratch, dst_ptrs, slot_offset, multicast):
+                src = np.ascontiguousarray(g_all[r].reshape(-1))
+                for p in dst_ptrs:
+                    ctypes.memmove(p + 4 * slot_offset, src.ctypes.data, src.nbytes)
+            def dp_sh_grad_combine(self, means3D, campos_views, gathered, slot_stride, degree, M_, out=None):
+                acc = np.zeros((P, M_, 3), np.float32)
+                for v in range(campos_views.shape[0]):
+                    g = gathered.view(-1).numpy()[v * slot_stride: v * slot_stride + 3 * P].reshape(P, 3)
+                    d = means3D.numpy() - campos_views[v].numpy()
+                    d = d / np.sqrt((d * d).sum(1, keepdims=True))
+                    acc += basis(d)[:, :, None] * g[:, None, :]
+                out.copy_(torch.from_numpy(acc))
+                return out
+
+        ex = dp.FactoredExchange(P, M, "cpu", transport="auto")
+        assert ex.transport == "nccl" and ex.world == 2 and ex.slot_stride % 64 == 0 and ex.slot_stride >= 3 * P
+        assert set(ex.out_buffers()) == {{"means2D", "colors", "cov3D", "means3D", "opacity", "scales", "rotations"}}
+        for i, name in enumerate(("means3D", "opacity", "scales", "rotations")):
+            ex.grads[name].fill_(float((r + 1) * (i + 1)))       # what the per-Gaussian backward would have written
+        native = FakeNative()
+        pending = ex.push_color_grads(native, None, None, None)
+        grads = ex.finish(native, torch.from_numpy(means), torch.from_numpy(campos), 1, pending)
+        for i, name in enumerate(("means3D", "opacity", "scales", "rotations")):
+            assert torch.all(grads[name] == 3.0 * (i + 1)), name
+        want = np.zeros((P, M, 3), np.float32)
+        for v in range(world):
+            d = means - campos[v]
+            d = d / np.sqrt((d * d).sum(1, keepdims=True))
+            want += basis(d)[:, :, None] * g_all[v][:, None, :]
+        assert np.array_equal(grads["sh"].numpy(), want)
+        both = [torch.zeros_like(grads["sh"]) for _ in range(world)]
+        dist.all_gather(both, grads["sh"])
+        assert torch.equal(both[0], both[1])
+        rx, slab = ex.bytes_per_step()
+        assert rx == (world - 1) * 12 * P and slab == 44 * P
+        dist.destroy_process_group()
+        open(os.path.join({str(tmp_path)!r}, f"ok{{r}}"), "w").write("ok")
+    """))
+    port = _free_port()
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
+                         capture_output=True, text=True, timeout=240)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+
+
 def test_camera_conventions():
     cam = gs_synth.look_at_camera((0.0, 0.0, -4.0), (0.0, 0.0, 0.0), 64, 48, 0.8)
     V = cam["viewmatrix"]            # transposed storage: element [4*i+j] of the transposed matrix
