@@ -101,18 +101,21 @@ class FactoredExchange:
         self.transport = self._pick_transport(transport)
         self._hdl = None
         if self.transport == "symm":
-            import torch.distributed._symmetric_memory as symm_mem
-            self.flat = symm_mem.empty(total, dtype=torch.float32, device=self.device)
-            self._hdl = symm_mem.rendezvous(self.flat, (group or dist.group.WORLD).group_name)
-            self.flat.zero_()
-            self._multicast = bool(self._hdl.multicast_ptr) and (multicast if multicast is not None else self.world > 2)
-            self._ev_push = torch.cuda.Event()
-            self._side = torch.cuda.Stream(device=self.device)
-            self._ev_fork, self._ev_join = torch.cuda.Event(), torch.cuda.Event()
-            self._slab_ptrs = [int(self._hdl.multicast_ptr)] if self._multicast else [int(p) for p in self._hdl.buffer_ptrs]
-            gather_off = 4 * slab_floats
-            self._gather_ptrs = [p + gather_off for p in self._slab_ptrs]
-        else:
+            try:
+                self._setup_symmetric(total, slab_floats, group, multicast)
+            except Exception as ex:  # no peer access / no symmetric-memory support on this box
+                if transport == "symm":
+                    raise
+                import warnings
+                warnings.warn(f"FactoredExchange: symmetric memory unavailable ({ex!r}); using torch.distributed collectives")
+                self.transport = "nccl"
+            if transport == "auto":
+                # every rank must take the same path: agree on the weakest
+                ok = torch.tensor([1 if self.transport == "symm" else 0], dtype=torch.int32, device=self.device)
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+                if int(ok.item()) == 0:
+                    self.transport, self._hdl = "nccl", None
+        if self.transport != "symm":
             self.flat = torch.zeros(total, dtype=torch.float32, device=self.device)
             self._multicast = False
             self._send = torch.zeros(self.slot_stride, dtype=torch.float32, device=self.device)
@@ -127,6 +130,19 @@ class FactoredExchange:
         self.local = {"means2D": torch.empty((self.P, 3), dtype=torch.float32, device=self.device),
                       "colors": torch.empty((self.P, 3), dtype=torch.float32, device=self.device),
                       "cov3D": torch.empty((self.P, 6), dtype=torch.float32, device=self.device)}
+
+    def _setup_symmetric(self, total, slab_floats, group, multicast):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.flat = symm_mem.empty(total, dtype=torch.float32, device=self.device)
+        self._hdl = symm_mem.rendezvous(self.flat, (group or dist.group.WORLD).group_name)
+        self.flat.zero_()
+        self._multicast = bool(self._hdl.multicast_ptr) and (multicast if multicast is not None else self.world > 2)
+        self._ev_push = torch.cuda.Event()
+        self._side = torch.cuda.Stream(device=self.device)
+        self._ev_fork, self._ev_join = torch.cuda.Event(), torch.cuda.Event()
+        self._slab_ptrs = [int(self._hdl.multicast_ptr)] if self._multicast else [int(p) for p in self._hdl.buffer_ptrs]
+        gather_off = 4 * slab_floats
+        self._gather_ptrs = [p + gather_off for p in self._slab_ptrs]
 
     def _pick_transport(self, transport):
         if transport not in ("auto", "symm", "nccl"):
