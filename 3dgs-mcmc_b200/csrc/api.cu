@@ -2,6 +2,7 @@
 // and stage orchestration. No torch types, no global state; everything runs on the caller's stream.
 #include "../../include/gs_b200.h"
 
+#include <cmath>
 #include <cstdio>
 #include <vector>
 
@@ -37,12 +38,12 @@ struct BwdScratch {
 // ---- optional per-stage timing (CUDA events on the caller's stream) and a kernel-launch counter ----
 enum Stage {
     ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_PACK, ST_RENDER_FWD, ST_BWD_ZERO, ST_RENDER_BWD,
-    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_DP_PUSH, ST_DP_COMBINE, ST_DP_ALL_REDUCE, ST_COUNT
+    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_DP_PUSH, ST_DP_COMBINE, ST_DP_ALL_REDUCE, ST_ADAM, ST_COUNT
 };
 const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "scan", "emit_instances", "tile_sort", "tile_ranges",
                                            "render_fwd", "bwd_zero", "render_bwd", "preprocess_bwd",
                                            "compute_relocation", "add_noise", "dp_color_grad_push", "dp_sh_grad_combine",
-                                           "dp_slab_all_reduce"};
+                                           "dp_slab_all_reduce", "adam_step"};
 struct Profiler {
     bool on = false;
     std::vector<cudaEvent_t> ev;
@@ -364,6 +365,38 @@ int gs_dp_slab_all_reduce(void* stream_, float* const* slab_ptrs, int n_ptrs, in
     prof_mark(stream, -1);
     rc = launch_slab_all_reduce(peers, multicast != 0, n_floats, rank, world, sms, stream);
     prof_mark(stream, ST_DP_ALL_REDUCE);
+    count_launches(1);
+    return rc;
+}
+
+int gs_adam_step(void* stream_, int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
+                 float* const* exp_avg_sq, const unsigned long long* numel, const double* lr, const int* step, double beta1,
+                 double beta2, double eps) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (n_tensors < 0 || n_tensors > 8) return GS_ERR_ARG;
+    if (n_tensors == 0) return GS_OK;
+    if (!params || !grads || !exp_avg || !exp_avg_sq || !numel || !lr || !step) return GS_ERR_ARG;
+    AdamLaunch L;
+    L.n_tensors = 0;
+    // torch computes these scalars in double and hands them to float kernels (torch/optim/adam.py, non-capturable path)
+    L.w1 = (float)(1.0 - beta1);
+    L.beta2 = (float)beta2;
+    L.w2 = (float)(1.0 - beta2);
+    L.eps = (float)eps;
+    for (int i = 0; i < n_tensors; ++i) {
+        if (numel[i] == 0) continue;
+        if (!params[i] || !grads[i] || !exp_avg[i] || !exp_avg_sq[i] || step[i] < 1) return GS_ERR_ARG;
+        AdamTensor& T = L.t[L.n_tensors++];
+        T.param = params[i]; T.grad = grads[i]; T.m = exp_avg[i]; T.v = exp_avg_sq[i]; T.n = numel[i];
+        const double bc1 = 1.0 - pow(beta1, (double)step[i]);
+        const double bc2 = 1.0 - pow(beta2, (double)step[i]);
+        T.neg_step_size = (float)(-(lr[i] / bc1));
+        T.bc2_sqrt = (float)sqrt(bc2);
+        T.vec_ok = 0;
+    }
+    prof_mark(stream, -1);
+    const int rc = launch_adam_step(L, stream);
+    prof_mark(stream, ST_ADAM);
     count_launches(1);
     return rc;
 }

@@ -102,6 +102,24 @@ struct DpPeers {
     int n;
 };
 
+// One multi-tensor Adam launch (optim.cu).
+struct AdamTensor {
+    float* param;
+    const float* grad;
+    float* m;
+    float* v;
+    unsigned long long n;
+    float neg_step_size;   // -(lr / (1 - beta1^step))
+    float bc2_sqrt;        // sqrt(1 - beta2^step)
+    int vec_ok;            // all four pointers 16-byte aligned (set by the launcher)
+};
+struct AdamLaunch {
+    AdamTensor t[8];
+    unsigned long long first_chunk[8];
+    int n_tensors;
+    float w1, beta2, w2, eps;   // 1 - beta1, beta2, 1 - beta2, eps
+};
+
 int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
 int launch_inclusive_scan(const uint2* rect, const uint64_t* order, int n, uint32_t* out, uint4* emit, uint32_t* block_sums,
@@ -126,6 +144,7 @@ int launch_add_noise(int P, float* xyz, const float* scaling_raw, const float* r
                      const float* noise, float lr_scale, unsigned long long seed, unsigned long long offset,
                      cudaStream_t stream);
 
+int launch_adam_step(AdamLaunch& L, cudaStream_t stream);
 int launch_color_grad_push(int P, const int* radii, const uint8_t* clamped, const float4* acc, const DpPeers& dst,
                            size_t slot_offset, bool multicast, cudaStream_t stream);
 int launch_sh_grad_combine(int P, int D, int M, int V, const float* means3D, const float* campos, const float* gathered,

@@ -48,6 +48,7 @@ SIGNATURES = {
     "gs_dp_sh_grad_combine": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p,
                                        _c_size_t, _c_void_p]),
     "gs_dp_slab_all_reduce": (_c_int, [_c_void_p, _c_void_p, _c_int, _c_int, _c_size_t, _c_int, _c_int]),
+    "gs_adam_step": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 7 + [ctypes.c_double] * 3),
     "gs_mark_visible": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4),
     "gs_compute_relocation": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 2),
     "gs_add_noise": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 5 + [_c_float, _c_ull, _c_ull]),
@@ -422,6 +423,35 @@ def add_noise(xyz, scaling_raw, rotation_raw, opacity_raw, lr_scale, noise=None,
                                  _ptr(opacity_raw), _ptr(noise), float(lr_scale), int(seed), int(offset)),
                "gs_add_noise")
     return xyz
+
+
+def adam_step(params, grads, exp_avgs, exp_avg_sqs, lrs, steps, beta1, beta2, eps):
+    """One multi-tensor Adam launch (gs_adam_step) over up to 8 contiguous float32 CUDA tensors; updates params,
+    exp_avgs and exp_avg_sqs in place. lrs / steps: per-tensor learning rate and (already incremented) step count."""
+    n = len(params)
+    if n == 0:
+        return
+    if n > 8:
+        for i in range(0, n, 8):
+            adam_step(params[i:i + 8], grads[i:i + 8], exp_avgs[i:i + 8], exp_avg_sqs[i:i + 8], lrs[i:i + 8],
+                      steps[i:i + 8], beta1, beta2, eps)
+        return
+    device = params[0].device
+    for group in (params, grads, exp_avgs, exp_avg_sqs):
+        for t in group:
+            if not t.is_cuda or t.device != device or t.dtype != torch.float32 or not t.is_contiguous():
+                raise RuntimeError("adam_step needs contiguous float32 CUDA tensors on one device (no CPU path exists)")
+    for p, g, m, v in zip(params, grads, exp_avgs, exp_avg_sqs):
+        if not (p.numel() == g.numel() == m.numel() == v.numel()):
+            raise RuntimeError("adam_step: param / grad / state sizes differ")
+    arr = lambda ts: ctypes.cast(_ptr_array([t.data_ptr() for t in ts]), _c_void_p)  # noqa: E731
+    numel = (ctypes.c_ulonglong * n)(*[t.numel() for t in params])
+    lr = (ctypes.c_double * n)(*[float(x) for x in lrs])
+    st = (ctypes.c_int * n)(*[int(x) for x in steps])
+    with torch.cuda.device(device):
+        _check(_lib.gs_adam_step(_stream(device), n, arr(params), arr(grads), arr(exp_avgs), arr(exp_avg_sqs),
+                                 ctypes.cast(numel, _c_void_p), ctypes.cast(lr, _c_void_p), ctypes.cast(st, _c_void_p),
+                                 float(beta1), float(beta2), float(eps)), "gs_adam_step")
 
 
 def debug_fetch(which, P, R, W, H, geom, binning, img, dtype):

@@ -482,6 +482,35 @@ def run_b200_arm(args):
                             "pairs_bwd": pairs_bwd, "pairs_fwd_lower_bound": pairs_fwd_lower,
                             "mpix_per_s": W * H / ms_per_step / 1e3}}
 
+    # ---- SURVEY.md 8 f1 ("next" rows), measured beside the hot path at N=1: the optimizer step over the same parameters ----
+    if n_gpus == 1:
+        try:
+            from diff_gaussian_rasterization.optim import FusedAdam
+
+            def time_opt(opt_cls, **kw):
+                ps = [torch.nn.Parameter(s[k].clone()) for k in ("means3D", "shs", "opacities", "scales", "rotations")]
+                opt = opt_cls([{"params": [p_], "lr": 1e-3} for p_ in ps], lr=0.0, eps=1e-15, **kw)
+                for p_ in ps:
+                    p_.grad = torch.randn_like(p_)
+                for _ in range(3):
+                    opt.step()
+                torch.cuda.synchronize()
+                ev0.record()
+                for _ in range(10):
+                    opt.step()
+                ev1.record()
+                torch.cuda.synchronize()
+                return ev0.elapsed_time(ev1) / 10
+            adam_ms = time_opt(FusedAdam)
+            torch_ms = time_opt(torch.optim.Adam)
+            adam_bytes = 28 * 59 * P
+            line["next_rows"] = {"adam_step": {
+                "ms": round(adam_ms, 4), "alg_GBps": round(adam_bytes / adam_ms / 1e6, 1), "hbm_frac": round(adam_bytes / adam_ms / 1e6 / hbm_peak, 4),
+                "torch_optim_adam_ms": round(torch_ms, 4),
+                "what": "one multi-tensor Adam launch over the 59 floats/Gaussian (28 B per float: grad, param, 2 moments in; param, 2 moments out) vs torch.optim.Adam (the reference's optimizer) on the same tensors"}}
+        except Exception as ex:
+            line["next_rows"] = {"adam_step": {"unavailable": repr(ex)[:200]}}
+
     # ---- baseline legs (rank 0, N=1 only): reference CUDA on the same box, CPU port on the host cores ----
     if n_gpus == 1 and not args.skip_baselines:
         try:

@@ -154,6 +154,16 @@ int gs_add_noise(void* stream, int P, float* xyz, const float* scaling_raw, cons
                  const float* opacity_raw, const float* noise, float lr_scale,
                  unsigned long long seed, unsigned long long offset);
 
+/* Multi-tensor Adam step (additive): one launch applies torch.optim.Adam's update (no weight decay,
+ * no amsgrad) to up to 8 parameter tensors - the reference's six parameter groups, scene/gaussian_model_static.py:191-200,
+ * stepped at train_static.py:129-130. Arrays are indexed by tensor: device pointers params / grads / exp_avg /
+ * exp_avg_sq, element counts, per-tensor learning rate and step count (>= 1, already incremented, as torch keeps one
+ * per parameter). Hyper-parameters are doubles, as torch keeps them: 1 - beta and the bias corrections are formed in
+ * double and rounded to FP32 once. */
+int gs_adam_step(void* stream, int n_tensors, float* const* params, const float* const* grads,
+                 float* const* exp_avg, float* const* exp_avg_sq, const unsigned long long* numel,
+                 const double* lr, const int* step, double beta1, double beta2, double eps);
+
 /* ---- measurement hooks (bench.py): per-stage timing with CUDA events recorded on the caller's stream between
  *      the stages of each call, and a counter of kernel launches made by this library. Process-global; not used
  *      by the compute path. gs_profile_enable(n) arms n event marks (0 disables); gs_profile_collect() waits for

@@ -216,3 +216,24 @@ def binoms_table(n_max=51):
         for k in range(n + 1):
             t[n, k] = comb(n, k)
     return t
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# SURVEY.md §8 f1 ("next" rows): the optimizer step either side of the rasterizer
+# ----------------------------------------------------------------------------------------------------------------------
+def adam_step(param, grad, exp_avg, exp_avg_sq, lr, step, beta1=0.9, beta2=0.999, eps=1e-15):
+    """One torch.optim.Adam update in numpy FP32 (the reference's optimizer: scene/gaussian_model_static.py:191-200,
+    eps=1e-15, betas (0.9, 0.999), no weight decay / amsgrad; stepped at train_static.py:129-130). Follows the op
+    sequence of torch's non-capturable path: lerp, mul+addcmul, sqrt / bias_correction2_sqrt + eps, addcdiv with
+    step_size = lr / bias_correction1, the scalars computed in double and rounded to FP32 where they meet tensors.
+    Returns (param, exp_avg, exp_avg_sq). Pinned against torch.optim.Adam by tests/test_oracle_golden.py."""
+    f = np.float32
+    p, g, m, v = (np.asarray(a, dtype=np.float32) for a in (param, grad, exp_avg, exp_avg_sq))
+    w1, w2 = f(1.0 - beta1), f(1.0 - beta2)
+    m = (m + w1 * (g - m)).astype(np.float32)
+    v = (v * f(beta2) + (w2 * g) * g).astype(np.float32)
+    bc1 = 1.0 - beta1 ** step
+    bc2_sqrt = (1.0 - beta2 ** step) ** 0.5
+    denom = (np.sqrt(v) / f(bc2_sqrt) + f(eps)).astype(np.float32)
+    p = (p + f(-(lr / bc1)) * (m / denom)).astype(np.float32)
+    return p, m, v
