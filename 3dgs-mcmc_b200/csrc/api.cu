@@ -38,12 +38,12 @@ struct BwdScratch {
 // ---- optional per-stage timing (CUDA events on the caller's stream) and a kernel-launch counter ----
 enum Stage {
     ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_PACK, ST_RENDER_FWD, ST_BWD_ZERO, ST_RENDER_BWD,
-    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_DP_PUSH, ST_DP_COMBINE, ST_DP_ALL_REDUCE, ST_ADAM, ST_COUNT
+    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_DP_PUSH, ST_DP_COMBINE, ST_DP_ALL_REDUCE, ST_ADAM, ST_LOSS_FWD, ST_LOSS_BWD, ST_COUNT
 };
 const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "scan", "emit_instances", "tile_sort", "tile_ranges",
                                            "render_fwd", "bwd_zero", "render_bwd", "preprocess_bwd",
                                            "compute_relocation", "add_noise", "dp_color_grad_push", "dp_sh_grad_combine",
-                                           "dp_slab_all_reduce", "adam_step"};
+                                           "dp_slab_all_reduce", "adam_step", "loss_fwd", "loss_bwd"};
 struct Profiler {
     bool on = false;
     std::vector<cudaEvent_t> ev;
@@ -397,6 +397,71 @@ int gs_adam_step(void* stream_, int n_tensors, float* const* params, const float
     prof_mark(stream, -1);
     const int rc = launch_adam_step(L, stream);
     prof_mark(stream, ST_ADAM);
+    count_launches(1);
+    return rc;
+}
+
+namespace {
+struct LossWS {
+    float *d_mu, *d_e11, *d_e12, *partial;
+    size_t bytes;
+    static LossWS carve(char* base, int C, int H, int W) {
+        Carver c(base);
+        LossWS w;
+        const size_t n = (size_t)C * H * W;
+        w.d_mu = c.take<float>(n);
+        w.d_e11 = c.take<float>(n);
+        w.d_e12 = c.take<float>(n);
+        w.partial = c.take<float>(2 * loss_partial_count(C, H, W));
+        w.bytes = align_up(c.off, kAlign);
+        return w;
+    }
+};
+int fill_loss_params(LossParams* p, int C, int H, int W, const float* image, const float* gt, const void* ws) {
+    if (C <= 0 || H <= 0 || W <= 0 || C > 65535 || !image || !gt || !ws) return GS_ERR_ARG;
+    LossWS w = LossWS::carve(aligned_base(ws), C, H, W);
+    p->C = C; p->H = H; p->W = W; p->img = image; p->gt = gt;
+    p->d_mu = w.d_mu; p->d_e11 = w.d_e11; p->d_e12 = w.d_e12; p->partial = w.partial; p->dL_dimg = nullptr;
+    // utils/loss_utils.py:27-29: torch.Tensor([exp(-(x - 5)^2 / (2 sigma^2))]) (python doubles -> FP32), divided by its FP32 sum
+    // (torch's sum of the 11 floats is the correctly rounded one: accumulate in double, round once)
+    float g[11];
+    double sum = 0.0;
+    for (int i = 0; i < 11; ++i) { g[i] = (float)exp(-(double)((i - 5) * (i - 5)) / (2.0 * 1.5 * 1.5)); sum += (double)g[i]; }
+    for (int i = 0; i < 11; ++i) p->win[i] = g[i] / (float)sum;
+    return GS_OK;
+}
+}  // namespace
+
+size_t gs_loss_workspace_bytes(int C, int H, int W) {
+    if (C <= 0 || H <= 0 || W <= 0) return kAlign;
+    return LossWS::carve(nullptr, C, H, W).bytes + kAlign;
+}
+
+int gs_photometric_loss_forward(void* stream_, int C, int H, int W, const float* image, const float* gt, void* ws,
+                                float* out_means) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    LossParams p;
+    int rc = fill_loss_params(&p, C, H, W, image, gt, ws);
+    if (rc) return rc;
+    if (!out_means) return GS_ERR_ARG;
+    prof_mark(stream, -1);
+    rc = launch_loss_forward(p, out_means, stream);
+    prof_mark(stream, ST_LOSS_FWD);
+    count_launches(2);
+    return rc;
+}
+
+int gs_photometric_loss_backward(void* stream_, int C, int H, int W, const float* image, const float* gt, const void* ws,
+                                 float c_l1, float c_ssim, const float* grad_scale, float* dL_dimage) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    LossParams p;
+    int rc = fill_loss_params(&p, C, H, W, image, gt, ws);
+    if (rc) return rc;
+    if (!dL_dimage) return GS_ERR_ARG;
+    p.dL_dimg = dL_dimage;
+    prof_mark(stream, -1);
+    rc = launch_loss_backward(p, c_l1, c_ssim, grad_scale, stream);
+    prof_mark(stream, ST_LOSS_BWD);
     count_launches(1);
     return rc;
 }

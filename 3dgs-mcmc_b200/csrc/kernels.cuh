@@ -102,6 +102,19 @@ struct DpPeers {
     int n;
 };
 
+// Fused L1 + SSIM loss (loss.cu). win = the normalised 11-tap Gaussian window (sigma 1.5) in FP32.
+struct LossParams {
+    int C, H, W;
+    const float* __restrict__ img;   // [C][H][W] render
+    const float* __restrict__ gt;    // [C][H][W] ground truth
+    float* __restrict__ d_mu;        // [C][H][W] dS/dmu   (forward out, backward in)
+    float* __restrict__ d_e11;       // [C][H][W] dS/de11
+    float* __restrict__ d_e12;       // [C][H][W] dS/de12
+    float* __restrict__ partial;     // [blocks][2] per-block sums of |x - y| and S
+    float* __restrict__ dL_dimg;     // [C][H][W] (backward out)
+    float win[11];
+};
+
 // One multi-tensor Adam launch (optim.cu).
 struct AdamTensor {
     float* param;
@@ -145,6 +158,9 @@ int launch_add_noise(int P, float* xyz, const float* scaling_raw, const float* r
                      cudaStream_t stream);
 
 int launch_adam_step(AdamLaunch& L, cudaStream_t stream);
+int launch_loss_forward(const LossParams& p, float* out_means, cudaStream_t stream);
+int launch_loss_backward(const LossParams& p, float c_l1, float c_ssim, const float* grad_scale, cudaStream_t stream);
+size_t loss_partial_count(int C, int H, int W);
 int launch_color_grad_push(int P, const int* radii, const uint8_t* clamped, const float4* acc, const DpPeers& dst,
                            size_t slot_offset, bool multicast, cudaStream_t stream);
 int launch_sh_grad_combine(int P, int D, int M, int V, const float* means3D, const float* campos, const float* gathered,

@@ -1,0 +1,215 @@
+// Fused photometric loss of the training step:
+//     loss = (1 - lambda) * mean |x - y|  +  lambda * (1 - mean ssim_map(x, y))
+// as train_static.py:94-97 composes it from utils/loss_utils.py:21-22 (l1_loss) and :40-67 (ssim / _ssim: 11x11
+// Gaussian window, sigma 1.5, zero padding 5, per-channel (groups = C), C1 = 0.01^2, C2 = 0.03^2, mean over all
+// elements). The reference runs five conv2d calls plus ~20 elementwise kernels forward and their autograd mirror
+// backward; here the forward is one tiled kernel (separable window, both images staged once in shared memory) that
+// also emits the three derivative maps, and the backward is one tiled kernel that convolves those maps and adds the
+// L1 term. x is the render (gets the gradient), y the ground truth (none).
+//
+// With mu = w*x, nu = w*y, e11 = w*x^2, e22 = w*y^2, e12 = w*xy (w* = windowed sum),
+//   A1 = 2 mu nu + C1, A2 = 2 (e12 - mu nu) + C2, B1 = mu^2 + nu^2 + C1, B2 = (e11 - mu^2) + (e22 - nu^2) + C2,
+//   S = A1 A2 / (B1 B2),
+//   dS/de11 = -S / B2,  dS/de12 = 2 A1 / (B1 B2),
+//   dS/dmu  = 2 nu (A2 - A1) / (B1 B2) - 2 mu S (1/B1 - 1/B2)          (total derivative, e11/e12 held fixed)
+// and  d(sum_q S_q)/dx_p = sum_q w(p - q) [ dS/dmu_q + 2 x_p dS/de11_q + y_p dS/de12_q ].
+#include "gs_common.cuh"
+#include "kernels.cuh"
+
+namespace gs {
+
+constexpr int kLossTile = 16;
+constexpr int kLossHalo = 5;
+constexpr int kLossSpan = kLossTile + 2 * kLossHalo;   // 26
+constexpr int kLossThreads = kLossTile * kLossTile;
+
+GS_DEV float block_sum_256(float v, float* s_red) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) s_red[warp] = v;
+    __syncthreads();
+    float t = 0.f;
+    if (threadIdx.x < kLossThreads / 32) t = s_red[threadIdx.x];
+    if (warp == 0) {
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    }
+    __syncthreads();
+    return t;   // valid in thread 0
+}
+
+__global__ void __launch_bounds__(kLossThreads) ssim_l1_fwd_kernel(const __grid_constant__ LossParams p) {
+    __shared__ float s_x[kLossSpan][kLossSpan + 1];
+    __shared__ float s_y[kLossSpan][kLossSpan + 1];
+    __shared__ float s_h[5][kLossSpan][kLossTile + 1];
+    __shared__ float s_red[kLossThreads / 32];
+    const int tx = threadIdx.x % kLossTile, ty = threadIdx.x / kLossTile;
+    const int x0 = blockIdx.x * kLossTile, y0 = blockIdx.y * kLossTile;
+    const size_t plane = (size_t)blockIdx.z * p.H * p.W;
+    const float* __restrict__ X = p.img + plane;
+    const float* __restrict__ Y = p.gt + plane;
+    // ---- stage both images with their halo (zero padding outside the image, F.conv2d padding=5) ----
+    for (int i = threadIdx.x; i < kLossSpan * kLossSpan; i += kLossThreads) {
+        const int r = i / kLossSpan, c = i - r * kLossSpan;
+        const int gy = y0 + r - kLossHalo, gx = x0 + c - kLossHalo;
+        float a = 0.f, b = 0.f;
+        if (gy >= 0 && gy < p.H && gx >= 0 && gx < p.W) {
+            a = X[(size_t)gy * p.W + gx];
+            b = Y[(size_t)gy * p.W + gx];
+        }
+        s_x[r][c] = a;
+        s_y[r][c] = b;
+    }
+    __syncthreads();
+    // ---- horizontal pass: 26 rows x 16 columns x 5 maps ----
+    for (int i = threadIdx.x; i < kLossSpan * kLossTile; i += kLossThreads) {
+        const int r = i / kLossTile, c = i - r * kLossTile;
+        float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; ++k) {
+            const float w = p.win[k], a = s_x[r][c + k], b = s_y[r][c + k];
+            m1 = fmaf(w, a, m1);
+            m2 = fmaf(w, b, m2);
+            e11 = fmaf(w, a * a, e11);
+            e22 = fmaf(w, b * b, e22);
+            e12 = fmaf(w, a * b, e12);
+        }
+        s_h[0][r][c] = m1; s_h[1][r][c] = m2; s_h[2][r][c] = e11; s_h[3][r][c] = e22; s_h[4][r][c] = e12;
+    }
+    __syncthreads();
+    // ---- vertical pass + SSIM and its partial derivatives at this thread's pixel ----
+    float mu = 0.f, nu = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; ++k) {
+        const float w = p.win[k];
+        mu = fmaf(w, s_h[0][ty + k][tx], mu);
+        nu = fmaf(w, s_h[1][ty + k][tx], nu);
+        e11 = fmaf(w, s_h[2][ty + k][tx], e11);
+        e22 = fmaf(w, s_h[3][ty + k][tx], e22);
+        e12 = fmaf(w, s_h[4][ty + k][tx], e12);
+    }
+    const int gx = x0 + tx, gy = y0 + ty;
+    const bool inside = gx < p.W && gy < p.H;
+    float ssim = 0.f, l1 = 0.f;
+    if (inside) {
+        const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+        const float mu_sq = mu * mu, nu_sq = nu * nu, munu = mu * nu;
+        const float s1 = e11 - mu_sq, s2 = e22 - nu_sq, s12 = e12 - munu;
+        const float A1 = 2.f * munu + C1, A2 = 2.f * s12 + C2, B1 = mu_sq + nu_sq + C1, B2 = s1 + s2 + C2;
+        const float inv_B1 = 1.f / B1, inv_B2 = 1.f / B2;
+        const float inv_B12 = inv_B1 * inv_B2;
+        ssim = (A1 * A2) * inv_B12;
+        const size_t o = plane + (size_t)gy * p.W + gx;
+        p.d_mu[o] = 2.f * nu * (A2 - A1) * inv_B12 - 2.f * mu * ssim * (inv_B1 - inv_B2);
+        p.d_e11[o] = -ssim * inv_B2;
+        p.d_e12[o] = 2.f * A1 * inv_B12;
+        l1 = fabsf(s_x[ty + kLossHalo][tx + kLossHalo] - s_y[ty + kLossHalo][tx + kLossHalo]);
+    }
+    // ---- per-block partial sums (summed in a fixed order by the reduce kernel: the loss value is deterministic) ----
+    const float l1_sum = block_sum_256(l1, s_red);
+    const float ssim_sum = block_sum_256(ssim, s_red);
+    if (threadIdx.x == 0) {
+        const size_t b = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        p.partial[2 * b] = l1_sum;
+        p.partial[2 * b + 1] = ssim_sum;
+    }
+}
+
+__global__ void __launch_bounds__(1024) loss_reduce_kernel(const float* __restrict__ partial, int nblocks, double inv_n,
+                                                           float* __restrict__ out) {
+    __shared__ double s_a[32], s_b[32];
+    double a = 0.0, b = 0.0;
+    for (int i = threadIdx.x; i < nblocks; i += 1024) {
+        a += (double)partial[2 * i];
+        b += (double)partial[2 * i + 1];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    if ((threadIdx.x & 31) == 0) { s_a[threadIdx.x >> 5] = a; s_b[threadIdx.x >> 5] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double ta = 0.0, tb = 0.0;
+        for (int w = 0; w < 32; ++w) { ta += s_a[w]; tb += s_b[w]; }
+        out[0] = (float)(ta * inv_n);   // mean |x - y|
+        out[1] = (float)(tb * inv_n);   // mean ssim_map
+    }
+}
+
+__global__ void __launch_bounds__(kLossThreads) ssim_l1_bwd_kernel(const __grid_constant__ LossParams p, float c_l1, float c_ssim,
+                                                                   const float* __restrict__ grad_scale) {
+    // dL/dimg = (upstream gradient of the scalar loss) x (c_l1 * sign(x - y) + c_ssim * d(sum S)/dx)
+    const float up = grad_scale ? __ldg(grad_scale) : 1.f;
+    const float w_l1 = c_l1 * up, w_ssim = c_ssim * up;
+    __shared__ float s_d[3][kLossSpan][kLossSpan + 1];
+    __shared__ float s_h[3][kLossSpan][kLossTile + 1];
+    const int tx = threadIdx.x % kLossTile, ty = threadIdx.x / kLossTile;
+    const int x0 = blockIdx.x * kLossTile, y0 = blockIdx.y * kLossTile;
+    const size_t plane = (size_t)blockIdx.z * p.H * p.W;
+    for (int i = threadIdx.x; i < kLossSpan * kLossSpan; i += kLossThreads) {
+        const int r = i / kLossSpan, c = i - r * kLossSpan;
+        const int gy = y0 + r - kLossHalo, gx = x0 + c - kLossHalo;
+        float a = 0.f, b = 0.f, d = 0.f;
+        if (gy >= 0 && gy < p.H && gx >= 0 && gx < p.W) {   // pixels outside the image have no ssim_map entry
+            const size_t o = plane + (size_t)gy * p.W + gx;
+            a = p.d_mu[o]; b = p.d_e11[o]; d = p.d_e12[o];
+        }
+        s_d[0][r][c] = a; s_d[1][r][c] = b; s_d[2][r][c] = d;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < kLossSpan * kLossTile; i += kLossThreads) {
+        const int r = i / kLossTile, c = i - r * kLossTile;
+        float a = 0.f, b = 0.f, d = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; ++k) {
+            const float w = p.win[k];
+            a = fmaf(w, s_d[0][r][c + k], a);
+            b = fmaf(w, s_d[1][r][c + k], b);
+            d = fmaf(w, s_d[2][r][c + k], d);
+        }
+        s_h[0][r][c] = a; s_h[1][r][c] = b; s_h[2][r][c] = d;
+    }
+    __syncthreads();
+    float a = 0.f, b = 0.f, d = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; ++k) {
+        const float w = p.win[k];
+        a = fmaf(w, s_h[0][ty + k][tx], a);
+        b = fmaf(w, s_h[1][ty + k][tx], b);
+        d = fmaf(w, s_h[2][ty + k][tx], d);
+    }
+    const int gx = x0 + tx, gy = y0 + ty;
+    if (gx < p.W && gy < p.H) {
+        const size_t o = plane + (size_t)gy * p.W + gx;
+        const float x = p.img[o], y = p.gt[o];
+        const float diff = x - y;
+        const float sgn = diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f);   // torch: d|t|/dt = sign(t), 0 at 0
+        p.dL_dimg[o] = w_ssim * (a + 2.f * x * b + y * d) + w_l1 * sgn;
+    }
+}
+
+int launch_loss_forward(const LossParams& p, float* out_means, cudaStream_t stream) {
+    const dim3 grid((p.W + kLossTile - 1) / kLossTile, (p.H + kLossTile - 1) / kLossTile, p.C);
+    ssim_l1_fwd_kernel<<<grid, kLossThreads, 0, stream>>>(p);
+    GS_LAUNCH_CHECK();
+    const int nblocks = (int)(grid.x * grid.y * grid.z);
+    loss_reduce_kernel<<<1, 1024, 0, stream>>>(p.partial, nblocks, 1.0 / ((double)p.C * p.H * p.W), out_means);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+int launch_loss_backward(const LossParams& p, float c_l1, float c_ssim, const float* grad_scale, cudaStream_t stream) {
+    const dim3 grid((p.W + kLossTile - 1) / kLossTile, (p.H + kLossTile - 1) / kLossTile, p.C);
+    ssim_l1_bwd_kernel<<<grid, kLossThreads, 0, stream>>>(p, c_l1, c_ssim, grad_scale);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+size_t loss_partial_count(int C, int H, int W) {
+    return (size_t)((W + kLossTile - 1) / kLossTile) * ((H + kLossTile - 1) / kLossTile) * C;
+}
+
+}  // namespace gs

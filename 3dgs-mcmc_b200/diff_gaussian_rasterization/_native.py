@@ -48,6 +48,10 @@ SIGNATURES = {
     "gs_dp_sh_grad_combine": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p,
                                        _c_size_t, _c_void_p]),
     "gs_dp_slab_all_reduce": (_c_int, [_c_void_p, _c_void_p, _c_int, _c_int, _c_size_t, _c_int, _c_int]),
+    "gs_loss_workspace_bytes": (_c_size_t, [_c_int, _c_int, _c_int]),
+    "gs_photometric_loss_forward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int] + [_c_void_p] * 4),
+    "gs_photometric_loss_backward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int] + [_c_void_p] * 3 + [_c_float, _c_float]
+                                     + [_c_void_p] * 2),
     "gs_adam_step": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 7 + [ctypes.c_double] * 3),
     "gs_mark_visible": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4),
     "gs_compute_relocation": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 2),
@@ -423,6 +427,49 @@ def add_noise(xyz, scaling_raw, rotation_raw, opacity_raw, lr_scale, noise=None,
                                  _ptr(opacity_raw), _ptr(noise), float(lr_scale), int(seed), int(offset)),
                "gs_add_noise")
     return xyz
+
+
+def _chw(t, name, device):
+    t = _f32_cuda(t, name, device)
+    if t.dim() == 4 and t.size(0) == 1:
+        t = t[0]
+    if t.dim() != 3:
+        raise RuntimeError(f"{name} must be [C, H, W] (or [1, C, H, W]), got {tuple(t.shape)}")
+    return t
+
+
+def photometric_loss_forward(image, gt):
+    """(means, ws): means = device float[2] {mean |image - gt|, mean ssim_map}; ws keeps the derivative maps for
+    photometric_loss_backward (gs_photometric_loss_forward)."""
+    device = image.device
+    if not image.is_cuda:
+        raise RuntimeError("image must be a CUDA tensor (no CPU path exists)")
+    image, gt = _chw(image, "image", device), _chw(gt, "gt", device)
+    if image.shape != gt.shape:
+        raise RuntimeError(f"image {tuple(image.shape)} and gt {tuple(gt.shape)} differ in shape")
+    C, H, W = (int(x) for x in image.shape)
+    with torch.cuda.device(device):
+        ws = torch.empty(_lib.gs_loss_workspace_bytes(C, H, W), dtype=torch.uint8, device=device)
+        means = torch.empty(2, dtype=torch.float32, device=device)
+        _check(_lib.gs_photometric_loss_forward(_stream(device), C, H, W, image.data_ptr(), gt.data_ptr(), ws.data_ptr(),
+                                                means.data_ptr()), "gs_photometric_loss_forward")
+    return means, ws
+
+
+def photometric_loss_backward(image, gt, ws, c_l1, c_ssim, grad_scale=None):
+    """dL/dimage = grad_scale * (c_l1 * sign(image - gt) + c_ssim * d(sum ssim_map)/dimage) (gs_photometric_loss_backward)."""
+    device = image.device
+    shape = image.shape
+    image, gt = _chw(image, "image", device), _chw(gt, "gt", device)
+    C, H, W = (int(x) for x in image.shape)
+    if grad_scale is not None:
+        grad_scale = _f32_cuda(grad_scale.reshape(1), "grad_scale", device)
+    with torch.cuda.device(device):
+        out = torch.empty((C, H, W), dtype=torch.float32, device=device)
+        _check(_lib.gs_photometric_loss_backward(_stream(device), C, H, W, image.data_ptr(), gt.data_ptr(), ws.data_ptr(),
+                                                 float(c_l1), float(c_ssim), _ptr(grad_scale), out.data_ptr()),
+               "gs_photometric_loss_backward")
+    return out.view(shape)
 
 
 def adam_step(params, grads, exp_avgs, exp_avg_sqs, lrs, steps, beta1, beta2, eps):

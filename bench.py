@@ -510,6 +510,47 @@ def run_b200_arm(args):
                 "what": "one multi-tensor Adam launch over the 59 floats/Gaussian (28 B per float: grad, param, 2 moments in; param, 2 moments out) vs torch.optim.Adam (the reference's optimizer) on the same tensors"}}
         except Exception as ex:
             line["next_rows"] = {"adam_step": {"unavailable": repr(ex)[:200]}}
+        try:
+            from diff_gaussian_rasterization import loss as fused_loss
+            import torch.nn.functional as F
+            gt_img = torch.rand((3, H, W), generator=gen).to(dev)
+            render = (gt_img + 0.05 * torch.randn((3, H, W), generator=gen).to(dev)).clamp(0, 1)
+            g1 = torch.tensor([math.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)])
+            g1 = (g1 / g1.sum()).to(dev)
+            window = (g1[:, None] @ g1[None, :]).expand(3, 1, 11, 11).contiguous()
+
+            def torch_loss(img):   # utils/loss_utils.py:21-67 + train_static.py:97, the reference's own torch ops
+                conv = lambda t: F.conv2d(t[None], window, padding=5, groups=3)[0]  # noqa: E731
+                mu1, mu2 = conv(img), conv(gt_img)
+                mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+                s1 = conv(img * img) - mu1_sq
+                s2 = conv(gt_img * gt_img) - mu2_sq
+                s12 = conv(img * gt_img) - mu1_mu2
+                m = ((2 * mu1_mu2 + 1e-4) * (2 * s12 + 9e-4)) / ((mu1_sq + mu2_sq + 1e-4) * (s1 + s2 + 9e-4))
+                return 0.8 * torch.abs(img - gt_img).mean() + 0.2 * (1.0 - m.mean())
+
+            def time_loss(fn):
+                def once():
+                    x = render.detach().requires_grad_(True)
+                    fn(x).backward()
+                for _ in range(3):
+                    once()
+                torch.cuda.synchronize()
+                ev0.record()
+                for _ in range(10):
+                    once()
+                ev1.record()
+                torch.cuda.synchronize()
+                return ev0.elapsed_time(ev1) / 10
+            fused_ms = time_loss(lambda x: fused_loss.photometric_loss(x, gt_img, 0.2))
+            torch_ms = time_loss(torch_loss)
+            loss_bytes = 3 * H * W * 4 * (2 + 3 + 3 + 2 + 1)   # fwd: 2 images in, 3 maps out; bwd: 3 maps + 2 images in, gradient out
+            line["next_rows"]["photometric_loss"] = {
+                "ms_fwd_bwd": round(fused_ms, 4), "alg_GBps": round(loss_bytes / fused_ms / 1e6, 1), "torch_ops_ms_fwd_bwd": round(torch_ms, 4),
+                "what": f"(1 - 0.2) * L1 + 0.2 * (1 - SSIM) at 3x{H}x{W}, forward + backward: fused kernels (csrc/loss.cu) vs the reference's "
+                        "torch op sequence (utils/loss_utils.py:21-67) on the same tensors"}
+        except Exception as ex:
+            line.setdefault("next_rows", {})["photometric_loss"] = {"unavailable": repr(ex)[:200]}
 
     # ---- baseline legs (rank 0, N=1 only): reference CUDA on the same box, CPU port on the host cores ----
     if n_gpus == 1 and not args.skip_baselines:

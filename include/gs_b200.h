@@ -164,6 +164,20 @@ int gs_adam_step(void* stream, int n_tensors, float* const* params, const float*
                  float* const* exp_avg, float* const* exp_avg_sq, const unsigned long long* numel,
                  const double* lr, const int* step, double beta1, double beta2, double eps);
 
+/* Fused photometric loss (additive): the loss of train_static.py:94-97,
+ *   loss = (1 - lambda) * l1_loss(image, gt) + lambda * (1 - ssim(image, gt)),
+ * with l1_loss / ssim of utils/loss_utils.py:21-22, :40-67 (11x11 Gaussian window sigma 1.5, zero padding, per channel).
+ * Forward: writes out_means[2] (device) = { mean |image - gt|, mean ssim_map } and keeps the three derivative maps in
+ * ws (gs_loss_workspace_bytes). Backward: dL_dimage[C][H][W] = up * (c_l1 * sign(image - gt) + c_ssim * d(sum ssim_map)/dimage)
+ * with up = *grad_scale (device scalar, the upstream gradient of the loss) or 1 when NULL; for the loss above
+ * c_l1 = (1 - lambda) / (C H W), c_ssim = -lambda / (C H W). The ground truth gets no gradient. */
+size_t gs_loss_workspace_bytes(int C, int H, int W);
+int gs_photometric_loss_forward(void* stream, int C, int H, int W, const float* image, const float* gt,
+                                void* ws, float* out_means);
+int gs_photometric_loss_backward(void* stream, int C, int H, int W, const float* image, const float* gt,
+                                 const void* ws, float c_l1, float c_ssim, const float* grad_scale,
+                                 float* dL_dimage);
+
 /* ---- measurement hooks (bench.py): per-stage timing with CUDA events recorded on the caller's stream between
  *      the stages of each call, and a counter of kernel launches made by this library. Process-global; not used
  *      by the compute path. gs_profile_enable(n) arms n event marks (0 disables); gs_profile_collect() waits for

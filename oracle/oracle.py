@@ -237,3 +237,58 @@ def adam_step(param, grad, exp_avg, exp_avg_sq, lr, step, beta1=0.9, beta2=0.999
     denom = (np.sqrt(v) / f(bc2_sqrt) + f(eps)).astype(np.float32)
     p = (p + f(-(lr / bc1)) * (m / denom)).astype(np.float32)
     return p, m, v
+
+
+def ssim_window():
+    """utils/loss_utils.py:27-29: exp(-(x - 5)^2 / (2 * 1.5^2)) for x in 0..10 as FP32, divided by its sum. torch's
+    CPU sum of these 11 floats equals the correctly rounded sum (3.7592328), which a float64 accumulation reproduces; a
+    sequential FP32 accumulation gives 3.7592325 (checked by tests/test_loss.py against torch itself)."""
+    g = np.array([np.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)], dtype=np.float32)
+    return (g / np.float32(g.astype(np.float64).sum())).astype(np.float32)
+
+
+def _win_conv(a, w):
+    """Per-plane 11x11 windowed sum with zero padding 5 (F.conv2d(..., padding=5, groups=C), loss_utils.py:48-56),
+    separable, in float64. a: [C, H, W]."""
+    C, H, W = a.shape
+    pad = np.zeros((C, H + 10, W + 10), np.float64)
+    pad[:, 5:5 + H, 5:5 + W] = a
+    tmp = np.zeros((C, H + 10, W), np.float64)
+    for k in range(11):
+        tmp += w[k] * pad[:, :, k:k + W]
+    out = np.zeros((C, H, W), np.float64)
+    for k in range(11):
+        out += w[k] * tmp[:, k:k + H, :]
+    return out
+
+
+def photometric_loss(img, gt, lambda_dssim=0.2):
+    """The training loss of train_static.py:94-97 in float64 numpy:
+    (1 - lambda) * l1_loss(img, gt) + lambda * (1 - ssim(img, gt)), l1_loss / ssim as utils/loss_utils.py:21-22, :40-67
+    (C1 = 0.01^2, C2 = 0.03^2, mean over all elements). Returns dict(l1, ssim, loss, grad_loss, grad_ssim); the
+    gradients (w.r.t. img) are the analytic derivative of the same expressions. Pinned against the reference's own
+    functions by tests/test_oracle_golden.py::test_loss_oracle_matches_reference_golden."""
+    x = np.asarray(img, np.float64)
+    y = np.asarray(gt, np.float64)
+    w = ssim_window().astype(np.float64)
+    n = x.size
+    mu, nu = _win_conv(x, w), _win_conv(y, w)
+    e11, e22, e12 = _win_conv(x * x, w), _win_conv(y * y, w), _win_conv(x * y, w)
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    A1 = 2 * mu * nu + C1
+    A2 = 2 * (e12 - mu * nu) + C2
+    B1 = mu * mu + nu * nu + C1
+    B2 = (e11 - mu * mu) + (e22 - nu * nu) + C2
+    S = A1 * A2 / (B1 * B2)
+    # partial derivatives of S w.r.t. the windowed sums that depend on x
+    dS_de11 = -S / B2
+    dS_de12 = 2 * A1 / (B1 * B2)
+    dS_dmu = 2 * nu * (A2 - A1) / (B1 * B2) - 2 * mu * S * (1 / B1 - 1 / B2)
+    grad_sum_S = _win_conv(dS_dmu, w) + 2 * x * _win_conv(dS_de11, w) + y * _win_conv(dS_de12, w)
+    grad_ssim = grad_sum_S / n
+    l1 = np.abs(x - y).mean()
+    grad_l1 = np.sign(x - y) / n
+    ssim_v = S.mean()
+    lam = float(lambda_dssim)
+    return {"l1": l1, "ssim": ssim_v, "loss": (1 - lam) * l1 + lam * (1 - ssim_v),
+            "grad_loss": (1 - lam) * grad_l1 - lam * grad_ssim, "grad_ssim": grad_ssim}
