@@ -18,10 +18,13 @@
 
 namespace gs {
 
-constexpr int kLossTile = 16;
+constexpr int kLossTile = 32;                          // output tile (pixels, square)
 constexpr int kLossHalo = 5;
-constexpr int kLossSpan = kLossTile + 2 * kLossHalo;   // 26
-constexpr int kLossThreads = kLossTile * kLossTile;
+constexpr int kLossSpan = kLossTile + 2 * kLossHalo;   // 42
+constexpr int kLossThreads = 256;
+constexpr int kLossBlock = 4;                          // outputs per thread along the filtered axis (register blocking:
+                                                       // 14 shared-memory loads feed 4 x 11 taps)
+constexpr int kLossGroups = kLossTile / kLossBlock;    // 8
 
 GS_DEV float block_sum_256(float v, float* s_red) {
 #pragma unroll
@@ -40,11 +43,11 @@ GS_DEV float block_sum_256(float v, float* s_red) {
 }
 
 __global__ void __launch_bounds__(kLossThreads) ssim_l1_fwd_kernel(const __grid_constant__ LossParams p) {
+    // odd row strides: the row-blocked horizontal pass and the column-per-lane vertical pass are both conflict free
     __shared__ float s_x[kLossSpan][kLossSpan + 1];
     __shared__ float s_y[kLossSpan][kLossSpan + 1];
     __shared__ float s_h[5][kLossSpan][kLossTile + 1];
     __shared__ float s_red[kLossThreads / 32];
-    const int tx = threadIdx.x % kLossTile, ty = threadIdx.x / kLossTile;
     const int x0 = blockIdx.x * kLossTile, y0 = blockIdx.y * kLossTile;
     const size_t plane = (size_t)blockIdx.z * p.H * p.W;
     const float* __restrict__ X = p.img + plane;
@@ -62,57 +65,78 @@ __global__ void __launch_bounds__(kLossThreads) ssim_l1_fwd_kernel(const __grid_
         s_y[r][c] = b;
     }
     __syncthreads();
-    // ---- horizontal pass: 26 rows x 16 columns x 5 maps ----
-    for (int i = threadIdx.x; i < kLossSpan * kLossTile; i += kLossThreads) {
-        const int r = i / kLossTile, c = i - r * kLossTile;
-        float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+    // ---- horizontal pass: 42 rows x 8 groups of 4 columns x 5 maps ----
+    for (int i = threadIdx.x; i < kLossSpan * kLossGroups; i += kLossThreads) {
+        const int r = i / kLossGroups, c0 = (i - r * kLossGroups) * kLossBlock;
+        float a[kLossBlock + 10], b[kLossBlock + 10], aa[kLossBlock + 10], bb[kLossBlock + 10], ab[kLossBlock + 10];
 #pragma unroll
-        for (int k = 0; k < 11; ++k) {
-            const float w = p.win[k], a = s_x[r][c + k], b = s_y[r][c + k];
-            m1 = fmaf(w, a, m1);
-            m2 = fmaf(w, b, m2);
-            e11 = fmaf(w, a * a, e11);
-            e22 = fmaf(w, b * b, e22);
-            e12 = fmaf(w, a * b, e12);
+        for (int j = 0; j < kLossBlock + 10; ++j) {
+            a[j] = s_x[r][c0 + j];
+            b[j] = s_y[r][c0 + j];
+            aa[j] = a[j] * a[j]; bb[j] = b[j] * b[j]; ab[j] = a[j] * b[j];
         }
-        s_h[0][r][c] = m1; s_h[1][r][c] = m2; s_h[2][r][c] = e11; s_h[3][r][c] = e22; s_h[4][r][c] = e12;
+#pragma unroll
+        for (int o = 0; o < kLossBlock; ++o) {
+            float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+            for (int k = 0; k < 11; ++k) {
+                const float w = p.win[k];
+                m1 = fmaf(w, a[o + k], m1);
+                m2 = fmaf(w, b[o + k], m2);
+                e11 = fmaf(w, aa[o + k], e11);
+                e22 = fmaf(w, bb[o + k], e22);
+                e12 = fmaf(w, ab[o + k], e12);
+            }
+            s_h[0][r][c0 + o] = m1; s_h[1][r][c0 + o] = m2; s_h[2][r][c0 + o] = e11; s_h[3][r][c0 + o] = e22;
+            s_h[4][r][c0 + o] = e12;
+        }
     }
     __syncthreads();
-    // ---- vertical pass + SSIM and its partial derivatives at this thread's pixel ----
-    float mu = 0.f, nu = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+    // ---- vertical pass: lane = column, each thread 4 rows; then SSIM and its partial derivatives per pixel ----
+    const int c = threadIdx.x % kLossTile, r0 = (threadIdx.x / kLossTile) * kLossBlock;
+    float v[5][kLossBlock];
 #pragma unroll
-    for (int k = 0; k < 11; ++k) {
-        const float w = p.win[k];
-        mu = fmaf(w, s_h[0][ty + k][tx], mu);
-        nu = fmaf(w, s_h[1][ty + k][tx], nu);
-        e11 = fmaf(w, s_h[2][ty + k][tx], e11);
-        e22 = fmaf(w, s_h[3][ty + k][tx], e22);
-        e12 = fmaf(w, s_h[4][ty + k][tx], e12);
+    for (int m = 0; m < 5; ++m) {
+        float q[kLossBlock + 10];
+#pragma unroll
+        for (int j = 0; j < kLossBlock + 10; ++j) q[j] = s_h[m][r0 + j][c];
+#pragma unroll
+        for (int o = 0; o < kLossBlock; ++o) {
+            float t = 0.f;
+#pragma unroll
+            for (int k = 0; k < 11; ++k) t = fmaf(p.win[k], q[o + k], t);
+            v[m][o] = t;
+        }
     }
-    const int gx = x0 + tx, gy = y0 + ty;
-    const bool inside = gx < p.W && gy < p.H;
-    float ssim = 0.f, l1 = 0.f;
-    if (inside) {
-        const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-        const float mu_sq = mu * mu, nu_sq = nu * nu, munu = mu * nu;
-        const float s1 = e11 - mu_sq, s2 = e22 - nu_sq, s12 = e12 - munu;
-        const float A1 = 2.f * munu + C1, A2 = 2.f * s12 + C2, B1 = mu_sq + nu_sq + C1, B2 = s1 + s2 + C2;
-        const float inv_B1 = 1.f / B1, inv_B2 = 1.f / B2;
-        const float inv_B12 = inv_B1 * inv_B2;
-        ssim = (A1 * A2) * inv_B12;
-        const size_t o = plane + (size_t)gy * p.W + gx;
-        p.d_mu[o] = 2.f * nu * (A2 - A1) * inv_B12 - 2.f * mu * ssim * (inv_B1 - inv_B2);
-        p.d_e11[o] = -ssim * inv_B2;
-        p.d_e12[o] = 2.f * A1 * inv_B12;
-        l1 = fabsf(s_x[ty + kLossHalo][tx + kLossHalo] - s_y[ty + kLossHalo][tx + kLossHalo]);
+    const int gx = x0 + c;
+    float ssim_acc = 0.f, l1_acc = 0.f;
+#pragma unroll
+    for (int o = 0; o < kLossBlock; ++o) {
+        const int gy = y0 + r0 + o;
+        if (gx < p.W && gy < p.H) {
+            const float mu = v[0][o], nu = v[1][o], e11 = v[2][o], e22 = v[3][o], e12 = v[4][o];
+            const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+            const float mu_sq = mu * mu, nu_sq = nu * nu, munu = mu * nu;
+            const float s1 = e11 - mu_sq, s2 = e22 - nu_sq, s12 = e12 - munu;
+            const float A1 = 2.f * munu + C1, A2 = 2.f * s12 + C2, B1 = mu_sq + nu_sq + C1, B2 = s1 + s2 + C2;
+            const float inv_B1 = 1.f / B1, inv_B2 = 1.f / B2;
+            const float inv_B12 = inv_B1 * inv_B2;
+            const float ssim = (A1 * A2) * inv_B12;
+            const size_t idx = plane + (size_t)gy * p.W + gx;
+            p.d_mu[idx] = 2.f * nu * (A2 - A1) * inv_B12 - 2.f * mu * ssim * (inv_B1 - inv_B2);
+            p.d_e11[idx] = -ssim * inv_B2;
+            p.d_e12[idx] = 2.f * A1 * inv_B12;
+            ssim_acc += ssim;
+            l1_acc += fabsf(s_x[r0 + o + kLossHalo][c + kLossHalo] - s_y[r0 + o + kLossHalo][c + kLossHalo]);
+        }
     }
     // ---- per-block partial sums (summed in a fixed order by the reduce kernel: the loss value is deterministic) ----
-    const float l1_sum = block_sum_256(l1, s_red);
-    const float ssim_sum = block_sum_256(ssim, s_red);
+    const float l1_sum = block_sum_256(l1_acc, s_red);
+    const float ssim_sum = block_sum_256(ssim_acc, s_red);
     if (threadIdx.x == 0) {
-        const size_t b = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-        p.partial[2 * b] = l1_sum;
-        p.partial[2 * b + 1] = ssim_sum;
+        const size_t bl = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        p.partial[2 * bl] = l1_sum;
+        p.partial[2 * bl + 1] = ssim_sum;
     }
 }
 
@@ -146,7 +170,6 @@ __global__ void __launch_bounds__(kLossThreads) ssim_l1_bwd_kernel(const __grid_
     const float w_l1 = c_l1 * up, w_ssim = c_ssim * up;
     __shared__ float s_d[3][kLossSpan][kLossSpan + 1];
     __shared__ float s_h[3][kLossSpan][kLossTile + 1];
-    const int tx = threadIdx.x % kLossTile, ty = threadIdx.x / kLossTile;
     const int x0 = blockIdx.x * kLossTile, y0 = blockIdx.y * kLossTile;
     const size_t plane = (size_t)blockIdx.z * p.H * p.W;
     for (int i = threadIdx.x; i < kLossSpan * kLossSpan; i += kLossThreads) {
@@ -160,34 +183,49 @@ __global__ void __launch_bounds__(kLossThreads) ssim_l1_bwd_kernel(const __grid_
         s_d[0][r][c] = a; s_d[1][r][c] = b; s_d[2][r][c] = d;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < kLossSpan * kLossTile; i += kLossThreads) {
-        const int r = i / kLossTile, c = i - r * kLossTile;
-        float a = 0.f, b = 0.f, d = 0.f;
+    for (int i = threadIdx.x; i < kLossSpan * kLossGroups; i += kLossThreads) {
+        const int r = i / kLossGroups, c0 = (i - r * kLossGroups) * kLossBlock;
 #pragma unroll
-        for (int k = 0; k < 11; ++k) {
-            const float w = p.win[k];
-            a = fmaf(w, s_d[0][r][c + k], a);
-            b = fmaf(w, s_d[1][r][c + k], b);
-            d = fmaf(w, s_d[2][r][c + k], d);
+        for (int m = 0; m < 3; ++m) {
+            float q[kLossBlock + 10];
+#pragma unroll
+            for (int j = 0; j < kLossBlock + 10; ++j) q[j] = s_d[m][r][c0 + j];
+#pragma unroll
+            for (int o = 0; o < kLossBlock; ++o) {
+                float t = 0.f;
+#pragma unroll
+                for (int k = 0; k < 11; ++k) t = fmaf(p.win[k], q[o + k], t);
+                s_h[m][r][c0 + o] = t;
+            }
         }
-        s_h[0][r][c] = a; s_h[1][r][c] = b; s_h[2][r][c] = d;
     }
     __syncthreads();
-    float a = 0.f, b = 0.f, d = 0.f;
+    const int c = threadIdx.x % kLossTile, r0 = (threadIdx.x / kLossTile) * kLossBlock;
+    float v[3][kLossBlock];
 #pragma unroll
-    for (int k = 0; k < 11; ++k) {
-        const float w = p.win[k];
-        a = fmaf(w, s_h[0][ty + k][tx], a);
-        b = fmaf(w, s_h[1][ty + k][tx], b);
-        d = fmaf(w, s_h[2][ty + k][tx], d);
+    for (int m = 0; m < 3; ++m) {
+        float q[kLossBlock + 10];
+#pragma unroll
+        for (int j = 0; j < kLossBlock + 10; ++j) q[j] = s_h[m][r0 + j][c];
+#pragma unroll
+        for (int o = 0; o < kLossBlock; ++o) {
+            float t = 0.f;
+#pragma unroll
+            for (int k = 0; k < 11; ++k) t = fmaf(p.win[k], q[o + k], t);
+            v[m][o] = t;
+        }
     }
-    const int gx = x0 + tx, gy = y0 + ty;
-    if (gx < p.W && gy < p.H) {
-        const size_t o = plane + (size_t)gy * p.W + gx;
-        const float x = p.img[o], y = p.gt[o];
-        const float diff = x - y;
-        const float sgn = diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f);   // torch: d|t|/dt = sign(t), 0 at 0
-        p.dL_dimg[o] = w_ssim * (a + 2.f * x * b + y * d) + w_l1 * sgn;
+    const int gx = x0 + c;
+#pragma unroll
+    for (int o = 0; o < kLossBlock; ++o) {
+        const int gy = y0 + r0 + o;
+        if (gx < p.W && gy < p.H) {
+            const size_t idx = plane + (size_t)gy * p.W + gx;
+            const float x = p.img[idx], y = p.gt[idx];
+            const float diff = x - y;
+            const float sgn = diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f);   // torch: d|t|/dt = sign(t), 0 at 0
+            p.dL_dimg[idx] = w_ssim * (v[0][o] + 2.f * x * v[1][o] + y * v[2][o]) + w_l1 * sgn;
+        }
     }
 }
 
