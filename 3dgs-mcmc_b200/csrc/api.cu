@@ -38,12 +38,13 @@ struct BwdScratch {
 // ---- optional per-stage timing (CUDA events on the caller's stream) and a kernel-launch counter ----
 enum Stage {
     ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_PACK, ST_RENDER_FWD, ST_BWD_ZERO, ST_RENDER_BWD,
-    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_DP_PUSH, ST_DP_COMBINE, ST_DP_ALL_REDUCE, ST_ADAM, ST_LOSS_FWD, ST_LOSS_BWD, ST_COUNT
+    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_DP_PUSH, ST_DP_COMBINE, ST_DP_ALL_REDUCE, ST_ADAM, ST_LOSS_FWD, ST_LOSS_BWD, ST_ACT_FWD, ST_ACT_BWD, ST_COUNT
 };
 const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "scan", "emit_instances", "tile_sort", "tile_ranges",
                                            "render_fwd", "bwd_zero", "render_bwd", "preprocess_bwd",
                                            "compute_relocation", "add_noise", "dp_color_grad_push", "dp_sh_grad_combine",
-                                           "dp_slab_all_reduce", "adam_step", "loss_fwd", "loss_bwd"};
+                                           "dp_slab_all_reduce", "adam_step", "loss_fwd", "loss_bwd", "activate_fwd",
+                                           "activate_bwd"};
 struct Profiler {
     bool on = false;
     std::vector<cudaEvent_t> ev;
@@ -462,6 +463,43 @@ int gs_photometric_loss_backward(void* stream_, int C, int H, int W, const float
     prof_mark(stream, -1);
     rc = launch_loss_backward(p, c_l1, c_ssim, grad_scale, stream);
     prof_mark(stream, ST_LOSS_BWD);
+    count_launches(1);
+    return rc;
+}
+
+size_t gs_activation_workspace_bytes(int P) {
+    return align_up(2 * sizeof(float) * activate_partial_count(P > 0 ? P : 0), kAlign) + kAlign;
+}
+
+int gs_activate_forward(void* stream_, int P, const float* raw_opacity, const float* raw_scaling, const float* raw_rotation,
+                        float* opacity, float* scaling, float* rotation, void* ws, float* out_means) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0) return GS_ERR_ARG;
+    if (P == 0) return GS_OK;
+    if (!raw_opacity || !raw_scaling || !raw_rotation || !opacity || !scaling || !rotation || !ws || !out_means) return GS_ERR_ARG;
+    if ((reinterpret_cast<size_t>(raw_rotation) | reinterpret_cast<size_t>(rotation)) & 15) return GS_ERR_ARG;
+    prof_mark(stream, -1);
+    const int rc = launch_activate_fwd(P, raw_opacity, raw_scaling, raw_rotation, opacity, scaling, rotation,
+                                       reinterpret_cast<float*>(aligned_base(ws)), out_means, stream);
+    prof_mark(stream, ST_ACT_FWD);
+    count_launches(2);
+    return rc;
+}
+
+int gs_activate_backward(void* stream_, int P, const float* raw_opacity, const float* raw_scaling, const float* raw_rotation,
+                         const float* g_opacity, const float* g_scaling, const float* g_rotation, float c_opacity,
+                         float c_scaling, const float* reg_grad, float* d_raw_opacity, float* d_raw_scaling,
+                         float* d_raw_rotation) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0) return GS_ERR_ARG;
+    if (P == 0) return GS_OK;
+    if (!raw_opacity || !raw_scaling || !raw_rotation || !d_raw_opacity || !d_raw_scaling || !d_raw_rotation) return GS_ERR_ARG;
+    if ((reinterpret_cast<size_t>(raw_rotation) | reinterpret_cast<size_t>(d_raw_rotation) | reinterpret_cast<size_t>(g_rotation)) & 15)
+        return GS_ERR_ARG;
+    prof_mark(stream, -1);
+    const int rc = launch_activate_bwd(P, raw_opacity, raw_scaling, raw_rotation, g_opacity, g_scaling, g_rotation, c_opacity,
+                                       c_scaling, reg_grad, d_raw_opacity, d_raw_scaling, d_raw_rotation, stream);
+    prof_mark(stream, ST_ACT_BWD);
     count_launches(1);
     return rc;
 }

@@ -161,6 +161,13 @@ int launch_adam_step(AdamLaunch& L, cudaStream_t stream);
 int launch_loss_forward(const LossParams& p, float* out_means, cudaStream_t stream);
 int launch_loss_backward(const LossParams& p, float c_l1, float c_ssim, const float* grad_scale, cudaStream_t stream);
 size_t loss_partial_count(int C, int H, int W);
+int launch_pair_reduce(const float* partial, int n, double inv_a, double inv_b, float* out, cudaStream_t stream);
+int launch_activate_fwd(int P, const float* raw_o, const float* raw_s, const float* raw_q, float* o, float* s, float* q,
+                        float* partial, float* out_means, cudaStream_t stream);
+int launch_activate_bwd(int P, const float* raw_o, const float* raw_s, const float* raw_q, const float* g_o, const float* g_s,
+                        const float* g_q, float c_o, float c_s, const float* reg_grad, float* d_o, float* d_s, float* d_q,
+                        cudaStream_t stream);
+size_t activate_partial_count(int P);
 int launch_color_grad_push(int P, const int* radii, const uint8_t* clamped, const float4* acc, const DpPeers& dst,
                            size_t slot_offset, bool multicast, cudaStream_t stream);
 int launch_sh_grad_combine(int P, int D, int M, int V, const float* means3D, const float* campos, const float* gathered,

@@ -140,8 +140,8 @@ __global__ void __launch_bounds__(kLossThreads) ssim_l1_fwd_kernel(const __grid_
     }
 }
 
-__global__ void __launch_bounds__(1024) loss_reduce_kernel(const float* __restrict__ partial, int nblocks, double inv_n,
-                                                           float* __restrict__ out) {
+__global__ void __launch_bounds__(1024) loss_reduce_kernel(const float* __restrict__ partial, int nblocks, double inv_a,
+                                                           double inv_b, float* __restrict__ out) {
     __shared__ double s_a[32], s_b[32];
     double a = 0.0, b = 0.0;
     for (int i = threadIdx.x; i < nblocks; i += 1024) {
@@ -158,8 +158,8 @@ __global__ void __launch_bounds__(1024) loss_reduce_kernel(const float* __restri
     if (threadIdx.x == 0) {
         double ta = 0.0, tb = 0.0;
         for (int w = 0; w < 32; ++w) { ta += s_a[w]; tb += s_b[w]; }
-        out[0] = (float)(ta * inv_n);   // mean |x - y|
-        out[1] = (float)(tb * inv_n);   // mean ssim_map
+        out[0] = (float)(ta * inv_a);   // loss: mean |x - y|
+        out[1] = (float)(tb * inv_b);   // loss: mean ssim_map
     }
 }
 
@@ -234,7 +234,13 @@ int launch_loss_forward(const LossParams& p, float* out_means, cudaStream_t stre
     ssim_l1_fwd_kernel<<<grid, kLossThreads, 0, stream>>>(p);
     GS_LAUNCH_CHECK();
     const int nblocks = (int)(grid.x * grid.y * grid.z);
-    loss_reduce_kernel<<<1, 1024, 0, stream>>>(p.partial, nblocks, 1.0 / ((double)p.C * p.H * p.W), out_means);
+    const double inv_n = 1.0 / ((double)p.C * p.H * p.W);
+    return launch_pair_reduce(p.partial, nblocks, inv_n, inv_n, out_means, stream);
+}
+
+// out[0] = inv_a * sum_i partial[2i], out[1] = inv_b * sum_i partial[2i+1], summed in a fixed order in double.
+int launch_pair_reduce(const float* partial, int n, double inv_a, double inv_b, float* out, cudaStream_t stream) {
+    loss_reduce_kernel<<<1, 1024, 0, stream>>>(partial, n, inv_a, inv_b, out);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

@@ -52,6 +52,9 @@ SIGNATURES = {
     "gs_photometric_loss_forward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int] + [_c_void_p] * 4),
     "gs_photometric_loss_backward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int] + [_c_void_p] * 3 + [_c_float, _c_float]
                                      + [_c_void_p] * 2),
+    "gs_activation_workspace_bytes": (_c_size_t, [_c_int]),
+    "gs_activate_forward": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 8),
+    "gs_activate_backward": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 6 + [_c_float, _c_float] + [_c_void_p] * 4),
     "gs_adam_step": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 7 + [ctypes.c_double] * 3),
     "gs_mark_visible": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4),
     "gs_compute_relocation": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 2),
@@ -470,6 +473,49 @@ def photometric_loss_backward(image, gt, ws, c_l1, c_ssim, grad_scale=None):
                                                  float(c_l1), float(c_ssim), _ptr(grad_scale), out.data_ptr()),
                "gs_photometric_loss_backward")
     return out.view(shape)
+
+
+def activate_forward(raw_opacity, raw_scaling, raw_rotation):
+    """(opacity, scaling, rotation, means): sigmoid / exp / normalize in one pass; means = device float[2]
+    {mean |opacity|, mean |scaling|} (gs_activate_forward)."""
+    device = raw_opacity.device
+    if not raw_opacity.is_cuda:
+        raise RuntimeError("raw_opacity must be a CUDA tensor (no CPU path exists)")
+    raw_opacity = _f32_cuda(raw_opacity, "raw_opacity", device)
+    raw_scaling = _f32_cuda(raw_scaling, "raw_scaling", device)
+    raw_rotation = _f32_cuda(raw_rotation, "raw_rotation", device)
+    P = int(raw_opacity.size(0))
+    if tuple(raw_scaling.shape) != (P, 3) or tuple(raw_rotation.shape) != (P, 4) or raw_opacity.numel() != P:
+        raise RuntimeError("expected raw_opacity [P,1], raw_scaling [P,3], raw_rotation [P,4]")
+    with torch.cuda.device(device):
+        opacity, scaling, rotation = torch.empty_like(raw_opacity), torch.empty_like(raw_scaling), torch.empty_like(raw_rotation)
+        means = torch.zeros(2, dtype=torch.float32, device=device)
+        if P:
+            ws = torch.empty(_lib.gs_activation_workspace_bytes(P), dtype=torch.uint8, device=device)
+            _check(_lib.gs_activate_forward(_stream(device), P, raw_opacity.data_ptr(), raw_scaling.data_ptr(),
+                                            raw_rotation.data_ptr(), opacity.data_ptr(), scaling.data_ptr(),
+                                            rotation.data_ptr(), ws.data_ptr(), means.data_ptr()), "gs_activate_forward")
+    return opacity, scaling, rotation, means
+
+
+def activate_backward(raw_opacity, raw_scaling, raw_rotation, g_opacity, g_scaling, g_rotation, c_opacity, c_scaling,
+                      reg_grad):
+    """Gradients w.r.t. the raw parameters (gs_activate_backward); g_* / reg_grad may be None."""
+    device = raw_opacity.device
+    P = int(raw_opacity.size(0))
+    g_opacity = _f32_cuda(g_opacity, "g_opacity", device)
+    g_scaling = _f32_cuda(g_scaling, "g_scaling", device)
+    g_rotation = _f32_cuda(g_rotation, "g_rotation", device)
+    if reg_grad is not None:
+        reg_grad = _f32_cuda(reg_grad.reshape(1), "reg_grad", device)
+    with torch.cuda.device(device):
+        d_o, d_s, d_q = torch.empty_like(raw_opacity), torch.empty_like(raw_scaling), torch.empty_like(raw_rotation)
+        if P:
+            _check(_lib.gs_activate_backward(_stream(device), P, raw_opacity.data_ptr(), raw_scaling.data_ptr(),
+                                             raw_rotation.data_ptr(), _ptr(g_opacity), _ptr(g_scaling), _ptr(g_rotation),
+                                             float(c_opacity), float(c_scaling), _ptr(reg_grad), d_o.data_ptr(),
+                                             d_s.data_ptr(), d_q.data_ptr()), "gs_activate_backward")
+    return d_o, d_s, d_q
 
 
 def adam_step(params, grads, exp_avgs, exp_avg_sqs, lrs, steps, beta1, beta2, eps):

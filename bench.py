@@ -467,6 +467,17 @@ def run_b200_arm(args):
                   ("" if n_gpus == 1 else " with the cross-rank gradient sum inside the backward" if factored else " + all_reduce of the 5 parameter gradients") +
                   "; pinned gt image (copy stream, one step ahead) and camera in, loss out"}
 
+    # ---- full training step (informational; SURVEY.md 8 f1 pieces around the hot path): raw parameters -> activations ->
+    #      rasterizer -> L1 + SSIM loss + the two regularisers -> backward (+ exchange) -> Adam -> MCMC noise, as
+    #      train_static.py:86-140 runs it. "fused": csrc/loss.cu + csrc/optim.cu + gs_add_noise; "torch_glue": the reference's
+    #      torch ops for loss / optimizer / noise around the same rasterizer (N = 1 only). ----
+    train_step = None
+    try:
+        train_step = run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_gpus, rank, K, min(Wm, 3), bg,
+                                        exchange if factored else None, barrier, ev0, ev1)
+    except Exception as ex:
+        train_step = {"unavailable": repr(ex)[:300]}
+
     if rank != 0:
         if n_gpus > 1:
             dist.destroy_process_group()
@@ -475,7 +486,7 @@ def run_b200_arm(args):
     line = {"metric": METRIC, "value": value, "unit": "views/s", "n_gpus": n_gpus, "steps": K, "warmup": Wm,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": workload_config(P, W, H, n_gpus, exchange_desc), "clocks": clocks, "e2e": e2e,
-            "gpu_launches": launches, "roofline": roofline, "stages": stage_report,
+            "gpu_launches": launches, "roofline": roofline, "stages": stage_report, "train_step": train_step,
             "step_ms": {"min": round(per_step[0], 4), "p50": round(per_step[len(per_step) // 2], 4), "max": round(per_step[-1], 4)},
             "scene_stats": {"num_rendered": R, "visible": visible, "instances_per_visible": round(R / max(visible, 1), 2),
                             "tile_list_mean": float(tile_len.float().mean().item()), "tile_list_p99": float(torch.quantile(tile_len.float(), 0.99).item()),
@@ -587,6 +598,112 @@ def run_b200_arm(args):
     print(json.dumps(line), flush=True)
     if n_gpus > 1:
         dist.destroy_process_group()
+
+
+def run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_gpus, rank, K, Wm, bg, exchange, barrier, ev0, ev1):
+    import torch.nn.functional as F
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, add_noise, dp
+    from diff_gaussian_rasterization import loss as fused_loss
+    from diff_gaussian_rasterization.optim import FusedAdam
+    from diff_gaussian_rasterization.activations import activate
+
+    lrs = {"xyz": 1.6e-4, "shs": 2.5e-3, "opacity": 0.05, "scaling": 5e-3, "rotation": 1e-3}   # arguments/__init__.py defaults
+    lam, opacity_reg, scale_reg, noise_lr = 0.2, 0.01, 0.01, 5e5
+    gt = torch.rand((3, H, W), generator=gen).to(dev)
+    g1 = torch.tensor([math.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)])
+    g1 = (g1 / g1.sum()).to(dev)
+    window = (g1[:, None] @ g1[None, :]).expand(3, 1, 11, 11).contiguous()
+
+    def torch_photometric(img):
+        conv = lambda t: F.conv2d(t[None], window, padding=5, groups=3)[0]  # noqa: E731
+        mu1, mu2 = conv(img), conv(gt)
+        mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+        s1, s2, s12 = conv(img * img) - mu1_sq, conv(gt * gt) - mu2_sq, conv(img * gt) - mu1_mu2
+        m = ((2 * mu1_mu2 + 1e-4) * (2 * s12 + 9e-4)) / ((mu1_sq + mu2_sq + 1e-4) * (s1 + s2 + 9e-4))
+        return (1.0 - lam) * torch.abs(img - gt).mean() + lam * (1.0 - m.mean())
+
+    def torch_noise(raw, xyz_lr):   # train_static.py:132-140 + utils/general_utils.py:78-110
+        sc, q = torch.exp(raw["scaling"]), F.normalize(raw["rotation"])
+        r, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+        R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y), 2 * (x * y + r * z), 1 - 2 * (x * x + z * z),
+                         2 * (y * z - r * x), 2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], 1).view(-1, 3, 3)
+        L = R * sc[:, None, :]
+        cov = L @ L.transpose(1, 2)
+        noise = torch.randn_like(raw["xyz"]) * (1 / (1 + torch.exp(-100 * ((1 - torch.sigmoid(raw["opacity"])) - 0.995)))) * noise_lr * xyz_lr
+        raw["xyz"].add_(torch.bmm(cov, noise.unsqueeze(-1)).squeeze(-1))
+
+    def make(fused):
+        raw = {"xyz": s["means3D"].clone(), "shs": s["shs"].clone(), "opacity": torch.logit(s["opacities"].clamp(1e-4, 1 - 1e-4)),
+               "scaling": torch.log(s["scales"]), "rotation": s["rotations"].clone()}
+        raw = {k: torch.nn.Parameter(v) for k, v in raw.items()}
+        opt_cls = FusedAdam if fused else torch.optim.Adam
+        opt = opt_cls([{"params": [raw[k]], "lr": lrs[k], "name": k} for k in raw], lr=0.0, eps=1e-15)
+        vp = None
+        if exchange is not None:
+            vp = dp.ViewParallelRasterizer.__new__(dp.ViewParallelRasterizer)
+            torch.nn.Module.__init__(vp)
+            vp.exchange = exchange
+        view_dev, proj_dev, campos_dev = (torch.empty(sh_, device=dev) for sh_ in ((4, 4), (4, 4), (3,)))
+
+        def step(i):
+            ch = cam_host[(i * n_gpus + rank) % len(cam_host)]
+            view_dev.copy_(ch["viewmatrix"], non_blocking=True)
+            proj_dev.copy_(ch["projmatrix"], non_blocking=True)
+            campos_dev.copy_(ch["campos"], non_blocking=True)
+            settings = GaussianRasterizationSettings(H, W, ch["tanfovx"], ch["tanfovy"], bg, 1.0, view_dev, proj_dev, 3, campos_dev, False, False)
+            if fused:
+                opacity, scaling, rotation, reg = activate(raw["opacity"], raw["scaling"], raw["rotation"], opacity_reg, scale_reg)
+            else:
+                opacity, scaling, rotation = torch.sigmoid(raw["opacity"]), torch.exp(raw["scaling"]), F.normalize(raw["rotation"])
+                reg = None
+            means2D = torch.zeros_like(raw["xyz"], requires_grad=True)
+            if vp is not None:
+                cv = torch.stack([torch.as_tensor(cams_np[(i * n_gpus + r) % len(cams_np)]["campos"]) for r in range(n_gpus)]).to(dev)
+                image = vp(settings, cv, raw["xyz"], means2D, opacity, raw["shs"], scaling, rotation)[0]
+            else:
+                image = GaussianRasterizer(settings)(means3D=raw["xyz"], means2D=means2D, shs=raw["shs"], opacities=opacity,
+                                                     scales=scaling, rotations=rotation)[0]
+            photo = fused_loss.photometric_loss(image, gt, lam) if fused else torch_photometric(image)
+            if reg is None:   # train_static.py:99-100
+                reg = opacity_reg * torch.abs(opacity).mean() + scale_reg * torch.abs(scaling).mean()
+            loss = photo / n_gpus + reg
+            loss.backward()
+            opt.step()
+            opt.zero_grad(set_to_none=True)
+            with torch.no_grad():
+                if fused:
+                    add_noise(raw["xyz"], raw["scaling"], raw["rotation"], raw["opacity"], noise_lr * lrs["xyz"], seed=7, offset=i)
+                else:
+                    torch_noise(raw, lrs["xyz"])
+            return loss
+
+        return step
+
+    out = {}
+    for name, fused in (("fused", True), ("torch_glue", False)):
+        if not fused and n_gpus > 1:
+            continue
+        step = make(fused)
+        for i in range(Wm):
+            step(i)
+        barrier()
+        ev0.record()
+        for i in range(K):
+            last = step(Wm + i)
+        ev1.record()
+        barrier()
+        ms = ev0.elapsed_time(ev1) / K
+        if n_gpus > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        out[name] = {"ms_per_step": round(ms, 4), "views_per_s": round(n_gpus * 1000.0 / ms, 2), "last_loss": float(last.item())}
+        del step
+        torch.cuda.empty_cache()
+    out["what"] = ("one full training iteration per view as train_static.py:86-140 (activations, render, L1+SSIM+regularisers, backward"
+                   + (", cross-rank gradient sum" if n_gpus > 1 else "") + ", Adam, MCMC noise) at the bench workload; 'fused' uses csrc/activations.cu, csrc/loss.cu, "
+                   "csrc/optim.cu and gs_add_noise, 'torch_glue' the reference's torch ops around the same rasterizer")
+    return out
 
 
 def main():

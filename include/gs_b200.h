@@ -178,6 +178,22 @@ int gs_photometric_loss_backward(void* stream, int C, int H, int W, const float*
                                  const void* ws, float c_l1, float c_ssim, const float* grad_scale,
                                  float* dL_dimage);
 
+/* Fused parameter activations + regularisers (additive): opacity = sigmoid(raw), scaling = exp(raw),
+ * rotation = raw / max(|raw|, 1e-12) (scene/gaussian_model_static.py:43-56, :126-146) in one pass, which also writes
+ * out_means[2] (device) = { mean |opacity|, mean |scaling| }, the two regulariser terms of train_static.py:99-100.
+ * Backward: d_raw_* from the gradients w.r.t. the activated tensors (any may be NULL = zero) plus the regularisers'
+ * own gradient, c_opacity * up * sign(opacity) and c_scaling * up * sign(scaling) with up = *reg_grad (device scalar;
+ * NULL = 0); for reg = w_o * mean|opacity| + w_s * mean|scaling|: c_opacity = w_o / P, c_scaling = w_s / (3 P).
+ * rotation pointers must be 16-byte aligned. */
+size_t gs_activation_workspace_bytes(int P);
+int gs_activate_forward(void* stream, int P, const float* raw_opacity, const float* raw_scaling,
+                        const float* raw_rotation, float* opacity, float* scaling, float* rotation,
+                        void* ws, float* out_means);
+int gs_activate_backward(void* stream, int P, const float* raw_opacity, const float* raw_scaling,
+                         const float* raw_rotation, const float* g_opacity, const float* g_scaling,
+                         const float* g_rotation, float c_opacity, float c_scaling, const float* reg_grad,
+                         float* d_raw_opacity, float* d_raw_scaling, float* d_raw_rotation);
+
 /* ---- measurement hooks (bench.py): per-stage timing with CUDA events recorded on the caller's stream between
  *      the stages of each call, and a counter of kernel launches made by this library. Process-global; not used
  *      by the compute path. gs_profile_enable(n) arms n event marks (0 disables); gs_profile_collect() waits for

@@ -292,3 +292,29 @@ def photometric_loss(img, gt, lambda_dssim=0.2):
     lam = float(lambda_dssim)
     return {"l1": l1, "ssim": ssim_v, "loss": (1 - lam) * l1 + lam * (1 - ssim_v),
             "grad_loss": (1 - lam) * grad_l1 - lam * grad_ssim, "grad_ssim": grad_ssim}
+
+
+def activate(raw_opacity, raw_scaling, raw_rotation, opacity_reg=0.0, scale_reg=0.0, g_opacity=None, g_scaling=None,
+             g_rotation=None, g_reg=1.0):
+    """The reference's parameter activations (scene/gaussian_model_static.py:43-56: sigmoid, exp, F.normalize with eps
+    1e-12) and the MCMC regularisers (train_static.py:99-100) in float64 numpy, with the analytic gradient w.r.t. the
+    raw parameters for upstream gradients g_* (None = 0) and g_reg. Pinned against the same torch ops by
+    tests/test_activations.py::test_activation_oracle_matches_torch_ops."""
+    ro, rs, rq = (np.asarray(a, np.float64) for a in (raw_opacity, raw_scaling, raw_rotation))
+    P = ro.shape[0]
+    o = 1.0 / (1.0 + np.exp(-ro))
+    s = np.exp(rs)
+    n = np.maximum(np.sqrt((rq * rq).sum(1, keepdims=True)), 1e-12)
+    q = rq / n
+    reg = opacity_reg * np.abs(o).mean() + scale_reg * np.abs(s).mean()
+    go = (0.0 if g_opacity is None else np.asarray(g_opacity, np.float64)) + g_reg * opacity_reg / P * np.sign(o)
+    gs = (0.0 if g_scaling is None else np.asarray(g_scaling, np.float64)) + g_reg * scale_reg / (3 * P) * np.sign(s)
+    d_o = go * o * (1 - o)
+    d_s = gs * s
+    if g_rotation is None:
+        d_q = np.zeros_like(rq)
+    else:
+        gq = np.asarray(g_rotation, np.float64)
+        d_q = (gq - q * (q * gq).sum(1, keepdims=True)) / n
+    return {"opacity": o, "scaling": s, "rotation": q, "reg": reg, "d_raw_opacity": d_o, "d_raw_scaling": d_s,
+            "d_raw_rotation": d_q}
