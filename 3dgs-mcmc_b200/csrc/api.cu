@@ -38,13 +38,13 @@ struct BwdScratch {
 // ---- optional per-stage timing (CUDA events on the caller's stream) and a kernel-launch counter ----
 enum Stage {
     ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_PACK, ST_RENDER_FWD, ST_BWD_ZERO, ST_RENDER_BWD,
-    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_DP_PUSH, ST_DP_COMBINE, ST_DP_ALL_REDUCE, ST_ADAM, ST_LOSS_FWD, ST_LOSS_BWD, ST_ACT_FWD, ST_ACT_BWD, ST_COUNT
+    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_DP_PUSH, ST_DP_COMBINE, ST_DP_ALL_REDUCE, ST_ADAM, ST_LOSS_FWD, ST_LOSS_BWD, ST_ACT_FWD, ST_ACT_BWD, ST_KNN, ST_COUNT
 };
 const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "scan", "emit_instances", "tile_sort", "tile_ranges",
                                            "render_fwd", "bwd_zero", "render_bwd", "preprocess_bwd",
                                            "compute_relocation", "add_noise", "dp_color_grad_push", "dp_sh_grad_combine",
                                            "dp_slab_all_reduce", "adam_step", "loss_fwd", "loss_bwd", "activate_fwd",
-                                           "activate_bwd"};
+                                           "activate_bwd", "knn_mean_dist2"};
 struct Profiler {
     bool on = false;
     std::vector<cudaEvent_t> ev;
@@ -501,6 +501,20 @@ int gs_activate_backward(void* stream_, int P, const float* raw_opacity, const f
                                        c_scaling, reg_grad, d_raw_opacity, d_raw_scaling, d_raw_rotation, stream);
     prof_mark(stream, ST_ACT_BWD);
     count_launches(1);
+    return rc;
+}
+
+size_t gs_knn_workspace_bytes(int P) { return knn_workspace_bytes(P) + kAlign; }
+
+int gs_knn_mean_dist2(void* stream_, int P, const float* points, float* mean_dist2, void* ws) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0) return GS_ERR_ARG;
+    if (P == 0) return GS_OK;
+    if (!points || !mean_dist2 || !ws) return GS_ERR_ARG;
+    prof_mark(stream, -1);
+    const int rc = launch_knn_mean_dist2(P, points, mean_dist2, aligned_base(ws), stream);
+    prof_mark(stream, ST_KNN);
+    count_launches(6 + 3 * 4);
     return rc;
 }
 

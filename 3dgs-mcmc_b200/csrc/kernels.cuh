@@ -168,6 +168,8 @@ int launch_activate_bwd(int P, const float* raw_o, const float* raw_s, const flo
                         const float* g_q, float c_o, float c_s, const float* reg_grad, float* d_o, float* d_s, float* d_q,
                         cudaStream_t stream);
 size_t activate_partial_count(int P);
+size_t knn_workspace_bytes(int P);
+int launch_knn_mean_dist2(int P, const float* points, float* out, char* ws, cudaStream_t stream);
 int launch_color_grad_push(int P, const int* radii, const uint8_t* clamped, const float4* acc, const DpPeers& dst,
                            size_t slot_offset, bool multicast, cudaStream_t stream);
 int launch_sh_grad_combine(int P, int D, int M, int V, const float* means3D, const float* campos, const float* gathered,

@@ -55,6 +55,8 @@ SIGNATURES = {
     "gs_activation_workspace_bytes": (_c_size_t, [_c_int]),
     "gs_activate_forward": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 8),
     "gs_activate_backward": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 6 + [_c_float, _c_float] + [_c_void_p] * 4),
+    "gs_knn_workspace_bytes": (_c_size_t, [_c_int]),
+    "gs_knn_mean_dist2": (_c_int, [_c_void_p, _c_int, _c_void_p, _c_void_p, _c_void_p]),
     "gs_adam_step": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 7 + [ctypes.c_double] * 3),
     "gs_mark_visible": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4),
     "gs_compute_relocation": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 2),
@@ -516,6 +518,24 @@ def activate_backward(raw_opacity, raw_scaling, raw_rotation, g_opacity, g_scali
                                              float(c_opacity), float(c_scaling), _ptr(reg_grad), d_o.data_ptr(),
                                              d_s.data_ptr(), d_q.data_ptr()), "gs_activate_backward")
     return d_o, d_s, d_q
+
+
+def knn_mean_dist2(points):
+    """Mean squared distance of every point to its 3 nearest other points (gs_knn_mean_dist2) -> float32 [P]."""
+    device = points.device
+    if not points.is_cuda:
+        raise RuntimeError("points must be a CUDA tensor (no CPU path exists)")
+    points = _f32_cuda(points, "points", device)
+    if points.dim() != 2 or points.size(1) != 3:
+        raise RuntimeError(f"points must be [P, 3], got {tuple(points.shape)}")
+    P = int(points.size(0))
+    with torch.cuda.device(device):
+        means = torch.zeros((P,), dtype=torch.float32, device=device)
+        if P:
+            ws = torch.empty(_lib.gs_knn_workspace_bytes(P), dtype=torch.uint8, device=device)
+            _check(_lib.gs_knn_mean_dist2(_stream(device), P, points.data_ptr(), means.data_ptr(), ws.data_ptr()),
+                   "gs_knn_mean_dist2")
+    return means
 
 
 def adam_step(params, grads, exp_avgs, exp_avg_sqs, lrs, steps, beta1, beta2, eps):

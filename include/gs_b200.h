@@ -194,6 +194,14 @@ int gs_activate_backward(void* stream, int P, const float* raw_opacity, const fl
                          const float* g_rotation, float c_opacity, float c_scaling, const float* reg_grad,
                          float* d_raw_opacity, float* d_raw_scaling, float* d_raw_rotation);
 
+/* distCUDA2: mean_dist2[i] = mean of the squared distances from points[i] to its three nearest other
+ * points; replaces simple_knn._C.distCUDA2 = SimpleKNN::knn (submodules/simple-knn/spatial.cu:15-26,
+ * simple_knn.cu:186-220), called at model initialisation (scene/gaussian_model_static.py:168). points[P][3],
+ * mean_dist2[P], ws of gs_knn_workspace_bytes(P) bytes. Bit-identical to the reference (exact neighbours, same
+ * distance expression, same averaging). */
+size_t gs_knn_workspace_bytes(int P);
+int gs_knn_mean_dist2(void* stream, int P, const float* points, float* mean_dist2, void* ws);
+
 /* ---- measurement hooks (bench.py): per-stage timing with CUDA events recorded on the caller's stream between
  *      the stages of each call, and a counter of kernel launches made by this library. Process-global; not used
  *      by the compute path. gs_profile_enable(n) arms n event marks (0 disables); gs_profile_collect() waits for

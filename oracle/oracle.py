@@ -47,6 +47,8 @@ def lib():
                                          _fp, _fp, _fp, _fp, _fp, _fp, _fp, _fp]
         L.orc_compute_relocation.argtypes = [_i, _fp, _fp, _ip, _fp, _i, _fp, _fp]
         L.orc_add_noise.argtypes = [_i, _fp, _fp, _fp, _fp, _fp, _f]
+        L.orc_knn_mean_dist2.argtypes = [_i, _fp, _fp]
+        L.orc_knn_mean_dist2.restype = None
         L.orc_num_threads.restype = _i
         for n in ("orc_preprocess", "orc_mark_visible", "orc_bin", "orc_render_fwd", "orc_render_bwd",
                   "orc_preprocess_bwd", "orc_compute_relocation", "orc_add_noise"):
@@ -318,3 +320,11 @@ def activate(raw_opacity, raw_scaling, raw_rotation, opacity_reg=0.0, scale_reg=
         d_q = (gq - q * (q * gq).sum(1, keepdims=True)) / n
     return {"opacity": o, "scaling": s, "rotation": q, "reg": reg, "d_raw_opacity": d_o, "d_raw_scaling": d_s,
             "d_raw_rotation": d_q}
+
+
+def knn_mean_dist2(points):
+    """distCUDA2 by brute force (oracle_cpu.c: orc_knn_mean_dist2) -> float32 [P]. O(P^2): small cases only."""
+    pts = _f32(points).reshape(-1, 3)
+    out = np.zeros(pts.shape[0], np.float32)
+    lib().orc_knn_mean_dist2(pts.shape[0], pts.reshape(-1), out)
+    return out

@@ -29,6 +29,7 @@
  * glibc's, not CUDA's, so float results agree with the GPU to a few ulp, not bit for bit; all integer
  * work (keys, order, ranges, counts) is exact given identical inputs.
  */
+#include <float.h>
 #include <math.h>
 #ifdef _OPENMP
 #include <omp.h>
@@ -583,4 +584,29 @@ int orc_num_threads(void) {
     }
 #endif
     return n;
+}
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * distCUDA2: mean of the squared distances to the three nearest other points. Follows
+ * submodules/simple-knn/simple_knn.cu:139-184 (updateKBest<3>, boxMeanDist) without its pruning: plain O(P^2).
+ * The reference's device code is compiled with nvcc's default contraction, which turns
+ * d.x*d.x + d.y*d.y + d.z*d.z into FMUL dy*dy; FFMA dx*dx + .; FFMA dz*dz + . (read off the SASS of
+ * `nvcc 12.9 -O3 -arch=sm_100`); this file is built with -ffp-contract=off, so the fused form is spelled out. A point is excluded by position only (coincident points
+ * count with distance 0), as in the reference.
+ * ------------------------------------------------------------------------------------------------------------------ */
+void orc_knn_mean_dist2(int P, const float* pts, float* out) {
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < P; ++i) {
+        float best[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
+        const float rx = pts[3 * i], ry = pts[3 * i + 1], rz = pts[3 * i + 2];
+        for (int j = 0; j < P; ++j) {
+            if (j == i) continue;
+            const float dx = pts[3 * j] - rx, dy = pts[3 * j + 1] - ry, dz = pts[3 * j + 2] - rz;
+            float dist = fmaf(dz, dz, fmaf(dx, dx, dy * dy));
+            for (int k = 0; k < 3; ++k) {
+                if (best[k] > dist) { const float t = best[k]; best[k] = dist; dist = t; }
+            }
+        }
+        out[i] = (best[0] + best[1] + best[2]) / 3.0f;
+    }
 }

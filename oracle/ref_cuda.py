@@ -116,3 +116,30 @@ def compute_relocation(opacity_old, scale_old, N, binoms, n_max):
                                      N.int().contiguous().data_ptr(), binoms.contiguous().data_ptr(), n_max,
                                      o.data_ptr(), s.data_ptr())
     return o, s
+
+
+# ---- the reference's simple-knn (oracle/_ref/libref_knn.so) ----
+_KNN_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libref_knn.so")
+_knn_lib = None
+
+
+def knn_available():
+    return os.path.exists(_KNN_PATH)
+
+
+def knn(points):
+    """distCUDA2 of the reference (SimpleKNN::knn) on a CUDA [P,3] tensor -> float32 [P]. Runs on the default stream."""
+    global _knn_lib
+    if _knn_lib is None:
+        if not knn_available():
+            raise FileNotFoundError(f"{_KNN_PATH} missing: run `make -C oracle ref` where /root/reference is mounted")
+        _knn_lib = ctypes.CDLL(_KNN_PATH)
+        _knn_lib.ref_knn.restype = _i
+        _knn_lib.ref_knn.argtypes = [_i, _vp, _vp]
+    pts = points.contiguous().float()
+    out = torch.zeros((pts.shape[0],), dtype=torch.float32, device=pts.device)
+    torch.cuda.synchronize()
+    rc = _knn_lib.ref_knn(int(pts.shape[0]), pts.data_ptr(), out.data_ptr())
+    if rc != 0:
+        raise RuntimeError(f"reference simple-knn failed: cudaError {rc}")
+    return out
