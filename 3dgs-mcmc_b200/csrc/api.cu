@@ -38,13 +38,13 @@ struct BwdScratch {
 // ---- optional per-stage timing (CUDA events on the caller's stream) and a kernel-launch counter ----
 enum Stage {
     ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_SORT, ST_PACK, ST_RENDER_FWD, ST_BWD_ZERO, ST_RENDER_BWD,
-    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_DP_PUSH, ST_DP_COMBINE, ST_DP_ALL_REDUCE, ST_ADAM, ST_LOSS_FWD, ST_LOSS_BWD, ST_ACT_FWD, ST_ACT_BWD, ST_KNN, ST_COUNT
+    ST_PREPROCESS_BWD, ST_RELOCATION, ST_ADD_NOISE, ST_DP_PUSH, ST_DP_COMBINE, ST_DP_ALL_REDUCE, ST_ADAM, ST_LOSS_FWD, ST_LOSS_BWD, ST_ACT_FWD, ST_ACT_BWD, ST_KNN, ST_SWIN_FWD, ST_SWIN_BWD, ST_COUNT
 };
 const char* const kStageNames[ST_COUNT] = {"preprocess_fwd", "depth_sort", "scan", "emit_instances", "tile_sort", "tile_ranges",
                                            "render_fwd", "bwd_zero", "render_bwd", "preprocess_bwd",
                                            "compute_relocation", "add_noise", "dp_color_grad_push", "dp_sh_grad_combine",
                                            "dp_slab_all_reduce", "adam_step", "loss_fwd", "loss_bwd", "activate_fwd",
-                                           "activate_bwd", "knn_mean_dist2"};
+                                           "activate_bwd", "knn_mean_dist2", "swin_gather_fwd", "swin_gather_bwd"};
 struct Profiler {
     bool on = false;
     std::vector<cudaEvent_t> ev;
@@ -500,6 +500,71 @@ int gs_activate_backward(void* stream_, int P, const float* raw_opacity, const f
     const int rc = launch_activate_bwd(P, raw_opacity, raw_scaling, raw_rotation, g_opacity, g_scaling, g_rotation, c_opacity,
                                        c_scaling, reg_grad, d_raw_opacity, d_raw_scaling, d_raw_rotation, stream);
     prof_mark(stream, ST_ACT_BWD);
+    count_launches(1);
+    return rc;
+}
+
+namespace {
+int fill_swin_set(SwinSet* s, const float* const* ptrs, bool required) {
+    if (!ptrs) return required ? GS_ERR_ARG : GS_OK;
+    const float** dst[10] = {&s->xyz, &s->rot, &s->dc, &s->rest, &s->opacity, &s->scaling, &s->v, &s->rotvec, &s->cen, &s->start};
+    for (int i = 0; i < 10; ++i) {
+        if (required && !ptrs[i]) return GS_ERR_ARG;
+        *dst[i] = ptrs[i];
+    }
+    if (reinterpret_cast<size_t>(s->rot) & 15) return GS_ERR_ARG;
+    return GS_OK;
+}
+int fill_swin_params(SwinParams* p, int Ki, int Km, int M, float frame, int deform, const long long* imm_idx,
+                     const long long* mat_idx, const float* const* imm_set, const float* const* mat_set) {
+    if (Ki < 0 || Km < 0 || M < 1) return GS_ERR_ARG;
+    SwinSet zero = {};
+    p->Ki = Ki; p->Km = Km; p->M = M; p->frame = frame; p->deform = deform; p->imm_idx = imm_idx; p->mat_idx = mat_idx;
+    p->imm = zero; p->mat = zero;
+    if ((Ki > 0 && !imm_idx) || (Km > 0 && !mat_idx)) return GS_ERR_ARG;
+    int rc = fill_swin_set(&p->imm, imm_set, Ki > 0);
+    if (rc) return rc;
+    return fill_swin_set(&p->mat, mat_set, Km > 0);
+}
+}  // namespace
+
+int gs_swin_gather_forward(void* stream_, int Ki, int Km, int M, float frame, int deform, const long long* imm_idx,
+                           const long long* mat_idx, const float* const* imm_set, const float* const* mat_set,
+                           float* out_xyz, float* out_rotation, float* out_feature, float* out_opacity, float* out_scaling) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SwinParams p;
+    int rc = fill_swin_params(&p, Ki, Km, M, frame, deform, imm_idx, mat_idx, imm_set, mat_set);
+    if (rc) return rc;
+    if (Ki + Km == 0) return GS_OK;
+    if (!out_xyz || !out_rotation || !out_feature || !out_opacity || !out_scaling || (reinterpret_cast<size_t>(out_rotation) & 15))
+        return GS_ERR_ARG;
+    p.out_xyz = out_xyz; p.out_rot = out_rotation; p.out_feat = out_feature; p.out_opacity = out_opacity; p.out_scaling = out_scaling;
+    prof_mark(stream, -1);
+    rc = launch_swin_gather_fwd(p, stream);
+    prof_mark(stream, ST_SWIN_FWD);
+    count_launches(1);
+    return rc;
+}
+
+int gs_swin_gather_backward(void* stream_, int Ki, int M, float frame, int deform, const long long* imm_idx,
+                            const float* const* imm_set, const float* const* out_grads, float* const* imm_grads) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SwinParams p;
+    int rc = fill_swin_params(&p, Ki, 0, M, frame, deform, imm_idx, nullptr, imm_set, nullptr);
+    if (rc) return rc;
+    if (Ki == 0) return GS_OK;
+    if (!out_grads || !imm_grads) return GS_ERR_ARG;
+    p.out_xyz = p.out_rot = p.out_feat = p.out_opacity = p.out_scaling = nullptr;
+    SwinGrads g;
+    g.g_xyz = out_grads[0]; g.g_rot = out_grads[1]; g.g_feat = out_grads[2]; g.g_opacity = out_grads[3]; g.g_scaling = out_grads[4];
+    for (int i = 0; i < 9; ++i)
+        if (!imm_grads[i]) return GS_ERR_ARG;
+    g.d_xyz = imm_grads[0]; g.d_rot = imm_grads[1]; g.d_dc = imm_grads[2]; g.d_rest = imm_grads[3]; g.d_opacity = imm_grads[4];
+    g.d_scaling = imm_grads[5]; g.d_v = imm_grads[6]; g.d_rotvec = imm_grads[7]; g.d_cen = imm_grads[8];
+    if ((reinterpret_cast<size_t>(g.d_rot) | reinterpret_cast<size_t>(g.g_rot)) & 15) return GS_ERR_ARG;
+    prof_mark(stream, -1);
+    rc = launch_swin_gather_bwd(p, g, stream);
+    prof_mark(stream, ST_SWIN_BWD);
     count_launches(1);
     return rc;
 }

@@ -115,6 +115,33 @@ struct LossParams {
     float win[11];
 };
 
+// Sliding-window gather (swin.cu). One parameter set of the swin model; all pointers are row-major FP32.
+struct SwinSet {
+    const float* xyz;      // [N][3]
+    const float* rot;      // [N][4]   raw quaternion (w, x, y, z)
+    const float* dc;       // [N][1][3]
+    const float* rest;     // [N][M-1][3]
+    const float* opacity;  // [N][1]   raw
+    const float* scaling;  // [N][3]   raw
+    const float* v;        // [N][3]   rigid velocity
+    const float* rotvec;   // [N][3]   rigid rotation vector per frame
+    const float* cen;      // [N][3]   rotation centre
+    const float* start;    // [N]      frame the age counts from
+};
+struct SwinParams {
+    int Ki, Km, M;
+    float frame;
+    int deform;
+    const long long* imm_idx;   // [Ki] rows of the immature set
+    const long long* mat_idx;   // [Km] rows of the matured set
+    SwinSet imm, mat;
+    float *out_xyz, *out_rot, *out_feat, *out_opacity, *out_scaling;   // [K][3], [K][4], [K][M][3], [K][1], [K][3]
+};
+struct SwinGrads {
+    const float *g_xyz, *g_rot, *g_feat, *g_opacity, *g_scaling;       // gradients of the five outputs (any may be null)
+    float *d_xyz, *d_rot, *d_dc, *d_rest, *d_opacity, *d_scaling, *d_v, *d_rotvec, *d_cen;   // immature set, zero-filled
+};
+
 // One multi-tensor Adam launch (optim.cu).
 struct AdamTensor {
     float* param;
@@ -168,6 +195,8 @@ int launch_activate_bwd(int P, const float* raw_o, const float* raw_s, const flo
                         const float* g_q, float c_o, float c_s, const float* reg_grad, float* d_o, float* d_s, float* d_q,
                         cudaStream_t stream);
 size_t activate_partial_count(int P);
+int launch_swin_gather_fwd(const SwinParams& p, cudaStream_t stream);
+int launch_swin_gather_bwd(const SwinParams& p, const SwinGrads& g, cudaStream_t stream);
 size_t knn_workspace_bytes(int P);
 int launch_knn_mean_dist2(int P, const float* points, float* out, char* ws, cudaStream_t stream);
 int launch_color_grad_push(int P, const int* radii, const uint8_t* clamped, const float4* acc, const DpPeers& dst,

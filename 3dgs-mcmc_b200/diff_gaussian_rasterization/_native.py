@@ -57,6 +57,8 @@ SIGNATURES = {
     "gs_activate_backward": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 6 + [_c_float, _c_float] + [_c_void_p] * 4),
     "gs_knn_workspace_bytes": (_c_size_t, [_c_int]),
     "gs_knn_mean_dist2": (_c_int, [_c_void_p, _c_int, _c_void_p, _c_void_p, _c_void_p]),
+    "gs_swin_gather_forward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_float, _c_int] + [_c_void_p] * 9),
+    "gs_swin_gather_backward": (_c_int, [_c_void_p, _c_int, _c_int, _c_float, _c_int] + [_c_void_p] * 4),
     "gs_adam_step": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 7 + [ctypes.c_double] * 3),
     "gs_mark_visible": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4),
     "gs_compute_relocation": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 4 + [_c_int] + [_c_void_p] * 2),
@@ -536,6 +538,70 @@ def knn_mean_dist2(points):
             _check(_lib.gs_knn_mean_dist2(_stream(device), P, points.data_ptr(), means.data_ptr(), ws.data_ptr()),
                    "gs_knn_mean_dist2")
     return means
+
+
+SWIN_SET_KEYS = ("xyz", "rotation", "features_dc", "features_rest", "opacity", "scaling", "rigid_v", "rigid_rotvec",
+                 "rigid_rotcen", "frame_start")
+
+
+def _swin_set(tensors, device, what):
+    out = []
+    for key, t in zip(SWIN_SET_KEYS, tensors):
+        t = _f32_cuda(t, f"{what}.{key}", device)
+        out.append(t)
+    return out
+
+
+def _idx64(t, device, name):
+    if t.device != device or t.dtype != torch.int64:
+        raise RuntimeError(f"{name} must be an int64 tensor on {device}")
+    return t.contiguous()
+
+
+def swin_gather_forward(frame, deform, imm_idx, mat_idx, imm_set, mat_set):
+    """Rasterizer inputs of the Gaussians alive at `frame` (gs_swin_gather_forward). imm_set / mat_set: the ten tensors
+    of SWIN_SET_KEYS. Returns (xyz, rotation, feature, opacity, scaling) for the Ki + Km active Gaussians."""
+    device = imm_set[0].device
+    if not imm_set[0].is_cuda:
+        raise RuntimeError("swin_gather needs CUDA tensors (no CPU path exists)")
+    imm_idx, mat_idx = _idx64(imm_idx, device, "imm_idx"), _idx64(mat_idx, device, "mat_idx")
+    Ki, Km = int(imm_idx.numel()), int(mat_idx.numel())
+    M = int(imm_set[3].size(1)) + 1
+    imm = _swin_set(imm_set, device, "immature")
+    mat = _swin_set(mat_set, device, "matured") if Km else None
+    K = Ki + Km
+    opts = dict(dtype=torch.float32, device=device)
+    with torch.cuda.device(device):
+        outs = (torch.empty((K, 3), **opts), torch.empty((K, 4), **opts), torch.empty((K, M, 3), **opts),
+                torch.empty((K, 1), **opts), torch.empty((K, 3), **opts))
+        if K:
+            ia = _ptr_array([t.data_ptr() for t in imm])
+            ma = _ptr_array([t.data_ptr() for t in mat]) if mat else None
+            _check(_lib.gs_swin_gather_forward(
+                _stream(device), Ki, Km, M, float(frame), 1 if deform else 0, _ptr(imm_idx), _ptr(mat_idx),
+                ctypes.cast(ia, _c_void_p), ctypes.cast(ma, _c_void_p) if ma is not None else None,
+                *[o.data_ptr() for o in outs]), "gs_swin_gather_forward")
+    return outs
+
+
+def swin_gather_backward(frame, deform, imm_idx, imm_set, out_grads):
+    """Gradients w.r.t. the first nine tensors of the immature set (dense, zero outside the gathered rows)."""
+    device = imm_set[0].device
+    imm_idx = _idx64(imm_idx, device, "imm_idx")
+    Ki = int(imm_idx.numel())
+    M = int(imm_set[3].size(1)) + 1
+    imm = _swin_set(imm_set, device, "immature")
+    grads = [_f32_cuda(g, "out_grad", device) if g is not None else None for g in out_grads]
+    with torch.cuda.device(device):
+        d = [torch.zeros_like(t) for t in imm[:9]]
+        if Ki:
+            ia = _ptr_array([t.data_ptr() for t in imm])
+            ga = _ptr_array([g.data_ptr() if g is not None and g.numel() else 0 for g in grads])
+            da = _ptr_array([t.data_ptr() for t in d])
+            _check(_lib.gs_swin_gather_backward(_stream(device), Ki, M, float(frame), 1 if deform else 0, imm_idx.data_ptr(),
+                                                ctypes.cast(ia, _c_void_p), ctypes.cast(ga, _c_void_p),
+                                                ctypes.cast(da, _c_void_p)), "gs_swin_gather_backward")
+    return d
 
 
 def adam_step(params, grads, exp_avgs, exp_avg_sqs, lrs, steps, beta1, beta2, eps):

@@ -202,6 +202,28 @@ int gs_activate_backward(void* stream, int P, const float* raw_opacity, const fl
 size_t gs_knn_workspace_bytes(int P);
 int gs_knn_mean_dist2(void* stream, int P, const float* points, float* mean_dist2, void* ws);
 
+/* Sliding-window gather + rigid deformation + activations (additive): the rasterizer inputs of the
+ * Gaussians alive at `frame`, as SwinGaussianModel.get_basic_para_at builds them (scene/gaussian_model.py:598-649 with
+ * utils/tempo_utils.py:4-84 rigid_deform and the activations of gaussian_model.py:43-56).
+ * A parameter set is a host array of 10 device pointers in this order:
+ *   xyz[N][3], rotation[N][4] (raw, w x y z), features_dc[N][1][3], features_rest[N][M-1][3], opacity[N][1] (raw),
+ *   scaling[N][3] (raw), rigid_v[N][3], rigid_rotvec[N][3], rigid_rotcen[N][3], frame_start[N] (float).
+ * Forward: active Gaussian k < Ki is row imm_idx[k] of the immature set, k >= Ki row mat_idx[k - Ki] of the matured
+ * set (int64 indices, as torch.nonzero returns them); age = frame - frame_start[row]; deform == 0 skips the motion
+ * (rigid_deform(skip=True)). Outputs for K = Ki + Km: xyz[K][3], rotation[K][4] (normalised), feature[K][M][3]
+ * (cat(dc, rest)), opacity[K][1] (sigmoid), scaling[K][3] (exp).
+ * Backward: out_grads = 5 device pointers (gradients of the outputs in that order, any may be NULL), imm_grads = 9
+ * zero-filled device tensors shaped like the first nine members of the immature set; rows imm_idx[k] are written
+ * (the matured set is detached in the reference and gets no gradient). */
+int gs_swin_gather_forward(void* stream, int Ki, int Km, int M, float frame, int deform,
+                           const long long* imm_idx, const long long* mat_idx,
+                           const float* const* imm_set, const float* const* mat_set,
+                           float* out_xyz, float* out_rotation, float* out_feature, float* out_opacity,
+                           float* out_scaling);
+int gs_swin_gather_backward(void* stream, int Ki, int M, float frame, int deform, const long long* imm_idx,
+                            const float* const* imm_set, const float* const* out_grads,
+                            float* const* imm_grads);
+
 /* ---- measurement hooks (bench.py): per-stage timing with CUDA events recorded on the caller's stream between
  *      the stages of each call, and a counter of kernel launches made by this library. Process-global; not used
  *      by the compute path. gs_profile_enable(n) arms n event marks (0 disables); gs_profile_collect() waits for

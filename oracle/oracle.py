@@ -328,3 +328,95 @@ def knn_mean_dist2(points):
     out = np.zeros(pts.shape[0], np.float32)
     lib().orc_knn_mean_dist2(pts.shape[0], pts.reshape(-1), out)
     return out
+
+
+SWIN_KEYS = ("xyz", "rotation", "features_dc", "features_rest", "opacity", "scaling", "rigid_v", "rigid_rotvec", "rigid_rotcen",
+             "frame_start")
+
+
+def _quat_mul(q1, q2):
+    """utils/tempo_utils.py:42-47 (w, x, y, z)."""
+    w1, x1, y1, z1 = (q1[:, i] for i in range(4))
+    w2, x2, y2, z2 = (q2[:, i] for i in range(4))
+    return np.stack((w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2, w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2,
+                     w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2, w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2), 1)
+
+
+def swin_gather(frame, imm, mat, imm_idx, mat_idx, deform=True, upstream=None):
+    """SwinGaussianModel.get_basic_para_at (scene/gaussian_model.py:598-649) in float64 numpy: gather both parameter
+    sets, age-based rigid_deform (utils/tempo_utils.py:49-84; rotvec2quat :4-17, rotvec2mat :19-40), F.normalize /
+    sigmoid / exp. With `upstream` (dict of gradients of the five outputs) also returns the analytic gradients w.r.t.
+    the nine immature parameter tensors under "grad". Pinned against goldens made with the reference's own
+    tempo_utils + autograd by tests/test_swin.py::test_swin_oracle_matches_reference_golden."""
+    f64 = lambda a: np.asarray(a, np.float64)  # noqa: E731
+    ii, mi = np.asarray(imm_idx, np.int64), np.asarray(mat_idx, np.int64)
+    Ki = len(ii)
+
+    def cat(k):
+        a = f64(imm[k])[ii]
+        return np.concatenate((a, f64(mat[k])[mi]), 0) if len(mi) else a
+    age = (frame - cat("frame_start"))[:, None]
+    xyz, rot = cat("xyz"), cat("rotation")
+    if deform:
+        v, rvec, cen = cat("rigid_v"), cat("rigid_rotvec"), cat("rigid_rotcen")
+        rv = rvec * age
+        a = np.sqrt((rv * rv).sum(1, keepdims=True))
+        inv = 1.0 / np.maximum(a, 1e-12)
+        u = rv * inv
+        s, c, sh, ch = np.sin(a), np.cos(a), np.sin(a / 2), np.cos(a / 2)
+        pt = xyz - cen
+        up_, uup = np.cross(u, pt), np.cross(u, np.cross(u, pt))
+        pos = pt + s * up_ + (1 - c) * uup + cen + v * age
+        q = np.concatenate((ch, u * sh), 1)
+        rr = _quat_mul(q, rot)
+    else:
+        pos, rr = xyz, rot
+    norm = np.sqrt((rr * rr).sum(1, keepdims=True))
+    ninv = 1.0 / np.maximum(norm, 1e-12)
+    out = {"xyz": pos, "rotation": rr * ninv,
+           "feature": np.concatenate((cat("features_dc"), cat("features_rest")), 1),
+           "opacity": 1.0 / (1.0 + np.exp(-cat("opacity"))), "scaling": np.exp(cat("scaling"))}
+    if upstream is None:
+        return out
+    g = {k: f64(upstream[k])[:Ki] for k in upstream}
+    sl = slice(0, Ki)
+    gx, gn = g["xyz"], g["rotation"]
+    nh = (rr * ninv)[sl]
+    h = np.where(norm[sl] > 1e-12, (gn - nh * (nh * gn).sum(1, keepdims=True)) * ninv[sl], gn * ninv[sl])
+    grads = {}
+    r = rot[sl]
+    if deform:
+        u_, s_, c_, sh_, ch_, pt_, a_, inv_, age_ = u[sl], s[sl], c[sl], sh[sl], ch[sl], pt[sl], a[sl], inv[sl], age[sl]
+        ug = np.cross(u_, gx)
+        d_pt = gx - s_ * ug + (1 - c_) * np.cross(u_, ug)
+        d_s = (gx * np.cross(u_, pt_)).sum(1, keepdims=True)
+        d_c = -(gx * np.cross(u_, np.cross(u_, pt_))).sum(1, keepdims=True)
+        gu, gp, upd = (gx * u_).sum(1, keepdims=True), (gx * pt_).sum(1, keepdims=True), (u_ * pt_).sum(1, keepdims=True)
+        d_u = s_ * np.cross(pt_, gx) + (1 - c_) * (gx * upd + pt_ * gu - 2 * u_ * gp)
+        q_ = q[sl]
+        w1, x1, y1, z1 = (q_[:, i:i + 1] for i in range(4))
+        w2, x2, y2, z2 = (r[:, i:i + 1] for i in range(4))
+        hw, hx, hy, hz = (h[:, i:i + 1] for i in range(4))
+        dq = np.concatenate((hw * w2 + hx * x2 + hy * y2 + hz * z2, -hw * x2 + hx * w2 - hy * z2 + hz * y2,
+                             -hw * y2 + hx * z2 + hy * w2 - hz * x2, -hw * z2 - hx * y2 + hy * x2 + hz * w2), 1)
+        d_rot = np.concatenate((hw * w1 + hx * x1 + hy * y1 + hz * z1, -hw * x1 + hx * w1 + hy * z1 - hz * y1,
+                                -hw * y1 - hx * z1 + hy * w1 + hz * x1, -hw * z1 + hx * y1 - hy * x1 + hz * w1), 1)
+        d_ch, d_sh = dq[:, :1], (u_ * dq[:, 1:]).sum(1, keepdims=True)
+        d_u = d_u + sh_ * dq[:, 1:]
+        d_a = d_s * c_ - d_c * s_ - 0.5 * d_ch * sh_ + 0.5 * d_sh * ch_
+        d_rv = np.where(a_ > 1e-12, (d_u - u_ * (u_ * d_u).sum(1, keepdims=True)) * inv_ + d_a * u_, d_u * inv_)
+        per = {"xyz": d_pt, "rotation": d_rot, "rigid_v": gx * age_, "rigid_rotvec": d_rv * age_, "rigid_rotcen": gx - d_pt}
+    else:
+        z3 = np.zeros_like(gx)
+        per = {"xyz": gx, "rotation": h, "rigid_v": z3, "rigid_rotvec": z3, "rigid_rotcen": z3}
+    o = out["opacity"][sl]
+    per["opacity"] = g["opacity"] * o * (1 - o)
+    per["scaling"] = g["scaling"] * out["scaling"][sl]
+    per["features_dc"] = g["feature"][:, :1]
+    per["features_rest"] = g["feature"][:, 1:]
+    for k in SWIN_KEYS[:9]:
+        full = np.zeros(np.asarray(imm[k]).shape, np.float64)
+        full[ii] = per[k]
+        grads[k] = full
+    out["grad"] = grads
+    return out
