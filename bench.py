@@ -562,6 +562,10 @@ def run_b200_arm(args):
                         "torch op sequence (utils/loss_utils.py:21-67) on the same tensors"}
         except Exception as ex:
             line.setdefault("next_rows", {})["photometric_loss"] = {"unavailable": repr(ex)[:200]}
+        try:
+            line["next_rows"].update(next_rows_swin_knn(torch, dev, s, ev0, ev1))
+        except Exception as ex:
+            line.setdefault("next_rows", {})["swin_gather"] = {"unavailable": repr(ex)[:200]}
 
     # ---- baseline legs (rank 0, N=1 only): reference CUDA on the same box, CPU port on the host cores ----
     if n_gpus == 1 and not args.skip_baselines:
@@ -598,6 +602,97 @@ def run_b200_arm(args):
     print(json.dumps(line), flush=True)
     if n_gpus > 1:
         dist.destroy_process_group()
+
+
+def next_rows_swin_knn(torch, dev, s, ev0, ev1):
+    """SURVEY.md 8 f2 / f3 at BASELINE.json config 5's shape (300K Gaussians alive per frame) and at the bench's 3M points."""
+    import torch.nn.functional as F
+    from diff_gaussian_rasterization import swin
+    from simple_knn._C import distCUDA2
+    out = {}
+
+    def timeit(fn, iters=10):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        ev0.record()
+        for _ in range(iters):
+            fn()
+        ev1.record()
+        torch.cuda.synchronize()
+        return ev0.elapsed_time(ev1) / iters
+
+    g = torch.Generator(device="cpu").manual_seed(9)
+
+    def mk(N):
+        t = {"xyz": torch.randn((N, 3), generator=g), "rotation": torch.randn((N, 4), generator=g), "features_dc": torch.randn((N, 1, 3), generator=g),
+             "features_rest": torch.randn((N, 15, 3), generator=g) * 0.1, "opacity": torch.randn((N, 1), generator=g),
+             "scaling": torch.randn((N, 3), generator=g) - 3, "rigid_v": torch.randn((N, 3), generator=g) * 0.05,
+             "rigid_rotvec": torch.randn((N, 3), generator=g) * 0.3, "rigid_rotcen": torch.randn((N, 3), generator=g),
+             "frame_start": torch.randint(0, 30, (N,), generator=g).float()}
+        return {k: v.to(dev) for k, v in t.items()}
+    imm, mat, frame = mk(400_000), mk(400_000), 11.0
+    for k in swin.SET_KEYS[:9]:
+        imm[k].requires_grad_(True)
+    ii = torch.nonzero(imm["frame_start"] <= frame, as_tuple=True)[0]
+    mi = torch.nonzero(mat["frame_start"] <= frame, as_tuple=True)[0]
+    K = int(ii.numel() + mi.numel())
+    ups = [torch.randn(sh_, device=dev) for sh_ in ((K, 3), (K, 4), (K, 16, 3), (K, 1), (K, 3))]
+    params = [imm[k] for k in swin.SET_KEYS[:9]]
+
+    def fused():
+        r = swin.gather_active(frame, imm, mat, ii, mi, deform=True)
+        torch.autograd.grad(sum((r[k] * u).sum() for k, u in zip(("xyz", "rotation", "feature", "opacity", "scaling"), ups)), params)
+
+    def rotvec2quat(rv):
+        ang = torch.norm(rv, dim=1, keepdim=True)
+        u = F.normalize(rv)
+        q = torch.zeros((rv.shape[0], 4), device=rv.device)
+        q[:, 0] = torch.cos(ang / 2).squeeze(-1)
+        q[:, 1:] = u * torch.sin(ang / 2)
+        return q
+
+    def rotvec2mat(rv):
+        ang = torch.norm(rv, dim=1, keepdim=True)
+        u = F.normalize(rv)
+        Kx = torch.zeros((rv.shape[0], 3, 3), device=rv.device)
+        Kx[:, 0, 1], Kx[:, 0, 2], Kx[:, 1, 0], Kx[:, 1, 2], Kx[:, 2, 0], Kx[:, 2, 1] = -u[:, 2], u[:, 1], u[:, 2], -u[:, 0], -u[:, 1], u[:, 0]
+        eye = torch.eye(3, device=rv.device).unsqueeze(0).repeat(rv.shape[0], 1, 1)
+        return eye + torch.sin(ang).unsqueeze(-1) * Kx + (1 - torch.cos(ang).unsqueeze(-1)) * torch.bmm(Kx, Kx)
+
+    def quat_mul(a, b):
+        w1, x1, y1, z1 = a[:, 0], a[:, 1], a[:, 2], a[:, 3]
+        w2, x2, y2, z2 = b[:, 0], b[:, 1], b[:, 2], b[:, 3]
+        return torch.stack((w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2, w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2,
+                            w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2, w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2), dim=1)
+
+    def torch_ops():   # scene/gaussian_model.py:598-649 + utils/tempo_utils.py:4-84, op for op
+        cat = lambda k: torch.cat((imm[k][ii], mat[k][mi]), dim=0)  # noqa: E731
+        age = torch.cat((frame - imm["frame_start"][ii], frame - mat["frame_start"][mi]), dim=0).unsqueeze(-1)
+        rot, pos, v, rvec, cen = cat("rotation"), cat("xyz"), cat("rigid_v"), cat("rigid_rotvec"), cat("rigid_rotcen")
+        rv = rvec * age
+        xyz = torch.bmm(rotvec2mat(rv), (pos - cen).unsqueeze(-1)).squeeze(-1)
+        xyz = xyz + cen + v * age
+        r = {"xyz": xyz, "rotation": F.normalize(quat_mul(rotvec2quat(rv), rot)),
+             "feature": torch.cat((torch.cat((imm["features_dc"][ii], imm["features_rest"][ii]), dim=1),
+                                   torch.cat((mat["features_dc"][mi], mat["features_rest"][mi]), dim=1)), dim=0),
+             "opacity": torch.sigmoid(cat("opacity")), "scaling": torch.exp(cat("scaling"))}
+        torch.autograd.grad(sum((r[k] * u).sum() for k, u in zip(("xyz", "rotation", "feature", "opacity", "scaling"), ups)), params)
+
+    fused_ms, torch_ms = timeit(fused), timeit(torch_ops)
+    out["swin_gather"] = {"ms_fwd_bwd": round(fused_ms, 4), "torch_ops_ms_fwd_bwd": round(torch_ms, 4), "active": K,
+                          "what": "get_basic_para_at(frame) for 2 x 400K stored Gaussians (immature + matured), forward + backward: fused kernels "
+                                  "(csrc/swin.cu) vs the reference's op sequence (scene/gaussian_model.py:598-649, utils/tempo_utils.py)"}
+    pts = s["means3D"]
+    knn_ms = timeit(lambda: distCUDA2(pts), iters=3)
+    out["distCUDA2"] = {"ms": round(knn_ms, 3), "points": int(pts.shape[0])}
+    try:
+        from oracle import ref_cuda
+        if ref_cuda.knn_available():
+            out["distCUDA2"]["reference_simple_knn_ms"] = round(timeit(lambda: ref_cuda.knn(pts), iters=2), 3)
+    except Exception:
+        pass
+    return out
 
 
 def run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_gpus, rank, K, Wm, bg, exchange, barrier, ev0, ev1):
