@@ -14,7 +14,7 @@ import pytest
 from oracle import oracle
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-SCENES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLD, "*.npz")) if "relocation" not in p and "loss_ssim" not in p)
+SCENES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLD, "*.npz")) if os.path.basename(p).startswith(("cube_", "garden_")))
 
 
 def load(name):
