@@ -23,6 +23,53 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
 
+def train_replica_check(args, C, dp, s, cam_t, dev, rank, world, P, W, H):
+    """Every rank holds a replica of the raw parameters and of the Adam state, renders a different view per step, and
+    applies the summed gradients: after K steps the replicas must agree bit for bit."""
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, add_noise
+    from diff_gaussian_rasterization import loss as fused_loss
+    from diff_gaussian_rasterization.activations import activate
+    from diff_gaussian_rasterization.optim import FusedAdam
+    raw = {"xyz": s["means3D"].clone(), "shs": s["shs"].clone(), "opacity": torch.logit(s["opacities"].clamp(1e-4, 1 - 1e-4)),
+           "scaling": torch.log(s["scales"]), "rotation": s["rotations"].clone()}
+    raw = {k: torch.nn.Parameter(v) for k, v in raw.items()}
+    lrs = {"xyz": 1.6e-4, "shs": 2.5e-3, "opacity": 0.05, "scaling": 5e-3, "rotation": 1e-3}
+    opt = FusedAdam([{"params": [raw[k]], "lr": lrs[k], "name": k} for k in raw], lr=0.0, eps=1e-15)
+    vp = dp.ViewParallelRasterizer(P, 16, dev)
+    bg = torch.zeros(3, device=dev)
+    gts = [torch.rand((3, H, W), generator=torch.Generator().manual_seed(500 + v)).to(dev) for v in range(len(cam_t))]
+    losses = []
+    for step in range(args.train_steps):
+        view = (step * world + rank) % len(cam_t)
+        c = cam_t[view]
+        cv = torch.stack([cam_t[(step * world + r) % len(cam_t)]["campos"] for r in range(world)])
+        settings = GaussianRasterizationSettings(H, W, c["tanfovx"], c["tanfovy"], bg, 1.0, c["viewmatrix"], c["projmatrix"], 3,
+                                                 c["campos"], False, False)
+        opacity, scaling, rotation, reg = activate(raw["opacity"], raw["scaling"], raw["rotation"], 0.01, 0.01)
+        means2D = torch.zeros_like(raw["xyz"], requires_grad=True)
+        image = vp(settings, cv, raw["xyz"], means2D, opacity, raw["shs"], scaling, rotation)[0]
+        loss = fused_loss.photometric_loss(image, gts[view], 0.2) / world + reg
+        loss.backward()
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        with torch.no_grad():
+            add_noise(raw["xyz"], raw["scaling"], raw["rotation"], raw["opacity"], 5e5 * lrs["xyz"], seed=7, offset=step)
+        losses.append(float(loss.item()))
+    torch.cuda.synchronize()
+    ident, moved = {}, {}
+    start = {"xyz": s["means3D"], "shs": s["shs"], "rotation": s["rotations"]}
+    for k, p_ in raw.items():
+        bits = p_.detach().contiguous().view(torch.int32).long().flatten()
+        h = torch.stack([bits.sum(), (bits * (torch.arange(bits.numel(), device=dev) % 1000003 + 1)).sum()])
+        hs = [torch.zeros_like(h) for _ in range(world)]
+        dist.all_gather(hs, h)
+        ident[k] = all(bool((x == hs[0]).all()) for x in hs)
+        if k in start:
+            moved[k] = float((p_.detach() - start[k]).abs().max())
+    return {"steps": args.train_steps, "identical_on_all_ranks": ident, "max_abs_change": moved, "transport": vp.exchange.transport,
+            "rank0_losses": losses}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--P", type=int, default=300000)
@@ -31,6 +78,9 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--transports", default="nccl,symm,symm-p2p")
     ap.add_argument("--breakdown", action="store_true")
+    ap.add_argument("--train-steps", type=int, default=0,
+                    help="also run this many full training iterations (activations, render, loss, exchange, Adam, noise) and "
+                         "check that the replicated parameters stay bit-identical on all ranks")
     args = ap.parse_args()
     import gs_synth
     from diff_gaussian_rasterization import _native as C, dp
@@ -139,6 +189,8 @@ def main():
             del ex
         except Exception as ex_:  # report, keep going with the next transport
             out[f"factored_{transport}"] = {"error": repr(ex_)[:400]}
+    if args.train_steps > 0:
+        out["train_replicas"] = train_replica_check(args, C, dp, s, cam_t, dev, rank, world, P, W, H)
     if rank == 0:
         print(json.dumps(out), flush=True)
     dist.barrier()
