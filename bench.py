@@ -48,6 +48,9 @@ def parse():
                     help="N > 1: gradient exchange. factored = all-gather masked dL/dRGB + rebuild the SH gradient + all-reduce "
                          "11 floats per Gaussian (dp.FactoredExchange); allreduce = NCCL all-reduce of the 59-float arena")
     ap.add_argument("--transport", default="auto", choices=["auto", "symm", "nccl"])
+    ap.add_argument("--train-step-leg", action="store_true",
+                    help="N > 1: also time the full training iteration (informational; on by default at N = 1 only, so that "
+                         "nothing after the two contract measurements can stall a multi-rank run)")
     return ap.parse_args()
 
 
@@ -496,6 +499,8 @@ def run_b200_arm(args):
     #      torch ops for loss / optimizer / noise around the same rasterizer (N = 1 only). ----
     train_step = None
     try:
+        if n_gpus > 1 and not args.train_step_leg:
+            raise RuntimeError("skipped at N > 1 (pass --train-step-leg); 8-GPU figure: profiles/r1_bench_3M_1080p_v16_n8.json")
         train_step = run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_gpus, rank, K, min(Wm, 3), bg,
                                         exchange if factored else None, barrier, ev0, ev1)
     except Exception as ex:
