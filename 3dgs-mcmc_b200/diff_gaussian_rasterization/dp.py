@@ -85,18 +85,23 @@ class FactoredExchange:
 
     SLAB_FIELDS = (("means3D", 3), ("opacity", 1), ("scales", 3), ("rotations", 4))
 
-    def __init__(self, P, M, device, group=None, transport="auto", multicast=None):
-        """multicast: None = use the NVSwitch multicast mapping when the symmetric allocation has one and world > 2
+    def __init__(self, P, M, device, group=None, transport="auto", multicast=None, capacity=None):
+        """capacity: number of Gaussians the (symmetric) buffers are sized for, >= P; the MCMC trainer grows the model
+        by 5 % every densification step up to cap_max (gaussian_model_static.py:460-492) - allocate once for cap_max and
+        call resize(P) after each growth instead of a new rendezvous.
+        multicast: None = use the NVSwitch multicast mapping when the symmetric allocation has one and world > 2
         (measured on 8xB200 at P = 3M: 2.73 ms backward+exchange with multicast against 2.94 ms with peer pointers at
         world 8, but 2.32 against 2.12 ms at world 2); True / False force it."""
         self.P, self.M = int(P), int(M)
+        self.capacity = int(capacity) if capacity is not None else self.P
+        if self.capacity < self.P:
+            raise ValueError(f"capacity {self.capacity} < P {self.P}")
         self.device = torch.device(device)
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if self.world > 1 else 0
-        self.slot_stride = _round_up(3 * self.P, 64)
-        slab_floats = _round_up(11 * self.P, 64)
-        self._n_slab = slab_floats
+        self.slot_stride = _round_up(3 * self.capacity, 64)      # fixed: slot r of the gather buffer starts at r * slot_stride
+        slab_floats = _round_up(11 * self.capacity, 64)
         total = slab_floats + self.world * self.slot_stride
         self.transport = self._pick_transport(transport)
         self._hdl = None
@@ -119,17 +124,29 @@ class FactoredExchange:
             self.flat = torch.zeros(total, dtype=torch.float32, device=self.device)
             self._multicast = False
             self._send = torch.zeros(self.slot_stride, dtype=torch.float32, device=self.device)
-        self.slab = self.flat[:slab_floats]
+        self._slab_capacity = slab_floats
         self.gathered = self.flat[slab_floats:].view(self.world, self.slot_stride)
+        self.resize(self.P)
+
+    def resize(self, P):
+        """Re-slice the buffers for P <= capacity Gaussians (no allocation of symmetric memory, no rendezvous). Every rank
+        must call it with the same P before the next backward."""
+        P = int(P)
+        if P > self.capacity:
+            raise ValueError(f"P {P} exceeds the capacity {self.capacity} this exchange was allocated for")
+        self.P = P
+        self._n_slab = _round_up(11 * P, 64)                      # the all-reduced prefix of the slab
+        self.slab = self.flat[: self._n_slab]
         self.grads = {}
         off = 0
         for name, w in self.SLAB_FIELDS:
-            self.grads[name] = self.slab[off: off + self.P * w].view(self.P, w)
-            off += self.P * w
-        self.grads["sh"] = torch.zeros((self.P, self.M, 3), dtype=torch.float32, device=self.device)
-        self.local = {"means2D": torch.empty((self.P, 3), dtype=torch.float32, device=self.device),
-                      "colors": torch.empty((self.P, 3), dtype=torch.float32, device=self.device),
-                      "cov3D": torch.empty((self.P, 6), dtype=torch.float32, device=self.device)}
+            self.grads[name] = self.flat[off: off + P * w].view(P, w)
+            off += P * w
+        self.grads["sh"] = torch.zeros((P, self.M, 3), dtype=torch.float32, device=self.device)
+        self.local = {"means2D": torch.empty((P, 3), dtype=torch.float32, device=self.device),
+                      "colors": torch.empty((P, 3), dtype=torch.float32, device=self.device),
+                      "cov3D": torch.empty((P, 6), dtype=torch.float32, device=self.device)}
+        return self
 
     def _setup_symmetric(self, total, slab_floats, group, multicast):
         import torch.distributed._symmetric_memory as symm_mem
@@ -277,9 +294,14 @@ class ViewParallelRasterizer(torch.nn.Module):
     """GaussianRasterizer for view-sharded training: construct once per model size, call once per step with this
     rank's settings and the camera positions of all ranks' views (rank order)."""
 
-    def __init__(self, P, M, device, group=None, transport="auto"):
+    def __init__(self, P, M, device, group=None, transport="auto", capacity=None):
         super().__init__()
-        self.exchange = FactoredExchange(P, M, device, group=group, transport=transport)
+        self.exchange = FactoredExchange(P, M, device, group=group, transport=transport, capacity=capacity)
+
+    def resize(self, P):
+        """After the model grew (add_new_gs): same buffers, P <= capacity Gaussians."""
+        self.exchange.resize(P)
+        return self
 
     def forward(self, raster_settings, campos_views, means3D, means2D, opacities, shs, scales, rotations):
         return _RasterizeGaussiansViewParallel.apply(means3D, means2D, shs, opacities, scales, rotations,

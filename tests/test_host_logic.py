@@ -76,6 +76,21 @@ def test_gradient_arena_layout():
     assert a.all_reduce() is a.flat                # no process group: no-op
 
 
+def test_factored_exchange_capacity_and_resize():
+    ex = dp.FactoredExchange(10, 4, "cpu", capacity=24)
+    assert ex.world == 1 and ex.P == 10 and ex.slot_stride >= 3 * 24
+    ptr = ex.flat.data_ptr()
+    ex.resize(17)
+    assert ex.flat.data_ptr() == ptr                      # same buffer, new views
+    assert ex.grads["means3D"].shape == (17, 3) and ex.grads["rotations"].shape == (17, 4) and ex.grads["sh"].shape == (17, 4, 3)
+    assert ex.grads["rotations"].data_ptr() == ptr + 4 * 17 * 7
+    assert ex._n_slab % 64 == 0 and ex._n_slab >= 11 * 17
+    with pytest.raises(ValueError):
+        ex.resize(25)
+    with pytest.raises(ValueError):
+        dp.FactoredExchange(10, 4, "cpu", capacity=5)
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))

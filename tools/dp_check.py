@@ -35,7 +35,8 @@ def train_replica_check(args, C, dp, s, cam_t, dev, rank, world, P, W, H):
     raw = {k: torch.nn.Parameter(v) for k, v in raw.items()}
     lrs = {"xyz": 1.6e-4, "shs": 2.5e-3, "opacity": 0.05, "scaling": 5e-3, "rotation": 1e-3}
     opt = FusedAdam([{"params": [raw[k]], "lr": lrs[k], "name": k} for k in raw], lr=0.0, eps=1e-15)
-    vp = dp.ViewParallelRasterizer(P, 16, dev)
+    vp = dp.ViewParallelRasterizer(P - 1000, 16, dev, capacity=P + 64)   # allocated for the cap, then grown: no new rendezvous
+    vp.resize(P)
     bg = torch.zeros(3, device=dev)
     gts = [torch.rand((3, H, W), generator=torch.Generator().manual_seed(500 + v)).to(dev) for v in range(len(cam_t))]
     losses = []
