@@ -7,6 +7,8 @@ exchange step named in BASELINE.json's north_star. The backward kernel writes it
 contiguous FP32 arena, so a single NCCL all-reduce (708 MB at 3M Gaussians) covers them; forward and render
 backward need no communication.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -104,6 +106,12 @@ class FactoredExchange:
         slab_floats = _round_up(11 * self.capacity, 64)
         total = slab_floats + self.world * self.slot_stride
         self.transport = self._pick_transport(transport)
+        # "classic": slab all-reduce beside the SH rebuild (default). "early_reduce": slab all-reduce while the gather is
+        # still in flight, SH rebuild alone afterwards - measured equal within noise on 8xB200 at P = 3M (2.67 vs 2.66 ms
+        # backward + exchange): the reduce then competes with the gather for NVLink ingress.
+        self.schedule = os.environ.get("GS_DP_SCHEDULE", "classic")
+        if self.schedule not in ("early_reduce", "classic"):
+            raise ValueError(f"GS_DP_SCHEDULE must be early_reduce or classic, got {self.schedule!r}")
         self._hdl = None
         if self.transport == "symm":
             try:
@@ -211,29 +219,39 @@ class FactoredExchange:
         """Stage 2 (after the per-Gaussian backward wrote the slab): sum the slab over the ranks and rebuild the summed
         SH gradient from the gathered colour gradients."""
         reduce_work = None
-        if self.world > 1:
-            if self.transport == "symm":
-                torch.cuda.current_stream(self.device).wait_event(self._ev_push)
-                self._hdl.barrier(channel=0)             # every rank's pushes and slab are written
-                # the slab all-reduce (NVLink bound) runs beside the SH rebuild (HBM bound)
-                main = torch.cuda.current_stream(self.device)
-                self._ev_fork.record(main)
-                self._side.wait_event(self._ev_fork)
-                with torch.cuda.stream(self._side):
-                    native.dp_slab_all_reduce(self.device, self._slab_ptrs, self._n_slab, self.rank, self.world,
-                                              self._multicast)
-                    self._ev_join.record(self._side)
-            else:
-                reduce_work = dist.all_reduce(self.slab, group=self.group, async_op=True)
-                pending.wait()
+        symm = self.world > 1 and self.transport == "symm"
+        if symm and self.schedule == "early_reduce":
+            # The slab is complete as soon as the per-Gaussian kernel ends, long before the gather (its NVLink ingress takes
+            # ~2x as long as that kernel at world 8): reduce the slab while the gather is still in flight, then rebuild
+            # the SH gradient with all SMs to itself.
+            main = torch.cuda.current_stream(self.device)
+            self._hdl.barrier(channel=0)                 # every rank's slab is written
+            native.dp_slab_all_reduce(self.device, self._slab_ptrs, self._n_slab, self.rank, self.world, self._multicast)
+            main.wait_event(self._ev_push)
+            self._hdl.barrier(channel=1)                 # every rank's pushes have landed; all slab slices too
+        elif symm:
+            torch.cuda.current_stream(self.device).wait_event(self._ev_push)
+            self._hdl.barrier(channel=0)                 # every rank's pushes and slab are written
+            # the slab all-reduce (NVLink bound) runs beside the SH rebuild (HBM bound)
+            main = torch.cuda.current_stream(self.device)
+            self._ev_fork.record(main)
+            self._side.wait_event(self._ev_fork)
+            with torch.cuda.stream(self._side):
+                native.dp_slab_all_reduce(self.device, self._slab_ptrs, self._n_slab, self.rank, self.world,
+                                          self._multicast)
+                self._ev_join.record(self._side)
+        elif self.world > 1:
+            reduce_work = dist.all_reduce(self.slab, group=self.group, async_op=True)
+            pending.wait()
         sh_grad = native.dp_sh_grad_combine(means3D, campos_views, self.gathered, self.slot_stride, degree, self.M,
                                             out=self.grads["sh"] if sh_out is None else sh_out)
-        if self.world > 1:
-            if self.transport == "symm":
-                torch.cuda.current_stream(self.device).wait_event(self._ev_join)
-                self._hdl.barrier(channel=1)             # all slices landed; peers are done reading this rank's buffers
-            else:
-                reduce_work.wait()
+        if symm and self.schedule == "early_reduce":
+            self._hdl.barrier(channel=2)                 # peers are done reading this rank's gather slots
+        elif symm:
+            torch.cuda.current_stream(self.device).wait_event(self._ev_join)
+            self._hdl.barrier(channel=1)                 # all slices landed; peers are done reading this rank's buffers
+        elif self.world > 1:
+            reduce_work.wait()
         if sh_out is not None:
             return dict(self.grads, sh=sh_grad)
         return self.grads
