@@ -192,6 +192,23 @@ __global__ void __launch_bounds__(kCombineThreads) sh_grad_combine_kernel(int P,
             }
         }
     }
+    // ---- rows out ----
+    if (kCoef == 16 && Mrow == 48 && (reinterpret_cast<size_t>(dL_dsh) & 15) == 0) {
+        // degree 3, M = 16 (the training configuration): each thread stores its own 192-byte row with twelve 16-byte
+        // stores. A warp instruction then covers 32 half-sectors; L2 merges the halves before they reach DRAM, and the
+        // kernel is instruction bound (77 % issue-slot utilisation with the shared-memory staging, which costs ~400
+        // instructions per warp against 12 here).
+        if (valid) {
+            float4* dst = reinterpret_cast<float4*>(dL_dsh + i * 48);
+#pragma unroll
+            for (int q = 0; q < 12; ++q) {
+                const int b0 = 4 * q;
+                dst[q] = make_float4(acc[b0 < 3 * kCoef ? b0 : 0], acc[b0 + 1 < 3 * kCoef ? b0 + 1 : 0], acc[b0 + 2 < 3 * kCoef ? b0 + 2 : 0],
+                                     acc[b0 + 3 < 3 * kCoef ? b0 + 3 : 0]);
+            }
+        }
+        return;
+    }
     const uint32_t row_mask = __ballot_sync(0xffffffffu, any);
     float* tile = &s_rows[warp][0];
     if (any) {
