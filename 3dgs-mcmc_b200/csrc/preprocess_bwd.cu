@@ -27,8 +27,10 @@ GS_DEV void store3(float* __restrict__ dst, size_t idx, float a, float b, float 
 // SH backward: returns dL/dmean through the view direction and writes dL_dsh for coefficients [0, (deg+1)^2).
 // `sh` and `dL_dsh` may be the same shared-memory row (see the kernel): every read of `sh` happens before the
 // first write of `dL_dsh`.
+// basis_out (optional, 16 floats) receives the basis values and dL_dRGB_out the clamp-masked colour gradient, for callers
+// that store the rows themselves; dL_dsh may then be null.
 GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* sh, uint8_t clamp_bits, V3 dL_dRGB,
-                          float* dL_dsh) {
+                          float* dL_dsh, float* basis_out = nullptr, V3* dL_dRGB_out = nullptr) {
     const V3 dir_orig = pos - campos;
     const V3 dir = dir_orig / sqrt(dot3(dir_orig, dir_orig));
     auto C = [&](int k) { return V3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]); };
@@ -67,10 +69,15 @@ GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* s
     const float3 dL_ddir = {dot3(dRGBdx, dL_dRGB), dot3(dRGBdy, dL_dRGB), dot3(dRGBdz, dL_dRGB)};
     const float3 dmean = dnormvdv3(float3{dir_orig.x, dir_orig.y, dir_orig.z}, dL_ddir);
     // ---- phase 2: dL/dsh[k] = basis_k(dir) * dL/dRGB ----
+    if (dL_dRGB_out) *dL_dRGB_out = dL_dRGB;
     auto W = [&](int k, float basis) {
-        dL_dsh[3 * k] = basis * dL_dRGB.x;
-        dL_dsh[3 * k + 1] = basis * dL_dRGB.y;
-        dL_dsh[3 * k + 2] = basis * dL_dRGB.z;
+        if (basis_out) {
+            basis_out[k] = basis;
+        } else {
+            dL_dsh[3 * k] = basis * dL_dRGB.x;
+            dL_dsh[3 * k + 1] = basis * dL_dRGB.y;
+            dL_dsh[3 * k + 2] = basis * dL_dRGB.z;
+        }
     };
     W(0, kSH0);
     if (deg > 0) {
@@ -267,13 +274,22 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
     }
     cp_async_wait_all();
     __syncwarp();
+    // Degree-3-sized rows (M = 16, the training layout): the thread stores its own 192-byte gradient row with twelve
+    // 16-byte stores straight from registers (basis x colour gradient), no shared-memory round trip: the kernel is
+    // co-limited by instruction issue, and the staging costs ~400 instructions per warp against ~40 here.
+    const bool direct_rows = staged && write_dsh && Mrow == 48 && (reinterpret_cast<size_t>(p.dL_dsh) & 15) == 0;
+    float basis[16];
+    V3 g_rgb(0.f, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) basis[k] = 0.f;
     if (visible) {
         const float3 mean = {p.means3D[3 * i], p.means3D[3 * i + 1], p.means3D[3 * i + 2]};
         // ---- colour -> SH and view direction ----
         if (p.shs) {
             const V3 campos(p.campos[0], p.campos[1], p.campos[2]);
             const float3 dsh_mean = sh_backward(p.D, V3(mean.x, mean.y, mean.z), campos, my_sh,
-                                                p.clamped[idx], V3(acc0.x, acc0.y, acc0.z), my_dsh);
+                                                p.clamped[idx], V3(acc0.x, acc0.y, acc0.z), my_dsh,
+                                                direct_rows ? basis : nullptr, direct_rows ? &g_rgb : nullptr);
             dmean.x += dsh_mean.x;
             dmean.y += dsh_mean.y;
             dmean.z += dsh_mean.z;
@@ -293,7 +309,22 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
         store3(p.dL_dscales, i, dscale[0], dscale[1], dscale[2]);
         reinterpret_cast<float4*>(p.dL_drots)[idx] = drot;
     }
-    if (staged) {
+    if (direct_rows) {
+        if (valid) {
+            const float gc[3] = {g_rgb.x, g_rgb.y, g_rgb.z};
+            float4* dst = reinterpret_cast<float4*>(p.dL_dsh + i * 48);
+#pragma unroll
+            for (int q = 0; q < 12; ++q) {
+                float v[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int f = 4 * q + j;
+                    v[j] = basis[f / 3] * gc[f % 3];      // basis is zero above the active degree and for culled Gaussians
+                }
+                dst[q] = make_float4(v[0], v[1], v[2], v[3]);
+            }
+        }
+    } else if (staged) {
         // ---- SH gradient rows out: coalesced, zeros for culled Gaussians and unused coefficients ----
         __syncwarp();
         if (rows_valid > 0 && write_dsh) {
