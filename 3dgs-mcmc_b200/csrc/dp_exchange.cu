@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(kCombineThreads) sh_grad_combine_kernel(int P,
                 any = true;
                 const V3 cam(campos[3 * v], campos[3 * v + 1], campos[3 * v + 2]);
                 const V3 dir_orig = pos - cam;
-                const V3 dir = dir_orig / sqrt(dot3(dir_orig, dir_orig));
+                const V3 dir = dir_orig / sqrt(norm2_fixed(dir_orig));
                 float b[16];
                 sh_basis(kDeg, dir.x, dir.y, dir.z, b);
 #pragma unroll

@@ -58,6 +58,10 @@ GS_DEV V3 operator*(float s, const V3& v) { return V3(s * v.x, s * v.y, s * v.z)
 GS_DEV V3 operator*(const V3& v, float s) { return V3(v.x * s, v.y * s, v.z * s); }
 GS_DEV V3 operator/(const V3& v, float s) { return V3(v.x / s, v.y / s, v.z / s); }
 GS_DEV float dot3(const V3& a, const V3& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+// |v|^2 with the contraction nvcc gives dot3(v, v) in a straight-line context (y*y, then x and z fused), spelled out:
+// the view direction must come out bit-identical in every kernel that rebuilds an SH basis from it (preprocess
+// backward, dp_exchange's sh_grad_combine), and the compiler's own contraction depends on block placement.
+GS_DEV float norm2_fixed(const V3& v) { return __fmaf_rn(v.z, v.z, __fmaf_rn(v.x, v.x, __fmul_rn(v.y, v.y))); }
 
 // Column-major 3x3: c[j] is column j, c[j][i] is row i of column j.
 struct M3 {

@@ -58,12 +58,29 @@ GS_DEV float3 cov2d_ewa(const float3& mean, float focal_x, float focal_y, float 
 // Evaluate SH colour. `sh` points at this Gaussian's [M][3] block.
 // Not inlined on purpose: bit-exact parity of the colours depends on which multiplies the compiler contracts
 // into FMAs, and that choice must not drift with edits to the caller.
+// kVec: sh is the thread's row in the 16-byte staged tile (sh_stage.cuh); it is pulled into registers with twelve
+// LDS.128 (chunks above the active degree hold stale shared memory and are never used).
+template <bool kVec>
 __device__ __noinline__ V3 sh_to_rgb(int deg, const V3 pos, const V3 campos, const float* __restrict__ sh, uint8_t& clamp_bits) {
     V3 dir = pos - campos;
     dir = dir / sqrt(dot3(dir, dir));
-    auto C = [&](int k) { return V3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]); };
+    float c48[kVec ? 48 : 1];
+    if (kVec) {
+#pragma unroll
+        for (int q = 0; q < 12; ++q) {
+            const float4 t = reinterpret_cast<const float4*>(sh)[q];
+            c48[kVec ? 4 * q : 0] = t.x; c48[kVec ? 4 * q + 1 : 0] = t.y; c48[kVec ? 4 * q + 2 : 0] = t.z; c48[kVec ? 4 * q + 3 : 0] = t.w;
+        }
+    }
+    auto C = [&](int k) {
+        return kVec ? V3(c48[kVec ? 3 * k : 0], c48[kVec ? 3 * k + 1 : 0], c48[kVec ? 3 * k + 2 : 0])
+                    : V3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]);
+    };
 
-    V3 result = kSH0 * C(0);
+    // explicitly rounded: with the row in registers the compiler duplicates this product into the degree > 0 path, where
+    // ptxas would fuse it with the subtraction that follows (the reference's build keeps a plain multiply here)
+    const V3 c0 = C(0);
+    V3 result(__fmul_rn(kSH0, c0.x), __fmul_rn(kSH0, c0.y), __fmul_rn(kSH0, c0.z));
     if (deg > 0) {
         const float x = dir.x, y = dir.y, z = dir.z;
         result = result - kSH1 * y * C(1) + kSH1 * z * C(2) - kSH1 * x * C(3);
@@ -98,7 +115,7 @@ constexpr int kPfThreads = 128;
 // would touch 32 different lines per load instruction (the reference's access pattern, forward.cu:29).
 // Every per-Gaussian output is written (defaults for culled ones, replacing three host-side fills).
 __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const PreprocessParams p) {
-    __shared__ float s_sh[kPfThreads / 32][32 * (kShMaxRow + 1)];
+    __shared__ __align__(16) float s_sh[kPfThreads / 32][kShTileFloats];
     __shared__ uint32_t s_tiles;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -134,9 +151,12 @@ __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const Prepro
     const uint32_t alive_mask = __ballot_sync(0xffffffffu, alive);
     float* tile = &s_sh[warp][0];
     const int ncoef3 = 3 * (p.D + 1) * (p.D + 1);
+    // degree-3-sized rows on a 16-byte aligned base (the training layout) move as 16-byte chunks
+    const bool rows16 = staged && Mrow == 48 && (reinterpret_cast<size_t>(p.shs) & 15) == 0;
     if (staged && alive_mask) {
         float* src = const_cast<float*>(p.shs) + (size_t)warp_first * Mrow;
-        if (Mrow == 48) stage_sh_rows<true, 48>(tile, row_stride, src, Mrow, rows_valid, alive_mask, ncoef3, lane);
+        if (rows16) stage_sh_rows16_load(reinterpret_cast<float4*>(tile), src, rows_valid, alive_mask, ncoef3, lane);
+        else if (Mrow == 48) stage_sh_rows<true, 48>(tile, row_stride, src, Mrow, rows_valid, alive_mask, ncoef3, lane);
         else stage_sh_rows<true, 0>(tile, row_stride, src, Mrow, rows_valid, alive_mask, ncoef3, lane);
     }
 
@@ -192,8 +212,13 @@ __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const Prepro
         if (use_sh) {
             uint8_t cb;
             const V3 campos(p.campos[0], p.campos[1], p.campos[2]);
-            const float* my_sh = staged ? tile + lane * row_stride : p.shs + i * Mrow;
-            const V3 c = sh_to_rgb(p.D, V3(p_orig.x, p_orig.y, p_orig.z), campos, my_sh, cb);
+            V3 c;
+            if (rows16) {
+                c = sh_to_rgb<true>(p.D, V3(p_orig.x, p_orig.y, p_orig.z), campos, tile + lane * (4 * kShPitch4), cb);
+            } else {
+                const float* my_sh = staged ? tile + lane * row_stride : p.shs + i * Mrow;
+                c = sh_to_rgb<false>(p.D, V3(p_orig.x, p_orig.y, p_orig.z), campos, my_sh, cb);
+            }
             p.rgb[3 * i + 0] = c.x;
             p.rgb[3 * i + 1] = c.y;
             p.rgb[3 * i + 2] = c.z;

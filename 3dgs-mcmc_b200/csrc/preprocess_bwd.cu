@@ -24,16 +24,22 @@ GS_DEV void store3(float* __restrict__ dst, size_t idx, float a, float b, float 
     dst[3 * idx + 2] = c;
 }
 
-// SH backward: returns dL/dmean through the view direction and writes dL_dsh for coefficients [0, (deg+1)^2).
-// `sh` and `dL_dsh` may be the same shared-memory row (see the kernel): every read of `sh` happens before the
-// first write of `dL_dsh`.
-// basis_out (optional, 16 floats) receives the basis values and dL_dRGB_out the clamp-masked colour gradient, for callers
-// that store the rows themselves; dL_dsh may then be null.
+// SH backward: returns dL/dmean through the view direction; basis_out[k] receives basis_k(dir) for k < (deg+1)^2 and
+// dL_dRGB_out the clamp-masked colour gradient: dL/dsh[k][ch] = basis_out[k] * dL_dRGB_out[ch], stored by the caller.
+// kVec: sh is the thread's row in the 16-byte staged tile (sh_stage.cuh), read with LDS.128; otherwise a row of floats in
+// shared or global memory. |dir|^2 is spelled out (norm2_fixed): with two inlined instantiations the compiler merges their
+// common prologue across blocks and its own FMA contraction of the dot product is lost.
+template <bool kVec>
 GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* sh, uint8_t clamp_bits, V3 dL_dRGB,
-                          float* dL_dsh, float* basis_out = nullptr, V3* dL_dRGB_out = nullptr) {
+                          float (&basis_out)[16], V3& dL_dRGB_out) {
     const V3 dir_orig = pos - campos;
-    const V3 dir = dir_orig / sqrt(dot3(dir_orig, dir_orig));
-    auto C = [&](int k) { return V3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]); };
+    const V3 dir = dir_orig / sqrt(norm2_fixed(dir_orig));
+    float c48[kVec ? 48 : 1];
+    if (kVec) sh_row_to_regs(reinterpret_cast<const float4*>(sh), 0, c48);
+    auto C = [&](int k) {
+        return kVec ? V3(c48[kVec ? 3 * k : 0], c48[kVec ? 3 * k + 1 : 0], c48[kVec ? 3 * k + 2 : 0])
+                    : V3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]);
+    };
     // Clamped channels pass no gradient.
     dL_dRGB.x *= (clamp_bits & 1) ? 0.f : 1.f;
     dL_dRGB.y *= (clamp_bits & 2) ? 0.f : 1.f;
@@ -69,16 +75,8 @@ GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* s
     const float3 dL_ddir = {dot3(dRGBdx, dL_dRGB), dot3(dRGBdy, dL_dRGB), dot3(dRGBdz, dL_dRGB)};
     const float3 dmean = dnormvdv3(float3{dir_orig.x, dir_orig.y, dir_orig.z}, dL_ddir);
     // ---- phase 2: dL/dsh[k] = basis_k(dir) * dL/dRGB ----
-    if (dL_dRGB_out) *dL_dRGB_out = dL_dRGB;
-    auto W = [&](int k, float basis) {
-        if (basis_out) {
-            basis_out[k] = basis;
-        } else {
-            dL_dsh[3 * k] = basis * dL_dRGB.x;
-            dL_dsh[3 * k + 1] = basis * dL_dRGB.y;
-            dL_dsh[3 * k + 2] = basis * dL_dRGB.z;
-        }
-    };
+    dL_dRGB_out = dL_dRGB;
+    auto W = [&](int k, float basis) { basis_out[k] = basis; };
     W(0, kSH0);
     if (deg > 0) {
         W(1, -kSH1 * y);
@@ -143,7 +141,7 @@ GS_DEV void cov3d_backward(const V3 scale, float mod, const float4 rot, const fl
 constexpr int kPbThreads = 128;
 
 __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PreprocessBwdParams p) {
-    __shared__ float s_sh[kPbThreads / 32][32 * (kShMaxRow + 1)];
+    __shared__ __align__(16) float s_sh[kPbThreads / 32][kShTileFloats];
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool valid = idx < p.P;
@@ -157,9 +155,17 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
     const int rows_valid = min(32, p.P - warp_first);
     const uint32_t vis_mask = __ballot_sync(0xffffffffu, visible);
     float* tile = &s_sh[warp][0];
+    const bool write_dsh = p.dL_dsh != nullptr;   // false: the caller rebuilds dL_dsh from the colour gradients (dp_exchange.cu)
+    const int ncoef = (p.D + 1) * (p.D + 1);
+    // Degree-3-sized rows (M = 16, the training layout) on 16-byte aligned bases move as 16-byte chunks both ways:
+    // cp.async.16 in, LDS.128 into registers, and the gradient rows (basis x masked colour gradient, formed in registers)
+    // parked with STS.128 and streamed out as 512-byte warp stores.
+    const bool rows16 = staged && Mrow == 48 && (reinterpret_cast<size_t>(p.shs) & 15) == 0 &&
+                        (!write_dsh || (reinterpret_cast<size_t>(p.dL_dsh) & 15) == 0);
     if (staged && rows_valid > 0) {
         float* src = const_cast<float*>(p.shs) + (size_t)warp_first * Mrow;
-        if (Mrow == 48) stage_sh_rows<true, 48>(tile, row_stride, src, Mrow, rows_valid, vis_mask, 0, lane);
+        if (rows16) stage_sh_rows16_load(reinterpret_cast<float4*>(tile), src, rows_valid, vis_mask, 3 * ncoef, lane);
+        else if (Mrow == 48) stage_sh_rows<true, 48>(tile, row_stride, src, Mrow, rows_valid, vis_mask, 0, lane);
         else stage_sh_rows<true, 0>(tile, row_stride, src, Mrow, rows_valid, vis_mask, 0, lane);
         // not waited for yet: the covariance / projection part below runs while the rows arrive
     }
@@ -182,8 +188,6 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
     float3 dmean = {0.f, 0.f, 0.f};
     float dscale[3] = {0.f, 0.f, 0.f};
     float4 drot = make_float4(0.f, 0.f, 0.f, 0.f);
-    const int ncoef = (p.D + 1) * (p.D + 1);
-    const bool write_dsh = p.dL_dsh != nullptr;   // false: the caller rebuilds dL_dsh from the colour gradients (dp_exchange.cu)
     float* my_dsh = p.shs ? (staged ? tile + lane * row_stride : (write_dsh ? p.dL_dsh + i * Mrow : nullptr)) : nullptr;
     const float* my_sh = p.shs ? (staged ? tile + lane * row_stride : p.shs + i * Mrow) : nullptr;
 
@@ -274,10 +278,6 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
     }
     cp_async_wait_all();
     __syncwarp();
-    // Degree-3-sized rows (M = 16, the training layout): the thread stores its own 192-byte gradient row with twelve
-    // 16-byte stores straight from registers (basis x colour gradient), no shared-memory round trip: the kernel is
-    // co-limited by instruction issue, and the staging costs ~400 instructions per warp against ~40 here.
-    const bool direct_rows = staged && write_dsh && Mrow == 48 && (reinterpret_cast<size_t>(p.dL_dsh) & 15) == 0;
     float basis[16];
     V3 g_rgb(0.f, 0.f, 0.f);
 #pragma unroll
@@ -287,9 +287,22 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
         // ---- colour -> SH and view direction ----
         if (p.shs) {
             const V3 campos(p.campos[0], p.campos[1], p.campos[2]);
-            const float3 dsh_mean = sh_backward(p.D, V3(mean.x, mean.y, mean.z), campos, my_sh,
-                                                p.clamped[idx], V3(acc0.x, acc0.y, acc0.z), my_dsh,
-                                                direct_rows ? basis : nullptr, direct_rows ? &g_rgb : nullptr);
+            const float3 dsh_mean =
+                rows16 ? sh_backward<true>(p.D, V3(mean.x, mean.y, mean.z), campos, tile + lane * (4 * kShPitch4), p.clamped[idx],
+                                           V3(acc0.x, acc0.y, acc0.z), basis, g_rgb)
+                       : sh_backward<false>(p.D, V3(mean.x, mean.y, mean.z), campos, my_sh, p.clamped[idx],
+                                            V3(acc0.x, acc0.y, acc0.z), basis, g_rgb);
+            if (!rows16 && my_dsh) {
+                // every read of the row (shared tile or memory) is above: the gradient row may now overwrite it
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    if (k < ncoef) {
+                        my_dsh[3 * k] = basis[k] * g_rgb.x;
+                        my_dsh[3 * k + 1] = basis[k] * g_rgb.y;
+                        my_dsh[3 * k + 2] = basis[k] * g_rgb.z;
+                    }
+                }
+            }
             dmean.x += dsh_mean.x;
             dmean.y += dsh_mean.y;
             dmean.z += dsh_mean.z;
@@ -309,10 +322,10 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
         store3(p.dL_dscales, i, dscale[0], dscale[1], dscale[2]);
         reinterpret_cast<float4*>(p.dL_drots)[idx] = drot;
     }
-    if (direct_rows) {
-        if (valid) {
+    if (rows16) {
+        if (write_dsh) {
+            float4* tile4 = reinterpret_cast<float4*>(tile);
             const float gc[3] = {g_rgb.x, g_rgb.y, g_rgb.z};
-            float4* dst = reinterpret_cast<float4*>(p.dL_dsh + i * 48);
 #pragma unroll
             for (int q = 0; q < 12; ++q) {
                 float v[4];
@@ -321,8 +334,10 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
                     const int f = 4 * q + j;
                     v[j] = basis[f / 3] * gc[f % 3];      // basis is zero above the active degree and for culled Gaussians
                 }
-                dst[q] = make_float4(v[0], v[1], v[2], v[3]);
+                tile4[lane * kShPitch4 + q] = make_float4(v[0], v[1], v[2], v[3]);
             }
+            __syncwarp();
+            if (rows_valid > 0) stage_sh_rows16_store(tile4, p.dL_dsh + (size_t)warp_first * 48, rows_valid, lane);
         }
     } else if (staged) {
         // ---- SH gradient rows out: coalesced, zeros for culled Gaussians and unused coefficients ----

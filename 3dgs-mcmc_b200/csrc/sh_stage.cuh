@@ -54,4 +54,50 @@ GS_DEV void stage_sh_rows(float* tile, int row_stride, float* gmem /* first row 
     }
 }
 
+// ---- 16-byte variant for degree-3-sized rows (48 floats = twelve 16-byte chunks, row base 16-byte aligned) ----
+// Tile layout [32][kShPitch4] float4: the 208-byte pitch makes a thread's STS.128 / LDS.128 on its own row conflict
+// free (13 r + q is distinct mod 8 over any 8 consecutive lanes) while the warp-wide sweeps move twelve fully
+// coalesced 512-byte lines instead of forty-eight 128-byte ones: a quarter of the copy instructions and index math.
+constexpr int kShPitch4 = 13;
+constexpr int kShTileFloats = 32 * 4 * kShPitch4;   // per warp; also covers the scalar layout (32 x 49)
+
+// Starts the copies of the rows in row_mask (only the chunks holding the first ncoef3 floats); the caller waits with
+// cp_async_wait_all() + __syncwarp() before reading.
+GS_DEV void stage_sh_rows16_load(float4* tile4, const float* gmem /* first row of the warp */, int rows_valid,
+                                 uint32_t row_mask, int ncoef3, int lane) {
+    const int nchunk = (ncoef3 + 3) >> 2;
+    const float4* src = reinterpret_cast<const float4*>(gmem);
+#pragma unroll
+    for (int it = 0; it < 12; ++it) {
+        const int c = it * 32 + lane;
+        const int r = c / 12, q = c - 12 * r;
+        if (r < rows_valid && ((row_mask >> r) & 1u) && q < nchunk)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(tile4 + r * kShPitch4 + q)), "l"(src + c)
+                         : "memory");
+    }
+}
+
+// The thread's own row into registers (every index static, so the array never touches local memory).
+GS_DEV void sh_row_to_regs(const float4* tile4, int lane, float* c48) {
+#pragma unroll
+    for (int q = 0; q < 12; ++q) {
+        const float4 t = tile4[lane * kShPitch4 + q];
+        c48[4 * q] = t.x; c48[4 * q + 1] = t.y; c48[4 * q + 2] = t.z; c48[4 * q + 3] = t.w;
+    }
+}
+
+// Rows parked by their threads (tile4[lane * kShPitch4 + q]) streamed out as coalesced 512-byte warp stores.
+GS_DEV void stage_sh_rows16_store(const float4* tile4, float* gmem /* first row of the warp */, int rows_valid, int lane) {
+    float4* dst = reinterpret_cast<float4*>(gmem);
+    const int chunks = rows_valid * 12;
+#pragma unroll
+    for (int it = 0; it < 12; ++it) {
+        const int c = it * 32 + lane;
+        if (c < chunks) {
+            const int r = c / 12;
+            __stcs(dst + c, tile4[r * kShPitch4 + (c - 12 * r)]);
+        }
+    }
+}
+
 }  // namespace gs
