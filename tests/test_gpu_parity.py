@@ -266,6 +266,47 @@ def test_non_default_stream_and_determinism():
     assert a[0] == b[0] and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]) and torch.equal(a[6], b[6])
 
 
+@pytest.mark.parametrize("degree", [3, 1])
+def test_sh_rows_4_byte_staging_matches_16_byte_staging(degree):
+    """Degree-3-sized SH rows (M = 16) on a 16-byte aligned base move as 16-byte chunks (csrc/sh_stage.cuh); any other
+    base takes the 4-byte staging. The same scene through both: image, colours and dL/dsh bit-identical (the bases are
+    formed by the same expressions), the other gradients to rounding. P is ragged (last warp has one row)."""
+    C = native()
+    scene, cam = helpers.make_case("cube", 20001, 250, 130, seed=5)
+    scene["scales"] = (scene["scales"] * 2).astype(np.float32)
+    s, c = helpers.torch_inputs(scene, cam, dev())
+    flat = torch.empty(s["shs"].numel() + 1, dtype=torch.float32, device=dev())
+    shifted = flat[1:].view_as(s["shs"])
+    shifted.copy_(s["shs"])
+    assert s["shs"].data_ptr() % 16 == 0 and shifted.data_ptr() % 16 == 4 and shifted.is_contiguous()
+    g = torch.Generator(device="cpu").manual_seed(3)
+    H, W = c["image_height"], c["image_width"]
+    dL = torch.randn((3, H, W), generator=g).to(dev())
+    e = torch.empty(0)
+    fwd = [C.rasterize_gaussians(*helpers.native_forward_args(dict(s, shs=shs), c, degree)) for shs in (s["shs"], shifted)]
+    (Ra, ca, ra, geom, binning, img, _), (Rb, cb, rb, geom_b, binning_b, img_b, _) = fwd
+    P = ra.numel()
+    assert Ra == Rb and Ra > 0 and torch.equal(ra, rb)
+    rgba = C.debug_fetch(6, P, Ra, W, H, geom, binning, img, torch.float32).view(-1, 3)[ra > 0]
+    rgbb = C.debug_fetch(6, P, Rb, W, H, geom_b, binning_b, img_b, torch.float32).view(-1, 3)[rb > 0]
+    assert helpers.bits_equal_count(rgba, rgbb) == 0 and helpers.bits_equal_count(ca, cb) == 0
+    # one tile backward (its float atomics reorder sums from run to run), then the per-Gaussian backward through both
+    # stagings on the same accumulators
+    scratch = C.backward_render(c["bg"], P, Ra, dL, geom, binning, img)
+    ga, gb = (dict(zip(GRAD_NAMES, C.backward_geometry(s["means3D"], ra, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"],
+                                                       c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, shs, degree,
+                                                       c["campos"], geom, scratch))) for shs in (s["shs"], shifted))
+    torch.cuda.synchronize()
+    assert float(ga["sh"].abs().max()) > 0
+    assert helpers.bits_equal_count(ga["sh"] + 0.0, gb["sh"] + 0.0) == 0
+    first_unused = 3 * (degree + 1) ** 2
+    if first_unused < 48:
+        assert float(ga["sh"].view(-1, 48)[:, first_unused:].abs().max()) == 0.0
+        assert float(gb["sh"].view(-1, 48)[:, first_unused:].abs().max()) == 0.0
+    for n in GRAD_NAMES:
+        assert helpers.rel_l2(ga[n], gb[n]) < 1e-6, (n, helpers.rel_l2(ga[n], gb[n]))
+
+
 # --------------------------------------------------------------------------------------------------------------------
 # golden vectors (from the reference) and the CPU oracle
 # --------------------------------------------------------------------------------------------------------------------
