@@ -501,6 +501,14 @@ __global__ void __launch_bounds__(256) block_bounds_kernel(int P, const uint32_t
 // t / w and t % w for t < 65536 * w... in practice t < number of tiles <= 65536: the float product is at least
 // 0.5 / w away from an integer, far above its rounding error.
 GS_DEV uint32_t div_small(uint32_t t, uint32_t w, float rw) { (void)w; return (uint32_t)(((float)t + 0.5f) * rw); }
+// 1 / w for div_small by one MUFU.RCP. (t + 0.5) / w is at least 0.5 / w away from an integer, a relative margin of
+// 0.5 / (t + 0.5) > 7.6e-6 for t < 65536 (the fast path's tile-count limit); rcp.approx (1 ulp) and the two roundings of
+// div_small add up to < 3e-7, so the truncation is exact. __frcp_rn costs ~20 instructions and a branch per slot.
+GS_DEV float rcp_small(uint32_t w) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"((float)w));
+    return r;
+}
 
 // hist[d][b] = number of slots of block b whose tile id has low digit d, from the rectangles alone.
 __global__ void __launch_bounds__(kBinThreads) bin_count1_kernel(const uint4* __restrict__ emit, const uint32_t* __restrict__ block_first,
@@ -523,7 +531,7 @@ __global__ void __launch_bounds__(kBinThreads) bin_count1_kernel(const uint4* __
         const uint32_t w = E.z & 0xffffu, h = E.z >> 16, x0 = E.y & 0xffffu, y0 = E.y >> 16;
         // clip the Gaussian's slots [E.w, E.w + w h) to the block: local positions [ta, tb)
         const uint32_t ta = max(slot_begin, E.w) - E.w, tb = min(slot_end, E.w + w * h) - E.w;
-        const float rw = __frcp_rn((float)w);
+        const float rw = rcp_small(w);
         const uint32_t ya = div_small(ta, w, rw), yb = div_small(tb - 1, w, rw);
         const uint32_t xa = ta - ya * w, xb = tb - 1 - yb * w + 1;
         for (uint32_t y = ya; y <= yb; ++y) {
@@ -711,7 +719,7 @@ __global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinSc
             if (e < tile_n) {
                 const uint4 E = __ldg(p.emit + r0 + s_owner[e]);
                 const uint32_t t = slot_begin + e - E.w, w = E.z & 0xffffu;
-                const uint32_t ty = div_small(t, w, __frcp_rn((float)w));
+                const uint32_t ty = div_small(t, w, rcp_small(w));
                 const uint32_t tx = t - ty * w;
                 const uint32_t tl = ((E.y >> 16) + ty) * p.grid_x + (E.y & 0xffffu) + tx;
                 key[i] = ((uint64_t)tl << 32) | E.x;
