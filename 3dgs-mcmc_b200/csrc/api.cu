@@ -65,7 +65,7 @@ inline void count_launches(int k) { g_prof.launches += (unsigned long long)k; }
 
 extern "C" {
 
-int gs_abi_version(void) { return 103; }
+int gs_abi_version(void) { return 104; }
 
 const char* gs_error_string(int code) {
     if (code == GS_OK) return "ok";
@@ -462,6 +462,29 @@ int gs_photometric_loss_backward(void* stream_, int C, int H, int W, const float
     p.dL_dimg = dL_dimage;
     prof_mark(stream, -1);
     rc = launch_loss_backward(p, c_l1, c_ssim, grad_scale, stream);
+    prof_mark(stream, ST_LOSS_BWD);
+    count_launches(1);
+    return rc;
+}
+
+size_t gs_l1_workspace_bytes(size_t n) { return align_up(2 * sizeof(float) * (size_t)l1_block_count(n), kAlign) + kAlign; }
+
+int gs_l1_loss_forward(void* stream_, size_t n, const float* x, const float* y, void* ws, float* out_mean) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (n == 0 || !x || !y || !ws || !out_mean) return GS_ERR_ARG;
+    float* partial = reinterpret_cast<float*>(align_up(reinterpret_cast<size_t>(ws), kAlign));
+    prof_mark(stream, -1);
+    const int rc = launch_l1_forward(n, x, y, partial, out_mean, stream);
+    prof_mark(stream, ST_LOSS_FWD);
+    count_launches(2);
+    return rc;
+}
+
+int gs_l1_loss_backward(void* stream_, size_t n, const float* x, const float* y, const float* grad_scale, float* dL_dx) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (n == 0 || !x || !y || !dL_dx) return GS_ERR_ARG;
+    prof_mark(stream, -1);
+    const int rc = launch_l1_backward(n, x, y, grad_scale, dL_dx, stream);
     prof_mark(stream, ST_LOSS_BWD);
     count_launches(1);
     return rc;

@@ -189,6 +189,9 @@ int launch_loss_forward(const LossParams& p, float* out_means, cudaStream_t stre
 int launch_loss_backward(const LossParams& p, float c_l1, float c_ssim, const float* grad_scale, cudaStream_t stream);
 size_t loss_partial_count(int C, int H, int W);
 int launch_pair_reduce(const float* partial, int n, double inv_a, double inv_b, float* out, cudaStream_t stream);
+int l1_block_count(size_t n);
+int launch_l1_forward(size_t n, const float* x, const float* y, float* partial, float* out_mean, cudaStream_t stream);
+int launch_l1_backward(size_t n, const float* x, const float* y, const float* grad_scale, float* dL_dx, cudaStream_t stream);
 int launch_activate_fwd(int P, const float* raw_o, const float* raw_s, const float* raw_q, float* o, float* s, float* q,
                         float* partial, float* out_means, cudaStream_t stream);
 int launch_activate_bwd(int P, const float* raw_o, const float* raw_s, const float* raw_q, const float* g_o, const float* g_s,

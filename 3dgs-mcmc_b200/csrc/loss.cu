@@ -256,4 +256,97 @@ size_t loss_partial_count(int C, int H, int W) {
     return (size_t)((W + kLossTile - 1) / kLossTile) * ((H + kLossTile - 1) / kLossTile) * C;
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Plain L1 (utils/loss_utils.py:21-22: torch.abs(network_output - gt).mean()) for callers that use it without the SSIM
+// term: one streaming pass + the fixed-order reduction above forward, one streaming pass backward
+// (grad * sign(x - y) / n, sign(0) = 0 as torch's abs backward), instead of torch's ~8 elementwise / reduction launches.
+// ------------------------------------------------------------------------------------------------------------------
+constexpr int kL1Threads = 256;
+constexpr int kL1Chunk = kL1Threads * 16;   // floats per block iteration (four float4 per thread)
+constexpr int kL1MaxBlocks = 2048;
+
+int l1_block_count(size_t n) {
+    const size_t chunks = (n + kL1Chunk - 1) / kL1Chunk;
+    return (int)(chunks < (size_t)kL1MaxBlocks ? (chunks ? chunks : 1) : (size_t)kL1MaxBlocks);
+}
+
+template <bool kVec>
+__global__ void __launch_bounds__(kL1Threads) l1_fwd_kernel(size_t n, const float* __restrict__ x, const float* __restrict__ y,
+                                                            float* __restrict__ partial) {
+    __shared__ float s_w[kL1Threads / 32];
+    float acc = 0.f;
+    // block b takes chunks b, b + gridDim.x, ...: the assignment, and so the summation order, is fixed
+    for (size_t base = (size_t)blockIdx.x * kL1Chunk; base < n; base += (size_t)gridDim.x * kL1Chunk) {
+        if (kVec && base + kL1Chunk <= n) {
+            float4 a[4], b[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const size_t e = base / 4 + (size_t)k * kL1Threads + threadIdx.x;
+                a[k] = __ldcs(reinterpret_cast<const float4*>(x) + e);
+                b[k] = __ldcs(reinterpret_cast<const float4*>(y) + e);
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                acc += (fabsf(a[k].x - b[k].x) + fabsf(a[k].y - b[k].y)) + (fabsf(a[k].z - b[k].z) + fabsf(a[k].w - b[k].w));
+        } else {
+            const size_t end = base + kL1Chunk < n ? base + kL1Chunk : n;
+            for (size_t e = base + threadIdx.x; e < end; e += kL1Threads) acc += fabsf(x[e] - y[e]);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < kL1Threads / 32; ++w) t += s_w[w];
+        partial[2 * blockIdx.x] = t;
+        partial[2 * blockIdx.x + 1] = 0.f;
+    }
+}
+
+GS_DEV float l1_sign(float d) { return d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f); }
+
+template <bool kVec>
+__global__ void __launch_bounds__(kL1Threads) l1_bwd_kernel(size_t n, const float* __restrict__ x, const float* __restrict__ y,
+                                                            const float* __restrict__ grad_scale, float inv_n,
+                                                            float* __restrict__ dL_dx) {
+    const float g = (grad_scale ? __ldg(grad_scale) : 1.f) * inv_n;
+    const size_t base = (size_t)blockIdx.x * kL1Chunk;
+    if (kVec && base + kL1Chunk <= n) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const size_t e = base / 4 + (size_t)k * kL1Threads + threadIdx.x;
+            const float4 a = __ldcs(reinterpret_cast<const float4*>(x) + e);
+            const float4 b = __ldcs(reinterpret_cast<const float4*>(y) + e);
+            reinterpret_cast<float4*>(dL_dx)[e] =
+                make_float4(g * l1_sign(a.x - b.x), g * l1_sign(a.y - b.y), g * l1_sign(a.z - b.z), g * l1_sign(a.w - b.w));
+        }
+    } else {
+        const size_t end = base + kL1Chunk < n ? base + kL1Chunk : n;
+        for (size_t e = base + threadIdx.x; e < end; e += kL1Threads) dL_dx[e] = g * l1_sign(x[e] - y[e]);
+    }
+}
+
+int launch_l1_forward(size_t n, const float* x, const float* y, float* partial, float* out_mean, cudaStream_t stream) {
+    const int nb = l1_block_count(n);
+    const bool vec = ((reinterpret_cast<size_t>(x) | reinterpret_cast<size_t>(y)) & 15) == 0;
+    if (vec) l1_fwd_kernel<true><<<nb, kL1Threads, 0, stream>>>(n, x, y, partial);
+    else l1_fwd_kernel<false><<<nb, kL1Threads, 0, stream>>>(n, x, y, partial);
+    GS_LAUNCH_CHECK();
+    return launch_pair_reduce(partial, nb, 1.0 / (double)n, 0.0, out_mean, stream);
+}
+
+int launch_l1_backward(size_t n, const float* x, const float* y, const float* grad_scale, float* dL_dx, cudaStream_t stream) {
+    const size_t chunks = (n + kL1Chunk - 1) / kL1Chunk;
+    if (chunks > 0x7fffffffull) return GS_ERR_ARG;
+    const bool vec = ((reinterpret_cast<size_t>(x) | reinterpret_cast<size_t>(y) | reinterpret_cast<size_t>(dL_dx)) & 15) == 0;
+    const float inv_n = (float)(1.0 / (double)n);
+    if (vec) l1_bwd_kernel<true><<<(unsigned)chunks, kL1Threads, 0, stream>>>(n, x, y, grad_scale, inv_n, dL_dx);
+    else l1_bwd_kernel<false><<<(unsigned)chunks, kL1Threads, 0, stream>>>(n, x, y, grad_scale, inv_n, dL_dx);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
 }  // namespace gs

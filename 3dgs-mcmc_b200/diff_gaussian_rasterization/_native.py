@@ -52,6 +52,9 @@ SIGNATURES = {
     "gs_photometric_loss_forward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int] + [_c_void_p] * 4),
     "gs_photometric_loss_backward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int] + [_c_void_p] * 3 + [_c_float, _c_float]
                                      + [_c_void_p] * 2),
+    "gs_l1_workspace_bytes": (_c_size_t, [_c_size_t]),
+    "gs_l1_loss_forward": (_c_int, [_c_void_p, _c_size_t] + [_c_void_p] * 4),
+    "gs_l1_loss_backward": (_c_int, [_c_void_p, _c_size_t] + [_c_void_p] * 4),
     "gs_activation_workspace_bytes": (_c_size_t, [_c_int]),
     "gs_activate_forward": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 8),
     "gs_activate_backward": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 6 + [_c_float, _c_float] + [_c_void_p] * 4),
@@ -477,6 +480,38 @@ def photometric_loss_backward(image, gt, ws, c_l1, c_ssim, grad_scale=None):
                                                  float(c_l1), float(c_ssim), _ptr(grad_scale), out.data_ptr()),
                "gs_photometric_loss_backward")
     return out.view(shape)
+
+
+def l1_loss_forward(x, y):
+    """Device float[2] whose element 0 is mean |x - y| (gs_l1_loss_forward); x, y: CUDA tensors of one shape."""
+    device = x.device
+    if not x.is_cuda:
+        raise RuntimeError("network_output must be a CUDA tensor (no CPU path exists)")
+    x, y = _f32_cuda(x, "network_output", device), _f32_cuda(y, "gt", device)
+    if x.shape != y.shape:
+        raise RuntimeError(f"network_output {tuple(x.shape)} and gt {tuple(y.shape)} differ in shape")
+    n = int(x.numel())
+    if n == 0:
+        raise RuntimeError("l1_loss of empty tensors")
+    with torch.cuda.device(device):
+        ws = torch.empty(_lib.gs_l1_workspace_bytes(n), dtype=torch.uint8, device=device)
+        means = torch.empty(2, dtype=torch.float32, device=device)
+        _check(_lib.gs_l1_loss_forward(_stream(device), n, x.data_ptr(), y.data_ptr(), ws.data_ptr(), means.data_ptr()),
+               "gs_l1_loss_forward")
+    return means
+
+
+def l1_loss_backward(x, y, grad_scale=None):
+    """grad_scale * sign(x - y) / numel (gs_l1_loss_backward), shaped like x."""
+    device = x.device
+    x, y = _f32_cuda(x, "network_output", device), _f32_cuda(y, "gt", device)
+    if grad_scale is not None:
+        grad_scale = _f32_cuda(grad_scale.reshape(1), "grad_scale", device)
+    with torch.cuda.device(device):
+        out = torch.empty_like(x)
+        _check(_lib.gs_l1_loss_backward(_stream(device), int(x.numel()), x.data_ptr(), y.data_ptr(), _ptr(grad_scale),
+                                        out.data_ptr()), "gs_l1_loss_backward")
+    return out
 
 
 def activate_forward(raw_opacity, raw_scaling, raw_rotation):

@@ -201,6 +201,7 @@ def run_b200_arm(args):
     import gs_synth
     from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, _native as C
     from diff_gaussian_rasterization import dp
+    from diff_gaussian_rasterization.loss import l1_loss
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -449,7 +450,7 @@ def run_b200_arm(args):
                 means3D=params["means3D"], means2D=means2D, shs=params["shs"], opacities=params["opacities"],
                 scales=params["scales"], rotations=params["rotations"])
         torch.cuda.current_stream().wait_event(gt_ready[slot])
-        loss = (image - gt_dev[slot]).abs().mean()
+        loss = l1_loss(image, gt_dev[slot])                 # the package's l1_loss (utils/loss_utils.py:21-22; csrc/loss.cu)
         loss.backward()
         gt_free[slot].record()
         if n_gpus > 1 and vp_raster is None:
@@ -499,7 +500,7 @@ def run_b200_arm(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
     e2e = {"value": n_gpus * 1000.0 * K / e2e_ms, "unit": "views/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-           "ms_per_step": e2e_ms / K, "api": ("dp.ViewParallelRasterizer" if factored else "GaussianRasterizer") + ".forward + L1 loss + loss.backward()" +
+           "ms_per_step": e2e_ms / K, "api": ("dp.ViewParallelRasterizer" if factored else "GaussianRasterizer") + ".forward + loss.l1_loss + loss.backward()" +
                   ("" if n_gpus == 1 else " with the cross-rank gradient sum inside the backward" if factored else " + all_reduce of the 5 parameter gradients") +
                   "; pinned gt image (copy stream, one step ahead) and camera in, loss out (async D2H into pinned memory, read one step later)"}
 

@@ -178,6 +178,15 @@ int gs_photometric_loss_backward(void* stream, int C, int H, int W, const float*
                                  const void* ws, float c_l1, float c_ssim, const float* grad_scale,
                                  float* dL_dimage);
 
+/* Plain L1 loss (additive): out_mean[0] = mean |x - y| over n floats (utils/loss_utils.py:21-22,
+ * torch.abs(network_output - gt).mean()); out_mean is device float[2] ([1] is written as 0). ws: gs_l1_workspace_bytes(n)
+ * of device scratch for the per-block partial sums, which are added in a fixed order in double. Backward:
+ * dL_dx = *grad_scale (device scalar, NULL = 1) * sign(x - y) / n, sign(0) = 0 as torch's abs backward. */
+size_t gs_l1_workspace_bytes(size_t n);
+int gs_l1_loss_forward(void* stream, size_t n, const float* x, const float* y, void* ws, float* out_mean);
+int gs_l1_loss_backward(void* stream, size_t n, const float* x, const float* y, const float* grad_scale,
+                        float* dL_dx);
+
 /* Fused parameter activations + regularisers (additive): opacity = sigmoid(raw), scaling = exp(raw),
  * rotation = raw / max(|raw|, 1e-12) (scene/gaussian_model_static.py:43-56, :126-146) in one pass, which also writes
  * out_means[2] (device) = { mean |opacity|, mean |scaling| }, the two regulariser terms of train_static.py:99-100.

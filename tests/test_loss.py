@@ -136,3 +136,48 @@ def test_fused_loss_full_size_1080p_vs_torch_and_properties():
     # linearity of the backward in the upstream gradient
     (g2,) = torch.autograd.grad(2.0 * loss.photometric_loss(img, gt, 0.2), img)
     assert helpers.rel_l2(g2, 2.0 * gm) < 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,shift", [((3, 1, 1), 0), ((3, 37, 53), 0), ((3, 64, 64), 1), ((3, 1080, 1920), 0), ((5, 4099), 3)])
+def test_fused_l1_loss_vs_oracle_and_torch(shape, shift):
+    """loss.l1_loss = torch.abs(network_output - gt).mean() (utils/loss_utils.py:21-22): value against the float64
+    oracle and torch, gradient against torch's (upstream gradient other than 1; exact zeros where the images agree).
+    shift > 0: tensors on a 4-byte aligned base (scalar path)."""
+    from diff_gaussian_rasterization import loss
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(len(shape) + shape[-1])
+    n = int(np.prod(shape))
+
+    def place(t):
+        flat = torch.empty(n + shift, device=dev)
+        v = flat[shift:].view(shape)
+        v.copy_(t)
+        return v
+
+    gt_h = torch.rand(shape, generator=g)
+    img_h = (gt_h + 0.1 * torch.randn(shape, generator=g)).clamp(0, 1)
+    img_h.view(-1)[::7] = gt_h.view(-1)[::7]                      # exact ties: sign(0) = 0
+    gt, img = place(gt_h), place(img_h)
+    assert shift == 0 or img.data_ptr() % 16 != 0
+    x = img.detach().requires_grad_(True)
+    L = loss.l1_loss(x, gt)
+    (gx,) = torch.autograd.grad(2.5 * L, x)
+    xr = img.detach().clone().requires_grad_(True)
+    Lr = torch.abs(xr - gt).mean()
+    (gr,) = torch.autograd.grad(2.5 * Lr, xr)
+    want = float(np.abs(img_h.double().numpy() - gt_h.double().numpy()).mean())
+    assert abs(L.item() - want) < 1e-6 * max(want, 1e-3)
+    assert abs(L.item() - Lr.item()) < VAL_TOL
+    assert helpers.rel_l2(gx, gr) < 1e-6
+    assert bool((gx.view(-1)[::7] == 0).all())
+    assert loss.l1_loss(x, gt).item() == L.item()                 # fixed summation order
+    if len(shape) == 3:
+        # the L1 term of the fused photometric loss is the same quantity
+        assert abs(loss.photometric_loss(x.detach().contiguous(), gt.contiguous(), 0.0).item() - L.item()) < VAL_TOL
+
+
+def test_l1_loss_rejects_cpu_tensors():
+    from diff_gaussian_rasterization import loss
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        loss.l1_loss(torch.zeros(3, 4, 4), torch.zeros(3, 4, 4))
