@@ -264,6 +264,15 @@ def _win_conv(a, w):
     return out
 
 
+def l1_loss(network_output, gt):
+    """utils/loss_utils.py:21-22, torch.abs(network_output - gt).mean(), in float64 numpy. Returns dict(l1, grad): grad is
+    sign(network_output - gt) / n with sign(0) = 0, torch's derivative of abs().mean()."""
+    x = np.asarray(network_output, np.float64)
+    y = np.asarray(gt, np.float64)
+    d = x - y
+    return {"l1": float(np.abs(d).mean()), "grad": np.sign(d) / d.size}
+
+
 def photometric_loss(img, gt, lambda_dssim=0.2):
     """The training loss of train_static.py:94-97 in float64 numpy:
     (1 - lambda) * l1_loss(img, gt) + lambda * (1 - ssim(img, gt)), l1_loss / ssim as utils/loss_utils.py:21-22, :40-67

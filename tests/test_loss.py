@@ -166,8 +166,9 @@ def test_fused_l1_loss_vs_oracle_and_torch(shape, shift):
     xr = img.detach().clone().requires_grad_(True)
     Lr = torch.abs(xr - gt).mean()
     (gr,) = torch.autograd.grad(2.5 * Lr, xr)
-    want = float(np.abs(img_h.double().numpy() - gt_h.double().numpy()).mean())
-    assert abs(L.item() - want) < 1e-6 * max(want, 1e-3)
+    want = oracle.l1_loss(img_h.numpy(), gt_h.numpy())
+    assert abs(L.item() - want["l1"]) < 1e-6 * max(want["l1"], 1e-3)
+    assert _rel(gx.cpu().numpy() / 2.5, want["grad"]) < 1e-6
     assert abs(L.item() - Lr.item()) < VAL_TOL
     assert helpers.rel_l2(gx, gr) < 1e-6
     assert bool((gx.view(-1)[::7] == 0).all())
@@ -175,6 +176,19 @@ def test_fused_l1_loss_vs_oracle_and_torch(shape, shift):
     if len(shape) == 3:
         # the L1 term of the fused photometric loss is the same quantity
         assert abs(loss.photometric_loss(x.detach().contiguous(), gt.contiguous(), 0.0).item() - L.item()) < VAL_TOL
+
+
+def test_l1_oracle_matches_torch_cpu():
+    g = torch.Generator().manual_seed(11)
+    gt = torch.rand((3, 19, 23), generator=g)
+    img = (gt + 0.1 * torch.randn((3, 19, 23), generator=g)).clamp(0, 1)
+    img.view(-1)[::5] = gt.view(-1)[::5]
+    x = img.double().requires_grad_(True)
+    L = torch.abs(x - gt.double()).mean()
+    (gx,) = torch.autograd.grad(L, x)
+    r = oracle.l1_loss(img.numpy(), gt.numpy())
+    assert abs(r["l1"] - L.item()) < 1e-15
+    assert np.array_equal(r["grad"], gx.numpy())
 
 
 def test_l1_loss_rejects_cpu_tensors():
