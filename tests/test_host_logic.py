@@ -228,3 +228,30 @@ def test_scene_generators_are_deterministic_and_well_formed():
     assert (a["scales"] > 0).all() and (a["opacities"] >= 0.005).all() and (a["opacities"] <= 0.99).all()
     c = gs_synth.scene_cube(1000, seed=1)
     assert np.abs(c["means3D"]).max() <= 1.3
+
+
+def test_binning_workspace_size_classes():
+    """_stable_size rounds the binning workspace up to 1/8-octave steps so that views with slightly different instance
+    counts reuse one cached block (no cudaMalloc inside the training loop): never smaller than asked, at most 12.5 %
+    larger, idempotent, monotone, and small sizes pass through."""
+    from diff_gaussian_rasterization import _native as C
+    prev = 0
+    for n in [0, 1, 4096, (1 << 20), (1 << 20) + 1, 3 << 20, 123456789, 780_000_000, (1 << 33) + 12345]:
+        s = C._stable_size(n)
+        assert s >= n and s <= n + (n >> 3) + 1
+        assert C._stable_size(s) == s
+        assert s >= prev
+        prev = s
+    assert C._stable_size(1000) == 1000
+    # neighbouring instance counts (camera to camera: a few per cent) land in at most two classes
+    base = 32_000_000 * 24
+    classes = {C._stable_size(int(base * (1 + 0.01 * k))) for k in range(6)}
+    assert len(classes) <= 2
+
+
+def test_l1_loss_symbols_and_python_api_exist():
+    from diff_gaussian_rasterization import _native as C, loss
+    for sym in ("gs_l1_workspace_bytes", "gs_l1_loss_forward", "gs_l1_loss_backward"):
+        assert sym in C.SIGNATURES
+    assert callable(loss.l1_loss) and "l1_loss" in loss.__all__
+    assert C._lib.gs_l1_workspace_bytes(1) > 0 and C._lib.gs_l1_workspace_bytes(3 * 1080 * 1920) >= 8 * 1519
