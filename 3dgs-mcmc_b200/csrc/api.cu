@@ -146,6 +146,7 @@ int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means
     pp.focal_x = W / (2.0f * tan_fovx);
     tiles_of(W, H, &pp.grid);
     pp.prefiltered = prefiltered;
+    pp.rot_aligned = is_aligned16(rotations) ? 1 : 0;
     pp.radii = radii; pp.is_used = is_used; pp.means2D = g.means2D; pp.depths = g.depths; pp.cov3D = g.cov3D;
     pp.rgb = g.rgb; pp.conic_opacity = g.conic_opacity; pp.tiles_touched = g.tiles_touched; pp.clamped = g.clamped;
     pp.rec = g.rec; pp.depth_keys = g.dkeys_a; pp.num_rendered = g.num_rendered;
@@ -275,6 +276,8 @@ int gs_backward_geometry(void* stream_, int P, int D, int M, int W, int H, const
     PreprocessBwdParams pb;
     pb.P = P; pb.D = D; pb.M = M; pb.means3D = means3D; pb.radii = radii; pb.shs = shs; pb.clamped = g.clamped;
     pb.scales = cov3D_precomp ? nullptr : scales; pb.rotations = rotations; pb.scale_modifier = scale_modifier;
+    pb.rot_aligned = is_aligned16(rotations) ? 1 : 0;
+    pb.drot_aligned = is_aligned16(dL_drotations) ? 1 : 0;
     pb.cov3D = cov3D_precomp ? cov3D_precomp : g.cov3D;
     pb.viewmatrix = viewmatrix; pb.projmatrix = projmatrix; pb.campos = campos;
     pb.focal_y = H / (2.0f * tan_fovy);

@@ -135,6 +135,18 @@ GS_DEV float3 dnormvdv3(float3 v, float3 dv) {
     return r;
 }
 
+// Quaternion i of a [P][4] array: one 16-byte access when the base is 16-byte aligned, four scalar ones otherwise
+// (a contiguous view with an odd storage offset, or an arena slice at an odd Gaussian count).
+GS_DEV float4 load_quat(const float* __restrict__ q, size_t i, bool aligned) {
+    if (aligned) return reinterpret_cast<const float4*>(q)[i];
+    return make_float4(q[4 * i], q[4 * i + 1], q[4 * i + 2], q[4 * i + 3]);
+}
+GS_DEV void store_quat(float* __restrict__ q, size_t i, bool aligned, const float4 v) {
+    if (aligned) { reinterpret_cast<float4*>(q)[i] = v; return; }
+    q[4 * i] = v.x; q[4 * i + 1] = v.y; q[4 * i + 2] = v.z; q[4 * i + 3] = v.w;
+}
+static inline bool is_aligned16(const void* p) { return (reinterpret_cast<size_t>(p) & 15) == 0; }
+
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 }  // namespace gs

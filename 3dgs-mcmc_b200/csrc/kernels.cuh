@@ -22,6 +22,7 @@ struct PreprocessParams {
     float tan_fovx, tan_fovy, focal_x, focal_y;
     uint2 grid;
     int prefiltered;
+    int rot_aligned;                     // rotations base is 16-byte aligned (float4 loads)
     // outputs
     int* __restrict__ radii;
     int* __restrict__ is_used;
@@ -75,6 +76,7 @@ struct PreprocessBwdParams {
     const float* __restrict__ scales;     // null when cov3D was precomputed
     const float* __restrict__ rotations;
     float scale_modifier;
+    int rot_aligned, drot_aligned;        // rotations / dL_drots bases are 16-byte aligned
     const float* __restrict__ cov3D;      // [6P] (precomputed or from the forward workspace)
     const float* __restrict__ viewmatrix;
     const float* __restrict__ projmatrix;

@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(256) add_noise_kernel(int P, float* __restrict
                                                         const float* __restrict__ rotation_raw,
                                                         const float* __restrict__ opacity_raw,
                                                         const float* __restrict__ noise /* [P,3] or null */, float lr_scale,
-                                                        unsigned long long seed, unsigned long long offset) {
+                                                        unsigned long long seed, unsigned long long offset, bool rot_aligned) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P) return;
     const size_t i = (size_t)idx;
@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(256) add_noise_kernel(int P, float* __restrict
     const float gs_ = gate * lr_scale;
     n.x *= gs_; n.y *= gs_; n.z *= gs_;
 
-    const float4 qr = reinterpret_cast<const float4*>(rotation_raw)[idx];
+    const float4 qr = load_quat(rotation_raw, i, rot_aligned);
     const float norm = sqrtf(qr.x * qr.x + qr.y * qr.y + qr.z * qr.z + qr.w * qr.w);
     const float r = qr.x / norm, x = qr.y / norm, y = qr.z / norm, z = qr.w / norm;
     const float s0 = expf(scaling_raw[3 * i]), s1 = expf(scaling_raw[3 * i + 1]), s2 = expf(scaling_raw[3 * i + 2]);
@@ -136,7 +136,8 @@ int launch_add_noise(int P, float* xyz, const float* scaling_raw, const float* r
                      const float* noise, float lr_scale, unsigned long long seed, unsigned long long offset,
                      cudaStream_t stream) {
     if (P <= 0) return GS_OK;
-    add_noise_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, xyz, scaling_raw, rotation_raw, opacity_raw, noise, lr_scale, seed, offset);
+    add_noise_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, xyz, scaling_raw, rotation_raw, opacity_raw, noise, lr_scale, seed, offset,
+                                                   is_aligned16(rotation_raw));
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const Prepro
             cov3D = p.cov3D_precomp + 6 * i;
         } else {
             const V3 s(p.scales[3 * i], p.scales[3 * i + 1], p.scales[3 * i + 2]);
-            const float4 q = reinterpret_cast<const float4*>(p.rotations)[idx];
+            const float4 q = load_quat(p.rotations, i, p.rot_aligned != 0);
             cov3d_from_scale_rot(s, p.scale_modifier, q, cov_local);
 #pragma unroll
             for (int k = 0; k < 6; ++k) p.cov3D[6 * i + k] = cov_local[k];

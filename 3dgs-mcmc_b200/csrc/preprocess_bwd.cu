@@ -310,7 +310,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
         // ---- 3D covariance -> scale, rotation ----
         if (p.scales) {
             const V3 sc(p.scales[3 * i], p.scales[3 * i + 1], p.scales[3 * i + 2]);
-            const float4 q = reinterpret_cast<const float4*>(p.rotations)[idx];
+            const float4 q = load_quat(p.rotations, i, p.rot_aligned != 0);
             cov3d_backward(sc, p.scale_modifier, q, dcov, dscale, &drot);
         }
     }
@@ -320,7 +320,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
 #pragma unroll
         for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * i + k] = dcov[k];
         store3(p.dL_dscales, i, dscale[0], dscale[1], dscale[2]);
-        reinterpret_cast<float4*>(p.dL_drots)[idx] = drot;
+        store_quat(p.dL_drots, i, p.drot_aligned != 0, drot);
     }
     if (rows16) {
         if (write_dsh) {

@@ -90,8 +90,7 @@ def load_library(path=_LIB_PATH):
 
 
 _lib = load_library()
-_pinned_counts = {}
-_count_events = {}
+_count_pool = {}   # device index -> free _CountSlot objects
 
 
 def _check(rc, what):
@@ -124,24 +123,30 @@ def _stream(device):
     return torch.cuda.current_stream(device).cuda_stream
 
 
-def _pinned_count(device):
-    key = device.index if device.index is not None else torch.cuda.current_device()
-    buf = _pinned_counts.get(key)
-    if buf is None:
-        buf = torch.zeros(1, dtype=torch.int32, pin_memory=True)
-        _pinned_counts[key] = buf
-    return buf
+class _CountSlot:
+    """One pinned host word + one host-visible event: where a forward's instance count lands. Checked out per CALL
+    (not per device), so two forwards in flight on two streams of one device - a prefetching evaluator beside the
+    trainer - can never read each other's count."""
+    __slots__ = ("buf", "event")
 
-
-def _count_event(device):
-    key = device.index if device.index is not None else torch.cuda.current_device()
-    ev = _count_events.get(key)
-    if ev is None:
-        ev = _lib.gs_host_event_create()
-        if not ev:
+    def __init__(self):
+        self.buf = torch.zeros(1, dtype=torch.int32, pin_memory=True)
+        self.event = _lib.gs_host_event_create()
+        if not self.event:
             raise RuntimeError("gs_host_event_create failed")
-        _count_events[key] = ev
-    return ev
+
+
+def _acquire_count_slot(device):
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    pool = _count_pool.setdefault(key, [])
+    try:
+        return key, pool.pop()           # list.pop / append are atomic under the GIL
+    except IndexError:
+        return key, _CountSlot()
+
+
+def _release_count_slot(key, slot):
+    _count_pool[key].append(slot)
 
 
 def _stable_size(nbytes):
@@ -192,8 +197,8 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         is_used = torch.empty((P,), dtype=torch.int32, device=device)
         geom = torch.empty(_lib.gs_geom_bytes(P), **byte_opts)
         img = torch.empty(_lib.gs_image_bytes(W, H), **byte_opts)
-        count = _pinned_count(device)
-        count_ev = _count_event(device)
+        slot_key, slot = _acquire_count_slot(device)
+        count, count_ev = slot.buf, slot.event
 
         _check(_lib.gs_forward_preprocess(
             stream, P, int(degree), M, _ptr(means3D), _ptr(sh), _ptr(colors), _ptr(opacity), _ptr(scales),
@@ -206,6 +211,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         # sort and scan enqueued behind it keep the GPU busy meanwhile.
         _check(_lib.gs_host_event_wait(count_ev), "gs_host_event_wait")
         rendered = int(count[0])
+        _release_count_slot(slot_key, slot)
         if debug:
             _debug_sync("preprocess")
 

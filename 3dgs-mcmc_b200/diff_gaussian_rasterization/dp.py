@@ -13,6 +13,10 @@ import torch
 import torch.distributed as dist
 
 
+def _round_up(n, m):
+    return (n + m - 1) // m * m
+
+
 class GradientArena:
     """Contiguous gradient storage laid out as [means3D | sh | opacity | scales | rotations] blocks."""
 
@@ -21,13 +25,17 @@ class GradientArena:
     def __init__(self, P, M, device):
         self.P, self.M = int(P), int(M)
         widths = [w if w is not None else 3 * self.M for _, w in self.FIELDS]
-        self.flat = torch.zeros(self.P * sum(widths), dtype=torch.float32, device=device)
+        # every field block starts on a 16-byte boundary whatever P is (the kernels' float4 paths; MCMC growth makes P
+        # arbitrary): up to 3 pad floats per block, zero and all-reduced along with the rest
+        starts, off = [], 0
+        for w in widths:
+            starts.append(off)
+            off = _round_up(off + self.P * w, 4)
+        self.flat = torch.zeros(off, dtype=torch.float32, device=device)
         self.views = {}
-        off = 0
-        for (name, _), w in zip(self.FIELDS, widths):
+        for (name, _), w, off in zip(self.FIELDS, widths, starts):
             block = self.flat[off: off + self.P * w]
             self.views[name] = block.view(self.P, self.M, 3) if name == "sh" else block.view(self.P, w)
-            off += self.P * w
         # gradients that are not parameters of the model (not reduced): kept to avoid per-step allocation
         self.local = {"means2D": torch.empty((self.P, 3), dtype=torch.float32, device=device),
                       "colors": torch.empty((self.P, 3), dtype=torch.float32, device=device),
@@ -49,7 +57,7 @@ class GradientArena:
         return self.flat
 
     def floats_per_gaussian(self):
-        return self.flat.numel() // max(self.P, 1)
+        return sum(w if w is not None else 3 * self.M for _, w in self.FIELDS)
 
 
 def shard_views(num_views, rank, world_size):
@@ -60,10 +68,6 @@ def shard_views(num_views, rank, world_size):
 # ----------------------------------------------------------------------------------------------------------------------
 # Factored exchange: all-gather 3 floats + all-reduce 11 floats per Gaussian instead of all-reducing 59
 # ----------------------------------------------------------------------------------------------------------------------
-def _round_up(n, m):
-    return (n + m - 1) // m * m
-
-
 class FactoredExchange:
     """Backward + cross-rank gradient sum for view-sharded training, one camera view per rank.
 
@@ -103,7 +107,7 @@ class FactoredExchange:
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if self.world > 1 else 0
         self.slot_stride = _round_up(3 * self.capacity, 64)      # fixed: slot r of the gather buffer starts at r * slot_stride
-        slab_floats = _round_up(11 * self.capacity, 64)
+        slab_floats = _round_up(11 * self.capacity + 12, 64)      # + the pad that aligns every field block (resize)
         total = slab_floats + self.world * self.slot_stride
         self.transport = self._pick_transport(transport)
         # "classic": slab all-reduce beside the SH rebuild (default). "early_reduce": slab all-reduce while the gather is
@@ -113,6 +117,11 @@ class FactoredExchange:
         if self.schedule not in ("early_reduce", "classic"):
             raise ValueError(f"GS_DP_SCHEDULE must be early_reduce or classic, got {self.schedule!r}")
         self._hdl = None
+        auto = transport == "auto" and self.world > 1
+        if auto:
+            # Every rank takes part in the agreement, whatever it picked locally: a rank whose symmetric-memory import
+            # failed must not skip a collective the others enter. Only if ALL ranks can do "symm" is the rendezvous tried.
+            self.transport = "symm" if self._all_ranks_agree(self.transport == "symm") else "nccl"
         if self.transport == "symm":
             try:
                 self._setup_symmetric(total, slab_floats, group, multicast)
@@ -122,12 +131,9 @@ class FactoredExchange:
                 import warnings
                 warnings.warn(f"FactoredExchange: symmetric memory unavailable ({ex!r}); using torch.distributed collectives")
                 self.transport = "nccl"
-            if transport == "auto":
-                # every rank must take the same path: agree on the weakest
-                ok = torch.tensor([1 if self.transport == "symm" else 0], dtype=torch.int32, device=self.device)
-                dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
-                if int(ok.item()) == 0:
-                    self.transport, self._hdl = "nccl", None
+            if auto and not self._all_ranks_agree(self.transport == "symm"):
+                # the rendezvous failed somewhere: everyone falls back together
+                self.transport, self._hdl = "nccl", None
         if self.transport != "symm":
             self.flat = torch.zeros(total, dtype=torch.float32, device=self.device)
             self._multicast = False
@@ -143,13 +149,13 @@ class FactoredExchange:
         if P > self.capacity:
             raise ValueError(f"P {P} exceeds the capacity {self.capacity} this exchange was allocated for")
         self.P = P
-        self._n_slab = _round_up(11 * P, 64)                      # the all-reduced prefix of the slab
-        self.slab = self.flat[: self._n_slab]
         self.grads = {}
         off = 0
-        for name, w in self.SLAB_FIELDS:
+        for name, w in self.SLAB_FIELDS:                          # every block 16-byte aligned for any P
             self.grads[name] = self.flat[off: off + P * w].view(P, w)
-            off += P * w
+            off = _round_up(off + P * w, 4)
+        self._n_slab = _round_up(off, 64)                         # the all-reduced prefix of the slab
+        self.slab = self.flat[: self._n_slab]
         self.grads["sh"] = torch.zeros((P, self.M, 3), dtype=torch.float32, device=self.device)
         self.local = {"means2D": torch.empty((P, 3), dtype=torch.float32, device=self.device),
                       "colors": torch.empty((P, 3), dtype=torch.float32, device=self.device),
@@ -168,6 +174,12 @@ class FactoredExchange:
         self._slab_ptrs = [int(self._hdl.multicast_ptr)] if self._multicast else [int(p) for p in self._hdl.buffer_ptrs]
         gather_off = 4 * slab_floats
         self._gather_ptrs = [p + gather_off for p in self._slab_ptrs]
+
+    def _all_ranks_agree(self, ok):
+        """MIN over the ranks of a local yes / no; a collective every rank of the group must call."""
+        t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)
+        return int(t.item()) == 1
 
     def _pick_transport(self, transport):
         if transport not in ("auto", "symm", "nccl"):

@@ -137,6 +137,44 @@ def test_factored_exchange_world_1_equals_fused_backward():
         assert helpers.rel_l2(grads[n], fused[n]) < 2e-5, n
 
 
+@pytest.mark.parametrize("P", [30001, 30002, 30003])
+def test_ragged_gaussian_counts_through_arena_and_exchange(P):
+    """MCMC growth makes P arbitrary (int(1.05 * P)). Every field block of GradientArena and of the exchange slab must stay
+    16-byte aligned for any P (the kernels' float4 paths), through resize() as well: same gradients as plain outputs."""
+    from diff_gaussian_rasterization import dp
+    C = native()
+    W, H = 320, 200
+    s, cs, dLs = _views("cube", P, W, H, 1, 3, 4.03, 0.6911)
+    c, dL = cs[0], dLs[0]
+    fwd = _forward(C, s, c, 3)
+    R, _, radii, geom, binning, img, _ = fwd
+    e = torch.empty(0)
+    scratch = C.backward_render(c["bg"], P, R, dL, geom, binning, img)
+    plain = dict(zip(NAMES, C.backward_geometry(s["means3D"], radii, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"],
+                                                c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3, c["campos"],
+                                                geom, scratch)))
+    arena = dp.GradientArena(P, 16, torch.device("cuda:0"))
+    for v in arena.views.values():
+        assert v.data_ptr() % 16 == 0
+    got = dict(zip(NAMES, C.backward_geometry(s["means3D"], radii, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"],
+                                              c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3, c["campos"],
+                                              geom, scratch, out_buffers=arena.backward_buffers())))
+    torch.cuda.synchronize()
+    for n in NAMES:
+        assert helpers.bits_equal_count(got[n] + 0.0, plain[n] + 0.0) == 0, n
+    # the exchange, allocated for a larger cap and resized down to the ragged P (and up again)
+    ex = dp.FactoredExchange(P - 7, 16, torch.device("cuda:0"), capacity=P + 1000)
+    ex.resize(P + 999).resize(P)
+    for v in ex.grads.values():
+        assert v.data_ptr() % 16 == 0 and v.shape[0] == P
+    grads = ex.backward(C, c["bg"], s["means3D"], radii, s["scales"], s["rotations"], 1.0, c["viewmatrix"],
+                        c["projmatrix"], c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"],
+                        c["campos"].view(1, 3), geom, R, binning, img)
+    torch.cuda.synchronize()
+    for n in ("means3D", "sh", "opacity", "scales", "rotations"):
+        assert helpers.rel_l2(grads[n], plain[n]) < 2e-5, n
+
+
 def test_dp_entry_points_reject_bad_arguments():
     C = native()
     dev = torch.device("cuda:0")

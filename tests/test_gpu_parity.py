@@ -58,6 +58,8 @@ def assert_forward_bit_exact(rep):
     ("cube", 20000, 250, 130, 4.03, 0.6911),       # ragged in both directions
     ("cube", 100000, 800, 800, 4.03, 0.6911),      # BASELINE config 1 shape
     ("garden", 300000, 1297, 840, 6.0, 1.2),       # BASELINE config 3 image size
+    ("garden", 3_000_000, 1297, 840, 6.0, 1.2),    # BASELINE config 3 at its cap_max
+    ("garden", 3_000_000, 1920, 1080, 6.0, 1.2),   # the benchmarked headline config, compared directly with the reference
 ])
 def test_forward_bit_exact_and_gradients_vs_reference(kind, P, W, H, rad, fovx):
     ref()
@@ -264,6 +266,86 @@ def test_non_default_stream_and_determinism():
         b = C.rasterize_gaussians(*args)
     st.synchronize()
     assert a[0] == b[0] and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]) and torch.equal(a[6], b[6])
+
+
+def test_concurrent_forwards_on_two_streams_do_not_share_the_count_word():
+    """Two host threads, each with its own stream, run forwards of DIFFERENT scenes at the same time (a prefetching
+    evaluator beside the trainer). Each call's instance count travels through its own pinned word + event
+    (_native._acquire_count_slot), so every result must equal the serial one."""
+    import threading
+    C = native()
+    cases = []
+    for seed, P, mul in ((17, 30000, 3.0), (18, 47000, 1.5)):
+        scene, cam = helpers.make_case("cube", P, 320, 200, seed=seed)
+        scene["scales"] = (scene["scales"] * mul).astype(np.float32)
+        s, c = helpers.torch_inputs(scene, cam, dev())
+        args = helpers.native_forward_args(s, c, 3)
+        want = C.rasterize_gaussians(*args)
+        cases.append((args, want))
+    torch.cuda.synchronize()
+    assert cases[0][1][0] != cases[1][1][0]          # different instance counts: a mix-up would be visible
+    errors = []
+
+    def worker(args, want):
+        try:
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                for _ in range(40):
+                    got = C.rasterize_gaussians(*args)
+                    if got[0] != want[0]:
+                        errors.append(("count", got[0], want[0]))
+                        return
+                st.synchronize()
+                if not (torch.equal(got[1], want[1]) and torch.equal(got[2], want[2]) and torch.equal(got[6], want[6])):
+                    errors.append("image / radii / is_used differ from the serial run")
+        except Exception as ex:  # noqa: BLE001
+            errors.append(repr(ex))
+
+    threads = [threading.Thread(target=worker, args=cs) for cs in cases]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+
+
+@pytest.mark.parametrize("offset", [1, 2, 3])
+def test_unaligned_rotations_and_rotation_gradient_take_the_scalar_path(offset):
+    """rotations / dL_drotations that are contiguous but not 16-byte aligned (a view at an odd storage offset; an arena
+    slice at an odd Gaussian count) must give the same bits as aligned ones instead of a misaligned-address fault."""
+    C = native()
+    scene, cam = helpers.make_case("cube", 5001, 128, 96, seed=4)
+    scene["scales"] = (scene["scales"] * 4).astype(np.float32)
+    s, c = helpers.torch_inputs(scene, cam, dev())
+    P, H, W = 5001, 96, 128
+    flat = torch.empty(4 * P + offset, device=dev())
+    rot_u = flat[offset:].view(P, 4)
+    rot_u.copy_(s["rotations"])
+    assert rot_u.data_ptr() % 16 != 0 and rot_u.is_contiguous()
+    a = C.rasterize_gaussians(*helpers.native_forward_args(s, c, 3))
+    b = C.rasterize_gaussians(*helpers.native_forward_args(dict(s, rotations=rot_u), c, 3))
+    assert a[0] == b[0] and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2])
+    dL = torch.randn((3, H, W), generator=torch.Generator().manual_seed(1)).to(dev())
+    e = torch.empty(0)
+    R, radii, geom, binning, img = a[0], a[2], a[3], a[4], a[5]
+    scratch = C.backward_render(c["bg"], P, R, dL, geom, binning, img)
+    drot_u = torch.empty(4 * P + offset, device=dev())[offset:].view(P, 4)
+    ga = C.backward_geometry(s["means3D"], radii, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+                             c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3, c["campos"], geom, scratch)
+    gb = C.backward_geometry(s["means3D"], radii, s["scales"], rot_u, 1.0, e, c["viewmatrix"], c["projmatrix"],
+                             c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3, c["campos"], geom, scratch,
+                             out_buffers={"rotations": drot_u})
+    torch.cuda.synchronize()
+    assert gb[7].data_ptr() == drot_u.data_ptr()
+    for x, y in zip(ga, gb):
+        assert helpers.bits_equal_count(x + 0.0, y + 0.0) == 0
+    # add_noise reads the raw quaternion the same way
+    from diff_gaussian_rasterization import add_noise
+    noise = torch.randn((P, 3), generator=torch.Generator().manual_seed(2)).to(dev())
+    raw_s, raw_o = torch.log(s["scales"]), torch.full((P, 1), -6.0, device=dev())
+    x1 = add_noise(s["means3D"].clone(), raw_s, s["rotations"], raw_o, 0.1, noise=noise)
+    x2 = add_noise(s["means3D"].clone(), raw_s, rot_u, raw_o, 0.1, noise=noise)
+    assert torch.equal(x1, x2)
 
 
 @pytest.mark.parametrize("degree", [3, 1])

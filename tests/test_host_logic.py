@@ -71,7 +71,7 @@ def test_gradient_arena_layout():
     for name in ("means3D", "sh", "opacity", "scales", "rotations"):
         assert bufs[name].is_contiguous()
         bufs[name].fill_(1.0)
-    assert float(a.flat.sum()) == 7 * 59          # the five parameter gradients tile the arena exactly
+    assert float(a.flat.sum()) == 7 * 59          # the five parameter gradients tile the arena (pad floats stay zero)
     assert dp.shard_views(8, 1, 4) == [1, 5]
     assert a.all_reduce() is a.flat                # no process group: no-op
 
@@ -83,7 +83,15 @@ def test_factored_exchange_capacity_and_resize():
     ex.resize(17)
     assert ex.flat.data_ptr() == ptr                      # same buffer, new views
     assert ex.grads["means3D"].shape == (17, 3) and ex.grads["rotations"].shape == (17, 4) and ex.grads["sh"].shape == (17, 4, 3)
-    assert ex.grads["rotations"].data_ptr() == ptr + 4 * 17 * 7
+    # every field block starts on a 16-byte boundary for any P (17 * 3 = 51 -> 52, + 17 -> 69 -> 72, + 51 -> 123 -> 124)
+    assert ex.grads["rotations"].data_ptr() == ptr + 4 * 124
+    for P in range(1, 40):
+        ex2 = dp.FactoredExchange(P, 4, "cpu", capacity=40)
+        offs = [(v.data_ptr() - ex2.flat.data_ptr()) // 4 for k, v in ex2.grads.items() if k != "sh"]
+        assert all(o % 4 == 0 for o in offs) and offs == sorted(offs)
+        assert ex2._n_slab <= ex2._slab_capacity and ex2._n_slab >= offs[-1] + 4 * P
+        a2 = dp.GradientArena(P, 16, "cpu")
+        assert all((v.data_ptr() - a2.flat.data_ptr()) % 16 == 0 for v in a2.views.values())
     assert ex._n_slab % 64 == 0 and ex._n_slab >= 11 * 17
     with pytest.raises(ValueError):
         ex.resize(25)
