@@ -256,6 +256,20 @@ int gs_backward_render(void* stream_, int P, unsigned int R, int W, int H, const
     return GS_OK;
 }
 
+int gs_debug_render_work(void* stream_, int P, unsigned int R, int W, int H, const void* geom_ws, const void* binning_ws,
+                         const void* image_ws, unsigned int* walked_per_tile, unsigned int* evaluated_per_tile) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P <= 0 || W <= 0 || H <= 0 || !geom_ws || !binning_ws || !image_ws || !walked_per_tile || !evaluated_per_tile) return GS_ERR_ARG;
+    uint2 grid;
+    const uint32_t tiles = tiles_of(W, H, &grid);
+    ImageWS img = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
+    GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
+    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, tiles);
+    RenderBwdParams rb = {};
+    rb.ranges = img.ranges; rb.ids = b.ids; rb.rec = g.rec; rb.W = W; rb.H = H; rb.tiles_x = (int)grid.x; rb.n_contrib = img.n_contrib;
+    return launch_render_work(rb, (int)tiles, walked_per_tile, evaluated_per_tile, stream);
+}
+
 int gs_backward_geometry(void* stream_, int P, int D, int M, int W, int H, const float* means3D, const float* shs,
                          const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
                          const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,

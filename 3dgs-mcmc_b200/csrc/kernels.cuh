@@ -179,6 +179,7 @@ int launch_debug_expand(uint32_t tiles, const uint2* ranges, const uint32_t* ids
 int launch_debug_low32(uint32_t n, const uint64_t* in, uint32_t* out);
 int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream);
 int launch_render_bwd(const RenderBwdParams& p, int tiles, cudaStream_t stream);
+int launch_render_work(const RenderBwdParams& p, int tiles, uint32_t* walked, uint32_t* survivors, cudaStream_t stream);
 int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream);
 int launch_compute_relocation(int P, const float* opacity_old, const float* scale_old, const int* N, const float* binoms,
                               int n_max, float* opacity_new, float* scale_new, cudaStream_t stream);

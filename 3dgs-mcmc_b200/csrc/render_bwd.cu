@@ -311,6 +311,50 @@ static int launch_variant(const RenderBwdParams& p, int tiles, cudaStream_t stre
     return GS_OK;
 }
 
+// Measurement only (gs_debug_render_work): per tile, the number of (warp patch, splat) positions the backward walks
+// (every list position below the patch's last blended one - the "pre-cull" count the roofline's evaluated_pairs is built
+// from) and how many of them survive the conservative patch cull and are actually evaluated per pixel (x 32 lanes).
+__global__ void __launch_bounds__(GS_TILE_PIX) render_work_kernel(const RenderBwdParams p, uint32_t* __restrict__ walked,
+                                                                  uint32_t* __restrict__ survivors) {
+    __shared__ uint32_t s_cnt[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x;
+    const int tile_x = tile % p.tiles_x, tile_y = tile / p.tiles_x;
+    const uint32_t px = tile_x * GS_TILE_X + (warp & 1) * 8 + (lane & 7);
+    const uint32_t py = tile_y * GS_TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+    const bool inside = px < (uint32_t)p.W && py < (uint32_t)p.H;
+    const float patch_x0 = (float)(tile_x * GS_TILE_X + (warp & 1) * 8), patch_y0 = (float)(tile_y * GS_TILE_Y + (warp >> 1) * 4);
+    if (tid < 2) s_cnt[tid] = 0;
+    __syncthreads();
+    const uint2 range = p.ranges[tile];
+    const int last = inside ? (int)p.n_contrib[(size_t)p.W * py + px] : 0;
+    const int warp_last = min((int)(range.y - range.x), __reduce_max_sync(0xffffffffu, last));
+    uint32_t surv = 0;
+    for (int base = 0; base < warp_last; base += 32) {
+        const int j = base + lane;
+        bool may = false;
+        if (j < warp_last) {
+            const float4* r = reinterpret_cast<const float4*>(p.rec + p.ids[range.x + j]);
+            const float4 t0 = __ldg(r), t1 = __ldg(r + 1);
+            may = patch_may_contribute(t0.x, t0.y, t0.z, t0.w, t1.x, t1.z, patch_x0, patch_y0);
+        }
+        surv += (uint32_t)__popc(__ballot_sync(0xffffffffu, may));
+    }
+    if (lane == 0) {
+        atomicAdd(&s_cnt[0], (uint32_t)warp_last);
+        atomicAdd(&s_cnt[1], surv);
+    }
+    __syncthreads();
+    if (tid == 0) { walked[tile] = s_cnt[0]; survivors[tile] = s_cnt[1]; }
+}
+
+int launch_render_work(const RenderBwdParams& p, int tiles, uint32_t* walked, uint32_t* survivors, cudaStream_t stream) {
+    if (tiles <= 0) return GS_OK;
+    render_work_kernel<<<tiles, GS_TILE_PIX, 0, stream>>>(p, walked, survivors);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
 int launch_render_bwd(const RenderBwdParams& p, int tiles, cudaStream_t stream) {
     if (tiles <= 0) return GS_OK;
     static const int variant = [] { const char* e = getenv("GS_BWD_VARIANT"); return e ? atoi(e) : 0; }();

@@ -71,6 +71,7 @@ SIGNATURES = {
     "gs_stage_count": (_c_int, []),
     "gs_stage_name": (ctypes.c_char_p, [_c_int]),
     "gs_launch_count": (_c_ull, []),
+    "gs_debug_render_work": (_c_int, [_c_void_p, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 5),
     "gs_debug_fetch": (ctypes.c_longlong, [_c_int, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 4 + [_c_size_t]),
 }
 
@@ -683,6 +684,19 @@ def debug_fetch(which, P, R, W, H, geom, binning, img, dtype):
     if nbytes:
         _lib.gs_debug_fetch(which, P, R, W, H, _ptr(geom), _ptr(binning), _ptr(img), out.data_ptr(), nbytes)
     return out.view(dtype)
+
+
+def debug_render_work(P, R, W, H, geom, binning, img):
+    """(walked, evaluated): int32 [tiles] each - (patch, splat) positions the backward walks per tile and those that
+    survive the patch cull (gs_debug_render_work). Measurement only."""
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    dev = img.device
+    walked = torch.zeros(tiles, dtype=torch.int32, device=dev)
+    evaluated = torch.zeros(tiles, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _check(_lib.gs_debug_render_work(_stream(dev), int(P), int(R), int(W), int(H), geom.data_ptr(), binning.data_ptr(),
+                                         img.data_ptr(), walked.data_ptr(), evaluated.data_ptr()), "gs_debug_render_work")
+    return walked, evaluated
 
 
 def _debug_sync(stage):

@@ -60,6 +60,39 @@ class GradientArena:
         return sum(w if w is not None else 3 * self.M for _, w in self.FIELDS)
 
 
+def replica_fingerprint(tensors):
+    """Two 64-bit integers that depend on every bit of the given tensors (sum of the raw words and a position-weighted
+    sum): equal on two ranks iff - up to collisions - their replicas are bit-identical."""
+    acc = None
+    for t in tensors:
+        t = t.detach().contiguous()
+        if t.numel() == 0:
+            continue
+        bits = (t.view(torch.int32) if t.element_size() == 4 else t.to(torch.int64)).flatten().long()
+        w = torch.arange(bits.numel(), device=bits.device) % 1000003 + 1
+        h = torch.stack([bits.sum(), (bits * w).sum(), torch.tensor(bits.numel(), device=bits.device)])
+        acc = h if acc is None else acc * 31 + h
+    return acc if acc is not None else torch.zeros(3, dtype=torch.int64)
+
+
+def assert_replicas_in_sync(tensors, group=None, what="replicated Gaussian parameters"):
+    """View-sharded training keeps a full replica of the model (and of its MCMC state) on every rank and relies on the
+    replicas evolving in lock step: the summed gradients are bit-identical on all ranks, and relocation / growth draw from
+    torch's device RNG seeded alike. A rank that diverged (different seed, a skipped step) would silently train a different
+    model and - after add_new_gs - hand resize() a different P, corrupting the symmetric buffers. Call this after every
+    relocation / growth step (it costs two tiny all-reduces): raises RuntimeError on every rank if any replica differs."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return True
+    h = replica_fingerprint(tensors).to(tensors[0].device)
+    lo, hi = h.clone(), h.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+    if not bool((lo == hi).all()):
+        raise RuntimeError(f"{what} differ between ranks (rank {dist.get_rank(group)}: fingerprint {h.tolist()}, "
+                           f"min {lo.tolist()}, max {hi.tolist()}): replicas are out of lock step")
+    return True
+
+
 def shard_views(num_views, rank, world_size):
     """Indices of the camera views rank `rank` renders in a step of `num_views` views (round-robin)."""
     return list(range(rank, num_views, world_size))

@@ -30,6 +30,18 @@ import numpy as np  # noqa: E402
 
 SCENE = dict(kind="garden", seed=0, fovx=1.2, cam_radius=6.0, elevation=20.0, ncams=16)
 METRIC = "train views/s (fwd+bwd rasterize, 3M Gaussians, 1920x1080, SH deg 3)"
+# BASELINE.json configs as presets of (scene kind, P, W, H, camera); "headline" is the one the metric is quoted on (config 3/4
+# shape at 3M / 1080p) and the default; the others produce the same JSON line for their own workload.
+CONFIGS = {
+    "headline": dict(kind="garden", P=3_000_000, W=1920, H=1080, fovx=1.2, cam_radius=6.0,
+                     name="BASELINE.json headline: garden-shaped 3M Gaussians at 1920x1080"),
+    "lego300k": dict(kind="cube", P=300_000, W=800, H=800, fovx=0.6911, cam_radius=4.03,
+                     name="BASELINE.json config 2: NeRF-synthetic-shaped (lego) random init at cap_max=300K, 800x800"),
+    "garden1297": dict(kind="garden", P=3_000_000, W=1297, H=840, fovx=1.2, cam_radius=6.0,
+                       name="BASELINE.json config 3: Mip-NeRF360-shaped (garden) cap_max=3M at 1297x840"),
+    "large6m": dict(kind="garden", P=6_000_000, W=1920, H=1080, fovx=1.2, cam_radius=6.0,
+                    name="BASELINE.json config 4: large scene, 6M Gaussians at 1920x1080, one view per GPU"),
+}
 FLOPS_PER_PAIR_FWD = 16   # ~16 FP32 ops + 1 exp per evaluated (pixel, splat) pair
 FLOPS_PER_PAIR_BWD = 45   # ~45 FP32 ops + 1 exp + 1 div per evaluated pair
 
@@ -40,30 +52,45 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--P", type=int, default=3_000_000)
-    ap.add_argument("--width", type=int, default=1920)
-    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--config", default="headline", choices=sorted(CONFIGS), help="workload preset (BASELINE.json configs)")
+    ap.add_argument("--P", type=int, default=None)
+    ap.add_argument("--width", type=int, default=None)
+    ap.add_argument("--height", type=int, default=None)
     ap.add_argument("--skip-baselines", action="store_true", help="skip the cpu_baseline and ref_cuda legs")
     ap.add_argument("--exchange", default="factored", choices=["factored", "allreduce"],
                     help="N > 1: gradient exchange. factored = all-gather masked dL/dRGB + rebuild the SH gradient + all-reduce "
                          "11 floats per Gaussian (dp.FactoredExchange); allreduce = NCCL all-reduce of the 59-float arena")
     ap.add_argument("--transport", default="auto", choices=["auto", "symm", "nccl"])
-    ap.add_argument("--train-step-leg", action="store_true",
-                    help="N > 1: also time the full training iteration (informational; on by default at N = 1 only, so that "
-                         "nothing after the two contract measurements can stall a multi-rank run)")
-    return ap.parse_args()
+    ap.add_argument("--no-train-step-leg", action="store_true", help="skip the full-training-iteration leg")
+    ap.add_argument("--legs-deadline", type=float, default=None,
+                    help="seconds the informational legs after the two contract measurements may take before the line is "
+                         "printed without them (default 600 at N = 1, 300 at N > 1)")
+    args = ap.parse_args()
+    cfg = CONFIGS[args.config]
+    args.P = args.P or cfg["P"]
+    args.width = args.width or cfg["W"]
+    args.height = args.height or cfg["H"]
+    SCENE.update(kind=cfg["kind"], fovx=cfg["fovx"], cam_radius=cfg["cam_radius"])
+    args.workload_name = cfg["name"]
+    return args
+
+
+def metric_name(args):
+    if args.config == "headline" and (args.P, args.width, args.height) == (3_000_000, 1920, 1080):
+        return METRIC
+    return f"train views/s (fwd+bwd rasterize, {args.P} Gaussians, {args.width}x{args.height}, SH deg 3)"
 
 
 def build_scene(P, W, H):
     import gs_synth
-    scene = gs_synth.scene_garden(P, SCENE["seed"])
+    scene = gs_synth.scene_cube(P, SCENE["seed"]) if SCENE["kind"] == "cube" else gs_synth.scene_garden(P, SCENE["seed"])
     cams = gs_synth.orbit_cameras(SCENE["ncams"], SCENE["cam_radius"], W, H, SCENE["fovx"], SCENE["elevation"])
     return scene, cams
 
 
-def workload_config(P, W, H, n_gpus, exchange=None):
-    return {"workload": f"synthetic garden scene (gs_synth.scene_garden seed 0): P={P} Gaussians, SH degree 3, "
-                        f"{W}x{H}, orbit cameras r=6 fovx=1.2; BASELINE.json config 3/4 shape at the headline size",
+def workload_config(P, W, H, n_gpus, exchange=None, name=None):
+    return {"workload": f"{name or CONFIGS['headline']['name']} - synthetic {SCENE['kind']} scene (gs_synth.scene_{SCENE['kind']} seed 0): "
+                        f"P={P} Gaussians, SH degree 3, {W}x{H}, {SCENE['ncams']} orbit cameras r={SCENE['cam_radius']} fovx={SCENE['fovx']}",
             "gaussians": P, "width": W, "height": H, "views_per_step": n_gpus,
             "parallelism": f"view-sharded dp{n_gpus}, replicated Gaussians" + (f", gradient exchange: {exchange}" if n_gpus > 1 else ""),
             "l2_policy": "inputs (708 MB of parameters, 0.9 GB of gradients, ~0.4 GB of instance keys/ids per step) exceed the 126 MB L2; no explicit flush"}
@@ -104,46 +131,54 @@ def cpu_port_step(scene, cam, dL, tile_step):
     return est, measured, t
 
 
-def cpu_baseline_leg(scene, cam, W, H, tile_step=16):
+def cpu_baseline_leg(scene, cam, W, H, tile_step=1):
+    """One FULL fwd+bwd step of the CPU port on every host core (about 5-10 s of CPU work at the headline size): nothing
+    is sampled or extrapolated."""
     from oracle import oracle
+    cores = oracle.set_num_threads()
     dL = np.random.default_rng(3).standard_normal((3, H, W)).astype(np.float32)
     est, measured, t = cpu_port_step(scene, cam, dL, tile_step)
-    return {"value": 1.0 / est, "unit": "views/s", "cores": oracle.num_threads(), "kind": "port",
-            "sample": f"one view: preprocess + binning + preprocess-backward on all {scene['means3D'].shape[0]} Gaussians, "
-                      f"render fwd+bwd on every {tile_step}th tile scaled x{tile_step}; {measured:.1f} s of CPU work, "
-                      f"estimated full step {est:.1f} s",
+    return {"value": 1.0 / est, "unit": "views/s", "cores": cores, "kind": "port",
+            "sample": f"one complete view, no sampling: preprocess + binning + render fwd + render bwd + preprocess-backward on all "
+                      f"{scene['means3D'].shape[0]} Gaussians and all tiles; {measured:.1f} s of wall time on {cores} threads",
+            "stage_seconds": {k: round(v, 3) for k, v in t.items()},
             "note": "the reference has no CPU implementation of this path; this is the plain-C restatement (oracle/oracle_cpu.c) with OpenMP"}
 
 
 def run_reference_arm(args):
     """--impl reference: the reference path on the host cores. The reference's own implementation is CUDA-only, so
-    this times the CPU port (kind 'port'). Rank 0 alone works; other ranks exit."""
+    this times the CPU port (kind 'port') - every step a COMPLETE fwd+bwd of one view (all Gaussians, all tiles; measured,
+    never scaled from a sample), on every core the process may use (torchrun's OMP_NUM_THREADS=1 is overridden). Rank 0
+    alone works; other ranks exit."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     from oracle import oracle
+    cores = oracle.set_num_threads()
     W, H, P = args.width, args.height, args.P
     scene, cams = build_scene(P, W, H)
     dL = np.random.default_rng(3).standard_normal((3, H, W)).astype(np.float32)
-    tile_step = 64
-    ests = []
+    tile_step, estimated = 1, False
+    secs = []
+    t_run = time.perf_counter()
     for i in range(args.warmup + args.steps):
         est, measured, _ = cpu_port_step(scene, cams[i % len(cams)], dL, tile_step)
         if i >= args.warmup:
-            ests.append(est)
-        # keep the whole run within a few minutes
-        if i == 0 and measured * (args.warmup + args.steps) > 240.0:
-            tile_step *= 4
-    sec = sum(ests) / len(ests)
-    value = args.gpus * 0 + 1.0 / sec  # one host, one view at a time
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "views/s", "n_gpus": args.gpus,
+            secs.append(est)
+        # a host so slow that the complete run would not end within ~8 minutes: sample tiles from here on and SAY so
+        if i == 0 and tile_step == 1 and measured * (args.warmup + args.steps) > 480.0:
+            tile_step, estimated = 16, True
+    wall = time.perf_counter() - t_run
+    sec = sum(secs) / len(secs)
+    value = 1.0 / sec  # one host, one view at a time
+    sample = ("each step: one complete view (all Gaussians, all tiles), measured" if not estimated else
+              f"host too slow for complete steps: render fwd+bwd on every {tile_step}th tile scaled x{tile_step} (ESTIMATED)")
+    line = {"impl": "reference", "metric": metric_name(args), "value": value, "unit": "views/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(P, W, H, args.gpus),
-            "cpu_baseline": {"value": value, "unit": "views/s", "cores": oracle.num_threads(), "kind": "port",
-                             "sample": f"each step: full preprocess/binning/preprocess-backward, render fwd+bwd on every "
-                                       f"{tile_step}th tile scaled x{tile_step}"},
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "estimated": estimated,
+            "config": workload_config(P, W, H, args.gpus, name=args.workload_name),
+            "cpu_baseline": {"value": value, "unit": "views/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "wall_seconds": round(wall, 2), "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
@@ -217,6 +252,7 @@ def run_b200_arm(args):
     W, H, P = args.width, args.height, args.P
     K, Wm = args.steps, args.warmup
 
+    metric = metric_name(args)
     scene_np, cams_np = build_scene(P, W, H)
     s = gs_synth.to_torch(scene_np, dev)
     cams = [gs_synth.to_torch(c, dev) for c in cams_np]
@@ -314,6 +350,13 @@ def run_b200_arm(args):
     pairs_bwd = int(patch_max.sum().item()) * 32
     # forward evaluates every position up to the tile's termination; bounded below by n_contrib, above by list length
     pairs_fwd_lower = int(n_contrib.long().sum().item())
+    # the same walk with the conservative patch cull applied (gs_debug_render_work): what the kernel actually evaluates
+    walked_t, evaluated_t = C.debug_render_work(P, R, W, H, state["geom"], state["binning"], state["img"])
+    pairs_walked = int(walked_t.long().sum().item()) * 32
+    pairs_post_cull = int(evaluated_t.long().sum().item()) * 32
+    work = evaluated_t.float()
+    tile_work = {"evaluated_per_tile_mean": float(work.mean().item()), "evaluated_per_tile_p50": float(work.median().item()),
+                 "evaluated_per_tile_p99": float(torch.quantile(work, 0.99).item()), "evaluated_per_tile_max": float(work.max().item())}
     tile_len = (ranges[:, 1] - ranges[:, 0]).long()
     sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
     peaks = {}
@@ -356,6 +399,14 @@ def run_b200_arm(args):
         ms = stage_ms(name)
         if ms:
             stage_report[name] = {"ms": round(ms, 4), "alg_GBps": round(b / ms / 1e6, 1), "hbm_frac": round(b / ms / 1e6 / hbm_peak, 4)}
+    if "tile_sort" in stage_report:
+        # the same launch group against ITS OWN minimum traffic (what this formulation has to move): emission table in,
+        # u64 keys out (pass 1); keys in twice (count, scatter) and u32 ids out (pass 2); block histograms are noise
+        own = visible * 16 + R * 8 + R * 8 + R * 8 + R * 4
+        ms_ = stage_report["tile_sort"]["ms"]
+        stage_report["tile_sort"].update(own_bytes=own, own_GBps=round(own / ms_ / 1e6, 1), own_hbm_frac=round(own / ms_ / 1e6 / hbm_peak, 4),
+                                         note="alg_GBps / hbm_frac charge the reference formulation's bytes (44 B/instance + 20 B/Gaussian); "
+                                              "own_* charge the bytes this formulation moves (28 B/instance + 16 B/Gaussian)")
     try:
         ncu_traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
     except Exception:
@@ -370,8 +421,14 @@ def run_b200_arm(args):
         roofline = {"kernel": dom, "bound": "fp32", "achieved": round(achieved, 3), "peak": round(fp32_peak_tflops, 2),
                     "unit": "TFLOP/s", "frac": round(achieved / fp32_peak_tflops, 4),
                     "traffic": (ncu_traffic.get(dom) or {}).get("bytes"), "traffic_source": (ncu_traffic.get(dom) or {}).get("capture"),
-                    "ms": round(dom_ms, 4), "evaluated_pairs": pairs,
-                    "note": "FP32-SIMT bound (no tensor-core work on this path): algorithmic flops = evaluated (pixel, splat) pairs x "
+                    "ms": round(dom_ms, 4), "evaluated_pairs": pairs, "evaluated_pairs_post_cull": pairs_post_cull,
+                    "post_cull_fraction": round(pairs_post_cull / max(pairs_walked, 1), 4),
+                    "ncu_pipe_utilisation": (ncu_traffic.get(dom) or {}).get("pipes"),
+                    "note": "evaluated_pairs is counted BEFORE the conservative patch cull (every list position below a patch's last blended "
+                            "one x 32 lanes): `frac` is algorithmic throughput against the FP32 peak, not pipe utilisation - the kernel skips "
+                            "the culled share (evaluated_pairs_post_cull is what it evaluates per pixel); the hardware view is "
+                            "ncu_pipe_utilisation (issue-slot / FMA-pipe %, profiles/). "
+                            "FP32-SIMT bound (no tensor-core work on this path): algorithmic flops = evaluated (pixel, splat) pairs x "
                             f"{FLOPS_PER_PAIR_BWD if dom == 'render_bwd' else FLOPS_PER_PAIR_FWD} (SURVEY.md 8d); peak = SMs x 128 lanes x 2 x max SM clock; "
                             f"hbm view of the same launch: {stage_report.get(dom)}"}
     else:
@@ -504,33 +561,64 @@ def run_b200_arm(args):
                   ("" if n_gpus == 1 else " with the cross-rank gradient sum inside the backward" if factored else " + all_reduce of the 5 parameter gradients") +
                   "; pinned gt image (copy stream, one step ahead) and camera in, loss out (async D2H into pinned memory, read one step later)"}
 
-    # ---- full training step (informational; SURVEY.md 8 f1 pieces around the hot path): raw parameters -> activations ->
-    #      rasterizer -> L1 + SSIM loss + the two regularisers -> backward (+ exchange) -> Adam -> MCMC noise, as
-    #      train_static.py:86-140 runs it. "fused": csrc/loss.cu + csrc/optim.cu + gs_add_noise; "torch_glue": the reference's
-    #      torch ops for loss / optimizer / noise around the same rasterizer (N = 1 only). ----
-    train_step = None
-    try:
-        if n_gpus > 1 and not args.train_step_leg:
-            raise RuntimeError("skipped at N > 1 (pass --train-step-leg); 8-GPU figure: profiles/r1_bench_3M_1080p_v16_n8.json")
-        train_step = run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_gpus, rank, K, min(Wm, 3), bg,
-                                        exchange if factored else None, barrier, ev0, ev1)
-    except Exception as ex:
-        train_step = {"unavailable": repr(ex)[:300]}
-
-    if rank != 0:
-        if n_gpus > 1:
-            dist.destroy_process_group()
-        return
-
-    line = {"metric": METRIC, "value": value, "unit": "views/s", "n_gpus": n_gpus, "steps": K, "warmup": Wm,
+    # ---- the contract line is complete here; everything below is informational and runs under a deadline: if a leg
+    #      stalls (one rank raising inside a collective would leave the others waiting), rank 0 prints the line with what
+    #      it has and every rank exits, so the two contract measurements above are never lost. ----
+    line = {"metric": metric, "value": value, "unit": "views/s", "n_gpus": n_gpus, "steps": K, "warmup": Wm,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": workload_config(P, W, H, n_gpus, exchange_desc), "clocks": clocks, "e2e": e2e,
-            "gpu_launches": launches, "roofline": roofline, "roofline_hbm": roofline_hbm, "stages": stage_report, "train_step": train_step,
+            "data": "synthetic", "config": workload_config(P, W, H, n_gpus, exchange_desc, name=args.workload_name), "clocks": clocks, "e2e": e2e,
+            "gpu_launches": launches, "roofline": roofline, "roofline_hbm": roofline_hbm, "stages": stage_report,
             "step_ms": {"min": round(per_step[0], 4), "p50": round(per_step[len(per_step) // 2], 4), "max": round(per_step[-1], 4)},
             "scene_stats": {"num_rendered": R, "visible": visible, "instances_per_visible": round(R / max(visible, 1), 2),
                             "tile_list_mean": float(tile_len.float().mean().item()), "tile_list_p99": float(torch.quantile(tile_len.float(), 0.99).item()),
-                            "pairs_bwd": pairs_bwd, "pairs_fwd_lower_bound": pairs_fwd_lower,
+                            "pairs_bwd": pairs_bwd, "pairs_fwd_lower_bound": pairs_fwd_lower, "pairs_walked": pairs_walked,
+                            "pairs_post_cull": pairs_post_cull, "tile_work": tile_work,
                             "mpix_per_s": W * H / ms_per_step / 1e3}}
+    printed = threading.Lock()
+
+    def emit(reason=None):
+        if not printed.acquire(blocking=False):
+            return
+        if reason:
+            line["legs_cut_short"] = reason
+        if rank == 0:
+            print(json.dumps(line), flush=True)
+
+    deadline_s = args.legs_deadline or (600.0 if n_gpus == 1 else 300.0)
+
+    def on_deadline():
+        emit(f"informational legs exceeded {deadline_s:.0f} s; printed without the unfinished ones")
+        os._exit(0)
+    watchdog = threading.Timer(deadline_s, on_deadline)
+    watchdog.daemon = True
+    watchdog.start()
+
+    # ---- N > 1: parity of the exchange that was just timed (the multimem / peer-pointer kernels) against the plain route:
+    #      the same views through dp.GradientArena + ONE NCCL all-reduce of all 59 floats per Gaussian ----
+    if n_gpus > 1 and factored:
+        try:
+            line["parity"] = exchange_parity_leg(torch, dist, C, dp, dev, s, cam_for(Wm + K), campos_tables[(Wm + K) % len(cams)], bg, dL,
+                                                 exchange, P, H, W, n_gpus)
+        except Exception as ex:
+            line["parity"] = {"unavailable": repr(ex)[:300]}
+
+    # ---- full training step (informational; SURVEY.md 8 f1 pieces around the hot path): raw parameters -> activations ->
+    #      rasterizer -> L1 + SSIM loss + the two regularisers -> backward (+ exchange) -> Adam -> MCMC noise, as
+    #      train_static.py:86-140 runs it. "fused": csrc/loss.cu + csrc/optim.cu + gs_add_noise; "torch_glue": the reference's
+    #      torch ops for loss / optimizer / noise around the same rasterizer (N = 1 only). Runs at every N. ----
+    if not args.no_train_step_leg:
+        try:
+            line["train_step"] = run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_gpus, rank, K, min(Wm, 3), bg,
+                                                    exchange if factored else None, barrier, ev0, ev1)
+        except Exception as ex:
+            line["train_step"] = {"unavailable": repr(ex)[:300]}
+
+    if rank != 0:
+        if n_gpus > 1:
+            barrier()
+            dist.destroy_process_group()
+        watchdog.cancel()
+        return
 
     # ---- SURVEY.md 8 f1 ("next" rows), measured beside the hot path at N=1: the optimizer step over the same parameters ----
     if n_gpus == 1:
@@ -606,41 +694,197 @@ def run_b200_arm(args):
         except Exception as ex:
             line.setdefault("next_rows", {})["swin_gather"] = {"unavailable": repr(ex)[:200]}
 
+    # ---- MCMC update kernels (north_star (5)): compute_relocation at K = 5 % of P with N drawn like
+    #      _sample_alives draws it (multinomial over the opacities -> bincount, gaussian_model_static.py:412-422), and add_noise
+    #      over all P; the reference's own relocation kernel timed beside ours on the same tensors ----
+    if n_gpus == 1:
+        try:
+            line["mcmc"] = mcmc_kernels_leg(torch, dev, s, P, hbm_peak, ev0, ev1, None if args.skip_baselines else "ref")
+        except Exception as ex:
+            line["mcmc"] = {"unavailable": repr(ex)[:300]}
+
     # ---- baseline legs (rank 0, N=1 only): reference CUDA on the same box, CPU port on the host cores ----
     if n_gpus == 1 and not args.skip_baselines:
         try:
             from oracle import ref_cuda
             if ref_cuda.available():
-                c = cams[0]
-
-                def ref_step():
-                    Rr, col, rad, used = ref_cuda.forward(bg, s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e,
-                                                          c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, s["shs"],
-                                                          3, c["campos"])
-                    ref_cuda.backward(bg, s["means3D"], rad, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
-                                      c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], Rr)
-                for _ in range(3):
-                    ref_step()
-                torch.cuda.synchronize()
-                ev0.record()
-                kk = max(3, min(K, 10))
-                for _ in range(kk):
-                    ref_step()
-                ev1.record()
-                torch.cuda.synchronize()
-                rms = ev0.elapsed_time(ev1) / kk
-                line["ref_cuda"] = {"ms_per_step": rms, "value": 1000.0 / rms, "unit": "views/s", "steps": kk,
-                                    "what": "the reference's own cuda_rasterizer compiled for sm_100 (oracle/_ref), same tensors, same box",
-                                    "speedup_device": rms / ms_per_step}
+                line["ref_cuda"] = ref_cuda_leg(torch, ref_cuda, dev, s, cams, bg, dL, H, W, K, ms_per_step, e2e["ms_per_step"], gt_host,
+                                                cam_host, l1_loss, ev0, ev1)
         except Exception as ex:  # baseline only; never fail the bench on it
             line["ref_cuda"] = {"unavailable": repr(ex)[:200]}
         try:
             line["cpu_baseline"] = cpu_baseline_leg(scene_np, cams_np[0], W, H)
         except Exception as ex:
             line["cpu_baseline"] = {"unavailable": repr(ex)[:200]}
-    print(json.dumps(line), flush=True)
+    watchdog.cancel()
+    emit()
     if n_gpus > 1:
+        barrier()
         dist.destroy_process_group()
+
+
+def ref_cuda_leg(torch, ref_cuda, dev, s, cams, bg, dL, H, W, K, our_ms, our_e2e_ms, gt_host, cam_host, l1_loss, ev0, ev1):
+    """The reference's own cuda_rasterizer (oracle/_ref, compiled for sm_100 from /root/reference) on the same box, tensors
+    and CAMERA CYCLE as the main arm: device-timed fwd+bwd with a forward / backward split, and an end-to-end variant through
+    the reference's autograd contract (oracle/ref_rasterizer.py) with the same pinned gt copy, L1 loss and loss read-back as
+    this arm's e2e loop."""
+    from oracle import ref_rasterizer
+    from diff_gaussian_rasterization import GaussianRasterizationSettings
+    e = torch.empty(0)
+    kk = max(3, min(K, 16))
+    fwd_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(kk)]
+
+    def ref_step(i, evs=None):
+        c = cams[i % len(cams)]
+        if evs:
+            evs[0].record()
+        Rr, col, rad, used = ref_cuda.forward(bg, s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e,
+                                              c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3, c["campos"])
+        if evs:
+            evs[1].record()
+        ref_cuda.backward(bg, s["means3D"], rad, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+                          c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], Rr)
+        if evs:
+            evs[2].record()
+    for i in range(3):
+        ref_step(i)
+    torch.cuda.synchronize()
+    ev0.record()
+    for i in range(kk):
+        ref_step(3 + i, fwd_ev[i])
+    ev1.record()
+    torch.cuda.synchronize()
+    rms = ev0.elapsed_time(ev1) / kk
+    fwd_ms = sum(a.elapsed_time(b) for a, b, _ in fwd_ev) / kk
+    bwd_ms = sum(b.elapsed_time(c_) for _, b, c_ in fwd_ev) / kk
+    out = {"ms_per_step": rms, "value": 1000.0 / rms, "unit": "views/s", "steps": kk, "forward_ms": round(fwd_ms, 4),
+           "backward_ms": round(bwd_ms, 4), "cameras": f"the main arm's cycle of {len(cams)} orbit cameras",
+           "what": "the reference's own cuda_rasterizer compiled for sm_100 (oracle/_ref), same tensors, same cameras, same box; "
+                   "forward / backward from CUDA events around the two library calls (the reference's glue zero-fills its outputs "
+                   "inside them, rasterize_points.cu:66-75,154-162); per-kernel times: profiles/ ncu launch list of this leg",
+           "speedup_device": rms / our_ms}
+    # end to end, as this arm's e2e loop: gt from pinned memory, autograd rasterizer, L1, backward, loss read back
+    params = {k: s[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    gt_dev = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    view_dev, proj_dev, campos_dev = (torch.empty(sh_, device=dev) for sh_ in ((4, 4), (4, 4), (3,)))
+
+    def e2e_step(i):
+        ch = cam_host[i % len(cam_host)]
+        gt_dev.copy_(gt_host[i % 2], non_blocking=True)
+        view_dev.copy_(ch["viewmatrix"], non_blocking=True)
+        proj_dev.copy_(ch["projmatrix"], non_blocking=True)
+        campos_dev.copy_(ch["campos"], non_blocking=True)
+        st = GaussianRasterizationSettings(H, W, ch["tanfovx"], ch["tanfovy"], bg, 1.0, view_dev, proj_dev, 3, campos_dev, False, False)
+        means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+        image, _, _ = ref_rasterizer.RefGaussianRasterizer(st)(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                                                               opacities=params["opacities"], scales=params["scales"],
+                                                               rotations=params["rotations"])
+        loss = l1_loss(image, gt_dev)
+        loss.backward()
+        v = float(loss.item())
+        for p_ in params.values():
+            p_.grad = None
+        return v
+    for i in range(2):
+        e2e_step(i)
+    torch.cuda.synchronize()
+    ev0.record()
+    for i in range(kk):
+        e2e_step(2 + i)
+    ev1.record()
+    torch.cuda.synchronize()
+    ems = ev0.elapsed_time(ev1) / kk
+    out["e2e"] = {"ms_per_step": ems, "value": 1000.0 / ems, "unit": "views/s", "speedup_e2e": ems / our_e2e_ms,
+                  "api": "oracle.ref_rasterizer.RefGaussianRasterizer (the reference's autograd contract over its CUDA) + loss.l1_loss + "
+                         "loss.backward(); pinned gt image and camera in, loss out (synchronous copy and read: the reference library runs "
+                         "on the legacy default stream)"}
+    return out
+
+
+def mcmc_kernels_leg(torch, dev, s, P, hbm_peak, ev0, ev1, ref):
+    from diff_gaussian_rasterization import add_noise, compute_relocation
+    from oracle import oracle
+    out = {}
+
+    def timeit(fn, iters=20):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        ev0.record()
+        for _ in range(iters):
+            fn()
+        ev1.record()
+        torch.cuda.synchronize()
+        return ev0.elapsed_time(ev1) / iters
+    g = torch.Generator(device=dev).manual_seed(11)
+    Kr = max(1, P // 20)
+    probs = s["opacities"].reshape(-1)
+    idx = torch.multinomial(probs / probs.sum(), Kr, replacement=True, generator=g)
+    ratio = torch.bincount(idx, minlength=P)
+    N = (ratio[idx] + 1).clamp_(1, 50).int()
+    op, sc = probs[idx].contiguous(), s["scales"][idx].contiguous()
+    binoms = torch.from_numpy(oracle.binoms_table(51)).to(dev)
+    ms = timeit(lambda: compute_relocation(op, sc, N, binoms, 51))
+    nbytes = Kr * (4 + 12 + 4 + 4 + 12)
+    out["compute_relocation"] = {"ms": round(ms, 5), "K": Kr, "N_mean": float(N.float().mean().item()), "N_max": int(N.max().item()),
+                                 "alg_GBps": round(nbytes / ms / 1e6, 2), "hbm_frac": round(nbytes / ms / 1e6 / hbm_peak, 5),
+                                 "bound": "latency / FP64 pow (36 B per relocated Gaussian: HBM time at peak would be "
+                                          f"{nbytes / hbm_peak / 1e6:.4f} ms)"}
+    if ref:
+        try:
+            from oracle import ref_cuda
+            if ref_cuda.available():
+                rms = timeit(lambda: ref_cuda.compute_relocation(op, sc, N, binoms, 51))
+                o1, s1 = compute_relocation(op, sc, N, binoms, 51)
+                o2, s2 = ref_cuda.compute_relocation(op, sc, N, binoms, 51)
+                torch.cuda.synchronize()
+                out["compute_relocation"].update(reference_kernel_ms=round(rms, 5), speedup=round(rms / ms, 2),
+                                                 bit_identical_to_reference=bool(torch.equal(o1, o2) and torch.equal(s1, s2)))
+        except Exception as ex:
+            out["compute_relocation"]["reference_kernel"] = repr(ex)[:120]
+    xyz = s["means3D"].clone()
+    raw_s, raw_o = torch.log(s["scales"]), torch.logit(s["opacities"].clamp(1e-4, 1 - 1e-4))
+    ms = timeit(lambda: add_noise(xyz, raw_s, s["rotations"], raw_o, 5e5 * 1.6e-4, seed=3, offset=0))
+    nbytes = P * (24 + 12 + 16 + 4)
+    out["add_noise"] = {"ms": round(ms, 5), "alg_GBps": round(nbytes / ms / 1e6, 1), "hbm_frac": round(nbytes / ms / 1e6 / hbm_peak, 4),
+                        "what": "one fused pass over all P (xyz read+write, raw scale / rotation / opacity read, in-kernel Philox); "
+                                "train_static.py:132-140 runs ~15 torch launches for it"}
+    return out
+
+
+def exchange_parity_leg(torch, dist, C, dp, dev, s, c, campos_views, bg, dL, exchange, P, H, W, world):
+    """Per-tensor relative L2 of the factored exchange's summed gradients (the kernels SCALE times: color_grad_push +
+    sh_grad_combine + slab_all_reduce over symmetric memory, multimem variants when multicast is on) against
+    dp.GradientArena + one NCCL all-reduce of the per-rank fused backward, on the same views; and whether the factored
+    result is bit-identical on every rank."""
+    e = torch.empty(0)
+    R, color, radii, geom, binning, img, is_used = C.rasterize_gaussians(
+        bg, s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+        c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3, c["campos"], False, False)
+    arena = dp.GradientArena(P, 16, dev)
+    C.rasterize_gaussians_backward(bg, s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+                                   c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], geom, R, binning, img, False,
+                                   out_buffers=arena.backward_buffers())
+    arena.all_reduce()
+    got = exchange.backward(C, bg, s["means3D"], radii, s["scales"], s["rotations"], 1.0, c["viewmatrix"], c["projmatrix"],
+                            c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], campos_views, geom, R, binning, img)
+    torch.cuda.synchronize()
+    rel, ident = {}, True
+    for k in ("means3D", "sh", "opacity", "scales", "rotations"):
+        a, b = got[k].double(), arena.views[k].double()
+        rel[k] = float((a - b).norm() / b.norm().clamp_min(1e-300))
+        h = dp.replica_fingerprint([got[k]]).to(dev)
+        hs = [torch.zeros_like(h) for _ in range(world)]
+        dist.all_gather(hs, h)
+        ident = ident and all(bool((x == hs[0]).all()) for x in hs)
+    worst = torch.tensor([max(rel.values())], dtype=torch.float64, device=dev)
+    dist.all_reduce(worst, op=dist.ReduceOp.MAX)
+    del arena
+    torch.cuda.empty_cache()
+    return {"rel_l2_vs_arena_nccl_all_reduce": rel, "max_rel_l2_over_ranks": float(worst.item()), "identical_on_all_ranks": ident,
+            "multicast": bool(getattr(exchange, "_multicast", False)), "transport": exchange.transport, "tolerance": 1e-5,
+            "ok": bool(float(worst.item()) <= 1e-5 and ident),
+            "what": "same views, same dL/dpix: factored exchange (timed above) vs GradientArena + one NCCL all_reduce of 59 floats/Gaussian"}
 
 
 def next_rows_swin_knn(torch, dev, s, ev0, ev1):

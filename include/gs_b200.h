@@ -257,6 +257,13 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H,
                          const void* geom_ws, const void* binning_ws, const void* image_ws,
                          void* dst, size_t max_bytes);
 
+/* Measurement hook (bench.py's roofline note, tools/tile_work.py): per tile of the last forward, the number of
+ * (8x4 pixel patch, splat) list positions the tile renderers walk in the backward (walked_per_tile[tiles]; x 32 lanes
+ * = the "evaluated pairs" figure of the roofline, counted BEFORE the conservative patch cull) and how many of them
+ * survive the cull and are evaluated per pixel (evaluated_per_tile[tiles]). Device arrays; asynchronous on `stream`. */
+int gs_debug_render_work(void* stream, int P, unsigned int R, int W, int H, const void* geom_ws, const void* binning_ws,
+                         const void* image_ws, unsigned int* walked_per_tile, unsigned int* evaluated_per_tile);
+
 #ifdef __cplusplus
 }
 #endif

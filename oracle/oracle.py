@@ -50,6 +50,8 @@ def lib():
         L.orc_knn_mean_dist2.argtypes = [_i, _fp, _fp]
         L.orc_knn_mean_dist2.restype = None
         L.orc_num_threads.restype = _i
+        L.orc_set_num_threads.argtypes = [_i]
+        L.orc_set_num_threads.restype = None
         for n in ("orc_preprocess", "orc_mark_visible", "orc_bin", "orc_render_fwd", "orc_render_bwd",
                   "orc_preprocess_bwd", "orc_compute_relocation", "orc_add_noise"):
             getattr(L, n).restype = None
@@ -71,6 +73,16 @@ def _opt(a):
 
 def num_threads():
     return int(lib().orc_num_threads())
+
+
+def set_num_threads(n=None):
+    """Use n OpenMP threads (default: every core this process may run on), whatever OMP_NUM_THREADS says - torchrun
+    exports OMP_NUM_THREADS=1 to its ranks. Returns the thread count now in effect."""
+    import os
+    if n is None:
+        n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    lib().orc_set_num_threads(int(n))
+    return num_threads()
 
 
 def preprocess(means3D, scales, rotations, opacities, shs, view, proj, campos, W, H, tanfovx, tanfovy, degree=3,

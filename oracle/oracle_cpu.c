@@ -574,6 +574,15 @@ void orc_add_noise(int P, float* xyz, const float* scaling_raw, const float* rot
     }
 }
 
+/* OMP_NUM_THREADS=1 is exported by torchrun to every rank; the timed CPU legs of bench.py override it explicitly. */
+void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int orc_num_threads(void) {
     int n = 1;
 #ifdef _OPENMP

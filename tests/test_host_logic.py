@@ -211,6 +211,52 @@ def test_factored_exchange_world_size_2_gloo(tmp_path):
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
 
 
+def test_replica_guard_world_size_2_gloo(tmp_path):
+    """dp.assert_replicas_in_sync: passes while the replicas are bit-identical (also after a resize to a ragged P), raises
+    on EVERY rank as soon as one rank's copy differs in a single bit - the guard view-sharded MCMC training calls after
+    each relocation / growth step."""
+    script = tmp_path / "worker.py"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script.write_text(textwrap.dedent(f"""
+        import os, sys
+        sys.path.insert(0, {os.path.join(root, '3dgs-mcmc_b200')!r})
+        import torch, torch.distributed as dist
+        from diff_gaussian_rasterization import dp
+        dist.init_process_group("gloo")
+        r = dist.get_rank()
+        g = torch.Generator().manual_seed(3)
+        xyz, op = torch.randn((1001, 3), generator=g), torch.randn((1001, 1), generator=g)
+        idx = torch.randint(0, 1001, (64,), generator=g)
+        assert dp.assert_replicas_in_sync([xyz, op, idx])
+        ex = dp.FactoredExchange(1001, 16, "cpu", capacity=1100)
+        ex.resize(1051)                               # int(1.05 * 1001): ragged
+        assert all(v.data_ptr() % 16 == 0 for k, v in ex.grads.items() if k != "sh")
+        if r == 1:
+            xyz.view(torch.int32)[500, 1] ^= 1        # one mantissa bit on one rank
+        try:
+            dp.assert_replicas_in_sync([xyz, op, idx])
+            raised = False
+        except RuntimeError as ex_:
+            raised = "out of lock step" in str(ex_)
+        assert raised
+        # a different Gaussian count (one rank grew, the other did not) is caught as well
+        try:
+            dp.assert_replicas_in_sync([op[: 1001 - r]])
+            raised = False
+        except RuntimeError:
+            raised = True
+        assert raised
+        dist.destroy_process_group()
+        open(os.path.join({str(tmp_path)!r}, f"ok{{r}}"), "w").write("ok")
+    """))
+    port = _free_port()
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
+                         capture_output=True, text=True, timeout=240)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+
+
 def test_camera_conventions():
     cam = gs_synth.look_at_camera((0.0, 0.0, -4.0), (0.0, 0.0, 0.0), 64, 48, 0.8)
     V = cam["viewmatrix"]            # transposed storage: element [4*i+j] of the transposed matrix

@@ -71,6 +71,105 @@ def train_replica_check(args, C, dp, s, cam_t, dev, rank, world, P, W, H):
             "rank0_losses": losses}
 
 
+def mcmc_lockstep_check(args, dp, dev, rank, world):
+    """Multi-rank MCMC lock step (SURVEY.md 5 last row; north_star "allreducing the per-Gaussian gradients and MCMC
+    statistics"): every rank runs the REFERENCE's own GaussianModel (scene/gaussian_model_static.py, staged unmodified
+    under baseline/_ref/py) as a replica - its activations, `relocate_gs`, `add_new_gs`, optimizer surgery - renders its own
+    view through dp.ViewParallelRasterizer, and applies the summed gradients with FusedAdam and the reference's inline noise
+    (train_static.py:132-140, torch.randn_like on the identically seeded device RNG). Every `interval` steps: relocation +
+    5 % growth (torch.multinomial / bincount, :412-422, :458-492), then ViewParallelRasterizer.resize(P) and
+    dp.assert_replicas_in_sync. The replicas must stay bit-identical throughout without any broadcast."""
+    import types
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import refenv
+    refenv.install()
+    import gs_synth
+    import scene.gaussian_model_static as gm_static
+    import utils.graphics_utils as graphics_utils
+    from scene.gaussian_model import build_scaling_rotation
+    from arguments import OptimizationParams
+    from diff_gaussian_rasterization import GaussianRasterizationSettings
+    from diff_gaussian_rasterization import loss as fused_loss
+    from diff_gaussian_rasterization.optim import FusedAdam
+
+    P0, cap, W, H = args.mcmc_P, int(args.mcmc_P * 1.18), args.width, args.height
+    ap = argparse.ArgumentParser()
+    opt = OptimizationParams(ap).extract(ap.parse_args([]))
+    truth = gs_synth.to_torch(gs_synth.scene_garden(P0, 1), dev)
+    cams = [gs_synth.to_torch(c, dev) for c in gs_synth.orbit_cameras(16, 6.0, W, H, 1.2, 20.0)]
+    bg = torch.zeros(3, device=dev)
+    from diff_gaussian_rasterization import GaussianRasterizer
+    gts = []
+    for c in cams:
+        st = GaussianRasterizationSettings(H, W, c["tanfovx"], c["tanfovy"], bg, 1.0, c["viewmatrix"], c["projmatrix"], 3, c["campos"], False, False)
+        with torch.no_grad():
+            gts.append(GaussianRasterizer(st)(means3D=truth["means3D"], means2D=torch.zeros_like(truth["means3D"]), shs=truth["shs"],
+                                              opacities=truth["opacities"], scales=truth["scales"], rotations=truth["rotations"])[0].clamp(0, 1))
+    rng = np.random.default_rng(4)
+    pts = (truth["means3D"].cpu().numpy() + rng.normal(0, 0.02, (P0, 3))).astype(np.float32)
+    pcd = graphics_utils.BasicPointCloud(points=pts, colors=rng.uniform(0, 1, (P0, 3)).astype(np.float32), normals=np.zeros((P0, 3), np.float32))
+    torch.manual_seed(0)                                  # safe_state() seeds every process alike (utils/general_utils.py:133-136)
+    g = gm_static.GaussianModel(3)
+    g.create_from_pcd(pcd, 1.0)
+    with torch.no_grad():
+        g._opacity[::9] = -7.0                             # some dead from the start, so that relocation has work
+    saved = torch.optim.Adam
+    torch.optim.Adam = FusedAdam
+    try:
+        g.training_setup(opt)
+    finally:
+        torch.optim.Adam = saved
+    g.active_sh_degree = 3
+    vp = dp.ViewParallelRasterizer(P0, 16, dev, capacity=cap)
+    params = lambda: [g._xyz, g._features_dc, g._features_rest, g._opacity, g._scaling, g._rotation]  # noqa: E731
+    state = lambda: [t for grp in g.optimizer.param_groups for t in (g.optimizer.state[grp["params"][0]]["exp_avg"],  # noqa: E731
+                                                                      g.optimizer.state[grp["params"][0]]["exp_avg_sq"])]
+    relocations = grown = 0
+    sizes, losses = [P0], []
+    for it in range(1, args.mcmc_steps + 1):
+        xyz_lr = g.update_learning_rate(it)
+        view = (it * world + rank) % len(cams)
+        c = cams[view]
+        cv = torch.stack([cams[(it * world + r) % len(cams)]["campos"] for r in range(world)])
+        settings = GaussianRasterizationSettings(H, W, c["tanfovx"], c["tanfovy"], bg, 1.0, c["viewmatrix"], c["projmatrix"], 3, c["campos"], False, False)
+        means2D = torch.zeros_like(g.get_xyz, requires_grad=True)
+        image = vp(settings, cv, g.get_xyz, means2D, g.get_opacity, g.get_features, g.get_scaling, g.get_rotation)[0]
+        loss = fused_loss.photometric_loss(image, gts[view], opt.lambda_dssim) / world
+        loss = loss + opt.opacity_reg * torch.abs(g.get_opacity).mean() + opt.scale_reg * torch.abs(g.get_scaling).mean()
+        loss.backward()
+        losses.append(float(loss.item()))
+        with torch.no_grad():
+            if it % args.mcmc_interval == 0:
+                dead = (g.get_opacity <= 0.005).squeeze(-1)
+                n_dead = int(dead.sum())
+                g.relocate_gs(dead_mask=dead)
+                added = g.add_new_gs(cap_max=cap)
+                relocations += n_dead
+                grown += int(added)
+                vp.resize(g.get_xyz.shape[0])
+                sizes.append(int(g.get_xyz.shape[0]))
+                dp.assert_replicas_in_sync(params() + state(), what=f"replicas after relocation/growth at step {it}")
+            g.optimizer.step()
+            g.optimizer.zero_grad(set_to_none=True)
+            L = build_scaling_rotation(g.get_scaling, g.get_rotation)
+            cov = L @ L.transpose(1, 2)
+            noise = torch.randn_like(g._xyz) * (1 / (1 + torch.exp(-100 * ((1 - g.get_opacity) - 0.995)))) * opt.noise_lr * xyz_lr
+            g._xyz.add_(torch.bmm(cov, noise.unsqueeze(-1)).squeeze(-1))
+    torch.cuda.synchronize()
+    ident = {}
+    for name, t in zip(("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation"), params()):
+        h = dp.replica_fingerprint([t]).to(dev)
+        hs = [torch.zeros_like(h) for _ in range(world)]
+        dist.all_gather(hs, h)
+        ident[name] = all(bool((x == hs[0]).all()) for x in hs)
+    dp.assert_replicas_in_sync(params() + state(), what="replicas at the end of the run")
+    return {"steps": args.mcmc_steps, "interval": args.mcmc_interval, "relocations": relocations, "grown_by": grown, "sizes": sizes,
+            "ragged_sizes": [s_ for s_ in sizes if s_ % 4], "identical_on_all_ranks": ident, "transport": vp.exchange.transport,
+            "multicast": bool(getattr(vp.exchange, "_multicast", False)), "model": "reference GaussianModel (baseline/_ref/py), unmodified",
+            "rank0_first_last_loss": [losses[0], losses[-1]]}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--P", type=int, default=300000)
@@ -82,6 +181,12 @@ def main():
     ap.add_argument("--train-steps", type=int, default=0,
                     help="also run this many full training iterations (activations, render, loss, exchange, Adam, noise) and "
                          "check that the replicated parameters stay bit-identical on all ranks")
+    ap.add_argument("--mcmc-steps", type=int, default=0,
+                    help="run this many training iterations of the reference's own GaussianModel as replicas, with relocation + "
+                         "growth + resize every --mcmc-interval steps, and check that they stay bit-identical")
+    ap.add_argument("--mcmc-interval", type=int, default=5)
+    ap.add_argument("--mcmc-P", type=int, default=100003)
+    ap.add_argument("--skip-exchange", action="store_true", help="only the --train-steps / --mcmc-steps checks")
     args = ap.parse_args()
     import gs_synth
     from diff_gaussian_rasterization import _native as C, dp
@@ -137,7 +242,7 @@ def main():
     def rel(a, b):
         return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30))
 
-    for transport in args.transports.split(","):
+    for transport in ([] if args.skip_exchange else args.transports.split(",")):
         try:
             ex = dp.FactoredExchange(P, 16, dev, transport=transport.split("-")[0],
                                      multicast=False if transport.endswith("-p2p") else None)
@@ -192,6 +297,8 @@ def main():
             out[f"factored_{transport}"] = {"error": repr(ex_)[:400]}
     if args.train_steps > 0:
         out["train_replicas"] = train_replica_check(args, C, dp, s, cam_t, dev, rank, world, P, W, H)
+    if args.mcmc_steps > 0:
+        out["mcmc_lockstep"] = mcmc_lockstep_check(args, dp, dev, rank, world)
     if rank == 0:
         print(json.dumps(out), flush=True)
     dist.barrier()
