@@ -147,8 +147,7 @@ int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means
     tiles_of(W, H, &pp.grid);
     pp.prefiltered = prefiltered;
     pp.rot_aligned = is_aligned16(rotations) ? 1 : 0;
-    pp.radii = radii; pp.is_used = is_used; pp.means2D = g.means2D; pp.depths = g.depths; pp.cov3D = g.cov3D;
-    pp.rgb = g.rgb; pp.conic_opacity = g.conic_opacity; pp.tiles_touched = g.tiles_touched; pp.clamped = g.clamped;
+    pp.radii = radii; pp.is_used = is_used; pp.cov3D = g.cov3D; pp.clamped = g.clamped;
     pp.rec = g.rec; pp.depth_keys = g.dkeys_a; pp.num_rendered = g.num_rendered;
     pp.rect = g.rect;
     prof_mark(stream, -1);
@@ -200,7 +199,7 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
         // Generic path (tile ids wider than two binning digits): emission, multi-pass radix sort, range detection.
         const int passes = sort_passes(tiles);
         if (R > 0) {
-            rc = launch_emit_instances(P, g.dkeys_a, g.means2D, g.point_offsets, radii, grid, b.inst_a, stream);
+            rc = launch_emit_instances(P, g.emit, grid, b.inst_a, stream);
             if (rc) return rc;
             prof_mark(stream, ST_DUPLICATE);
             rc = launch_radix_sort(b.inst_a, b.inst_b, R, 32, passes, b.sort_scratch, b.error_flag, stream);
@@ -682,13 +681,19 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const v
         GeomWS g = GeomWS::carve(aligned_base(geom_ws), Ps);
         switch (which) {
             case 31: src = g.num_rendered + 1; n = 4; break;
-            case 0: src = g.depths; n = Ps * 4; break;
+            case 0: case 3: case 5: case 6: case 7: {
+                // the reference's per-Gaussian arrays, unpacked from the render records / tile rectangles (zeros for
+                // Gaussians that are not visible: the forward writes no record for them)
+                static const size_t width[8] = {4, 0, 0, 8, 0, 16, 12, 4};
+                n = Ps * width[which];
+                if (dst && n > 0 && n <= max_bytes) {
+                    if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+                    if (launch_debug_unpack(which, (uint32_t)P, g.rec, g.rect, dst)) return -1;
+                }
+                return (long long)n;
+            }
             case 1: src = g.clamped; n = Ps; break;
-            case 3: src = g.means2D; n = Ps * 8; break;
             case 4: src = g.cov3D; n = Ps * 24; break;
-            case 5: src = g.conic_opacity; n = Ps * 16; break;
-            case 6: src = g.rgb; n = Ps * 12; break;
-            case 7: src = g.tiles_touched; n = Ps * 4; break;
             case 8: src = g.point_offsets; n = Ps * 4; break;
             case 2: src = g.rec; n = Ps * sizeof(SplatRec); break;
             case 9:  // Gaussian indices in (depth, index) order; culled ones last
@@ -712,7 +717,7 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const v
                 GeomWS g = GeomWS::carve(aligned_base(geom_ws), Ps);
                 ImageWS im = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
                 if (cudaDeviceSynchronize() != cudaSuccess) return -1;
-                if (launch_debug_expand(tiles, im.ranges, b.ids, g.depths, which == 12 ? (uint64_t*)dst : nullptr,
+                if (launch_debug_expand(tiles, im.ranges, b.ids, g.rec, which == 12 ? (uint64_t*)dst : nullptr,
                                         which == 13 ? (uint64_t*)dst : nullptr))
                     return -1;
             }

@@ -146,32 +146,21 @@ int launch_inclusive_scan(const uint2* rect, const uint64_t* order, int n, uint3
 // ------------------------------------------------------------------------------------------------
 constexpr uint32_t kCoopTiles = 16;
 
-__global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint64_t* __restrict__ depth_order,
-                                                             const float2* __restrict__ means2D,
-                                                             const uint32_t* __restrict__ offsets,
-                                                             const int* __restrict__ radii, uint2 grid,
+__global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint4* __restrict__ emit, uint2 grid,
                                                              uint64_t* __restrict__ inst) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
-    uint32_t off = 0, w = 0, h = 0, idx = 0;
-    uint2 rmin = {0, 0}, rmax = {0, 0};
+    uint32_t off = 0, w = 0, h = 0, idx = 0, x0 = 0, y0 = 0;
     if (r < P) {
-        const uint64_t dk = depth_order[r];
-        idx = (uint32_t)dk;
-        const int rad = (uint32_t)(dk >> 32) != 0xffffffffu ? radii[idx] : 0;
-        if (rad > 0) {
-            off = (r == 0) ? 0 : offsets[r - 1];
-            tile_rect(means2D[idx], rad, rmin, rmax, grid);
-            w = rmax.x - rmin.x;
-            h = rmax.y - rmin.y;
-        }
+        const uint4 E = emit[r];   // (idx, x0 | y0 << 16, w | h << 16, first slot) of the Gaussian of depth rank r
+        idx = E.x; x0 = E.y & 0xffffu; y0 = E.y >> 16; w = E.z & 0xffffu; h = E.z >> 16; off = E.w;
     }
     const uint32_t n = w * h;
     // Small footprints: serial emission by the owning lane.
     if (n > 0 && n <= kCoopTiles) {
         uint32_t o = off;
-        for (uint32_t y = rmin.y; y < rmax.y; ++y)
-            for (uint32_t x = rmin.x; x < rmax.x; ++x) inst[o++] = ((uint64_t)(y * grid.x + x) << 32) | idx;
+        for (uint32_t y = y0; y < y0 + h; ++y)
+            for (uint32_t x = x0; x < x0 + w; ++x) inst[o++] = ((uint64_t)(y * grid.x + x) << 32) | idx;
     }
     // Large footprints: the warp emits them together.
     uint32_t big = __ballot_sync(0xffffffffu, n > kCoopTiles);
@@ -181,8 +170,8 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint64
         const uint32_t s_off = __shfl_sync(0xffffffffu, off, src);
         const uint32_t s_w = __shfl_sync(0xffffffffu, w, src);
         const uint32_t s_n = __shfl_sync(0xffffffffu, n, src);
-        const uint32_t s_x0 = __shfl_sync(0xffffffffu, rmin.x, src);
-        const uint32_t s_y0 = __shfl_sync(0xffffffffu, rmin.y, src);
+        const uint32_t s_x0 = __shfl_sync(0xffffffffu, x0, src);
+        const uint32_t s_y0 = __shfl_sync(0xffffffffu, y0, src);
         const uint32_t s_idx = __shfl_sync(0xffffffffu, idx, src);
         for (uint32_t t = lane; t < s_n; t += 32) {
             const uint32_t ty = t / s_w, tx = t - ty * s_w;
@@ -191,10 +180,9 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint64
     }
 }
 
-int launch_emit_instances(int P, const uint64_t* depth_order, const float2* means2D, const uint32_t* offsets,
-                          const int* radii, uint2 grid, uint64_t* inst, cudaStream_t stream) {
+int launch_emit_instances(int P, const uint4* emit, uint2 grid, uint64_t* inst, cudaStream_t stream) {
     if (P <= 0) return GS_OK;
-    emit_instances_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, depth_order, means2D, offsets, radii, grid, inst);
+    emit_instances_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, emit, grid, inst);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
@@ -909,21 +897,50 @@ int launch_strip_ids(uint32_t n, const uint64_t* in, uint32_t* out, cudaStream_t
 // keys (tile << 32 | depth_bits) and raw instances (tile << 32 | idx), rebuilt from the ranges and the ids.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) debug_expand_kernel(uint32_t tiles, const uint2* __restrict__ ranges,
-                                                           const uint32_t* __restrict__ ids, const float* __restrict__ depths,
+                                                           const uint32_t* __restrict__ ids, const SplatRec* __restrict__ rec,
                                                            uint64_t* __restrict__ keys, uint64_t* __restrict__ raw) {
     const uint32_t tile = blockIdx.x;
     if (tile >= tiles) return;
     const uint2 rg = ranges[tile];
     for (uint32_t i = rg.x + threadIdx.x; i < rg.y; i += blockDim.x) {
         const uint32_t id = ids[i];
-        if (keys) keys[i] = ((uint64_t)tile << 32) | __float_as_uint(depths[id]);
+        if (keys) keys[i] = ((uint64_t)tile << 32) | __float_as_uint(rec[id].depth);
         if (raw) raw[i] = ((uint64_t)tile << 32) | id;
     }
 }
 
-int launch_debug_expand(uint32_t tiles, const uint2* ranges, const uint32_t* ids, const float* depths, uint64_t* keys, uint64_t* raw) {
+int launch_debug_expand(uint32_t tiles, const uint2* ranges, const uint32_t* ids, const SplatRec* rec, uint64_t* keys, uint64_t* raw) {
     if (tiles == 0) return GS_OK;
-    debug_expand_kernel<<<tiles, 256>>>(tiles, ranges, ids, depths, keys, raw);
+    debug_expand_kernel<<<tiles, 256>>>(tiles, ranges, ids, rec, keys, raw);
+    GS_LAUNCH_CHECK();
+    GS_CUDA_TRY(cudaDeviceSynchronize());
+    return GS_OK;
+}
+
+// The reference's per-Gaussian state arrays unpacked from the render records (which: 0 depths, 3 means2D, 5 conic_opacity,
+// 6 rgb) and the tile rectangles (7 tiles_touched). Gaussians without a record (culled) read as zeros.
+__global__ void __launch_bounds__(256) debug_unpack_kernel(int which, uint32_t P, const SplatRec* __restrict__ rec,
+                                                            const uint2* __restrict__ rect, void* __restrict__ dst) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const uint2 rc = rect[i];
+    const bool vis = rc.y != 0u;
+    SplatRec r = {};
+    if (vis) r = rec[i];
+    float* f = reinterpret_cast<float*>(dst);
+    switch (which) {
+        case 0: f[i] = r.depth; break;
+        case 3: f[2 * i] = r.x; f[2 * i + 1] = r.y; break;
+        case 5: f[4 * i] = r.A; f[4 * i + 1] = r.B; f[4 * i + 2] = r.C; f[4 * i + 3] = r.opacity; break;
+        case 6: f[3 * i] = r.r; f[3 * i + 1] = r.g; f[3 * i + 2] = r.b; break;
+        case 7: reinterpret_cast<uint32_t*>(dst)[i] = rect_tiles(rc); break;
+        default: break;
+    }
+}
+
+int launch_debug_unpack(int which, uint32_t P, const SplatRec* rec, const uint2* rect, void* dst) {
+    if (P == 0) return GS_OK;
+    debug_unpack_kernel<<<(P + 255) / 256, 256>>>(which, P, rec, rect, dst);
     GS_LAUNCH_CHECK();
     GS_CUDA_TRY(cudaDeviceSynchronize());
     return GS_OK;

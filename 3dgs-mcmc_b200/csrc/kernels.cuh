@@ -26,12 +26,7 @@ struct PreprocessParams {
     // outputs
     int* __restrict__ radii;
     int* __restrict__ is_used;
-    float2* __restrict__ means2D;
-    float* __restrict__ depths;
     float* __restrict__ cov3D;
-    float* __restrict__ rgb;
-    float4* __restrict__ conic_opacity;
-    uint32_t* __restrict__ tiles_touched;
     uint8_t* __restrict__ clamped;
     SplatRec* __restrict__ rec;          // [P] render records (visible Gaussians only)
     uint64_t* __restrict__ depth_keys;   // [P] (depth_bits << 32 | idx); depth_bits = ~0 when culled
@@ -170,12 +165,12 @@ int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1
                         const uint32_t* offsets, const BinningWS& b, uint2* ranges, cudaStream_t stream);
 int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* scratch, cudaStream_t stream);
 int launch_strip_ids(uint32_t n, const uint64_t* in, uint32_t* out, cudaStream_t stream);
-int launch_emit_instances(int P, const uint64_t* depth_order, const float2* means2D, const uint32_t* offsets,
-                          const int* radii, uint2 grid, uint64_t* inst, cudaStream_t stream);
+int launch_emit_instances(int P, const uint4* emit, uint2 grid, uint64_t* inst, cudaStream_t stream);
 int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, int first_bit, int passes, char* scratch,
                       uint32_t* error_flag, cudaStream_t stream);
 int launch_tile_ranges(uint32_t R, const uint64_t* inst, uint2* ranges, uint32_t tiles, cudaStream_t stream);
-int launch_debug_expand(uint32_t tiles, const uint2* ranges, const uint32_t* ids, const float* depths, uint64_t* keys, uint64_t* raw);
+int launch_debug_expand(uint32_t tiles, const uint2* ranges, const uint32_t* ids, const SplatRec* rec, uint64_t* keys, uint64_t* raw);
+int launch_debug_unpack(int which, uint32_t P, const SplatRec* rec, const uint2* rect, void* dst);
 int launch_debug_low32(uint32_t n, const uint64_t* in, uint32_t* out);
 int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream);
 int launch_render_bwd(const RenderBwdParams& p, int tiles, cudaStream_t stream);

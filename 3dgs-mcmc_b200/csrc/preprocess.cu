@@ -219,18 +219,12 @@ __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const Prepro
                 const float* my_sh = staged ? tile + lane * row_stride : p.shs + i * Mrow;
                 c = sh_to_rgb<false>(p.D, V3(p_orig.x, p_orig.y, p_orig.z), campos, my_sh, cb);
             }
-            p.rgb[3 * i + 0] = c.x;
-            p.rgb[3 * i + 1] = c.y;
-            p.rgb[3 * i + 2] = c.z;
             p.clamped[idx] = cb;
             col = make_float3(c.x, c.y, c.z);
         } else {
             col = make_float3(p.colors_precomp[3 * i], p.colors_precomp[3 * i + 1], p.colors_precomp[3 * i + 2]);
         }
         const float opacity = p.opacities[idx];
-        p.depths[idx] = p_view.z;
-        p.means2D[idx] = point_image;
-        p.conic_opacity[idx] = {conic.x, conic.y, conic.z, opacity};
         // Render record. thr is a conservative reject threshold: power < thr  ==>  opacity * expf(power) < 1/255
         // (1e-3 slack in the exponent, far above the expf / logf / product rounding errors), so the renderers can
         // skip expf — and whole pixel patches — for such pairs without changing any decision.
@@ -249,7 +243,6 @@ __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const Prepro
     if (valid) {
         p.is_used[idx] = 0;
         p.radii[idx] = out_radius;
-        p.tiles_touched[idx] = out_tiles;
         p.rect[idx] = out_rect;
         p.depth_keys[idx] = ((uint64_t)depth_bits << 32) | (uint32_t)idx;
     }

@@ -70,14 +70,11 @@ static_assert(sizeof(SplatRec) == 48, "SplatRec must be 48 bytes");
 
 // Per-Gaussian state written by preprocess, read by binning / render / backward.
 struct GeomWS {
-    float* depths;            // [P]   view-space z
-    float2* means2D;          // [P]   pixel coordinates
-    float4* conic_opacity;    // [P]   (A, B, C, opacity)
-    float* rgb;               // [3P]  clamped SH colour
-    float* cov3D;             // [6P]  upper triangle of Sigma
-    SplatRec* rec;            // [P]   48-byte render record of every visible Gaussian (what the tile renderers gather)
+    float* cov3D;             // [6P]  upper triangle of Sigma (read again by the per-Gaussian backward)
+    SplatRec* rec;            // [P]   48-byte render record of every visible Gaussian: pixel mean, conic, opacity, colour,
+                              //       depth - what the tile renderers gather; the reference's separate depths / means2D /
+                              //       conic_opacity / rgb arrays are NOT kept (gs_debug_fetch unpacks them from here)
     uint8_t* clamped;         // [P]   bit c set when channel c was clamped to 0
-    uint32_t* tiles_touched;  // [P]
     uint32_t* point_offsets;  // [P]   inclusive scan of tiles_touched taken in depth order
     uint32_t* scan_block_sums;  // [ceil(P/kScanBlock)+1]
     uint32_t* num_rendered;   // [0] device copy of R, [1] depth-sort error flag
@@ -92,14 +89,9 @@ struct GeomWS {
     __host__ static GeomWS carve(char* base, size_t P) {
         Carver c(base);
         GeomWS g;
-        g.depths = c.take<float>(P);
-        g.means2D = c.take<float2>(P);
-        g.conic_opacity = c.take<float4>(P);
-        g.rgb = c.take<float>(3 * P);
         g.cov3D = c.take<float>(6 * P);
         g.rec = c.take<SplatRec>(P);
         g.clamped = c.take<uint8_t>(P);
-        g.tiles_touched = c.take<uint32_t>(P);
         g.point_offsets = c.take<uint32_t>(P);
         g.scan_block_sums = c.take<uint32_t>((P + kScanBlock - 1) / kScanBlock + 1);
         g.num_rendered = c.take<uint32_t>(4);
