@@ -65,7 +65,7 @@ inline void count_launches(int k) { g_prof.launches += (unsigned long long)k; }
 
 extern "C" {
 
-int gs_abi_version(void) { return 104; }
+int gs_abi_version(void) { return 105; }
 
 const char* gs_error_string(int code) {
     if (code == GS_OK) return "ok";
@@ -109,8 +109,8 @@ unsigned long long gs_launch_count(void) { return g_prof.launches; }
 
 size_t gs_geom_bytes(int P) { return GeomWS::carve(nullptr, (size_t)(P > 0 ? P : 0)).bytes + kAlign; }
 size_t gs_image_bytes(int W, int H) { return ImageWS::carve(nullptr, (size_t)W, (size_t)H).bytes + kAlign; }
-size_t gs_binning_bytes(unsigned int R, int W, int H) {
-    return BinningWS::carve(nullptr, R, tiles_of(W, H, nullptr)).bytes + kAlign;
+size_t gs_binning_bytes(unsigned int R, int W, int H, int P) {
+    return BinningWS::carve(nullptr, R, tiles_of(W, H, nullptr), (size_t)(P > 0 ? P : 0)).bytes + kAlign;
 }
 size_t gs_backward_scratch_bytes(int P) { return BwdScratch::carve(nullptr, (size_t)(P > 0 ? P : 0)).bytes + kAlign; }
 
@@ -181,13 +181,13 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
     const uint32_t tiles = tiles_of(W, H, &grid);
     ImageWS img = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
-    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, tiles);
+    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, tiles, (size_t)(P > 0 ? P : 0));
     if (P == 0) R = 0;
 
     int rc = GS_OK;
     prof_mark(stream, -1);
     if (P > 0) GS_CUDA_TRY(cudaMemsetAsync(b.error_flag, 0, 16, stream));
-    if (P > 0 && bin_fast_path(tiles)) {
+    if (P > 0 && bin_fast_path(tiles, (size_t)P)) {
         // Two fused binning passes (count -> scan -> scatter each); the tile ranges fall out of the second count.
         int bits1, bits2;
         bin_digit_bits(tiles, &bits1, &bits2);
@@ -236,7 +236,7 @@ int gs_backward_render(void* stream_, int P, unsigned int R, int W, int H, const
     const uint32_t tiles = tiles_of(W, H, &grid);
     ImageWS img = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
-    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, tiles);
+    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, tiles, (size_t)(P > 0 ? P : 0));
     BwdScratch sc = BwdScratch::carve(aligned_base(scratch), (size_t)P);
     prof_mark(stream, -1);
     GS_CUDA_TRY(cudaMemsetAsync(sc.acc_color_opacity, 0, sc.bytes, stream));
@@ -263,7 +263,7 @@ int gs_debug_render_work(void* stream_, int P, unsigned int R, int W, int H, con
     const uint32_t tiles = tiles_of(W, H, &grid);
     ImageWS img = ImageWS::carve(aligned_base(image_ws), (size_t)W, (size_t)H);
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
-    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, tiles);
+    BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, tiles, (size_t)(P > 0 ? P : 0));
     RenderBwdParams rb = {};
     rb.ranges = img.ranges; rb.ids = b.ids; rb.rec = g.rec; rb.W = W; rb.H = H; rb.tiles_x = (int)grid.x; rb.n_contrib = img.n_contrib;
     return launch_render_work(rb, (int)tiles, walked_per_tile, evaluated_per_tile, stream);
@@ -707,7 +707,7 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const v
         }
     } else if (which < 20 || which == 30) {
         if (!binning_ws) return -1;
-        BinningWS b = BinningWS::carve(aligned_base(binning_ws), Rs, tiles);
+        BinningWS b = BinningWS::carve(aligned_base(binning_ws), Rs, tiles, Ps);
         if (which == 12 || which == 13) {
             // Views of the sorted list in the reference's key format (tile << 32 | depth_bits) / as raw instances
             // (tile << 32 | idx), rebuilt from the tile ranges and the sorted ids.

@@ -19,6 +19,8 @@
 #include "kernels.cuh"
 #include "workspace.cuh"
 
+#include <cstdlib>
+
 namespace gs {
 
 // ------------------------------------------------------------------------------------------------
@@ -582,18 +584,38 @@ __global__ void __launch_bounds__(1024) bin_scan_kernel(uint32_t* __restrict__ h
     if (!do_ranges && tid == 0) totals[blockIdx.x] = carry;
 }
 
+// Pass-1 output word: (high tile digit << kshift) | idx with kshift = 32 - bits2. The low digit of element e is implied by
+// its position: pass 1 wrote digit d's run at [start[d], start[d + 1]), start = exclusive scan of the pass-1 digit totals.
+//
 // hist[d][b] = number of keys of block b with high digit d; tile_counts[tile] += per-tile counts of the block.
-__global__ void __launch_bounds__(kBinThreads) bin_count2_kernel(const uint64_t* __restrict__ keys, uint32_t R, int bits1, int bits2,
-                                                                  uint32_t* __restrict__ hist, uint32_t nb,
-                                                                  uint32_t* __restrict__ tile_counts) {
+__global__ void __launch_bounds__(kBinThreads) bin_count2_kernel(const uint32_t* __restrict__ keys, uint32_t R, int bits1, int bits2,
+                                                                  const uint32_t* __restrict__ totals1, uint32_t* __restrict__ hist,
+                                                                  uint32_t nb, uint32_t* __restrict__ tile_counts) {
     __shared__ uint32_t s_t[kTileSpan][256];
+    __shared__ uint32_t s_start[257];     // exclusive scan of the pass-1 digit totals (+ R at [bins1])
+    __shared__ uint32_t s_scan[33];
     __shared__ uint32_t s_lo[2];
     const int tid = threadIdx.x;
     const uint32_t b = blockIdx.x;
     const uint32_t slot_begin = b * (uint32_t)kBinTile, n = min((uint32_t)kBinTile, R - slot_begin);
-    const uint32_t mask1 = (1u << bits1) - 1u;
+    const int bins1 = 1 << bits1;
+    const int kshift = 32 - bits2;
     for (int i = tid; i < kTileSpan * 256; i += kBinThreads) (&s_t[0][0])[i] = 0;
-    if (tid < 2) s_lo[tid] = (uint32_t)(keys[(size_t)slot_begin + (tid ? n - 1 : 0)] >> 32) & mask1;
+    {
+        const uint32_t v = tid < bins1 ? totals1[tid] : 0u;
+        uint32_t total;
+        const uint32_t ex = block_excl_scan(v, s_scan, &total);
+        s_start[tid] = ex;                       // entries >= bins1 hold R: the searches below stop there
+        if (tid == 0) s_start[256] = total;
+    }
+    __syncthreads();
+    // low digits of the block's first and last slot: the largest d with start[d] <= slot (thread d checks its own run)
+    if (tid < bins1) {
+        const uint32_t lo = s_start[tid], hi = s_start[tid + 1];
+        if (lo <= slot_begin && slot_begin < hi) s_lo[0] = (uint32_t)tid;
+        const uint32_t last = slot_begin + n - 1u;
+        if (lo <= last && last < hi) s_lo[1] = (uint32_t)tid;
+    }
     __syncthreads();
     // The keys are sorted by the low digit: the block holds low digits lmin..lmax only.
     const uint32_t lmin = s_lo[0], span = s_lo[1] - lmin + 1u;
@@ -602,13 +624,22 @@ __global__ void __launch_bounds__(kBinThreads) bin_count2_kernel(const uint64_t*
     for (int i = 0; i < kBinItems; ++i) {
         const uint32_t e = i * kBinThreads + tid;
         if (e < n) {
-            const uint32_t tile = (uint32_t)(keys[(size_t)slot_begin + e] >> 32);
-            const uint32_t hi = tile >> bits1;
+            const uint32_t pos = slot_begin + e;
+            const uint32_t hi = keys[(size_t)pos] >> kshift;
             if (compact) {
-                atomicAdd(&s_t[(tile & mask1) - lmin][hi], 1u);
+                uint32_t l = 0;
+#pragma unroll
+                for (int k = 1; k < kTileSpan; ++k) l += (k < (int)span && s_start[lmin + k] <= pos) ? 1u : 0u;
+                atomicAdd(&s_t[l][hi], 1u);
             } else {
+                // many short runs in one block (tiny scenes): binary search for the run that holds pos
+                uint32_t lo_d = lmin, hi_d = lmin + span - 1u;
+                while (lo_d < hi_d) {
+                    const uint32_t mid = (lo_d + hi_d + 1u) >> 1;
+                    if (s_start[mid] <= pos) lo_d = mid; else hi_d = mid - 1u;
+                }
                 atomicAdd(&s_t[0][hi], 1u);
-                atomicAdd(tile_counts + tile, 1u);
+                atomicAdd(tile_counts + ((hi << bits1) | lo_d), 1u);
             }
         }
     }
@@ -633,11 +664,14 @@ struct BinScatterParams {
     const uint32_t* __restrict__ block_first;
     const uint32_t* __restrict__ block_last;
     uint32_t grid_x;
-    // pass 2 input
+    // pass 0 (depth ordering of the Gaussians): u64 keys in and out, digit in the upper word
     const uint64_t* __restrict__ keys_in;
-    // outputs
-    uint64_t* __restrict__ keys_out;         // pass 1
-    uint32_t* __restrict__ ids_out;          // pass 2
+    uint64_t* __restrict__ keys_out;
+    // pass 1 output / pass 2 input: (high tile digit << kshift) | idx
+    const uint32_t* __restrict__ keys32_in;
+    uint32_t* __restrict__ keys32_out;
+    int kshift;                              // 32 - bits2
+    uint32_t* __restrict__ ids_out;          // pass 2 output
     uint32_t n;                              // R
     uint32_t nb;
     int shift, bits;                         // digit = (tile >> shift) & (2^bits - 1)
@@ -645,15 +679,26 @@ struct BinScatterParams {
     const uint32_t* __restrict__ totals;     // [2^bits] digit totals
 };
 
-template <int PASS, int BITS>
-__global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinScatterParams p) {
-    __shared__ __align__(16) uint64_t s_keys[kBinTile];              // 32 KB (pass 1 first uses it as u16 owner[kBinTile])
+template <int PASS>
+struct BinKey { using type = uint32_t; };
+template <>
+struct BinKey<0> { using type = uint64_t; };
+
+// PASS 0: u64 keys (depth_bits << 32 | idx), digit = BITS bits of the upper word at p.shift      (depth ordering)
+// PASS 1: slots expanded from the emission table, digit = low BITS bits of the tile id; writes (high digit << kshift) | idx
+// PASS 2: those 32-bit words, digit = word >> kshift (the high tile digit); writes the Gaussian index
+template <int PASS, int BITS, int MINB = 4>
+__global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const BinScatterParams p) {
+    using Key = typename BinKey<PASS>::type;
+    __shared__ __align__(16) Key s_keys[kBinTile];                   // 32 / 16 KB (pass 1 first uses it as u16 owner[kBinTile])
+    __shared__ uint8_t s_dig[PASS == 1 ? kBinTile : 16];             // pass 1: the low digit travels beside the word, not in it
     __shared__ uint32_t s_hist[kBinThreads / 32][256];               // per-warp digit counts -> block positions
     __shared__ uint32_t s_gbase[256];                                // global position of slot 0 of each digit's run
     __shared__ uint32_t s_scan[33];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int bins = 1 << BITS;
+    constexpr uint32_t dmask = (uint32_t)bins - 1u;
     for (int i = tid; i < (kBinThreads / 32) * 256; i += kBinThreads) (&s_hist[0][0])[i] = 0;
     if (PASS == 1)
         for (int i = tid; i < kBinTile / 8; i += kBinThreads) reinterpret_cast<uint4*>(s_keys)[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -663,8 +708,11 @@ __global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinSc
     const uint32_t tile_n = min((uint32_t)kBinTile, p.n - slot_begin);
     const uint32_t warp_base = warp * (32 * kBinItems) + lane;   // item i of this thread is slot warp_base + 32 i
 
-    // ---- 1. keys into registers, warp-striped ----
-    uint64_t key[kBinItems];
+    // ---- 1. keys into registers, warp-striped; dig[k >> 2] byte (k & 3) = digit of item k ----
+    Key key[kBinItems];
+    uint32_t dig[kBinItems / 4];
+#pragma unroll
+    for (int q = 0; q < kBinItems / 4; ++q) dig[q] = 0u;
     if (PASS == 1) {
         uint16_t* s_owner = reinterpret_cast<uint16_t*>(s_keys);
         const uint32_t r0 = p.block_first[tile];
@@ -703,35 +751,42 @@ __global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinSc
 #pragma unroll
         for (int i = 0; i < kBinItems; ++i) {
             const uint32_t e = warp_base + i * 32;
-            key[i] = ~0ull;
+            key[i] = 0u;
             if (e < tile_n) {
                 const uint4 E = __ldg(p.emit + r0 + s_owner[e]);
                 const uint32_t t = slot_begin + e - E.w, w = E.z & 0xffffu;
                 const uint32_t ty = div_small(t, w, rcp_small(w));
                 const uint32_t tx = t - ty * w;
                 const uint32_t tl = ((E.y >> 16) + ty) * p.grid_x + (E.y & 0xffffu) + tx;
-                key[i] = ((uint64_t)tl << 32) | E.x;
+                key[i] = (Key)(((tl >> BITS) << p.kshift) | E.x);
+                dig[i >> 2] |= (tl & dmask) << (8 * (i & 3));
             }
         }
     } else {
 #pragma unroll
         for (int i = 0; i < kBinItems; ++i) {
             const uint32_t e = warp_base + i * 32;
-            key[i] = e < tile_n ? p.keys_in[(size_t)slot_begin + e] : ~0ull;
+            uint32_t d = 0u;
+            if (PASS == 0) {
+                key[i] = e < tile_n ? (Key)p.keys_in[(size_t)slot_begin + e] : (Key)~0ull;
+                d = (uint32_t)((uint64_t)key[i] >> (32 + p.shift)) & dmask;
+            } else {
+                key[i] = e < tile_n ? (Key)p.keys32_in[(size_t)slot_begin + e] : (Key)0u;
+                d = (uint32_t)key[i] >> p.kshift;
+            }
+            dig[i >> 2] |= (d & 0xffu) << (8 * (i & 3));
         }
     }
 
     // ---- 2. stable rank inside the warp: peer mask per item from ballots, running per-warp digit counters kept by
     //         one leader lane per distinct digit (plain LDS / STS; __syncwarp orders them between items) ----
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const uint32_t dmask = (uint32_t)bins - 1u;
-    const int dshift = 32 + p.shift;   // digits live in the upper word of the key (tile id / depth bits)
     uint16_t rank[kBinItems];
     uint32_t* const wh = s_hist[warp];
 #pragma unroll
     for (int k = 0; k < kBinItems; ++k) {
         const bool valid = warp_base + k * 32 < tile_n;
-        const uint32_t d = (uint32_t)(key[k] >> dshift) & dmask;   // invalid slots (all-ones key) are masked out below
+        const uint32_t d = (dig[k >> 2] >> (8 * (k & 3))) & 0xffu;   // invalid slots are masked out below
         const uint32_t peers = peer_mask<BITS>(d) & __ballot_sync(0xffffffffu, valid);
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
@@ -772,16 +827,28 @@ __global__ void __launch_bounds__(kBinThreads, 4) bin_scatter_kernel(const BinSc
 #pragma unroll
     for (int i = 0; i < kBinItems; ++i) {
         const uint32_t e = warp_base + i * 32;
-        if (e < tile_n) s_keys[s_hist[warp][(uint32_t)(key[i] >> dshift) & dmask] + rank[i]] = key[i];
+        if (e < tile_n) {
+            const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
+            const uint32_t at = s_hist[warp][d] + rank[i];
+            s_keys[at] = key[i];
+            if (PASS == 1) s_dig[at] = (uint8_t)d;
+        }
     }
     __syncthreads();
+    const uint32_t idmask = PASS == 2 ? ((p.kshift < 32 ? (1u << p.kshift) : 0u) - 1u) : 0u;
 #pragma unroll
     for (int i = 0; i < kBinItems; ++i) {
         const uint32_t s = i * kBinThreads + tid;
         if (s < tile_n) {
-            const uint64_t k = s_keys[s];
-            const uint32_t pos = s_gbase[(uint32_t)(k >> dshift) & dmask] + s;
-            if (PASS == 2) p.ids_out[pos] = (uint32_t)k; else p.keys_out[pos] = k;
+            const Key k = s_keys[s];
+            uint32_t d;
+            if (PASS == 0) d = (uint32_t)((uint64_t)k >> (32 + p.shift)) & dmask;
+            else if (PASS == 1) d = s_dig[s];
+            else d = (uint32_t)k >> p.kshift;
+            const uint32_t pos = s_gbase[d] + s;
+            if (PASS == 0) p.keys_out[pos] = (uint64_t)k;
+            else if (PASS == 1) p.keys32_out[pos] = (uint32_t)k;
+            else p.ids_out[pos] = (uint32_t)k & idmask;
         }
     }
 }
@@ -813,7 +880,10 @@ __global__ void __launch_bounds__(kBinThreads) bin_count_kernel(const uint64_t* 
 
 template <int PASS, int BITS>
 static void launch_scatter(const BinScatterParams& sp, uint32_t nb, cudaStream_t stream) {
-    bin_scatter_kernel<PASS, BITS><<<nb, kBinThreads, 0, stream>>>(sp);
+    // GS_BIN_MINB=5 (measurement): 5 resident CTAs per SM at 48 registers (more spills) instead of 4 at 64
+    static const int minb = [] { const char* e = getenv("GS_BIN_MINB"); return e ? atoi(e) : 4; }();
+    if (PASS != 0 && minb == 5) bin_scatter_kernel<PASS, BITS, 5><<<nb, kBinThreads, 0, stream>>>(sp);
+    else bin_scatter_kernel<PASS, BITS, 4><<<nb, kBinThreads, 0, stream>>>(sp);
 }
 template <int PASS>
 static int dispatch_scatter(int bits, const BinScatterParams& sp, uint32_t nb, cudaStream_t stream) {
@@ -844,13 +914,14 @@ int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1
     bin_scan_kernel<<<bins1, 1024, 0, stream>>>(b.hist1, nb, bins1, b.totals, nullptr, 0, nullptr);
     BinScatterParams sp;
     sp.emit = emit; sp.offsets = offsets; sp.block_first = b.block_first; sp.block_last = b.block_last; sp.grid_x = grid.x;
-    sp.keys_in = nullptr; sp.keys_out = b.keys1; sp.ids_out = nullptr; sp.n = R; sp.nb = nb;
+    sp.keys_in = nullptr; sp.keys_out = nullptr; sp.keys32_in = nullptr; sp.keys32_out = b.keys1; sp.kshift = 32 - bits2;
+    sp.ids_out = nullptr; sp.n = R; sp.nb = nb;
     sp.shift = 0; sp.bits = bits1; sp.scanned = b.hist1; sp.totals = b.totals;
     int rc = dispatch_scatter<1>(bits1, sp, nb, stream);
     if (rc) return rc;
-    bin_count2_kernel<<<nb, kBinThreads, 0, stream>>>(b.keys1, R, bits1, bits2, b.hist2, nb, b.tile_counts);
+    bin_count2_kernel<<<nb, kBinThreads, 0, stream>>>(b.keys1, R, bits1, bits2, b.totals, b.hist2, nb, b.tile_counts);
     bin_scan_kernel<<<bins2 + 1, 1024, 0, stream>>>(b.hist2, nb, bins2, b.totals + 256, b.tile_counts, tiles, ranges);
-    sp.keys_in = b.keys1; sp.keys_out = nullptr; sp.ids_out = b.ids;
+    sp.keys32_in = b.keys1; sp.keys32_out = nullptr; sp.ids_out = b.ids;
     sp.shift = bits1; sp.bits = bits2; sp.scanned = b.hist2; sp.totals = b.totals + 256;
     rc = dispatch_scatter<2>(bits2, sp, nb, stream);
     if (rc) return rc;

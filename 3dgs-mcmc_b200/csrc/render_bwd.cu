@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX, MIN_CTAS) render_bwd_kernel(const
                     const float col[3] = {q2.x, q2.y, q2.z};
                     // 1 - alpha is in [0.01, 1]: the approximate reciprocal (1 ulp) stands in for the reference's two
                     // divisions; the difference is far inside the gradient tolerance.
-                    const float inv_1ma = __fdividef(1.0f, 1.f - alpha);
+                    const float inv_1ma = rcp_approx(1.f - alpha);
                     T = T * inv_1ma;
                     u = alpha * T;
                     float dL_dalpha = 0.0f;

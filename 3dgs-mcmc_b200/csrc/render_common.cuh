@@ -25,11 +25,14 @@ GS_DEV float rcp_approx(const float x) {
     return y;
 }
 
-GS_DEV bool patch_may_contribute(const float mx, const float my, const float A, const float B, const float C,
-                                 const float thr, const float X0, const float Y0) {
+// box_may_contribute is the same test for any axis-aligned box of pixel centres [X0, X0 + BW] x [Y0, Y0 + BH]: the warp's
+// 8x4 patch (BW = 7, BH = 3) or the CTA's whole 16x16 tile (BW = BH = 15, the first level of the forward's two-level cull).
+template <int BW, int BH>
+GS_DEV bool box_may_contribute(const float mx, const float my, const float A, const float B, const float C,
+                               const float thr, const float X0, const float Y0) {
     if (!(A > 1e-30f) || !(C > 1e-30f)) return true;   // (also keeps the bare reciprocals below in range)
-    const float hx = (mx - X0) + 1e-3f, lx = (mx - X0) - (kPatchW + 1e-3f);
-    const float hy = (my - Y0) + 1e-3f, ly = (my - Y0) - (kPatchH + 1e-3f);
+    const float hx = (mx - X0) + 1e-3f, lx = (mx - X0) - ((float)BW + 1e-3f);
+    const float hy = (my - Y0) + 1e-3f, ly = (my - Y0) - ((float)BH + 1e-3f);
     const bool inside = (lx <= 0.0f) && (hx >= 0.0f) && (ly <= 0.0f) && (hy >= 0.0f);
     // The clamp points only have to be near the edge minima (q is stationary there: an error d in t costs C d^2,
     // far below the allowance), so bare rcp.approx (no range-scaling guards) is enough.
@@ -55,6 +58,11 @@ GS_DEV bool patch_may_contribute(const float mx, const float my, const float A, 
     return !(pmax + 4e-6f * mag + 1e-4f < thr);
 }
 
+GS_DEV bool patch_may_contribute(const float mx, const float my, const float A, const float B, const float C,
+                                 const float thr, const float X0, const float Y0) {
+    return box_may_contribute<7, 3>(mx, my, A, B, C, thr, X0, Y0);
+}
+
 // ------------------------------------------------------------------------------------------------
 // Shared-memory staging of one tile's splats, used by both renderers.
 //   id ring     : kInstStages x (CH + 8) u32 Gaussian ids, filled by 1-D bulk copies (one issuing thread);
@@ -72,18 +80,19 @@ constexpr int kInstStages = 4;
 constexpr int kGatherAhead = 2;
 constexpr int kInstPad = 8;   // ring slots per stage beyond CH (16-byte alignment slack on both ends)
 
-template <int CH = kChunk>
+template <int CH = kChunk, int RS = kRecStages>
 GS_DEV void stager_init(uint64_t* inst_full, uint64_t* rec_full) {
 #pragma unroll
     for (int s = 0; s < kInstStages; ++s) mbar_init(&inst_full[s], 1);
 #pragma unroll
-    for (int s = 0; s < kRecStages; ++s) mbar_init(&rec_full[s], CH);
+    for (int s = 0; s < RS; ++s) mbar_init(&rec_full[s], CH);
     mbar_fence_init();
 }
 
-// CH = records per chunk (the forward uses kChunk; the backward picks its own to fit its shared-memory budget).
-template <int CH = kChunk>
+// CH = records per chunk, RS = record ring depth, GA = chunks the record gather runs ahead of the consumer (GA < RS).
+template <int CH = kChunk, int RS = kRecStages, int GA = kGatherAhead>
 struct Stager {
+    static_assert(GA >= 1 && GA < RS, "the stage being refilled must not be the one being read");
     static_assert(CH % 4 == 0 && CH <= GS_TILE_PIX, "chunk starts must keep the 16-byte phase of the tile's first id");
     const uint32_t* __restrict__ ids;
     const SplatRec* __restrict__ rec;
@@ -120,7 +129,7 @@ struct Stager {
     // Threads 0..CH-1: gather the records of stream chunk k (its ids must have been issued).
     GS_DEV void gather(int tid, int k) {
         if (tid < CH) {
-            const int lc = list_chunk(k), n = chunk_n(lc), si = k % kInstStages, sr = k % kRecStages;
+            const int lc = list_chunk(k), n = chunk_n(lc), si = k % kInstStages, sr = k % RS;
             mbar_wait(&inst_full[si], (uint32_t)((k / kInstStages) & 1));
             if (tid < n) {
                 const uint32_t id = s_inst[si * (CH + kInstPad) + mis + tid];
@@ -137,14 +146,14 @@ struct Stager {
     GS_DEV void prologue(int tid) {
         if (tid == 0)
             for (; inst_issued < min(kInstStages, nchunks); ++inst_issued) issue_inst(inst_issued);
-        for (; gathered < min(kGatherAhead, nchunks); ++gathered) gather(tid, gathered);
+        for (; gathered < min(GA, nchunks); ++gathered) gather(tid, gathered);
     }
 
     // Call at iteration c (consumer about to read stream chunk c), after the CTA-wide barrier at the loop top.
     GS_DEV void advance(int tid, int c) {
-        if (c + kGatherAhead < nchunks) {
-            gather(tid, c + kGatherAhead);
-            gathered = c + kGatherAhead + 1;
+        if (c + GA < nchunks) {
+            gather(tid, c + GA);
+            gathered = c + GA + 1;
         }
         if (tid == 0 && c + kInstStages < nchunks) {
             issue_inst(c + kInstStages);

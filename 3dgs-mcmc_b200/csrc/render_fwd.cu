@@ -18,14 +18,30 @@
 #include "render_common.cuh"
 #include "workspace.cuh"
 
+#include <cstdlib>
+
 namespace gs {
 
+// CH records per staged chunk, RS record stages, GA gather-ahead. kTwoLevel: two-level cull (see below).
+//
+// Two-level cull. Most of a tile's list never reaches its pixels: the reference puts a Gaussian into every tile its
+// 3-sigma bounding SQUARE touches, but only 42 % of those instances come within alpha >= 1/255 of ANY pixel of the tile,
+// and the forward - unlike the backward, which stops at the last blended position - walks the list until its pixels
+// saturate, which most never do. Testing every record against every warp's patch (8 tests per record) was 58 % of this
+// kernel's instructions. Level 1: thread r tests record r of the chunk against the whole 16x16 tile, once per CTA
+// (box_may_contribute<15, 15>: the same conservative test, wider box); the ballots give a survivor bitmap of the chunk.
+// Level 2: every warp compacts the bitmap into a list of record indices (list order preserved) and runs its patch test
+// only on those. Nothing that can contribute is ever dropped, so image / final_T / n_contrib / is_used are unchanged.
+template <int CH, int RS, int GA, bool kTwoLevel>
 __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwdParams p) {
-    __shared__ __align__(128) SplatRec s_rec[kRecStages][kChunk];
-    __shared__ __align__(16) uint32_t s_inst[kInstStages][kChunk + kInstPad];
+    constexpr int kWords = CH / 32;              // survivor bitmap words per chunk
+    __shared__ __align__(128) SplatRec s_rec[RS][CH];
+    __shared__ __align__(16) uint32_t s_inst[kInstStages][CH + kInstPad];
     __shared__ __align__(8) uint64_t s_inst_full[kInstStages];
-    __shared__ __align__(8) uint64_t s_rec_full[kRecStages];
-    __shared__ int s_used[kRecStages][kChunk];  // id+1 of splats blended by some pixel, 0 otherwise
+    __shared__ __align__(8) uint64_t s_rec_full[RS];
+    __shared__ int s_used[RS][CH];  // id+1 of splats blended by some pixel, 0 otherwise
+    __shared__ uint32_t s_mask[kTwoLevel ? kWords : 1];
+    __shared__ uint8_t s_cidx[kTwoLevel ? GS_TILE_PIX / 32 : 1][kTwoLevel ? CH : 1];   // per warp: compacted record indices
     __shared__ uint32_t s_maxc;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -36,30 +52,31 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
     const bool inside = px < (uint32_t)p.W && py < (uint32_t)p.H;
     const uint32_t pix_id = (uint32_t)p.W * py + px;
     const float2 pixf = {(float)px, (float)py};
-    const float patch_x0 = (float)(tile_x * GS_TILE_X + (warp & 1) * 8), patch_y0 = (float)(tile_y * GS_TILE_Y + (warp >> 1) * 4);
+    const float tile_x0 = (float)(tile_x * GS_TILE_X), tile_y0 = (float)(tile_y * GS_TILE_Y);
+    const float patch_x0 = tile_x0 + (float)((warp & 1) * 8), patch_y0 = tile_y0 + (float)((warp >> 1) * 4);
 
     const uint2 range = p.ranges[tile];
     const int n_total = (int)(range.y - range.x);
-    const int nchunks = (n_total + kChunk - 1) / kChunk;
+    const int nchunks = (n_total + CH - 1) / CH;
 
-    for (int i = tid; i < kRecStages * kChunk; i += GS_TILE_PIX) (&s_used[0][0])[i] = 0;
+    for (int i = tid; i < RS * CH; i += GS_TILE_PIX) (&s_used[0][0])[i] = 0;
     if (tid == 0) {
         s_maxc = 0;
-        stager_init<kChunk>(s_inst_full, s_rec_full);
+        stager_init<CH, RS>(s_inst_full, s_rec_full);
     }
     __syncthreads();
 
-    // List chunk c covers positions [c*kChunk, c*kChunk + n) of the tile's list.
-    Stager<kChunk> st(p.ids, p.rec, range.x, n_total, nchunks, /*reversed=*/false, &s_inst[0][0], s_inst_full, &s_rec[0][0], s_rec_full);
+    // List chunk c covers positions [c*CH, c*CH + n) of the tile's list.
+    Stager<CH, RS, GA> st(p.ids, p.rec, range.x, n_total, nchunks, /*reversed=*/false, &s_inst[0][0], s_inst_full, &s_rec[0][0], s_rec_full);
     st.prologue(tid);
 
     auto flush_used = [&](int c) {
-        const int s = c % kRecStages;
-        if (tid < kChunk) {
-            const int u = s_used[s][tid];
+        const int s = c % RS;
+        for (int i = tid; i < CH; i += GS_TILE_PIX) {
+            const int u = s_used[s][i];
             if (u) {
                 p.is_used[u - 1] = 1;
-                s_used[s][tid] = 0;
+                s_used[s][i] = 0;
             }
         }
     };
@@ -68,6 +85,32 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
     uint32_t last_contributor = 0;
     float C[3] = {0.f, 0.f, 0.f};
     bool done = !inside;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+
+    // Blend record j of the chunk into this lane's pixel (the reference's expression tree, forward.cu:330-358).
+    auto blend = [&](const float4* __restrict__ rec, const int s, const int c, const int j) {
+        if (done) return;
+        const float4 q0 = rec[3 * j];      // x, y, A, B
+        const float4 q1 = rec[3 * j + 1];  // C, opacity, thr, id
+        const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
+        const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
+        if (power > 0.0f) return;
+        if (power < q1.z) return;  // cannot reach alpha >= 1/255 (see preprocess_fwd_kernel)
+        const float alpha = min(0.99f, q1.y * exp(power));
+        if (alpha < 1.0f / 255.0f) return;
+        const float test_T = T * (1 - alpha);
+        if (test_T < 0.0001f) {
+            done = true;
+            return;
+        }
+        const float4 q2 = rec[3 * j + 2];  // r, g, b
+        C[0] += q2.x * alpha * T;
+        C[1] += q2.y * alpha * T;
+        C[2] += q2.z * alpha * T;
+        T = test_T;
+        last_contributor = (uint32_t)(c * CH + j + 1);
+        s_used[s][j] = __float_as_int(q1.w) + 1;
+    };
 
     int c = 0;
     for (; c < nchunks; ++c) {
@@ -76,46 +119,70 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
         if (ndone == GS_TILE_PIX) break;
         st.advance(tid, c);
 
-        const int s = c % kRecStages;
-        const int n = min(kChunk, n_total - c * kChunk);
-        mbar_wait(&s_rec_full[s], (uint32_t)((c / kRecStages) & 1));
-        // Lane-parallel patch cull: lane l tests splat base+l against this warp's 8x4 patch; only the survivors
-        // are evaluated per pixel. Positions keep their list index, so n_contrib is unchanged.
-        if (!__all_sync(0xffffffffu, done)) {
-            const float4* __restrict__ rec = reinterpret_cast<const float4*>(&s_rec[s][0]);
-            for (int base = 0; base < n; base += 32) {
-                if (__all_sync(0xffffffffu, done)) break;
-                const int jt = base + lane;
+        const int s = c % RS;
+        const int n = min(CH, n_total - c * CH);
+        mbar_wait(&s_rec_full[s], (uint32_t)((c / RS) & 1));
+        const float4* __restrict__ rec = reinterpret_cast<const float4*>(&s_rec[s][0]);
+        if (kTwoLevel) {
+            // ---- level 1: one tile-level test per record, once per CTA ----
+            if (tid < CH) {
                 bool may = false;
-                if (jt < n) {
-                    const float4 t0 = rec[3 * jt], t1 = rec[3 * jt + 1];
-                    may = patch_may_contribute(t0.x, t0.y, t0.z, t0.w, t1.x, t1.z, patch_x0, patch_y0);
+                if (tid < n) {
+                    const float4 t0 = rec[3 * tid], t1 = rec[3 * tid + 1];
+                    may = box_may_contribute<GS_TILE_X - 1, GS_TILE_Y - 1>(t0.x, t0.y, t0.z, t0.w, t1.x, t1.z, tile_x0, tile_y0);
                 }
-                uint32_t m = __ballot_sync(0xffffffffu, may);
-                while (m) {
-                    const int j = base + __ffs(m) - 1;
-                    m &= m - 1;
-                    if (done) continue;
-                    const float4 q0 = rec[3 * j];      // x, y, A, B
-                    const float4 q1 = rec[3 * j + 1];  // C, opacity, thr, id
-                    const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
-                    const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
-                    if (power > 0.0f) continue;
-                    if (power < q1.z) continue;  // cannot reach alpha >= 1/255 (see preprocess_one)
-                    const float alpha = min(0.99f, q1.y * exp(power));
-                    if (alpha < 1.0f / 255.0f) continue;
-                    const float test_T = T * (1 - alpha);
-                    if (test_T < 0.0001f) {
-                        done = true;
-                        continue;
+                const uint32_t m = __ballot_sync(0xffffffffu, may);
+                if (lane == 0) s_mask[warp] = m;
+            }
+            __syncthreads();
+            // ---- level 2: per warp, compact the tile-level survivors (list order kept), patch-test those ----
+            if (!__all_sync(0xffffffffu, done)) {
+                uint8_t* const cidx = s_cidx[warp];
+                int total = 0;
+#pragma unroll
+                for (int w = 0; w < kWords; ++w) {
+                    const uint32_t m = s_mask[w];
+                    if ((m >> lane) & 1u) cidx[total + __popc(m & lt_mask)] = (uint8_t)(32 * w + lane);
+                    total += __popc(m);
+                }
+                __syncwarp();
+                for (int base = 0; base < total; base += 32) {
+                    if (__all_sync(0xffffffffu, done)) break;
+                    const int k = base + lane;
+                    bool may = false;
+                    int jt = 0;
+                    if (k < total) {
+                        jt = cidx[k];
+                        const float4 t0 = rec[3 * jt], t1 = rec[3 * jt + 1];
+                        may = patch_may_contribute(t0.x, t0.y, t0.z, t0.w, t1.x, t1.z, patch_x0, patch_y0);
                     }
-                    const float4 q2 = rec[3 * j + 2];  // r, g, b
-                    C[0] += q2.x * alpha * T;
-                    C[1] += q2.y * alpha * T;
-                    C[2] += q2.z * alpha * T;
-                    T = test_T;
-                    last_contributor = (uint32_t)(c * kChunk + j + 1);
-                    s_used[s][j] = __float_as_int(q1.w) + 1;
+                    uint32_t m = __ballot_sync(0xffffffffu, may);
+                    while (m) {
+                        const int b = __ffs(m) - 1;
+                        m &= m - 1;
+                        blend(rec, s, c, __shfl_sync(0xffffffffu, jt, b));
+                    }
+                }
+                __syncwarp();   // cidx is rewritten for the next chunk only after every lane has read it
+            }
+        } else {
+            // Lane-parallel patch cull: lane l tests splat base+l against this warp's 8x4 patch; only the survivors
+            // are evaluated per pixel. Positions keep their list index, so n_contrib is unchanged.
+            if (!__all_sync(0xffffffffu, done)) {
+                for (int base = 0; base < n; base += 32) {
+                    if (__all_sync(0xffffffffu, done)) break;
+                    const int jt = base + lane;
+                    bool may = false;
+                    if (jt < n) {
+                        const float4 t0 = rec[3 * jt], t1 = rec[3 * jt + 1];
+                        may = patch_may_contribute(t0.x, t0.y, t0.z, t0.w, t1.x, t1.z, patch_x0, patch_y0);
+                    }
+                    uint32_t m = __ballot_sync(0xffffffffu, may);
+                    while (m) {
+                        const int j = base + __ffs(m) - 1;
+                        m &= m - 1;
+                        blend(rec, s, c, j);
+                    }
                 }
             }
         }
@@ -141,7 +208,14 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
 
 int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream) {
     if (tiles <= 0) return GS_OK;
-    render_fwd_kernel<<<tiles, GS_TILE_PIX, 0, stream>>>(p);
+    // GS_FWD_VARIANT (measurement): 0 = one-level cull (round 1), 2 = two-level with 128-record chunks, default = two-level
+    // with 256-record chunks (one level-1 test per thread)
+    static const int variant = [] { const char* e = getenv("GS_FWD_VARIANT"); return e ? atoi(e) : 1; }();
+    switch (variant) {
+        case 0: render_fwd_kernel<128, 3, 2, false><<<tiles, GS_TILE_PIX, 0, stream>>>(p); break;
+        case 2: render_fwd_kernel<128, 3, 2, true><<<tiles, GS_TILE_PIX, 0, stream>>>(p); break;
+        default: render_fwd_kernel<256, 2, 1, true><<<tiles, GS_TILE_PIX, 0, stream>>>(p); break;
+    }
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

@@ -32,11 +32,14 @@ __host__ inline void bin_digit_bits(uint32_t tiles, int* bits1, int* bits2) {
     *bits2 = bits - *bits1;
 }
 // GS_FORCE_GENERIC_BINNING=1 selects the generic path everywhere (tests exercise it on small images that way).
-__host__ inline bool bin_fast_path(uint32_t tiles) {
+// The fast path carries an instance between its two passes as ONE 32-bit word, (high tile digit << (32 - bits2)) | idx
+// (the low digit is implied by the position after pass 1), so the Gaussian index must fit in 32 - bits2 bits: 67M
+// Gaussians at 1080p, 16.7M at the 65536-tile limit. Anything larger takes the generic path.
+__host__ inline bool bin_fast_path(uint32_t tiles, size_t P) {
     static const bool force_generic = [] { const char* e = getenv("GS_FORCE_GENERIC_BINNING"); return e && e[0] == '1'; }();
     int b1, b2;
     bin_digit_bits(tiles, &b1, &b2);
-    return b1 <= kBinMaxBits && !force_generic;
+    return b1 <= kBinMaxBits && P <= ((size_t)1 << (32 - b2)) && !force_generic;
 }
 
 // Scratch of one radix sort of n keys: per-pass digit histograms, tile tickets, look-back status words.
@@ -145,7 +148,7 @@ struct BinningWS {
                             //         renderers' 16-byte-aligned bulk copies may start 3 entries early / end 3 late
     uint32_t* error_flag;   // [4] set if a look-back spin ran out
     // fast path
-    uint64_t* keys1;        // [R] pass-1 output (tile << 32 | idx), stably sorted by the low tile digit
+    uint32_t* keys1;        // [R] pass-1 output (high tile digit << (32 - bits2)) | idx, stably sorted by the low tile digit
     uint32_t* block_first;  // [nb] depth rank of the Gaussian owning the first slot of pass-1 block b
     uint32_t* block_last;   // [nb] ... owning its last slot
     uint32_t* totals;       // [2][256] digit totals of the two passes
@@ -160,17 +163,17 @@ struct BinningWS {
     size_t sort_scratch_bytes;
     size_t bytes;
 
-    __host__ static BinningWS carve(char* base, size_t R, uint32_t tiles) {
+    __host__ static BinningWS carve(char* base, size_t R, uint32_t tiles, size_t P) {
         const size_t Rp = R > 0 ? R : 1;
         Carver c(base);
         BinningWS b = {};
         b.ids = c.take<uint32_t>(Rp + 8);
         b.error_flag = c.take<uint32_t>(4);
-        if (bin_fast_path(tiles)) {
+        if (bin_fast_path(tiles, P)) {
             int bits1, bits2;
             bin_digit_bits(tiles, &bits1, &bits2);
             b.nb = (Rp + kBinTile - 1) / kBinTile;
-            b.keys1 = c.take<uint64_t>(Rp);
+            b.keys1 = c.take<uint32_t>(Rp);
             b.block_first = c.take<uint32_t>(b.nb);
             b.block_last = c.take<uint32_t>(b.nb);
             b.totals = c.take<uint32_t>(2 * 256);

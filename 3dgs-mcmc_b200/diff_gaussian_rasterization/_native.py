@@ -29,7 +29,7 @@ SIGNATURES = {
     "gs_error_string": (ctypes.c_char_p, [_c_int]),
     "gs_geom_bytes": (_c_size_t, [_c_int]),
     "gs_image_bytes": (_c_size_t, [_c_int, _c_int]),
-    "gs_binning_bytes": (_c_size_t, [_c_uint, _c_int, _c_int]),
+    "gs_binning_bytes": (_c_size_t, [_c_uint, _c_int, _c_int, _c_int]),
     "gs_backward_scratch_bytes": (_c_size_t, [_c_int]),
     "gs_forward_preprocess": (_c_int, [_c_void_p, _c_int, _c_int, _c_int] + [_c_void_p] * 5 + [_c_float]
                               + [_c_void_p] * 5 + [_c_int, _c_int, _c_float, _c_float, _c_int]
@@ -216,7 +216,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         if debug:
             _debug_sync("preprocess")
 
-        binning = torch.empty(_stable_size(_lib.gs_binning_bytes(rendered, W, H)), **byte_opts)
+        binning = torch.empty(_stable_size(_lib.gs_binning_bytes(rendered, W, H, P)), **byte_opts)
         _check(_lib.gs_forward_render(
             stream, P, rendered, W, H, _ptr(background), _ptr(colors), radii.data_ptr(), geom.data_ptr(),
             binning.data_ptr(), img.data_ptr(), out_color.data_ptr(), is_used.data_ptr()), "gs_forward_render")

@@ -52,7 +52,7 @@ const char* gs_error_string(int code);
  *      (cuda_rasterizer/rasterizer_impl.h:65-72). ---- */
 size_t gs_geom_bytes(int P);
 size_t gs_image_bytes(int W, int H);
-size_t gs_binning_bytes(unsigned int R, int W, int H);
+size_t gs_binning_bytes(unsigned int R, int W, int H, int P);
 size_t gs_backward_scratch_bytes(int P);
 
 /* Forward, stage 1: preprocess (cull, project, covariance, conic, radius, SH colour), then the depth order of

@@ -27,7 +27,7 @@ class _Absent:
         raise RuntimeError(f"{self._name} is a stub: the real module is not installed in this image")
 
     def __getattr__(self, item):
-        raise RuntimeError(f"{self._name}.{item}: stub module, not installed in this image")
+        raise AttributeError(f"{self._name}.{item}: stub module, not installed in this image")
 
 
 def install():
@@ -54,7 +54,10 @@ def install():
         except ImportError:
             m = types.ModuleType("open3d")
             m.__stub__ = True
-            m.__getattr__ = lambda item: (_ for _ in ()).throw(RuntimeError(f"open3d.{item}: stub module"))
+
+            def _absent_attr(item):     # AttributeError (not RuntimeError): inspect / hasattr probe modules for dunders
+                raise AttributeError(f"open3d.{item}: stub module, not installed in this image")
+            m.__getattr__ = _absent_attr
             sys.modules["open3d"] = m
     # this repository's rasterizer must be the one the reference code binds
     import diff_gaussian_rasterization as dgr

@@ -40,7 +40,7 @@ def test_sizes_and_errors_without_gpu():
     g1, g2 = lib.gs_geom_bytes(1000), lib.gs_geom_bytes(2000)
     assert g2 > g1 >= 1000 * 73
     assert lib.gs_image_bytes(1920, 1080) >= 1920 * 1080 * 8 + 8160 * 12
-    assert lib.gs_binning_bytes(1000000, 1920, 1080) >= 1000000 * 12  # u64 pass-1 keys + u32 sorted ids
+    assert lib.gs_binning_bytes(1000000, 1920, 1080, 50000) >= 1000000 * 8  # u32 pass-1 keys + u32 sorted ids
     assert lib.gs_backward_scratch_bytes(1000) >= 1000 * 36
     assert lib.gs_error_string(0) == b"ok"
     assert b"invalid argument" in lib.gs_error_string(-1)
