@@ -7,9 +7,17 @@
 // that the torch glue zero-fills first (rasterize_points.cu:154-162, 300 B per Gaussian). This kernel
 // reads the render-backward accumulators once and writes every output gradient for every Gaussian
 // (zeros for culled ones and for SH coefficients above the active degree), so the outputs need no
-// memset and dL_dmeans3D is never read back. Expressions follow the reference so results agree to
-// rounding; the three contributions to dL_dmeans3D are added in the reference's order
-// (covariance path, projection path, view-direction path).
+// memset and dL_dmeans3D is never read back.
+//
+// The arithmetic is derived from the maths, in matrix form (tests/test_bwd_math.py restates it in float64 numpy and pins it
+// against the CPU oracle of the reference's scalar expansions; gradients agree with the reference CUDA to rounding):
+//   M = J Wv (2x3),  S = M Sigma M^T + 0.3 I,  conic K = S^-1
+//   G_S = -adj(S) G_K adj(S) / (det^2 + 1e-7),  G_K = [[gA, gB], [gB, gC]]   (the tile backward accumulates half of d/dB)
+//   G_Sigma = M^T G_S M  (dL_dcov3D: off-diagonals doubled),  G_M = 2 G_S M Sigma,  G_J = G_M Wv^T,  then through J to the mean
+//   colour: s_k = <sh_k, g>,  dL/ddir = sum_k s_k grad B_k(dir),  dL/dv = (dL/ddir - d <d, dL/ddir>) / |v|
+//   Sigma = A A^T, A = R diag(s):  G_A = 2 G_Sigma A,  dL/ds_j = <G_A[:, j], R[:, j]>,  G_R = G_A diag(s),
+//   quaternion (r, u): a = axial(G_R - G_R^T),  dL/dr = 2 <u, a>,  dL/du = 2 [(G_R + G_R^T) u - 2 tr(G_R) u + r a]
+// The three contributions to dL_dmeans3D are added in the order covariance path, projection path, view-direction path.
 #include "bulk_copy.cuh"
 #include "gs_common.cuh"
 #include "kernels.cuh"
@@ -33,7 +41,9 @@ template <bool kVec>
 GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* sh, uint8_t clamp_bits, V3 dL_dRGB,
                           float (&basis_out)[16], V3& dL_dRGB_out) {
     const V3 dir_orig = pos - campos;
-    const V3 dir = dir_orig / sqrt(norm2_fixed(dir_orig));
+    const float norm = sqrt(norm2_fixed(dir_orig));
+    const V3 dir = dir_orig / norm;
+    const float inv_norm = 1.0f / norm;
     float c48[kVec ? 48 : 1];
     if (kVec) sh_row_to_regs(reinterpret_cast<const float4*>(sh), 0, c48);
     auto C = [&](int k) {
@@ -45,35 +55,39 @@ GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* s
     dL_dRGB.y *= (clamp_bits & 2) ? 0.f : 1.f;
     dL_dRGB.z *= (clamp_bits & 4) ? 0.f : 1.f;
 
-    V3 dRGBdx(0.f, 0.f, 0.f), dRGBdy(0.f, 0.f, 0.f), dRGBdz(0.f, 0.f, 0.f);
     const float x = dir.x, y = dir.y, z = dir.z;
     const float xx = x * x, yy = y * y, zz = z * z;
     const float xy = x * y, yz = y * z, xz = x * z;
-    // ---- phase 1: derivative of the colour w.r.t. the view direction (reads the coefficients) ----
+    // ---- phase 1: the colour is sum_k B_k(dir) sh_k, so dL/ddir = sum_k <sh_k, g> grad B_k(dir): one dot product per
+    //      coefficient, then the gradients of the basis polynomials (reads the coefficients) ----
+    auto S = [&](int k) { return dot3(C(k), dL_dRGB); };
+    V3 g_dir(0.f, 0.f, 0.f);
     if (deg > 0) {
-        dRGBdx = -kSH1 * C(3);
-        dRGBdy = -kSH1 * C(1);
-        dRGBdz = kSH1 * C(2);
+        // B1 = -c1 y, B2 = c1 z, B3 = -c1 x
+        g_dir = V3(-kSH1 * S(3), -kSH1 * S(1), kSH1 * S(2));
         if (deg > 1) {
-            dRGBdx = dRGBdx + (kSH2[0] * y * C(4) + kSH2[2] * 2.f * -x * C(6) + kSH2[3] * z * C(7) + kSH2[4] * 2.f * x * C(8));
-            dRGBdy = dRGBdy + (kSH2[0] * x * C(4) + kSH2[1] * z * C(5) + kSH2[2] * 2.f * -y * C(6) + kSH2[4] * 2.f * -y * C(8));
-            dRGBdz = dRGBdz + (kSH2[1] * y * C(5) + kSH2[2] * 2.f * 2.f * z * C(6) + kSH2[3] * x * C(7));
+            // B4 = a xy, B5 = b yz, B6 = c (2zz - xx - yy), B7 = d xz, B8 = e (xx - yy)
+            const float s4 = kSH2[0] * S(4), s5 = kSH2[1] * S(5), s6 = kSH2[2] * S(6), s7 = kSH2[3] * S(7), s8 = kSH2[4] * S(8);
+            g_dir.x += s4 * y - 2.f * s6 * x + s7 * z + 2.f * s8 * x;
+            g_dir.y += s4 * x + s5 * z - 2.f * s6 * y - 2.f * s8 * y;
+            g_dir.z += s5 * y + 4.f * s6 * z + s7 * x;
             if (deg > 2) {
-                dRGBdx = dRGBdx + (kSH3[0] * C(9) * 3.f * 2.f * xy + kSH3[1] * C(10) * yz + kSH3[2] * C(11) * -2.f * xy +
-                                   kSH3[3] * C(12) * -3.f * 2.f * xz + kSH3[4] * C(13) * (-3.f * xx + 4.f * zz - yy) +
-                                   kSH3[5] * C(14) * 2.f * xz + kSH3[6] * C(15) * 3.f * (xx - yy));
-                dRGBdy = dRGBdy + (kSH3[0] * C(9) * 3.f * (xx - yy) + kSH3[1] * C(10) * xz +
-                                   kSH3[2] * C(11) * (-3.f * yy + 4.f * zz - xx) + kSH3[3] * C(12) * -3.f * 2.f * yz +
-                                   kSH3[4] * C(13) * -2.f * xy + kSH3[5] * C(14) * -2.f * yz +
-                                   kSH3[6] * C(15) * -3.f * 2.f * xy);
-                dRGBdz = dRGBdz + (kSH3[1] * C(10) * xy + kSH3[2] * C(11) * 4.f * 2.f * yz +
-                                   kSH3[3] * C(12) * 3.f * (2.f * zz - xx - yy) + kSH3[4] * C(13) * 4.f * 2.f * xz +
-                                   kSH3[5] * C(14) * (xx - yy));
+                // B9 = a y (3xx - yy), B10 = b xyz, B11 = c y (4zz - xx - yy), B12 = d z (2zz - 3xx - 3yy),
+                // B13 = e x (4zz - xx - yy), B14 = f z (xx - yy), B15 = g x (xx - 3yy)
+                const float s9 = kSH3[0] * S(9), s10 = kSH3[1] * S(10), s11 = kSH3[2] * S(11), s12 = kSH3[3] * S(12);
+                const float s13 = kSH3[4] * S(13), s14 = kSH3[5] * S(14), s15 = kSH3[6] * S(15);
+                const float dxy = xx - yy;
+                g_dir.x += 6.f * s9 * xy + s10 * yz - 2.f * s11 * xy - 6.f * s12 * xz + s13 * (4.f * zz - 3.f * xx - yy) +
+                           2.f * s14 * xz + 3.f * s15 * dxy;
+                g_dir.y += 3.f * s9 * dxy + s10 * xz + s11 * (4.f * zz - xx - 3.f * yy) - 6.f * s12 * yz - 2.f * s13 * xy -
+                           2.f * s14 * yz - 6.f * s15 * xy;
+                g_dir.z += s10 * xy + 8.f * s11 * yz + s12 * (6.f * zz - 3.f * xx - 3.f * yy) + 8.f * s13 * xz + s14 * dxy;
             }
         }
     }
-    const float3 dL_ddir = {dot3(dRGBdx, dL_dRGB), dot3(dRGBdy, dL_dRGB), dot3(dRGBdz, dL_dRGB)};
-    const float3 dmean = dnormvdv3(float3{dir_orig.x, dir_orig.y, dir_orig.z}, dL_ddir);
+    // through the normalisation dir = v / |v|: the component of the gradient along dir is projected out
+    const float along = dot3(dir, g_dir);
+    const float3 dmean = {(g_dir.x - dir.x * along) * inv_norm, (g_dir.y - dir.y * along) * inv_norm, (g_dir.z - dir.z * along) * inv_norm};
     // ---- phase 2: dL/dsh[k] = basis_k(dir) * dL/dRGB ----
     dL_dRGB_out = dL_dRGB;
     auto W = [&](int k, float basis) { basis_out[k] = basis; };
@@ -102,39 +116,46 @@ GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* s
     return dmean;
 }
 
-// Sigma = M^T M with M = S R: gradient w.r.t. scale and the (un-normalised) quaternion.
-GS_DEV void cov3d_backward(const V3 scale, float mod, const float4 rot, const float* dL_dcov3D, float* __restrict__ dL_dscale,
+// Sigma = A A^T with A = R diag(s), s = mod * scale, R the rotation polynomial of the quaternion as given (not normalised):
+// gradient w.r.t. s (returned as is, like the reference: backward.cu:318-321) and the quaternion. dcov: the six-vector
+// gradient (off-diagonal entries count both symmetric positions).
+GS_DEV void cov3d_backward(const V3 scale, float mod, const float4 rot, const float* dcov, float* __restrict__ dL_dscale,
                            float4* __restrict__ dL_drot) {
     const float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
-    const M3 R(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-               2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-               2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
-    const V3 s = mod * scale;
-    const M3 S(s.x, 0.f, 0.f, 0.f, s.y, 0.f, 0.f, 0.f, s.z);
-    const M3 Mx = S * R;
-    const M3 dL_dSigma(dL_dcov3D[0], 0.5f * dL_dcov3D[1], 0.5f * dL_dcov3D[2],
-                       0.5f * dL_dcov3D[1], dL_dcov3D[3], 0.5f * dL_dcov3D[4],
-                       0.5f * dL_dcov3D[2], 0.5f * dL_dcov3D[4], dL_dcov3D[5]);
-    const M3 dL_dM = (2.0f * Mx) * dL_dSigma;
-    const M3 Rt = transpose(R);
-    M3 dL_dMt = transpose(dL_dM);
-
-    dL_dscale[0] = dot3(Rt[0], dL_dMt[0]);
-    dL_dscale[1] = dot3(Rt[1], dL_dMt[1]);
-    dL_dscale[2] = dot3(Rt[2], dL_dMt[2]);
-
-    dL_dMt[0] = dL_dMt[0] * s.x;
-    dL_dMt[1] = dL_dMt[1] * s.y;
-    dL_dMt[2] = dL_dMt[2] * s.z;
-
+    // rows of R
+    const float R[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+                           {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+                           {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+    const float sv[3] = {mod * scale.x, mod * scale.y, mod * scale.z};
+    // full symmetric gradient matrix
+    const float G[3][3] = {{dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]},
+                           {0.5f * dcov[1], dcov[3], 0.5f * dcov[4]},
+                           {0.5f * dcov[2], 0.5f * dcov[4], dcov[5]}};
+    // G_A = 2 G A, A[i][j] = R[i][j] s_j;  dL/ds_j = sum_i G_A[i][j] R[i][j];  G_R[i][j] = G_A[i][j] s_j
+    float GR[3][3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        float ds = 0.f;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            const float ga = 2.f * sv[j] * (G[i][0] * R[0][j] + G[i][1] * R[1][j] + G[i][2] * R[2][j]);
+            ds += ga * R[i][j];
+            GR[i][j] = ga * sv[j];
+        }
+        dL_dscale[j] = ds;
+    }
+    // R is quadratic in (r, u): its derivative contracts G_R into the axial vector of its antisymmetric part and the
+    // symmetric part applied to u
+    const float ax = GR[2][1] - GR[1][2], ay = GR[0][2] - GR[2][0], az = GR[1][0] - GR[0][1];
+    const float tr2 = 2.f * (GR[0][0] + GR[1][1] + GR[2][2]);
+    const float sx = 2.f * GR[0][0] * x + (GR[0][1] + GR[1][0]) * y + (GR[0][2] + GR[2][0]) * z;
+    const float sy = (GR[0][1] + GR[1][0]) * x + 2.f * GR[1][1] * y + (GR[1][2] + GR[2][1]) * z;
+    const float sz = (GR[0][2] + GR[2][0]) * x + (GR[1][2] + GR[2][1]) * y + 2.f * GR[2][2] * z;
     float4 dq;
-    dq.x = 2 * z * (dL_dMt[0][1] - dL_dMt[1][0]) + 2 * y * (dL_dMt[2][0] - dL_dMt[0][2]) + 2 * x * (dL_dMt[1][2] - dL_dMt[2][1]);
-    dq.y = 2 * y * (dL_dMt[1][0] + dL_dMt[0][1]) + 2 * z * (dL_dMt[2][0] + dL_dMt[0][2]) + 2 * r * (dL_dMt[1][2] - dL_dMt[2][1]) -
-           4 * x * (dL_dMt[2][2] + dL_dMt[1][1]);
-    dq.z = 2 * x * (dL_dMt[1][0] + dL_dMt[0][1]) + 2 * r * (dL_dMt[2][0] - dL_dMt[0][2]) + 2 * z * (dL_dMt[1][2] + dL_dMt[2][1]) -
-           4 * y * (dL_dMt[2][2] + dL_dMt[0][0]);
-    dq.w = 2 * r * (dL_dMt[0][1] - dL_dMt[1][0]) + 2 * x * (dL_dMt[2][0] + dL_dMt[0][2]) + 2 * y * (dL_dMt[1][2] + dL_dMt[2][1]) -
-           4 * z * (dL_dMt[1][1] + dL_dMt[0][0]);
+    dq.x = 2.f * (x * ax + y * ay + z * az);
+    dq.y = 2.f * (sx - tr2 * x + r * ax);
+    dq.z = 2.f * (sy - tr2 * y + r * ay);
+    dq.w = 2.f * (sz - tr2 * z + r * az);
     *dL_drot = dq;  // gradient w.r.t. the quaternion as given; normalisation is the caller's (PyTorch's) job
 }
 
@@ -195,85 +216,59 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
         const float3 mean = {p.means3D[3 * i], p.means3D[3 * i + 1], p.means3D[3 * i + 2]};
         const float* cov3D = p.cov3D + 6 * i;
         const float* view = p.viewmatrix;
-        const float3 dL_dconic = {acc1.z, acc1.w, acc2};
 
         // ---- conic -> cov2D -> cov3D and view-space mean ----
+        // rows of the world -> view rotation (view is the transposed 4x4 the rasterizer takes)
+        const V3 w0(view[0], view[4], view[8]), w1(view[1], view[5], view[9]), w2(view[2], view[6], view[10]);
         float3 t = xform_point_4x3(mean, view);
-        const float limx = 1.3f * p.tan_fovx;
-        const float limy = 1.3f * p.tan_fovy;
-        const float txtz = t.x / t.z;
-        const float tytz = t.y / t.z;
+        const float limx = 1.3f * p.tan_fovx, limy = 1.3f * p.tan_fovy;
+        const float txtz = t.x / t.z, tytz = t.y / t.z;
+        const bool x_free = !(txtz < -limx || txtz > limx), y_free = !(tytz < -limy || tytz > limy);   // clamped axes pass no gradient
         t.x = min(limx, max(-limx, txtz)) * t.z;
         t.y = min(limy, max(-limy, tytz)) * t.z;
-        const float x_grad_mul = txtz < -limx || txtz > limx ? 0 : 1;
-        const float y_grad_mul = tytz < -limy || tytz > limy ? 0 : 1;
-        const float h_x = p.focal_x, h_y = p.focal_y;
+        const float iz = 1.f / t.z, iz2 = iz * iz;
+        // J = [[j00, 0, j02], [0, j11, j12]],  M = J Wv
+        const float j00 = p.focal_x * iz, j02 = -p.focal_x * t.x * iz2, j11 = p.focal_y * iz, j12 = -p.focal_y * t.y * iz2;
+        const V3 m0 = j00 * w0 + j02 * w2, m1 = j11 * w1 + j12 * w2;
+        // Sigma (symmetric) times the rows of M
+        const float c0 = cov3D[0], c1 = cov3D[1], c2 = cov3D[2], c3 = cov3D[3], c4 = cov3D[4], c5 = cov3D[5];
+        auto sig = [&](const V3& v) { return V3(c0 * v.x + c1 * v.y + c2 * v.z, c1 * v.x + c3 * v.y + c4 * v.z, c2 * v.x + c4 * v.y + c5 * v.z); };
+        const V3 ms0 = sig(m0), ms1 = sig(m1);
+        const float a = dot3(m0, ms0) + 0.3f, b = dot3(m0, ms1), c = dot3(m1, ms1) + 0.3f;
+        const float det = a * c - b * b;
+        const float scale_s = -1.0f / (det * det + 0.0000001f);
+        // G_S = -adj(S) G_K adj(S) / (det^2 + eps), adj(S) = [[c, -b], [-b, a]], G_K = [[gA, gB], [gB, gC]]
+        const float gA = acc1.z, gB = acc1.w, gC = acc2;
+        const float k0 = c * gA - b * gB, k1 = c * gB - b * gC;     // first row of adj(S) G_K
+        const float k2 = a * gB - b * gA, k3 = a * gC - b * gB;     // second row
+        const float s00 = scale_s * (k0 * c - k1 * b), s01 = scale_s * (k1 * a - k0 * b), s11 = scale_s * (k3 * a - k2 * b);
+        // G_Sigma = M^T G_S M = s00 m0 m0^T + s01 (m0 m1^T + m1 m0^T) + s11 m1 m1^T
+        const V3 u0 = s00 * m0 + s01 * m1, u1 = s01 * m0 + s11 * m1;   // rows of G_S M
+        dcov[0] = m0.x * u0.x + m1.x * u1.x;
+        dcov[3] = m0.y * u0.y + m1.y * u1.y;
+        dcov[5] = m0.z * u0.z + m1.z * u1.z;
+        dcov[1] = 2.f * (m0.x * u0.y + m1.x * u1.y);     // off-diagonal entries appear twice in the symmetric matrix
+        dcov[2] = 2.f * (m0.x * u0.z + m1.x * u1.z);
+        dcov[4] = 2.f * (m0.y * u0.z + m1.y * u1.z);
+        // G_M = 2 G_S M Sigma, G_J = G_M Wv^T (only J's four non-constant entries are needed)
+        const V3 gm0 = 2.f * (s00 * ms0 + s01 * ms1), gm1 = 2.f * (s01 * ms0 + s11 * ms1);
+        const float gj00 = dot3(gm0, w0), gj02 = dot3(gm0, w2), gj11 = dot3(gm1, w1), gj12 = dot3(gm1, w2);
+        // through J(t): j00 = fx / tz, j02 = -fx tx / tz^2 (and the y row alike)
+        const float gx = x_free ? -p.focal_x * iz2 * gj02 : 0.f;
+        const float gy = y_free ? -p.focal_y * iz2 * gj12 : 0.f;
+        const float gz = -iz2 * (p.focal_x * gj00 + p.focal_y * gj11) + 2.f * iz2 * iz * (p.focal_x * t.x * gj02 + p.focal_y * t.y * gj12);
+        const V3 dm = gx * w0 + gy * w1 + gz * w2;
+        dmean = {dm.x, dm.y, dm.z};
 
-        const M3 J(h_x / t.z, 0.0f, -(h_x * t.x) / (t.z * t.z), 0.0f, h_y / t.z, -(h_y * t.y) / (t.z * t.z), 0.f, 0.f, 0.f);
-        const M3 Wm(view[0], view[4], view[8], view[1], view[5], view[9], view[2], view[6], view[10]);
-        const M3 Vrk(cov3D[0], cov3D[1], cov3D[2], cov3D[1], cov3D[3], cov3D[4], cov3D[2], cov3D[4], cov3D[5]);
-        const M3 T = Wm * J;
-        M3 cov2D = transpose(T) * transpose(Vrk) * T;
-
-        const float a = cov2D[0][0] += 0.3f;
-        const float b = cov2D[0][1];
-        const float c = cov2D[1][1] += 0.3f;
-        const float denom = a * c - b * b;
-        float dL_da = 0, dL_db = 0, dL_dc = 0;
-        const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
-        if (denom2inv != 0) {
-            dL_da = denom2inv * (-c * c * dL_dconic.x + 2 * b * c * dL_dconic.y + (denom - a * c) * dL_dconic.z);
-            dL_dc = denom2inv * (-a * a * dL_dconic.z + 2 * a * b * dL_dconic.y + (denom - a * c) * dL_dconic.x);
-            dL_db = denom2inv * 2 * (b * c * dL_dconic.x - (denom + 2 * b * b) * dL_dconic.y + a * b * dL_dconic.z);
-
-            dcov[0] = (T[0][0] * T[0][0] * dL_da + T[0][0] * T[1][0] * dL_db + T[1][0] * T[1][0] * dL_dc);
-            dcov[3] = (T[0][1] * T[0][1] * dL_da + T[0][1] * T[1][1] * dL_db + T[1][1] * T[1][1] * dL_dc);
-            dcov[5] = (T[0][2] * T[0][2] * dL_da + T[0][2] * T[1][2] * dL_db + T[1][2] * T[1][2] * dL_dc);
-            // Off-diagonal entries appear twice in the symmetric matrix.
-            dcov[1] = 2 * T[0][0] * T[0][1] * dL_da + (T[0][0] * T[1][1] + T[0][1] * T[1][0]) * dL_db + 2 * T[1][0] * T[1][1] * dL_dc;
-            dcov[2] = 2 * T[0][0] * T[0][2] * dL_da + (T[0][0] * T[1][2] + T[0][2] * T[1][0]) * dL_db + 2 * T[1][0] * T[1][2] * dL_dc;
-            dcov[4] = 2 * T[0][2] * T[0][1] * dL_da + (T[0][1] * T[1][2] + T[0][2] * T[1][1]) * dL_db + 2 * T[1][1] * T[1][2] * dL_dc;
-        }
-
-        const float dL_dT00 = 2 * (T[0][0] * Vrk[0][0] + T[0][1] * Vrk[0][1] + T[0][2] * Vrk[0][2]) * dL_da +
-                              (T[1][0] * Vrk[0][0] + T[1][1] * Vrk[0][1] + T[1][2] * Vrk[0][2]) * dL_db;
-        const float dL_dT01 = 2 * (T[0][0] * Vrk[1][0] + T[0][1] * Vrk[1][1] + T[0][2] * Vrk[1][2]) * dL_da +
-                              (T[1][0] * Vrk[1][0] + T[1][1] * Vrk[1][1] + T[1][2] * Vrk[1][2]) * dL_db;
-        const float dL_dT02 = 2 * (T[0][0] * Vrk[2][0] + T[0][1] * Vrk[2][1] + T[0][2] * Vrk[2][2]) * dL_da +
-                              (T[1][0] * Vrk[2][0] + T[1][1] * Vrk[2][1] + T[1][2] * Vrk[2][2]) * dL_db;
-        const float dL_dT10 = 2 * (T[1][0] * Vrk[0][0] + T[1][1] * Vrk[0][1] + T[1][2] * Vrk[0][2]) * dL_dc +
-                              (T[0][0] * Vrk[0][0] + T[0][1] * Vrk[0][1] + T[0][2] * Vrk[0][2]) * dL_db;
-        const float dL_dT11 = 2 * (T[1][0] * Vrk[1][0] + T[1][1] * Vrk[1][1] + T[1][2] * Vrk[1][2]) * dL_dc +
-                              (T[0][0] * Vrk[1][0] + T[0][1] * Vrk[1][1] + T[0][2] * Vrk[1][2]) * dL_db;
-        const float dL_dT12 = 2 * (T[1][0] * Vrk[2][0] + T[1][1] * Vrk[2][1] + T[1][2] * Vrk[2][2]) * dL_dc +
-                              (T[0][0] * Vrk[2][0] + T[0][1] * Vrk[2][1] + T[0][2] * Vrk[2][2]) * dL_db;
-
-        const float dL_dJ00 = Wm[0][0] * dL_dT00 + Wm[0][1] * dL_dT01 + Wm[0][2] * dL_dT02;
-        const float dL_dJ02 = Wm[2][0] * dL_dT00 + Wm[2][1] * dL_dT01 + Wm[2][2] * dL_dT02;
-        const float dL_dJ11 = Wm[1][0] * dL_dT10 + Wm[1][1] * dL_dT11 + Wm[1][2] * dL_dT12;
-        const float dL_dJ12 = Wm[2][0] * dL_dT10 + Wm[2][1] * dL_dT11 + Wm[2][2] * dL_dT12;
-
-        const float tz = 1.f / t.z;
-        const float tz2 = tz * tz;
-        const float tz3 = tz2 * tz;
-        const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
-        const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
-        const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 + (2 * h_y * t.y) * tz3 * dL_dJ12;
-        dmean = xform_vec_4x3_T({dL_dtx, dL_dty, dL_dtz}, view);
-
-        // ---- screen-space mean -> 3D mean through the projection ----
+        // ---- screen-space mean -> 3D mean through the perspective division: pix = P_row(axis) . p / (P_row(3) . p) ----
         const float* proj = p.projmatrix;
-        const float4 m_hom = xform_point_4x4(mean, proj);
-        const float m_w = 1.0f / (m_hom.w + 0.0000001f);
-        const float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
-        const float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
-        float3 dproj;
-        dproj.x = (proj[0] * m_w - proj[3] * mul1) * acc1.x + (proj[1] * m_w - proj[3] * mul2) * acc1.y;
-        dproj.y = (proj[4] * m_w - proj[7] * mul1) * acc1.x + (proj[5] * m_w - proj[7] * mul2) * acc1.y;
-        dproj.z = (proj[8] * m_w - proj[11] * mul1) * acc1.x + (proj[9] * m_w - proj[11] * mul2) * acc1.y;
-        dmean.x += dproj.x;
-        dmean.y += dproj.y;
-        dmean.z += dproj.z;
+        const float4 hom = xform_point_4x4(mean, proj);
+        const float iw = 1.0f / (hom.w + 0.0000001f);
+        const float fx_ = acc1.x * iw, fy_ = acc1.y * iw;                 // gradient per unit of the homogeneous x / y
+        const float fw = -(fx_ * hom.x + fy_ * hom.y) * iw;               // and of w
+        dmean.x += proj[0] * fx_ + proj[1] * fy_ + proj[3] * fw;
+        dmean.y += proj[4] * fx_ + proj[5] * fy_ + proj[7] * fw;
+        dmean.z += proj[8] * fx_ + proj[9] * fy_ + proj[11] * fw;
 
     }
     cp_async_wait_all();

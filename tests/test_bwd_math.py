@@ -6,7 +6,8 @@ checked against the reference CUDA on the GPU box (tests/test_gpu_parity.py).
 Formulation (column vectors, world -> view rotation Wv, view-space mean t, J the 2x3 projection Jacobian, M = J Wv):
 
   cov2D      S = M Sigma M^T + 0.3 I,   conic K = S^-1
-  conic      G_K = [[gA, gB/2], [gB/2, gC]]      (the off-diagonal parameter appears twice in the quadratic form)
+  conic      G_K = [[gA, gB], [gB, gC]]          (the tile backward accumulates HALF of d/dB for the off-diagonal parameter,
+                                                  backward.cu:517, so gB already is the entry of the symmetric gradient matrix)
   cov2D      G_S = -adj(S) G_K adj(S) / (det^2 + 1e-7)          (dK = -K dS K, with the reference's regularised 1/det^2)
   Sigma      G_Sigma = M^T G_S M                                  (dL_dcov3D: diagonal as is, off-diagonals doubled)
   M          G_M = 2 G_S M Sigma,  G_J = G_M Wv^T                 (2x3 products instead of per-entry expansions)
@@ -84,7 +85,7 @@ def backward_one(mean, scale, q, sh, clamp_bits, deg, view, proj, campos, W, H, 
     S = M @ Sigma @ M.T + 0.3 * np.eye(2)
     det = S[0, 0] * S[1, 1] - S[0, 1] ** 2
     adj = np.array([[S[1, 1], -S[0, 1]], [-S[0, 1], S[0, 0]]])
-    G_K = np.array([[g_conic[0], 0.5 * g_conic[1]], [0.5 * g_conic[1], g_conic[2]]])
+    G_K = np.array([[g_conic[0], g_conic[1]], [g_conic[1], g_conic[2]]])
     G_S = -(adj @ G_K @ adj) / (det * det + 1e-7)
     G_Sigma = M.T @ G_S @ M
     dcov = np.array([G_Sigma[0, 0], 2 * G_Sigma[0, 1], 2 * G_Sigma[0, 2], G_Sigma[1, 1], 2 * G_Sigma[1, 2], G_Sigma[2, 2]])
@@ -125,7 +126,7 @@ def backward_one(mean, scale, q, sh, clamp_bits, deg, view, proj, campos, W, H, 
     G_full = np.array([[dcov[0], 0.5 * dcov[1], 0.5 * dcov[2]], [0.5 * dcov[1], dcov[3], 0.5 * dcov[4]],
                        [0.5 * dcov[2], 0.5 * dcov[4], dcov[5]]])
     G_A = 2 * G_full @ A
-    dscale = mod * np.einsum("ij,ij->j", G_A, R)
+    dscale = np.einsum("ij,ij->j", G_A, R)      # w.r.t. (mod * scale), as the reference returns it (backward.cu:318-321)
     G_R = G_A * s[None, :]
     r_, u = q[0], q[1:]
     a = np.array([G_R[2, 1] - G_R[1, 2], G_R[0, 2] - G_R[2, 0], G_R[1, 0] - G_R[0, 1]])
@@ -143,8 +144,8 @@ def test_matrix_formulation_matches_the_oracle():
         pre = oracle.preprocess(scene["means3D"], scene["scales"], scene["rotations"], scene["opacities"], scene["shs"],
                                 cam["viewmatrix"], cam["projmatrix"], cam["campos"], W, H, cam["tanfovx"], cam["tanfovy"], deg, 1.3)
         rng = np.random.default_rng(deg)
-        g2d = rng.standard_normal((P, 2)).astype(np.float32)
-        gcon = rng.standard_normal((P, 3)).astype(np.float32)
+        g2d = rng.standard_normal((P, 3)).astype(np.float32)       # the reference's layouts: float3 (z unused) ...
+        gcon = rng.standard_normal((P, 4)).astype(np.float32)      # ... and float4 (x = A, y = B, w = C; z unused)
         gcol = rng.standard_normal((P, 3)).astype(np.float32)
         want = oracle.preprocess_bwd(scene["means3D"], pre["radii"], scene["shs"], pre["clamped"], scene["scales"], scene["rotations"],
                                      1.3, pre["cov3D"], cam["viewmatrix"], cam["projmatrix"], cam["campos"], W, H, cam["tanfovx"],
@@ -159,7 +160,7 @@ def test_matrix_formulation_matches_the_oracle():
                                                 scene["rotations"][i].astype(np.float64), scene["shs"][i], bits, deg,
                                                 np.asarray(cam["viewmatrix"]), np.asarray(cam["projmatrix"]),
                                                 np.asarray(cam["campos"], np.float64), W, H, cam["tanfovx"], cam["tanfovy"],
-                                                g2d[i].astype(np.float64), gcon[i].astype(np.float64), gcol[i].astype(np.float64), mod=1.3)
+                                                g2d[i, :2].astype(np.float64), gcon[i, [0, 1, 3]].astype(np.float64), gcol[i].astype(np.float64), mod=1.3)
             got["dL_dmeans3D"][i], got["dL_dcov3D"][i], got["dL_dsh"][i], got["dL_dscales"][i], got["dL_drots"][i] = dm, dc, dsh, dsc, dq
         for k in want:
             num = np.linalg.norm(got[k] - want[k].astype(np.float64))
