@@ -60,6 +60,7 @@ inline void prof_mark(cudaStream_t stream, int stage) {
     ++g_prof.n;
 }
 inline void count_launches(int k) { g_prof.launches += (unsigned long long)k; }
+unsigned long long* g_fwd_counters = nullptr;   // set by gs_debug_forward_work for the next forward(s); measurement only
 
 }  // namespace
 
@@ -220,6 +221,7 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
     rp.ranges = img.ranges; rp.ids = b.ids; rp.rec = g.rec; rp.W = W; rp.H = H; rp.tiles_x = (int)grid.x; rp.bg = background;
     rp.final_T = img.final_T; rp.n_contrib = img.n_contrib; rp.out_color = out_color; rp.is_used = is_used;
     rp.tile_max_contrib = img.tile_max_contrib;
+    rp.counters = g_fwd_counters;
     rc = launch_render_fwd(rp, (int)tiles, stream);
     prof_mark(stream, ST_RENDER_FWD);
     count_launches(1);
@@ -252,6 +254,11 @@ int gs_backward_render(void* stream_, int P, unsigned int R, int W, int H, const
         prof_mark(stream, ST_RENDER_BWD);
         count_launches(1);
     }
+    return GS_OK;
+}
+
+int gs_debug_forward_work(unsigned long long* device_counters) {
+    g_fwd_counters = device_counters;
     return GS_OK;
 }
 

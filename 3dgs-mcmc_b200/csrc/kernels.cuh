@@ -45,6 +45,7 @@ struct RenderFwdParams {
     float* __restrict__ out_color;
     int* __restrict__ is_used;
     uint32_t* __restrict__ tile_max_contrib;
+    unsigned long long* counters;        // measurement only (gs_debug_forward_work): null on the product path
 };
 
 struct RenderBwdParams {

@@ -32,7 +32,7 @@ namespace gs {
 // (box_may_contribute<15, 15>: the same conservative test, wider box); the ballots give a survivor bitmap of the chunk.
 // Level 2: every warp compacts the bitmap into a list of record indices (list order preserved) and runs its patch test
 // only on those. Nothing that can contribute is ever dropped, so image / final_T / n_contrib / is_used are unchanged.
-template <int CH, int RS, int GA, bool kTwoLevel>
+template <int CH, int RS, int GA, bool kTwoLevel, bool kCount = false>
 __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwdParams p) {
     constexpr int kWords = CH / 32;              // survivor bitmap words per chunk
     __shared__ __align__(128) SplatRec s_rec[RS][CH];
@@ -81,6 +81,10 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
         }
     };
 
+    // kCount (measurement build of the same kernel, gs_debug_forward_work): per-thread tallies, summed into p.counters at the end:
+    // [0] warp-chunks walked, [1] records patch-tested (x 1 lane each), [2] (warp, record) pairs evaluated per pixel,
+    // [3] (pixel, record) blends, [4] records that survived the tile-level test (per warp-chunk)
+    unsigned long long cnt[5] = {0, 0, 0, 0, 0};
     float T = 1.0f;
     uint32_t last_contributor = 0;
     float C[3] = {0.f, 0.f, 0.f};
@@ -110,6 +114,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
         T = test_T;
         last_contributor = (uint32_t)(c * CH + j + 1);
         s_used[s][j] = __float_as_int(q1.w) + 1;
+        if (kCount) ++cnt[3];
     };
 
     int c = 0;
@@ -146,9 +151,11 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
                     total += __popc(m);
                 }
                 __syncwarp();
+                if (kCount && lane == 0) { ++cnt[0]; cnt[4] += (unsigned)total; }
                 for (int base = 0; base < total; base += 32) {
                     if (__all_sync(0xffffffffu, done)) break;
                     const int k = base + lane;
+                    if (kCount && k < total) ++cnt[1];
                     bool may = false;
                     int jt = 0;
                     if (k < total) {
@@ -157,6 +164,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
                         may = patch_may_contribute(t0.x, t0.y, t0.z, t0.w, t1.x, t1.z, patch_x0, patch_y0);
                     }
                     uint32_t m = __ballot_sync(0xffffffffu, may);
+                    if (kCount && lane == 0) cnt[2] += (unsigned)__popc(m);
                     while (m) {
                         const int b = __ffs(m) - 1;
                         m &= m - 1;
@@ -169,15 +177,18 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
             // Lane-parallel patch cull: lane l tests splat base+l against this warp's 8x4 patch; only the survivors
             // are evaluated per pixel. Positions keep their list index, so n_contrib is unchanged.
             if (!__all_sync(0xffffffffu, done)) {
+                if (kCount && lane == 0) { ++cnt[0]; cnt[4] += (unsigned)n; }
                 for (int base = 0; base < n; base += 32) {
                     if (__all_sync(0xffffffffu, done)) break;
                     const int jt = base + lane;
                     bool may = false;
+                    if (kCount && jt < n) ++cnt[1];
                     if (jt < n) {
                         const float4 t0 = rec[3 * jt], t1 = rec[3 * jt + 1];
                         may = patch_may_contribute(t0.x, t0.y, t0.z, t0.w, t1.x, t1.z, patch_x0, patch_y0);
                     }
                     uint32_t m = __ballot_sync(0xffffffffu, may);
+                    if (kCount && lane == 0) cnt[2] += (unsigned)__popc(m);
                     while (m) {
                         const int j = base + __ffs(m) - 1;
                         m &= m - 1;
@@ -204,6 +215,13 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
     }
     __syncthreads();
     if (tid == 0) p.tile_max_contrib[tile] = s_maxc;
+    if (kCount && p.counters) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const unsigned long long v = cnt[k];
+            if (v) atomicAdd(p.counters + k, v);
+        }
+    }
 }
 
 int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream) {
@@ -211,6 +229,12 @@ int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream) 
     // GS_FWD_VARIANT (measurement): 0 = one-level cull (round 1), 2 = two-level with 128-record chunks, default = two-level
     // with 256-record chunks (one level-1 test per thread)
     static const int variant = [] { const char* e = getenv("GS_FWD_VARIANT"); return e ? atoi(e) : 1; }();
+    if (p.counters) {   // measurement: the same kernels with tallies
+        if (variant == 0) render_fwd_kernel<128, 3, 2, false, true><<<tiles, GS_TILE_PIX, 0, stream>>>(p);
+        else render_fwd_kernel<256, 2, 1, true, true><<<tiles, GS_TILE_PIX, 0, stream>>>(p);
+        GS_LAUNCH_CHECK();
+        return GS_OK;
+    }
     switch (variant) {
         case 0: render_fwd_kernel<128, 3, 2, false><<<tiles, GS_TILE_PIX, 0, stream>>>(p); break;
         case 2: render_fwd_kernel<128, 3, 2, true><<<tiles, GS_TILE_PIX, 0, stream>>>(p); break;

@@ -71,6 +71,7 @@ SIGNATURES = {
     "gs_stage_count": (_c_int, []),
     "gs_stage_name": (ctypes.c_char_p, [_c_int]),
     "gs_launch_count": (_c_ull, []),
+    "gs_debug_forward_work": (_c_int, [_c_void_p]),
     "gs_debug_render_work": (_c_int, [_c_void_p, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 5),
     "gs_debug_fetch": (ctypes.c_longlong, [_c_int, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 4 + [_c_size_t]),
 }
@@ -160,6 +161,22 @@ def _stable_size(nbytes):
     return (nbytes + step - 1) // step * step
 
 
+_binning_high_water = {}   # device index -> bytes
+
+
+def _binning_capacity(key, need):
+    """Bytes to allocate for a binning workspace that needs `need`: the device's high-water mark, raised with 25 % headroom
+    whenever a view needs more (and dropped when a view needs less than a quarter of it). The instance count changes with
+    every camera; a per-call exact size would make torch's caching allocator call cudaMalloc - a device-wide stall of
+    10-30 ms at these sizes - each time a larger view shows up; with one size per device the block released by the previous
+    step is simply handed back."""
+    cap = _binning_high_water.get(key, 0)
+    if need > cap or need < cap // 4:
+        cap = _stable_size(need + need // 4)
+        _binning_high_water[key] = cap
+    return cap
+
+
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
                         prefiltered, debug):
@@ -216,7 +233,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         if debug:
             _debug_sync("preprocess")
 
-        binning = torch.empty(_stable_size(_lib.gs_binning_bytes(rendered, W, H, P)), **byte_opts)
+        binning = torch.empty(_binning_capacity(slot_key, _lib.gs_binning_bytes(rendered, W, H, P)), **byte_opts)
         _check(_lib.gs_forward_render(
             stream, P, rendered, W, H, _ptr(background), _ptr(colors), radii.data_ptr(), geom.data_ptr(),
             binning.data_ptr(), img.data_ptr(), out_color.data_ptr(), is_used.data_ptr()), "gs_forward_render")
@@ -684,6 +701,11 @@ def debug_fetch(which, P, R, W, H, geom, binning, img, dtype):
     if nbytes:
         _lib.gs_debug_fetch(which, P, R, W, H, _ptr(geom), _ptr(binning), _ptr(img), out.data_ptr(), nbytes)
     return out.view(dtype)
+
+
+def debug_forward_work(counters):
+    """Arm (tensor of 5 int64 on the device, zeroed) or disarm (None) the tallying forward kernel (gs_debug_forward_work)."""
+    _check(_lib.gs_debug_forward_work(counters.data_ptr() if counters is not None else None), "gs_debug_forward_work")
 
 
 def debug_render_work(P, R, W, H, geom, binning, img):

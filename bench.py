@@ -352,6 +352,22 @@ def run_b200_arm(args):
     pairs_fwd_lower = int(n_contrib.long().sum().item())
     # the same walk with the conservative patch cull applied (gs_debug_render_work): what the kernel actually evaluates
     walked_t, evaluated_t = C.debug_render_work(P, R, W, H, state["geom"], state["binning"], state["img"])
+    # and what the FORWARD kernel does on the same view (tallying build of the same kernel; outside the timed region)
+    fwd_work = None
+    try:
+        ctr = torch.zeros(5, dtype=torch.int64, device=dev)
+        C.debug_forward_work(ctr)
+        c_ = cam_for(Wm + K - 1)
+        C.rasterize_gaussians(bg, s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e, c_["viewmatrix"], c_["projmatrix"],
+                              c_["tanfovx"], c_["tanfovy"], H, W, s["shs"], 3, c_["campos"], False, False)
+        torch.cuda.synchronize()
+        C.debug_forward_work(None)
+        v = [int(x) for x in ctr.tolist()]
+        fwd_work = {"warp_chunks_walked": v[0], "records_patch_tested": v[1], "warp_record_pairs_evaluated": v[2],
+                    "pixel_record_blends": v[3], "tile_level_survivors_over_warp_chunks": v[4]}
+    except Exception as ex:
+        C.debug_forward_work(None)
+        fwd_work = {"unavailable": repr(ex)[:200]}
     pairs_walked = int(walked_t.long().sum().item()) * 32
     pairs_post_cull = int(evaluated_t.long().sum().item()) * 32
     work = evaluated_t.float()
@@ -572,7 +588,7 @@ def run_b200_arm(args):
             "scene_stats": {"num_rendered": R, "visible": visible, "instances_per_visible": round(R / max(visible, 1), 2),
                             "tile_list_mean": float(tile_len.float().mean().item()), "tile_list_p99": float(torch.quantile(tile_len.float(), 0.99).item()),
                             "pairs_bwd": pairs_bwd, "pairs_fwd_lower_bound": pairs_fwd_lower, "pairs_walked": pairs_walked,
-                            "pairs_post_cull": pairs_post_cull, "tile_work": tile_work,
+                            "pairs_post_cull": pairs_post_cull, "tile_work": tile_work, "forward_work": fwd_work,
                             "mpix_per_s": W * H / ms_per_step / 1e3}}
     printed = threading.Lock()
 

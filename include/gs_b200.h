@@ -264,6 +264,12 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H,
 int gs_debug_render_work(void* stream, int P, unsigned int R, int W, int H, const void* geom_ws, const void* binning_ws,
                          const void* image_ws, unsigned int* walked_per_tile, unsigned int* evaluated_per_tile);
 
+/* Measurement hook: while device_counters (5 x u64 in device memory, zeroed by the caller) is non-null, gs_forward_render
+ * launches the tallying build of the forward tile kernel, which adds to it: [0] warp-chunks walked, [1] records patch-tested,
+ * [2] (warp, record) pairs evaluated per pixel, [3] (pixel, record) blends, [4] tile-level survivors summed over warp-chunks.
+ * Pass NULL to return to the product kernel. Process-global; not used by the compute path. */
+int gs_debug_forward_work(unsigned long long* device_counters);
+
 #ifdef __cplusplus
 }
 #endif

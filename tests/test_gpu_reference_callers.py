@@ -390,6 +390,7 @@ class SyntheticDynamicScene:
 
 def _run_train_static(tmp, iterations, fused_adam):
     import scene
+    import utils.loss_utils  # noqa: F401  (train_static.py binds l1_loss from here)
     from diff_gaussian_rasterization.optim import FusedAdam
     saved = (scene.DynamicScene, sys.argv, sys.stdout, torch.optim.Adam, random.getstate())
     losses = []

@@ -303,6 +303,21 @@ def test_binning_workspace_size_classes():
     assert len(classes) <= 2
 
 
+def test_binning_workspace_high_water_capacity():
+    """One allocation size per device: a slightly larger view is served from the headroom (no new size -> no cudaMalloc in
+    the training loop), a much larger one raises the mark once, a much smaller scene lowers it again."""
+    from diff_gaussian_rasterization import _native as C
+    key = "test-device"
+    a = C._binning_capacity(key, 400_000_000)
+    assert a >= 500_000_000 * 0.99 and C._stable_size(a) == a
+    for k in range(1, 24):                      # views up to 24 % larger: same size
+        assert C._binning_capacity(key, int(400_000_000 * (1 + 0.01 * k))) == a
+    b = C._binning_capacity(key, 600_000_000)
+    assert b > a and C._binning_capacity(key, 400_000_000) == b
+    c = C._binning_capacity(key, 1_000_000)     # a tiny scene afterwards does not keep allocating half a gigabyte
+    assert c < 2_000_000
+
+
 def test_l1_loss_symbols_and_python_api_exist():
     from diff_gaussian_rasterization import _native as C, loss
     for sym in ("gs_l1_workspace_bytes", "gs_l1_loss_forward", "gs_l1_loss_backward"):
