@@ -7,6 +7,7 @@ exchange step named in BASELINE.json's north_star. The backward kernel writes it
 contiguous FP32 arena, so a single NCCL all-reduce (708 MB at 3M Gaussians) covers them; forward and render
 backward need no communication.
 """
+import contextlib
 import os
 
 import torch
@@ -77,8 +78,9 @@ def replica_fingerprint(tensors):
 
 def assert_replicas_in_sync(tensors, group=None, what="replicated Gaussian parameters"):
     """View-sharded training keeps a full replica of the model (and of its MCMC state) on every rank and relies on the
-    replicas evolving in lock step: the summed gradients are bit-identical on all ranks, and relocation / growth draw from
-    torch's device RNG seeded alike. A rank that diverged (different seed, a skipped step) would silently train a different
+    replicas evolving in lock step: the summed gradients are bit-identical on all ranks, the noise comes from the device
+    RNG seeded alike, and relocation / growth draw inside lockstep_sampling(). A rank that diverged (different seed, a
+    skipped step, a draw outside lockstep_sampling) would silently train a different
     model and - after add_new_gs - hand resize() a different P, corrupting the symmetric buffers. Call this after every
     relocation / growth step (it costs two tiny all-reduces): raises RuntimeError on every rank if any replica differs."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
@@ -91,6 +93,35 @@ def assert_replicas_in_sync(tensors, group=None, what="replicated Gaussian param
         raise RuntimeError(f"{what} differ between ranks (rank {dist.get_rank(group)}: fingerprint {h.tolist()}, "
                            f"min {lo.tolist()}, max {hi.tolist()}): replicas are out of lock step")
     return True
+
+
+@contextlib.contextmanager
+def lockstep_sampling(group=None, src=0):
+    """Make the MCMC draws of relocate_gs / add_new_gs (scene/gaussian_model_static.py:412-422: torch.multinomial over the
+    alive opacities) the same on every rank.
+
+    Seeding every process alike is not enough: on CUDA torch.multinomial normalises with a floating-point cumsum whose
+    summation order is not fixed from launch to launch (it is on torch's own list of nondeterministic ops), so two
+    replicas holding bit-identical probabilities can draw different indices - measured on 2 x B200: the replicas of
+    tools/dp_check.py --mcmc-steps agreed through every training step and parted at the first relocation. Inside this
+    context every rank still makes each draw (the device RNG streams stay aligned for the noise that follows) and rank
+    `src`'s indices - K int64 per draw - are broadcast over them: this is the "MCMC statistics" half of the north star's
+    exchange. The reference's callers run unchanged inside the context."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        yield
+        return
+    real = torch.multinomial
+    src_global = dist.get_global_rank(group, src) if group is not None else src
+
+    def multinomial(*args, **kwargs):
+        out = real(*args, **kwargs)
+        dist.broadcast(out, src=src_global, group=group)
+        return out
+    torch.multinomial = multinomial
+    try:
+        yield
+    finally:
+        torch.multinomial = real
 
 
 def shard_views(num_views, rank, world_size):

@@ -179,7 +179,7 @@ def run_reference_arm(args):
             "cpu_baseline": {"value": value, "unit": "views/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "wall_seconds": round(wall, 2), "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print_result(line)
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -598,7 +598,7 @@ def run_b200_arm(args):
         if reason:
             line["legs_cut_short"] = reason
         if rank == 0:
-            print(json.dumps(line), flush=True)
+            print_result(line)
 
     deadline_s = args.legs_deadline or (600.0 if n_gpus == 1 else 300.0)
 
@@ -1100,8 +1100,31 @@ def run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_g
     return out
 
 
+_RESULT_FD = None
+
+
+def _reserve_stdout():
+    """The contract is ONE JSON line on stdout. Libraries write there too (NCCL prints its version banner on the first
+    communicator), so keep a private duplicate of fd 1 for the result and point fd 1 at stderr for everything else."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def print_result(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
     args = parse()
+    _reserve_stdout()
     if args.impl == "reference":
         run_reference_arm(args)
     else:

@@ -257,6 +257,45 @@ def test_replica_guard_world_size_2_gloo(tmp_path):
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
 
 
+def test_lockstep_sampling_world_size_2_gloo(tmp_path):
+    """dp.lockstep_sampling: ranks whose multinomial draws would differ (here: differently seeded generators, on CUDA:
+    the unordered cumsum inside torch.multinomial) end up with rank 0's indices; outside the context torch.multinomial is
+    the stock function again. The caller is the reference's _sample_alives (scene/gaussian_model_static.py:412-422)."""
+    script = tmp_path / "worker.py"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script.write_text(textwrap.dedent(f"""
+        import os, sys
+        sys.path.insert(0, {os.path.join(root, '3dgs-mcmc_b200')!r})
+        import torch, torch.distributed as dist
+        from diff_gaussian_rasterization import dp
+        dist.init_process_group("gloo")
+        r = dist.get_rank()
+        stock = torch.multinomial
+        torch.manual_seed(10 + r)                      # the ranks would draw differently
+        probs = torch.linspace(0.1, 1.0, 5000)
+        with dp.lockstep_sampling():
+            idx = torch.multinomial(probs, 700, replacement=True)
+            ratio = torch.bincount(idx, minlength=5000)
+        assert torch.multinomial is stock
+        both = [torch.zeros_like(idx) for _ in range(2)]
+        dist.all_gather(both, idx)
+        assert torch.equal(both[0], both[1])
+        assert dp.assert_replicas_in_sync([idx, ratio])
+        free = torch.multinomial(probs, 700, replacement=True)
+        both = [torch.zeros_like(free) for _ in range(2)]
+        dist.all_gather(both, free)
+        assert not torch.equal(both[0], both[1])        # without the context the differently seeded ranks disagree
+        dist.destroy_process_group()
+        open(os.path.join({str(tmp_path)!r}, f"ok{{r}}"), "w").write("ok")
+    """))
+    port = _free_port()
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
+                         capture_output=True, text=True, timeout=240)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+
+
 def test_camera_conventions():
     cam = gs_synth.look_at_camera((0.0, 0.0, -4.0), (0.0, 0.0, 0.0), 64, 48, 0.8)
     V = cam["viewmatrix"]            # transposed storage: element [4*i+j] of the transposed matrix

@@ -77,8 +77,9 @@ def mcmc_lockstep_check(args, dp, dev, rank, world):
     under baseline/_ref/py) as a replica - its activations, `relocate_gs`, `add_new_gs`, optimizer surgery - renders its own
     view through dp.ViewParallelRasterizer, and applies the summed gradients with FusedAdam and the reference's inline noise
     (train_static.py:132-140, torch.randn_like on the identically seeded device RNG). Every `interval` steps: relocation +
-    5 % growth (torch.multinomial / bincount, :412-422, :458-492), then ViewParallelRasterizer.resize(P) and
-    dp.assert_replicas_in_sync. The replicas must stay bit-identical throughout without any broadcast."""
+    5 % growth (torch.multinomial / bincount, :412-422, :458-492) inside dp.lockstep_sampling() - the sampled indices are the
+    one thing that is broadcast, because torch's CUDA multinomial is not reproducible from launch to launch - then
+    ViewParallelRasterizer.resize(P) and dp.assert_replicas_in_sync. The replicas must stay bit-identical throughout."""
     import types
     import numpy as np
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -127,6 +128,22 @@ def mcmc_lockstep_check(args, dp, dev, rank, world):
                                                                       g.optimizer.state[grp["params"][0]]["exp_avg_sq"])]
     relocations = grown = 0
     sizes, losses = [P0], []
+    names = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
+    trace = []
+
+    def differing(tag, tensors, labels):
+        """--mcmc-debug: which of the given replicated tensors differ between the ranks right now."""
+        if not args.mcmc_debug:
+            return
+        bad = []
+        for lab, t in zip(labels, tensors):
+            h = dp.replica_fingerprint([t]).to(dev)
+            hs = [torch.zeros_like(h) for _ in range(world)]
+            dist.all_gather(hs, h)
+            if not all(bool((x == hs[0]).all()) for x in hs):
+                bad.append(lab)
+        if bad:
+            trace.append({"step": it, "at": tag, "differ": bad})
     for it in range(1, args.mcmc_steps + 1):
         xyz_lr = g.update_learning_rate(it)
         view = (it * world + rank) % len(cams)
@@ -140,25 +157,36 @@ def mcmc_lockstep_check(args, dp, dev, rank, world):
         loss.backward()
         losses.append(float(loss.item()))
         with torch.no_grad():
+            differing("grads after backward", [t.grad for t in params()], names)
             if it % args.mcmc_interval == 0:
                 dead = (g.get_opacity <= 0.005).squeeze(-1)
                 n_dead = int(dead.sum())
-                g.relocate_gs(dead_mask=dead)
-                added = g.add_new_gs(cap_max=cap)
+                differing("before relocation", params() + state(), names + tuple(f"state{i}" for i in range(12)))
+                with dp.lockstep_sampling():              # rank 0's multinomial draws, broadcast (dp.py: why seeding alone fails)
+                    g.relocate_gs(dead_mask=dead)
+                    differing("after relocate_gs", params() + state(), names + tuple(f"state{i}" for i in range(12)))
+                    added = g.add_new_gs(cap_max=cap)
+                differing("after add_new_gs", params() + state(), names + tuple(f"state{i}" for i in range(12)))
                 relocations += n_dead
                 grown += int(added)
                 vp.resize(g.get_xyz.shape[0])
                 sizes.append(int(g.get_xyz.shape[0]))
-                dp.assert_replicas_in_sync(params() + state(), what=f"replicas after relocation/growth at step {it}")
+                if not args.mcmc_debug:
+                    dp.assert_replicas_in_sync(params() + state(), what=f"replicas after relocation/growth at step {it}")
             g.optimizer.step()
             g.optimizer.zero_grad(set_to_none=True)
             L = build_scaling_rotation(g.get_scaling, g.get_rotation)
             cov = L @ L.transpose(1, 2)
             noise = torch.randn_like(g._xyz) * (1 / (1 + torch.exp(-100 * ((1 - g.get_opacity) - 0.995)))) * opt.noise_lr * xyz_lr
             g._xyz.add_(torch.bmm(cov, noise.unsqueeze(-1)).squeeze(-1))
+            differing("after Adam + noise", params(), names)
+            if args.mcmc_debug and len(trace) >= 6:
+                break
     torch.cuda.synchronize()
+    if args.mcmc_debug:
+        return {"debug_trace": trace}
     ident = {}
-    for name, t in zip(("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation"), params()):
+    for name, t in zip(names, params()):
         h = dp.replica_fingerprint([t]).to(dev)
         hs = [torch.zeros_like(h) for _ in range(world)]
         dist.all_gather(hs, h)
@@ -185,6 +213,7 @@ def main():
                     help="run this many training iterations of the reference's own GaussianModel as replicas, with relocation + "
                          "growth + resize every --mcmc-interval steps, and check that they stay bit-identical")
     ap.add_argument("--mcmc-interval", type=int, default=5)
+    ap.add_argument("--mcmc-debug", action="store_true", help="report where the replicas first differ instead of raising")
     ap.add_argument("--mcmc-P", type=int, default=100003)
     ap.add_argument("--skip-exchange", action="store_true", help="only the --train-steps / --mcmc-steps checks")
     args = ap.parse_args()
