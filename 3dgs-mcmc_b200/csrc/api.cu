@@ -66,7 +66,7 @@ unsigned long long* g_fwd_counters = nullptr;   // set by gs_debug_forward_work 
 
 extern "C" {
 
-int gs_abi_version(void) { return 105; }
+int gs_abi_version(void) { return 106; }
 
 const char* gs_error_string(int code) {
     if (code == GS_OK) return "ok";
@@ -276,18 +276,22 @@ int gs_debug_render_work(void* stream_, int P, unsigned int R, int W, int H, con
     return launch_render_work(rb, (int)tiles, walked_per_tile, evaluated_per_tile, stream);
 }
 
-int gs_backward_geometry(void* stream_, int P, int D, int M, int W, int H, const float* means3D, const float* shs,
-                         const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
-                         const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,
-                         float tan_fovy, const int* radii, const void* geom_ws, const void* scratch, float* dL_dmeans2D,
-                         float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
-                         float* dL_dscales, float* dL_drotations) {
+static int fill_peers(DpPeers* peers, float* const* ptrs, int n);
+
+// push: null = the dense outputs; else the "records" exchange (the five parameter gradients leave as chunk records)
+static int backward_geometry_impl(void* stream_, int P, int D, int M, int W, int H, const float* means3D, const float* shs,
+                                  const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                                  const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,
+                                  float tan_fovy, const int* radii, const void* geom_ws, const void* scratch, float* dL_dmeans2D,
+                                  float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                                  float* dL_dscales, float* dL_drotations, const DpPeers* push, size_t push_offset,
+                                  int push_multicast) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return GS_ERR_ARG;
     if (P == 0) return GS_OK;
-    if (!means3D || !radii || !geom_ws || !scratch || !viewmatrix || !projmatrix) return GS_ERR_ARG;
-    if (!dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || !dL_dscales || !dL_drotations)
-        return GS_ERR_ARG;
+    if (!means3D || !radii || !geom_ws || !scratch || !viewmatrix || !projmatrix || !dL_dmeans2D) return GS_ERR_ARG;
+    if (!push && (!dL_dcolors || !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || !dL_dscales || !dL_drotations)) return GS_ERR_ARG;
+    if (push && (!shs || !scales || !rotations || cov3D_precomp || (push_offset & 3))) return GS_ERR_ARG;
     if (shs && !campos) return GS_ERR_ARG;
     if (shs && !dL_dsh && 3 * M > 48) return GS_ERR_ARG;   // factored mode needs the staged SH rows (sh_stage.cuh: kShMaxRow)
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
@@ -306,10 +310,37 @@ int gs_backward_geometry(void* stream_, int P, int D, int M, int W, int H, const
     pb.acc_color_opacity = sc.acc_color_opacity; pb.acc_mean_conic = sc.acc_mean_conic; pb.acc_conic_w = sc.acc_conic_w;
     pb.dL_dmeans3D = dL_dmeans3D; pb.dL_dmeans2D = dL_dmeans2D; pb.dL_dcolors = dL_dcolors; pb.dL_dopacity = dL_dopacity;
     pb.dL_dcov3D = dL_dcov3D; pb.dL_dsh = dL_dsh; pb.dL_dscales = dL_dscales; pb.dL_drots = dL_drotations;
+    pb.push.n = 0; pb.push_offset = 0; pb.push_multicast = 0;
+    if (push) { pb.push = *push; pb.push_offset = push_offset; pb.push_multicast = push_multicast; }
     const int rc = launch_preprocess_bwd(pb, stream);
     prof_mark(stream, ST_PREPROCESS_BWD);
     count_launches(1);
     return rc;
+}
+
+int gs_backward_geometry(void* stream_, int P, int D, int M, int W, int H, const float* means3D, const float* shs,
+                         const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                         const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,
+                         float tan_fovy, const int* radii, const void* geom_ws, const void* scratch, float* dL_dmeans2D,
+                         float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                         float* dL_dscales, float* dL_drotations) {
+    return backward_geometry_impl(stream_, P, D, M, W, H, means3D, shs, scales, scale_modifier, rotations, cov3D_precomp,
+                                  viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii, geom_ws, scratch, dL_dmeans2D,
+                                  dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, nullptr, 0, 0);
+}
+
+int gs_backward_geometry_push(void* stream_, int P, int D, int M, int W, int H, const float* means3D, const float* shs,
+                              const float* scales, float scale_modifier, const float* rotations, const float* viewmatrix,
+                              const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                              const void* geom_ws, const void* scratch, float* dL_dmeans2D, float* const* dst_ptrs, int n_dst,
+                              int multicast, size_t slot_offset) {
+    DpPeers peers;
+    const int rc = fill_peers(&peers, dst_ptrs, n_dst);
+    if (rc) return rc;
+    if (multicast && n_dst != 1) return GS_ERR_ARG;
+    return backward_geometry_impl(stream_, P, D, M, W, H, means3D, shs, scales, scale_modifier, rotations, nullptr, viewmatrix,
+                                  projmatrix, campos, tan_fovx, tan_fovy, radii, geom_ws, scratch, dL_dmeans2D, nullptr, nullptr,
+                                  nullptr, nullptr, nullptr, nullptr, nullptr, &peers, slot_offset, multicast);
 }
 
 int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H, const float* background,
@@ -344,10 +375,41 @@ static int fill_peers(DpPeers* peers, float* const* ptrs, int n) {
     return GS_OK;
 }
 
-int gs_dp_color_grad_push(void* stream_, int P, const int* radii, const void* geom_ws, const void* scratch,
-                          float* const* dst_ptrs, int n_dst, int multicast, size_t slot_offset) {
+size_t gs_dp_slot_floats(int P, int layout) {
+    if (P <= 0) return 0;
+    if (layout == GS_DP_RECORDS) return (size_t)kRecFloats * (size_t)((P + kRecChunk - 1) / kRecChunk);
+    return layout == GS_DP_SPARSE ? dp_sparse_slot_floats(P) : ((size_t)3 * P + 3) / 4 * 4;
+}
+
+int gs_dp_grad_record_combine(void* stream_, int P, int D, int M, int V, const float* means3D, const float* campos_views,
+                              const float* records, size_t slot_stride, int outputs_are_zero, float* dL_dmeans3D,
+                              float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dsh) {
     cudaStream_t stream = (cudaStream_t)stream_;
-    if (P < 0 || (slot_offset & 3)) return GS_ERR_ARG;
+    if (P < 0 || D < 0 || D > 3 || V < 1) return GS_ERR_ARG;
+    if (P == 0) return GS_OK;
+    if (!means3D || !campos_views || !records || !dL_dmeans3D || !dL_dopacity || !dL_dscales || !dL_drotations || !dL_dsh)
+        return GS_ERR_ARG;
+    if (slot_stride < gs_dp_slot_floats(P, GS_DP_RECORDS) || (slot_stride & 3) || (reinterpret_cast<size_t>(records) & 15))
+        return GS_ERR_ARG;
+    prof_mark(stream, -1);
+    if (!outputs_are_zero) {
+        GS_CUDA_TRY(cudaMemsetAsync(dL_dmeans3D, 0, (size_t)P * 3 * sizeof(float), stream));
+        GS_CUDA_TRY(cudaMemsetAsync(dL_dopacity, 0, (size_t)P * sizeof(float), stream));
+        GS_CUDA_TRY(cudaMemsetAsync(dL_dscales, 0, (size_t)P * 3 * sizeof(float), stream));
+        GS_CUDA_TRY(cudaMemsetAsync(dL_drotations, 0, (size_t)P * 4 * sizeof(float), stream));
+        GS_CUDA_TRY(cudaMemsetAsync(dL_dsh, 0, (size_t)P * M * 3 * sizeof(float), stream));
+    }
+    const int rc = launch_grad_record_combine(P, D, M, V, means3D, campos_views, records, slot_stride, dL_dmeans3D, dL_dopacity,
+                                              dL_dscales, dL_drotations, dL_dsh, stream);
+    prof_mark(stream, ST_DP_COMBINE);
+    count_launches(outputs_are_zero ? 1 : 6);
+    return rc;
+}
+
+int gs_dp_color_grad_push(void* stream_, int P, const int* radii, const void* geom_ws, const void* scratch,
+                          float* const* dst_ptrs, int n_dst, int multicast, size_t slot_offset, int layout) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P < 0 || (slot_offset & 3) || (layout != GS_DP_DENSE && layout != GS_DP_SPARSE)) return GS_ERR_ARG;
     if (P == 0) return GS_OK;
     if (!radii || !geom_ws || !scratch) return GS_ERR_ARG;
     DpPeers peers;
@@ -357,20 +419,30 @@ int gs_dp_color_grad_push(void* stream_, int P, const int* radii, const void* ge
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
     BwdScratch sc = BwdScratch::carve(aligned_base(scratch), (size_t)P);
     prof_mark(stream, -1);
-    rc = launch_color_grad_push(P, radii, g.clamped, sc.acc_color_opacity, peers, slot_offset, multicast != 0, stream);
+    if (layout == GS_DP_SPARSE) {
+        int dev = 0, sms = 0;
+        GS_CUDA_TRY(cudaGetDevice(&dev));
+        GS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        rc = launch_color_grad_push_sparse(P, radii, g.clamped, sc.acc_color_opacity, peers, slot_offset, multicast != 0, sms, stream);
+    } else {
+        rc = launch_color_grad_push(P, radii, g.clamped, sc.acc_color_opacity, peers, slot_offset, multicast != 0, stream);
+    }
     prof_mark(stream, ST_DP_PUSH);
     count_launches(1);
     return rc;
 }
 
 int gs_dp_sh_grad_combine(void* stream_, int P, int D, int M, int V, const float* means3D, const float* campos_views,
-                          const float* color_grads, size_t slot_stride, float* dL_dsh) {
+                          const float* color_grads, size_t slot_stride, int layout, float* dL_dsh) {
     cudaStream_t stream = (cudaStream_t)stream_;
-    if (P < 0 || D < 0 || D > 3 || V < 1) return GS_ERR_ARG;
+    if (P < 0 || D < 0 || D > 3 || V < 1 || (layout != GS_DP_DENSE && layout != GS_DP_SPARSE)) return GS_ERR_ARG;
     if (P == 0) return GS_OK;
-    if (!means3D || !campos_views || !color_grads || !dL_dsh || slot_stride < (size_t)3 * P) return GS_ERR_ARG;
+    if (!means3D || !campos_views || !color_grads || !dL_dsh) return GS_ERR_ARG;
+    if (slot_stride < (layout == GS_DP_SPARSE ? dp_sparse_slot_floats(P) : (size_t)3 * P)) return GS_ERR_ARG;
+    if (layout == GS_DP_SPARSE && ((reinterpret_cast<size_t>(color_grads) & 15) || (slot_stride & 3))) return GS_ERR_ARG;
     prof_mark(stream, -1);
-    const int rc = launch_sh_grad_combine(P, D, M, V, means3D, campos_views, color_grads, slot_stride, dL_dsh, stream);
+    const int rc = launch_sh_grad_combine(P, D, M, V, means3D, campos_views, color_grads, slot_stride, layout == GS_DP_SPARSE,
+                                          dL_dsh, stream);
     prof_mark(stream, ST_DP_COMBINE);
     count_launches(1);
     return rc;

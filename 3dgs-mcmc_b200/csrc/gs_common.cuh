@@ -45,6 +45,36 @@ __device__ constexpr float kSH3[7] = {-0.5900435899266435f, 2.890611442640554f, 
                                      0.3731763325901154f,  -0.4570457994644658f, 1.445305721320277f,
                                      -0.5900435899266435f};
 
+// Real SH basis b[0..(deg+1)^2) at the unit direction (x, y, z), every operation rounded on its own (no FMA contraction):
+// the per-Gaussian backward (preprocess_bwd.cu) and the exchange's rebuild kernels (dp_exchange.cu) must produce the same
+// bits from the same direction whatever the compiler does around them.
+__device__ __forceinline__ void sh_basis_rn(int deg, float x, float y, float z, float* __restrict__ b) {
+    b[0] = kSH0;
+    if (deg < 1) return;
+    b[1] = __fmul_rn(-kSH1, y);
+    b[2] = __fmul_rn(kSH1, z);
+    b[3] = __fmul_rn(-kSH1, x);
+    if (deg < 2) return;
+    const float xx = __fmul_rn(x, x), yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+    const float xy = __fmul_rn(x, y), yz = __fmul_rn(y, z), xz = __fmul_rn(x, z);
+    const float xx_yy = __fsub_rn(xx, yy);
+    b[4] = __fmul_rn(kSH2[0], xy);
+    b[5] = __fmul_rn(kSH2[1], yz);
+    b[6] = __fmul_rn(kSH2[2], __fsub_rn(__fsub_rn(__fmul_rn(2.f, zz), xx), yy));
+    b[7] = __fmul_rn(kSH2[3], xz);
+    b[8] = __fmul_rn(kSH2[4], xx_yy);
+    if (deg < 3) return;
+    const float four_zz_xx_yy = __fsub_rn(__fsub_rn(__fmul_rn(4.f, zz), xx), yy);
+    b[9] = __fmul_rn(__fmul_rn(kSH3[0], y), __fsub_rn(__fmul_rn(3.f, xx), yy));
+    b[10] = __fmul_rn(__fmul_rn(kSH3[1], xy), z);
+    b[11] = __fmul_rn(__fmul_rn(kSH3[2], y), four_zz_xx_yy);
+    b[12] = __fmul_rn(__fmul_rn(kSH3[3], z), __fsub_rn(__fsub_rn(__fmul_rn(2.f, zz), __fmul_rn(3.f, xx)), __fmul_rn(3.f, yy)));
+    b[13] = __fmul_rn(__fmul_rn(kSH3[4], x), four_zz_xx_yy);
+    b[14] = __fmul_rn(__fmul_rn(kSH3[5], z), xx_yy);
+    b[15] = __fmul_rn(__fmul_rn(kSH3[6], x), __fsub_rn(xx, __fmul_rn(3.f, yy)));
+}
+
+
 struct V3 {
     float x, y, z;
     GS_DEV V3() {}

@@ -63,6 +63,21 @@ struct RenderBwdParams {
     float* __restrict__ acc_conic_w;         // [P] dL/dconic.w
 };
 
+// Up to 8 device pointers to the same symmetric buffer on the ranks of one node (index = rank), or one NVSwitch
+// multicast pointer in ptr[0] with n == 1 (dp_exchange.cu).
+struct DpPeers {
+    float* ptr[8];
+    int n;
+};
+
+// Gradient records (dp_exchange.cu, "records" layout): per chunk of kRecChunk consecutive Gaussians one record of
+// kRecFloats floats = kRecChunk/32 x (u32 mask, u32 set bits before this word), then 14 floats per set bit in index order:
+// masked dL/dRGB 3 | dL/dmean3D 3 | dL/dopacity 1 | dL/dscale 3 | dL/drotation 4.
+constexpr int kRecChunk = 128;
+constexpr int kRecHeader = 2 * (kRecChunk / 32);
+constexpr int kRecWidth = 14;
+constexpr int kRecFloats = kRecHeader + kRecWidth * kRecChunk;
+
 struct PreprocessBwdParams {
     int P, D, M;
     const float* __restrict__ means3D;
@@ -91,13 +106,12 @@ struct PreprocessBwdParams {
     float* __restrict__ dL_dsh;        // [P,M,3]; null with shs non-null = factored exchange (dp_exchange.cu): rows not written
     float* __restrict__ dL_dscales;    // [P,3]
     float* __restrict__ dL_drots;      // [P,4]
-};
-
-// Up to 8 device pointers to the same symmetric buffer on the ranks of one node (index = rank), or one NVSwitch
-// multicast pointer in ptr[0] with n == 1 (dp_exchange.cu).
-struct DpPeers {
-    float* ptr[8];
-    int n;
+    // View-sharded exchange, "records" layout: push.n > 0 = instead of the dense dL_dmeans3D / dL_dopacity / dL_dscales /
+    // dL_drots / dL_dsh arrays (then null, like dL_dcolors / dL_dcov3D may be), every block stores its chunk's record at float
+    // offset push_offset + block * kRecFloats of each buffer in push (peer pointers, or one multicast pointer).
+    DpPeers push;
+    size_t push_offset;
+    int push_multicast;
 };
 
 // Fused L1 + SSIM loss (loss.cu). win = the normalised 11-tap Gaussian window (sigma 1.5) in FP32.
@@ -203,8 +217,14 @@ size_t knn_workspace_bytes(int P);
 int launch_knn_mean_dist2(int P, const float* points, float* out, char* ws, cudaStream_t stream);
 int launch_color_grad_push(int P, const int* radii, const uint8_t* clamped, const float4* acc, const DpPeers& dst,
                            size_t slot_offset, bool multicast, cudaStream_t stream);
+int launch_color_grad_push_sparse(int P, const int* radii, const uint8_t* clamped, const float4* acc, const DpPeers& dst,
+                                  size_t slot_offset, bool multicast, int sm_count, cudaStream_t stream);
+size_t dp_sparse_slot_floats(int P);
+int launch_grad_record_combine(int P, int D, int M, int V, const float* means3D, const float* campos, const float* gathered,
+                               size_t slot_stride, float* dL_dmeans3D, float* dL_dopacity, float* dL_dscales, float* dL_drots,
+                               float* dL_dsh, cudaStream_t stream);
 int launch_sh_grad_combine(int P, int D, int M, int V, const float* means3D, const float* campos, const float* gathered,
-                           size_t slot_stride, float* dL_dsh, cudaStream_t stream);
+                           size_t slot_stride, bool sparse, float* dL_dsh, cudaStream_t stream);
 int launch_slab_all_reduce(const DpPeers& peers, bool multicast, size_t n_floats, int rank, int world, int sm_count,
                            cudaStream_t stream);
 

@@ -90,29 +90,7 @@ GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* s
     const float3 dmean = {(g_dir.x - dir.x * along) * inv_norm, (g_dir.y - dir.y * along) * inv_norm, (g_dir.z - dir.z * along) * inv_norm};
     // ---- phase 2: dL/dsh[k] = basis_k(dir) * dL/dRGB ----
     dL_dRGB_out = dL_dRGB;
-    auto W = [&](int k, float basis) { basis_out[k] = basis; };
-    W(0, kSH0);
-    if (deg > 0) {
-        W(1, -kSH1 * y);
-        W(2, kSH1 * z);
-        W(3, -kSH1 * x);
-        if (deg > 1) {
-            W(4, kSH2[0] * xy);
-            W(5, kSH2[1] * yz);
-            W(6, kSH2[2] * (2.f * zz - xx - yy));
-            W(7, kSH2[3] * xz);
-            W(8, kSH2[4] * (xx - yy));
-            if (deg > 2) {
-                W(9, kSH3[0] * y * (3.f * xx - yy));
-                W(10, kSH3[1] * xy * z);
-                W(11, kSH3[2] * y * (4.f * zz - xx - yy));
-                W(12, kSH3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy));
-                W(13, kSH3[4] * x * (4.f * zz - xx - yy));
-                W(14, kSH3[5] * z * (xx - yy));
-                W(15, kSH3[6] * x * (xx - 3.f * yy));
-            }
-        }
-    }
+    sh_basis_rn(deg, x, y, z, basis_out);
     return dmean;
 }
 
@@ -160,6 +138,8 @@ GS_DEV void cov3d_backward(const V3 scale, float mod, const float4 rot, const fl
 }
 
 constexpr int kPbThreads = 128;
+static_assert(kPbThreads == kRecChunk, "one block of the per-Gaussian backward produces one gradient record chunk");
+static_assert(kRecFloats <= (kPbThreads / 32) * kShTileFloats, "the record is staged in the (dead) SH tile");
 
 __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PreprocessBwdParams p) {
     __shared__ __align__(16) float s_sh[kPbThreads / 32][kShTileFloats];
@@ -201,8 +181,8 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
     // Pass-through outputs.
     if (valid) {
         store3(p.dL_dmeans2D, i, acc1.x, acc1.y, 0.f);
-        store3(p.dL_dcolors, i, acc0.x, acc0.y, acc0.z);
-        p.dL_dopacity[idx] = acc0.w;
+        if (p.dL_dcolors) store3(p.dL_dcolors, i, acc0.x, acc0.y, acc0.z);
+        if (p.dL_dopacity) p.dL_dopacity[idx] = acc0.w;
     }
 
     float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -310,10 +290,58 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
         }
     }
 
+    if (p.push.n > 0) {
+        // ---- view-sharded exchange: this block's chunk record goes straight to every rank's gather buffer ----
+        // (the SH tile is dead here: every warp is past sh_backward once the block has met at the first barrier)
+        __shared__ int s_cnt[kPbThreads / 32];
+        uint32_t* rec = reinterpret_cast<uint32_t*>(&s_sh[0][0]);
+        const float vals[kRecWidth] = {g_rgb.x, g_rgb.y, g_rgb.z, dmean.x, dmean.y, dmean.z, acc0.w,
+                                       dscale[0], dscale[1], dscale[2], drot.x, drot.y, drot.z, drot.w};
+        bool nz = false;
+#pragma unroll
+        for (int k = 0; k < kRecWidth; ++k) nz |= vals[k] != 0.f;
+        nz &= visible;
+        const uint32_t m = __ballot_sync(0xffffffffu, nz);
+        if (lane == 0) s_cnt[warp] = __popc(m);
+        __syncthreads();
+        int before = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < kPbThreads / 32; ++w) {
+            const int n = s_cnt[w];
+            before += w < warp ? n : 0;
+            total += n;
+        }
+        if (lane == 0) {
+            rec[2 * warp] = m;
+            rec[2 * warp + 1] = (uint32_t)before;
+        }
+        if (nz) {
+            float* r = reinterpret_cast<float*>(rec) + kRecHeader + kRecWidth * (before + __popc(m & ((1u << lane) - 1u)));
+#pragma unroll
+            for (int k = 0; k < kRecWidth; k += 2) *reinterpret_cast<float2*>(r + k) = make_float2(vals[k], vals[k + 1]);
+        }
+        __syncthreads();
+        const int n4 = kRecHeader / 4 + ((kRecWidth * total + 3) >> 2);      // 16-byte pieces: header + packed records
+        const size_t base = p.push_offset + (size_t)blockIdx.x * kRecFloats;
+        for (int q = threadIdx.x; q < n4; q += kPbThreads) {
+            const float4 v = reinterpret_cast<const float4*>(rec)[q];
+#pragma unroll 1
+            for (int d = 0; d < p.push.n; ++d) {
+                float* out = p.push.ptr[d] + base + 4 * q;
+                if (p.push_multicast)
+                    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(out), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+                else
+                    *reinterpret_cast<float4*>(out) = v;
+            }
+        }
+        return;
+    }
     if (valid) {
         store3(p.dL_dmeans3D, i, dmean.x, dmean.y, dmean.z);
+        if (p.dL_dcov3D) {
 #pragma unroll
-        for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * i + k] = dcov[k];
+            for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * i + k] = dcov[k];
+        }
         store3(p.dL_dscales, i, dscale[0], dscale[1], dscale[2]);
         store_quat(p.dL_drots, i, p.drot_aligned != 0, drot);
     }

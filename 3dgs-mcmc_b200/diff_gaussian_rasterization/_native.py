@@ -43,10 +43,15 @@ SIGNATURES = {
     "gs_backward_render": (_c_int, [_c_void_p, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 6),
     "gs_backward_geometry": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int] + [_c_void_p] * 3 + [_c_float]
                              + [_c_void_p] * 5 + [_c_float, _c_float] + [_c_void_p] * 11),
+    "gs_dp_slot_floats": (_c_size_t, [_c_int, _c_int]),
+    "gs_backward_geometry_push": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int] + [_c_void_p] * 3 + [_c_float]
+                                  + [_c_void_p] * 4 + [_c_float, _c_float] + [_c_void_p] * 5 + [_c_int, _c_int, _c_size_t]),
+    "gs_dp_grad_record_combine": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p,
+                                           _c_size_t, _c_int] + [_c_void_p] * 5),
     "gs_dp_color_grad_push": (_c_int, [_c_void_p, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_int,
-                                       _c_size_t]),
+                                       _c_size_t, _c_int]),
     "gs_dp_sh_grad_combine": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p,
-                                       _c_size_t, _c_void_p]),
+                                       _c_size_t, _c_int, _c_void_p]),
     "gs_dp_slab_all_reduce": (_c_int, [_c_void_p, _c_void_p, _c_int, _c_int, _c_size_t, _c_int, _c_int]),
     "gs_loss_workspace_bytes": (_c_size_t, [_c_int, _c_int, _c_int]),
     "gs_photometric_loss_forward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int] + [_c_void_p] * 4),
@@ -365,20 +370,87 @@ def _ptr_array(ptrs):
     return arr
 
 
-def dp_color_grad_push(P, radii, geomBuffer, scratch, dst_ptrs, slot_offset, multicast=False):
+DP_LAYOUTS = {"dense": 0, "sparse": 1, "records": 2}
+
+
+def backward_geometry_push(means3D, radii, scales, rotations, scale_modifier, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W,
+                           sh, degree, campos, geomBuffer, scratch, dst_ptrs, slot_offset, multicast=False, means2D_out=None):
+    """Second half of the backward for the "records" exchange (gs_backward_geometry_push): the parameter gradients leave as
+    sparse chunk records at float offset slot_offset of every buffer in dst_ptrs; returns dL_dmeans2D [P, 3]."""
+    device = means3D.device
+    P, M = int(means3D.size(0)), int(sh.size(1))
+    means3D = _f32_cuda(means3D, "means3D", device)
+    scales = _f32_cuda(scales, "scales", device)
+    rotations = _f32_cuda(rotations, "rotations", device)
+    viewmatrix = _f32_cuda(viewmatrix, "viewmatrix", device)
+    projmatrix = _f32_cuda(projmatrix, "projmatrix", device)
+    sh = _f32_cuda(sh, "sh", device)
+    campos = _f32_cuda(campos, "campos", device)
+    radii = radii.contiguous()
+    arr = _ptr_array(dst_ptrs)
+    with torch.cuda.device(device):
+        if means2D_out is None:
+            means2D_out = torch.empty((P, 3), dtype=torch.float32, device=device)
+        elif tuple(means2D_out.shape) != (P, 3) or means2D_out.dtype != torch.float32 or not means2D_out.is_contiguous():
+            raise RuntimeError(f"means2D_out must be a contiguous float32 {(P, 3)} tensor")
+        if P:
+            _check(_lib.gs_backward_geometry_push(
+                _stream(device), P, int(degree), M, int(W), int(H), _ptr(means3D), _ptr(sh), _ptr(scales),
+                float(scale_modifier), _ptr(rotations), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), float(tan_fovx),
+                float(tan_fovy), radii.data_ptr(), geomBuffer.data_ptr(), scratch.data_ptr(), means2D_out.data_ptr(),
+                ctypes.cast(arr, _c_void_p), len(dst_ptrs), 1 if multicast else 0, int(slot_offset)), "gs_backward_geometry_push")
+    return means2D_out
+
+
+def dp_grad_record_combine(means3D, campos_views, records, slot_stride, degree, M, outs=None, outputs_are_zero=False):
+    """Gradients summed over the V views whose chunk records sit in records[V, slot_stride] (gs_dp_grad_record_combine).
+    outs: dict of contiguous float32 tensors "means3D" [P,3], "opacity" [P,1], "scales" [P,3], "rotations" [P,4], "sh" [P,M,3]
+    (allocated when None); outputs_are_zero=True promises they hold zeros already."""
+    device = means3D.device
+    P, V = int(means3D.size(0)), int(campos_views.size(0))
+    means3D = _f32_cuda(means3D, "means3D", device)
+    campos_views = _f32_cuda(campos_views, "campos_views", device)
+    records = _f32_cuda(records, "records", device)
+    if records.numel() < V * slot_stride:
+        raise RuntimeError("records is smaller than V * slot_stride floats")
+    shapes = {"means3D": (P, 3), "opacity": (P, 1), "scales": (P, 3), "rotations": (P, 4), "sh": (P, int(M), 3)}
+    if outs is None:
+        outs = {k: torch.empty(shp, dtype=torch.float32, device=device) for k, shp in shapes.items()}
+        outputs_are_zero = False
+    for k, shp in shapes.items():
+        t = outs[k]
+        if tuple(t.shape) != shp or t.dtype != torch.float32 or not t.is_contiguous() or t.device != device:
+            raise RuntimeError(f"outs[{k!r}] must be a contiguous float32 {shp} tensor on {device}")
+    if P:
+        with torch.cuda.device(device):
+            _check(_lib.gs_dp_grad_record_combine(
+                _stream(device), P, int(degree), int(M), V, means3D.data_ptr(), campos_views.data_ptr(), records.data_ptr(),
+                int(slot_stride), 1 if outputs_are_zero else 0, outs["means3D"].data_ptr(), outs["opacity"].data_ptr(),
+                outs["scales"].data_ptr(), outs["rotations"].data_ptr(), outs["sh"].data_ptr()), "gs_dp_grad_record_combine")
+    return outs
+
+
+def dp_slot_floats(P, layout="sparse"):
+    """Floats one view's slot of the gather buffer needs for P Gaussians (gs_dp_slot_floats)."""
+    return int(_lib.gs_dp_slot_floats(int(P), DP_LAYOUTS[layout]))
+
+
+def dp_color_grad_push(P, radii, geomBuffer, scratch, dst_ptrs, slot_offset, multicast=False, layout="dense"):
     """Masked dL/dRGB of this rank's view -> float offset slot_offset of every buffer in dst_ptrs (raw device
-    pointers: this rank's own buffer and its peers', or one multicast pointer). gs_dp_color_grad_push."""
+    pointers: this rank's own buffer and its peers', or one multicast pointer). layout "dense": [P][3] floats; "sparse":
+    bit masks + the non-zero triples only (include/gs_b200.h). gs_dp_color_grad_push."""
     device = radii.device
     arr = _ptr_array(dst_ptrs)
     with torch.cuda.device(device):
         _check(_lib.gs_dp_color_grad_push(_stream(device), int(P), radii.data_ptr(), geomBuffer.data_ptr(),
                                           scratch.data_ptr(), ctypes.cast(arr, _c_void_p), len(dst_ptrs),
-                                          1 if multicast else 0, int(slot_offset)), "gs_dp_color_grad_push")
+                                          1 if multicast else 0, int(slot_offset), DP_LAYOUTS[layout]),
+               "gs_dp_color_grad_push")
 
 
-def dp_sh_grad_combine(means3D, campos_views, color_grads, slot_stride, degree, M, out=None):
+def dp_sh_grad_combine(means3D, campos_views, color_grads, slot_stride, degree, M, out=None, layout="dense"):
     """dL_dsh[P, M, 3] summed over the V views whose masked colour gradients sit in color_grads[V, slot_stride]
-    (gs_dp_sh_grad_combine)."""
+    in the given layout (gs_dp_sh_grad_combine)."""
     device = means3D.device
     P = int(means3D.size(0))
     V = int(campos_views.size(0))
@@ -395,7 +467,7 @@ def dp_sh_grad_combine(means3D, campos_views, color_grads, slot_stride, degree, 
         with torch.cuda.device(device):
             _check(_lib.gs_dp_sh_grad_combine(_stream(device), P, int(degree), int(M), V, means3D.data_ptr(),
                                               campos_views.data_ptr(), color_grads.data_ptr(), int(slot_stride),
-                                              out.data_ptr()), "gs_dp_sh_grad_combine")
+                                              DP_LAYOUTS[layout], out.data_ptr()), "gs_dp_sh_grad_combine")
     return out
 
 

@@ -143,6 +143,16 @@ class FactoredExchange:
     gather + a 132 MB all-reduce, against a 708 MB all-reduce; the summed gradients are the same on every rank bit
     for bit (views are added in rank order).
 
+    layout (what travels; all three give the same sums, views added in rank order):
+      "records" (default) where a view's colour gradient is zero (culled, or never blended: 92 % of the Gaussians per view
+              at the bench scene) so are its other gradients, so the per-Gaussian backward itself stores - per chunk of 128
+              Gaussians - a bit mask and the 14-float records of the non-zero ones into every rank's gather buffer, and each
+              rank adds the views in rank order (gs_backward_geometry_push + gs_dp_grad_record_combine). No all-reduce, no
+              slab, ONE barrier per step (the gather buffer is double buffered), outputs are fresh tensors (zeroed on a side
+              stream while the tile backward runs) that autograd takes without a copy.
+      "sparse" colour gradients as bit masks + non-zero triples, the other 11 floats all-reduced in a symmetric slab.
+      "dense"  colour gradients as [P][3] floats, the other 11 floats all-reduced.
+
     transport:
       "symm"  torch symmetric memory over NVLink: the kernel that masks dL_dRGB stores it straight into every rank's
               gather buffer (NVSwitch multicast store when available, else peer stores) - the all-gather is fused
@@ -155,7 +165,7 @@ class FactoredExchange:
 
     SLAB_FIELDS = (("means3D", 3), ("opacity", 1), ("scales", 3), ("rotations", 4))
 
-    def __init__(self, P, M, device, group=None, transport="auto", multicast=None, capacity=None):
+    def __init__(self, P, M, device, group=None, transport="auto", multicast=None, capacity=None, layout=None):
         """capacity: number of Gaussians the (symmetric) buffers are sized for, >= P; the MCMC trainer grows the model
         by 5 % every densification step up to cap_max (gaussian_model_static.py:460-492) - allocate once for cap_max and
         call resize(P) after each growth instead of a new rendezvous.
@@ -170,10 +180,27 @@ class FactoredExchange:
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if self.world > 1 else 0
-        self.slot_stride = _round_up(3 * self.capacity, 64)      # fixed: slot r of the gather buffer starts at r * slot_stride
-        slab_floats = _round_up(11 * self.capacity + 12, 64)      # + the pad that aligns every field block (resize)
-        total = slab_floats + self.world * self.slot_stride
         self.transport = self._pick_transport(transport)
+        layout = os.environ.get("GS_DP_LAYOUT") if layout is None else layout
+        if layout is None:
+            # records need the gather to be cheap for absent Gaussians: peer stores. Through an NCCL all-gather whole
+            # slots would travel, so that fallback keeps the dense gather + all-reduce.
+            layout = "records" if (self.world == 1 or self.transport == "symm") and self.device.type == "cuda" else "dense"
+        self.layout = layout
+        if self.layout not in ("records", "sparse", "dense"):
+            raise ValueError(f"layout must be records, sparse or dense, got {self.layout!r}")
+        # fixed: slot r of a gather buffer starts at r * slot_stride floats (include/gs_b200.h: gs_dp_slot_floats)
+        per_layout = {"records": (self.capacity + 127) // 128 * 1800, "sparse": (self.capacity + 255) // 256 * 784,
+                      "dense": 3 * self.capacity}
+        self.slot_stride = _round_up(per_layout[self.layout], 64)
+        self._step = 0
+        if self.layout == "records":
+            slab_floats = 0
+            self._nbuf = 2 if self.world > 1 else 1               # double buffered: one barrier per step is enough
+        else:
+            slab_floats = _round_up(11 * self.capacity + 12, 64)  # + the pad that aligns every field block (resize)
+            self._nbuf = 1
+        total = slab_floats + self._nbuf * self.world * self.slot_stride
         # "classic": slab all-reduce beside the SH rebuild (default). "early_reduce": slab all-reduce while the gather is
         # still in flight, SH rebuild alone afterwards - measured equal within noise on 8xB200 at P = 3M (2.67 vs 2.66 ms
         # backward + exchange): the reduce then competes with the gather for NVLink ingress.
@@ -203,7 +230,11 @@ class FactoredExchange:
             self._multicast = False
             self._send = torch.zeros(self.slot_stride, dtype=torch.float32, device=self.device)
         self._slab_capacity = slab_floats
-        self.gathered = self.flat[slab_floats:].view(self.world, self.slot_stride)
+        self._gathered_all = self.flat[slab_floats:].view(self._nbuf, self.world, self.slot_stride)
+        self.gathered = self._gathered_all[0]
+        if self.device.type == "cuda":
+            self._zero_stream = torch.cuda.Stream(device=self.device, priority=-1)
+            self._ev_zero_fork, self._ev_zero = torch.cuda.Event(), torch.cuda.Event()
         self.resize(self.P)
 
     def resize(self, P):
@@ -214,6 +245,9 @@ class FactoredExchange:
             raise ValueError(f"P {P} exceeds the capacity {self.capacity} this exchange was allocated for")
         self.P = P
         self.grads = {}
+        if self.layout == "records":                              # no slab, no persistent outputs: nothing to re-slice
+            self.local = {}
+            return self
         off = 0
         for name, w in self.SLAB_FIELDS:                          # every block 16-byte aligned for any P
             self.grads[name] = self.flat[off: off + P * w].view(P, w)
@@ -275,7 +309,7 @@ class FactoredExchange:
         gather buffer. "symm": the kernel's own NVLink stores; "nccl": an asynchronous all-gather that overlaps the
         per-Gaussian backward kernel. Returns a handle for finish()."""
         if self.world == 1:
-            native.dp_color_grad_push(self.P, radii, geom, scratch, [self.gathered.data_ptr()], 0, False)
+            native.dp_color_grad_push(self.P, radii, geom, scratch, [self.gathered.data_ptr()], 0, False, layout=self.layout)
             return None
         if self.transport == "symm":
             # on the side stream: the NVLink stores (36 MB out, (world-1) x 36 MB in at P = 3M) drain while the
@@ -285,10 +319,10 @@ class FactoredExchange:
             self._side.wait_event(self._ev_fork)
             with torch.cuda.stream(self._side):
                 native.dp_color_grad_push(self.P, radii, geom, scratch, self._gather_ptrs, self.rank * self.slot_stride,
-                                          self._multicast)
+                                          self._multicast, layout=self.layout)
                 self._ev_push.record(self._side)
             return None
-        native.dp_color_grad_push(self.P, radii, geom, scratch, [self._send.data_ptr()], 0, False)
+        native.dp_color_grad_push(self.P, radii, geom, scratch, [self._send.data_ptr()], 0, False, layout=self.layout)
         return dist.all_gather_into_tensor(self.gathered.view(-1), self._send, group=self.group, async_op=True)
 
     def finish(self, native, means3D, campos_views, degree, pending=None, sh_out=None):
@@ -320,7 +354,7 @@ class FactoredExchange:
             reduce_work = dist.all_reduce(self.slab, group=self.group, async_op=True)
             pending.wait()
         sh_grad = native.dp_sh_grad_combine(means3D, campos_views, self.gathered, self.slot_stride, degree, self.M,
-                                            out=self.grads["sh"] if sh_out is None else sh_out)
+                                            out=self.grads["sh"] if sh_out is None else sh_out, layout=self.layout)
         if symm and self.schedule == "early_reduce":
             self._hdl.barrier(channel=2)                 # peers are done reading this rank's gather slots
         elif symm:
@@ -339,6 +373,10 @@ class FactoredExchange:
         of the step's views in rank order (every rank knows the step's view list; row `rank` equals `campos`).
         Returns {"means3D", "sh", "opacity", "scales", "rotations"}: gradients summed over all ranks."""
         H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
+        if self.layout == "records":
+            return self._backward_records(native, bg, means3D, radii, scales, rotations, scale_modifier, viewmatrix, projmatrix,
+                                          tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, campos_views, geom, R, binning,
+                                          img, H, W)
         e = torch.empty(0)
         scratch = native.backward_render(bg, self.P, R, dL_dout_color, geom, binning, img)
         pending = self.push_color_grads(native, radii, geom, scratch)
@@ -346,6 +384,59 @@ class FactoredExchange:
                                  tan_fovy, H, W, sh, degree, campos, geom, scratch, out_buffers=self.out_buffers(),
                                  write_sh=False)
         return self.finish(native, means3D, campos_views, degree, pending, sh_out=sh_out)
+
+
+    OUT_FIELDS = (("means3D", 3), ("opacity", 1), ("scales", 3), ("rotations", 4))
+
+    def _fresh_zeroed_outputs(self):
+        """The five summed-gradient tensors as views of ONE fresh allocation, zero-filled on a high-priority side stream so
+        that the 708 MB fill (P = 3M) runs under the compute-bound tile backward instead of on the critical path. Fresh,
+        because autograd keeps what backward returns as .grad without a copy only if nobody else holds it."""
+        P, M = self.P, self.M
+        widths = [w for _, w in self.OUT_FIELDS] + [3 * M]
+        starts, off = [], 0
+        for w in widths:
+            starts.append(off)
+            off = _round_up(off + P * w, 4)
+        flat = torch.empty(off, dtype=torch.float32, device=self.device)
+        main = torch.cuda.current_stream(self.device)
+        self._ev_zero_fork.record(main)
+        self._zero_stream.wait_event(self._ev_zero_fork)
+        with torch.cuda.stream(self._zero_stream):
+            flat.zero_()
+            self._ev_zero.record(self._zero_stream)
+        outs = {name: flat[o: o + P * w].view(P, w) for (name, w), o in zip(self.OUT_FIELDS, starts)}
+        outs["sh"] = flat[starts[-1]: starts[-1] + P * 3 * M].view(P, M, 3)
+        return outs
+
+    def _backward_records(self, native, bg, means3D, radii, scales, rotations, scale_modifier, viewmatrix, projmatrix, tan_fovx,
+                          tan_fovy, dL_dout_color, sh, degree, campos, campos_views, geom, R, binning, img, H, W):
+        outs = self._fresh_zeroed_outputs()
+        scratch = native.backward_render(bg, self.P, R, dL_dout_color, geom, binning, img)
+        buf = self._step % self._nbuf
+        self._step += 1
+        gathered = self._gathered_all[buf]
+        base = buf * self.world * self.slot_stride
+        symm = self.world > 1 and self.transport == "symm"
+        if symm:
+            dst, off, mc = self._gather_ptrs, base + self.rank * self.slot_stride, self._multicast
+        elif self.world > 1:
+            dst, off, mc = [self._send.data_ptr()], 0, False
+        else:
+            dst, off, mc = [gathered.data_ptr()], 0, False
+        # the per-Gaussian backward stores its chunk records straight into every rank's gather buffer
+        self.local = {"means2D": native.backward_geometry_push(means3D, radii, scales, rotations, scale_modifier, viewmatrix,
+                                                               projmatrix, tan_fovx, tan_fovy, H, W, sh, degree, campos, geom,
+                                                               scratch, dst, off, mc)}
+        if symm:
+            # every rank's records have landed. The one barrier of the step: rank r overwrites this buffer again two steps from
+            # now, after the barrier of the next step, which no rank enters before its combine below is done.
+            self._hdl.barrier(channel=0)
+        elif self.world > 1:
+            dist.all_gather_into_tensor(gathered.view(-1), self._send, group=self.group)
+        torch.cuda.current_stream(self.device).wait_event(self._ev_zero)
+        return native.dp_grad_record_combine(means3D, campos_views, gathered, self.slot_stride, degree, self.M, outs=outs,
+                                             outputs_are_zero=True)
 
 
 # ----------------------------------------------------------------------------------------------------------------------
@@ -375,6 +466,12 @@ class _RasterizeGaussiansViewParallel(torch.autograd.Function):
         from . import _native as C
         s, ex = ctx.raster_settings, ctx.exchange
         means3D, scales, rotations, radii, sh, campos_views, geom, binning, img = ctx.saved_tensors
+        if ex.layout == "records":
+            # fresh tensors already: autograd keeps them as .grad without a copy
+            g = ex.backward(C, s.bg, means3D, radii, scales, rotations, s.scale_modifier, s.viewmatrix, s.projmatrix,
+                            s.tanfovx, s.tanfovy, grad_out_color, sh, s.sh_degree, s.campos, campos_views, geom,
+                            ctx.num_rendered, binning, img)
+            return (g["means3D"], ex.local["means2D"], g["sh"], g["opacity"], g["scales"], g["rotations"], None, None, None)
         g = ex.backward(C, s.bg, means3D, radii, scales, rotations, s.scale_modifier, s.viewmatrix, s.projmatrix,
                         s.tanfovx, s.tanfovy, grad_out_color, sh, s.sh_degree, s.campos, campos_views, geom,
                         ctx.num_rendered, binning, img, sh_out=torch.empty_like(sh))

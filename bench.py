@@ -407,7 +407,9 @@ def run_b200_arm(args):
     }
     if factored:
         # NVLink / HBM bytes of the exchange kernels per rank and step
-        alg_bytes["dp_color_grad_push"] = P * (21 + 12) + (n_gpus - 1) * P * 12   # read acc+clamp+radii, write own slot, receive the others
+        # read acc+clamp+radii, write own slot, receive the others: the DENSE figure (12 B per Gaussian and view); the sparse
+        # layout moves 12 B per non-zero gradient + 0.25 B per Gaussian (parity.nonzero_color_grad_fraction_rank0)
+        alg_bytes["dp_color_grad_push"] = P * (21 + 12) + (n_gpus - 1) * P * 12
         alg_bytes["dp_slab_all_reduce"] = 2 * P * 44                               # slab read + written once per rank (two-shot)
         alg_bytes["dp_sh_grad_combine"] = P * (12 + 12 * n_gpus + 192)              # means + V colour triples in, 48 floats out
     stage_report = {}
@@ -895,10 +897,14 @@ def exchange_parity_leg(torch, dist, C, dp, dev, s, c, campos_views, bg, dL, exc
         ident = ident and all(bool((x == hs[0]).all()) for x in hs)
     worst = torch.tensor([max(rel.values())], dtype=torch.float64, device=dev)
     dist.all_reduce(worst, op=dist.ReduceOp.MAX)
+    # what the sparse layout saves: Gaussians of this rank's view whose colour gradient is exactly zero (culled, or never blended)
+    nonzero = float((arena.local["colors"] != 0).any(1).float().mean().item())
+    visible = float((radii > 0).float().mean().item())
     del arena
     torch.cuda.empty_cache()
     return {"rel_l2_vs_arena_nccl_all_reduce": rel, "max_rel_l2_over_ranks": float(worst.item()), "identical_on_all_ranks": ident,
             "multicast": bool(getattr(exchange, "_multicast", False)), "transport": exchange.transport, "tolerance": 1e-5,
+            "layout": exchange.layout, "visible_fraction_rank0": round(visible, 4), "nonzero_color_grad_fraction_rank0": round(nonzero, 4),
             "ok": bool(float(worst.item()) <= 1e-5 and ident),
             "what": "same views, same dL/dpix: factored exchange (timed above) vs GradientArena + one NCCL all_reduce of 59 floats/Gaussian"}
 

@@ -130,14 +130,49 @@ int gs_backward_geometry(void* stream, int P, int D, int M, int W, int H,
  * gs_dp_slab_all_reduce: in-place sum of a float slab that every rank holds at the same symmetric address.
  *   slab_ptrs[world] are the peer-mapped pointers in rank order (or one multicast pointer with multicast != 0);
  *   this rank reduces slice `rank` of `world` and stores it to every rank. n_floats must be a multiple of 4.
- *   The caller brackets the call with cross-rank barriers (all slabs written before; all slices landed after). */
+ *   The caller brackets the call with cross-rank barriers (all slabs written before; all slices landed after).
+ *
+ * layout (both calls must use the same one; gs_dp_slot_floats(P, layout) = floats one view's slot needs):
+ *   GS_DP_DENSE   [P][3] floats, zeros included.
+ *   GS_DP_SPARSE  per chunk of 256 Gaussians a 784-float record: 8 x (u32 mask, u32 set bits before this word) followed by
+ *                 the chunk's non-zero triples packed in index order. Only the header and the non-zero triples are
+ *                 stored (a Gaussian that was culled or never blended has an exactly zero gradient), from a bounded
+ *                 number of CTAs. Results are bit-identical to GS_DP_DENSE. slot_offset / slot_stride multiples of 4. */
+#define GS_DP_DENSE 0
+#define GS_DP_SPARSE 1
+#define GS_DP_RECORDS 2 /* gs_backward_geometry_push / gs_dp_grad_record_combine below */
+size_t gs_dp_slot_floats(int P, int layout);
 int gs_dp_color_grad_push(void* stream, int P, const int* radii, const void* geom_ws, const void* scratch,
-                          float* const* dst_ptrs, int n_dst, int multicast, size_t slot_offset);
+                          float* const* dst_ptrs, int n_dst, int multicast, size_t slot_offset, int layout);
 int gs_dp_sh_grad_combine(void* stream, int P, int D, int M, int V, const float* means3D,
-                          const float* campos_views, const float* color_grads, size_t slot_stride,
+                          const float* campos_views, const float* color_grads, size_t slot_stride, int layout,
                           float* dL_dsh);
 int gs_dp_slab_all_reduce(void* stream, float* const* slab_ptrs, int n_ptrs, int multicast, size_t n_floats,
                           int rank, int world);
+
+/* "Records" exchange (the default over symmetric memory): no all-reduce at all. Where a view's colour gradient is zero
+ * (culled, or never blended) so are its gradients w.r.t. the mean, opacity, scale and rotation, so only the Gaussians with
+ * a gradient travel, whole:
+ * gs_backward_geometry_push: gs_backward_geometry for the shs + scales/rotations path, but instead of the dense parameter
+ *   gradients every 128-Gaussian chunk leaves as a record of 1800 floats at float offset slot_offset + chunk * 1800 of every
+ *   buffer in dst_ptrs[n_dst] (or through one multicast pointer): 4 x (u32 mask, u32 set bits before this word), then per
+ *   set bit 14 floats {masked dL_dRGB 3, dL_dmean3D 3, dL_dopacity 1, dL_dscale 3, dL_drotation 4} in index order. Only the
+ *   header and the packed records are stored. dL_dmeans2D [P][3] (this view's own) is still written densely.
+ * gs_dp_grad_record_combine: from V such slots (records + v * slot_stride, slot_stride >= gs_dp_slot_floats(P,
+ *   GS_DP_RECORDS)) the gradients summed over the views in view order - bit-identical on every rank, and equal to adding the
+ *   per-view outputs of gs_backward in that order: dL_dmeans3D [P][3], dL_dopacity [P], dL_dscales [P][3],
+ *   dL_drotations [P][4], dL_dsh [P][M][3] (basis(dir_v) (x) dL_dRGB_v). Only rows some view touched are written:
+ *   outputs_are_zero != 0 promises the outputs hold zeros already (zero them off the critical path), 0 makes the call clear
+ *   them first. V <= 32. */
+int gs_backward_geometry_push(void* stream, int P, int D, int M, int W, int H, const float* means3D, const float* shs,
+                              const float* scales, float scale_modifier, const float* rotations,
+                              const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,
+                              float tan_fovy, const int* radii, const void* geom_ws, const void* scratch,
+                              float* dL_dmeans2D, float* const* dst_ptrs, int n_dst, int multicast, size_t slot_offset);
+int gs_dp_grad_record_combine(void* stream, int P, int D, int M, int V, const float* means3D,
+                              const float* campos_views, const float* records, size_t slot_stride,
+                              int outputs_are_zero, float* dL_dmeans3D, float* dL_dopacity, float* dL_dscales,
+                              float* dL_drotations, float* dL_dsh);
 
 /* present[i] = (view * means3D[i]).z > 0.2 ; one byte per Gaussian (bool). */
 int gs_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix,

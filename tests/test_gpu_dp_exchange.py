@@ -79,20 +79,46 @@ def test_split_backward_equals_fused_backward(kind, P, W, H, rad, fovx):
             assert helpers.bits_equal_count(nosh[n], split[n]) == 0, n
 
 
+def _decode_sparse_slot(slot, P):
+    """[P, 3] colour gradients from one sparse slot (include/gs_b200.h GS_DP_SPARSE): per 256 Gaussians 8 x (mask, before)
+    words, then the non-zero triples in index order. Also checks the header's running counts."""
+    import numpy as np
+    raw = slot.cpu().numpy()
+    words = raw.view(np.uint32)
+    out = np.zeros((P, 3), np.float32)
+    for c in range((P + 255) // 256):
+        base = c * 784
+        seen = 0
+        for w in range(8):
+            mask, before = int(words[base + 2 * w]), int(words[base + 2 * w + 1])
+            assert before == seen
+            for lane in range(32):
+                if (mask >> lane) & 1:
+                    i = c * 256 + 32 * w + lane
+                    assert i < P
+                    out[i] = raw[base + 16 + 3 * seen: base + 19 + 3 * seen]
+                    assert out[i].any()
+                    seen += 1
+    return torch.from_numpy(out).to(slot.device)
+
+
 @pytest.mark.parametrize("kind,P,W,H,V,degree,rad,fovx", [
     ("cube", 20001, 250, 130, 3, 3, 4.03, 0.6911),      # P not a multiple of 4: scalar tail of the push kernel
     ("cube", 5000, 96, 64, 2, 1, 4.03, 0.6911),         # lower degree, M = 4 rows
     ("cube", 5000, 96, 64, 2, 0, 4.03, 0.6911),
     ("garden", 200000, 800, 450, 4, 3, 6.0, 1.2),
 ])
-def test_factored_sh_gradient_equals_sum_of_per_view_gradients(kind, P, W, H, V, degree, rad, fovx):
+@pytest.mark.parametrize("layout", ["dense", "sparse"])
+def test_factored_sh_gradient_equals_sum_of_per_view_gradients(kind, P, W, H, V, degree, rad, fovx, layout):
     """Masked dL/dRGB per view + gs_dp_sh_grad_combine == sum over views (in order) of the per-view dL_dsh that the
-    same scratch gives through the ordinary backward, bit for bit."""
+    same scratch gives through the ordinary backward, bit for bit - in the dense [P][3] layout and in the sparse one
+    (bit masks + non-zero triples only), whose slot is decoded here to check what travels."""
     C = native()
     dev = torch.device("cuda:0")
     s, cs, dLs = _views(kind, P, W, H, V, degree, rad, fovx)
     M = s["shs"].shape[1]
-    slot_stride = (3 * P + 63) // 64 * 64
+    slot_stride = (C.dp_slot_floats(P, layout) + 63) // 64 * 64
+    assert slot_stride >= 3 * P
     gathered = torch.full((V, slot_stride), float("nan"), device=dev)
     e = torch.empty(0)
     total = torch.zeros((P, M, 3), device=dev)
@@ -100,25 +126,103 @@ def test_factored_sh_gradient_equals_sum_of_per_view_gradients(kind, P, W, H, V,
     for v, (c, dL) in enumerate(zip(cs, dLs)):
         R, _, radii, geom, binning, img, _ = _forward(C, s, c, degree)
         scratch = C.backward_render(c["bg"], P, R, dL, geom, binning, img)
-        C.dp_color_grad_push(P, radii, geom, scratch, [gathered.data_ptr()], v * slot_stride, False)
+        C.dp_color_grad_push(P, radii, geom, scratch, [gathered.data_ptr()], v * slot_stride, False, layout=layout)
         outs = dict(zip(NAMES, C.backward_geometry(s["means3D"], radii, s["scales"], s["rotations"], 1.0, e,
                                                    c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W,
                                                    s["shs"], degree, c["campos"], geom, scratch)))
         total = total + outs["sh"]
         # the pushed colour gradient is the backward's dL_dcolors with the clamp mask applied
-        g = gathered[v, : 3 * P].view(P, 3)
+        g = gathered[v, : 3 * P].view(P, 3) if layout == "dense" else _decode_sparse_slot(gathered[v], P)
         assert torch.isfinite(g).all()
         changed = g != outs["colors"]
         assert bool(((g == 0) | ~changed).all())
-    sh = C.dp_sh_grad_combine(s["means3D"], campos, gathered, slot_stride, degree, M)
+        assert bool(((g != 0).any(1) | (outs["sh"].abs().amax((1, 2)) == 0)).all())   # nothing non-zero was dropped
+    sh = C.dp_sh_grad_combine(s["means3D"], campos, gathered, slot_stride, degree, M, layout=layout)
     torch.cuda.synchronize()
     assert sh.shape == total.shape
     assert float(total.abs().max()) > 0
     assert helpers.bits_equal_count(sh + 0.0, total + 0.0) == 0, helpers.rel_l2(sh, total)
 
 
-def test_factored_exchange_world_1_equals_fused_backward():
-    """dp.FactoredExchange without a process group: same gradients as the fused backward."""
+def _decode_records(slot, P):
+    """{index: 14 floats} from one slot in the records layout (include/gs_b200.h GS_DP_RECORDS); checks the running counts."""
+    import numpy as np
+    raw = slot.cpu().numpy()
+    words = raw.view(np.uint32)
+    out = {}
+    for c in range((P + 127) // 128):
+        base = c * 1800
+        seen = 0
+        for w in range(4):
+            mask, before = int(words[base + 2 * w]), int(words[base + 2 * w + 1])
+            assert before == seen
+            for lane in range(32):
+                if (mask >> lane) & 1:
+                    i = c * 128 + 32 * w + lane
+                    assert i < P
+                    out[i] = raw[base + 8 + 14 * seen: base + 22 + 14 * seen].copy()
+                    seen += 1
+    return out
+
+
+@pytest.mark.parametrize("kind,P,W,H,V,degree,rad,fovx", [
+    ("cube", 20001, 250, 130, 3, 3, 4.03, 0.6911),      # ragged P: a partial last chunk
+    ("cube", 5000, 96, 64, 2, 1, 4.03, 0.6911),
+    ("cube", 5000, 96, 64, 2, 0, 4.03, 0.6911),
+    ("cube", 5000, 96, 64, 5, 2, 4.03, 0.6911),         # V not a multiple of the view batch, 27-float rows
+    ("garden", 200000, 800, 450, 4, 3, 6.0, 1.2),
+])
+def test_gradient_records_equal_sum_of_per_view_gradients(kind, P, W, H, V, degree, rad, fovx):
+    """The records exchange on one GPU: every view's per-Gaussian backward pushes its chunk records into its slot
+    (gs_backward_geometry_push), gs_dp_grad_record_combine adds the views in order. All five parameter gradients must equal
+    the sum, in view order, of what the ordinary backward gives per view - bit for bit - and a record must exist exactly for
+    the Gaussians whose gradient is not all zero."""
+    C = native()
+    dev = torch.device("cuda:0")
+    s, cs, dLs = _views(kind, P, W, H, V, degree, rad, fovx)
+    M = s["shs"].shape[1]
+    stride = (C.dp_slot_floats(P, "records") + 63) // 64 * 64
+    gathered = torch.full((V, stride), float("nan"), device=dev)
+    e = torch.empty(0)
+    keys = ("means3D", "opacity", "scales", "rotations", "sh")
+    total = None
+    campos = torch.stack([c["campos"] for c in cs])
+    for v, (c, dL) in enumerate(zip(cs, dLs)):
+        R, _, radii, geom, binning, img, _ = _forward(C, s, c, degree)
+        scratch = C.backward_render(c["bg"], P, R, dL, geom, binning, img)
+        m2d = C.backward_geometry_push(s["means3D"], radii, s["scales"], s["rotations"], 1.0, c["viewmatrix"], c["projmatrix"],
+                                       c["tanfovx"], c["tanfovy"], H, W, s["shs"], degree, c["campos"], geom, scratch,
+                                       [gathered.data_ptr()], v * stride, False)
+        outs = dict(zip(NAMES, C.backward_geometry(s["means3D"], radii, s["scales"], s["rotations"], 1.0, e,
+                                                   c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W,
+                                                   s["shs"], degree, c["campos"], geom, scratch)))
+        assert helpers.bits_equal_count(m2d + 0.0, outs["means2D"] + 0.0) == 0
+        total = {k: outs[k].clone() for k in keys} if total is None else {k: total[k] + outs[k] for k in keys}
+        if P <= 20001:
+            recs = _decode_records(gathered[v], P)
+            nonzero = torch.zeros(P, dtype=torch.bool, device=dev)
+            for k in keys:
+                nonzero |= (outs[k].reshape(P, -1) != 0).any(1)
+            assert sorted(recs) == nonzero.nonzero().flatten().tolist()
+            i = next(iter(recs))
+            import numpy as np
+            want = np.concatenate([outs[k][i].cpu().numpy().reshape(-1) for k in ("means3D", "opacity", "scales", "rotations")])
+            assert np.array_equal(recs[i][3:], want)
+    got = C.dp_grad_record_combine(s["means3D"], campos, gathered, stride, degree, M)
+    # ... and into outputs the caller zeroed itself
+    pre = {k: torch.zeros_like(v) for k, v in got.items()}
+    C.dp_grad_record_combine(s["means3D"], campos, gathered, stride, degree, M, outs=pre, outputs_are_zero=True)
+    torch.cuda.synchronize()
+    assert float(total["sh"].abs().max()) > 0 and float(total["rotations"].abs().max()) > 0
+    for k in keys:
+        assert got[k].shape == total[k].shape
+        assert helpers.bits_equal_count(got[k] + 0.0, total[k] + 0.0) == 0, (k, helpers.rel_l2(got[k], total[k]))
+        assert helpers.bits_equal_count(pre[k] + 0.0, total[k] + 0.0) == 0, k
+
+
+@pytest.mark.parametrize("layout", ["records", "sparse", "dense"])
+def test_factored_exchange_world_1_equals_fused_backward(layout):
+    """dp.FactoredExchange without a process group: same gradients as the fused backward, in every layout."""
     from diff_gaussian_rasterization import dp
     C = native()
     P, W, H = 30000, 320, 200
@@ -127,18 +231,22 @@ def test_factored_exchange_world_1_equals_fused_backward():
     fwd = _forward(C, s, c, 3)
     R, _, radii, geom, binning, img, _ = fwd
     fused = _fused_backward(C, s, c, 3, dL, fwd)
-    ex = dp.FactoredExchange(P, 16, torch.device("cuda:0"))
-    assert ex.world == 1
-    grads = ex.backward(C, c["bg"], s["means3D"], radii, s["scales"], s["rotations"], 1.0, c["viewmatrix"],
-                        c["projmatrix"], c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"],
-                        c["campos"].view(1, 3), geom, R, binning, img)
+    ex = dp.FactoredExchange(P, 16, torch.device("cuda:0"), layout=layout)
+    assert ex.world == 1 and ex.layout == layout
+    assert dp.FactoredExchange(P, 16, torch.device("cuda:0")).layout == "records"     # the default
+    for _ in range(3):                                   # the buffers are reused step after step
+        grads = ex.backward(C, c["bg"], s["means3D"], radii, s["scales"], s["rotations"], 1.0, c["viewmatrix"],
+                            c["projmatrix"], c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"],
+                            c["campos"].view(1, 3), geom, R, binning, img)
     torch.cuda.synchronize()
     for n in ("means3D", "sh", "opacity", "scales", "rotations"):
-        assert helpers.rel_l2(grads[n], fused[n]) < 2e-5, n
+        assert helpers.rel_l2(grads[n].reshape(fused[n].shape), fused[n]) < 2e-5, n    # two runs of the tile backward: atomics
+    assert helpers.rel_l2(ex.local["means2D"], fused["means2D"]) < 2e-5
 
 
+@pytest.mark.parametrize("layout", ["records", "sparse"])
 @pytest.mark.parametrize("P", [30001, 30002, 30003])
-def test_ragged_gaussian_counts_through_arena_and_exchange(P):
+def test_ragged_gaussian_counts_through_arena_and_exchange(P, layout):
     """MCMC growth makes P arbitrary (int(1.05 * P)). Every field block of GradientArena and of the exchange slab must stay
     16-byte aligned for any P (the kernels' float4 paths), through resize() as well: same gradients as plain outputs."""
     from diff_gaussian_rasterization import dp
@@ -163,7 +271,7 @@ def test_ragged_gaussian_counts_through_arena_and_exchange(P):
     for n in NAMES:
         assert helpers.bits_equal_count(got[n] + 0.0, plain[n] + 0.0) == 0, n
     # the exchange, allocated for a larger cap and resized down to the ragged P (and up again)
-    ex = dp.FactoredExchange(P - 7, 16, torch.device("cuda:0"), capacity=P + 1000)
+    ex = dp.FactoredExchange(P - 7, 16, torch.device("cuda:0"), capacity=P + 1000, layout=layout)
     ex.resize(P + 999).resize(P)
     for v in ex.grads.values():
         assert v.data_ptr() % 16 == 0 and v.shape[0] == P
@@ -185,6 +293,13 @@ def test_dp_entry_points_reject_bad_arguments():
         C.dp_slab_all_reduce(dev, [x.data_ptr(), x.data_ptr()], 6, 0, 2)   # not a multiple of 4 floats
     with pytest.raises(RuntimeError):
         C.dp_sh_grad_combine(torch.zeros((8, 3), device=dev), torch.zeros((1, 3), device=dev), x, 8, 3, 16)  # stride < 3P
+    with pytest.raises(RuntimeError):
+        C.dp_sh_grad_combine(torch.zeros((8, 3), device=dev), torch.zeros((1, 3), device=dev), x, 32, 3, 16, layout="sparse")  # < one chunk
+    with pytest.raises(RuntimeError):                                  # a records slot is 1800 floats per 128 Gaussians
+        C.dp_grad_record_combine(torch.zeros((8, 3), device=dev), torch.zeros((1, 3), device=dev), torch.zeros(1024, device=dev), 1024, 3, 16)
+    with pytest.raises(RuntimeError):                                  # more views than the header staging holds
+        C.dp_grad_record_combine(torch.zeros((8, 3), device=dev), torch.zeros((33, 3), device=dev), torch.zeros(33 * 1856, device=dev), 1856, 3, 16)
+    assert C.dp_slot_floats(129, "records") == 3600 and C.dp_slot_floats(257, "sparse") == 1568 and C.dp_slot_floats(5, "dense") == 16
 
 
 def test_slab_all_reduce_single_device_two_buffers():

@@ -165,11 +165,11 @@ def test_factored_exchange_world_size_2_gloo(tmp_path):
             return np.stack([np.full(len(d), c0, np.float32), -c1 * d[:, 1], c1 * d[:, 2], -c1 * d[:, 0]], 1).astype(np.float32)
 
         class FakeNative:                              # stands in for _native on a box without a GPU (test only)
-            def dp_color_grad_push(self, P_, radii, geom, scratch, dst_ptrs, slot_offset, multicast):
+            def dp_color_grad_push(self, P_, radii, geom, scratch, dst_ptrs, slot_offset, multicast, layout=None):
                 src = np.ascontiguousarray(g_all[r].reshape(-1))
                 for p in dst_ptrs:
                     ctypes.memmove(p + 4 * slot_offset, src.ctypes.data, src.nbytes)
-            def dp_sh_grad_combine(self, means3D, campos_views, gathered, slot_stride, degree, M_, out=None):
+            def dp_sh_grad_combine(self, means3D, campos_views, gathered, slot_stride, degree, M_, out=None, layout=None):
                 acc = np.zeros((P, M_, 3), np.float32)
                 for v in range(campos_views.shape[0]):
                     g = gathered.view(-1).numpy()[v * slot_stride: v * slot_stride + 3 * P].reshape(P, 3)

@@ -204,7 +204,8 @@ def main():
     ap.add_argument("--width", type=int, default=1297)
     ap.add_argument("--height", type=int, default=840)
     ap.add_argument("--iters", type=int, default=10)
-    ap.add_argument("--transports", default="nccl,symm,symm-p2p")
+    ap.add_argument("--transports", default="nccl,symm:dense,symm:sparse,symm:records,symm-p2p:records",
+                    help="comma list of transport[-p2p][:layout]; -p2p = peer pointers instead of the multicast mapping")
     ap.add_argument("--breakdown", action="store_true")
     ap.add_argument("--train-steps", type=int, default=0,
                     help="also run this many full training iterations (activations, render, loss, exchange, Adam, noise) and "
@@ -273,8 +274,9 @@ def main():
 
     for transport in ([] if args.skip_exchange else args.transports.split(",")):
         try:
-            ex = dp.FactoredExchange(P, 16, dev, transport=transport.split("-")[0],
-                                     multicast=False if transport.endswith("-p2p") else None)
+            tname, _, layout = transport.partition(":")
+            ex = dp.FactoredExchange(P, 16, dev, transport=tname.split("-")[0],
+                                     multicast=False if tname.endswith("-p2p") else None, layout=layout or None)
 
             def step():
                 return ex.backward(C, bg, s["means3D"], radii, s["scales"], s["rotations"], 1.0, c["viewmatrix"],
@@ -294,8 +296,31 @@ def main():
                 ident = ident and all(bool((x == hs[0]).all()) for x in hs)
             out[f"factored_{transport}"] = {"rel_l2_vs_full_all_reduce": diffs, "identical_on_all_ranks": ident,
                                             "multicast": bool(getattr(ex, "_multicast", False)),
-                                            "transport": ex.transport}
-            if args.breakdown:
+                                            "transport": ex.transport, "layout": ex.layout}
+            if args.breakdown and ex.layout == "records":
+                scratch = C.backward_render(bg, P, R, dL, geom, binning, img)
+                bd = {"layout": "records"}
+                bd["backward_render"] = timed(lambda: C.backward_render(bg, P, R, dL, geom, binning, img))
+                own = ex._gathered_all[0]
+                dst, mc = (ex._gather_ptrs, ex._multicast) if ex.transport == "symm" else ([own.data_ptr()], False)
+
+                def push_only():
+                    C.backward_geometry_push(s["means3D"], radii, s["scales"], s["rotations"], 1.0, c["viewmatrix"], c["projmatrix"],
+                                             c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3, c["campos"], geom, scratch, dst,
+                                             rank * ex.slot_stride if ex.transport == "symm" else 0, mc)
+                    if ex.transport == "symm":
+                        ex._hdl.barrier(channel=0)
+                bd["geometry_push+barrier"] = timed(push_only)
+                bd["geometry_with_sh_dense_outputs"] = timed(lambda: C.backward_geometry(
+                    s["means3D"], radii, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"], c["tanfovx"],
+                    c["tanfovy"], H, W, s["shs"], 3, c["campos"], geom, scratch, out_buffers=arena.backward_buffers()))
+                outs = ex._fresh_zeroed_outputs()
+                torch.cuda.current_stream().wait_event(ex._ev_zero)
+                bd["combine_prezeroed"] = timed(lambda: C.dp_grad_record_combine(s["means3D"], campos_views, own, ex.slot_stride, 3, 16,
+                                                                                 outs=outs, outputs_are_zero=True))
+                bd["zero_fill_708MB_at_3M"] = timed(lambda: outs["sh"].zero_())
+                out[f"breakdown_{transport}"] = bd
+            elif args.breakdown:
                 scratch = C.backward_render(bg, P, R, dL, geom, binning, img)
                 bd = {}
                 bd["backward_render"] = timed(lambda: C.backward_render(bg, P, R, dL, geom, binning, img))
@@ -307,7 +332,8 @@ def main():
                     s["means3D"], radii, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"], c["tanfovx"],
                     c["tanfovy"], H, W, s["shs"], 3, c["campos"], geom, scratch, out_buffers=arena.backward_buffers()))
                 bd["combine"] = timed(lambda: C.dp_sh_grad_combine(s["means3D"], campos_views, ex.gathered, ex.slot_stride, 3, 16,
-                                                                   out=ex.grads["sh"]))
+                                                                   out=ex.grads["sh"], layout=ex.layout))
+                bd["layout"] = ex.layout
                 if ex.transport == "symm":
                     bd["slab_all_reduce_alone"] = timed(lambda: C.dp_slab_all_reduce(dev, ex._slab_ptrs, ex._n_slab, rank, world, ex._multicast))
                     bd["barrier"] = timed(lambda: ex._hdl.barrier(channel=0))
