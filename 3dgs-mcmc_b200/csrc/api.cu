@@ -66,7 +66,7 @@ unsigned long long* g_fwd_counters = nullptr;   // set by gs_debug_forward_work 
 
 extern "C" {
 
-int gs_abi_version(void) { return 106; }
+int gs_abi_version(void) { return 107; }
 
 const char* gs_error_string(int code) {
     if (code == GS_OK) return "ok";
@@ -119,14 +119,20 @@ static inline char* aligned_base(const void* p) {
     return reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(p), kAlign));
 }
 
-int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means3D, const float* shs,
-                          const float* colors_precomp, const float* opacities, const float* scales,
-                          float scale_modifier, const float* rotations, const float* cov3D_precomp,
-                          const float* viewmatrix, const float* projmatrix, const float* campos, int W, int H,
-                          float tan_fovx, float tan_fovy, int prefiltered, int* radii, int* is_used, void* geom_ws,
-                          unsigned int* num_rendered_host, void* count_ready_event) {
+// split SH layout (features_dc [P][1][3] + features_rest [P][15][3]): both 16-byte aligned, M = 16
+static bool split_sh_ok(const float* dc, const float* rest, int M) {
+    return dc && rest && M == 16 && is_aligned16(dc) && is_aligned16(rest);
+}
+
+static int forward_preprocess_impl(void* stream_, int P, int D, int M, const float* means3D, const float* shs, const float* shs_rest,
+                                   const float* colors_precomp, const float* opacities, const float* scales,
+                                   float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                                   const float* viewmatrix, const float* projmatrix, const float* campos, int W, int H,
+                                   float tan_fovx, float tan_fovy, int prefiltered, int* radii, int* is_used, void* geom_ws,
+                                   unsigned int* num_rendered_host, void* count_ready_event) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (P < 0 || W <= 0 || H <= 0 || D < 0 || D > 3) return GS_ERR_ARG;
+    if (P > 0 && shs_rest && (colors_precomp || !split_sh_ok(shs, shs_rest, M))) return GS_ERR_ARG;
     if (P > 0 && (!means3D || !opacities || !viewmatrix || !projmatrix || !radii || !is_used || !geom_ws)) return GS_ERR_ARG;
     if (P > 0 && !colors_precomp && (!shs || !campos || M < (D + 1) * (D + 1))) return GS_ERR_ARG;
     if (P > 0 && !cov3D_precomp && (!scales || !rotations)) return GS_ERR_ARG;
@@ -140,7 +146,7 @@ int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means
     PreprocessParams pp;
     pp.P = P; pp.D = D; pp.M = M;
     pp.means3D = means3D; pp.scales = scales; pp.scale_modifier = scale_modifier; pp.rotations = rotations;
-    pp.opacities = opacities; pp.shs = shs; pp.cov3D_precomp = cov3D_precomp; pp.colors_precomp = colors_precomp;
+    pp.opacities = opacities; pp.shs = shs; pp.shs_rest = shs_rest; pp.cov3D_precomp = cov3D_precomp; pp.colors_precomp = colors_precomp;
     pp.viewmatrix = viewmatrix; pp.projmatrix = projmatrix; pp.campos = campos;
     pp.W = W; pp.H = H; pp.tan_fovx = tan_fovx; pp.tan_fovy = tan_fovy;
     pp.focal_y = H / (2.0f * tan_fovy);
@@ -169,6 +175,29 @@ int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means
     prof_mark(stream, ST_SCAN);
     count_launches(1 + 3 * kDepthSortPasses + 3);
     return GS_OK;
+}
+
+int gs_forward_preprocess(void* stream_, int P, int D, int M, const float* means3D, const float* shs,
+                          const float* colors_precomp, const float* opacities, const float* scales,
+                          float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                          const float* viewmatrix, const float* projmatrix, const float* campos, int W, int H,
+                          float tan_fovx, float tan_fovy, int prefiltered, int* radii, int* is_used, void* geom_ws,
+                          unsigned int* num_rendered_host, void* count_ready_event) {
+    return forward_preprocess_impl(stream_, P, D, M, means3D, shs, nullptr, colors_precomp, opacities, scales, scale_modifier,
+                                   rotations, cov3D_precomp, viewmatrix, projmatrix, campos, W, H, tan_fovx, tan_fovy, prefiltered,
+                                   radii, is_used, geom_ws, num_rendered_host, count_ready_event);
+}
+
+int gs_forward_preprocess_split_sh(void* stream_, int P, int D, const float* means3D, const float* features_dc,
+                                   const float* features_rest, const float* opacities, const float* scales,
+                                   float scale_modifier, const float* rotations, const float* viewmatrix,
+                                   const float* projmatrix, const float* campos, int W, int H, float tan_fovx, float tan_fovy,
+                                   int prefiltered, int* radii, int* is_used, void* geom_ws, unsigned int* num_rendered_host,
+                                   void* count_ready_event) {
+    if (P > 0 && (!features_dc || !features_rest)) return GS_ERR_ARG;
+    return forward_preprocess_impl(stream_, P, D, 16, means3D, features_dc, features_rest, nullptr, opacities, scales,
+                                   scale_modifier, rotations, nullptr, viewmatrix, projmatrix, campos, W, H, tan_fovx, tan_fovy,
+                                   prefiltered, radii, is_used, geom_ws, num_rendered_host, count_ready_event);
 }
 
 int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const float* background,
@@ -230,6 +259,18 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
 
 int gs_backward_render(void* stream_, int P, unsigned int R, int W, int H, const float* background, const void* geom_ws,
                        const void* binning_ws, const void* image_ws, const float* dL_dpix, void* scratch) {
+    return gs_backward_render_ev(stream_, P, R, W, H, background, geom_ws, binning_ws, image_ws, dL_dpix, scratch, nullptr);
+}
+
+int gs_stream_wait_event(void* stream_, void* event) {
+    if (!event) return GS_ERR_ARG;
+    GS_CUDA_TRY(cudaStreamWaitEvent((cudaStream_t)stream_, (cudaEvent_t)event, 0));
+    return GS_OK;
+}
+
+int gs_backward_render_ev(void* stream_, int P, unsigned int R, int W, int H, const float* background, const void* geom_ws,
+                          const void* binning_ws, const void* image_ws, const float* dL_dpix, void* scratch,
+                          void* cleared_event) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (P < 0 || W <= 0 || H <= 0) return GS_ERR_ARG;
     if (P == 0) return GS_OK;
@@ -243,6 +284,7 @@ int gs_backward_render(void* stream_, int P, unsigned int R, int W, int H, const
     prof_mark(stream, -1);
     GS_CUDA_TRY(cudaMemsetAsync(sc.acc_color_opacity, 0, sc.bytes, stream));
     prof_mark(stream, ST_BWD_ZERO);
+    if (cleared_event) GS_CUDA_TRY(cudaEventRecord((cudaEvent_t)cleared_event, stream));
     if (R > 0) {
         RenderBwdParams rb;
         rb.ranges = img.ranges; rb.ids = b.ids; rb.rec = g.rec; rb.tile_max_contrib = img.tile_max_contrib;
@@ -280,7 +322,7 @@ static int fill_peers(DpPeers* peers, float* const* ptrs, int n);
 
 // push: null = the dense outputs; else the "records" exchange (the five parameter gradients leave as chunk records)
 static int backward_geometry_impl(void* stream_, int P, int D, int M, int W, int H, const float* means3D, const float* shs,
-                                  const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                                  const float* shs_rest, float* dL_dsh_rest, const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
                                   const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,
                                   float tan_fovy, const int* radii, const void* geom_ws, const void* scratch, float* dL_dmeans2D,
                                   float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
@@ -294,11 +336,14 @@ static int backward_geometry_impl(void* stream_, int P, int D, int M, int W, int
     if (push && (!shs || !scales || !rotations || cov3D_precomp || (push_offset & 3))) return GS_ERR_ARG;
     if (shs && !campos) return GS_ERR_ARG;
     if (shs && !dL_dsh && 3 * M > 48) return GS_ERR_ARG;   // factored mode needs the staged SH rows (sh_stage.cuh: kShMaxRow)
+    if (shs_rest && (!split_sh_ok(shs, shs_rest, M) || (dL_dsh != nullptr) != (dL_dsh_rest != nullptr))) return GS_ERR_ARG;
+    if (shs_rest && dL_dsh && !split_sh_ok(dL_dsh, dL_dsh_rest, M)) return GS_ERR_ARG;
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
     BwdScratch sc = BwdScratch::carve(aligned_base(scratch), (size_t)P);
     prof_mark(stream, -1);
     PreprocessBwdParams pb;
     pb.P = P; pb.D = D; pb.M = M; pb.means3D = means3D; pb.radii = radii; pb.shs = shs; pb.clamped = g.clamped;
+    pb.shs_rest = shs_rest; pb.dL_dsh_rest = dL_dsh_rest;
     pb.scales = cov3D_precomp ? nullptr : scales; pb.rotations = rotations; pb.scale_modifier = scale_modifier;
     pb.rot_aligned = is_aligned16(rotations) ? 1 : 0;
     pb.drot_aligned = is_aligned16(dL_drotations) ? 1 : 0;
@@ -324,13 +369,27 @@ int gs_backward_geometry(void* stream_, int P, int D, int M, int W, int H, const
                          float tan_fovy, const int* radii, const void* geom_ws, const void* scratch, float* dL_dmeans2D,
                          float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
                          float* dL_dscales, float* dL_drotations) {
-    return backward_geometry_impl(stream_, P, D, M, W, H, means3D, shs, scales, scale_modifier, rotations, cov3D_precomp,
-                                  viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii, geom_ws, scratch, dL_dmeans2D,
-                                  dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, nullptr, 0, 0);
+    return backward_geometry_impl(stream_, P, D, M, W, H, means3D, shs, nullptr, nullptr, scales, scale_modifier, rotations,
+                                  cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii, geom_ws, scratch,
+                                  dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations,
+                                  nullptr, 0, 0);
+}
+
+int gs_backward_geometry_split_sh(void* stream_, int P, int D, int W, int H, const float* means3D, const float* features_dc,
+                                  const float* features_rest, const float* scales, float scale_modifier, const float* rotations,
+                                  const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,
+                                  float tan_fovy, const int* radii, const void* geom_ws, const void* scratch, float* dL_dmeans2D,
+                                  float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                                  float* dL_dfeatures_dc, float* dL_dfeatures_rest, float* dL_dscales, float* dL_drotations) {
+    if (P > 0 && (!features_dc || !features_rest || !dL_dfeatures_dc || !dL_dfeatures_rest)) return GS_ERR_ARG;
+    return backward_geometry_impl(stream_, P, D, 16, W, H, means3D, features_dc, features_rest, dL_dfeatures_rest, scales,
+                                  scale_modifier, rotations, nullptr, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii,
+                                  geom_ws, scratch, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dfeatures_dc,
+                                  dL_dscales, dL_drotations, nullptr, 0, 0);
 }
 
 int gs_backward_geometry_push(void* stream_, int P, int D, int M, int W, int H, const float* means3D, const float* shs,
-                              const float* scales, float scale_modifier, const float* rotations, const float* viewmatrix,
+                              const float* shs_rest, const float* scales, float scale_modifier, const float* rotations, const float* viewmatrix,
                               const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy, const int* radii,
                               const void* geom_ws, const void* scratch, float* dL_dmeans2D, float* const* dst_ptrs, int n_dst,
                               int multicast, size_t slot_offset) {
@@ -338,9 +397,9 @@ int gs_backward_geometry_push(void* stream_, int P, int D, int M, int W, int H, 
     const int rc = fill_peers(&peers, dst_ptrs, n_dst);
     if (rc) return rc;
     if (multicast && n_dst != 1) return GS_ERR_ARG;
-    return backward_geometry_impl(stream_, P, D, M, W, H, means3D, shs, scales, scale_modifier, rotations, nullptr, viewmatrix,
-                                  projmatrix, campos, tan_fovx, tan_fovy, radii, geom_ws, scratch, dL_dmeans2D, nullptr, nullptr,
-                                  nullptr, nullptr, nullptr, nullptr, nullptr, &peers, slot_offset, multicast);
+    return backward_geometry_impl(stream_, P, D, M, W, H, means3D, shs, shs_rest, nullptr, scales, scale_modifier, rotations, nullptr,
+                                  viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, radii, geom_ws, scratch, dL_dmeans2D, nullptr,
+                                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, &peers, slot_offset, multicast);
 }
 
 int gs_backward(void* stream_, int P, int D, int M, unsigned int R, int W, int H, const float* background,
@@ -383,7 +442,7 @@ size_t gs_dp_slot_floats(int P, int layout) {
 
 int gs_dp_grad_record_combine(void* stream_, int P, int D, int M, int V, const float* means3D, const float* campos_views,
                               const float* records, size_t slot_stride, int outputs_are_zero, float* dL_dmeans3D,
-                              float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dsh) {
+                              float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dsh, float* dL_dsh_rest) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (P < 0 || D < 0 || D > 3 || V < 1) return GS_ERR_ARG;
     if (P == 0) return GS_OK;
@@ -397,10 +456,11 @@ int gs_dp_grad_record_combine(void* stream_, int P, int D, int M, int V, const f
         GS_CUDA_TRY(cudaMemsetAsync(dL_dopacity, 0, (size_t)P * sizeof(float), stream));
         GS_CUDA_TRY(cudaMemsetAsync(dL_dscales, 0, (size_t)P * 3 * sizeof(float), stream));
         GS_CUDA_TRY(cudaMemsetAsync(dL_drotations, 0, (size_t)P * 4 * sizeof(float), stream));
-        GS_CUDA_TRY(cudaMemsetAsync(dL_dsh, 0, (size_t)P * M * 3 * sizeof(float), stream));
+        GS_CUDA_TRY(cudaMemsetAsync(dL_dsh, 0, (size_t)P * (dL_dsh_rest ? 1 : M) * 3 * sizeof(float), stream));
+        if (dL_dsh_rest) GS_CUDA_TRY(cudaMemsetAsync(dL_dsh_rest, 0, (size_t)P * (M - 1) * 3 * sizeof(float), stream));
     }
     const int rc = launch_grad_record_combine(P, D, M, V, means3D, campos_views, records, slot_stride, dL_dmeans3D, dL_dopacity,
-                                              dL_dscales, dL_drotations, dL_dsh, stream);
+                                              dL_dscales, dL_drotations, dL_dsh, dL_dsh_rest, stream);
     prof_mark(stream, ST_DP_COMBINE);
     count_launches(outputs_are_zero ? 1 : 6);
     return rc;

@@ -382,7 +382,8 @@ __global__ void __launch_bounds__(32 * kRcWarps) grad_record_combine_kernel(int 
                                                                            const float* __restrict__ gathered,   // [V][slot_stride]
                                                                            size_t slot_stride, float* __restrict__ dL_dmeans3D,
                                                                            float* __restrict__ dL_dopacity, float* __restrict__ dL_dscales,
-                                                                           float* __restrict__ dL_drots, float* __restrict__ dL_dsh) {
+                                                                           float* __restrict__ dL_drots, float* __restrict__ dL_dsh,
+                                                                           float* __restrict__ dL_dsh_rest) {
     constexpr int kCoef = (kDeg + 1) * (kDeg + 1);
     constexpr int kWords = kRecChunk / 32;
     __shared__ uint2 s_hdr[kRcWarps][kRcMaxViews][kWords];
@@ -479,6 +480,15 @@ __global__ void __launch_bounds__(32 * kRcWarps) grad_record_combine_kernel(int 
         dL_dopacity[i] = sum[3];
         dL_dscales[3 * i] = sum[4]; dL_dscales[3 * i + 1] = sum[5]; dL_dscales[3 * i + 2] = sum[6];
         dL_drots[4 * i] = sum[7]; dL_drots[4 * i + 1] = sum[8]; dL_drots[4 * i + 2] = sum[9]; dL_drots[4 * i + 3] = sum[10];
+        if (dL_dsh_rest) {
+            // split layout: dL_dsh is the [P][1][3] gradient of features_dc, dL_dsh_rest the [P][M-1][3] one of features_rest
+#pragma unroll
+            for (int k = 0; k < 3; ++k) dL_dsh[3 * i + k] = acc[k];
+            float* rrow = dL_dsh_rest + i * (size_t)(3 * (M - 1));
+#pragma unroll
+            for (int k = 3; k < 3 * kCoef; ++k) rrow[k - 3] = acc[k];
+            continue;
+        }
         float* row = dL_dsh + i * (size_t)(3 * M);
         if ((3 * kCoef) % 4 == 0 && ((3 * M) % 4) == 0 && (reinterpret_cast<size_t>(dL_dsh) & 15) == 0) {
 #pragma unroll
@@ -493,14 +503,15 @@ __global__ void __launch_bounds__(32 * kRcWarps) grad_record_combine_kernel(int 
 
 int launch_grad_record_combine(int P, int D, int M, int V, const float* means3D, const float* campos, const float* gathered,
                                size_t slot_stride, float* dL_dmeans3D, float* dL_dopacity, float* dL_dscales, float* dL_drots,
-                               float* dL_dsh, cudaStream_t stream) {
+                               float* dL_dsh, float* dL_dsh_rest, cudaStream_t stream) {
     if (P <= 0) return GS_OK;
     if (M < (D + 1) * (D + 1) || V < 1 || V > kRcMaxViews) return GS_ERR_ARG;
     const int nchunks = (P + kRecChunk - 1) / kRecChunk;
     const int blocks = (nchunks + kRcWarps - 1) / kRcWarps;
 #define GS_RC_LAUNCH(DEG)                                                                                                        \
     grad_record_combine_kernel<DEG><<<blocks, 32 * kRcWarps, 0, stream>>>(P, M, V, means3D, campos, gathered, slot_stride,       \
-                                                                          dL_dmeans3D, dL_dopacity, dL_dscales, dL_drots, dL_dsh)
+                                                                          dL_dmeans3D, dL_dopacity, dL_dscales, dL_drots, dL_dsh,  \
+                                                                          dL_dsh_rest)
     switch (D) {
         case 0: GS_RC_LAUNCH(0); break;
         case 1: GS_RC_LAUNCH(1); break;

@@ -13,6 +13,7 @@ struct PreprocessParams {
     const float* __restrict__ rotations;
     const float* __restrict__ opacities;
     const float* __restrict__ shs;
+    const float* __restrict__ shs_rest;  // non-null: split layout, shs = features_dc [P][1][3], this = features_rest [P][15][3] (M = 16)
     const float* __restrict__ cov3D_precomp;
     const float* __restrict__ colors_precomp;
     const float* __restrict__ viewmatrix;
@@ -83,6 +84,7 @@ struct PreprocessBwdParams {
     const float* __restrict__ means3D;
     const int* __restrict__ radii;
     const float* __restrict__ shs;        // null when colours were precomputed
+    const float* __restrict__ shs_rest;   // non-null: split layout (shs = features_dc, this = features_rest; M = 16)
     const uint8_t* __restrict__ clamped;
     const float* __restrict__ scales;     // null when cov3D was precomputed
     const float* __restrict__ rotations;
@@ -104,6 +106,7 @@ struct PreprocessBwdParams {
     float* __restrict__ dL_dopacity;   // [P]
     float* __restrict__ dL_dcov3D;     // [P,6]
     float* __restrict__ dL_dsh;        // [P,M,3]; null with shs non-null = factored exchange (dp_exchange.cu): rows not written
+    float* __restrict__ dL_dsh_rest;   // split layout: dL_dsh is [P,1,3] and this [P,15,3]
     float* __restrict__ dL_dscales;    // [P,3]
     float* __restrict__ dL_drots;      // [P,4]
     // View-sharded exchange, "records" layout: push.n > 0 = instead of the dense dL_dmeans3D / dL_dopacity / dL_dscales /
@@ -222,7 +225,7 @@ int launch_color_grad_push_sparse(int P, const int* radii, const uint8_t* clampe
 size_t dp_sparse_slot_floats(int P);
 int launch_grad_record_combine(int P, int D, int M, int V, const float* means3D, const float* campos, const float* gathered,
                                size_t slot_stride, float* dL_dmeans3D, float* dL_dopacity, float* dL_dscales, float* dL_drots,
-                               float* dL_dsh, cudaStream_t stream);
+                               float* dL_dsh, float* dL_dsh_rest, cudaStream_t stream);
 int launch_sh_grad_combine(int P, int D, int M, int V, const float* means3D, const float* campos, const float* gathered,
                            size_t slot_stride, bool sparse, float* dL_dsh, cudaStream_t stream);
 int launch_slab_all_reduce(const DpPeers& peers, bool multicast, size_t n_floats, int rank, int world, int sm_count,

@@ -60,16 +60,24 @@ GS_DEV float3 cov2d_ewa(const float3& mean, float focal_x, float focal_y, float 
 // into FMAs, and that choice must not drift with edits to the caller.
 // kVec: sh is the thread's row in the 16-byte staged tile (sh_stage.cuh); it is pulled into registers with twelve
 // LDS.128 (chunks above the active degree hold stale shared memory and are never used).
-template <bool kVec>
-__device__ __noinline__ V3 sh_to_rgb(int deg, const V3 pos, const V3 campos, const float* __restrict__ sh, uint8_t& clamp_bits) {
+// kSplit (with kVec): sh is the warp's pair of split tiles (features_dc / features_rest staged as they lie) and the row is
+// gathered from them instead; the arithmetic below is the same expression tree for both layouts (the bit-identity is
+// tested: tests/test_gpu_dp_exchange.py::test_split_sh_tensors_equal_the_concatenated_layout).
+template <bool kVec, bool kSplit = false>
+__device__ __noinline__ V3 sh_to_rgb(int deg, const V3 pos, const V3 campos, const float* __restrict__ sh, uint8_t& clamp_bits,
+                                     int split_lane = 0) {
     V3 dir = pos - campos;
     dir = dir / sqrt(dot3(dir, dir));
     float c48[kVec ? 48 : 1];
     if (kVec) {
+        if (kSplit) {
+            sh_split_row_to_regs(sh, split_lane, c48);
+        } else {
 #pragma unroll
-        for (int q = 0; q < 12; ++q) {
-            const float4 t = reinterpret_cast<const float4*>(sh)[q];
-            c48[kVec ? 4 * q : 0] = t.x; c48[kVec ? 4 * q + 1 : 0] = t.y; c48[kVec ? 4 * q + 2 : 0] = t.z; c48[kVec ? 4 * q + 3 : 0] = t.w;
+            for (int q = 0; q < 12; ++q) {
+                const float4 t = reinterpret_cast<const float4*>(sh)[q];
+                c48[kVec ? 4 * q : 0] = t.x; c48[kVec ? 4 * q + 1 : 0] = t.y; c48[kVec ? 4 * q + 2 : 0] = t.z; c48[kVec ? 4 * q + 3 : 0] = t.w;
+            }
         }
     }
     auto C = [&](int k) {
@@ -114,6 +122,7 @@ constexpr int kPfThreads = 128;
 // frustum test, so the copies overlap phase 1; a thread reading its own 192-byte row straight from global memory
 // would touch 32 different lines per load instruction (the reference's access pattern, forward.cu:29).
 // Every per-Gaussian output is written (defaults for culled ones, replacing three host-side fills).
+template <bool kSplit>
 __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const PreprocessParams p) {
     __shared__ __align__(16) float s_sh[kPfThreads / 32][kShTileFloats];
     __shared__ uint32_t s_tiles;
@@ -152,8 +161,13 @@ __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const Prepro
     float* tile = &s_sh[warp][0];
     const int ncoef3 = 3 * (p.D + 1) * (p.D + 1);
     // degree-3-sized rows on a 16-byte aligned base (the training layout) move as 16-byte chunks
-    const bool rows16 = staged && Mrow == 48 && (reinterpret_cast<size_t>(p.shs) & 15) == 0;
-    if (staged && alive_mask) {
+    const bool split = kSplit && use_sh;                   // shs = features_dc [P][1][3], shs_rest = features_rest [P][15][3]
+    const bool rows16 = !split && staged && Mrow == 48 && (reinterpret_cast<size_t>(p.shs) & 15) == 0;
+    if (split) {
+        if (alive_mask)
+            stage_sh_split_load(tile, p.shs + (size_t)warp_first * 3, p.shs_rest + (size_t)warp_first * kShSplitRestRow, rows_valid,
+                                alive_mask, lane);
+    } else if (staged && alive_mask) {
         float* src = const_cast<float*>(p.shs) + (size_t)warp_first * Mrow;
         if (rows16) stage_sh_rows16_load(reinterpret_cast<float4*>(tile), src, rows_valid, alive_mask, ncoef3, lane);
         else if (Mrow == 48) stage_sh_rows<true, 48>(tile, row_stride, src, Mrow, rows_valid, alive_mask, ncoef3, lane);
@@ -213,7 +227,9 @@ __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const Prepro
             uint8_t cb;
             const V3 campos(p.campos[0], p.campos[1], p.campos[2]);
             V3 c;
-            if (rows16) {
+            if (kSplit) {
+                c = sh_to_rgb<true, kSplit>(p.D, V3(p_orig.x, p_orig.y, p_orig.z), campos, tile, cb, lane);
+            } else if (rows16) {
                 c = sh_to_rgb<true>(p.D, V3(p_orig.x, p_orig.y, p_orig.z), campos, tile + lane * (4 * kShPitch4), cb);
             } else {
                 const float* my_sh = staged ? tile + lane * row_stride : p.shs + i * Mrow;
@@ -264,7 +280,8 @@ __global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* _
 
 int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream) {
     if (p.P <= 0) return GS_OK;
-    preprocess_fwd_kernel<<<(p.P + kPfThreads - 1) / kPfThreads, kPfThreads, 0, stream>>>(p);
+    if (p.shs_rest && !p.colors_precomp) preprocess_fwd_kernel<true><<<(p.P + kPfThreads - 1) / kPfThreads, kPfThreads, 0, stream>>>(p);
+    else preprocess_fwd_kernel<false><<<(p.P + kPfThreads - 1) / kPfThreads, kPfThreads, 0, stream>>>(p);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

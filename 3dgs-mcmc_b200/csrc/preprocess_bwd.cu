@@ -37,15 +37,19 @@ GS_DEV void store3(float* __restrict__ dst, size_t idx, float a, float b, float 
 // kVec: sh is the thread's row in the 16-byte staged tile (sh_stage.cuh), read with LDS.128; otherwise a row of floats in
 // shared or global memory. |dir|^2 is spelled out (norm2_fixed): with two inlined instantiations the compiler merges their
 // common prologue across blocks and its own FMA contraction of the dot product is lost.
+// split_lane >= 0 (kVec only): sh is the warp's pair of split tiles (sh_stage.cuh) and the row is gathered from them.
 template <bool kVec>
 GS_DEV float3 sh_backward(int deg, const V3 pos, const V3 campos, const float* sh, uint8_t clamp_bits, V3 dL_dRGB,
-                          float (&basis_out)[16], V3& dL_dRGB_out) {
+                          float (&basis_out)[16], V3& dL_dRGB_out, int split_lane = -1) {
     const V3 dir_orig = pos - campos;
     const float norm = sqrt(norm2_fixed(dir_orig));
     const V3 dir = dir_orig / norm;
     const float inv_norm = 1.0f / norm;
     float c48[kVec ? 48 : 1];
-    if (kVec) sh_row_to_regs(reinterpret_cast<const float4*>(sh), 0, c48);
+    if (kVec) {
+        if (split_lane >= 0) sh_split_row_to_regs(sh, split_lane, c48);
+        else sh_row_to_regs(reinterpret_cast<const float4*>(sh), 0, c48);
+    }
     auto C = [&](int k) {
         return kVec ? V3(c48[kVec ? 3 * k : 0], c48[kVec ? 3 * k + 1 : 0], c48[kVec ? 3 * k + 2 : 0])
                     : V3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]);
@@ -161,9 +165,14 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
     // Degree-3-sized rows (M = 16, the training layout) on 16-byte aligned bases move as 16-byte chunks both ways:
     // cp.async.16 in, LDS.128 into registers, and the gradient rows (basis x masked colour gradient, formed in registers)
     // parked with STS.128 and streamed out as 512-byte warp stores.
-    const bool rows16 = staged && Mrow == 48 && (reinterpret_cast<size_t>(p.shs) & 15) == 0 &&
+    const bool split = p.shs != nullptr && p.shs_rest != nullptr;    // features_dc / features_rest as two tensors (M = 16)
+    const bool rows16 = !split && staged && Mrow == 48 && (reinterpret_cast<size_t>(p.shs) & 15) == 0 &&
                         (!write_dsh || (reinterpret_cast<size_t>(p.dL_dsh) & 15) == 0);
-    if (staged && rows_valid > 0) {
+    if (split) {
+        if (rows_valid > 0 && vis_mask)
+            stage_sh_split_load(tile, p.shs + (size_t)warp_first * 3, p.shs_rest + (size_t)warp_first * kShSplitRestRow, rows_valid,
+                                vis_mask, lane);
+    } else if (staged && rows_valid > 0) {
         float* src = const_cast<float*>(p.shs) + (size_t)warp_first * Mrow;
         if (rows16) stage_sh_rows16_load(reinterpret_cast<float4*>(tile), src, rows_valid, vis_mask, 3 * ncoef, lane);
         else if (Mrow == 48) stage_sh_rows<true, 48>(tile, row_stride, src, Mrow, rows_valid, vis_mask, 0, lane);
@@ -189,7 +198,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
     float3 dmean = {0.f, 0.f, 0.f};
     float dscale[3] = {0.f, 0.f, 0.f};
     float4 drot = make_float4(0.f, 0.f, 0.f, 0.f);
-    float* my_dsh = p.shs ? (staged ? tile + lane * row_stride : (write_dsh ? p.dL_dsh + i * Mrow : nullptr)) : nullptr;
+    float* my_dsh = (p.shs && !split) ? (staged ? tile + lane * row_stride : (write_dsh ? p.dL_dsh + i * Mrow : nullptr)) : nullptr;
     const float* my_sh = p.shs ? (staged ? tile + lane * row_stride : p.shs + i * Mrow) : nullptr;
 
     if (visible) {
@@ -263,11 +272,13 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
         if (p.shs) {
             const V3 campos(p.campos[0], p.campos[1], p.campos[2]);
             const float3 dsh_mean =
-                rows16 ? sh_backward<true>(p.D, V3(mean.x, mean.y, mean.z), campos, tile + lane * (4 * kShPitch4), p.clamped[idx],
+                split  ? sh_backward<true>(p.D, V3(mean.x, mean.y, mean.z), campos, tile, p.clamped[idx],
+                                           V3(acc0.x, acc0.y, acc0.z), basis, g_rgb, lane)
+                : rows16 ? sh_backward<true>(p.D, V3(mean.x, mean.y, mean.z), campos, tile + lane * (4 * kShPitch4), p.clamped[idx],
                                            V3(acc0.x, acc0.y, acc0.z), basis, g_rgb)
                        : sh_backward<false>(p.D, V3(mean.x, mean.y, mean.z), campos, my_sh, p.clamped[idx],
                                             V3(acc0.x, acc0.y, acc0.z), basis, g_rgb);
-            if (!rows16 && my_dsh) {
+            if (!rows16 && !split && my_dsh) {
                 // every read of the row (shared tile or memory) is above: the gradient row may now overwrite it
 #pragma unroll
                 for (int k = 0; k < 16; ++k) {
@@ -345,7 +356,22 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
         store3(p.dL_dscales, i, dscale[0], dscale[1], dscale[2]);
         store_quat(p.dL_drots, i, p.drot_aligned != 0, drot);
     }
-    if (rows16) {
+    if (split) {
+        if (write_dsh) {
+            // every lane's reads of the tiles are done (sh_backward pulled the rows into registers): the gradient rows go
+            // into the same places and leave as 16-byte chunks of the two gradient tensors
+            __syncwarp();
+            const float gc[3] = {g_rgb.x, g_rgb.y, g_rgb.z};
+#pragma unroll
+            for (int k = 0; k < 3; ++k) tile[3 * lane + k] = basis[0] * gc[k];
+#pragma unroll
+            for (int k = 0; k < kShSplitRestRow; ++k) tile[kShSplitDc + kShSplitRestRow * lane + k] = basis[1 + k / 3] * gc[k % 3];
+            __syncwarp();
+            if (rows_valid > 0)
+                stage_sh_split_store(tile, p.dL_dsh + (size_t)warp_first * 3, p.dL_dsh_rest + (size_t)warp_first * kShSplitRestRow,
+                                     rows_valid, lane);
+        }
+    } else if (rows16) {
         if (write_dsh) {
             float4* tile4 = reinterpret_cast<float4*>(tile);
             const float gc[3] = {g_rgb.x, g_rgb.y, g_rgb.z};

@@ -100,4 +100,69 @@ GS_DEV void stage_sh_rows16_store(const float4* tile4, float* gmem /* first row 
     }
 }
 
+// ---- split SH tensors: features_dc [P][1][3] and features_rest [P][15][3] (scene/gaussian_model_static.py:139-144) ----
+// The model keeps the two apart and the reference concatenates them every iteration. Their rows (12 B and 180 B) are not
+// 16-byte aligned, but a warp's 32 rows are contiguous in each tensor and 16-byte sized (384 B = 24 chunks, 5760 B = 360
+// chunks), so they are copied as they lie into two linear tiles - dc at floats [0, 96), rest at [96, 1536) of the warp's
+// tile - with cp.async.16, and a thread walks its rows with scalar LDS / STS at strides 3 and 45 floats (both odd: conflict
+// free). The same instruction count as the 16-byte path of the concatenated layout, no copy of the 576 MB tensor.
+constexpr int kShSplitDc = 96;            // floats of the dc tile (32 rows x 3)
+constexpr int kShSplitRestRow = 45;
+static_assert(kShSplitDc + 32 * kShSplitRestRow <= kShTileFloats, "split tiles fit the warp's staging tile");
+
+// Starts the copies of every 16-byte chunk that holds part of a row in row_mask; the caller waits with
+// cp_async_wait_all() + __syncwarp(). A chunk that would run past the last row of the tensor is copied float by float.
+GS_DEV void stage_sh_split_load(float* tile, const float* dc /* first row of the warp */, const float* rest, int rows_valid,
+                                uint32_t row_mask, int lane) {
+#pragma unroll
+    for (int it = 0; it < 12; ++it) {
+        const int c = it * 32 + lane;                     // chunk of the warp's 24 + 360
+        const bool is_dc = c < 24;
+        const int f0 = 4 * (is_dc ? c : c - 24);          // first float of the chunk within its tensor block
+        const int rowlen = is_dc ? 3 : kShSplitRestRow;
+        const int r0 = f0 / rowlen, r1 = (f0 + 3) / rowlen;
+        if (r0 >= rows_valid) continue;
+        const bool wanted = ((row_mask >> r0) & 1u) || (r1 < 32 && ((row_mask >> r1) & 1u));
+        if (!wanted) continue;
+        const float* src = (is_dc ? dc : rest) + f0;
+        float* dst = tile + (is_dc ? 0 : kShSplitDc) + f0;
+        const int floats_left = rows_valid * rowlen - f0;
+        if (floats_left >= 4) {
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+        } else {
+            for (int k = 0; k < floats_left; ++k)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst + k)), "l"(src + k) : "memory");
+        }
+    }
+}
+
+// The thread's own rows from the split tiles into registers, in the concatenated order (dc first).
+GS_DEV void sh_split_row_to_regs(const float* tile, int lane, float* c48) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) c48[k] = tile[3 * lane + k];
+#pragma unroll
+    for (int k = 0; k < kShSplitRestRow; ++k) c48[3 + k] = tile[kShSplitDc + kShSplitRestRow * lane + k];
+}
+
+// Gradient rows parked in the split tiles (thread `lane`: dc at tile[3 lane ...], rest at tile[96 + 45 lane ...]) streamed out
+// to the two gradient tensors as coalesced 16-byte stores; the ragged end of the last warp goes float by float.
+GS_DEV void stage_sh_split_store(const float* tile, float* dc /* first row of the warp */, float* rest, int rows_valid, int lane) {
+#pragma unroll
+    for (int it = 0; it < 12; ++it) {
+        const int c = it * 32 + lane;
+        const bool is_dc = c < 24;
+        const int f0 = 4 * (is_dc ? c : c - 24);
+        const int rowlen = is_dc ? 3 : kShSplitRestRow;
+        const int floats_left = rows_valid * rowlen - f0;
+        if (floats_left <= 0) continue;
+        const float* src = tile + (is_dc ? 0 : kShSplitDc) + f0;
+        float* dst = (is_dc ? dc : rest) + f0;
+        if (floats_left >= 4) {
+            __stcs(reinterpret_cast<float4*>(dst), *reinterpret_cast<const float4*>(src));
+        } else {
+            for (int k = 0; k < floats_left; ++k) dst[k] = src[k];
+        }
+    }
+}
+
 }  // namespace gs

@@ -90,8 +90,45 @@ class _RasterizeGaussians(torch.autograd.Function):
                 grad_rotations, grad_cov3Ds_precomp, None)
 
 
+class _RasterizeGaussiansSplitSH(torch.autograd.Function):
+    """Additive: the SH coefficients as the model stores them, features_dc [P,1,3] and features_rest [P,15,3]
+    (scene/gaussian_model_static.py:139-144), instead of their concatenation. Same kernels and arithmetic as
+    _RasterizeGaussians - bit-identical image and gradients - without the 576 MB copy (P = 3M) of get_features on the way
+    in and autograd's split of the gradient on the way out."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh_dc, sh_rest, opacities, scales, rotations, raster_settings):
+        s = raster_settings
+        absent = torch.Tensor([])
+        num_rendered, color, radii, geom_buffer, binning_buffer, img_buffer, is_used = _C.rasterize_gaussians(
+            s.bg, means3D, absent, opacities, scales, rotations, s.scale_modifier, absent, s.viewmatrix, s.projmatrix,
+            s.tanfovx, s.tanfovy, s.image_height, s.image_width, (sh_dc, sh_rest), s.sh_degree, s.campos, s.prefiltered,
+            s.debug)
+        ctx.raster_settings = s
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(means3D, scales, rotations, radii, sh_dc, sh_rest, geom_buffer, binning_buffer, img_buffer)
+        ctx.mark_non_differentiable(radii, is_used)
+        return color, radii, is_used
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _grad_radii, _grad_is_used):
+        s = ctx.raster_settings
+        means3D, scales, rotations, radii, sh_dc, sh_rest, geom_buffer, binning_buffer, img_buffer = ctx.saved_tensors
+        absent = torch.Tensor([])
+        (grad_means2D, _grad_colors, grad_opacities, grad_means3D, _grad_cov3D, grad_sh, grad_scales,
+         grad_rotations) = _C.rasterize_gaussians_backward(
+            s.bg, means3D, radii, absent, scales, rotations, s.scale_modifier, absent, s.viewmatrix, s.projmatrix,
+            s.tanfovx, s.tanfovy, grad_out_color, (sh_dc, sh_rest), s.sh_degree, s.campos, geom_buffer, ctx.num_rendered,
+            binning_buffer, img_buffer, s.debug)
+        return (grad_means3D, grad_means2D, grad_sh[0], grad_sh[1], grad_opacities, grad_scales, grad_rotations, None)
+
+
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings):
+    if isinstance(sh, (tuple, list)):
+        if colors_precomp.numel() or cov3Ds_precomp.numel():
+            raise Exception('Split SH tensors (features_dc, features_rest) go with scales / rotations only!')
+        return _RasterizeGaussiansSplitSH.apply(means3D, means2D, sh[0], sh[1], opacities, scales, rotations, raster_settings)
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
                                      cov3Ds_precomp, raster_settings)
 

@@ -41,13 +41,19 @@ SIGNATURES = {
     "gs_backward": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 5
                     + [_c_float] + [_c_void_p] * 5 + [_c_float, _c_float] + [_c_void_p] * 14),
     "gs_backward_render": (_c_int, [_c_void_p, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 6),
+    "gs_backward_render_ev": (_c_int, [_c_void_p, _c_int, _c_uint, _c_int, _c_int] + [_c_void_p] * 7),
+    "gs_stream_wait_event": (_c_int, [_c_void_p, _c_void_p]),
     "gs_backward_geometry": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int] + [_c_void_p] * 3 + [_c_float]
                              + [_c_void_p] * 5 + [_c_float, _c_float] + [_c_void_p] * 11),
     "gs_dp_slot_floats": (_c_size_t, [_c_int, _c_int]),
-    "gs_backward_geometry_push": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int] + [_c_void_p] * 3 + [_c_float]
+    "gs_backward_geometry_push": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int] + [_c_void_p] * 4 + [_c_float]
                                   + [_c_void_p] * 4 + [_c_float, _c_float] + [_c_void_p] * 5 + [_c_int, _c_int, _c_size_t]),
     "gs_dp_grad_record_combine": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p,
-                                           _c_size_t, _c_int] + [_c_void_p] * 5),
+                                           _c_size_t, _c_int] + [_c_void_p] * 6),
+    "gs_forward_preprocess_split_sh": (_c_int, [_c_void_p, _c_int, _c_int] + [_c_void_p] * 5 + [_c_float] + [_c_void_p] * 4
+                                       + [_c_int, _c_int, _c_float, _c_float, _c_int] + [_c_void_p] * 5),
+    "gs_backward_geometry_split_sh": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int] + [_c_void_p] * 4 + [_c_float]
+                                      + [_c_void_p] * 4 + [_c_float, _c_float] + [_c_void_p] * 12),
     "gs_dp_color_grad_push": (_c_int, [_c_void_p, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_int, _c_int,
                                        _c_size_t, _c_int]),
     "gs_dp_sh_grad_combine": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p,
@@ -209,9 +215,13 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     cov3D_precomp = _f32_cuda(cov3D_precomp, "cov3D_precomp", device)
     viewmatrix = _f32_cuda(viewmatrix, "viewmatrix", device)
     projmatrix = _f32_cuda(projmatrix, "projmatrix", device)
-    sh = _f32_cuda(sh, "sh", device)
+    split = isinstance(sh, (tuple, list))     # (features_dc [P,1,3], features_rest [P,15,3]) read as they lie (additive)
+    if split:
+        sh_dc, sh_rest = _split_sh(sh, P, device)
+    else:
+        sh = _f32_cuda(sh, "sh", device)
     campos = _f32_cuda(campos, "campos", device)
-    M = int(sh.size(1)) if sh is not None and sh.numel() != 0 else 0
+    M = 16 if split else (int(sh.size(1)) if sh is not None and sh.numel() != 0 else 0)
 
     with torch.cuda.device(device):
         stream = _stream(device)
@@ -223,12 +233,19 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         slot_key, slot = _acquire_count_slot(device)
         count, count_ev = slot.buf, slot.event
 
-        _check(_lib.gs_forward_preprocess(
-            stream, P, int(degree), M, _ptr(means3D), _ptr(sh), _ptr(colors), _ptr(opacity), _ptr(scales),
-            float(scale_modifier), _ptr(rotations), _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix),
-            _ptr(campos), W, H, float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
-            radii.data_ptr(), is_used.data_ptr(), geom.data_ptr(), count.data_ptr(), count_ev),
-            "gs_forward_preprocess")
+        if split:
+            _check(_lib.gs_forward_preprocess_split_sh(
+                stream, P, int(degree), _ptr(means3D), sh_dc.data_ptr(), sh_rest.data_ptr(), _ptr(opacity), _ptr(scales),
+                float(scale_modifier), _ptr(rotations), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), W, H,
+                float(tan_fovx), float(tan_fovy), int(bool(prefiltered)), radii.data_ptr(), is_used.data_ptr(),
+                geom.data_ptr(), count.data_ptr(), count_ev), "gs_forward_preprocess_split_sh")
+        else:
+            _check(_lib.gs_forward_preprocess(
+                stream, P, int(degree), M, _ptr(means3D), _ptr(sh), _ptr(colors), _ptr(opacity), _ptr(scales),
+                float(scale_modifier), _ptr(rotations), _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix),
+                _ptr(campos), W, H, float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
+                radii.data_ptr(), is_used.data_ptr(), geom.data_ptr(), count.data_ptr(), count_ev),
+                "gs_forward_preprocess")
         # The one host wait of the forward (the reference blocks the stream here, rasterizer_impl.cu:282): the
         # binning workspace is sized from the instance count. Only the preprocess kernel is waited for; the depth
         # sort and scan enqueued behind it keep the GPU busy meanwhile.
@@ -262,6 +279,17 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     device = means3D.device
     P = int(means3D.size(0))
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
+    if isinstance(sh, (tuple, list)):
+        # split SH tensors: the two halves of the backward; dL_dsh comes back as (dL_dfeatures_dc, dL_dfeatures_rest)
+        if P == 0:
+            z = lambda *shape: torch.zeros(shape, dtype=torch.float32, device=device)  # noqa: E731
+            return z(0, 3), z(0, 3), z(0, 1), z(0, 3), z(0, 6), (z(0, 1, 3), z(0, 15, 3)), z(0, 3), z(0, 4)
+        scratch = backward_render(background, P, R, dL_dout_color, geomBuffer, binningBuffer, imageBuffer)
+        outs = backward_geometry(means3D, radii, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix, projmatrix,
+                                 tan_fovx, tan_fovy, H, W, sh, degree, campos, geomBuffer, scratch, out_buffers=out_buffers)
+        if debug:
+            _debug_sync("backward")
+        return outs
     M = int(sh.size(1)) if sh is not None and sh.numel() != 0 else 0
     opts = dict(dtype=torch.float32, device=device)
     shapes = [(P, 3), (P, 3), (P, 1), (P, 3), (P, 6), (P, M, 3), (P, 3), (P, 4)]
@@ -320,18 +348,32 @@ def _backward_outputs(P, M, device, out_buffers, want_sh):
     return outs
 
 
-def backward_render(background, P, R, dL_dout_color, geomBuffer, binningBuffer, imageBuffer):
+def new_event():
+    """A CUDA event without timing owned by the library (gs_host_event_create), as an opaque handle."""
+    ev = _lib.gs_host_event_create()
+    if not ev:
+        raise RuntimeError("gs_host_event_create failed")
+    return ev
+
+
+def stream_wait_event(stream, event):
+    """Make the torch stream wait for a library event (gs_stream_wait_event)."""
+    _check(_lib.gs_stream_wait_event(ctypes.c_void_p(stream.cuda_stream), event), "gs_stream_wait_event")
+
+
+def backward_render(background, P, R, dL_dout_color, geomBuffer, binningBuffer, imageBuffer, cleared_event=None):
     """First half of the backward (gs_backward_render): zero the per-Gaussian accumulators and run the tile kernel.
-    Returns the scratch tensor that backward_geometry / dp_color_grad_push read."""
+    Returns the scratch tensor that backward_geometry / dp_color_grad_push read. cleared_event (new_event()): recorded
+    between the two, so that side-stream work can be ordered after the clear and beside the tile kernel."""
     device = dL_dout_color.device
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     background = _f32_cuda(background, "bg", device)
     dL_dout_color = _f32_cuda(dL_dout_color, "dL_dout_color", device)
     with torch.cuda.device(device):
         scratch = torch.empty(max(_lib.gs_backward_scratch_bytes(P), 16), dtype=torch.uint8, device=device)
-        _check(_lib.gs_backward_render(_stream(device), int(P), int(R), W, H, _ptr(background), geomBuffer.data_ptr(),
-                                       binningBuffer.data_ptr(), imageBuffer.data_ptr(), dL_dout_color.data_ptr(),
-                                       scratch.data_ptr()), "gs_backward_render")
+        _check(_lib.gs_backward_render_ev(_stream(device), int(P), int(R), W, H, _ptr(background), geomBuffer.data_ptr(),
+                                          binningBuffer.data_ptr(), imageBuffer.data_ptr(), dL_dout_color.data_ptr(),
+                                          scratch.data_ptr(), cleared_event), "gs_backward_render")
     return scratch
 
 
@@ -341,16 +383,36 @@ def backward_geometry(means3D, radii, scales, rotations, scale_modifier, cov3D_p
     rebuilds the cross-view sum with dp_sh_grad_combine); the returned tuple has None in its place."""
     device = means3D.device
     P = int(means3D.size(0))
-    M = int(sh.size(1)) if sh is not None and sh.numel() != 0 else 0
+    split = isinstance(sh, (tuple, list))
+    M = 16 if split else (int(sh.size(1)) if sh is not None and sh.numel() != 0 else 0)
     means3D = _f32_cuda(means3D, "means3D", device)
     scales = _f32_cuda(scales, "scales", device)
     rotations = _f32_cuda(rotations, "rotations", device)
     cov3D_precomp = _f32_cuda(cov3D_precomp, "cov3D_precomp", device)
     viewmatrix = _f32_cuda(viewmatrix, "viewmatrix", device)
     projmatrix = _f32_cuda(projmatrix, "projmatrix", device)
-    sh = _f32_cuda(sh, "sh", device)
     campos = _f32_cuda(campos, "campos", device)
     radii = radii.contiguous()
+    if split:
+        if not write_sh:
+            raise RuntimeError("split SH tensors: write_sh=False is the records exchange (backward_geometry_push)")
+        sh_dc, sh_rest = _split_sh(sh, P, device)
+        with torch.cuda.device(device):
+            outs = _backward_outputs(P, M, device, out_buffers, want_sh=False)
+            dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, _, dL_dscales, dL_drotations = outs
+            buf = (out_buffers or {}).get("sh")
+            d_dc, d_rest = _split_sh(buf, P, device) if buf is not None else (
+                torch.empty((P, 1, 3), dtype=torch.float32, device=device), torch.empty((P, 15, 3), dtype=torch.float32, device=device))
+            if P:
+                _check(_lib.gs_backward_geometry_split_sh(
+                    _stream(device), P, int(degree), int(W), int(H), _ptr(means3D), sh_dc.data_ptr(), sh_rest.data_ptr(),
+                    _ptr(scales), float(scale_modifier), _ptr(rotations), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos),
+                    float(tan_fovx), float(tan_fovy), radii.data_ptr(), geomBuffer.data_ptr(), scratch.data_ptr(),
+                    dL_dmeans2D.data_ptr(), dL_dcolors.data_ptr(), dL_dopacity.data_ptr(), dL_dmeans3D.data_ptr(),
+                    dL_dcov3D.data_ptr(), d_dc.data_ptr(), d_rest.data_ptr(), dL_dscales.data_ptr(), dL_drotations.data_ptr()),
+                    "gs_backward_geometry_split_sh")
+        return (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, (d_dc, d_rest), dL_dscales, dL_drotations)
+    sh = _f32_cuda(sh, "sh", device)
     with torch.cuda.device(device):
         outs = _backward_outputs(P, M, device, out_buffers, want_sh=write_sh)
         dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations = outs
@@ -363,6 +425,18 @@ def backward_geometry(means3D, radii, scales, rotations, scale_modifier, cov3D_p
                 dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(), _ptr(dL_dsh), dL_dscales.data_ptr(),
                 dL_drotations.data_ptr()), "gs_backward_geometry")
     return tuple(outs)
+
+
+def _split_sh(pair, P, device):
+    """(features_dc [P,1,3], features_rest [P,15,3]) as contiguous float32 CUDA tensors on 16-byte aligned bases."""
+    dc, rest = pair
+    for name, t, shape in (("features_dc", dc, (P, 1, 3)), ("features_rest", rest, (P, 15, 3))):
+        if not isinstance(t, torch.Tensor) or t.dtype != torch.float32 or t.device != device or tuple(t.shape) != shape:
+            raise RuntimeError(f"split SH: {name} must be a float32 {shape} tensor on {device} (degree-3 storage, M = 16)")
+    dc, rest = dc.contiguous(), rest.contiguous()
+    if dc.data_ptr() % 16 or rest.data_ptr() % 16:
+        raise RuntimeError("split SH: features_dc / features_rest must start on 16-byte boundaries")
+    return dc, rest
 
 
 def _ptr_array(ptrs):
@@ -378,13 +452,17 @@ def backward_geometry_push(means3D, radii, scales, rotations, scale_modifier, vi
     """Second half of the backward for the "records" exchange (gs_backward_geometry_push): the parameter gradients leave as
     sparse chunk records at float offset slot_offset of every buffer in dst_ptrs; returns dL_dmeans2D [P, 3]."""
     device = means3D.device
-    P, M = int(means3D.size(0)), int(sh.size(1))
+    P = int(means3D.size(0))
+    if isinstance(sh, (tuple, list)):
+        sh, sh_rest = _split_sh(sh, P, device)
+        M = 16
+    else:
+        sh, sh_rest, M = _f32_cuda(sh, "sh", device), None, int(sh.size(1))
     means3D = _f32_cuda(means3D, "means3D", device)
     scales = _f32_cuda(scales, "scales", device)
     rotations = _f32_cuda(rotations, "rotations", device)
     viewmatrix = _f32_cuda(viewmatrix, "viewmatrix", device)
     projmatrix = _f32_cuda(projmatrix, "projmatrix", device)
-    sh = _f32_cuda(sh, "sh", device)
     campos = _f32_cuda(campos, "campos", device)
     radii = radii.contiguous()
     arr = _ptr_array(dst_ptrs)
@@ -395,17 +473,19 @@ def backward_geometry_push(means3D, radii, scales, rotations, scale_modifier, vi
             raise RuntimeError(f"means2D_out must be a contiguous float32 {(P, 3)} tensor")
         if P:
             _check(_lib.gs_backward_geometry_push(
-                _stream(device), P, int(degree), M, int(W), int(H), _ptr(means3D), _ptr(sh), _ptr(scales),
+                _stream(device), P, int(degree), M, int(W), int(H), _ptr(means3D), _ptr(sh), _ptr(sh_rest), _ptr(scales),
                 float(scale_modifier), _ptr(rotations), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), float(tan_fovx),
                 float(tan_fovy), radii.data_ptr(), geomBuffer.data_ptr(), scratch.data_ptr(), means2D_out.data_ptr(),
                 ctypes.cast(arr, _c_void_p), len(dst_ptrs), 1 if multicast else 0, int(slot_offset)), "gs_backward_geometry_push")
     return means2D_out
 
 
-def dp_grad_record_combine(means3D, campos_views, records, slot_stride, degree, M, outs=None, outputs_are_zero=False):
+def dp_grad_record_combine(means3D, campos_views, records, slot_stride, degree, M, outs=None, outputs_are_zero=False,
+                           split_sh=False):
     """Gradients summed over the V views whose chunk records sit in records[V, slot_stride] (gs_dp_grad_record_combine).
     outs: dict of contiguous float32 tensors "means3D" [P,3], "opacity" [P,1], "scales" [P,3], "rotations" [P,4], "sh" [P,M,3]
-    (allocated when None); outputs_are_zero=True promises they hold zeros already."""
+    (allocated when None); outputs_are_zero=True promises they hold zeros already. split_sh (or an "sh_rest" entry in outs):
+    "sh" is the [P,1,3] gradient of features_dc and "sh_rest" the [P,M-1,3] one of features_rest."""
     device = means3D.device
     P, V = int(means3D.size(0)), int(campos_views.size(0))
     means3D = _f32_cuda(means3D, "means3D", device)
@@ -413,7 +493,12 @@ def dp_grad_record_combine(means3D, campos_views, records, slot_stride, degree, 
     records = _f32_cuda(records, "records", device)
     if records.numel() < V * slot_stride:
         raise RuntimeError("records is smaller than V * slot_stride floats")
-    shapes = {"means3D": (P, 3), "opacity": (P, 1), "scales": (P, 3), "rotations": (P, 4), "sh": (P, int(M), 3)}
+    shapes = {"means3D": (P, 3), "opacity": (P, 1), "scales": (P, 3), "rotations": (P, 4)}
+    split = split_sh or (outs is not None and "sh_rest" in outs)
+    if split:
+        shapes.update(sh=(P, 1, 3), sh_rest=(P, int(M) - 1, 3))     # gradients of features_dc / features_rest
+    else:
+        shapes["sh"] = (P, int(M), 3)
     if outs is None:
         outs = {k: torch.empty(shp, dtype=torch.float32, device=device) for k, shp in shapes.items()}
         outputs_are_zero = False
@@ -426,7 +511,8 @@ def dp_grad_record_combine(means3D, campos_views, records, slot_stride, degree, 
             _check(_lib.gs_dp_grad_record_combine(
                 _stream(device), P, int(degree), int(M), V, means3D.data_ptr(), campos_views.data_ptr(), records.data_ptr(),
                 int(slot_stride), 1 if outputs_are_zero else 0, outs["means3D"].data_ptr(), outs["opacity"].data_ptr(),
-                outs["scales"].data_ptr(), outs["rotations"].data_ptr(), outs["sh"].data_ptr()), "gs_dp_grad_record_combine")
+                outs["scales"].data_ptr(), outs["rotations"].data_ptr(), outs["sh"].data_ptr(),
+                outs["sh_rest"].data_ptr() if split else None), "gs_dp_grad_record_combine")
     return outs
 
 

@@ -234,7 +234,7 @@ class FactoredExchange:
         self.gathered = self._gathered_all[0]
         if self.device.type == "cuda":
             self._zero_stream = torch.cuda.Stream(device=self.device, priority=-1)
-            self._ev_zero_fork, self._ev_zero = torch.cuda.Event(), torch.cuda.Event()
+            self._ev_zero, self._ev_cleared = torch.cuda.Event(), None
         self.resize(self.P)
 
     def resize(self, P):
@@ -388,31 +388,40 @@ class FactoredExchange:
 
     OUT_FIELDS = (("means3D", 3), ("opacity", 1), ("scales", 3), ("rotations", 4))
 
-    def _fresh_zeroed_outputs(self):
-        """The five summed-gradient tensors as views of ONE fresh allocation, zero-filled on a high-priority side stream so
-        that the 708 MB fill (P = 3M) runs under the compute-bound tile backward instead of on the critical path. Fresh,
-        because autograd keeps what backward returns as .grad without a copy only if nobody else holds it."""
+    def _fresh_outputs(self, split_sh=False):
+        """The five summed-gradient tensors as views of ONE fresh allocation (returned with them; zero-filled by the caller).
+        Fresh, because autograd keeps what backward returns as .grad without a copy only if nobody else holds it."""
         P, M = self.P, self.M
-        widths = [w for _, w in self.OUT_FIELDS] + [3 * M]
+        widths = [w for _, w in self.OUT_FIELDS] + ([3, 3 * (M - 1)] if split_sh else [3 * M])
         starts, off = [], 0
         for w in widths:
             starts.append(off)
             off = _round_up(off + P * w, 4)
         flat = torch.empty(off, dtype=torch.float32, device=self.device)
-        main = torch.cuda.current_stream(self.device)
-        self._ev_zero_fork.record(main)
-        self._zero_stream.wait_event(self._ev_zero_fork)
+        outs = {name: flat[o: o + P * w].view(P, w) for (name, w), o in zip(self.OUT_FIELDS, starts)}
+        if split_sh:                                        # gradients of features_dc / features_rest, as the model stores them
+            outs["sh"] = flat[starts[-2]: starts[-2] + P * 3].view(P, 1, 3)
+            outs["sh_rest"] = flat[starts[-1]: starts[-1] + P * 3 * (M - 1)].view(P, M - 1, 3)
+        else:
+            outs["sh"] = flat[starts[-1]: starts[-1] + P * 3 * M].view(P, M, 3)
+        return flat, outs
+
+    def _zero_beside_tile_backward(self, native, flat):
+        """Zero-fill `flat` (708 MB at P = 3M) on the side stream, ordered after the accumulator clear at the head of the
+        backward (the event gs_backward_render_ev records): the fill then runs under the compute-bound tile kernel, which
+        leaves HBM idle, instead of sharing bandwidth with the clear (measured: the clear took 0.116 ms instead of 0.023)."""
+        native.stream_wait_event(self._zero_stream, self._ev_cleared)
         with torch.cuda.stream(self._zero_stream):
             flat.zero_()
             self._ev_zero.record(self._zero_stream)
-        outs = {name: flat[o: o + P * w].view(P, w) for (name, w), o in zip(self.OUT_FIELDS, starts)}
-        outs["sh"] = flat[starts[-1]: starts[-1] + P * 3 * M].view(P, M, 3)
-        return outs
 
     def _backward_records(self, native, bg, means3D, radii, scales, rotations, scale_modifier, viewmatrix, projmatrix, tan_fovx,
                           tan_fovy, dL_dout_color, sh, degree, campos, campos_views, geom, R, binning, img, H, W):
-        outs = self._fresh_zeroed_outputs()
-        scratch = native.backward_render(bg, self.P, R, dL_dout_color, geom, binning, img)
+        flat, outs = self._fresh_outputs(split_sh=isinstance(sh, (tuple, list)))
+        if self._ev_cleared is None:
+            self._ev_cleared = native.new_event()
+        scratch = native.backward_render(bg, self.P, R, dL_dout_color, geom, binning, img, cleared_event=self._ev_cleared)
+        self._zero_beside_tile_backward(native, flat)
         buf = self._step % self._nbuf
         self._step += 1
         gathered = self._gathered_all[buf]
@@ -449,15 +458,21 @@ class _RasterizeGaussiansViewParallel(torch.autograd.Function):
     this rank's own screen-space gradient (the densification statistic is per view, as in the reference)."""
 
     @staticmethod
-    def forward(ctx, means3D, means2D, sh, opacities, scales, rotations, raster_settings, campos_views, exchange):
+    def forward(ctx, means3D, means2D, sh, sh_rest, opacities, scales, rotations, raster_settings, campos_views, exchange):
+        """sh_rest None: sh is the concatenated [P,M,3] tensor; else sh = features_dc [P,1,3], sh_rest = features_rest
+        [P,15,3] read as they lie (records layout only)."""
         from . import _native as C
         s = raster_settings
         e = torch.empty(0)
+        if sh_rest is not None and exchange.layout != "records":
+            raise RuntimeError("split SH tensors need the records exchange layout")
         R, color, radii, geom, binning, img, is_used = C.rasterize_gaussians(
             s.bg, means3D, e, opacities, scales, rotations, s.scale_modifier, e, s.viewmatrix, s.projmatrix, s.tanfovx,
-            s.tanfovy, s.image_height, s.image_width, sh, s.sh_degree, s.campos, s.prefiltered, s.debug)
-        ctx.raster_settings, ctx.num_rendered, ctx.exchange = s, R, exchange
-        ctx.save_for_backward(means3D, scales, rotations, radii, sh, campos_views, geom, binning, img)
+            s.tanfovy, s.image_height, s.image_width, sh if sh_rest is None else (sh, sh_rest), s.sh_degree, s.campos,
+            s.prefiltered, s.debug)
+        ctx.raster_settings, ctx.num_rendered, ctx.exchange, ctx.split = s, R, exchange, sh_rest is not None
+        ctx.save_for_backward(means3D, scales, rotations, radii, sh, campos_views, geom, binning, img,
+                              *([sh_rest] if sh_rest is not None else []))
         ctx.mark_non_differentiable(radii, is_used)
         return color, radii, is_used
 
@@ -465,19 +480,20 @@ class _RasterizeGaussiansViewParallel(torch.autograd.Function):
     def backward(ctx, grad_out_color, _grad_radii, _grad_is_used):
         from . import _native as C
         s, ex = ctx.raster_settings, ctx.exchange
-        means3D, scales, rotations, radii, sh, campos_views, geom, binning, img = ctx.saved_tensors
+        means3D, scales, rotations, radii, sh, campos_views, geom, binning, img = ctx.saved_tensors[:9]
         if ex.layout == "records":
             # fresh tensors already: autograd keeps them as .grad without a copy
             g = ex.backward(C, s.bg, means3D, radii, scales, rotations, s.scale_modifier, s.viewmatrix, s.projmatrix,
-                            s.tanfovx, s.tanfovy, grad_out_color, sh, s.sh_degree, s.campos, campos_views, geom,
-                            ctx.num_rendered, binning, img)
-            return (g["means3D"], ex.local["means2D"], g["sh"], g["opacity"], g["scales"], g["rotations"], None, None, None)
+                            s.tanfovx, s.tanfovy, grad_out_color, (sh, ctx.saved_tensors[9]) if ctx.split else sh, s.sh_degree,
+                            s.campos, campos_views, geom, ctx.num_rendered, binning, img)
+            return (g["means3D"], ex.local["means2D"], g["sh"], g.get("sh_rest"), g["opacity"], g["scales"], g["rotations"],
+                    None, None, None)
         g = ex.backward(C, s.bg, means3D, radii, scales, rotations, s.scale_modifier, s.viewmatrix, s.projmatrix,
                         s.tanfovx, s.tanfovy, grad_out_color, sh, s.sh_degree, s.campos, campos_views, geom,
                         ctx.num_rendered, binning, img, sh_out=torch.empty_like(sh))
         # the exchange's buffers are reused next step: autograd gets its own tensors (copies of the small ones, a fresh
         # tensor for the SH gradient)
-        return (g["means3D"].clone(), ex.local["means2D"].clone(), g["sh"], g["opacity"].clone(), g["scales"].clone(),
+        return (g["means3D"].clone(), ex.local["means2D"].clone(), g["sh"], None, g["opacity"].clone(), g["scales"].clone(),
                 g["rotations"].clone(), None, None, None)
 
 
@@ -495,5 +511,8 @@ class ViewParallelRasterizer(torch.nn.Module):
         return self
 
     def forward(self, raster_settings, campos_views, means3D, means2D, opacities, shs, scales, rotations):
-        return _RasterizeGaussiansViewParallel.apply(means3D, means2D, shs, opacities, scales, rotations,
+        """shs: the concatenated [P,M,3] tensor, or the pair (features_dc [P,1,3], features_rest [P,15,3]) as the model
+        stores them (no 576 MB cat; the gradients come back per tensor)."""
+        sh, sh_rest = shs if isinstance(shs, (tuple, list)) else (shs, None)
+        return _RasterizeGaussiansViewParallel.apply(means3D, means2D, sh, sh_rest, opacities, scales, rotations,
                                                      raster_settings, campos_views, self.exchange)

@@ -263,8 +263,13 @@ def run_b200_arm(args):
     factored = n_gpus > 1 and args.exchange == "factored"
     arena = None if factored else dp.GradientArena(P, 16, dev)
     exchange = dp.FactoredExchange(P, 16, dev, transport=args.transport) if factored else None
-    if factored:
-        exchange_desc = (f"factored ({exchange.transport}" + (", NVSwitch multicast" if exchange._multicast else "") +
+    if factored and exchange.layout == "records":
+        exchange_desc = (f"records ({exchange.transport}" + (", NVSwitch multicast" if exchange._multicast else "") +
+                         "): the per-Gaussian backward stores a bit mask + 56 B per Gaussian with a non-zero gradient straight "
+                         "into every rank's double-buffered gather slots, one barrier, every rank adds the views in rank order "
+                         "(SH gradient rebuilt as basis x dL/dRGB); no all-reduce")
+    elif factored:
+        exchange_desc = (f"factored {exchange.layout} ({exchange.transport}" + (", NVSwitch multicast" if exchange._multicast else "") +
                          "): all-gather of the masked dL/dRGB (12 B/Gaussian/view) fused into its producer kernel, summed SH "
                          "gradient rebuilt per rank, two-shot all-reduce of the other 11 floats/Gaussian")
     else:
@@ -405,7 +410,11 @@ def run_b200_arm(args):
         "preprocess_bwd": visible * (531 - (192 if factored else 0)) + (P - visible) * (304 - (192 if factored else 0)),
         "bwd_zero": P * 36,
     }
-    if factored:
+    if factored and exchange.layout == "records":
+        # the push is part of preprocess_bwd; the combine writes only the rows some view touched (708 MB of zero fill runs on a
+        # side stream under render_bwd): charged the dense output it stands for, 59 floats per Gaussian
+        alg_bytes["dp_sh_grad_combine"] = P * 59 * 4
+    elif factored:
         # NVLink / HBM bytes of the exchange kernels per rank and step
         # read acc+clamp+radii, write own slot, receive the others: the DENSE figure (12 B per Gaussian and view); the sparse
         # layout moves 12 B per non-zero gradient + 0.25 B per Gaussian (parity.nonzero_color_grad_fraction_rank0)

@@ -161,18 +161,47 @@ int gs_dp_slab_all_reduce(void* stream, float* const* slab_ptrs, int n_ptrs, int
  * gs_dp_grad_record_combine: from V such slots (records + v * slot_stride, slot_stride >= gs_dp_slot_floats(P,
  *   GS_DP_RECORDS)) the gradients summed over the views in view order - bit-identical on every rank, and equal to adding the
  *   per-view outputs of gs_backward in that order: dL_dmeans3D [P][3], dL_dopacity [P], dL_dscales [P][3],
- *   dL_drotations [P][4], dL_dsh [P][M][3] (basis(dir_v) (x) dL_dRGB_v). Only rows some view touched are written:
+ *   dL_drotations [P][4], dL_dsh [P][M][3] (basis(dir_v) (x) dL_dRGB_v; with dL_dsh_rest non-NULL: dL_dsh [P][1][3] and
+ *   dL_dsh_rest [P][M-1][3], see the split SH entry points below). Only rows some view touched are written:
  *   outputs_are_zero != 0 promises the outputs hold zeros already (zero them off the critical path), 0 makes the call clear
  *   them first. V <= 32. */
+/* gs_backward_render that also records cleared_event (from gs_host_event_create; may be NULL) on the stream right after the
+ * accumulator clear, before the tile kernel: gs_stream_wait_event(side_stream, cleared_event) lets memory-bound side work
+ * (the zero fill of the records exchange's outputs) start under the compute-bound tile kernel instead of beside the clear. */
+int gs_backward_render_ev(void* stream, int P, unsigned int R, int W, int H, const float* background,
+                          const void* geom_ws, const void* binning_ws, const void* image_ws, const float* dL_dpix,
+                          void* scratch, void* cleared_event);
+int gs_stream_wait_event(void* stream, void* event);
 int gs_backward_geometry_push(void* stream, int P, int D, int M, int W, int H, const float* means3D, const float* shs,
-                              const float* scales, float scale_modifier, const float* rotations,
+                              const float* shs_rest, const float* scales, float scale_modifier, const float* rotations,
                               const float* viewmatrix, const float* projmatrix, const float* campos, float tan_fovx,
                               float tan_fovy, const int* radii, const void* geom_ws, const void* scratch,
                               float* dL_dmeans2D, float* const* dst_ptrs, int n_dst, int multicast, size_t slot_offset);
 int gs_dp_grad_record_combine(void* stream, int P, int D, int M, int V, const float* means3D,
                               const float* campos_views, const float* records, size_t slot_stride,
                               int outputs_are_zero, float* dL_dmeans3D, float* dL_dopacity, float* dL_dscales,
-                              float* dL_drotations, float* dL_dsh);
+                              float* dL_drotations, float* dL_dsh, float* dL_dsh_rest);
+
+/* Split SH tensors (additive). The model stores features_dc [P][1][3] and features_rest [P][15][3] apart and the
+ * reference concatenates them on every call of get_features (scene/gaussian_model_static.py:139-144: a 576 MB copy at
+ * P = 3M, and autograd splits the gradient again). These entry points read - and differentiate into - the two tensors as
+ * they lie: the same kernels, the same arithmetic instructions, bit-identical results to the concatenated layout.
+ * M is 16 (degree-3 storage); all four SH pointers 16-byte aligned. In gs_backward_geometry_push / gs_dp_grad_record_combine
+ * above, shs_rest / dL_dsh_rest non-NULL select the same layout (shs = features_dc, dL_dsh = its [P][1][3] gradient). */
+int gs_forward_preprocess_split_sh(void* stream, int P, int D, const float* means3D, const float* features_dc,
+                                   const float* features_rest, const float* opacities, const float* scales,
+                                   float scale_modifier, const float* rotations, const float* viewmatrix,
+                                   const float* projmatrix, const float* campos, int W, int H, float tan_fovx,
+                                   float tan_fovy, int prefiltered, int* radii, int* is_used, void* geom_ws,
+                                   unsigned int* num_rendered_host, void* count_ready_event);
+int gs_backward_geometry_split_sh(void* stream, int P, int D, int W, int H, const float* means3D,
+                                  const float* features_dc, const float* features_rest, const float* scales,
+                                  float scale_modifier, const float* rotations, const float* viewmatrix,
+                                  const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy,
+                                  const int* radii, const void* geom_ws, const void* scratch, float* dL_dmeans2D,
+                                  float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                                  float* dL_dfeatures_dc, float* dL_dfeatures_rest, float* dL_dscales,
+                                  float* dL_drotations);
 
 /* present[i] = (view * means3D[i]).z > 0.2 ; one byte per Gaussian (bool). */
 int gs_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix,

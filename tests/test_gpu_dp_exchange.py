@@ -317,3 +317,103 @@ def test_slab_all_reduce_single_device_two_buffers():
     torch.cuda.synchronize()
     assert helpers.bits_equal_count(a, want) == 0
     assert helpers.bits_equal_count(b, want) == 0
+
+
+@pytest.mark.parametrize("kind,P,W,H,degree,rad,fovx", [
+    ("cube", 20001, 250, 130, 3, 4.03, 0.6911),          # ragged last warp: the float-by-float tail of the split staging
+    ("cube", 5003, 96, 64, 1, 4.03, 0.6911),
+    ("cube", 5000, 96, 64, 0, 4.03, 0.6911),
+    ("cube", 4999, 96, 64, 2, 4.03, 0.6911),
+    ("garden", 200000, 800, 450, 3, 6.0, 1.2),
+])
+def test_split_sh_tensors_equal_the_concatenated_layout(kind, P, W, H, degree, rad, fovx):
+    """features_dc [P,1,3] / features_rest [P,15,3] read as they lie (gs_forward_preprocess_split_sh,
+    gs_backward_geometry_split_sh, and the records push / combine) give the same bits as the reference's
+    cat((features_dc, features_rest), dim=1) layout (scene/gaussian_model_static.py:139-144): image, radii, every gradient."""
+    C = native()
+    dev = torch.device("cuda:0")
+    s, cs, dLs = _views(kind, P, W, H, 2, degree, rad, fovx)
+    if s["shs"].shape[1] < 16:       # degree-3 storage with a lower active degree, as in the first 3000 training iterations
+        g = torch.Generator(device="cpu").manual_seed(11)
+        pad = torch.randn((P, 16 - s["shs"].shape[1], 3), generator=g).to(dev) * 0.1
+        s["shs"] = torch.cat((s["shs"], pad), 1).contiguous()
+    dc, rest = s["shs"][:, :1].contiguous(), s["shs"][:, 1:].contiguous()
+    e = torch.empty(0)
+    stride = (C.dp_slot_floats(P, "records") + 63) // 64 * 64
+    slots = {name: torch.zeros((2, stride), device=dev) for name in ("cat", "split")}
+    for v, (c, dL) in enumerate(zip(cs, dLs)):
+        fwd_cat = _forward(C, s, c, degree)
+        fwd_split = C.rasterize_gaussians(c["bg"], s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e,
+                                          c["viewmatrix"], c["projmatrix"], c["tanfovx"], c["tanfovy"], H, W, (dc, rest), degree,
+                                          c["campos"], False, False)
+        assert fwd_cat[0] == fwd_split[0]
+        assert helpers.bits_equal_count(fwd_cat[1], fwd_split[1]) == 0          # image
+        assert torch.equal(fwd_cat[2], fwd_split[2]) and torch.equal(fwd_cat[6], fwd_split[6])   # radii, is_used
+        R, _, radii, geom, binning, img, _ = fwd_split
+        scratch = C.backward_render(c["bg"], P, R, dL, geom, binning, img)
+        args = (s["means3D"], radii, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"], c["tanfovx"],
+                c["tanfovy"], H, W)
+        cat = dict(zip(NAMES, C.backward_geometry(*args, s["shs"], degree, c["campos"], geom, scratch)))
+        split = dict(zip(NAMES, C.backward_geometry(*args, (dc, rest), degree, c["campos"], geom, scratch)))
+        for n in NAMES:
+            if n != "sh":
+                assert helpers.bits_equal_count(split[n] + 0.0, cat[n] + 0.0) == 0, n
+        assert float(cat["sh"].abs().max()) > 0
+        assert split["sh"][0].shape == (P, 1, 3) and split["sh"][1].shape == (P, 15, 3)
+        assert helpers.bits_equal_count(torch.cat(split["sh"], 1) + 0.0, cat["sh"] + 0.0) == 0
+        # records: the same chunk records whichever layout the SH coefficients were read from
+        pargs = (s["means3D"], radii, s["scales"], s["rotations"], 1.0, c["viewmatrix"], c["projmatrix"], c["tanfovx"],
+                 c["tanfovy"], H, W)
+        C.backward_geometry_push(*pargs, s["shs"], degree, c["campos"], geom, scratch, [slots["cat"].data_ptr()], v * stride)
+        C.backward_geometry_push(*pargs, (dc, rest), degree, c["campos"], geom, scratch, [slots["split"].data_ptr()], v * stride)
+    torch.cuda.synchronize()
+    if P <= 20001:                                   # (the pad floats closing a chunk's run are not part of the record)
+        for v in range(2):
+            ra, rb = _decode_records(slots["cat"][v], P), _decode_records(slots["split"][v], P)
+            assert sorted(ra) == sorted(rb) and all((ra[i].view("i4") == rb[i].view("i4")).all() for i in ra)
+    campos = torch.stack([c["campos"] for c in cs])
+    whole = C.dp_grad_record_combine(s["means3D"], campos, slots["cat"], stride, degree, 16)
+    parts = C.dp_grad_record_combine(s["means3D"], campos, slots["split"], stride, degree, 16, split_sh=True)
+    assert parts["sh"].shape == (P, 1, 3) and parts["sh_rest"].shape == (P, 15, 3)
+    assert helpers.bits_equal_count(torch.cat((parts["sh"], parts["sh_rest"]), 1) + 0.0, whole["sh"] + 0.0) == 0
+    for n in ("means3D", "opacity", "scales", "rotations"):
+        assert helpers.bits_equal_count(parts[n] + 0.0, whole[n] + 0.0) == 0, n
+
+
+def test_split_sh_through_the_public_rasterizer():
+    """GaussianRasterizer(shs=(features_dc, features_rest)): gradients arrive on the two leaves, equal (up to the tile
+    backward's atomics) to those of the concatenated call; dp.ViewParallelRasterizer takes the pair as well."""
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, dp
+    P, W, H = 30000, 320, 200
+    s, cs, dLs = _views("cube", P, W, H, 1, 3, 4.03, 0.6911)
+    c, dL = cs[0], dLs[0]
+    st = GaussianRasterizationSettings(H, W, c["tanfovx"], c["tanfovy"], c["bg"], 1.0, c["viewmatrix"], c["projmatrix"], 3,
+                                       c["campos"], False, False)
+
+    def leaves():
+        return {k: s[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "scales", "rotations")}
+
+    a = leaves()
+    shs = s["shs"].clone().requires_grad_(True)
+    img_a = GaussianRasterizer(st)(means3D=a["means3D"], means2D=torch.zeros_like(a["means3D"]), opacities=a["opacities"], shs=shs,
+                                   scales=a["scales"], rotations=a["rotations"])[0]
+    (img_a * dL).sum().backward()
+    results = {}
+    for name in ("single", "view_parallel"):
+        b = leaves()
+        dc, rest = s["shs"][:, :1].clone().requires_grad_(True), s["shs"][:, 1:].clone().requires_grad_(True)
+        if name == "single":
+            img_b = GaussianRasterizer(st)(means3D=b["means3D"], means2D=torch.zeros_like(b["means3D"]), opacities=b["opacities"],
+                                           shs=(dc, rest), scales=b["scales"], rotations=b["rotations"])[0]
+        else:
+            vp = dp.ViewParallelRasterizer(P, 16, torch.device("cuda:0"))
+            img_b = vp(st, c["campos"].view(1, 3), b["means3D"], torch.zeros_like(b["means3D"]), b["opacities"], (dc, rest),
+                       b["scales"], b["rotations"])[0]
+        assert helpers.bits_equal_count(img_a, img_b) == 0
+        (img_b * dL).sum().backward()
+        assert dc.grad.shape == (P, 1, 3) and rest.grad.shape == (P, 15, 3)
+        assert helpers.rel_l2(torch.cat((dc.grad, rest.grad), 1), shs.grad) < 2e-5, name
+        for k in b:
+            assert helpers.rel_l2(b[k].grad, a[k].grad) < 2e-5, (name, k)
+        results[name] = True
+    assert len(results) == 2

@@ -314,8 +314,8 @@ def main():
                 bd["geometry_with_sh_dense_outputs"] = timed(lambda: C.backward_geometry(
                     s["means3D"], radii, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"], c["tanfovx"],
                     c["tanfovy"], H, W, s["shs"], 3, c["campos"], geom, scratch, out_buffers=arena.backward_buffers()))
-                outs = ex._fresh_zeroed_outputs()
-                torch.cuda.current_stream().wait_event(ex._ev_zero)
+                flat_out, outs = ex._fresh_outputs()
+                flat_out.zero_()
                 bd["combine_prezeroed"] = timed(lambda: C.dp_grad_record_combine(s["means3D"], campos_views, own, ex.slot_stride, 3, 16,
                                                                                  outs=outs, outputs_are_zero=True))
                 bd["zero_fill_708MB_at_3M"] = timed(lambda: outs["sh"].zero_())
