@@ -1016,7 +1016,8 @@ def run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_g
     from diff_gaussian_rasterization.optim import FusedAdam
     from diff_gaussian_rasterization.activations import activate
 
-    lrs = {"xyz": 1.6e-4, "shs": 2.5e-3, "opacity": 0.05, "scaling": 5e-3, "rotation": 1e-3}   # arguments/__init__.py defaults
+    # arguments/__init__.py defaults; features_rest trains at feature_lr / 20 (scene/gaussian_model_static.py:186-187)
+    lrs = {"xyz": 1.6e-4, "f_dc": 2.5e-3, "f_rest": 2.5e-3 / 20.0, "opacity": 0.05, "scaling": 5e-3, "rotation": 1e-3}
     lam, opacity_reg, scale_reg, noise_lr = 0.2, 0.01, 0.01, 5e5
     gt = torch.rand((3, H, W), generator=gen).to(dev)
     g1 = torch.tensor([math.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)])
@@ -1041,8 +1042,10 @@ def run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_g
         noise = torch.randn_like(raw["xyz"]) * (1 / (1 + torch.exp(-100 * ((1 - torch.sigmoid(raw["opacity"])) - 0.995)))) * noise_lr * xyz_lr
         raw["xyz"].add_(torch.bmm(cov, noise.unsqueeze(-1)).squeeze(-1))
 
-    def make(fused):
-        raw = {"xyz": s["means3D"].clone(), "shs": s["shs"].clone(), "opacity": torch.logit(s["opacities"].clamp(1e-4, 1 - 1e-4)),
+    def make(fused, split_sh):
+        # the model's own parameter set: features_dc and features_rest are separate tensors (gaussian_model_static.py:175-176)
+        raw = {"xyz": s["means3D"].clone(), "f_dc": s["shs"][:, :1].clone(), "f_rest": s["shs"][:, 1:].clone(),
+               "opacity": torch.logit(s["opacities"].clamp(1e-4, 1 - 1e-4)),
                "scaling": torch.log(s["scales"]), "rotation": s["rotations"].clone()}
         raw = {k: torch.nn.Parameter(v) for k, v in raw.items()}
         opt_cls = FusedAdam if fused else torch.optim.Adam
@@ -1066,11 +1069,14 @@ def run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_g
                 opacity, scaling, rotation = torch.sigmoid(raw["opacity"]), torch.exp(raw["scaling"]), F.normalize(raw["rotation"])
                 reg = None
             means2D = torch.zeros_like(raw["xyz"], requires_grad=True)
+            # get_features (gaussian_model_static.py:139-144) concatenates the two tensors on every call; the split path hands
+            # them to the rasterizer as they lie
+            shs = (raw["f_dc"], raw["f_rest"]) if split_sh else torch.cat((raw["f_dc"], raw["f_rest"]), dim=1)
             if vp is not None:
                 cv = torch.stack([torch.as_tensor(cams_np[(i * n_gpus + r) % len(cams_np)]["campos"]) for r in range(n_gpus)]).to(dev)
-                image = vp(settings, cv, raw["xyz"], means2D, opacity, raw["shs"], scaling, rotation)[0]
+                image = vp(settings, cv, raw["xyz"], means2D, opacity, shs, scaling, rotation)[0]
             else:
-                image = GaussianRasterizer(settings)(means3D=raw["xyz"], means2D=means2D, shs=raw["shs"], opacities=opacity,
+                image = GaussianRasterizer(settings)(means3D=raw["xyz"], means2D=means2D, shs=shs, opacities=opacity,
                                                      scales=scaling, rotations=rotation)[0]
             photo = fused_loss.photometric_loss(image, gt, lam) if fused else torch_photometric(image)
             if reg is None:   # train_static.py:99-100
@@ -1089,10 +1095,11 @@ def run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_g
         return step
 
     out = {}
-    for name, fused in (("fused", True), ("torch_glue", False)):
-        if not fused and n_gpus > 1:
+    split_ok = exchange is None or exchange.layout == "records"
+    for name, fused, split_sh in (("fused", True, split_ok), ("fused_cat_sh", True, False), ("torch_glue", False, False)):
+        if name != "fused" and n_gpus > 1:
             continue
-        step = make(fused)
+        step = make(fused, split_sh)
         for i in range(Wm):
             step(i)
         barrier()
@@ -1110,8 +1117,10 @@ def run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_g
         del step
         torch.cuda.empty_cache()
     out["what"] = ("one full training iteration per view as train_static.py:86-140 (activations, render, L1+SSIM+regularisers, backward"
-                   + (", cross-rank gradient sum" if n_gpus > 1 else "") + ", Adam, MCMC noise) at the bench workload; 'fused' uses csrc/activations.cu, csrc/loss.cu, "
-                   "csrc/optim.cu and gs_add_noise, 'torch_glue' the reference's torch ops around the same rasterizer")
+                   + (", cross-rank gradient sum" if n_gpus > 1 else "") + ", Adam, MCMC noise) at the bench workload, on the model's own six parameter "
+                   "tensors (features_dc / features_rest separate); 'fused' uses csrc/activations.cu, csrc/loss.cu, csrc/optim.cu, gs_add_noise "
+                   "and hands the two SH tensors to the rasterizer as they lie, 'fused_cat_sh' the same with get_features' torch.cat, "
+                   "'torch_glue' the reference's torch ops around the same rasterizer")
     return out
 
 
