@@ -39,7 +39,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
     __shared__ __align__(16) uint32_t s_inst[kInstStages][CH + kInstPad];
     __shared__ __align__(8) uint64_t s_inst_full[kInstStages];
     __shared__ __align__(8) uint64_t s_rec_full[RS];
-    __shared__ int s_used[RS][CH];  // id+1 of splats blended by some pixel, 0 otherwise
+    __shared__ int s_used[RS][CH];  // id of splats blended by some pixel, -1 otherwise
     __shared__ uint32_t s_mask[kTwoLevel ? kWords : 1];
     __shared__ uint8_t s_cidx[kTwoLevel ? GS_TILE_PIX / 32 : 1][kTwoLevel ? CH : 1];   // per warp: compacted record indices
     __shared__ uint32_t s_maxc;
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
     const int n_total = (int)(range.y - range.x);
     const int nchunks = (n_total + CH - 1) / CH;
 
-    for (int i = tid; i < RS * CH; i += GS_TILE_PIX) (&s_used[0][0])[i] = 0;
+    for (int i = tid; i < RS * CH; i += GS_TILE_PIX) (&s_used[0][0])[i] = -1;
     if (tid == 0) {
         s_maxc = 0;
         stager_init<CH, RS>(s_inst_full, s_rec_full);
@@ -74,9 +74,9 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
         const int s = c % RS;
         for (int i = tid; i < CH; i += GS_TILE_PIX) {
             const int u = s_used[s][i];
-            if (u) {
-                p.is_used[u - 1] = 1;
-                s_used[s][i] = 0;
+            if (u >= 0) {
+                p.is_used[u] = 1;
+                s_used[s][i] = -1;
             }
         }
     };
@@ -88,23 +88,25 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
     float T = 1.0f;
     uint32_t last_contributor = 0;
     float C[3] = {0.f, 0.f, 0.f};
-    bool done = !inside;
+    // `gate` is the pixel's "done" state folded into the alpha-threshold test: -inf while the pixel still blends (the test
+    // is then exactly the record's own `power < thr`), +inf once it has saturated (every record fails the test).
+    float gate = inside ? -INFINITY : INFINITY;
+#define done (gate > 0.0f)
     const uint32_t lt_mask = (1u << lane) - 1u;
 
     // Blend record j of the chunk into this lane's pixel (the reference's expression tree, forward.cu:330-358).
     auto blend = [&](const float4* __restrict__ rec, const int s, const int c, const int j) {
-        if (done) return;
         const float4 q0 = rec[3 * j];      // x, y, A, B
         const float4 q1 = rec[3 * j + 1];  // C, opacity, thr, id
         const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
         const float power = -0.5f * (q0.z * d.x * d.x + q1.x * d.y * d.y) - q0.w * d.x * d.y;
         if (power > 0.0f) return;
-        if (power < q1.z) return;  // cannot reach alpha >= 1/255 (see preprocess_fwd_kernel)
+        if (power < fmaxf(q1.z, gate)) return;  // cannot reach alpha >= 1/255 (see preprocess_fwd_kernel), or pixel done
         const float alpha = min(0.99f, q1.y * exp(power));
         if (alpha < 1.0f / 255.0f) return;
         const float test_T = T * (1 - alpha);
         if (test_T < 0.0001f) {
-            done = true;
+            asm volatile("mov.f32 %0, 0f7f800000;" : "=f"(gate));   // +inf; volatile: not to be hoisted and undone on the blend path
             return;
         }
         const float4 q2 = rec[3 * j + 2];  // r, g, b
@@ -113,7 +115,7 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
         C[2] += q2.z * alpha * T;
         T = test_T;
         last_contributor = (uint32_t)(c * CH + j + 1);
-        s_used[s][j] = __float_as_int(q1.w) + 1;
+        s_used[s][j] = __float_as_int(q1.w);
         if (kCount) ++cnt[3];
     };
 
@@ -223,6 +225,8 @@ __global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwd
         }
     }
 }
+
+#undef done
 
 int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream) {
     if (tiles <= 0) return GS_OK;
