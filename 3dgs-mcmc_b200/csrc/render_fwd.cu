@@ -33,7 +33,7 @@ namespace gs {
 // Level 2: every warp compacts the bitmap into a list of record indices (list order preserved) and runs its patch test
 // only on those. Nothing that can contribute is ever dropped, so image / final_T / n_contrib / is_used are unchanged.
 template <int CH, int RS, int GA, bool kTwoLevel, bool kCount = false>
-__global__ void __launch_bounds__(GS_TILE_PIX) render_fwd_kernel(const RenderFwdParams p) {
+__global__ void __launch_bounds__(GS_TILE_PIX, 6) render_fwd_kernel(const RenderFwdParams p) {
     constexpr int kWords = CH / 32;              // survivor bitmap words per chunk
     __shared__ __align__(128) SplatRec s_rec[RS][CH];
     __shared__ __align__(16) uint32_t s_inst[kInstStages][CH + kInstPad];
