@@ -687,25 +687,33 @@ struct BinKey<0> { using type = uint64_t; };
 // PASS 0: u64 keys (depth_bits << 32 | idx), digit = BITS bits of the upper word at p.shift      (depth ordering)
 // PASS 1: slots expanded from the emission table, digit = low BITS bits of the tile id; writes (high digit << kshift) | idx
 // PASS 2: those 32-bit words, digit = word >> kshift (the high tile digit); writes the Gaussian index
-template <int PASS, int BITS, int MINB = 4>
-__global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const BinScatterParams p) {
+//
+// Stable in-warp ranks (kAtomicPeers, the default): every lane ORs its lane bit into a per-warp, per-digit mask word in shared
+// memory (ATOMS.OR: one instruction whatever the number of digit bits, and independent of the order in which the hardware
+// resolves lanes that hit the same word), reads the word back - that IS the set of lanes holding the same digit - and the
+// group's lowest lane advances the digit's running count and clears the word. ~15 instructions per slot against ~55 for
+// the BITS ballots + leader election of peer_mask<BITS> (kept as the other template branch; GS_BIN_RANK=ballot selects it).
+template <int PASS, int BITS, bool kAtomicPeers, bool kFull>
+GS_DEV void bin_scatter_body(const BinScatterParams& p, typename BinKey<PASS>::type* __restrict__ s_keys, uint8_t* __restrict__ s_dig,
+                             uint32_t (*s_hist)[256], uint32_t* __restrict__ s_gbase, uint32_t* __restrict__ s_scan) {
     using Key = typename BinKey<PASS>::type;
-    __shared__ __align__(16) Key s_keys[kBinTile];                   // 32 / 16 KB (pass 1 first uses it as u16 owner[kBinTile])
-    __shared__ uint8_t s_dig[PASS == 1 ? kBinTile : 16];             // pass 1: the low digit travels beside the word, not in it
-    __shared__ uint32_t s_hist[kBinThreads / 32][256];               // per-warp digit counts -> block positions
-    __shared__ uint32_t s_gbase[256];                                // global position of slot 0 of each digit's run
-    __shared__ uint32_t s_scan[33];
+    // per-warp peer masks [warps][256]: s_keys is idle while the ranks are formed (pass 1: its first 8 KB are the owner
+    // table, the masks take the second 8 KB)
+    uint32_t* const s_peer = reinterpret_cast<uint32_t*>(s_keys) + (PASS == 1 ? kBinTile / 2 : 0);
+    static_assert(sizeof(Key) * kBinTile >= (PASS == 1 ? 8192 : 0) + (kBinThreads / 32) * 256 * 4, "peer masks must fit in s_keys");
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int bins = 1 << BITS;
     constexpr uint32_t dmask = (uint32_t)bins - 1u;
     for (int i = tid; i < (kBinThreads / 32) * 256; i += kBinThreads) (&s_hist[0][0])[i] = 0;
+    if (kAtomicPeers)
+        for (int i = tid; i < (kBinThreads / 32) * 256; i += kBinThreads) s_peer[i] = 0;
     if (PASS == 1)
         for (int i = tid; i < kBinTile / 8; i += kBinThreads) reinterpret_cast<uint4*>(s_keys)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
     const uint32_t tile = blockIdx.x;
     const uint32_t slot_begin = tile * (uint32_t)kBinTile;
-    const uint32_t tile_n = min((uint32_t)kBinTile, p.n - slot_begin);
+    const uint32_t tile_n = kFull ? (uint32_t)kBinTile : min((uint32_t)kBinTile, p.n - slot_begin);
     const uint32_t warp_base = warp * (32 * kBinItems) + lane;   // item i of this thread is slot warp_base + 32 i
 
     // ---- 1. keys into registers, warp-striped; dig[k >> 2] byte (k & 3) = digit of item k ----
@@ -752,7 +760,7 @@ __global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const Bi
         for (int i = 0; i < kBinItems; ++i) {
             const uint32_t e = warp_base + i * 32;
             key[i] = 0u;
-            if (e < tile_n) {
+            if (kFull || e < tile_n) {
                 const uint4 E = __ldg(p.emit + r0 + s_owner[e]);
                 const uint32_t t = slot_begin + e - E.w, w = E.z & 0xffffu;
                 const uint32_t ty = div_small(t, w, rcp_small(w));
@@ -768,10 +776,10 @@ __global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const Bi
             const uint32_t e = warp_base + i * 32;
             uint32_t d = 0u;
             if (PASS == 0) {
-                key[i] = e < tile_n ? (Key)p.keys_in[(size_t)slot_begin + e] : (Key)~0ull;
+                key[i] = (kFull || e < tile_n) ? (Key)p.keys_in[(size_t)slot_begin + e] : (Key)~0ull;
                 d = (uint32_t)((uint64_t)key[i] >> (32 + p.shift)) & dmask;
             } else {
-                key[i] = e < tile_n ? (Key)p.keys32_in[(size_t)slot_begin + e] : (Key)0u;
+                key[i] = (kFull || e < tile_n) ? (Key)p.keys32_in[(size_t)slot_begin + e] : (Key)0u;
                 d = (uint32_t)key[i] >> p.kshift;
             }
             dig[i >> 2] |= (d & 0xffu) << (8 * (i & 3));
@@ -783,20 +791,46 @@ __global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const Bi
     const uint32_t lt_mask = (1u << lane) - 1u;
     uint16_t rank[kBinItems];
     uint32_t* const wh = s_hist[warp];
+    if (kAtomicPeers) {
+        // same 256-word stride per warp as s_hist: a digit's mask and its running count sit at a constant distance
+        const ptrdiff_t peer_off = (s_peer + warp * 256) - wh;
+        const uint32_t lane_bit = 1u << lane;
 #pragma unroll
-    for (int k = 0; k < kBinItems; ++k) {
-        const bool valid = warp_base + k * 32 < tile_n;
-        const uint32_t d = (dig[k >> 2] >> (8 * (k & 3))) & 0xffu;   // invalid slots are masked out below
-        const uint32_t peers = peer_mask<BITS>(d) & __ballot_sync(0xffffffffu, valid);
-        const int leader = __ffs(peers) - 1;
-        uint32_t old = 0;
-        if (valid && lane == leader) {
-            old = wh[d];
-            wh[d] = old + (uint32_t)__popc(peers);
+        for (int k = 0; k < kBinItems; ++k) {
+            const bool valid = kFull || warp_base + k * 32 < tile_n;
+            uint32_t* const hp = wh + ((dig[k >> 2] >> (8 * (k & 3))) & 0xffu);
+            if (valid) atomicOr(hp + peer_off, lane_bit);
+            __syncwarp();
+            uint32_t peers = 0u, old = 0u;
+            if (valid) {
+                peers = hp[peer_off];
+                old = hp[0];
+            }
+            __syncwarp();
+            const uint32_t before = peers & lt_mask;
+            if (valid && before == 0u) {   // lowest lane of the group
+                hp[0] = old + (uint32_t)__popc(peers);
+                hp[peer_off] = 0u;
+            }
+            rank[k] = (uint16_t)(old + __popc(before));
+            __syncwarp();
         }
-        old = __shfl_sync(0xffffffffu, old, leader & 31);
-        rank[k] = (uint16_t)(old + __popc(peers & lt_mask));
-        __syncwarp();
+    } else {
+#pragma unroll
+        for (int k = 0; k < kBinItems; ++k) {
+            const bool valid = kFull || warp_base + k * 32 < tile_n;
+            const uint32_t d = (dig[k >> 2] >> (8 * (k & 3))) & 0xffu;   // invalid slots are masked out below
+            const uint32_t peers = peer_mask<BITS>(d) & __ballot_sync(0xffffffffu, valid);
+            const int leader = __ffs(peers) - 1;
+            uint32_t old = 0;
+            if (valid && lane == leader) {
+                old = wh[d];
+                wh[d] = old + (uint32_t)__popc(peers);
+            }
+            old = __shfl_sync(0xffffffffu, old, leader & 31);
+            rank[k] = (uint16_t)(old + __popc(peers & lt_mask));
+            __syncwarp();
+        }
     }
     __syncthreads();   // (also: every read of s_owner is done, s_keys may be overwritten)
 
@@ -827,7 +861,7 @@ __global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const Bi
 #pragma unroll
     for (int i = 0; i < kBinItems; ++i) {
         const uint32_t e = warp_base + i * 32;
-        if (e < tile_n) {
+        if (kFull || e < tile_n) {
             const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
             const uint32_t at = s_hist[warp][d] + rank[i];
             s_keys[at] = key[i];
@@ -839,7 +873,7 @@ __global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const Bi
 #pragma unroll
     for (int i = 0; i < kBinItems; ++i) {
         const uint32_t s = i * kBinThreads + tid;
-        if (s < tile_n) {
+        if (kFull || s < tile_n) {
             const Key k = s_keys[s];
             uint32_t d;
             if (PASS == 0) d = (uint32_t)((uint64_t)k >> (32 + p.shift)) & dmask;
@@ -851,6 +885,19 @@ __global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const Bi
             else p.ids_out[pos] = (uint32_t)k & idmask;
         }
     }
+}
+
+// kFull: every slot of the block exists (all blocks but the last) - no validity predicates anywhere.
+template <int PASS, int BITS, int MINB = 4, bool kAtomicPeers = true>
+__global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const BinScatterParams p) {
+    using Key = typename BinKey<PASS>::type;
+    __shared__ __align__(16) Key s_keys[kBinTile];                   // 32 / 16 KB (pass 1 first uses it as u16 owner[kBinTile])
+    __shared__ uint8_t s_dig[PASS == 1 ? kBinTile : 16];             // pass 1: the low digit travels beside the word, not in it
+    __shared__ uint32_t s_hist[kBinThreads / 32][256];               // per-warp digit counts -> block positions
+    __shared__ uint32_t s_gbase[256];                                // global position of slot 0 of each digit's run
+    __shared__ uint32_t s_scan[33];
+    if ((blockIdx.x + 1u) * (uint32_t)kBinTile <= p.n) bin_scatter_body<PASS, BITS, kAtomicPeers, true>(p, s_keys, s_dig, s_hist, s_gbase, s_scan);
+    else bin_scatter_body<PASS, BITS, kAtomicPeers, false>(p, s_keys, s_dig, s_hist, s_gbase, s_scan);
 }
 
 // hist[d][b] = number of keys of block b whose digit (key >> shift) & (2^bits - 1) is d. Generic counterpart of
@@ -882,7 +929,13 @@ template <int PASS, int BITS>
 static void launch_scatter(const BinScatterParams& sp, uint32_t nb, cudaStream_t stream) {
     // GS_BIN_MINB=5 (measurement): 5 resident CTAs per SM at 48 registers (more spills) instead of 4 at 64
     static const int minb = [] { const char* e = getenv("GS_BIN_MINB"); return e ? atoi(e) : 4; }();
-    if (PASS != 0 && minb == 5) bin_scatter_kernel<PASS, BITS, 5><<<nb, kBinThreads, 0, stream>>>(sp);
+    // GS_BIN_RANK=ballot (measurement): in-warp ranks from BITS ballots instead of the shared-memory peer masks. The depth
+    // ordering (pass 0) always uses ballots: its upper digits repeat heavily inside a warp (a handful of exponents), and lanes
+    // that hit the same mask word serialise in ATOMS (measured 24 -> 32 us per pass with the masks).
+    static const bool ballot = [] { const char* e = getenv("GS_BIN_RANK"); return e && e[0] == 'b'; }();
+    if (ballot || PASS == 0) bin_scatter_kernel<PASS, BITS, 4, false><<<nb, kBinThreads, 0, stream>>>(sp);
+    else if (minb == 5) bin_scatter_kernel<PASS, BITS, 5><<<nb, kBinThreads, 0, stream>>>(sp);
+    else if (minb == 3) bin_scatter_kernel<PASS, BITS, 3><<<nb, kBinThreads, 0, stream>>>(sp);
     else bin_scatter_kernel<PASS, BITS, 4><<<nb, kBinThreads, 0, stream>>>(sp);
 }
 template <int PASS>
