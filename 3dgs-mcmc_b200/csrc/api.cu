@@ -167,10 +167,10 @@ static int forward_preprocess_impl(void* stream_, int P, int D, int M, const flo
         GS_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, g.num_rendered, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
     if (count_ready_event) GS_CUDA_TRY(cudaEventRecord((cudaEvent_t)count_ready_event, stream));
     // Depth order of the Gaussians: stable sort of (depth_bits << 32 | idx) on the depth field.
-    rc = launch_depth_sort(g.dkeys_a, g.dkeys_b, (uint32_t)P, reinterpret_cast<uint32_t*>(g.dsort_scratch), stream);
+    rc = launch_depth_sort(g.dkeys_a, g.dkeys_b, (uint32_t)P, reinterpret_cast<uint32_t*>(g.dsort_scratch), g.rect, g.emit, stream);
     if (rc) return rc;
     prof_mark(stream, ST_DEPTH_SORT);
-    rc = launch_inclusive_scan(g.rect, g.dkeys_a, P, g.point_offsets, g.emit, g.scan_block_sums, stream);
+    rc = launch_inclusive_scan(P, g.point_offsets, g.emit, g.scan_block_sums, stream);
     if (rc) return rc;
     prof_mark(stream, ST_SCAN);
     count_launches(1 + 3 * kDepthSortPasses + 3);

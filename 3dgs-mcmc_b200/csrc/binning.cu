@@ -62,13 +62,14 @@ GS_DEV uint32_t block_excl_scan(uint32_t v, uint32_t* smem_warp, uint32_t* total
 // ------------------------------------------------------------------------------------------------
 // Inclusive scan of the per-Gaussian tile counts taken in depth order:
 //     out[r] = sum_{r' <= r} tiles(order[r'] & 0xffffffff),  tiles = w * h of the Gaussian's tile rectangle.
-// Three small kernels: block sums -> scan of block sums -> apply. The apply kernel also writes the
-// depth-ordered emission table the first binning pass expands: (idx, x0 | y0 << 16, w | h << 16, first slot).
+// Three small kernels: block sums -> scan of block sums -> apply, all streaming over the depth-ordered emission table
+// (idx, x0 | y0 << 16, w | h << 16, tile count) that the LAST pass of the depth sort wrote while it had every key's final
+// position in hand (one random gather of the rectangle per Gaussian, instead of one in each of two scan kernels); the apply
+// kernel replaces the count by the first emission slot: the table the first binning pass expands.
 // ------------------------------------------------------------------------------------------------
 GS_DEV uint32_t rect_tiles(const uint2 rc) { return (rc.y & 0xffffu) * (rc.y >> 16); }
 
-__global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uint2* __restrict__ rect,
-                                                                       const uint64_t* __restrict__ order, int n,
+__global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uint4* __restrict__ emit, int n,
                                                                        uint32_t* __restrict__ block_sums) {
     __shared__ uint32_t sw[33];
     const size_t base = (size_t)blockIdx.x * kScanBlock;
@@ -76,7 +77,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uin
 #pragma unroll
     for (int i = 0; i < kScanItems; ++i) {
         const size_t k = base + (size_t)i * kScanThreads + threadIdx.x;
-        if (k < (size_t)n) s += rect_tiles(rect[(uint32_t)order[k]]);
+        if (k < (size_t)n) s += emit[k].w;
     }
     uint32_t total;
     block_excl_scan(s, sw, &total);
@@ -97,46 +98,48 @@ __global__ void __launch_bounds__(1024) scan_spine_kernel(uint32_t* __restrict__
     }
 }
 
-__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(const uint2* __restrict__ rect,
-                                                                  const uint64_t* __restrict__ order, int n,
-                                                                  const uint32_t* __restrict__ block_offsets,
+// emit[r].w: tile count in, first emission slot out; out[r] = first slot of rank r + 1.
+// Warp w of a block owns 256 consecutive entries and walks them 32 at a time (lane-consecutive 16-byte loads and stores:
+// the table moves as whole, coalesced uint4s), carrying the running sum from round to round.
+__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(int n, const uint32_t* __restrict__ block_offsets,
                                                                   uint32_t* __restrict__ out, uint4* __restrict__ emit) {
-    __shared__ uint32_t sw[33];
-    // Blocked arrangement: thread t owns items [t*8, t*8+8) of the block so the scan order is the list order.
-    const size_t base = (size_t)blockIdx.x * kScanBlock + (size_t)threadIdx.x * kScanItems;
-    uint32_t v[kScanItems], idx[kScanItems];
-    uint2 rc[kScanItems];
-    uint32_t s = 0;
+    __shared__ uint32_t sw[kScanThreads / 32];
+    static_assert(kScanItems * 32 * (kScanThreads / 32) == kScanBlock, "one warp per kScanItems * 32 entries");
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t base = (size_t)blockIdx.x * kScanBlock + (size_t)warp * (kScanItems * 32) + lane;
+    uint4 E[kScanItems];
+    uint32_t excl[kScanItems];
+    uint32_t carry = 0;
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-        idx[i] = 0;
-        rc[i] = make_uint2(0u, 0u);
-        if (base + i < (size_t)n) {
-            idx[i] = (uint32_t)order[base + i];
-            rc[i] = rect[idx[i]];
-        }
-        v[i] = rect_tiles(rc[i]);
-        s += v[i];
+    for (int r = 0; r < kScanItems; ++r) E[r] = base + r * 32 < (size_t)n ? emit[base + r * 32] : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+    for (int r = 0; r < kScanItems; ++r) {
+        const uint32_t incl = warp_incl_scan(E[r].w, lane);
+        excl[r] = carry + incl - E[r].w;
+        carry += __shfl_sync(0xffffffffu, incl, 31);
     }
-    uint32_t total;
-    uint32_t run = block_excl_scan(s, sw, &total) + block_offsets[blockIdx.x];
+    if (lane == 0) sw[warp] = carry;
+    __syncthreads();
+    uint32_t woff = block_offsets[blockIdx.x];
+    for (int w = 0; w < warp; ++w) woff += sw[w];
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-        if (base + i < (size_t)n) {
-            emit[base + i] = make_uint4(idx[i], rc[i].x, rc[i].y, run);
-            out[base + i] = run + v[i];
+    for (int r = 0; r < kScanItems; ++r) {
+        if (base + r * 32 < (size_t)n) {
+            const uint32_t run = woff + excl[r], v = E[r].w;
+            E[r].w = run;
+            emit[base + r * 32] = E[r];
+            out[base + r * 32] = run + v;
         }
-        run += v[i];
     }
 }
 
-int launch_inclusive_scan(const uint2* rect, const uint64_t* order, int n, uint32_t* out, uint4* emit, uint32_t* block_sums,
-                          cudaStream_t stream) {
+// emit: the depth-ordered table (idx, x0 | y0 << 16, w | h << 16, tile count) written by the last pass of launch_depth_sort.
+int launch_inclusive_scan(int n, uint32_t* out, uint4* emit, uint32_t* block_sums, cudaStream_t stream) {
     if (n <= 0) return GS_OK;
     const int nb = (n + kScanBlock - 1) / kScanBlock;
-    scan_block_sums_kernel<<<nb, kScanThreads, 0, stream>>>(rect, order, n, block_sums);
+    scan_block_sums_kernel<<<nb, kScanThreads, 0, stream>>>(emit, n, block_sums);
     scan_spine_kernel<<<1, 1024, 0, stream>>>(block_sums, nb);
-    scan_apply_kernel<<<nb, kScanThreads, 0, stream>>>(rect, order, n, block_sums, out, emit);
+    scan_apply_kernel<<<nb, kScanThreads, 0, stream>>>(n, block_sums, out, emit);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
@@ -620,26 +623,42 @@ __global__ void __launch_bounds__(kBinThreads) bin_count2_kernel(const uint32_t*
     // The keys are sorted by the low digit: the block holds low digits lmin..lmax only.
     const uint32_t lmin = s_lo[0], span = s_lo[1] - lmin + 1u;
     const bool compact = span <= (uint32_t)kTileSpan;
-#pragma unroll 4
+    const bool single = span == 1u;   // the usual case: a low digit's run is ~R / 2^bits1 keys, far longer than a block
+    // all 16 loads in flight before the first shared-memory atomic
+    uint32_t hv[kBinItems];
+#pragma unroll
     for (int i = 0; i < kBinItems; ++i) {
         const uint32_t e = i * kBinThreads + tid;
-        if (e < n) {
-            const uint32_t pos = slot_begin + e;
-            const uint32_t hi = keys[(size_t)pos] >> kshift;
-            if (compact) {
-                uint32_t l = 0;
+        hv[i] = e < n ? keys[(size_t)slot_begin + e] >> kshift : 0u;
+    }
+    if (single) {
+        // one low digit in the whole block: the rows of s_t serve as per-warp copies of the high-digit histogram
+        static_assert(kTileSpan == kBinThreads / 32, "per-warp copies use one row of s_t each");
 #pragma unroll
-                for (int k = 1; k < kTileSpan; ++k) l += (k < (int)span && s_start[lmin + k] <= pos) ? 1u : 0u;
-                atomicAdd(&s_t[l][hi], 1u);
-            } else {
-                // many short runs in one block (tiny scenes): binary search for the run that holds pos
-                uint32_t lo_d = lmin, hi_d = lmin + span - 1u;
-                while (lo_d < hi_d) {
-                    const uint32_t mid = (lo_d + hi_d + 1u) >> 1;
-                    if (s_start[mid] <= pos) lo_d = mid; else hi_d = mid - 1u;
+        for (int i = 0; i < kBinItems; ++i)
+            if (i * kBinThreads + tid < (int)n) atomicAdd(&s_t[tid >> 5][hv[i]], 1u);
+    } else {
+#pragma unroll 4
+        for (int i = 0; i < kBinItems; ++i) {
+            const uint32_t e = i * kBinThreads + tid;
+            if (e < n) {
+                const uint32_t pos = slot_begin + e;
+                const uint32_t hi = hv[i];
+                if (compact) {
+                    uint32_t l = 0;
+#pragma unroll
+                    for (int k = 1; k < kTileSpan; ++k) l += (k < (int)span && s_start[lmin + k] <= pos) ? 1u : 0u;
+                    atomicAdd(&s_t[l][hi], 1u);
+                } else {
+                    // many short runs in one block (tiny scenes): binary search for the run that holds pos
+                    uint32_t lo_d = lmin, hi_d = lmin + span - 1u;
+                    while (lo_d < hi_d) {
+                        const uint32_t mid = (lo_d + hi_d + 1u) >> 1;
+                        if (s_start[mid] <= pos) lo_d = mid; else hi_d = mid - 1u;
+                    }
+                    atomicAdd(&s_t[0][hi], 1u);
+                    atomicAdd(tile_counts + ((hi << bits1) | lo_d), 1u);
                 }
-                atomicAdd(&s_t[0][hi], 1u);
-                atomicAdd(tile_counts + ((hi << bits1) | lo_d), 1u);
             }
         }
     }
@@ -647,11 +666,17 @@ __global__ void __launch_bounds__(kBinThreads) bin_count2_kernel(const uint32_t*
     const int bins2 = 1 << bits2;
     if (tid < bins2) {
         uint32_t c = 0;
-        const int rows = compact ? (int)span : 1;
-        for (int l = 0; l < rows; ++l) {
-            const uint32_t t = s_t[l][tid];
-            c += t;
-            if (compact && t) atomicAdd(tile_counts + (((uint32_t)tid << bits1) | (lmin + l)), t);
+        if (single) {
+#pragma unroll
+            for (int w = 0; w < kTileSpan; ++w) c += s_t[w][tid];
+            if (c) atomicAdd(tile_counts + (((uint32_t)tid << bits1) | lmin), c);
+        } else {
+            const int rows = compact ? (int)span : 1;
+            for (int l = 0; l < rows; ++l) {
+                const uint32_t t = s_t[l][tid];
+                c += t;
+                if (compact && t) atomicAdd(tile_counts + (((uint32_t)tid << bits1) | (lmin + l)), t);
+            }
         }
         hist[(size_t)tid * nb + b] = c;
     }
@@ -664,9 +689,12 @@ struct BinScatterParams {
     const uint32_t* __restrict__ block_first;
     const uint32_t* __restrict__ block_last;
     uint32_t grid_x;
-    // pass 0 (depth ordering of the Gaussians): u64 keys in and out, digit in the upper word
+    // pass 0 (depth ordering of the Gaussians): u64 keys in and out, digit in the upper word; the last pass also gathers
+    // every Gaussian's tile rectangle and writes the depth-ordered emission table (rect / emit_out non-null)
     const uint64_t* __restrict__ keys_in;
     uint64_t* __restrict__ keys_out;
+    const uint2* __restrict__ rect;
+    uint4* __restrict__ emit_out;
     // pass 1 output / pass 2 input: (high tile digit << kshift) | idx
     const uint32_t* __restrict__ keys32_in;
     uint32_t* __restrict__ keys32_out;
@@ -880,8 +908,14 @@ GS_DEV void bin_scatter_body(const BinScatterParams& p, typename BinKey<PASS>::t
             else if (PASS == 1) d = s_dig[s];
             else d = (uint32_t)k >> p.kshift;
             const uint32_t pos = s_gbase[d] + s;
-            if (PASS == 0) p.keys_out[pos] = (uint64_t)k;
-            else if (PASS == 1) p.keys32_out[pos] = (uint32_t)k;
+            if (PASS == 0) {
+                p.keys_out[pos] = (uint64_t)k;
+                if (p.emit_out) {
+                    const uint32_t idx = (uint32_t)k;
+                    const uint2 rc = __ldg(p.rect + idx);
+                    p.emit_out[pos] = make_uint4(idx, rc.x, rc.y, rect_tiles(rc));
+                }
+            } else if (PASS == 1) p.keys32_out[pos] = (uint32_t)k;
             else p.ids_out[pos] = (uint32_t)k & idmask;
         }
     }
@@ -911,10 +945,17 @@ __global__ void __launch_bounds__(kBinThreads) bin_count_kernel(const uint64_t* 
     const uint32_t dmask = (1u << bits) - 1u;
     for (int i = tid; i < (kBinThreads / 32) * 256; i += kBinThreads) (&s_h[0][0])[i] = 0;
     __syncthreads();
-#pragma unroll 4
+    // all 16 loads in flight before the first shared-memory atomic (the kernel is latency bound: 733 blocks, one wave)
+    uint64_t kv[kBinItems];
+#pragma unroll
     for (int i = 0; i < kBinItems; ++i) {
         const uint32_t e = i * kBinThreads + tid;
-        if (e < cnt) atomicAdd(&s_h[warp][(uint32_t)(keys[(size_t)slot_begin + e] >> shift) & dmask], 1u);
+        kv[i] = e < cnt ? keys[(size_t)slot_begin + e] : 0ull;
+    }
+#pragma unroll
+    for (int i = 0; i < kBinItems; ++i) {
+        const uint32_t e = i * kBinThreads + tid;
+        if (e < cnt) atomicAdd(&s_h[warp][(uint32_t)(kv[i] >> shift) & dmask], 1u);
     }
     __syncthreads();
     if (tid < (1 << bits)) {
@@ -967,7 +1008,7 @@ int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1
     bin_scan_kernel<<<bins1, 1024, 0, stream>>>(b.hist1, nb, bins1, b.totals, nullptr, 0, nullptr);
     BinScatterParams sp;
     sp.emit = emit; sp.offsets = offsets; sp.block_first = b.block_first; sp.block_last = b.block_last; sp.grid_x = grid.x;
-    sp.keys_in = nullptr; sp.keys_out = nullptr; sp.keys32_in = nullptr; sp.keys32_out = b.keys1; sp.kshift = 32 - bits2;
+    sp.keys_in = nullptr; sp.keys_out = nullptr; sp.rect = nullptr; sp.emit_out = nullptr; sp.keys32_in = nullptr; sp.keys32_out = b.keys1; sp.kshift = 32 - bits2;
     sp.ids_out = nullptr; sp.n = R; sp.nb = nb;
     sp.shift = 0; sp.bits = bits1; sp.scanned = b.hist1; sp.totals = b.totals;
     int rc = dispatch_scatter<1>(bits1, sp, nb, stream);
@@ -984,7 +1025,9 @@ int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1
 
 // Stable LSD sort of n u64 keys on the 32 bits [32, 64) in four 8-bit passes (count -> scan -> scatter each, no
 // look-back): the depth ordering of the Gaussians. The sorted keys end up in keys_a. scratch: (256 * nb + 256) u32.
-int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* scratch, cudaStream_t stream) {
+// rect / emit (optional, both or neither): the last pass also writes emit[rank] = (idx, rect[idx].x, rect[idx].y, tiles).
+int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* scratch, const uint2* rect, uint4* emit,
+                      cudaStream_t stream) {
     if (n == 0) return GS_OK;
     const uint32_t nb = (n + kBinTile - 1) / kBinTile;
     uint32_t* hist = scratch;
@@ -997,6 +1040,7 @@ int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* 
         BinScatterParams sp = {};
         sp.keys_in = in; sp.keys_out = out; sp.n = n; sp.nb = nb; sp.shift = 8 * pass; sp.bits = 8;
         sp.scanned = hist; sp.totals = totals;
+        if (pass == 3) { sp.rect = rect; sp.emit_out = emit; }
         launch_scatter<0, 8>(sp, nb, stream);
     }
     GS_LAUNCH_CHECK();

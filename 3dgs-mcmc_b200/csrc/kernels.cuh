@@ -177,11 +177,11 @@ struct AdamLaunch {
 
 int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
-int launch_inclusive_scan(const uint2* rect, const uint64_t* order, int n, uint32_t* out, uint4* emit, uint32_t* block_sums,
-                          cudaStream_t stream);
+int launch_inclusive_scan(int n, uint32_t* out, uint4* emit, uint32_t* block_sums, cudaStream_t stream);
 int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1, int bits2, const uint4* emit,
                         const uint32_t* offsets, const BinningWS& b, uint2* ranges, cudaStream_t stream);
-int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* scratch, cudaStream_t stream);
+int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* scratch, const uint2* rect, uint4* emit,
+                      cudaStream_t stream);
 int launch_strip_ids(uint32_t n, const uint64_t* in, uint32_t* out, cudaStream_t stream);
 int launch_emit_instances(int P, const uint4* emit, uint2 grid, uint64_t* inst, cudaStream_t stream);
 int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, int first_bit, int passes, char* scratch,
