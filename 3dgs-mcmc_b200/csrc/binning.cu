@@ -892,7 +892,10 @@ GS_DEV void bin_scatter_body(const BinScatterParams& p, typename BinKey<PASS>::t
         if (kFull || e < tile_n) {
             const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
             const uint32_t at = s_hist[warp][d] + rank[i];
-            s_keys[at] = key[i];
+            // pass 2 reads its word again (L1 / L2 hit) instead of carrying 16 registers through the ranking: the freed
+            // registers buy a fifth resident CTA, which the latency-bound ranking (dependent shared-memory round trips) needs
+            if (PASS == 2) s_keys[at] = (Key)__ldg(p.keys32_in + (size_t)slot_begin + e);
+            else s_keys[at] = key[i];
             if (PASS == 1) s_dig[at] = (uint8_t)d;
         }
     }
@@ -969,12 +972,13 @@ __global__ void __launch_bounds__(kBinThreads) bin_count_kernel(const uint64_t* 
 template <int PASS, int BITS>
 static void launch_scatter(const BinScatterParams& sp, uint32_t nb, cudaStream_t stream) {
     // GS_BIN_MINB=5 (measurement): 5 resident CTAs per SM at 48 registers (more spills) instead of 4 at 64
-    static const int minb = [] { const char* e = getenv("GS_BIN_MINB"); return e ? atoi(e) : 4; }();
+    static const int minb = [] { const char* e = getenv(PASS == 2 ? "GS_BIN_MINB2" : "GS_BIN_MINB"); return e ? atoi(e) : 4; }();
     // GS_BIN_RANK=ballot (measurement): in-warp ranks from BITS ballots instead of the shared-memory peer masks. The depth
     // ordering (pass 0) always uses ballots: its upper digits repeat heavily inside a warp (a handful of exponents), and lanes
     // that hit the same mask word serialise in ATOMS (measured 24 -> 32 us per pass with the masks).
     static const bool ballot = [] { const char* e = getenv("GS_BIN_RANK"); return e && e[0] == 'b'; }();
     if (ballot || PASS == 0) bin_scatter_kernel<PASS, BITS, 4, false><<<nb, kBinThreads, 0, stream>>>(sp);
+    else if (minb == 6) bin_scatter_kernel<PASS, BITS, 6><<<nb, kBinThreads, 0, stream>>>(sp);
     else if (minb == 5) bin_scatter_kernel<PASS, BITS, 5><<<nb, kBinThreads, 0, stream>>>(sp);
     else if (minb == 3) bin_scatter_kernel<PASS, BITS, 3><<<nb, kBinThreads, 0, stream>>>(sp);
     else bin_scatter_kernel<PASS, BITS, 4><<<nb, kBinThreads, 0, stream>>>(sp);
