@@ -41,6 +41,9 @@ CONFIGS = {
                        name="BASELINE.json config 3: Mip-NeRF360-shaped (garden) cap_max=3M at 1297x840"),
     "large6m": dict(kind="garden", P=6_000_000, W=1920, H=1080, fovx=1.2, cam_radius=6.0,
                     name="BASELINE.json config 4: large scene, 6M Gaussians at 1920x1080, one view per GPU"),
+    "swin": dict(kind="garden", P=800_000, W=1352, H=1014, fovx=1.2, cam_radius=6.0,
+                 name="BASELINE.json config 5: train_swin.py sliding-window step, 30 frames, ~300K Gaussians alive per frame "
+                      "(2 x 400K stored: immature + matured), 1352x1014"),
 }
 FLOPS_PER_PAIR_FWD = 16   # ~16 FP32 ops + 1 exp per evaluated (pixel, splat) pair
 FLOPS_PER_PAIR_BWD = 45   # ~45 FP32 ops + 1 exp + 1 div per evaluated pair
@@ -1124,6 +1127,229 @@ def run_train_step_leg(torch, dist, dev, s, cams_np, cam_host, gen, H, W, P, n_g
     return out
 
 
+# ------------------------------------------------------------------------------------------------------------------
+# BASELINE.json config 5: the sliding-window training step of train_swin.py:148-261
+# ------------------------------------------------------------------------------------------------------------------
+SWIN_FRAMES = 30
+
+
+def swin_model(torch, dev, N_each, seed=0):
+    """Two stored sets (immature, matured) of N_each garden-shaped Gaussians with SwinGaussianModel's tensors
+    (scene/gaussian_model.py:36-75, raw parameters) and lifetimes [frame_start, frame_end) of 15 frames whose starts are
+    spread over the window so that ~1/3 of the stored Gaussians are alive at any frame."""
+    import gs_synth
+    sc = gs_synth.scene_garden(2 * N_each, seed)
+    g = torch.Generator(device="cpu").manual_seed(seed + 1)
+    sets = []
+    for h in range(2):
+        sl = slice(h * N_each, (h + 1) * N_each)
+        t = {"xyz": torch.from_numpy(sc["means3D"][sl].copy()), "rotation": torch.from_numpy(sc["rotations"][sl].copy()),
+             "features_dc": torch.from_numpy(sc["shs"][sl, :1].copy()), "features_rest": torch.from_numpy(sc["shs"][sl, 1:].copy()),
+             "opacity": torch.logit(torch.from_numpy(sc["opacities"][sl].copy()).clamp(1e-4, 1 - 1e-4)),
+             "scaling": torch.log(torch.from_numpy(sc["scales"][sl].copy())),
+             "rigid_v": torch.randn((N_each, 3), generator=g) * 0.002, "rigid_rotvec": torch.randn((N_each, 3), generator=g) * 0.01}
+        t["rigid_rotcen"] = t["xyz"] + torch.randn((N_each, 3), generator=g) * 0.05
+        t["frame_start"] = torch.randint(-14, SWIN_FRAMES, (N_each,), generator=g).float()
+        t = {k: v.float().contiguous().to(dev) for k, v in t.items()}
+        t["frame_end"] = t["frame_start"] + 15.0
+        sets.append(t)
+    return sets
+
+
+def run_swin_arm(args):
+    """One step = train_swin.py:148-261 for one camera view per GPU, all views of one frame (a multi-camera rig): active-set
+    gather with rigid deformation and activations (get_basic_para_at), rasterize, L1 + SSIM + regularisers, backward with the
+    cross-rank gradient sum, backward of the gather, Adam on the immature set's nine tensors, MCMC noise on the alive immature
+    Gaussians. The frame advances every step, so the alive set (and its size) changes every step."""
+    import torch
+    import torch.distributed as dist
+    import gs_synth
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, _native as C, add_noise, dp, swin
+    from diff_gaussian_rasterization import loss as fused_loss
+    from diff_gaussian_rasterization.optim import FusedAdam
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this implementation has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    n_gpus = world
+    W, H, K, Wm = args.width, args.height, args.steps, args.warmup
+    N_each = args.P // 2
+    imm, mat = swin_model(torch, dev, N_each)
+    train_keys = swin.SET_KEYS[:9]
+    for k in train_keys:
+        imm[k] = torch.nn.Parameter(imm[k])
+    # derive_idx_of_active(frame) (scene/gaussian_model.py:592-595) for every frame of the window; the sets only change at a
+    # relocation step, so the index lists are built once here instead of with two torch.nonzero syncs per iteration
+    idx = []
+    for f in range(SWIN_FRAMES):
+        ii = torch.nonzero((imm["frame_start"] <= f) & (imm["frame_end"] > f), as_tuple=True)[0]
+        mi = torch.nonzero((mat["frame_start"] <= f) & (mat["frame_end"] > f), as_tuple=True)[0]
+        idx.append((ii, mi))
+    alive = [int(a.numel() + b.numel()) for a, b in idx]
+    cap = max(alive)
+    cams_np = gs_synth.orbit_cameras(SCENE["ncams"], SCENE["cam_radius"], W, H, SCENE["fovx"], SCENE["elevation"])
+    cam_host = [{k: (torch.from_numpy(np.ascontiguousarray(v)).pin_memory() if isinstance(v, np.ndarray) else v)
+                 for k, v in c.items()} for c in cams_np]
+    bg = torch.zeros(3, dtype=torch.float32, device=dev)
+    gen = torch.Generator(device="cpu").manual_seed(5)
+    gt_host = [torch.rand((3, H, W), generator=gen).pin_memory() for _ in range(2)]
+    gt_dev = [g.to(dev) for g in gt_host]
+    # arguments/__init__.py defaults; the rigid-motion groups train at the position rate (scene/gaussian_model.py training_setup)
+    lrs = {"xyz": 1.6e-4, "rotation": 1e-3, "features_dc": 2.5e-3, "features_rest": 2.5e-3 / 20.0, "opacity": 0.05, "scaling": 5e-3,
+           "rigid_v": 1.6e-4, "rigid_rotvec": 1.6e-4, "rigid_rotcen": 1.6e-4}
+    lam, opacity_reg, scale_reg, noise_lr = 0.2, 0.01, 0.01, 5e5
+    opt = FusedAdam([{"params": [imm[k]], "lr": lrs[k], "name": k} for k in train_keys], lr=0.0, eps=1e-15)
+    vp = dp.ViewParallelRasterizer(cap, 16, dev, transport=args.transport, capacity=cap) if n_gpus > 1 else None
+    view_dev, proj_dev, campos_dev = (torch.empty(sh_, device=dev) for sh_ in ((4, 4), (4, 4), (3,)))
+    campos_views_dev = torch.empty((n_gpus, 3), dtype=torch.float32, device=dev)
+    campos_views_host = [torch.stack([torch.as_tensor(cams_np[(i * n_gpus + r) % len(cams_np)]["campos"]) for r in range(n_gpus)]).pin_memory()
+                         for i in range(len(cams_np))]
+    loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+
+    def step(i, host_inputs):
+        f = i % SWIN_FRAMES
+        ii, mi = idx[f]
+        ch = cam_host[(i * n_gpus + rank) % len(cam_host)]
+        view_dev.copy_(ch["viewmatrix"], non_blocking=True)
+        proj_dev.copy_(ch["projmatrix"], non_blocking=True)
+        campos_dev.copy_(ch["campos"], non_blocking=True)
+        gt = gt_dev[i % 2]
+        if host_inputs:
+            gt.copy_(gt_host[i % 2], non_blocking=True)
+        settings = GaussianRasterizationSettings(H, W, ch["tanfovx"], ch["tanfovy"], bg, 1.0, view_dev, proj_dev, 3, campos_dev, False, False)
+        r = swin.gather_active(float(f), imm, mat, ii, mi, deform=True)
+        Ka = int(r["xyz"].shape[0])
+        means2D = torch.zeros((Ka, 3), dtype=torch.float32, device=dev, requires_grad=True)
+        if vp is not None:
+            vp.resize(Ka)
+            campos_views_dev.copy_(campos_views_host[i % len(campos_views_host)], non_blocking=True)
+            image = vp(settings, campos_views_dev, r["xyz"], means2D, r["opacity"], r["feature"], r["scaling"], r["rotation"])[0]
+        else:
+            image = GaussianRasterizer(settings)(means3D=r["xyz"], means2D=means2D, shs=r["feature"], opacities=r["opacity"],
+                                                 scales=r["scaling"], rotations=r["rotation"])[0]
+        loss = fused_loss.photometric_loss(image, gt, lam) / n_gpus   # train_swin.py:172-175
+        loss = loss + opacity_reg * torch.abs(r["opacity"]).mean() + scale_reg * torch.abs(r["scaling"]).mean()   # :177-178
+        loss.backward()
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        with torch.no_grad():   # train_swin.py:237-251: only the alive immature Gaussians are perturbed
+            x = imm["xyz"].data[ii]
+            add_noise(x, imm["scaling"].data[ii], imm["rotation"].data[ii], imm["opacity"].data[ii], noise_lr * lrs["xyz"], seed=7, offset=i)
+            imm["xyz"].data[ii] = x
+        if host_inputs:
+            loss_host[i % 2].copy_(loss.detach(), non_blocking=True)
+        return loss
+
+    def barrier():
+        if n_gpus > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(host_inputs, profile):
+        for i in range(Wm):
+            step(i, host_inputs)
+        barrier()
+        if profile:
+            C.profile_enable(K * 16 + 8)
+        l0 = C.launch_count()
+        sampler = ClockSampler(local_rank) if profile else None
+        if sampler:
+            sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ev0.record()
+        for i in range(K):
+            last = step(Wm + i, host_inputs)
+        ev1.record()
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        ms = ev0.elapsed_time(ev1) / K
+        launches = C.launch_count() - l0
+        stages = C.profile_collect() if profile else {}
+        if profile:
+            C.profile_enable(0)
+        if n_gpus > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, launches, stages, clocks, float(last.item())
+
+    ms, launches, stages, clocks, last_loss = timed(False, True)
+    e2e_ms, _, _, _, _ = timed(True, False)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    stage_report = {n: {"ms": round(t / c, 4)} for n, (t, c) in stages.items() if c}
+    Ka = sum(alive) / len(alive)
+    adam_bytes = 28 * sum(int(imm[k].numel()) for k in train_keys)
+    dom = max(stage_report, key=lambda n: stage_report[n]["ms"]) if stage_report else None
+    roofline = None
+    if dom:
+        dms = stage_report[dom]["ms"]
+        if dom in ("render_bwd", "render_fwd"):
+            sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+            peak = sm_count * 128 * 2 * float((clocks or {}).get("sm_max_mhz") or 1965.0) * 1e6 / 1e12
+            roofline = {"kernel": dom, "bound": "fp32", "achieved": None, "peak": round(peak, 2), "unit": "TFLOP/s", "frac": None, "traffic": None,
+                        "ms": dms, "note": "FP32-issue bound tile kernel; its per-pair roofline is measured on the headline config "
+                                           "(python bench.py), where the evaluated pairs are counted; here the alive set changes every step"}
+        else:
+            per = {"preprocess_fwd": 311, "preprocess_bwd": 531}.get(dom)
+            ach = (Ka * per / (dms * 1e-3) / 1e9) if per else None
+            roofline = {"kernel": dom, "bound": "hbm", "achieved": round(ach, 1) if ach else None, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": round(ach / hbm_peak, 4) if ach else None, "traffic": None, "ms": dms}
+    line = {"metric": f"train views/s (train_swin.py step, {SWIN_FRAMES}-frame window, ~{int(round(Ka, -3))} Gaussians alive, {W}x{H}, SH deg 3)",
+            "value": round(n_gpus * 1000.0 / ms, 2), "unit": "views/s", "n_gpus": n_gpus, "steps": K, "warmup": Wm, "ms_per_step": round(ms, 4),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload_name + f" - 2 x {N_each} stored Gaussians (gs_synth.scene_garden seed 0), lifetimes of 15 frames, "
+                                   f"{min(alive)}..{max(alive)} alive per frame, one camera view of the step's frame per GPU, 16 orbit cameras",
+                       "gaussians_stored": 2 * N_each, "alive_min": min(alive), "alive_max": max(alive), "width": W, "height": H,
+                       "views_per_step": n_gpus, "parallelism": f"view-sharded dp{n_gpus}, replicated Gaussians"
+                       + (f", gradient exchange: {vp.exchange.layout} ({vp.exchange.transport})" if vp is not None else ""),
+                       "l2_policy": "per step ~60 MB of alive parameters + 190 MB of stored parameters and Adam state + 16 MB of images: "
+                                    "larger than the 126 MB L2 together; no explicit flush"},
+            "clocks": clocks,
+            "e2e": {"value": round(n_gpus * 1000.0 / e2e_ms, 2), "unit": "views/s", "ms_per_step": round(e2e_ms, 4),
+                    "h2d_bytes_per_step": 3 * H * W * 4 + (16 + 16 + 3) * 4 + (n_gpus * 12 if vp is not None else 0), "d2h_bytes_per_step": 4,
+                    "api": "swin.gather_active + " + ("dp.ViewParallelRasterizer" if vp is not None else "GaussianRasterizer") +
+                           " + loss.photometric_loss + backward + FusedAdam + add_noise; pinned gt image and camera in, loss out "
+                           "(async D2H into pinned memory)"},
+            "gpu_launches": launches, "roofline": roofline, "stages": stage_report, "last_loss": last_loss,
+            "adam": {"alg_bytes": adam_bytes, "what": "28 B per float over the immature set's nine tensors (stored, not alive, count)"},
+            "what": "train_swin.py:148-261 per view: get_basic_para_at(frame) (fused gather + rigid deformation + activations, csrc/swin.cu), "
+                    "render, (1 - 0.2) L1 + 0.2 (1 - SSIM) + opacity / scale regularisers, backward (+ cross-rank gradient sum), Adam on the "
+                    "immature set, noise on the alive immature Gaussians; ARAP loss and relocation are off, as in the reference's default "
+                    "iterations between densification steps"}
+    if rank == 0 and n_gpus == 1 and not args.skip_baselines:
+        try:
+            f0 = 0
+            ii, mi = idx[f0]
+            with torch.no_grad():
+                r = swin.gather_active(float(f0), imm, mat, ii, mi, deform=True)
+            scene = {"means3D": r["xyz"].cpu().numpy(), "scales": r["scaling"].cpu().numpy(), "rotations": r["rotation"].cpu().numpy(),
+                     "opacities": r["opacity"].cpu().numpy(), "shs": r["feature"].cpu().numpy()}
+            cb = cpu_baseline_leg(scene, cams_np[0], W, H)
+            cb["sample"] = (f"frame {f0}'s alive set through the C oracle's rasterizer forward + backward; the gather, loss and optimizer "
+                            "are not in the CPU figure. " + cb["sample"])
+            line["cpu_baseline"] = cb
+        except Exception as ex:
+            line["cpu_baseline"] = {"unavailable": repr(ex)[:300]}
+    if rank == 0:
+        print_result(line)
+    if n_gpus > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 _RESULT_FD = None
 
 
@@ -1151,6 +1377,8 @@ def main():
     _reserve_stdout()
     if args.impl == "reference":
         run_reference_arm(args)
+    elif args.config == "swin":
+        run_swin_arm(args)
     else:
         run_b200_arm(args)
 
