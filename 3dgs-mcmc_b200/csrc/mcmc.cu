@@ -42,7 +42,8 @@ __global__ void __launch_bounds__(kRelocThreads) compute_relocation_kernel(int P
     if (N_idx <= kRelocMaxN) {
         for (int i = 1; i <= N_idx; ++i) {
             const int kn = i - 1;  // the new term of this row
-            s_term[kn][t] = (float)((pow(-1.0, (double)kn) / sqrt((double)(kn + 1))) * pow((double)o_new, (double)(kn + 1)));
+            // pow(-1, kn) is exactly +-1 for an integer kn: the sign is taken directly instead of through the general FP64 pow
+            s_term[kn][t] = (float)((((kn & 1) ? -1.0 : 1.0) / sqrt((double)(kn + 1))) * pow((double)o_new, (double)(kn + 1)));
             const float* __restrict__ row = binoms + (size_t)(i - 1) * n_max;
             for (int k = 0; k <= kn; ++k) denom_sum += (row[k] * s_term[k][t]);
         }
