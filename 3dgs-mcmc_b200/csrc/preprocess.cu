@@ -150,30 +150,6 @@ __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const Prepro
         __trap();
     }
 
-    // ---- SH rows of the Gaussians that passed the frustum test: start the copies now ----
-    const int Mrow = 3 * p.M;
-    const bool use_sh = p.colors_precomp == nullptr;
-    const bool staged = use_sh && Mrow <= kShMaxRow;
-    const int row_stride = Mrow | 1;
-    const int warp_first = idx - lane;
-    const int rows_valid = min(32, p.P - warp_first);
-    const uint32_t alive_mask = __ballot_sync(0xffffffffu, alive);
-    float* tile = &s_sh[warp][0];
-    const int ncoef3 = 3 * (p.D + 1) * (p.D + 1);
-    // degree-3-sized rows on a 16-byte aligned base (the training layout) move as 16-byte chunks
-    const bool split = kSplit && use_sh;                   // shs = features_dc [P][1][3], shs_rest = features_rest [P][15][3]
-    const bool rows16 = !split && staged && Mrow == 48 && (reinterpret_cast<size_t>(p.shs) & 15) == 0;
-    if (split) {
-        if (alive_mask)
-            stage_sh_split_load(tile, p.shs + (size_t)warp_first * 3, p.shs_rest + (size_t)warp_first * kShSplitRestRow, rows_valid,
-                                alive_mask, lane);
-    } else if (staged && alive_mask) {
-        float* src = const_cast<float*>(p.shs) + (size_t)warp_first * Mrow;
-        if (rows16) stage_sh_rows16_load(reinterpret_cast<float4*>(tile), src, rows_valid, alive_mask, ncoef3, lane);
-        else if (Mrow == 48) stage_sh_rows<true, 48>(tile, row_stride, src, Mrow, rows_valid, alive_mask, ncoef3, lane);
-        else stage_sh_rows<true, 0>(tile, row_stride, src, Mrow, rows_valid, alive_mask, ncoef3, lane);
-    }
-
     // ---- phase 1 ----
     bool visible = false;
     float3 conic = {0.f, 0.f, 0.f};
@@ -214,6 +190,32 @@ __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const Prepro
                 depth_bits = __float_as_uint(p_view.z);
             }
         }
+    }
+
+    // ---- SH rows of the VISIBLE Gaussians only. Round 1 started these copies right after the frustum test, under phase 1; but
+    //      ~20 % of the Gaussians in front of the camera touch no tile (off screen), the kernel is DRAM bound (70 % of peak),
+    //      and their 192-byte rows were 13 % of its read traffic. The other resident warps cover the copy latency. ----
+    const int Mrow = 3 * p.M;
+    const bool use_sh = p.colors_precomp == nullptr;
+    const bool staged = use_sh && Mrow <= kShMaxRow;
+    const int row_stride = Mrow | 1;
+    const int warp_first = idx - lane;
+    const int rows_valid = min(32, p.P - warp_first);
+    const uint32_t alive_mask = __ballot_sync(0xffffffffu, visible);   // rows to stage
+    float* tile = &s_sh[warp][0];
+    const int ncoef3 = 3 * (p.D + 1) * (p.D + 1);
+    // degree-3-sized rows on a 16-byte aligned base (the training layout) move as 16-byte chunks
+    const bool split = kSplit && use_sh;                   // shs = features_dc [P][1][3], shs_rest = features_rest [P][15][3]
+    const bool rows16 = !split && staged && Mrow == 48 && (reinterpret_cast<size_t>(p.shs) & 15) == 0;
+    if (split) {
+        if (alive_mask)
+            stage_sh_split_load(tile, p.shs + (size_t)warp_first * 3, p.shs_rest + (size_t)warp_first * kShSplitRestRow, rows_valid,
+                                alive_mask, lane);
+    } else if (staged && alive_mask) {
+        float* src = const_cast<float*>(p.shs) + (size_t)warp_first * Mrow;
+        if (rows16) stage_sh_rows16_load(reinterpret_cast<float4*>(tile), src, rows_valid, alive_mask, ncoef3, lane);
+        else if (Mrow == 48) stage_sh_rows<true, 48>(tile, row_stride, src, Mrow, rows_valid, alive_mask, ncoef3, lane);
+        else stage_sh_rows<true, 0>(tile, row_stride, src, Mrow, rows_valid, alive_mask, ncoef3, lane);
     }
 
     // ---- the SH rows have landed ----
