@@ -71,6 +71,8 @@ GS_DEV uint32_t rect_tiles(const uint2 rc) { return (rc.y & 0xffffu) * (rc.y >> 
 
 __global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uint4* __restrict__ emit, int n,
                                                                        uint32_t* __restrict__ block_sums) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ uint32_t sw[33];
     const size_t base = (size_t)blockIdx.x * kScanBlock;
     uint32_t s = 0;
@@ -86,6 +88,8 @@ __global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uin
 
 // Single block: exclusive scan of block_sums in place.
 __global__ void __launch_bounds__(1024) scan_spine_kernel(uint32_t* __restrict__ block_sums, int nb) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ uint32_t sw[33];
     uint32_t carry = 0;
     for (int base = 0; base < nb; base += 1024) {
@@ -103,6 +107,8 @@ __global__ void __launch_bounds__(1024) scan_spine_kernel(uint32_t* __restrict__
 // the table moves as whole, coalesced uint4s), carrying the running sum from round to round.
 __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(int n, const uint32_t* __restrict__ block_offsets,
                                                                   uint32_t* __restrict__ out, uint4* __restrict__ emit) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ uint32_t sw[kScanThreads / 32];
     static_assert(kScanItems * 32 * (kScanThreads / 32) == kScanBlock, "one warp per kScanItems * 32 entries");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -137,9 +143,9 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(int n, const u
 int launch_inclusive_scan(int n, uint32_t* out, uint4* emit, uint32_t* block_sums, cudaStream_t stream) {
     if (n <= 0) return GS_OK;
     const int nb = (n + kScanBlock - 1) / kScanBlock;
-    scan_block_sums_kernel<<<nb, kScanThreads, 0, stream>>>(emit, n, block_sums);
-    scan_spine_kernel<<<1, 1024, 0, stream>>>(block_sums, nb);
-    scan_apply_kernel<<<nb, kScanThreads, 0, stream>>>(n, block_sums, out, emit);
+    launch_pdl(scan_block_sums_kernel, dim3(nb), dim3(kScanThreads), 0, stream, emit, n, block_sums);
+    launch_pdl(scan_spine_kernel, dim3(1), dim3(1024), 0, stream, block_sums, nb);
+    launch_pdl(scan_apply_kernel, dim3(nb), dim3(kScanThreads), 0, stream, n, block_sums, out, emit);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
@@ -480,6 +486,8 @@ GS_DEV uint32_t peer_mask(const uint32_t d) {
 // Depth rank of the Gaussian owning the first / last emission slot of every pass-1 block.
 __global__ void __launch_bounds__(256) block_bounds_kernel(int P, const uint32_t* __restrict__ offsets, uint32_t R,
                                                             uint32_t* __restrict__ first, uint32_t* __restrict__ last) {
+    pdl_trigger();
+    pdl_wait();
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= P) return;
     const uint32_t s1 = offsets[r], s0 = r ? offsets[r - 1] : 0u;
@@ -507,6 +515,8 @@ GS_DEV float rcp_small(uint32_t w) {
 __global__ void __launch_bounds__(kBinThreads) bin_count1_kernel(const uint4* __restrict__ emit, const uint32_t* __restrict__ block_first,
                                                                   const uint32_t* __restrict__ block_last, uint32_t R, uint32_t grid_x,
                                                                   int bits, uint32_t* __restrict__ hist, uint32_t nb) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ int s_diff[256];
     __shared__ int s_all;
     __shared__ uint32_t s_scan[33];
@@ -561,6 +571,8 @@ __global__ void __launch_bounds__(kBinThreads) bin_count1_kernel(const uint4* __
 constexpr int kScanPer = 8;
 __global__ void __launch_bounds__(1024) bin_scan_kernel(uint32_t* __restrict__ hist, uint32_t nb, int bins, uint32_t* __restrict__ totals,
                                                          const uint32_t* __restrict__ tile_counts, uint32_t tiles, uint2* __restrict__ ranges) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ uint32_t sw[33];
     const int tid = threadIdx.x;
     const bool do_ranges = (int)blockIdx.x == bins;
@@ -598,6 +610,8 @@ __global__ void __launch_bounds__(1024) bin_scan_kernel(uint32_t* __restrict__ h
 __global__ void __launch_bounds__(kBinThreads) bin_count2_kernel(const uint32_t* __restrict__ keys, uint32_t R, int bits1, int bits2,
                                                                   const uint32_t* __restrict__ totals1, uint32_t* __restrict__ hist,
                                                                   uint32_t nb, uint32_t* __restrict__ tile_counts) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ uint32_t s_t[kTileSpan][256];
     __shared__ uint32_t s_start[257];     // exclusive scan of the pass-1 digit totals (+ R at [bins1])
     __shared__ uint32_t s_scan[33];
@@ -931,6 +945,8 @@ GS_DEV void bin_scatter_body(const BinScatterParams& p, typename BinKey<PASS>::t
 // kFull: every slot of the block exists (all blocks but the last) - no validity predicates anywhere.
 template <int PASS, int BITS, int MINB = 4, bool kAtomicPeers = true>
 __global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const BinScatterParams p) {
+    pdl_trigger();
+    pdl_wait();
     using Key = typename BinKey<PASS>::type;
     __shared__ __align__(16) Key s_keys[kBinTile];                   // 32 / 16 KB (pass 1 first uses it as u16 owner[kBinTile])
     __shared__ uint8_t s_dig[PASS == 1 ? kBinTile : 16];             // pass 1: the low digit travels beside the word, not in it
@@ -945,6 +961,8 @@ __global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const Bi
 // bin_count1/2 for plain u64 keys (the depth ordering of the Gaussians).
 __global__ void __launch_bounds__(kBinThreads) bin_count_kernel(const uint64_t* __restrict__ keys, uint32_t n, int shift, int bits,
                                                                  uint32_t* __restrict__ hist, uint32_t nb) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ uint32_t s_h[kBinThreads / 32][256];
     const int tid = threadIdx.x, warp = tid >> 5;
     const uint32_t b = blockIdx.x;
@@ -981,11 +999,11 @@ static void launch_scatter(const BinScatterParams& sp, uint32_t nb, cudaStream_t
     // ordering (pass 0) always uses ballots: its upper digits repeat heavily inside a warp (a handful of exponents), and lanes
     // that hit the same mask word serialise in ATOMS (measured 24 -> 32 us per pass with the masks).
     static const bool ballot = [] { const char* e = getenv("GS_BIN_RANK"); return e && e[0] == 'b'; }();
-    if (ballot || PASS == 0) bin_scatter_kernel<PASS, BITS, 4, false><<<nb, kBinThreads, 0, stream>>>(sp);
-    else if (minb == 6) bin_scatter_kernel<PASS, BITS, 6><<<nb, kBinThreads, 0, stream>>>(sp);
-    else if (minb == 5) bin_scatter_kernel<PASS, BITS, 5><<<nb, kBinThreads, 0, stream>>>(sp);
-    else if (minb == 3) bin_scatter_kernel<PASS, BITS, 3><<<nb, kBinThreads, 0, stream>>>(sp);
-    else bin_scatter_kernel<PASS, BITS, 4><<<nb, kBinThreads, 0, stream>>>(sp);
+    if (ballot || PASS == 0) launch_pdl(bin_scatter_kernel<PASS, BITS, 4, false>, dim3(nb), dim3(kBinThreads), 0, stream, sp);
+    else if (minb == 6) launch_pdl(bin_scatter_kernel<PASS, BITS, 6, true>, dim3(nb), dim3(kBinThreads), 0, stream, sp);
+    else if (minb == 5) launch_pdl(bin_scatter_kernel<PASS, BITS, 5, true>, dim3(nb), dim3(kBinThreads), 0, stream, sp);
+    else if (minb == 3) launch_pdl(bin_scatter_kernel<PASS, BITS, 3, true>, dim3(nb), dim3(kBinThreads), 0, stream, sp);
+    else launch_pdl(bin_scatter_kernel<PASS, BITS, 4, true>, dim3(nb), dim3(kBinThreads), 0, stream, sp);
 }
 template <int PASS>
 static int dispatch_scatter(int bits, const BinScatterParams& sp, uint32_t nb, cudaStream_t stream) {
@@ -1011,9 +1029,9 @@ int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1
     }
     const uint32_t nb = (R + kBinTile - 1) / kBinTile;
     const int bins1 = 1 << bits1, bins2 = 1 << bits2;
-    block_bounds_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, offsets, R, b.block_first, b.block_last);
-    bin_count1_kernel<<<nb, kBinThreads, 0, stream>>>(emit, b.block_first, b.block_last, R, grid.x, bits1, b.hist1, nb);
-    bin_scan_kernel<<<bins1, 1024, 0, stream>>>(b.hist1, nb, bins1, b.totals, nullptr, 0, nullptr);
+    launch_pdl(block_bounds_kernel, dim3((P + 255) / 256), dim3(256), 0, stream, P, offsets, R, b.block_first, b.block_last);
+    launch_pdl(bin_count1_kernel, dim3(nb), dim3(kBinThreads), 0, stream, emit, b.block_first, b.block_last, R, grid.x, bits1, b.hist1, nb);
+    launch_pdl(bin_scan_kernel, dim3(bins1), dim3(1024), 0, stream, b.hist1, nb, bins1, b.totals, nullptr, 0u, nullptr);
     BinScatterParams sp;
     sp.emit = emit; sp.offsets = offsets; sp.block_first = b.block_first; sp.block_last = b.block_last; sp.grid_x = grid.x;
     sp.keys_in = nullptr; sp.keys_out = nullptr; sp.rect = nullptr; sp.emit_out = nullptr; sp.keys32_in = nullptr; sp.keys32_out = b.keys1; sp.kshift = 32 - bits2;
@@ -1021,8 +1039,8 @@ int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1
     sp.shift = 0; sp.bits = bits1; sp.scanned = b.hist1; sp.totals = b.totals;
     int rc = dispatch_scatter<1>(bits1, sp, nb, stream);
     if (rc) return rc;
-    bin_count2_kernel<<<nb, kBinThreads, 0, stream>>>(b.keys1, R, bits1, bits2, b.totals, b.hist2, nb, b.tile_counts);
-    bin_scan_kernel<<<bins2 + 1, 1024, 0, stream>>>(b.hist2, nb, bins2, b.totals + 256, b.tile_counts, tiles, ranges);
+    launch_pdl(bin_count2_kernel, dim3(nb), dim3(kBinThreads), 0, stream, b.keys1, R, bits1, bits2, b.totals, b.hist2, nb, b.tile_counts);
+    launch_pdl(bin_scan_kernel, dim3(bins2 + 1), dim3(1024), 0, stream, b.hist2, nb, bins2, b.totals + 256, b.tile_counts, tiles, ranges);
     sp.keys32_in = b.keys1; sp.keys32_out = nullptr; sp.ids_out = b.ids;
     sp.shift = bits1; sp.bits = bits2; sp.scanned = b.hist2; sp.totals = b.totals + 256;
     rc = dispatch_scatter<2>(bits2, sp, nb, stream);
@@ -1043,8 +1061,8 @@ int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* 
     for (int pass = 0; pass < 4; ++pass) {
         const uint64_t* in = (pass & 1) ? keys_b : keys_a;
         uint64_t* out = (pass & 1) ? keys_a : keys_b;
-        bin_count_kernel<<<nb, kBinThreads, 0, stream>>>(in, n, 32 + 8 * pass, 8, hist, nb);
-        bin_scan_kernel<<<256, 1024, 0, stream>>>(hist, nb, 256, totals, nullptr, 0, nullptr);
+        launch_pdl(bin_count_kernel, dim3(nb), dim3(kBinThreads), 0, stream, in, n, 32 + 8 * pass, 8, hist, nb);
+        launch_pdl(bin_scan_kernel, dim3(256), dim3(1024), 0, stream, hist, nb, 256, totals, nullptr, 0u, nullptr);
         BinScatterParams sp = {};
         sp.keys_in = in; sp.keys_out = out; sp.n = n; sp.nb = nb; sp.shift = 8 * pass; sp.bits = 8;
         sp.scanned = hist; sp.totals = totals;

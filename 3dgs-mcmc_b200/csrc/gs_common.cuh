@@ -36,6 +36,31 @@
 
 namespace gs {
 
+// ------------------------------------------------------------------------------------------------
+// Programmatic dependent launch (sm_90+). A step is a chain of ~25 short dependent kernels on one stream; between two of
+// them the stream normally drains, flushes and only then starts launching the next grid (~2 us each). A kernel launched
+// with launch_pdl() may have its CTAs scheduled as soon as every CTA of its predecessor has executed pdl_trigger() (i.e. the
+// predecessor is fully resident); they park at pdl_wait(), which returns once the predecessor grid has COMPLETED and its
+// writes are visible. Rule for every kernel on the chain: `pdl_trigger(); pdl_wait();` are its first statements, before
+// any global-memory access. Both are no-ops for a grid launched the ordinary way or preceded by a memset / memcpy.
+// Used for scenes of >= 1M Gaussians (pdl_hint); GS_PDL=0 / 1 forces it off / on.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();               // api.cu
+void pdl_hint(long long gaussians);   // api.cu: called at the head of every entry point that launches a chain
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // Spherical-harmonics basis constants (real SH, degrees 0..3).
 __device__ constexpr float kSH0 = 0.28209479177387814f;
 __device__ constexpr float kSH1 = 0.4886025119029199f;

@@ -146,6 +146,8 @@ static_assert(kPbThreads == kRecChunk, "one block of the per-Gaussian backward p
 static_assert(kRecFloats <= (kPbThreads / 32) * kShTileFloats, "the record is staged in the (dead) SH tile");
 
 __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const PreprocessBwdParams p) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ __align__(16) float s_sh[kPbThreads / 32][kShTileFloats];
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -405,7 +407,7 @@ __global__ void __launch_bounds__(kPbThreads) preprocess_bwd_kernel(const Prepro
 
 int launch_preprocess_bwd(const PreprocessBwdParams& p, cudaStream_t stream) {
     if (p.P <= 0) return GS_OK;
-    preprocess_bwd_kernel<<<(p.P + kPbThreads - 1) / kPbThreads, kPbThreads, 0, stream>>>(p);
+    launch_pdl(preprocess_bwd_kernel, dim3((p.P + kPbThreads - 1) / kPbThreads), dim3(kPbThreads), 0, stream, p);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

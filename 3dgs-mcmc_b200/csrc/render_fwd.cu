@@ -34,6 +34,8 @@ namespace gs {
 // only on those. Nothing that can contribute is ever dropped, so image / final_T / n_contrib / is_used are unchanged.
 template <int CH, int RS, int GA, bool kTwoLevel, bool kCount = false>
 __global__ void __launch_bounds__(GS_TILE_PIX, 6) render_fwd_kernel(const RenderFwdParams p) {
+    pdl_trigger();
+    pdl_wait();
     constexpr int kWords = CH / 32;              // survivor bitmap words per chunk
     __shared__ __align__(128) SplatRec s_rec[RS][CH];
     __shared__ __align__(16) uint32_t s_inst[kInstStages][CH + kInstPad];
@@ -242,7 +244,7 @@ int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream) 
     switch (variant) {
         case 0: render_fwd_kernel<128, 3, 2, false><<<tiles, GS_TILE_PIX, 0, stream>>>(p); break;
         case 2: render_fwd_kernel<128, 3, 2, true><<<tiles, GS_TILE_PIX, 0, stream>>>(p); break;
-        default: render_fwd_kernel<256, 2, 1, true><<<tiles, GS_TILE_PIX, 0, stream>>>(p); break;
+        default: launch_pdl(render_fwd_kernel<256, 2, 1, true, false>, dim3(tiles), dim3(GS_TILE_PIX), 0, stream, p); break;
     }
     GS_LAUNCH_CHECK();
     return GS_OK;
