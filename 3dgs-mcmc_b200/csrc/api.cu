@@ -187,7 +187,8 @@ static int forward_preprocess_impl(void* stream_, int P, int D, int M, const flo
     rc = launch_inclusive_scan(P, g.point_offsets, g.emit, g.scan_block_sums, stream);
     if (rc) return rc;
     prof_mark(stream, ST_SCAN);
-    count_launches(1 + 3 * kDepthSortPasses + 3);
+    // preprocess + depth sort (count [+ scan] + scatter per pass) + the two scan kernels
+    count_launches(1 + 3 * kDepthSortPasses + 2);
     return GS_OK;
 }
 

@@ -62,7 +62,7 @@ GS_DEV uint32_t block_excl_scan(uint32_t v, uint32_t* smem_warp, uint32_t* total
 // ------------------------------------------------------------------------------------------------
 // Inclusive scan of the per-Gaussian tile counts taken in depth order:
 //     out[r] = sum_{r' <= r} tiles(order[r'] & 0xffffffff),  tiles = w * h of the Gaussian's tile rectangle.
-// Three small kernels: block sums -> scan of block sums -> apply, all streaming over the depth-ordered emission table
+// Two small kernels: block sums -> apply (each block first adds up the sums of the blocks before it), both streaming over the depth-ordered emission table
 // (idx, x0 | y0 << 16, w | h << 16, tile count) that the LAST pass of the depth sort wrote while it had every key's final
 // position in hand (one random gather of the rectangle per Gaussian, instead of one in each of two scan kernels); the apply
 // kernel replaces the count by the first emission slot: the table the first binning pass expands.
@@ -86,30 +86,14 @@ __global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uin
     if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
 }
 
-// Single block: exclusive scan of block_sums in place.
-__global__ void __launch_bounds__(1024) scan_spine_kernel(uint32_t* __restrict__ block_sums, int nb) {
-    pdl_trigger();
-    pdl_wait();
-    __shared__ uint32_t sw[33];
-    uint32_t carry = 0;
-    for (int base = 0; base < nb; base += 1024) {
-        const int k = base + threadIdx.x;
-        const uint32_t v = k < nb ? block_sums[k] : 0;
-        uint32_t total;
-        const uint32_t ex = block_excl_scan(v, sw, &total);
-        if (k < nb) block_sums[k] = carry + ex;
-        carry += total;
-    }
-}
-
 // emit[r].w: tile count in, first emission slot out; out[r] = first slot of rank r + 1.
 // Warp w of a block owns 256 consecutive entries and walks them 32 at a time (lane-consecutive 16-byte loads and stores:
 // the table moves as whole, coalesced uint4s), carrying the running sum from round to round.
-__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(int n, const uint32_t* __restrict__ block_offsets,
+__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(int n, const uint32_t* __restrict__ block_sums,
                                                                   uint32_t* __restrict__ out, uint4* __restrict__ emit) {
     pdl_trigger();
     pdl_wait();
-    __shared__ uint32_t sw[kScanThreads / 32];
+    __shared__ uint32_t sw[kScanThreads / 32], sb[kScanThreads / 32];
     static_assert(kScanItems * 32 * (kScanThreads / 32) == kScanBlock, "one warp per kScanItems * 32 entries");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const size_t base = (size_t)blockIdx.x * kScanBlock + (size_t)warp * (kScanItems * 32) + lane;
@@ -124,10 +108,16 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(int n, const u
         excl[r] = carry + incl - E[r].w;
         carry += __shfl_sync(0xffffffffu, incl, 31);
     }
-    if (lane == 0) sw[warp] = carry;
+    // offset of this block = sum of the sums of the blocks before it (at most a few thousand words, L2 resident): every block
+    // adds them up itself instead of a one-block "spine" kernel between the two passes (one launch fewer per step)
+    uint32_t before = 0;
+    for (uint32_t j = threadIdx.x; j < blockIdx.x; j += kScanThreads) before += __ldg(block_sums + j);
+    before = __reduce_add_sync(0xffffffffu, before);
+    if (lane == 0) { sw[warp] = carry; sb[warp] = before; }
     __syncthreads();
-    uint32_t woff = block_offsets[blockIdx.x];
-    for (int w = 0; w < warp; ++w) woff += sw[w];
+    uint32_t woff = 0;
+#pragma unroll
+    for (int w = 0; w < kScanThreads / 32; ++w) woff += sb[w] + (w < warp ? sw[w] : 0u);
 #pragma unroll
     for (int r = 0; r < kScanItems; ++r) {
         if (base + r * 32 < (size_t)n) {
@@ -144,7 +134,6 @@ int launch_inclusive_scan(int n, uint32_t* out, uint4* emit, uint32_t* block_sum
     if (n <= 0) return GS_OK;
     const int nb = (n + kScanBlock - 1) / kScanBlock;
     launch_pdl(scan_block_sums_kernel, dim3(nb), dim3(kScanThreads), 0, stream, emit, n, block_sums);
-    launch_pdl(scan_spine_kernel, dim3(1), dim3(1024), 0, stream, block_sums, nb);
     launch_pdl(scan_apply_kernel, dim3(nb), dim3(kScanThreads), 0, stream, n, block_sums, out, emit);
     GS_LAUNCH_CHECK();
     return GS_OK;
@@ -462,6 +451,10 @@ int launch_tile_ranges(uint32_t R, const uint64_t* inst, uint2* ranges, uint32_t
 // inter-block dependency inside any kernel (no tickets, flags, spins or fences).
 // ================================================================================================
 constexpr int kBinThreads = 256;
+// Depth sorts of at most this many blocks let the count kernel's last block do the digit scan (no bin_scan_kernel launch).
+// 0 = never: measured at 300K Gaussians (74 blocks) the serial tail (fence, ticket, one block scanning 256 rows) costs more
+// than the 256-CTA scan kernel and its launch: depth sort 0.096 -> 0.157 ms. Kept for the record and for GS_FUSE_SCAN.
+constexpr uint32_t kFuseScanMaxBlocks = 0;
 constexpr int kBinItems = kBinTile / kBinThreads;  // 16
 constexpr int kTileSpan = 8;                        // low digits per block that bin_count2_kernel aggregates in shared memory
 static_assert(kBinItems == 16 && kBinThreads == 256, "the binning kernels are written for 256 threads x 16 slots");
@@ -960,7 +953,7 @@ __global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const Bi
 // hist[d][b] = number of keys of block b whose digit (key >> shift) & (2^bits - 1) is d. Generic counterpart of
 // bin_count1/2 for plain u64 keys (the depth ordering of the Gaussians).
 __global__ void __launch_bounds__(kBinThreads) bin_count_kernel(const uint64_t* __restrict__ keys, uint32_t n, int shift, int bits,
-                                                                 uint32_t* __restrict__ hist, uint32_t nb) {
+                                                                 uint32_t* __restrict__ hist, uint32_t nb, uint32_t* __restrict__ totals, uint32_t* __restrict__ done_counter) {
     pdl_trigger();
     pdl_wait();
     __shared__ uint32_t s_h[kBinThreads / 32][256];
@@ -989,6 +982,33 @@ __global__ void __launch_bounds__(kBinThreads) bin_count_kernel(const uint64_t* 
         for (int w = 0; w < kBinThreads / 32; ++w) c += s_h[w][tid];
         hist[(size_t)tid * nb + b] = c;
     }
+    // Small inputs (done_counter non-null, nb <= kFuseScanMaxBlocks): the LAST block to finish scans all digit rows in place
+    // (thread d: exclusive scan of hist[d][0..nb), totals[d]) - what bin_scan_kernel does with 256 CTAs, without its launch.
+    // At 300K Gaussians the chain is bound by the host's launch rate, not by the work.
+    if (done_counter == nullptr) return;
+    __shared__ bool s_last;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = atomicAdd(done_counter, 1u) == nb - 1u;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (tid < (1 << bits)) {
+        uint32_t* row = hist + (size_t)tid * nb;
+        uint32_t run = 0;
+        for (uint32_t j = 0; j < nb; j += 8) {
+            uint32_t v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) v[q] = j + q < nb ? __ldcg(row + j + q) : 0u;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                if (j + q < nb) row[j + q] = run;
+                run += v[q];
+            }
+        }
+        totals[tid] = run;
+    }
+    if (tid == 0) *done_counter = 0u;   // ready for the next pass
 }
 
 template <int PASS, int BITS>
@@ -1050,7 +1070,7 @@ int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1
 }
 
 // Stable LSD sort of n u64 keys on the 32 bits [32, 64) in four 8-bit passes (count -> scan -> scatter each, no
-// look-back): the depth ordering of the Gaussians. The sorted keys end up in keys_a. scratch: (256 * nb + 256) u32.
+// look-back): the depth ordering of the Gaussians. The sorted keys end up in keys_a. scratch: (256 * nb + 256 + 1) u32.
 // rect / emit (optional, both or neither): the last pass also writes emit[rank] = (idx, rect[idx].x, rect[idx].y, tiles).
 int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* scratch, const uint2* rect, uint4* emit,
                       cudaStream_t stream) {
@@ -1058,11 +1078,19 @@ int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* 
     const uint32_t nb = (n + kBinTile - 1) / kBinTile;
     uint32_t* hist = scratch;
     uint32_t* totals = scratch + (size_t)256 * nb;
+    uint32_t* done_counter = totals + 256;                  // one word, self-resetting; zeroed here once per call
+    static const uint32_t fuse_max = [] { const char* e = getenv("GS_FUSE_SCAN"); return e ? (uint32_t)atoi(e) : kFuseScanMaxBlocks; }();
+    const bool fuse_scan = nb <= fuse_max;
+    if (fuse_scan) GS_CUDA_TRY(cudaMemsetAsync(done_counter, 0, sizeof(uint32_t), stream));
     for (int pass = 0; pass < 4; ++pass) {
         const uint64_t* in = (pass & 1) ? keys_b : keys_a;
         uint64_t* out = (pass & 1) ? keys_a : keys_b;
-        launch_pdl(bin_count_kernel, dim3(nb), dim3(kBinThreads), 0, stream, in, n, 32 + 8 * pass, 8, hist, nb);
-        launch_pdl(bin_scan_kernel, dim3(256), dim3(1024), 0, stream, hist, nb, 256, totals, nullptr, 0u, nullptr);
+        if (fuse_scan) {
+            launch_pdl(bin_count_kernel, dim3(nb), dim3(kBinThreads), 0, stream, in, n, 32 + 8 * pass, 8, hist, nb, totals, done_counter);
+        } else {
+            launch_pdl(bin_count_kernel, dim3(nb), dim3(kBinThreads), 0, stream, in, n, 32 + 8 * pass, 8, hist, nb, (uint32_t*)nullptr, (uint32_t*)nullptr);
+            launch_pdl(bin_scan_kernel, dim3(256), dim3(1024), 0, stream, hist, nb, 256, totals, nullptr, 0u, nullptr);
+        }
         BinScatterParams sp = {};
         sp.keys_in = in; sp.keys_out = out; sp.n = n; sp.nb = nb; sp.shift = 8 * pass; sp.bits = 8;
         sp.scanned = hist; sp.totals = totals;

@@ -229,7 +229,7 @@ size_t knn_workspace_bytes(int P) {
     const size_t n = (size_t)(P > 0 ? P : 0);
     c.take<uint64_t>(n); c.take<uint64_t>(n); c.take<uint32_t>(n); c.take<float4>(n);
     c.take<KnnBounds>(1024 + 1);
-    c.take<uint32_t>(256 * ((n + kBinTile - 1) / kBinTile) + 256);
+    c.take<uint32_t>(256 * ((n + kBinTile - 1) / kBinTile) + 256 + 64);   // + the depth sort's done counter
     return align_up(c.off, kAlign);
 }
 
@@ -242,7 +242,7 @@ int launch_knn_mean_dist2(int P, const float* points, float* out, char* ws, cuda
     uint32_t* codes = c.take<uint32_t>(n);
     float4* sorted = c.take<float4>(n);
     KnnBounds* bounds = c.take<KnnBounds>(1024 + 1);
-    uint32_t* scratch = c.take<uint32_t>(256 * ((n + kBinTile - 1) / kBinTile) + 256);
+    uint32_t* scratch = c.take<uint32_t>(256 * ((n + kBinTile - 1) / kBinTile) + 256 + 64);   // + the depth sort's done counter
     const int blocks = (P + kKnnThreads - 1) / kKnnThreads;
     const int rblocks = blocks < 1024 ? blocks : 1024;
     knn_bounds_partial_kernel<<<rblocks, kKnnThreads, 0, stream>>>(P, points, bounds + 1);
