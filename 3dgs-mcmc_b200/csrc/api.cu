@@ -181,10 +181,10 @@ static int forward_preprocess_impl(void* stream_, int P, int D, int M, const flo
         GS_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, g.num_rendered, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
     if (count_ready_event) GS_CUDA_TRY(cudaEventRecord((cudaEvent_t)count_ready_event, stream));
     // Depth order of the Gaussians: stable sort of (depth_bits << 32 | idx) on the depth field.
-    rc = launch_depth_sort(g.dkeys_a, g.dkeys_b, (uint32_t)P, reinterpret_cast<uint32_t*>(g.dsort_scratch), g.rect, g.emit, stream);
+    rc = launch_depth_sort(g.dkeys_a, g.dkeys_b, (uint32_t)P, g.num_rendered + 2, reinterpret_cast<uint32_t*>(g.dsort_scratch), g.rect, g.emit, stream);
     if (rc) return rc;
     prof_mark(stream, ST_DEPTH_SORT);
-    rc = launch_inclusive_scan(P, g.point_offsets, g.emit, g.scan_block_sums, stream);
+    rc = launch_inclusive_scan(P, g.num_rendered + 2, g.point_offsets, g.emit, g.scan_block_sums, stream);
     if (rc) return rc;
     prof_mark(stream, ST_SCAN);
     // preprocess + depth sort (count [+ scan] + scatter per pass) + the two scan kernels
@@ -237,7 +237,7 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
         // Two fused binning passes (count -> scan -> scatter each); the tile ranges fall out of the second count.
         int bits1, bits2;
         bin_digit_bits(tiles, &bits1, &bits2);
-        rc = launch_fast_binning(P, R, grid, tiles, bits1, bits2, g.emit, g.point_offsets, b, img.ranges, stream);
+        rc = launch_fast_binning(P, g.num_rendered + 2, R, grid, tiles, bits1, bits2, g.emit, g.point_offsets, b, img.ranges, stream);
         if (rc) return rc;
         prof_mark(stream, ST_SORT);
         count_launches(R > 0 ? 7 : 0);
@@ -245,7 +245,7 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
         // Generic path (tile ids wider than two binning digits): emission, multi-pass radix sort, range detection.
         const int passes = sort_passes(tiles);
         if (R > 0) {
-            rc = launch_emit_instances(P, g.emit, grid, b.inst_a, stream);
+            rc = launch_emit_instances(P, g.num_rendered + 2, g.emit, grid, b.inst_a, stream);
             if (rc) return rc;
             prof_mark(stream, ST_DUPLICATE);
             rc = launch_radix_sort(b.inst_a, b.inst_b, R, 32, passes, b.sort_scratch, b.error_flag, stream);
@@ -850,15 +850,20 @@ long long gs_debug_fetch(int which, int P, unsigned int R, int W, int H, const v
             }
             case 1: src = g.clamped; n = Ps; break;
             case 4: src = g.cov3D; n = Ps * 24; break;
-            case 8: src = g.point_offsets; n = Ps * 4; break;
-            case 2: src = g.rec; n = Ps * sizeof(SplatRec); break;
-            case 9:  // Gaussian indices in (depth, index) order; culled ones last
+            case 8:   // inclusive scan of the tile counts in depth order; entries of the culled Gaussians (last) repeat R
+            case 9: { // Gaussian indices in (depth, index) order; culled ones last
                 n = Ps * 4;
                 if (dst && n > 0 && n <= max_bytes) {
                     if (cudaDeviceSynchronize() != cudaSuccess) return -1;
-                    if (launch_debug_low32((uint32_t)P, g.dkeys_a, (uint32_t*)dst)) return -1;
+                    uint32_t cnt[4] = {0, 0, 0, 0};
+                    if (cudaMemcpy(cnt, g.num_rendered, sizeof(cnt), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+                    if (launch_debug_depth_order((uint32_t)P, cnt[2], cnt[0], g.dkeys_a, g.rect, g.point_offsets,
+                                                 which == 9 ? (uint32_t*)dst : nullptr, which == 8 ? (uint32_t*)dst : nullptr)) return -1;
                 }
                 return (long long)n;
+            }
+            case 2: src = g.rec; n = Ps * sizeof(SplatRec); break;
+            // (case 9: above)
             default: return -1;
         }
     } else if (which < 20 || which == 30) {

@@ -69,10 +69,12 @@ GS_DEV uint32_t block_excl_scan(uint32_t v, uint32_t* smem_warp, uint32_t* total
 // ------------------------------------------------------------------------------------------------
 GS_DEV uint32_t rect_tiles(const uint2 rc) { return (rc.y & 0xffffu) * (rc.y >> 16); }
 
-__global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uint4* __restrict__ emit, int n,
+__global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uint4* __restrict__ emit, int n_host,
+                                                                       const uint32_t* __restrict__ n_dev,
                                                                        uint32_t* __restrict__ block_sums) {
     pdl_trigger();
     pdl_wait();
+    const int n = n_dev ? (int)*n_dev : n_host;   // the grid is sized for n_host >= n; blocks past the end sum nothing
     __shared__ uint32_t sw[33];
     const size_t base = (size_t)blockIdx.x * kScanBlock;
     uint32_t s = 0;
@@ -89,10 +91,13 @@ __global__ void __launch_bounds__(kScanThreads) scan_block_sums_kernel(const uin
 // emit[r].w: tile count in, first emission slot out; out[r] = first slot of rank r + 1.
 // Warp w of a block owns 256 consecutive entries and walks them 32 at a time (lane-consecutive 16-byte loads and stores:
 // the table moves as whole, coalesced uint4s), carrying the running sum from round to round.
-__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(int n, const uint32_t* __restrict__ block_sums,
+__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(int n_host, const uint32_t* __restrict__ n_dev,
+                                                                  const uint32_t* __restrict__ block_sums,
                                                                   uint32_t* __restrict__ out, uint4* __restrict__ emit) {
     pdl_trigger();
     pdl_wait();
+    const int n = n_dev ? (int)*n_dev : n_host;
+    if ((size_t)blockIdx.x * kScanBlock >= (size_t)n) return;
     __shared__ uint32_t sw[kScanThreads / 32], sb[kScanThreads / 32];
     static_assert(kScanItems * 32 * (kScanThreads / 32) == kScanBlock, "one warp per kScanItems * 32 entries");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -130,11 +135,12 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(int n, const u
 }
 
 // emit: the depth-ordered table (idx, x0 | y0 << 16, w | h << 16, tile count) written by the last pass of launch_depth_sort.
-int launch_inclusive_scan(int n, uint32_t* out, uint4* emit, uint32_t* block_sums, cudaStream_t stream) {
+// n_dev (optional): the entry count on the device (<= n, which then only sizes the grids).
+int launch_inclusive_scan(int n, const uint32_t* n_dev, uint32_t* out, uint4* emit, uint32_t* block_sums, cudaStream_t stream) {
     if (n <= 0) return GS_OK;
     const int nb = (n + kScanBlock - 1) / kScanBlock;
-    launch_pdl(scan_block_sums_kernel, dim3(nb), dim3(kScanThreads), 0, stream, emit, n, block_sums);
-    launch_pdl(scan_apply_kernel, dim3(nb), dim3(kScanThreads), 0, stream, n, block_sums, out, emit);
+    launch_pdl(scan_block_sums_kernel, dim3(nb), dim3(kScanThreads), 0, stream, emit, n, n_dev, block_sums);
+    launch_pdl(scan_apply_kernel, dim3(nb), dim3(kScanThreads), 0, stream, n, n_dev, block_sums, out, emit);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
@@ -146,8 +152,10 @@ int launch_inclusive_scan(int n, uint32_t* out, uint4* emit, uint32_t* block_sum
 // ------------------------------------------------------------------------------------------------
 constexpr uint32_t kCoopTiles = 16;
 
-__global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint4* __restrict__ emit, uint2 grid,
+__global__ void __launch_bounds__(256) emit_instances_kernel(int P_host, const uint32_t* __restrict__ n_dev,
+                                                             const uint4* __restrict__ emit, uint2 grid,
                                                              uint64_t* __restrict__ inst) {
+    const int P = n_dev ? (int)*n_dev : P_host;   // depth ranks that exist (the visible Gaussians)
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     uint32_t off = 0, w = 0, h = 0, idx = 0, x0 = 0, y0 = 0;
@@ -180,9 +188,9 @@ __global__ void __launch_bounds__(256) emit_instances_kernel(int P, const uint4*
     }
 }
 
-int launch_emit_instances(int P, const uint4* emit, uint2 grid, uint64_t* inst, cudaStream_t stream) {
+int launch_emit_instances(int P, const uint32_t* n_dev, const uint4* emit, uint2 grid, uint64_t* inst, cudaStream_t stream) {
     if (P <= 0) return GS_OK;
-    emit_instances_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, emit, grid, inst);
+    emit_instances_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, n_dev, emit, grid, inst);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
@@ -477,10 +485,12 @@ GS_DEV uint32_t peer_mask(const uint32_t d) {
 }
 
 // Depth rank of the Gaussian owning the first / last emission slot of every pass-1 block.
-__global__ void __launch_bounds__(256) block_bounds_kernel(int P, const uint32_t* __restrict__ offsets, uint32_t R,
+__global__ void __launch_bounds__(256) block_bounds_kernel(int P_host, const uint32_t* __restrict__ n_dev,
+                                                            const uint32_t* __restrict__ offsets, uint32_t R,
                                                             uint32_t* __restrict__ first, uint32_t* __restrict__ last) {
     pdl_trigger();
     pdl_wait();
+    const int P = n_dev ? (int)*n_dev : P_host;
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= P) return;
     const uint32_t s1 = offsets[r], s0 = r ? offsets[r - 1] : 0u;
@@ -711,7 +721,9 @@ struct BinScatterParams {
     uint32_t* __restrict__ keys32_out;
     int kshift;                              // 32 - bits2
     uint32_t* __restrict__ ids_out;          // pass 2 output
-    uint32_t n;                              // R
+    uint32_t n;                              // R (pass 0: number of keys, or its upper bound when n_dev is set)
+    const uint32_t* __restrict__ n_dev;      // pass 0, optional: the key count on the device (the visible Gaussians)
+    int drop_sentinel;                       // pass 0, first pass: keys whose depth word is ~0 (culled) are not carried on
     uint32_t nb;
     int shift, bits;                         // digit = (tile >> shift) & (2^bits - 1)
     const uint32_t* __restrict__ scanned;    // [2^bits][nb] exclusive scan over blocks (bin_scan_kernel)
@@ -733,8 +745,9 @@ struct BinKey<0> { using type = uint64_t; };
 // group's lowest lane advances the digit's running count and clears the word. ~15 instructions per slot against ~55 for
 // the BITS ballots + leader election of peer_mask<BITS> (kept as the other template branch; GS_BIN_RANK=ballot selects it).
 template <int PASS, int BITS, bool kAtomicPeers, bool kFull>
-GS_DEV void bin_scatter_body(const BinScatterParams& p, typename BinKey<PASS>::type* __restrict__ s_keys, uint8_t* __restrict__ s_dig,
-                             uint32_t (*s_hist)[256], uint32_t* __restrict__ s_gbase, uint32_t* __restrict__ s_scan) {
+GS_DEV void bin_scatter_body(const BinScatterParams& p, const uint32_t n_keys, typename BinKey<PASS>::type* __restrict__ s_keys,
+                             uint8_t* __restrict__ s_dig, uint32_t (*s_hist)[256], uint32_t* __restrict__ s_gbase,
+                             uint32_t* __restrict__ s_scan) {
     using Key = typename BinKey<PASS>::type;
     // per-warp peer masks [warps][256]: s_keys is idle while the ranks are formed (pass 1: its first 8 KB are the owner
     // table, the masks take the second 8 KB)
@@ -752,7 +765,7 @@ GS_DEV void bin_scatter_body(const BinScatterParams& p, typename BinKey<PASS>::t
     __syncthreads();
     const uint32_t tile = blockIdx.x;
     const uint32_t slot_begin = tile * (uint32_t)kBinTile;
-    const uint32_t tile_n = kFull ? (uint32_t)kBinTile : min((uint32_t)kBinTile, p.n - slot_begin);
+    const uint32_t tile_n = kFull ? (uint32_t)kBinTile : min((uint32_t)kBinTile, n_keys - slot_begin);
     const uint32_t warp_base = warp * (32 * kBinItems) + lane;   // item i of this thread is slot warp_base + 32 i
 
     // ---- 1. keys into registers, warp-striped; dig[k >> 2] byte (k & 3) = digit of item k ----
@@ -830,13 +843,20 @@ GS_DEV void bin_scatter_body(const BinScatterParams& p, typename BinKey<PASS>::t
     const uint32_t lt_mask = (1u << lane) - 1u;
     uint16_t rank[kBinItems];
     uint32_t* const wh = s_hist[warp];
+    // does slot k of this thread hold a key? (first depth-sort pass: sentinel keys - culled Gaussians, and the ~0 padding
+    // past the end - are dropped here, so the later passes, the scans and the emission table see the visible ones only)
+    auto item_valid = [&](const int k) -> bool {
+        if (kFull) return true;
+        if (PASS == 0 && p.drop_sentinel) return (uint32_t)((uint64_t)key[k] >> 32) != 0xffffffffu;
+        return warp_base + k * 32 < tile_n;
+    };
     if (kAtomicPeers) {
         // same 256-word stride per warp as s_hist: a digit's mask and its running count sit at a constant distance
         const ptrdiff_t peer_off = (s_peer + warp * 256) - wh;
         const uint32_t lane_bit = 1u << lane;
 #pragma unroll
         for (int k = 0; k < kBinItems; ++k) {
-            const bool valid = kFull || warp_base + k * 32 < tile_n;
+            const bool valid = item_valid(k);
             uint32_t* const hp = wh + ((dig[k >> 2] >> (8 * (k & 3))) & 0xffu);
             if (valid) atomicOr(hp + peer_off, lane_bit);
             __syncwarp();
@@ -857,7 +877,7 @@ GS_DEV void bin_scatter_body(const BinScatterParams& p, typename BinKey<PASS>::t
     } else {
 #pragma unroll
         for (int k = 0; k < kBinItems; ++k) {
-            const bool valid = kFull || warp_base + k * 32 < tile_n;
+            const bool valid = item_valid(k);
             const uint32_t d = (dig[k >> 2] >> (8 * (k & 3))) & 0xffu;   // invalid slots are masked out below
             const uint32_t peers = peer_mask<BITS>(d) & __ballot_sync(0xffffffffu, valid);
             const int leader = __ffs(peers) - 1;
@@ -888,6 +908,7 @@ GS_DEV void bin_scatter_body(const BinScatterParams& p, typename BinKey<PASS>::t
     }
     uint32_t total;
     const uint32_t lbase = block_excl_scan(count, s_scan, &total);   // start of digit d's run inside the block
+    const uint32_t block_keys = total;                               // keys of this block that are carried on
     const uint32_t dbase = block_excl_scan(tot_d, s_scan, &total);   // start of digit d in the output
     if (tid < bins) {
 #pragma unroll
@@ -900,7 +921,7 @@ GS_DEV void bin_scatter_body(const BinScatterParams& p, typename BinKey<PASS>::t
 #pragma unroll
     for (int i = 0; i < kBinItems; ++i) {
         const uint32_t e = warp_base + i * 32;
-        if (kFull || e < tile_n) {
+        if (item_valid(i)) {
             const uint32_t d = (dig[i >> 2] >> (8 * (i & 3))) & 0xffu;
             const uint32_t at = s_hist[warp][d] + rank[i];
             // pass 2 reads its word again (L1 / L2 hit) instead of carrying 16 registers through the ranking: the freed
@@ -915,7 +936,7 @@ GS_DEV void bin_scatter_body(const BinScatterParams& p, typename BinKey<PASS>::t
 #pragma unroll
     for (int i = 0; i < kBinItems; ++i) {
         const uint32_t s = i * kBinThreads + tid;
-        if (kFull || s < tile_n) {
+        if (kFull || s < block_keys) {
             const Key k = s_keys[s];
             uint32_t d;
             if (PASS == 0) d = (uint32_t)((uint64_t)k >> (32 + p.shift)) & dmask;
@@ -946,20 +967,24 @@ __global__ void __launch_bounds__(kBinThreads, MINB) bin_scatter_kernel(const Bi
     __shared__ uint32_t s_hist[kBinThreads / 32][256];               // per-warp digit counts -> block positions
     __shared__ uint32_t s_gbase[256];                                // global position of slot 0 of each digit's run
     __shared__ uint32_t s_scan[33];
-    if ((blockIdx.x + 1u) * (uint32_t)kBinTile <= p.n) bin_scatter_body<PASS, BITS, kAtomicPeers, true>(p, s_keys, s_dig, s_hist, s_gbase, s_scan);
-    else bin_scatter_body<PASS, BITS, kAtomicPeers, false>(p, s_keys, s_dig, s_hist, s_gbase, s_scan);
+    const uint32_t n_keys = (PASS == 0 && p.n_dev) ? *p.n_dev : p.n;
+    if (blockIdx.x * (uint32_t)kBinTile >= n_keys) return;   // the grid was sized for an upper bound
+    if ((blockIdx.x + 1u) * (uint32_t)kBinTile <= n_keys && !(PASS == 0 && p.drop_sentinel)) bin_scatter_body<PASS, BITS, kAtomicPeers, true>(p, n_keys, s_keys, s_dig, s_hist, s_gbase, s_scan);
+    else bin_scatter_body<PASS, BITS, kAtomicPeers, false>(p, n_keys, s_keys, s_dig, s_hist, s_gbase, s_scan);
 }
 
 // hist[d][b] = number of keys of block b whose digit (key >> shift) & (2^bits - 1) is d. Generic counterpart of
 // bin_count1/2 for plain u64 keys (the depth ordering of the Gaussians).
-__global__ void __launch_bounds__(kBinThreads) bin_count_kernel(const uint64_t* __restrict__ keys, uint32_t n, int shift, int bits,
+__global__ void __launch_bounds__(kBinThreads) bin_count_kernel(const uint64_t* __restrict__ keys, uint32_t n_host,
+                                                                 const uint32_t* __restrict__ n_dev, int drop_sentinel, int shift, int bits,
                                                                  uint32_t* __restrict__ hist, uint32_t nb, uint32_t* __restrict__ totals, uint32_t* __restrict__ done_counter) {
     pdl_trigger();
     pdl_wait();
     __shared__ uint32_t s_h[kBinThreads / 32][256];
     const int tid = threadIdx.x, warp = tid >> 5;
     const uint32_t b = blockIdx.x;
-    const uint32_t slot_begin = b * (uint32_t)kBinTile, cnt = min((uint32_t)kBinTile, n - slot_begin);
+    const uint32_t n = n_dev ? *n_dev : n_host;   // blocks past the end count nothing (their histogram columns are zero)
+    const uint32_t slot_begin = b * (uint32_t)kBinTile, cnt = slot_begin < n ? min((uint32_t)kBinTile, n - slot_begin) : 0u;
     const uint32_t dmask = (1u << bits) - 1u;
     for (int i = tid; i < (kBinThreads / 32) * 256; i += kBinThreads) (&s_h[0][0])[i] = 0;
     __syncthreads();
@@ -973,7 +998,7 @@ __global__ void __launch_bounds__(kBinThreads) bin_count_kernel(const uint64_t* 
 #pragma unroll
     for (int i = 0; i < kBinItems; ++i) {
         const uint32_t e = i * kBinThreads + tid;
-        if (e < cnt) atomicAdd(&s_h[warp][(uint32_t)(kv[i] >> shift) & dmask], 1u);
+        if (e < cnt && !(drop_sentinel && (uint32_t)(kv[i] >> 32) == 0xffffffffu)) atomicAdd(&s_h[warp][(uint32_t)(kv[i] >> shift) & dmask], 1u);
     }
     __syncthreads();
     if (tid < (1 << bits)) {
@@ -1040,7 +1065,7 @@ static int dispatch_scatter(int bits, const BinScatterParams& sp, uint32_t nb, c
     }
     return GS_OK;
 }
-int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1, int bits2, const uint4* emit,
+int launch_fast_binning(int P, const uint32_t* n_dev, uint32_t R, uint2 grid, uint32_t tiles, int bits1, int bits2, const uint4* emit,
                         const uint32_t* offsets, const BinningWS& b, uint2* ranges, cudaStream_t stream) {
     GS_CUDA_TRY(cudaMemsetAsync(b.tile_counts, 0, (size_t)tiles * sizeof(uint32_t), stream));
     if (R == 0 || P <= 0) {
@@ -1049,12 +1074,12 @@ int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1
     }
     const uint32_t nb = (R + kBinTile - 1) / kBinTile;
     const int bins1 = 1 << bits1, bins2 = 1 << bits2;
-    launch_pdl(block_bounds_kernel, dim3((P + 255) / 256), dim3(256), 0, stream, P, offsets, R, b.block_first, b.block_last);
+    launch_pdl(block_bounds_kernel, dim3((P + 255) / 256), dim3(256), 0, stream, P, n_dev, offsets, R, b.block_first, b.block_last);
     launch_pdl(bin_count1_kernel, dim3(nb), dim3(kBinThreads), 0, stream, emit, b.block_first, b.block_last, R, grid.x, bits1, b.hist1, nb);
     launch_pdl(bin_scan_kernel, dim3(bins1), dim3(1024), 0, stream, b.hist1, nb, bins1, b.totals, nullptr, 0u, nullptr);
     BinScatterParams sp;
     sp.emit = emit; sp.offsets = offsets; sp.block_first = b.block_first; sp.block_last = b.block_last; sp.grid_x = grid.x;
-    sp.keys_in = nullptr; sp.keys_out = nullptr; sp.rect = nullptr; sp.emit_out = nullptr; sp.keys32_in = nullptr; sp.keys32_out = b.keys1; sp.kshift = 32 - bits2;
+    sp.keys_in = nullptr; sp.keys_out = nullptr; sp.rect = nullptr; sp.emit_out = nullptr; sp.n_dev = nullptr; sp.drop_sentinel = 0; sp.keys32_in = nullptr; sp.keys32_out = b.keys1; sp.kshift = 32 - bits2;
     sp.ids_out = nullptr; sp.n = R; sp.nb = nb;
     sp.shift = 0; sp.bits = bits1; sp.scanned = b.hist1; sp.totals = b.totals;
     int rc = dispatch_scatter<1>(bits1, sp, nb, stream);
@@ -1072,8 +1097,10 @@ int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1
 // Stable LSD sort of n u64 keys on the 32 bits [32, 64) in four 8-bit passes (count -> scan -> scatter each, no
 // look-back): the depth ordering of the Gaussians. The sorted keys end up in keys_a. scratch: (256 * nb + 256 + 1) u32.
 // rect / emit (optional, both or neither): the last pass also writes emit[rank] = (idx, rect[idx].x, rect[idx].y, tiles).
-int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* scratch, const uint2* rect, uint4* emit,
-                      cudaStream_t stream) {
+// n_dev (optional): the input's n keys include sentinels (depth word ~0); *n_dev of them are real. The sentinels are dropped
+// by the first pass and the sorted real keys end up in keys_a[0, *n_dev).
+int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, const uint32_t* n_dev, uint32_t* scratch, const uint2* rect,
+                      uint4* emit, cudaStream_t stream) {
     if (n == 0) return GS_OK;
     const uint32_t nb = (n + kBinTile - 1) / kBinTile;
     uint32_t* hist = scratch;
@@ -1085,14 +1112,18 @@ int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* 
     for (int pass = 0; pass < 4; ++pass) {
         const uint64_t* in = (pass & 1) ? keys_b : keys_a;
         uint64_t* out = (pass & 1) ? keys_a : keys_b;
+        // n_dev set: the input holds n keys of which *n_dev are real and the rest carry the sentinel depth ~0. The first pass
+        // reads all n and drops the sentinels; from then on only *n_dev keys exist.
+        const int drop = (n_dev != nullptr && pass == 0) ? 1 : 0;
+        const uint32_t* pass_n_dev = pass == 0 ? nullptr : n_dev;
         if (fuse_scan) {
-            launch_pdl(bin_count_kernel, dim3(nb), dim3(kBinThreads), 0, stream, in, n, 32 + 8 * pass, 8, hist, nb, totals, done_counter);
+            launch_pdl(bin_count_kernel, dim3(nb), dim3(kBinThreads), 0, stream, in, n, pass_n_dev, drop, 32 + 8 * pass, 8, hist, nb, totals, done_counter);
         } else {
-            launch_pdl(bin_count_kernel, dim3(nb), dim3(kBinThreads), 0, stream, in, n, 32 + 8 * pass, 8, hist, nb, (uint32_t*)nullptr, (uint32_t*)nullptr);
+            launch_pdl(bin_count_kernel, dim3(nb), dim3(kBinThreads), 0, stream, in, n, pass_n_dev, drop, 32 + 8 * pass, 8, hist, nb, (uint32_t*)nullptr, (uint32_t*)nullptr);
             launch_pdl(bin_scan_kernel, dim3(256), dim3(1024), 0, stream, hist, nb, 256, totals, nullptr, 0u, nullptr);
         }
         BinScatterParams sp = {};
-        sp.keys_in = in; sp.keys_out = out; sp.n = n; sp.nb = nb; sp.shift = 8 * pass; sp.bits = 8;
+        sp.keys_in = in; sp.keys_out = out; sp.n = n; sp.n_dev = pass_n_dev; sp.drop_sentinel = drop; sp.nb = nb; sp.shift = 8 * pass; sp.bits = 8;
         sp.scanned = hist; sp.totals = totals;
         if (pass == 3) { sp.rect = rect; sp.emit_out = emit; }
         launch_scatter<0, 8>(sp, nb, stream);
@@ -1171,6 +1202,37 @@ int launch_debug_unpack(int which, uint32_t P, const SplatRec* rec, const uint2*
 __global__ void __launch_bounds__(256) debug_low32_kernel(uint32_t n, const uint64_t* __restrict__ in, uint32_t* __restrict__ out) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = (uint32_t)in[i];
+}
+
+// Tests read the depth order and its scan as P-sized arrays with the culled Gaussians last (in index order, zero tiles each).
+// One block: the visible prefix is the sorted keys' low words, the culled ones are compacted behind it.
+__global__ void __launch_bounds__(1024) debug_depth_order_kernel(uint32_t P, uint32_t n_vis, uint32_t R, const uint64_t* __restrict__ sorted,
+                                                                 const uint2* __restrict__ rect, const uint32_t* __restrict__ offsets,
+                                                                 uint32_t* __restrict__ order_out, uint32_t* __restrict__ offsets_out) {
+    __shared__ uint32_t sw[33];
+    for (uint32_t i = threadIdx.x; i < P; i += 1024) {
+        if (order_out && i < n_vis) order_out[i] = (uint32_t)sorted[i];
+        if (offsets_out) offsets_out[i] = i < n_vis ? offsets[i] : R;
+    }
+    if (!order_out) return;
+    uint32_t carry = n_vis;
+    for (uint32_t base = 0; base < P; base += 1024) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t c = (i < P && rect_tiles(rect[i]) == 0u) ? 1u : 0u;
+        uint32_t total;
+        const uint32_t ex = block_excl_scan(c, sw, &total);
+        if (c) order_out[carry + ex] = i;
+        carry += total;
+    }
+}
+
+int launch_debug_depth_order(uint32_t P, uint32_t n_vis, uint32_t R, const uint64_t* sorted, const uint2* rect, const uint32_t* offsets,
+                             uint32_t* order_out, uint32_t* offsets_out) {
+    if (P == 0) return GS_OK;
+    debug_depth_order_kernel<<<1, 1024>>>(P, n_vis, R, sorted, rect, offsets, order_out, offsets_out);
+    GS_LAUNCH_CHECK();
+    GS_CUDA_TRY(cudaDeviceSynchronize());
+    return GS_OK;
 }
 
 int launch_debug_low32(uint32_t n, const uint64_t* in, uint32_t* out) {

@@ -30,9 +30,9 @@ struct PreprocessParams {
     float* __restrict__ cov3D;
     uint8_t* __restrict__ clamped;
     SplatRec* __restrict__ rec;          // [P] render records (visible Gaussians only)
-    uint64_t* __restrict__ depth_keys;   // [P] (depth_bits << 32 | idx); depth_bits = ~0 when culled
+    uint64_t* __restrict__ depth_keys;   // [P] (depth_bits << 32 | idx); depth_bits = ~0 when culled (dropped by the sort's first pass)
     uint2* __restrict__ rect;            // [P] (x0 | y0 << 16, w | h << 16) tile rectangle, zero when culled
-    uint32_t* __restrict__ num_rendered; // [1] += sum of tiles_touched (zeroed by the caller)
+    uint32_t* __restrict__ num_rendered; // [0] += sum of tiles_touched, [2] += visible Gaussians (zeroed by the caller)
 };
 
 struct RenderFwdParams {
@@ -177,19 +177,21 @@ struct AdamLaunch {
 
 int launch_preprocess_fwd(const PreprocessParams& p, cudaStream_t stream);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
-int launch_inclusive_scan(int n, uint32_t* out, uint4* emit, uint32_t* block_sums, cudaStream_t stream);
-int launch_fast_binning(int P, uint32_t R, uint2 grid, uint32_t tiles, int bits1, int bits2, const uint4* emit,
+int launch_inclusive_scan(int n, const uint32_t* n_dev, uint32_t* out, uint4* emit, uint32_t* block_sums, cudaStream_t stream);
+int launch_fast_binning(int P, const uint32_t* n_dev, uint32_t R, uint2 grid, uint32_t tiles, int bits1, int bits2, const uint4* emit,
                         const uint32_t* offsets, const BinningWS& b, uint2* ranges, cudaStream_t stream);
-int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, uint32_t* scratch, const uint2* rect, uint4* emit,
-                      cudaStream_t stream);
+int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, const uint32_t* n_dev, uint32_t* scratch, const uint2* rect,
+                      uint4* emit, cudaStream_t stream);
 int launch_strip_ids(uint32_t n, const uint64_t* in, uint32_t* out, cudaStream_t stream);
-int launch_emit_instances(int P, const uint4* emit, uint2 grid, uint64_t* inst, cudaStream_t stream);
+int launch_emit_instances(int P, const uint32_t* n_dev, const uint4* emit, uint2 grid, uint64_t* inst, cudaStream_t stream);
 int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, int first_bit, int passes, char* scratch,
                       uint32_t* error_flag, cudaStream_t stream);
 int launch_tile_ranges(uint32_t R, const uint64_t* inst, uint2* ranges, uint32_t tiles, cudaStream_t stream);
 int launch_debug_expand(uint32_t tiles, const uint2* ranges, const uint32_t* ids, const SplatRec* rec, uint64_t* keys, uint64_t* raw);
 int launch_debug_unpack(int which, uint32_t P, const SplatRec* rec, const uint2* rect, void* dst);
 int launch_debug_low32(uint32_t n, const uint64_t* in, uint32_t* out);
+int launch_debug_depth_order(uint32_t P, uint32_t n_vis, uint32_t R, const uint64_t* sorted, const uint2* rect, const uint32_t* offsets,
+                             uint32_t* order_out, uint32_t* offsets_out);
 int launch_render_fwd(const RenderFwdParams& p, int tiles, cudaStream_t stream);
 int launch_render_bwd(const RenderBwdParams& p, int tiles, cudaStream_t stream);
 int launch_render_work(const RenderBwdParams& p, int tiles, uint32_t* walked, uint32_t* survivors, cudaStream_t stream);

@@ -249,7 +249,7 @@ int launch_knn_mean_dist2(int P, const float* points, float* out, char* ws, cuda
     knn_bounds_final_kernel<<<1, 32, 0, stream>>>(rblocks, bounds + 1, bounds);
     knn_keys_kernel<<<blocks, kKnnThreads, 0, stream>>>(P, points, bounds, keys_a);
     GS_LAUNCH_CHECK();
-    const int rc = launch_depth_sort(keys_a, keys_b, (uint32_t)P, scratch, nullptr, nullptr, stream);
+    const int rc = launch_depth_sort(keys_a, keys_b, (uint32_t)P, nullptr, scratch, nullptr, nullptr, stream);
     if (rc) return rc;
     knn_gather_kernel<<<blocks, kKnnThreads, 0, stream>>>(P, keys_a, points, codes, sorted);
     knn_search_kernel<<<blocks, kKnnThreads, 0, stream>>>(P, codes, sorted, bounds, out);

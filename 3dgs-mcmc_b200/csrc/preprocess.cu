@@ -125,10 +125,10 @@ constexpr int kPfThreads = 128;
 template <bool kSplit>
 __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const PreprocessParams p) {
     __shared__ __align__(16) float s_sh[kPfThreads / 32][kShTileFloats];
-    __shared__ uint32_t s_tiles;
+    __shared__ uint32_t s_tiles, s_vis;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) s_tiles = 0;
+    if (threadIdx.x == 0) { s_tiles = 0; s_vis = 0; }
     __syncthreads();
     const bool valid = idx < p.P;
     const size_t i = (size_t)(valid ? idx : 0);
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const Prepro
     int out_radius = 0;
     uint32_t out_tiles = 0;
     uint2 out_rect = {0u, 0u};
-    uint32_t depth_bits = 0xffffffffu;  // culled Gaussians sort behind every visible one
+    uint32_t depth_bits = 0xffffffffu;  // sentinel: culled Gaussians are dropped by the first depth-sort pass
 
     const float3 p_orig = {p.means3D[3 * i], p.means3D[3 * i + 1], p.means3D[3 * i + 2]};
     const float4 p_hom = xform_point_4x4(p_orig, p.projmatrix);
@@ -262,13 +262,20 @@ __global__ void __launch_bounds__(kPfThreads) preprocess_fwd_kernel(const Prepro
         p.is_used[idx] = 0;
         p.radii[idx] = out_radius;
         p.rect[idx] = out_rect;
-        p.depth_keys[idx] = ((uint64_t)depth_bits << 32) | (uint32_t)idx;
+        p.depth_keys[idx] = ((uint64_t)depth_bits << 32) | (uint32_t)idx;   // index order: ties in depth stay in index order
     }
     // Instance count R = sum of tiles_touched: one atomic per warp into shared memory, one per block to global.
     const uint32_t wsum = __reduce_add_sync(0xffffffffu, out_tiles);
     if (lane == 0 && wsum) atomicAdd(&s_tiles, wsum);
+    // num_rendered[2] counts the visible Gaussians: the depth sort drops the culled ones (sentinel keys) in its first pass
+    // and runs its other passes, the scans and the emission table on the visible ones only.
+    const uint32_t vis_mask = __ballot_sync(0xffffffffu, visible);
+    if (lane == 0 && vis_mask) atomicAdd(&s_vis, (uint32_t)__popc(vis_mask));
     __syncthreads();
-    if (threadIdx.x == 0 && s_tiles) atomicAdd(p.num_rendered, s_tiles);
+    if (threadIdx.x == 0) {
+        if (s_tiles) atomicAdd(p.num_rendered, s_tiles);
+        if (s_vis) atomicAdd(p.num_rendered + 2, s_vis);
+    }
 }
 
 __global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* __restrict__ means3D,

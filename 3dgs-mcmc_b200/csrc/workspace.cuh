@@ -80,7 +80,7 @@ struct GeomWS {
     uint8_t* clamped;         // [P]   bit c set when channel c was clamped to 0
     uint32_t* point_offsets;  // [P]   inclusive scan of tiles_touched taken in depth order
     uint32_t* scan_block_sums;  // [ceil(P/kScanBlock)+1]
-    uint32_t* num_rendered;   // [0] device copy of R, [1] depth-sort error flag
+    uint32_t* num_rendered;   // [0] device copy of R, [1] depth-sort error flag, [2] number of visible Gaussians (= depth keys)
     uint2* rect;              // [P]   (x0 | y0 << 16, w | h << 16) tile rectangle; w = h = 0 when culled
     uint4* emit;              // [P]   depth-ordered emission table: (idx, x0 | y0 << 16, w | h << 16, first slot)
     uint64_t* dkeys_a;        // [P]   (depth_bits << 32 | idx), culled Gaussians carry depth_bits = ~0; sorted in place
