@@ -50,13 +50,13 @@ constexpr int kBwdWarps = GS_TILE_PIX / 32;
 constexpr int kRowPitch = 36;
 
 // Dynamic shared-memory layout of render_bwd_kernel<CH, ROWS>.
-template <int CH, int ROWS>
+template <int CH, int ROWS, int RS = kRecStages>
 struct BwdSmem {
     static constexpr size_t kRec = 0;
-    static constexpr size_t kInst = kRec + sizeof(SplatRec) * kRecStages * CH;
+    static constexpr size_t kInst = kRec + sizeof(SplatRec) * RS * CH;
     static constexpr size_t kInstFull = kInst + sizeof(uint32_t) * kInstStages * (CH + kInstPad);
     static constexpr size_t kRecFull = kInstFull + sizeof(uint64_t) * kInstStages;
-    static constexpr size_t kRows = (kRecFull + sizeof(uint64_t) * kRecStages + 127) / 128 * 128;
+    static constexpr size_t kRows = (kRecFull + sizeof(uint64_t) * RS + 127) / 128 * 128;
     static constexpr size_t kDpix = kRows + sizeof(float) * kBwdWarps * 2 * ROWS * kRowPitch;
     static constexpr size_t kBytes = kDpix + sizeof(float4) * kBwdWarps * 32;
 };
@@ -172,9 +172,9 @@ GS_DEV void flush_rows(const RenderBwdParams& p, const float* __restrict__ U, co
     __syncwarp();  // the rows may be overwritten once every lane has read them
 }
 
-template <int CH, int ROWS, int MIN_CTAS>
+template <int CH, int ROWS, int MIN_CTAS, int RS = kRecStages, int GA = kGatherAhead>
 __global__ void __launch_bounds__(GS_TILE_PIX, MIN_CTAS) render_bwd_kernel(const RenderBwdParams p) {
-    using L = BwdSmem<CH, ROWS>;
+    using L = BwdSmem<CH, ROWS, RS>;
     extern __shared__ __align__(128) unsigned char smem[];
     SplatRec* s_rec = reinterpret_cast<SplatRec*>(smem + L::kRec);
     uint32_t* s_inst = reinterpret_cast<uint32_t*>(smem + L::kInst);
@@ -196,10 +196,10 @@ __global__ void __launch_bounds__(GS_TILE_PIX, MIN_CTAS) render_bwd_kernel(const
     const int nchunks = (n_total + CH - 1) / CH;
     if (nchunks == 0) return;
 
-    if (tid == 0) stager_init<CH>(s_inst_full, s_rec_full);
+    if (tid == 0) stager_init<CH, RS>(s_inst_full, s_rec_full);
     __syncthreads();
     // Stream chunk k is list chunk c = nchunks-1-k.
-    Stager<CH> st(p.ids, p.rec, range.x, n_total, nchunks, /*reversed=*/true, s_inst, s_inst_full, s_rec, s_rec_full);
+    Stager<CH, RS, GA> st(p.ids, p.rec, range.x, n_total, nchunks, /*reversed=*/true, s_inst, s_inst_full, s_rec, s_rec_full);
     st.prologue(tid);
 
     float* const U = reinterpret_cast<float*>(smem + L::kRows) + warp * (2 * ROWS * kRowPitch);
@@ -236,10 +236,10 @@ __global__ void __launch_bounds__(GS_TILE_PIX, MIN_CTAS) render_bwd_kernel(const
     for (int k = 0; k < nchunks; ++k) {
         if (k > 0) __syncthreads();  // every warp is done with chunk k-1: its stages can be refilled
         st.advance(tid, k);
-        const int s = k % kRecStages;
+        const int s = k % RS;
         const int c = nchunks - 1 - k;
         const int n = min(CH, n_total - c * CH);
-        mbar_wait(&s_rec_full[s], (uint32_t)((k / kRecStages) & 1));
+        mbar_wait(&s_rec_full[s], (uint32_t)((k / RS) & 1));
         const float4* __restrict__ rec = reinterpret_cast<const float4*>(s_rec + s * CH);
         // Positions >= warp_last were blended by no pixel of this warp.
         const int jstart = min(n - 1, warp_last - 1 - c * CH);
@@ -304,10 +304,10 @@ __global__ void __launch_bounds__(GS_TILE_PIX, MIN_CTAS) render_bwd_kernel(const
     st.drain(tid);  // every copy was consumed (no early exit); this only retires the cp.async groups
 }
 
-template <int CH, int ROWS, int MIN_CTAS>
+template <int CH, int ROWS, int MIN_CTAS, int RS = kRecStages, int GA = kGatherAhead>
 static int launch_variant(const RenderBwdParams& p, int tiles, cudaStream_t stream) {
-    auto kern = render_bwd_kernel<CH, ROWS, MIN_CTAS>;
-    constexpr size_t bytes = BwdSmem<CH, ROWS>::kBytes;
+    auto kern = render_bwd_kernel<CH, ROWS, MIN_CTAS, RS, GA>;
+    constexpr size_t bytes = BwdSmem<CH, ROWS, RS>::kBytes;
     GS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     kern<<<tiles, GS_TILE_PIX, bytes, stream>>>(p);
     GS_LAUNCH_CHECK();
@@ -360,11 +360,17 @@ int launch_render_work(const RenderBwdParams& p, int tiles, uint32_t* walked, ui
 
 int launch_render_bwd(const RenderBwdParams& p, int tiles, cudaStream_t stream) {
     if (tiles <= 0) return GS_OK;
-    static const int variant = [] { const char* e = getenv("GS_BWD_VARIANT"); return e ? atoi(e) : 0; }();
+    // GS_BWD_VARIANT (measurement). Default since round 2: 128-record chunks, two record stages (55 KB of shared memory), 64
+    // registers -> 4 CTAs per SM. After the per-pair instruction cuts the kernel no longer saturates the issue slots at 3 CTAs
+    // (72.6 % issue utilisation, few eligible warps): 1.182 -> 1.138 ms. 0 = three record stages at 80 registers / 3 CTAs
+    // (round 1), 1 = 64-record chunks at 4 CTAs (1.166), 2 = 8-row flushes at 4 CTAs (1.187), 3 = 256-record chunks (1.182).
+    static const int variant = [] { const char* e = getenv("GS_BWD_VARIANT"); return e ? atoi(e) : 4; }();
     switch (variant) {
+        case 0: return launch_variant<128, 16, 3>(p, tiles, stream);
         case 1: return launch_variant<64, 16, 4>(p, tiles, stream);
         case 2: return launch_variant<128, 8, 4>(p, tiles, stream);
-        default: return launch_variant<128, 16, 3>(p, tiles, stream);
+        case 3: return launch_variant<256, 16, 3, 2, 1>(p, tiles, stream);
+        default: return launch_variant<128, 16, 4, 2, 1>(p, tiles, stream);
     }
 }
 
