@@ -441,6 +441,8 @@ def run_b200_arm(args):
         ncu_traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
     except Exception:
         ncu_traffic = {}
+    if not (args.config == "headline" and (P, W, H) == (3_000_000, 1920, 1080)):
+        ncu_traffic = {}   # the capture is of the headline workload: no DRAM-traffic figure is quoted for other configs
     dom = max(("render_bwd", "render_fwd", "tile_sort", "preprocess_bwd", "preprocess_fwd"),
               key=lambda n: stage_ms(n) or 0.0)
     dom_ms = stage_ms(dom)
