@@ -893,33 +893,46 @@ def exchange_parity_leg(torch, dist, C, dp, dev, s, c, campos_views, bg, dL, exc
     R, color, radii, geom, binning, img, is_used = C.rasterize_gaussians(
         bg, s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
         c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3, c["campos"], False, False)
-    arena = dp.GradientArena(P, 16, dev)
-    C.rasterize_gaussians_backward(bg, s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
-                                   c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], geom, R, binning, img, False,
-                                   out_buffers=arena.backward_buffers())
-    arena.all_reduce()
+    def baseline_arm():
+        a_ = dp.GradientArena(P, 16, dev)
+        C.rasterize_gaussians_backward(bg, s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+                                       c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], geom, R, binning, img, False,
+                                       out_buffers=a_.backward_buffers())
+        a_.all_reduce()
+        return a_
+
+    arena = baseline_arm()
+    # The tile backward sums with float atomics, so two runs of the SAME arm differ (as two runs of the reference do): the
+    # baseline arm is run twice and its own run-to-run relative L2 is reported as the noise floor of the comparison.
+    arena2 = baseline_arm()
     got = exchange.backward(C, bg, s["means3D"], radii, s["scales"], s["rotations"], 1.0, c["viewmatrix"], c["projmatrix"],
                             c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], campos_views, geom, R, binning, img)
     torch.cuda.synchronize()
-    rel, ident = {}, True
+    rel, noise, ident = {}, {}, True
     for k in ("means3D", "sh", "opacity", "scales", "rotations"):
-        a, b = got[k].double(), arena.views[k].double()
+        a, b, b2 = got[k].double(), arena.views[k].double(), arena2.views[k].double()
         rel[k] = float((a - b).norm() / b.norm().clamp_min(1e-300))
+        noise[k] = float((b2 - b).norm() / b.norm().clamp_min(1e-300))
         h = dp.replica_fingerprint([got[k]]).to(dev)
         hs = [torch.zeros_like(h) for _ in range(world)]
         dist.all_gather(hs, h)
         ident = ident and all(bool((x == hs[0]).all()) for x in hs)
-    worst = torch.tensor([max(rel.values())], dtype=torch.float64, device=dev)
+    del arena2
+    # a tensor passes at 1e-5, or within twice the baseline arm's own run-to-run difference when that is larger
+    excess = max(rel[k] / max(1e-5, 2.0 * noise[k]) for k in rel)
+    worst = torch.tensor([max(rel.values()), excess], dtype=torch.float64, device=dev)
     dist.all_reduce(worst, op=dist.ReduceOp.MAX)
     # what the sparse layout saves: Gaussians of this rank's view whose colour gradient is exactly zero (culled, or never blended)
     nonzero = float((arena.local["colors"] != 0).any(1).float().mean().item())
     visible = float((radii > 0).float().mean().item())
     del arena
     torch.cuda.empty_cache()
-    return {"rel_l2_vs_arena_nccl_all_reduce": rel, "max_rel_l2_over_ranks": float(worst.item()), "identical_on_all_ranks": ident,
-            "multicast": bool(getattr(exchange, "_multicast", False)), "transport": exchange.transport, "tolerance": 1e-5,
+    return {"rel_l2_vs_arena_nccl_all_reduce": rel, "baseline_arm_run_to_run_rel_l2": noise,
+            "max_rel_l2_over_ranks": float(worst[0].item()), "identical_on_all_ranks": ident,
+            "multicast": bool(getattr(exchange, "_multicast", False)), "transport": exchange.transport,
+            "tolerance": "1e-5, or 2x the baseline arm's own run-to-run relative L2 (float-atomic summation order) where that is larger",
             "layout": exchange.layout, "visible_fraction_rank0": round(visible, 4), "nonzero_color_grad_fraction_rank0": round(nonzero, 4),
-            "ok": bool(float(worst.item()) <= 1e-5 and ident),
+            "ok": bool(float(worst[1].item()) <= 1.0 and ident),
             "what": "same views, same dL/dpix: factored exchange (timed above) vs GradientArena + one NCCL all_reduce of 59 floats/Gaussian"}
 
 
