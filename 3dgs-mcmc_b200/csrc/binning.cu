@@ -1,20 +1,22 @@
-// Binning for sm_100a: depth ordering of the Gaussians, tile-instance emission, a stable onesweep
-// radix sort of the instances by tile, tile ranges and the per-tile ranges of the sorted list
-// the render kernels walk.
+// Binning for sm_100a: depth ordering of the visible Gaussians, the depth-ordered emission table, a stable
+// two-digit partition of the tile instances by tile id, and the per-tile ranges the render kernels walk.
 //
 // The reference sorts R instance pairs (tile << 32 | depth_bits, gaussian_idx) with a 6-pass CUB radix
 // sort over 44-45 significant bits (cuda_rasterizer/rasterizer_impl.cu:70-138, :278-318; ~152 B of
-// HBM traffic per instance). The sorted order is unique — (tile, depth, gaussian index), because the
-// emission is index-ordered and the sort is stable — so any algorithm that produces that order is
-// bit-identical. This file gets there with far less traffic:
-//   1. sort the P Gaussians once by (depth_bits, index)      — 4 passes over P keys (P << R, L2-resident);
-//   2. scan tiles_touched in that order and emit every Gaussian's tile instances in that order, as
-//      u64 (tile << 32 | gaussian_idx);
-//   3. stable-sort the R instances by the tile field only     — ceil(log2(tiles)/8) = 2 passes at 1080p;
-//      stability preserves the (depth, index) order inside each tile.
-// That is 8 B (histogram) + 2 x 16 B per instance instead of 8 + 6 x 24 B. Both sorts use the same
-// kernels: one histogram of every digit up front, then one kernel per 8-bit digit with decoupled
-// look-back (onesweep), keys only, u64.
+// HBM traffic per instance). The sorted order is unique - (tile, depth, gaussian index), because the
+// emission is index-ordered and the sort is stable - so any algorithm that produces that order is
+// bit-identical. This file gets there with far less work:
+//   1. sort the Gaussians once by (depth_bits, index): four count -> scan -> scatter passes over P keys
+//      (launch_depth_sort; culled Gaussians carry a sentinel depth and are dropped by the first pass; the last
+//      pass writes the depth-ordered emission table (idx, rectangle, tile count));
+//   2. scan the tile counts in that order (launch_inclusive_scan): every Gaussian's instances own a known range
+//      of emission slots;
+//   3. stable-partition the instances by tile id in two digits (launch_fast_binning): pass 1 expands the slots
+//      in registers from the emission table (no instance list in emission order is ever written) and its block
+//      histograms come analytically from the rectangles; pass 2's count also yields the per-tile counts, from
+//      which the tile ranges follow by one scan. No inter-block dependency inside any kernel.
+// Images of more than 65536 tiles take the generic path further down (emission + onesweep radix sort with
+// decoupled look-back + range detection), which is also what GS_FORCE_GENERIC_BINNING=1 exercises.
 #include "gs_common.cuh"
 #include "kernels.cuh"
 #include "workspace.cuh"
