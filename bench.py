@@ -315,8 +315,6 @@ def run_b200_arm(args):
     for i in range(Wm):
         device_step(i)
     barrier()
-    marks = K * 16 + 8
-    C.profile_enable(marks)
     launches0 = C.launch_count()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -334,6 +332,13 @@ def run_b200_arm(args):
     total_ms = ev0.elapsed_time(ev1)
     per_step = sorted(step_ev[i].elapsed_time(step_ev[i + 1]) for i in range(K))
     launches = C.launch_count() - launches0
+    # Per-stage times come from a SECOND, instrumented run of the same K steps (outside the timed region): the library's
+    # stage marks are event records between the kernels, which break the programmatic-dependent-launch chains and cost
+    # ~0.07 ms per step at the headline size - they do not belong in `value`.
+    C.profile_enable(K * 16 + 8)
+    for i in range(K):
+        device_step(Wm + i)
+    barrier()
     stages = C.profile_collect()
     C.profile_enable(0)
     if n_gpus > 1:
@@ -480,20 +485,33 @@ def run_b200_arm(args):
                         "traffic_source": (ncu_traffic.get(hbm_dom) or {}).get("capture"), "ms": round(hbm_ms, 4), "peak_source": peak_src}
 
     # ---- e2e: public API, host buffers in, loss out ----
-    # Every step copies its own ground-truth image and camera from pinned host memory (inside the timed region) and
-    # reads the loss back. The image copy of step i+1 is issued on a copy stream while step i computes (double
-    # buffered), as a data loader would; the camera (140 B) is copied on the compute stream.
+    # Every step copies its own ground-truth image and camera packet from pinned host memory (inside the timed region) and
+    # reads the loss back. Both copies of step i+1 are issued on a copy stream while step i computes, as a data loader would,
+    # into one of THREE device slots: slot (i+1) % 3 was last read by step i-2, whose loss the host has already read back when it
+    # issues the copy (the read-back below runs one step late), so the reuse needs no device-side "buffer free" event - only
+    # the compute stream's wait for the copy. (Measured with tools/e2e_gap.py: a copy-stream wait on an event recorded behind
+    # the backward costs 0.11 ms per step, three separate 64-byte camera copies on the compute stream 0.05 ms.)
+    NSLOT = 3
     params = {k: s[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
     gt_host = [torch.rand((3, H, W), generator=gen).pin_memory() for _ in range(2)]
     cam_host = [{k: (torch.from_numpy(np.ascontiguousarray(v)).pin_memory() if isinstance(v, np.ndarray) else v)
                  for k, v in c.items()} for c in cams_np]
-    gt_dev = [torch.empty((3, H, W), dtype=torch.float32, device=dev) for _ in range(2)]
-    gt_ready = [torch.cuda.Event() for _ in range(2)]
-    gt_free = [torch.cuda.Event() for _ in range(2)]
+    ncam = len(cams_np)
+
+    def cam_packet(step):
+        """viewmatrix 16 | projmatrix 16 | campos 3 | campos of every rank's view 3 * n_gpus, one pinned buffer per step of the cycle."""
+        c_ = cams_np[(step * n_gpus + rank) % ncam]
+        parts = [np.asarray(c_["viewmatrix"], np.float32).ravel(), np.asarray(c_["projmatrix"], np.float32).ravel(),
+                 np.asarray(c_["campos"], np.float32).ravel()]
+        parts += [np.asarray(cams_np[(step * n_gpus + r) % ncam]["campos"], np.float32).ravel() for r in range(n_gpus)]
+        return torch.from_numpy(np.concatenate(parts)).pin_memory()
+
+    cam_packets = [cam_packet(i) for i in range(ncam)]
+    npk = 35 + 3 * n_gpus
+    gt_dev = [torch.empty((3, H, W), dtype=torch.float32, device=dev) for _ in range(NSLOT)]
+    cam_dev = [torch.empty(npk, dtype=torch.float32, device=dev) for _ in range(NSLOT)]
+    in_ready = [torch.cuda.Event() for _ in range(NSLOT)]
     copy_stream = torch.cuda.Stream(device=dev)
-    view_dev = torch.empty((4, 4), dtype=torch.float32, device=dev)
-    proj_dev = torch.empty((4, 4), dtype=torch.float32, device=dev)
-    campos_dev = torch.empty((3,), dtype=torch.float32, device=dev)
     h2d = gt_dev[0].numel() * 4 + (16 + 16 + 3) * 4
     losses = []
     vp_raster = None
@@ -503,51 +521,43 @@ def run_b200_arm(args):
         vp_raster = dp.ViewParallelRasterizer.__new__(dp.ViewParallelRasterizer)
         torch.nn.Module.__init__(vp_raster)
         vp_raster.exchange = exchange
-        campos_views_host = [torch.stack([torch.as_tensor(cams_np[(i * n_gpus + r) % len(cams_np)]["campos"]) for r in range(n_gpus)]).pin_memory()
-                             for i in range(len(cams_np))]
-        campos_views_dev = torch.empty((n_gpus, 3), dtype=torch.float32, device=dev)
         h2d += n_gpus * 3 * 4
 
-    def prefetch_gt(step):
-        slot = step % 2
+    def prefetch_inputs(step):
+        slot = step % NSLOT
         with torch.cuda.stream(copy_stream):
-            copy_stream.wait_event(gt_free[slot])          # the step that last read this buffer is done with it
-            gt_dev[slot].copy_(gt_host[slot], non_blocking=True)
-            gt_ready[slot].record(copy_stream)
-
-    for slot in range(2):
-        gt_free[slot].record()
+            gt_dev[slot].copy_(gt_host[step % 2], non_blocking=True)
+            cam_dev[slot].copy_(cam_packets[step % ncam], non_blocking=True)
+            in_ready[slot].record(copy_stream)
 
     def e2e_step(step, first=False):
         ch = cam_host[(step * n_gpus + rank) % len(cam_host)]
-        slot = step % 2
+        slot = step % NSLOT
         if first:
-            prefetch_gt(step)
-        prefetch_gt(step + 1)                              # next step's image travels while this step computes
-        view_dev.copy_(ch["viewmatrix"], non_blocking=True)
-        proj_dev.copy_(ch["projmatrix"], non_blocking=True)
-        campos_dev.copy_(ch["campos"], non_blocking=True)
+            prefetch_inputs(step)
+        prefetch_inputs(step + 1)                          # next step's image and camera travel while this step computes
+        torch.cuda.current_stream().wait_event(in_ready[slot])
+        pk = cam_dev[slot]
+        view_dev, proj_dev, campos_dev = pk[0:16].view(4, 4), pk[16:32].view(4, 4), pk[32:35]
         settings = GaussianRasterizationSettings(H, W, ch["tanfovx"], ch["tanfovy"], bg, 1.0, view_dev, proj_dev, 3,
                                                  campos_dev, False, False)
         means2D = torch.zeros_like(params["means3D"], requires_grad=True)
         if vp_raster is not None:
-            campos_views_dev.copy_(campos_views_host[step % len(campos_views_host)], non_blocking=True)
-            image, radii_, used_ = vp_raster(settings, campos_views_dev, params["means3D"], means2D, params["opacities"],
+            image, radii_, used_ = vp_raster(settings, pk[35:].view(n_gpus, 3), params["means3D"], means2D, params["opacities"],
                                              params["shs"], params["scales"], params["rotations"])
         else:
             image, radii_, used_ = GaussianRasterizer(settings)(
                 means3D=params["means3D"], means2D=means2D, shs=params["shs"], opacities=params["opacities"],
                 scales=params["scales"], rotations=params["rotations"])
-        torch.cuda.current_stream().wait_event(gt_ready[slot])
         loss = l1_loss(image, gt_dev[slot])                 # the package's l1_loss (utils/loss_utils.py:21-22; csrc/loss.cu)
         loss.backward()
-        gt_free[slot].record()
         if n_gpus > 1 and vp_raster is None:
             for p_ in params.values():
                 dist.all_reduce(p_.grad)
         # the step's D2H result read: asynchronous copy into pinned memory, consumed one step later (after the next step's
         # work has been queued), so the host's launch latency is not exposed - every step's loss is still read inside the
-        # timed region; the last one is drained before the closing event
+        # timed region; the last one is drained before the closing event. Reading step i-1's loss is also what tells the
+        # host that the input slots of step i-1 and older are free again.
         slot_l = step % 2
         loss_host[slot_l].copy_(loss.detach().reshape(1), non_blocking=True)
         loss_ready[slot_l].record()
@@ -1222,19 +1232,25 @@ def run_swin_arm(args):
     lam, opacity_reg, scale_reg, noise_lr = 0.2, 0.01, 0.01, 5e5
     opt = FusedAdam([{"params": [imm[k]], "lr": lrs[k], "name": k} for k in train_keys], lr=0.0, eps=1e-15)
     vp = dp.ViewParallelRasterizer(cap, 16, dev, transport=args.transport, capacity=cap) if n_gpus > 1 else None
-    view_dev, proj_dev, campos_dev = (torch.empty(sh_, device=dev) for sh_ in ((4, 4), (4, 4), (3,)))
-    campos_views_dev = torch.empty((n_gpus, 3), dtype=torch.float32, device=dev)
-    campos_views_host = [torch.stack([torch.as_tensor(cams_np[(i * n_gpus + r) % len(cams_np)]["campos"]) for r in range(n_gpus)]).pin_memory()
-                         for i in range(len(cams_np))]
+    # the step's camera travels as ONE pinned packet: viewmatrix 16 | projmatrix 16 | campos 3 | campos of every rank's view
+    def cam_packet(i):
+        c_ = cams_np[(i * n_gpus + rank) % len(cams_np)]
+        parts = [np.asarray(c_["viewmatrix"], np.float32).ravel(), np.asarray(c_["projmatrix"], np.float32).ravel(),
+                 np.asarray(c_["campos"], np.float32).ravel()]
+        parts += [np.asarray(cams_np[(i * n_gpus + r) % len(cams_np)]["campos"], np.float32).ravel() for r in range(n_gpus)]
+        return torch.from_numpy(np.concatenate(parts)).pin_memory()
+
+    cam_packets = [cam_packet(i) for i in range(len(cams_np))]
+    cam_dev = [torch.empty(35 + 3 * n_gpus, dtype=torch.float32, device=dev) for _ in range(2)]
     loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
 
     def step(i, host_inputs):
         f = i % SWIN_FRAMES
         ii, mi = idx[f]
         ch = cam_host[(i * n_gpus + rank) % len(cam_host)]
-        view_dev.copy_(ch["viewmatrix"], non_blocking=True)
-        proj_dev.copy_(ch["projmatrix"], non_blocking=True)
-        campos_dev.copy_(ch["campos"], non_blocking=True)
+        pk = cam_dev[i % 2]
+        pk.copy_(cam_packets[i % len(cam_packets)], non_blocking=True)
+        view_dev, proj_dev, campos_dev = pk[0:16].view(4, 4), pk[16:32].view(4, 4), pk[32:35]
         gt = gt_dev[i % 2]
         if host_inputs:
             gt.copy_(gt_host[i % 2], non_blocking=True)
@@ -1244,8 +1260,7 @@ def run_swin_arm(args):
         means2D = torch.zeros((Ka, 3), dtype=torch.float32, device=dev, requires_grad=True)
         if vp is not None:
             vp.resize(Ka)
-            campos_views_dev.copy_(campos_views_host[i % len(campos_views_host)], non_blocking=True)
-            image = vp(settings, campos_views_dev, r["xyz"], means2D, r["opacity"], r["feature"], r["scaling"], r["rotation"])[0]
+            image = vp(settings, pk[35:].view(n_gpus, 3), r["xyz"], means2D, r["opacity"], r["feature"], r["scaling"], r["rotation"])[0]
         else:
             image = GaussianRasterizer(settings)(means3D=r["xyz"], means2D=means2D, shs=r["feature"], opacities=r["opacity"],
                                                  scales=r["scaling"], rotations=r["rotation"])[0]
@@ -1267,14 +1282,14 @@ def run_swin_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(host_inputs, profile):
+    def timed(host_inputs, profile, sample=False):
         for i in range(Wm):
             step(i, host_inputs)
         barrier()
         if profile:
             C.profile_enable(K * 16 + 8)
         l0 = C.launch_count()
-        sampler = ClockSampler(local_rank) if profile else None
+        sampler = ClockSampler(local_rank) if sample else None
         if sampler:
             sampler.start()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -1296,8 +1311,9 @@ def run_swin_arm(args):
             ms = float(t.item())
         return ms, launches, stages, clocks, float(last.item())
 
-    ms, launches, stages, clocks, last_loss = timed(False, True)
+    ms, launches, _, clocks, last_loss = timed(False, False, sample=True)
     e2e_ms, _, _, _, _ = timed(True, False)
+    _, _, stages, _, _ = timed(False, True)   # per-stage times: a second, instrumented run (the marks cost time)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
