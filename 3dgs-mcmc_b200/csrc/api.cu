@@ -771,6 +771,7 @@ int gs_knn_mean_dist2(void* stream_, int P, const float* points, float* mean_dis
     if (P < 0) return GS_ERR_ARG;
     if (P == 0) return GS_OK;
     if (!points || !mean_dist2 || !ws) return GS_ERR_ARG;
+    pdl_hint(P);
     prof_mark(stream, -1);
     const int rc = launch_knn_mean_dist2(P, points, mean_dist2, aligned_base(ws), stream);
     prof_mark(stream, ST_KNN);
