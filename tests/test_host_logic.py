@@ -363,3 +363,21 @@ def test_l1_loss_symbols_and_python_api_exist():
         assert sym in C.SIGNATURES
     assert callable(loss.l1_loss) and "l1_loss" in loss.__all__
     assert C._lib.gs_l1_workspace_bytes(1) > 0 and C._lib.gs_l1_workspace_bytes(3 * 1080 * 1920) >= 8 * 1519
+
+
+def test_bench_presets_cover_baseline_configs(monkeypatch):
+    """bench.py --config names one preset per BASELINE.json config that fits the bench contract (2-5; config 1 is the CPU
+    oracle's parity case), and the default is the headline metric."""
+    import importlib
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    monkeypatch.syspath_prepend(root)
+    bench = importlib.import_module("bench")
+    assert {"headline", "lego300k", "garden1297", "large6m", "swin"} <= set(bench.CONFIGS)
+    monkeypatch.setattr(sys, "argv", ["bench.py"])
+    args = bench.parse()
+    assert (args.P, args.width, args.height, args.gpus) == (3_000_000, 1920, 1080, 1) and args.warmup >= 3
+    assert bench.metric_name(args) == bench.METRIC and "3M Gaussians" in bench.METRIC
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--config", "swin", "--gpus", "8"])
+    args = bench.parse()
+    assert (args.width, args.height) == (1352, 1014) and args.P == 800_000
