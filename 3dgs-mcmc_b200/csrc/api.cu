@@ -180,14 +180,23 @@ static int forward_preprocess_impl(void* stream_, int P, int D, int M, const flo
     if (num_rendered_host)
         GS_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, g.num_rendered, sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
     if (count_ready_event) GS_CUDA_TRY(cudaEventRecord((cudaEvent_t)count_ready_event, stream));
-    // Depth order of the Gaussians: stable sort of (depth_bits << 32 | idx) on the depth field.
+    // Depth order of the Gaussians: stable sort of (depth_bits << 32 | idx) on the depth field, then the scan of the tile
+    // counts in that order. Small scenes: both in one cooperative kernel; else the kernel chain.
+    bool fused = false;
+    rc = launch_small_depth_sort_scan(g.dkeys_a, g.dkeys_b, (uint32_t)P, g.num_rendered + 2, reinterpret_cast<uint32_t*>(g.dsort_scratch),
+                                      g.rect, g.emit, g.point_offsets, g.scan_block_sums, stream, &fused);
+    if (rc) return rc;
+    if (fused) {
+        prof_mark(stream, ST_DEPTH_SORT);
+        count_launches(2);
+        return GS_OK;
+    }
     rc = launch_depth_sort(g.dkeys_a, g.dkeys_b, (uint32_t)P, g.num_rendered + 2, reinterpret_cast<uint32_t*>(g.dsort_scratch), g.rect, g.emit, stream);
     if (rc) return rc;
     prof_mark(stream, ST_DEPTH_SORT);
     rc = launch_inclusive_scan(P, g.num_rendered + 2, g.point_offsets, g.emit, g.scan_block_sums, stream);
     if (rc) return rc;
     prof_mark(stream, ST_SCAN);
-    // preprocess + depth sort (count [+ scan] + scatter per pass) + the two scan kernels
     count_launches(1 + 3 * kDepthSortPasses + 2);
     return GS_OK;
 }

@@ -21,6 +21,7 @@
 #include "kernels.cuh"
 #include "workspace.cuh"
 
+#include <cooperative_groups.h>
 #include <cstdlib>
 
 namespace gs {
@@ -1093,6 +1094,192 @@ int launch_fast_binning(int P, const uint32_t* n_dev, uint32_t R, uint2 grid, ui
     rc = dispatch_scatter<2>(bits2, sp, nb, stream);
     if (rc) return rc;
     GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Small scenes: the whole depth ordering (4 x count -> scan -> scatter) AND the tile-count scan in ONE cooperative kernel.
+// At 300K Gaussians the fourteen launches of the chain cost ~0.11 ms for ~0.03 ms of work: every kernel is a few microseconds
+// behind a launch and a drain. With at most one wave of blocks (cooperative launch: co-residency is guaranteed by the
+// driver, or the launch fails and the caller takes the multi-kernel path) the phases are separated by grid-wide barriers
+// instead. Same arithmetic, same per-block code (bin_scatter_body), same results bit for bit.
+// ------------------------------------------------------------------------------------------------
+struct SmallSortParams {
+    uint64_t* keys_a;
+    uint64_t* keys_b;
+    uint32_t n;                 // keys in keys_a (sentinels included when n_dev is set)
+    const uint32_t* n_dev;      // optional: the number of real keys (device)
+    uint32_t* hist;             // [256][nb]
+    uint32_t* totals;           // [256]
+    uint32_t nb;
+    const uint2* rect;
+    uint4* emit;
+    uint32_t* offsets;          // [n] inclusive scan of the tile counts in depth order
+    uint32_t* block_sums;       // [ceil(n / kScanBlock)]
+};
+
+__global__ void __launch_bounds__(kBinThreads, 2) small_depth_sort_scan_kernel(const SmallSortParams q) {
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    __shared__ __align__(16) uint64_t s_keys[kBinTile];
+    __shared__ uint8_t s_dig[16];
+    __shared__ uint32_t s_hist[kBinThreads / 32][256];
+    __shared__ uint32_t s_gbase[256];
+    __shared__ uint32_t s_scan[33];
+    static_assert(kScanThreads == kBinThreads && kBinTile == 2 * kScanBlock, "one sort block = two scan blocks, same thread count");
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t b = blockIdx.x, nb = q.nb;
+    const uint32_t n_real = q.n_dev ? *q.n_dev : q.n;
+
+    for (int pass = 0; pass < 4; ++pass) {
+        uint64_t* in = (pass & 1) ? q.keys_b : q.keys_a;
+        uint64_t* out = (pass & 1) ? q.keys_a : q.keys_b;
+        const bool drop = q.n_dev != nullptr && pass == 0;
+        const uint32_t n_in = pass == 0 ? q.n : n_real;
+        const int shift = 32 + 8 * pass;
+        // ---- count: this block's digit histogram -> hist[d][b] ----
+        for (int i = tid; i < (kBinThreads / 32) * 256; i += kBinThreads) (&s_hist[0][0])[i] = 0;
+        __syncthreads();
+        {
+            const uint32_t slot_begin = b * (uint32_t)kBinTile, cnt = slot_begin < n_in ? min((uint32_t)kBinTile, n_in - slot_begin) : 0u;
+            uint64_t kv[kBinItems];
+#pragma unroll
+            for (int i = 0; i < kBinItems; ++i) {
+                const uint32_t e = i * kBinThreads + tid;
+                kv[i] = e < cnt ? in[(size_t)slot_begin + e] : ~0ull;
+            }
+#pragma unroll
+            for (int i = 0; i < kBinItems; ++i) {
+                const uint32_t e = i * kBinThreads + tid;
+                if (e < cnt && !(drop && (uint32_t)(kv[i] >> 32) == 0xffffffffu)) atomicAdd(&s_hist[warp][(uint32_t)(kv[i] >> shift) & 0xffu], 1u);
+            }
+        }
+        __syncthreads();
+        {
+            uint32_t c = 0;
+#pragma unroll
+            for (int w = 0; w < kBinThreads / 32; ++w) c += s_hist[w][tid];
+            q.hist[(size_t)tid * nb + b] = c;
+        }
+        grid.sync();
+        // ---- scan: digit rows d = b, b + nb, ... in place (exclusive over the blocks), totals[d] ----
+        for (uint32_t d = b; d < 256u; d += nb) {
+            uint32_t* row = q.hist + (size_t)d * nb;
+            uint32_t carry = 0;
+            for (uint32_t base = 0; base < nb; base += kBinThreads) {
+                const uint32_t v = base + tid < nb ? row[base + tid] : 0u;
+                uint32_t total;
+                const uint32_t ex = block_excl_scan(v, s_scan, &total);
+                if (base + tid < nb) row[base + tid] = carry + ex;
+                carry += total;
+            }
+            if (tid == 0) q.totals[d] = carry;
+        }
+        grid.sync();
+        // ---- scatter (the multi-kernel path's per-block code) ----
+        {
+            BinScatterParams sp = {};
+            sp.keys_in = in; sp.keys_out = out; sp.n = q.n; sp.nb = nb; sp.shift = 8 * pass; sp.bits = 8;
+            sp.drop_sentinel = drop ? 1 : 0;
+            sp.scanned = q.hist; sp.totals = q.totals;
+            if (pass == 3) { sp.rect = q.rect; sp.emit_out = q.emit; }
+            const uint32_t n_keys = n_in;
+            if (b * (uint32_t)kBinTile < n_keys) {
+                if ((b + 1u) * (uint32_t)kBinTile <= n_keys && !drop) bin_scatter_body<0, 8, false, true>(sp, n_keys, s_keys, s_dig, s_hist, s_gbase, s_scan);
+                else bin_scatter_body<0, 8, false, false>(sp, n_keys, s_keys, s_dig, s_hist, s_gbase, s_scan);
+            }
+        }
+        grid.sync();
+    }
+    if (q.emit == nullptr) return;   // sort only (every block takes this branch together)
+
+    // ---- inclusive scan of the tile counts in depth order: emit[r].w count in, first slot out; offsets[r] ----
+    uint32_t* const sw = s_scan;                       // 8 warp sums
+    uint32_t* const sb = &s_gbase[0];                  // 8 partial "blocks before" sums
+    const int n = (int)n_real;
+    uint32_t excl[2][kScanItems];
+    uint4 E[2][kScanItems];
+    uint32_t wcarry[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const size_t base = ((size_t)2 * b + h) * kScanBlock + (size_t)warp * (kScanItems * 32) + lane;
+        uint32_t carry = 0;
+#pragma unroll
+        for (int r = 0; r < kScanItems; ++r) E[h][r] = base + r * 32 < (size_t)n ? q.emit[base + r * 32] : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (int r = 0; r < kScanItems; ++r) {
+            const uint32_t incl = warp_incl_scan(E[h][r].w, lane);
+            excl[h][r] = carry + incl - E[h][r].w;
+            carry += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        wcarry[h] = carry;
+        if (lane == 0) sw[warp] = carry;
+        __syncthreads();
+        if (tid == 0) {
+            uint32_t t = 0;
+            for (int w = 0; w < kBinThreads / 32; ++w) t += sw[w];
+            q.block_sums[2 * b + h] = t;
+        }
+        __syncthreads();
+    }
+    grid.sync();
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const uint32_t sblock = 2 * b + h;
+        const size_t base = (size_t)sblock * kScanBlock + (size_t)warp * (kScanItems * 32) + lane;
+        uint32_t before = 0;
+        for (uint32_t j = tid; j < sblock; j += kBinThreads) before += q.block_sums[j];
+        before = __reduce_add_sync(0xffffffffu, before);
+        __syncthreads();
+        if (lane == 0) { sw[warp] = wcarry[h]; sb[warp] = before; }
+        __syncthreads();
+        uint32_t woff = 0;
+#pragma unroll
+        for (int w = 0; w < kBinThreads / 32; ++w) woff += sb[w] + (w < warp ? sw[w] : 0u);
+#pragma unroll
+        for (int r = 0; r < kScanItems; ++r) {
+            if (base + r * 32 < (size_t)n) {
+                const uint32_t run = woff + excl[h][r], v = E[h][r].w;
+                E[h][r].w = run;
+                q.emit[base + r * 32] = E[h][r];
+                q.offsets[base + r * 32] = run + v;
+            }
+        }
+    }
+}
+
+// Returns GS_OK with *done = true when the cooperative kernel was launched; *done = false when the input is too large for one
+// co-resident wave (or the launch was refused): the caller then runs launch_depth_sort + launch_inclusive_scan.
+int launch_small_depth_sort_scan(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, const uint32_t* n_dev, uint32_t* scratch,
+                                 const uint2* rect, uint4* emit, uint32_t* offsets, uint32_t* block_sums, cudaStream_t stream,
+                                 bool* done) {
+    *done = false;
+    if (n == 0) return GS_OK;
+    static const int enabled = [] { const char* e = getenv("GS_SMALL_SORT"); return e ? atoi(e) : 1; }();
+    const uint32_t nb = (n + kBinTile - 1) / kBinTile;
+    static int capacity = -1;
+    if (capacity < 0) {
+        int dev = 0, sms = 0, per_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        int coop = 0;
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, small_depth_sort_scan_kernel, kBinThreads, 0);
+        capacity = coop ? sms * per_sm : 0;
+        if (cudaGetLastError() != cudaSuccess) capacity = 0;
+    }
+    // one block per SM at most: beyond that the separate kernels (more parallel scans) win
+    if (!enabled || (int)nb > capacity || nb > 160u) return GS_OK;
+    SmallSortParams q;
+    q.keys_a = keys_a; q.keys_b = keys_b; q.n = n; q.n_dev = n_dev; q.hist = scratch; q.totals = scratch + (size_t)256 * nb; q.nb = nb;
+    q.rect = rect; q.emit = emit; q.offsets = offsets; q.block_sums = block_sums;
+    void* args[] = {(void*)&q};
+    const cudaError_t e = cudaLaunchCooperativeKernel((const void*)small_depth_sort_scan_kernel, dim3(nb), dim3(kBinThreads), args, 0, stream);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();   // refused (e.g. MPS / partitioned device): not an error of ours, take the other path
+        return GS_OK;
+    }
+    *done = true;
     return GS_OK;
 }
 

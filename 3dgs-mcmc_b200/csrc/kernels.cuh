@@ -182,6 +182,9 @@ int launch_fast_binning(int P, const uint32_t* n_dev, uint32_t R, uint2 grid, ui
                         const uint32_t* offsets, const BinningWS& b, uint2* ranges, cudaStream_t stream);
 int launch_depth_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, const uint32_t* n_dev, uint32_t* scratch, const uint2* rect,
                       uint4* emit, cudaStream_t stream);
+int launch_small_depth_sort_scan(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, const uint32_t* n_dev, uint32_t* scratch,
+                                 const uint2* rect, uint4* emit, uint32_t* offsets, uint32_t* block_sums, cudaStream_t stream,
+                                 bool* done);
 int launch_strip_ids(uint32_t n, const uint64_t* in, uint32_t* out, cudaStream_t stream);
 int launch_emit_instances(int P, const uint32_t* n_dev, const uint4* emit, uint2 grid, uint64_t* inst, cudaStream_t stream);
 int launch_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, int first_bit, int passes, char* scratch,
