@@ -660,7 +660,7 @@ print(json.dumps(out))
 def test_switchable_code_paths_give_the_default_result(tmp_path):
     """GS_BIN_RANK=ballot (round-1 in-warp ranks), GS_PDL=1 / 0 (programmatic dependent launch forced on / off),
     GS_BWD_VARIANT=0 (three record stages, 3 CTAs/SM), GS_FUSE_SCAN (digit scan in the count kernel's last block),
-    GS_FWD_VARIANT=0 (one-level cull): the forward state (sorted ids, keys, ranges, n_contrib, depth order, scan, image, radii,
+    GS_FWD_VARIANT=0 (one-level cull), GS_SMALL_SORT=0 (kernel chain instead of the cooperative small-scene kernel): the forward state (sorted ids, keys, ranges, n_contrib, depth order, scan, image, radii,
     is_used) must be bit-identical to the default build's, the gradients within the atomic-order tolerance."""
     import json
     import subprocess
@@ -676,7 +676,8 @@ def test_switchable_code_paths_give_the_default_result(tmp_path):
 
     base = run("default")
     variants = {"ballot": {"GS_BIN_RANK": "ballot"}, "pdl_on": {"GS_PDL": "1"}, "pdl_off": {"GS_PDL": "0"}, "bwd0": {"GS_BWD_VARIANT": "0"},
-                "fuse_scan": {"GS_FUSE_SCAN": "100000"}, "fwd0": {"GS_FWD_VARIANT": "0"}}
+                "fuse_scan": {"GS_FUSE_SCAN": "100000", "GS_SMALL_SORT": "0"}, "fwd0": {"GS_FWD_VARIANT": "0"},
+                "kernel_chain": {"GS_SMALL_SORT": "0"}}
     for name, env in variants.items():
         got = run(name, **env)
         assert got == base, (name, got, base)
