@@ -85,6 +85,7 @@ const char* gs_error_string(int code) {
     if (code == GS_OK) return "ok";
     if (code == GS_ERR_ARG) return "gs_b200: invalid argument";
     if (code == GS_ERR_WORKSPACE) return "gs_b200: workspace too small or misaligned";
+    if (code == GS_ERR_LIMIT) return "gs_b200: input larger than the fixed capacity of this entry point";
     if (code > 0) return cudaGetErrorString((cudaError_t)code);
     return "gs_b200: unknown error";
 }

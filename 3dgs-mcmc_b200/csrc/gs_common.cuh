@@ -21,6 +21,7 @@
 #define GS_OK 0
 #define GS_ERR_ARG (-1)
 #define GS_ERR_WORKSPACE (-2)
+#define GS_ERR_LIMIT (-3)
 
 #define GS_CUDA_TRY(expr)                                  \
     do {                                                   \

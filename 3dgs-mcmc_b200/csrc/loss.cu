@@ -13,6 +13,8 @@
 //   dS/de11 = -S / B2,  dS/de12 = 2 A1 / (B1 B2),
 //   dS/dmu  = 2 nu (A2 - A1) / (B1 B2) - 2 mu S (1/B1 - 1/B2)          (total derivative, e11/e12 held fixed)
 // and  d(sum_q S_q)/dx_p = sum_q w(p - q) [ dS/dmu_q + 2 x_p dS/de11_q + y_p dS/de12_q ].
+#include <mutex>
+
 #include "gs_common.cuh"
 #include "kernels.cuh"
 
@@ -349,4 +351,60 @@ int launch_l1_backward(size_t n, const float* x, const float* y, const float* gr
     return GS_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// gs_l1_loss_forward_static: the L1 forward for callers that have no way to hand this library a scratch buffer.
+//
+// gs_l1_loss_forward needs a caller-allocated workspace for its per-block partial sums. Some hosts of this library
+// cannot produce one: a plugin running inside an engine that owns the device allocator and does not expose it, a
+// real-time loop in which cudaMalloc's implicit device synchronisation is forbidden, or a process whose memory
+// budget was carved up front and that must not grow. For them the partial sums live in the array below, which is
+// part of the library image: each GPU that loads the library carries these 16 KB until the process exits, and no
+// call ever allocates or frees anything.
+//
+// The price is a size limit and shared state. The array holds one pair of floats per block and one block per 4096
+// elements, so n is limited to kL1StaticMaxN = 2048 * 4096 = 8 388 608 floats (a 3 x 1080 x 1920 image is 6 220 800);
+// larger inputs are refused with GS_ERR_LIMIT. Up to that size the launch shape, the summation order and therefore
+// the result are the same as gs_l1_loss_forward's, bit for bit. Every call on a device uses the same array: two calls
+// whose kernels can overlap on that GPU (different streams, no dependency) race on it, so keep the calls ordered.
+// The array keeps whatever the previous call left; that is harmless because each call writes every slot it later
+// reads (slots [0, 2 * blocks)) and nothing is accumulated into it, so there is nothing that has to be zeroed.
+// ------------------------------------------------------------------------------------------------------------------
+constexpr size_t kL1StaticMaxN = (size_t)kL1MaxBlocks * kL1Chunk;
+static __device__ __align__(256) float g_l1_static_partial[2 * kL1MaxBlocks];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_l1_static_mutex;
+float* g_l1_static_ptr[kMaxDevices] = {};   // device address of g_l1_static_partial on each device, once resolved
+
+// In host code `g_l1_static_partial` is only a handle for the runtime, not a pointer a kernel could use; the real
+// address differs per device and is looked up once per device, with that device current.
+int l1_static_scratch(float** out) {
+    int dev = -1;
+    GS_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return GS_ERR_ARG;
+    std::lock_guard<std::mutex> lock(g_l1_static_mutex);
+    if (!g_l1_static_ptr[dev]) {
+        float* ptr = nullptr;
+        GS_CUDA_TRY(cudaGetSymbolAddress((void**)&ptr, g_l1_static_partial));
+        if (!ptr) return (int)cudaErrorInvalidSymbol;
+        g_l1_static_ptr[dev] = ptr;
+    }
+    *out = g_l1_static_ptr[dev];
+    return GS_OK;
+}
+}  // namespace
+
 }  // namespace gs
+
+// Declared in include/gs_b200.h. `stream` must belong to the current device. The first call on each device resolves
+// the scratch address (cudaGetSymbolAddress, which may load the module); make that first call outside any stream capture.
+extern "C" int gs_l1_loss_forward_static(void* stream_, size_t n, const float* x, const float* y, float* out_mean) {
+    if (n == 0 || !x || !y || !out_mean) return GS_ERR_ARG;
+    if (n > gs::kL1StaticMaxN) return GS_ERR_LIMIT;
+    float* partial = nullptr;
+    const int rc = gs::l1_static_scratch(&partial);
+    if (rc) return rc;
+    return gs::launch_l1_forward(n, x, y, partial, out_mean, (cudaStream_t)stream_);
+}

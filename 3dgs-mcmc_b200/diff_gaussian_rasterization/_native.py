@@ -66,6 +66,7 @@ SIGNATURES = {
     "gs_l1_workspace_bytes": (_c_size_t, [_c_size_t]),
     "gs_l1_loss_forward": (_c_int, [_c_void_p, _c_size_t] + [_c_void_p] * 4),
     "gs_l1_loss_backward": (_c_int, [_c_void_p, _c_size_t] + [_c_void_p] * 4),
+    "gs_l1_loss_forward_static": (_c_int, [_c_void_p, _c_size_t] + [_c_void_p] * 3),
     "gs_activation_workspace_bytes": (_c_size_t, [_c_int]),
     "gs_activate_forward": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 8),
     "gs_activate_backward": (_c_int, [_c_void_p, _c_int] + [_c_void_p] * 6 + [_c_float, _c_float] + [_c_void_p] * 4),

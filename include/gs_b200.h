@@ -41,6 +41,7 @@ extern "C" {
 #define GS_B200_OK 0
 #define GS_B200_ERR_ARG (-1)
 #define GS_B200_ERR_WORKSPACE (-2)
+#define GS_B200_ERR_LIMIT (-3) /* input larger than an entry point's fixed capacity */
 
 /* Library / ABI version (major*100 + minor). */
 int gs_abi_version(void);
@@ -250,6 +251,21 @@ size_t gs_l1_workspace_bytes(size_t n);
 int gs_l1_loss_forward(void* stream, size_t n, const float* x, const float* y, void* ws, float* out_mean);
 int gs_l1_loss_backward(void* stream, size_t n, const float* x, const float* y, const float* grad_scale,
                         float* dL_dx);
+
+/* gs_l1_loss_forward without a workspace argument, for callers that cannot give it one. This entry point has no
+ * counterpart in the reference (which gets all of its temporaries from torch's allocator); it exists for hosts that are
+ * not allowed to allocate device memory at the point of the call: a plugin inside an engine that keeps the device
+ * allocator to itself, a frame loop that must not hit cudaMalloc's device-wide synchronisation, a process with a memory
+ * budget fixed at start-up. The per-block partial sums go into a 16 KB array that is part of the library image (every GPU
+ * that loads the library holds it until the process exits); the call itself allocates and frees nothing.
+ *   - n <= GS_L1_STATIC_MAX_N, else GS_B200_ERR_LIMIT. Within the limit the result equals gs_l1_loss_forward's bit for bit.
+ *   - `stream` must belong to the current device. The first call on each device looks up the array's device address
+ *     (cudaGetSymbolAddress); issue that first call before starting any stream capture.
+ *   - All calls on one device share the array. Calls that may overlap on the GPU (different streams without an
+ *     ordering between them) race on it; serialise them. Nothing in the array has to be cleared between calls: every
+ *     slot a call reads it has written first. */
+#define GS_L1_STATIC_MAX_N ((size_t)8388608) /* 2048 blocks x 4096 floats; 3 x 1080 x 1920 = 6 220 800 fits */
+int gs_l1_loss_forward_static(void* stream, size_t n, const float* x, const float* y, float* out_mean);
 
 /* Fused parameter activations + regularisers (additive): opacity = sigmoid(raw), scaling = exp(raw),
  * rotation = raw / max(|raw|, 1e-12) (scene/gaussian_model_static.py:43-56, :126-146) in one pass, which also writes
