@@ -180,39 +180,27 @@ class FactoredExchange:
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if self.world > 1 else 0
-        self.transport = self._pick_transport(transport)
-        layout = os.environ.get("GS_DP_LAYOUT") if layout is None else layout
-        if layout is None:
-            # records need the gather to be cheap for absent Gaussians: peer stores. Through an NCCL all-gather whole
-            # slots would travel, so that fallback keeps the dense gather + all-reduce.
-            layout = "records" if (self.world == 1 or self.transport == "symm") and self.device.type == "cuda" else "dense"
-        self.layout = layout
-        if self.layout not in ("records", "sparse", "dense"):
-            raise ValueError(f"layout must be records, sparse or dense, got {self.layout!r}")
-        # fixed: slot r of a gather buffer starts at r * slot_stride floats (include/gs_b200.h: gs_dp_slot_floats)
-        per_layout = {"records": (self.capacity + 127) // 128 * 1800, "sparse": (self.capacity + 255) // 256 * 784,
-                      "dense": 3 * self.capacity}
-        self.slot_stride = _round_up(per_layout[self.layout], 64)
-        self._step = 0
-        if self.layout == "records":
-            slab_floats = 0
-            self._nbuf = 2 if self.world > 1 else 1               # double buffered: one barrier per step is enough
-        else:
-            slab_floats = _round_up(11 * self.capacity + 12, 64)  # + the pad that aligns every field block (resize)
-            self._nbuf = 1
-        total = slab_floats + self._nbuf * self.world * self.slot_stride
         # "classic": slab all-reduce beside the SH rebuild (default). "early_reduce": slab all-reduce while the gather is
         # still in flight, SH rebuild alone afterwards - measured equal within noise on 8xB200 at P = 3M (2.67 vs 2.66 ms
         # backward + exchange): the reduce then competes with the gather for NVLink ingress.
         self.schedule = os.environ.get("GS_DP_SCHEDULE", "classic")
         if self.schedule not in ("early_reduce", "classic"):
             raise ValueError(f"GS_DP_SCHEDULE must be early_reduce or classic, got {self.schedule!r}")
+        requested_layout = os.environ.get("GS_DP_LAYOUT") if layout is None else layout
+        if requested_layout not in (None, "records", "sparse", "dense"):
+            raise ValueError(f"layout must be records, sparse or dense, got {requested_layout!r}")
+        self._step = 0
         self._hdl = None
+        # Order matters: the transport is settled first (local pick -> agreement of all ranks -> rendezvous -> second
+        # agreement), and only the FINAL transport decides the layout, the slot stride, the buffering depth and the buffer
+        # size. Every rank therefore derives the same sizes, also when the symmetric set-up fails on some or all ranks.
+        self.transport = self._pick_transport(transport)
         auto = transport == "auto" and self.world > 1
         if auto:
             # Every rank takes part in the agreement, whatever it picked locally: a rank whose symmetric-memory import
             # failed must not skip a collective the others enter. Only if ALL ranks can do "symm" is the rendezvous tried.
             self.transport = "symm" if self._all_ranks_agree(self.transport == "symm") else "nccl"
+        slab_floats, total = self._plan(requested_layout)
         if self.transport == "symm":
             try:
                 self._setup_symmetric(total, slab_floats, group, multicast)
@@ -223,9 +211,10 @@ class FactoredExchange:
                 warnings.warn(f"FactoredExchange: symmetric memory unavailable ({ex!r}); using torch.distributed collectives")
                 self.transport = "nccl"
             if auto and not self._all_ranks_agree(self.transport == "symm"):
-                # the rendezvous failed somewhere: everyone falls back together
-                self.transport, self._hdl = "nccl", None
+                self.transport = "nccl"          # the rendezvous failed somewhere: everyone falls back together
         if self.transport != "symm":
+            self._hdl = None
+            slab_floats, total = self._plan(requested_layout)   # the fallback's own layout and sizes, on a plain buffer
             self.flat = torch.zeros(total, dtype=torch.float32, device=self.device)
             self._multicast = False
             self._send = torch.zeros(self.slot_stride, dtype=torch.float32, device=self.device)
@@ -259,6 +248,28 @@ class FactoredExchange:
                       "colors": torch.empty((P, 3), dtype=torch.float32, device=self.device),
                       "cov3D": torch.empty((P, 6), dtype=torch.float32, device=self.device)}
         return self
+
+    @staticmethod
+    def _auto_layout(world, transport, device_type):
+        """Layout when the caller names none. Records need the gather to be cheap for absent Gaussians, i.e. peer stores:
+        through an NCCL all-gather whole 56 B / Gaussian slots would travel (169 MB per rank and step at 3M, against 36 MB
+        gathered + 132 MB all-reduced), so that transport keeps the dense gather + slab all-reduce."""
+        return "records" if (world == 1 or transport == "symm") and device_type == "cuda" else "dense"
+
+    def _plan(self, requested_layout):
+        """Set layout / slot_stride / _nbuf for the CURRENT self.transport; return (slab_floats, total floats)."""
+        self.layout = requested_layout or self._auto_layout(self.world, self.transport, self.device.type)
+        # fixed: slot r of a gather buffer starts at r * slot_stride floats (include/gs_b200.h: gs_dp_slot_floats)
+        per_layout = {"records": (self.capacity + 127) // 128 * 1800, "sparse": (self.capacity + 255) // 256 * 784,
+                      "dense": 3 * self.capacity}
+        self.slot_stride = _round_up(per_layout[self.layout], 64)
+        if self.layout == "records":
+            slab_floats = 0
+            self._nbuf = 2 if self.world > 1 else 1               # double buffered: one barrier per step is enough
+        else:
+            slab_floats = _round_up(11 * self.capacity + 12, 64)  # + the pad that aligns every field block (resize)
+            self._nbuf = 1
+        return slab_floats, slab_floats + self._nbuf * self.world * self.slot_stride
 
     def _setup_symmetric(self, total, slab_floats, group, multicast):
         import torch.distributed._symmetric_memory as symm_mem
@@ -301,8 +312,18 @@ class FactoredExchange:
         return out
 
     def bytes_per_step(self):
-        """(bytes this rank receives in the gather, bytes of the all-reduced slab)."""
-        return (self.world - 1) * 3 * self.P * 4, 11 * self.P * 4
+        """(bytes this rank receives in the gather, bytes of the all-reduced slab). "dense": exact. "sparse" / "records":
+        the upper bound (every Gaussian present: headers + one triple / one 14-float record each); what actually travels
+        over symmetric memory is the headers plus the non-zero entries only, while a torch.distributed all-gather moves
+        whole slots (slot_stride floats per view)."""
+        peers = self.world - 1
+        if self.layout == "records":
+            per_view = self.slot_stride * 4 if self.transport != "symm" else (self.P + 127) // 128 * 32 + 56 * self.P
+            return peers * per_view, 0
+        if self.layout == "sparse":
+            per_view = self.slot_stride * 4 if self.transport != "symm" else (self.P + 255) // 256 * 64 + 12 * self.P
+            return peers * per_view, 11 * self.P * 4
+        return peers * 3 * self.P * 4, 11 * self.P * 4
 
     def push_color_grads(self, native, radii, geom, scratch):
         """Stage 1 (right after the tile backward): this rank's masked dL_dRGB goes to slot `rank` of every rank's

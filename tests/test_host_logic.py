@@ -211,6 +211,67 @@ def test_factored_exchange_world_size_2_gloo(tmp_path):
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
 
 
+def test_factored_exchange_auto_layout_follows_the_final_transport():
+    from diff_gaussian_rasterization import dp
+    f = dp.FactoredExchange._auto_layout
+    assert f(1, "nccl", "cuda") == "records" and f(8, "symm", "cuda") == "records"
+    assert f(8, "nccl", "cuda") == "dense" and f(2, "symm", "cpu") == "dense"
+    ex = dp.FactoredExchange(1000, 16, "cpu", layout="records")         # world 1: upper bound of what a view would send
+    assert ex.bytes_per_step() == (0, 0)
+
+
+def test_factored_exchange_rendezvous_failure_on_one_rank_world_size_2_gloo(tmp_path):
+    """The symmetric-memory set-up fails on rank 1 only (forced). Both ranks must end on the same transport AND on the
+    layout / slot stride / buffer size that belong to it - a rank left on the records layout would enter the all-gather
+    with a different size and hang or corrupt the run."""
+    script = tmp_path / "worker.py"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script.write_text(textwrap.dedent(f"""
+        import os, sys, warnings
+        sys.path.insert(0, {os.path.join(root, '3dgs-mcmc_b200')!r})
+        import torch, torch.distributed as dist
+        from diff_gaussian_rasterization import dp
+        dist.init_process_group("gloo")
+        r, world = dist.get_rank(), dist.get_world_size()
+        X = dp.FactoredExchange
+        X._pick_transport = lambda self, t: "symm"                  # every rank believes it can do symmetric memory
+        X._auto_layout = staticmethod(lambda world, transport, dev: "records" if transport == "symm" else "dense")
+        tried = []
+        def setup(self, total, slab_floats, group, multicast):
+            tried.append((self.layout, self.slot_stride, total))
+            if r == 1:
+                raise RuntimeError("forced: no peer access on this rank")
+            self.flat, self._hdl, self._multicast = torch.zeros(total), object(), False
+        X._setup_symmetric = setup
+        P, cap = 1001, 1100
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            ex = X(P, 16, "cpu", capacity=cap)
+        # the rendezvous was attempted once, with the records layout's double-buffered gather and no slab
+        assert len(tried) == 1 and tried[0][0] == "records" and tried[0][2] == 2 * world * tried[0][1]
+        assert ex.transport == "nccl" and ex._hdl is None and ex.layout == "dense" and ex._nbuf == 1
+        assert ex.slot_stride == (3 * cap + 63) // 64 * 64
+        slab = (11 * cap + 12 + 63) // 64 * 64
+        assert ex.flat.numel() == slab + world * ex.slot_stride and ex._send.numel() == ex.slot_stride
+        mine = torch.tensor([ex.slot_stride, ex.flat.numel(), ex._nbuf], dtype=torch.int64)
+        both = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(both, mine)
+        assert torch.equal(both[0], both[1])
+        ex._send.fill_(float(r + 1))                                # the fallback's gather runs with matching sizes
+        dist.all_gather_into_tensor(ex.gathered.view(-1), ex._send)
+        assert torch.all(ex.gathered[0] == 1.0) and torch.all(ex.gathered[1] == 2.0)
+        assert ex.bytes_per_step() == ((world - 1) * 12 * P, 44 * P)
+        dist.destroy_process_group()
+        open(os.path.join({str(tmp_path)!r}, f"ok{{r}}"), "w").write("ok")
+    """))
+    port = _free_port()
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
+                         capture_output=True, text=True, timeout=240)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+
+
 def test_replica_guard_world_size_2_gloo(tmp_path):
     """dp.assert_replicas_in_sync: passes while the replicas are bit-identical (also after a resize to a ragged P), raises
     on EVERY rank as soon as one rank's copy differs in a single bit - the guard view-sharded MCMC training calls after
