@@ -22,7 +22,9 @@
 #include "workspace.cuh"
 
 #include <cooperative_groups.h>
+#include <atomic>
 #include <cstdlib>
+#include <mutex>
 
 namespace gs {
 
@@ -1162,18 +1164,29 @@ __global__ void __launch_bounds__(kBinThreads, 2) small_depth_sort_scan_kernel(c
             q.hist[(size_t)tid * nb + b] = c;
         }
         grid.sync();
-        // ---- scan: digit rows d = b, b + nb, ... in place (exclusive over the blocks), totals[d] ----
-        for (uint32_t d = b; d < 256u; d += nb) {
-            uint32_t* row = q.hist + (size_t)d * nb;
-            uint32_t carry = 0;
-            for (uint32_t base = 0; base < nb; base += kBinThreads) {
-                const uint32_t v = base + tid < nb ? row[base + tid] : 0u;
-                uint32_t total;
-                const uint32_t ex = block_excl_scan(v, s_scan, &total);
-                if (base + tid < nb) row[base + tid] = carry + ex;
-                carry += total;
+        // ---- scan: every digit row in place (exclusive over the blocks), totals[d]. A row has nb <= 160 words, so one WARP
+        // scans a row with shuffles (no block barrier) and the grid's 8 * nb warps share the 256 rows; with a single block
+        // a row is one word and thread d settles row d directly. (Round 2 gave each row to a whole block: at nb = 1 that was
+        // 256 block-wide scans of one element per pass, 0.46 ms in the driver's 4K-Gaussian capture.) ----
+        static_assert(kBinThreads == 256, "thread d owns digit row d in the single-block case");
+        if (nb == 1u) {
+            const uint32_t v = q.hist[tid];
+            q.totals[tid] = v;
+            q.hist[tid] = 0u;
+        } else {
+            constexpr uint32_t kWarps = kBinThreads / 32;
+            for (uint32_t d = b * kWarps + (uint32_t)warp; d < 256u; d += nb * kWarps) {
+                uint32_t* row = q.hist + (size_t)d * nb;
+                uint32_t carry = 0;
+                for (uint32_t base = 0; base < nb; base += 32u) {
+                    const bool live = base + (uint32_t)lane < nb;
+                    const uint32_t v = live ? row[base + lane] : 0u;
+                    const uint32_t incl = warp_incl_scan(v, lane);
+                    if (live) row[base + lane] = carry + incl - v;
+                    carry += __shfl_sync(0xffffffffu, incl, 31);
+                }
+                if (lane == 0) q.totals[d] = carry;
             }
-            if (tid == 0) q.totals[d] = carry;
         }
         grid.sync();
         // ---- scatter (the multi-kernel path's per-block code) ----
@@ -1248,6 +1261,14 @@ __global__ void __launch_bounds__(kBinThreads, 2) small_depth_sort_scan_kernel(c
     }
 }
 
+constexpr int kMaxCoopDevices = 64;
+static std::mutex g_coop_mutex;
+static std::atomic<int> g_coop_capacity[kMaxCoopDevices] = {
+#define GS_M1x8 {-1}, {-1}, {-1}, {-1}, {-1}, {-1}, {-1}, {-1}
+    GS_M1x8, GS_M1x8, GS_M1x8, GS_M1x8, GS_M1x8, GS_M1x8, GS_M1x8, GS_M1x8
+#undef GS_M1x8
+};
+
 // Returns GS_OK with *done = true when the cooperative kernel was launched; *done = false when the input is too large for one
 // co-resident wave (or the launch was refused): the caller then runs launch_depth_sort + launch_inclusive_scan.
 int launch_small_depth_sort_scan(uint64_t* keys_a, uint64_t* keys_b, uint32_t n, const uint32_t* n_dev, uint32_t* scratch,
@@ -1257,16 +1278,24 @@ int launch_small_depth_sort_scan(uint64_t* keys_a, uint64_t* keys_b, uint32_t n,
     if (n == 0) return GS_OK;
     static const int enabled = [] { const char* e = getenv("GS_SMALL_SORT"); return e ? atoi(e) : 1; }();
     const uint32_t nb = (n + kBinTile - 1) / kBinTile;
-    static int capacity = -1;
+    // Co-resident block capacity of the cooperative kernel, per device (a process may drive several), looked up once under a
+    // lock from the return codes of the queries themselves; 0 = not available on that device (also remembered after the
+    // first refused launch, so a refusal is not retried on every step).
+    int dev = 0;
+    GS_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxCoopDevices) return GS_OK;
+    int capacity = g_coop_capacity[dev].load(std::memory_order_acquire);
     if (capacity < 0) {
-        int dev = 0, sms = 0, per_sm = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        int coop = 0;
-        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, small_depth_sort_scan_kernel, kBinThreads, 0);
-        capacity = coop ? sms * per_sm : 0;
-        if (cudaGetLastError() != cudaSuccess) capacity = 0;
+        std::lock_guard<std::mutex> lock(g_coop_mutex);
+        capacity = g_coop_capacity[dev].load(std::memory_order_relaxed);
+        if (capacity < 0) {
+            int sms = 0, per_sm = 0, coop = 0;
+            const bool ok = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess &&
+                            cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess &&
+                            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, small_depth_sort_scan_kernel, kBinThreads, 0) == cudaSuccess;
+            capacity = (ok && coop) ? sms * per_sm : 0;
+            g_coop_capacity[dev].store(capacity, std::memory_order_release);
+        }
     }
     // one block per SM at most: beyond that the separate kernels (more parallel scans) win
     if (!enabled || (int)nb > capacity || nb > 160u) return GS_OK;
@@ -1277,6 +1306,7 @@ int launch_small_depth_sort_scan(uint64_t* keys_a, uint64_t* keys_b, uint32_t n,
     const cudaError_t e = cudaLaunchCooperativeKernel((const void*)small_depth_sort_scan_kernel, dim3(nb), dim3(kBinThreads), args, 0, stream);
     if (e != cudaSuccess) {
         (void)cudaGetLastError();   // refused (e.g. MPS / partitioned device): not an error of ours, take the other path
+        g_coop_capacity[dev].store(0, std::memory_order_release);   // ... from now on, without asking again
         return GS_OK;
     }
     *done = true;

@@ -27,6 +27,7 @@
 #include "render_common.cuh"
 #include "workspace.cuh"
 
+#include <atomic>
 #include <cstdlib>
 
 namespace gs {
@@ -308,7 +309,16 @@ template <int CH, int ROWS, int MIN_CTAS, int RS = kRecStages, int GA = kGatherA
 static int launch_variant(const RenderBwdParams& p, int tiles, cudaStream_t stream) {
     auto kern = render_bwd_kernel<CH, ROWS, MIN_CTAS, RS, GA>;
     constexpr size_t bytes = BwdSmem<CH, ROWS, RS>::kBytes;
-    GS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    // The opt-in to more than 48 KB of dynamic shared memory is per function and per device and sticks: set it the first time
+    // this instantiation runs on a device, not on every step (small scenes are bound by the host's launch rate).
+    static std::atomic<unsigned long long> configured{0};
+    int dev = 0;
+    GS_CUDA_TRY(cudaGetDevice(&dev));
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (dev >= 64 || !(configured.load(std::memory_order_acquire) & bit)) {
+        GS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        if (dev < 64) configured.fetch_or(bit, std::memory_order_release);
+    }
     kern<<<tiles, GS_TILE_PIX, bytes, stream>>>(p);
     GS_LAUNCH_CHECK();
     return GS_OK;

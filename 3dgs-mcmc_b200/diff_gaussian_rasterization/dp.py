@@ -9,6 +9,7 @@ backward need no communication.
 """
 import contextlib
 import os
+import threading
 
 import torch
 import torch.distributed as dist
@@ -69,7 +70,16 @@ def replica_fingerprint(tensors):
         t = t.detach().contiguous()
         if t.numel() == 0:
             continue
-        bits = (t.view(torch.int32) if t.element_size() == 4 else t.to(torch.int64)).flatten().long()
+        # the raw storage words, never converted values: t.to(int64) would map every fp16 / bf16 / fp64 value in (-1, 1)
+        # to 0 and hide a divergence there
+        raw = {1: torch.uint8, 2: torch.int16, 4: torch.int32, 8: torch.int64}.get(t.element_size())
+        if t.dtype == torch.bool:
+            bits = t.to(torch.uint8)
+        elif raw is None or t.is_complex():
+            bits = t.flatten().view(torch.uint8)
+        else:
+            bits = t.view(raw)
+        bits = bits.flatten().long()
         w = torch.arange(bits.numel(), device=bits.device) % 1000003 + 1
         h = torch.stack([bits.sum(), (bits * w).sum(), torch.tensor(bits.numel(), device=bits.device)])
         acc = h if acc is None else acc * 31 + h
@@ -95,6 +105,9 @@ def assert_replicas_in_sync(tensors, group=None, what="replicated Gaussian param
     return True
 
 
+_lockstep_guard = threading.Lock()
+
+
 @contextlib.contextmanager
 def lockstep_sampling(group=None, src=0):
     """Make the MCMC draws of relocate_gs / add_new_gs (scene/gaussian_model_static.py:412-422: torch.multinomial over the
@@ -106,22 +119,38 @@ def lockstep_sampling(group=None, src=0):
     tools/dp_check.py --mcmc-steps agreed through every training step and parted at the first relocation. Inside this
     context every rank still makes each draw (the device RNG streams stay aligned for the noise that follows) and rank
     `src`'s indices - K int64 per draw - are broadcast over them: this is the "MCMC statistics" half of the north star's
-    exchange. The reference's callers run unchanged inside the context."""
+    exchange. The reference's callers run unchanged inside the context. Both torch.multinomial and Tensor.multinomial are
+    covered; other RNG calls are not (the reference's relocation draws through torch.multinomial only). One context at a time
+    per process; draws made by other threads while it is open are left alone."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         yield
         return
-    real = torch.multinomial
+    real, real_method = torch.multinomial, torch.Tensor.multinomial
     src_global = dist.get_global_rank(group, src) if group is not None else src
+    owner = threading.get_ident()
+
+    def in_step(out):
+        # Only the thread that opened the context is in lock step with the other ranks. A draw from any other thread (an
+        # evaluator, a data loader) gets the stock function: broadcasting there would enter a collective the peers never call.
+        if threading.get_ident() == owner:
+            dist.broadcast(out, src=src_global, group=group)
+        return out
 
     def multinomial(*args, **kwargs):
-        out = real(*args, **kwargs)
-        dist.broadcast(out, src=src_global, group=group)
-        return out
-    torch.multinomial = multinomial
+        return in_step(real(*args, **kwargs))
+
+    def multinomial_method(self, *args, **kwargs):
+        return in_step(real_method(self, *args, **kwargs))
+
+    if not _lockstep_guard.acquire(blocking=False):
+        raise RuntimeError("lockstep_sampling is already active in this process (it is neither re-entrant nor shareable "
+                           "between threads)")
+    torch.multinomial, torch.Tensor.multinomial = multinomial, multinomial_method
     try:
         yield
     finally:
-        torch.multinomial = real
+        torch.multinomial, torch.Tensor.multinomial = real, real_method
+        _lockstep_guard.release()
 
 
 def shard_views(num_views, rank, world_size):

@@ -318,6 +318,23 @@ def test_replica_guard_world_size_2_gloo(tmp_path):
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
 
 
+def test_replica_fingerprint_sees_every_bit_of_any_dtype():
+    """Values are never converted: a one-bit change in fp16 / bf16 / fp64 / int8 state (all of them collapse under
+    .to(int64) for magnitudes below 1) changes the fingerprint."""
+    from diff_gaussian_rasterization import dp
+    g = torch.Generator().manual_seed(4)
+    for dtype, word in ((torch.float16, torch.int16), (torch.bfloat16, torch.int16), (torch.float64, torch.int64),
+                        (torch.float32, torch.int32), (torch.int8, torch.int8)):
+        base = (torch.rand(257, generator=g) * 0.9).to(dtype) if dtype != torch.int8 else torch.arange(257).to(dtype)
+        other = base.clone()
+        other.view(word)[100] ^= 1
+        assert not torch.equal(dp.replica_fingerprint([base]), dp.replica_fingerprint([other])), dtype
+        assert torch.equal(dp.replica_fingerprint([base]), dp.replica_fingerprint([base.clone()]))
+    flags = torch.zeros(64, dtype=torch.bool)
+    flipped = flags.clone(); flipped[7] = True
+    assert not torch.equal(dp.replica_fingerprint([flags]), dp.replica_fingerprint([flipped]))
+
+
 def test_lockstep_sampling_world_size_2_gloo(tmp_path):
     """dp.lockstep_sampling: ranks whose multinomial draws would differ (here: differently seeded generators, on CUDA:
     the unordered cumsum inside torch.multinomial) end up with rank 0's indices; outside the context torch.multinomial is
@@ -331,13 +348,27 @@ def test_lockstep_sampling_world_size_2_gloo(tmp_path):
         from diff_gaussian_rasterization import dp
         dist.init_process_group("gloo")
         r = dist.get_rank()
-        stock = torch.multinomial
+        stock, stock_method = torch.multinomial, torch.Tensor.multinomial
         torch.manual_seed(10 + r)                      # the ranks would draw differently
         probs = torch.linspace(0.1, 1.0, 5000)
         with dp.lockstep_sampling():
             idx = torch.multinomial(probs, 700, replacement=True)
             ratio = torch.bincount(idx, minlength=5000)
-        assert torch.multinomial is stock
+            idx_m = probs.multinomial(700, replacement=True)            # the method form is in lock step too
+            import threading
+            seen = []
+            t = threading.Thread(target=lambda: seen.append(torch.multinomial(probs, 50, replacement=True)))
+            t.start(); t.join()                                          # another thread: stock draw, no collective
+            try:
+                with dp.lockstep_sampling():
+                    nested = True
+            except RuntimeError:
+                nested = False
+            assert not nested
+        assert torch.multinomial is stock and torch.Tensor.multinomial is stock_method and len(seen) == 1
+        both = [torch.zeros_like(idx_m) for _ in range(2)]
+        dist.all_gather(both, idx_m)
+        assert torch.equal(both[0], both[1])
         both = [torch.zeros_like(idx) for _ in range(2)]
         dist.all_gather(both, idx)
         assert torch.equal(both[0], both[1])
