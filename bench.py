@@ -182,6 +182,28 @@ def run_reference_arm(args):
             "cpu_baseline": {"value": value, "unit": "views/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "views/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "wall_seconds": round(wall, 2), "gpu_launches": 0}
+    # The anchor north_star names is the reference's CUDA rasterizer on this box. The driver's ratio is computed from `value`
+    # above (the CPU port, as the tier rules ask); this block puts the CUDA baseline into the same record: the unmodified
+    # reference kernels (oracle/_ref), device-timed fwd+bwd on the same scene and camera cycle. None of this repo's kernels run.
+    try:
+        import torch
+        from oracle import ref_cuda
+        if torch.cuda.is_available() and ref_cuda.available():
+            import gs_synth
+            dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+            torch.cuda.set_device(dev)
+            s = gs_synth.to_torch(scene, dev)
+            cams_t = [gs_synth.to_torch(c, dev) for c in cams]
+            bg = torch.zeros(3, dtype=torch.float32, device=dev)
+            gen = torch.Generator(device="cpu").manual_seed(5)
+            dLt = (torch.randn((3, H, W), generator=gen) / (3 * H * W)).to(dev)
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            line["ref_cuda"] = ref_cuda_leg(torch, ref_cuda, dev, s, cams_t, bg, dLt, H, W, 16, None, None, None, None, None, ev0, ev1,
+                                            with_e2e=False)
+        else:
+            line["ref_cuda"] = {"unavailable": "no CUDA device or oracle/_ref/libref_dgr.so not present"}
+    except Exception as ex:  # informational; the CPU line above is the contract
+        line["ref_cuda"] = {"unavailable": repr(ex)[:200]}
     print_result(line)
 
 
@@ -643,6 +665,10 @@ def run_b200_arm(args):
                                                  exchange, P, H, W, n_gpus)
         except Exception as ex:
             line["parity"] = {"unavailable": repr(ex)[:300]}
+        # top-level verdict the driver's record keeps; a failed or crashed parity block makes the run exit non-zero
+        line["parity_ok"] = bool(line["parity"].get("ok", False))
+        line["parity_max_rel_l2_over_ranks"] = line["parity"].get("max_rel_l2_over_ranks")
+        line["parity_identical_on_all_ranks"] = line["parity"].get("identical_on_all_ranks")
 
     # ---- full training step (informational; SURVEY.md 8 f1 pieces around the hot path): raw parameters -> activations ->
     #      rasterizer -> L1 + SSIM loss + the two regularisers -> backward (+ exchange) -> Adam -> MCMC noise, as
@@ -660,7 +686,7 @@ def run_b200_arm(args):
             barrier()
             dist.destroy_process_group()
         watchdog.cancel()
-        return
+        return 3 if line.get("parity_ok") is False else 0
 
     # ---- SURVEY.md 8 f1 ("next" rows), measured beside the hot path at N=1: the optimizer step over the same parameters ----
     if n_gpus == 1:
@@ -763,15 +789,15 @@ def run_b200_arm(args):
     if n_gpus > 1:
         barrier()
         dist.destroy_process_group()
+    return 3 if line.get("parity_ok") is False else 0
 
 
-def ref_cuda_leg(torch, ref_cuda, dev, s, cams, bg, dL, H, W, K, our_ms, our_e2e_ms, gt_host, cam_host, l1_loss, ev0, ev1):
+def ref_cuda_leg(torch, ref_cuda, dev, s, cams, bg, dL, H, W, K, our_ms, our_e2e_ms, gt_host, cam_host, l1_loss, ev0, ev1,
+                 with_e2e=True):
     """The reference's own cuda_rasterizer (oracle/_ref, compiled for sm_100 from /root/reference) on the same box, tensors
     and CAMERA CYCLE as the main arm: device-timed fwd+bwd with a forward / backward split, and an end-to-end variant through
     the reference's autograd contract (oracle/ref_rasterizer.py) with the same pinned gt copy, L1 loss and loss read-back as
     this arm's e2e loop."""
-    from oracle import ref_rasterizer
-    from diff_gaussian_rasterization import GaussianRasterizationSettings
     e = torch.empty(0)
     kk = max(3, min(K, 16))
     fwd_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(kk)]
@@ -804,13 +830,17 @@ def ref_cuda_leg(torch, ref_cuda, dev, s, cams, bg, dL, H, W, K, our_ms, our_e2e
            "what": "the reference's own cuda_rasterizer compiled for sm_100 (oracle/_ref), same tensors, same cameras, same box; "
                    "forward / backward from CUDA events around the two library calls (the reference's glue zero-fills its outputs "
                    "inside them, rasterize_points.cu:66-75,154-162); per-kernel times: profiles/ ncu launch list of this leg",
-           "speedup_device": rms / our_ms}
+           "speedup_device": (rms / our_ms) if our_ms else None}
+    if not with_e2e:
+        return out
+    from oracle import ref_rasterizer
+    from diff_gaussian_rasterization import GaussianRasterizationSettings
     # end to end, as this arm's e2e loop: gt from pinned memory, autograd rasterizer, L1, backward, loss read back
     params = {k: s[k].clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
     gt_dev = torch.empty((3, H, W), dtype=torch.float32, device=dev)
     view_dev, proj_dev, campos_dev = (torch.empty(sh_, device=dev) for sh_ in ((4, 4), (4, 4), (3,)))
 
-    def e2e_step(i):
+    def sync_step(i):
         ch = cam_host[i % len(cam_host)]
         gt_dev.copy_(gt_host[i % 2], non_blocking=True)
         view_dev.copy_(ch["viewmatrix"], non_blocking=True)
@@ -827,19 +857,90 @@ def ref_cuda_leg(torch, ref_cuda, dev, s, cams, bg, dL, H, W, K, our_ms, our_e2e
         for p_ in params.values():
             p_.grad = None
         return v
+
+    # The same pipelined harness as this arm's e2e loop (the two arms must not differ in the harness):
+    # one packed camera packet and the gt image prefetched one step ahead on a copy stream into 3 slots, the loss copied
+    # asynchronously into pinned memory and read one step later. The reference library launches on the legacy default
+    # stream, which is torch's current stream here, so the event waits order its kernels exactly as they order ours.
+    NSLOT = 3
+    packets = [torch.cat([ch["viewmatrix"].reshape(-1), ch["projmatrix"].reshape(-1), ch["campos"].reshape(-1)]).pin_memory()
+               for ch in cam_host]
+    gt_slots = [torch.empty((3, H, W), dtype=torch.float32, device=dev) for _ in range(NSLOT)]
+    cam_slots = [torch.empty(35, dtype=torch.float32, device=dev) for _ in range(NSLOT)]
+    in_ready = [torch.cuda.Event() for _ in range(NSLOT)]
+    copy_stream = torch.cuda.Stream(device=dev)
+    loss_host = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+    loss_ready = [torch.cuda.Event() for _ in range(2)]
+    pending, losses = [], []
+
+    def prefetch(i):
+        slot = i % NSLOT
+        with torch.cuda.stream(copy_stream):
+            gt_slots[slot].copy_(gt_host[i % 2], non_blocking=True)
+            cam_slots[slot].copy_(packets[i % len(packets)], non_blocking=True)
+            in_ready[slot].record(copy_stream)
+
+    def drain():
+        sl = pending.pop(0)
+        loss_ready[sl].synchronize()
+        losses.append(float(loss_host[sl][0]))
+
+    def piped_step(i, first=False):
+        ch = cam_host[i % len(cam_host)]
+        slot = i % NSLOT
+        if first:
+            prefetch(i)
+        prefetch(i + 1)
+        torch.cuda.current_stream().wait_event(in_ready[slot])
+        pk = cam_slots[slot]
+        st = GaussianRasterizationSettings(H, W, ch["tanfovx"], ch["tanfovy"], bg, 1.0, pk[0:16].view(4, 4), pk[16:32].view(4, 4), 3,
+                                           pk[32:35], False, False)
+        means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+        image, _, _ = ref_rasterizer.RefGaussianRasterizer(st)(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                                                               opacities=params["opacities"], scales=params["scales"],
+                                                               rotations=params["rotations"])
+        loss = l1_loss(image, gt_slots[slot])
+        loss.backward()
+        sl = i % 2
+        loss_host[sl].copy_(loss.detach().reshape(1), non_blocking=True)
+        loss_ready[sl].record()
+        pending.append(sl)
+        if len(pending) > 1:
+            drain()
+        for p_ in params.values():
+            p_.grad = None
+
     for i in range(2):
-        e2e_step(i)
+        sync_step(i)
     torch.cuda.synchronize()
     ev0.record()
     for i in range(kk):
-        e2e_step(2 + i)
+        sync_step(2 + i)
     ev1.record()
     torch.cuda.synchronize()
+    sync_ms = ev0.elapsed_time(ev1) / kk
+    for i in range(3):
+        piped_step(i, first=(i == 0))
+    while pending:
+        drain()
+    torch.cuda.synchronize()
+    n0 = len(losses)
+    ev0.record()
+    for i in range(kk):
+        piped_step(3 + i)
+    while pending:
+        drain()
+    ev1.record()
+    torch.cuda.synchronize()
+    assert len(losses) - n0 == kk
     ems = ev0.elapsed_time(ev1) / kk
     out["e2e"] = {"ms_per_step": ems, "value": 1000.0 / ems, "unit": "views/s", "speedup_e2e": ems / our_e2e_ms,
                   "api": "oracle.ref_rasterizer.RefGaussianRasterizer (the reference's autograd contract over its CUDA) + loss.l1_loss + "
-                         "loss.backward(); pinned gt image and camera in, loss out (synchronous copy and read: the reference library runs "
-                         "on the legacy default stream)"}
+                         "loss.backward(); the SAME harness as this arm's e2e loop: packed camera packet and pinned gt image prefetched one "
+                         "step ahead on a copy stream, loss copied asynchronously into pinned memory and read one step later",
+                  "synchronous_harness": {"ms_per_step": sync_ms, "speedup_e2e": sync_ms / our_e2e_ms,
+                                          "what": "round 2's reference loop: four H2D copies on the main stream and a blocking "
+                                                  "loss.item() every step (shown for continuity; it flatters this arm at small scenes)"}}
     return out
 
 
@@ -1411,7 +1512,10 @@ def main():
     elif args.config == "swin":
         run_swin_arm(args)
     else:
-        run_b200_arm(args)
+        rc = run_b200_arm(args)
+        if rc:
+            sys.stderr.write("bench.py: the multi-GPU parity block failed (see parity / parity_ok in the line); exit code 3\n")
+            sys.exit(rc)
 
 
 if __name__ == "__main__":

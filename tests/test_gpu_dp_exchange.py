@@ -2,7 +2,8 @@
 device: the views of a step are rendered one after the other and the factored exchange (masked dL/dRGB per view +
 rebuilt SH gradient + summed 11-float slab) is compared with the plain sum of the per-view gradients of the fused
 backward — which the other GPU tests compare with the reference CUDA rasterizer. The 2-GPU transports (NVLink
-symmetric memory and NCCL) are checked by tools/dp_check.py under torchrun on the GPU box.
+symmetric memory and NCCL) are checked by tools/dp_check.py under torchrun; the last test here runs it on two ranks
+when the box has two GPUs.
 """
 import pytest
 import torch
@@ -417,3 +418,41 @@ def test_split_sh_through_the_public_rasterizer():
             assert helpers.rel_l2(b[k].grad, a[k].grad) < 2e-5, (name, k)
         results[name] = True
     assert len(results) == 2
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs on one node (gpurun --gpus 2)")
+def test_two_rank_exchange_matches_full_all_reduce_every_transport():
+    """The cross-DEVICE part the single-GPU tests cannot reach: two ranks under torchrun (tools/dp_check.py), every
+    transport x layout (NCCL collectives; symmetric memory with dense / sparse / records layouts, multicast and peer
+    pointers) against dp.GradientArena + one NCCL all-reduce of all 59 floats per Gaussian. Tolerance 1e-4 relative L2
+    per tensor (both arms sum the tile backward with float atomics, run-to-run noise ~1e-6), and the summed gradients
+    must be bit-identical on both ranks. Also a short replicated training run: the replicas stay in lock step."""
+    import json
+    import os
+    import socket
+    import subprocess
+    import sys
+    sock = socket.socket()
+    sock.bind(("127.0.0.1", 0))
+    port = sock.getsockname()[1]
+    sock.close()
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(helpers.ROOT, "tools", "dp_check.py"), "--P", "100003", "--width", "640",
+           "--height", "400", "--iters", "2", "--train-steps", "6"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-4000:]
+    line = [ln for ln in out.stdout.splitlines() if ln.startswith("{")][-1]
+    res = json.loads(line)
+    assert res["world"] == 2
+    checked = 0
+    for key, val in res.items():
+        if not key.startswith("factored_"):
+            continue
+        assert "error" not in val, (key, val)
+        assert val["identical_on_all_ranks"], key
+        for name, r in val["rel_l2_vs_full_all_reduce"].items():
+            assert r < 1e-4, (key, name, r)
+        checked += 1
+    assert checked >= 5
+    tr = res["train_replicas"]
+    assert tr["steps"] == 6 and all(tr["identical_on_all_ranks"].values()), tr
