@@ -5,7 +5,7 @@
  * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load it.
  *
  * Parity status: PINNED on the GPU box against the reference's own CUDA code (oracle/_ref, built from
- * /root/reference by oracle/Makefile) by tests/test_gpu_oracle_pin.py, and here against the committed
+ * /root/reference by oracle/Makefile) by tests/test_gpu_parity.py::test_against_cpu_oracle, and here against the committed
  * golden vectors in tests/golden/ that were generated from that reference run
  * (tests/golden/make_golden.py). The reference ships no tests or golden vectors of its own
  * (SURVEY.md §4).

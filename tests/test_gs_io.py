@@ -115,3 +115,45 @@ def test_ply_loader_reads_ascii_and_big_endian(tmp_path):
         got = gs_io.load_ply(str(path), max_sh_degree=0)
         assert np.array_equal(got["xyz"], vals[:, :3]) and got["features_rest"].shape == (2, 0, 3)
         assert np.array_equal(got["rotation"], vals[:, -4:])
+
+
+def test_ply_bytes_against_a_literal_golden(tmp_path):
+    """Byte parity of save_ply without plyfile (absent from the image) and without gs_io's own helpers: the header is
+    written out literally as plyfile emits it for the structured array of gaussian_model_static.py:229-249 (native byte
+    order on x86 = binary_little_endian, one `property float <name>` per 'f4' field, names in the order of
+    construct_list_of_attributes :214-226), and the rows are packed one float at a time in that order, with the
+    transpose(1, 2).flatten(1) of the two SH tensors spelled out as index arithmetic. SH degree 1, two Gaussians."""
+    import struct
+    N, K = 2, 3                                   # K = (degree + 1)^2 - 1 rest coefficients
+    xyz = [[0.5, -1.25, 2.0], [3.0, 4.5, -6.0]]
+    dc = [[[0.125, 0.25, 0.375]], [[-0.5, -0.625, -0.75]]]                                   # [N][1][3]
+    rest = [[[(100 * n + 10 * k + c) / 8.0 for c in range(3)] for k in range(K)] for n in range(N)]   # [N][K][3]
+    opacity = [[-2.0], [1.5]]
+    scaling = [[-3.0, -3.5, -4.0], [-1.0, -1.5, -2.5]]
+    rotation = [[1.0, 0.0, 0.0, 0.0], [0.5, -0.5, 0.5, -0.5]]
+    golden_header = (
+        "ply\n"
+        "format binary_little_endian 1.0\n"
+        "element vertex 2\n"
+        "property float x\nproperty float y\nproperty float z\n"
+        "property float nx\nproperty float ny\nproperty float nz\n"
+        "property float f_dc_0\nproperty float f_dc_1\nproperty float f_dc_2\n"
+        "property float f_rest_0\nproperty float f_rest_1\nproperty float f_rest_2\n"
+        "property float f_rest_3\nproperty float f_rest_4\nproperty float f_rest_5\n"
+        "property float f_rest_6\nproperty float f_rest_7\nproperty float f_rest_8\n"
+        "property float opacity\n"
+        "property float scale_0\nproperty float scale_1\nproperty float scale_2\n"
+        "property float rot_0\nproperty float rot_1\nproperty float rot_2\nproperty float rot_3\n"
+        "end_header\n").encode("ascii")
+    body = b""
+    for n in range(N):
+        row = list(xyz[n]) + [0.0, 0.0, 0.0]
+        row += [dc[n][0][c] for c in range(3)]                       # transpose(1, 2).flatten(1) of [1][3]: channel major
+        row += [rest[n][k][c] for c in range(3) for k in range(K)]   # f_rest_{c * K + k} = features_rest[n, k, c]
+        row += opacity[n] + scaling[n] + rotation[n]
+        assert len(row) == 26
+        body += b"".join(struct.pack("<f", v) for v in row)
+    path = str(tmp_path / "point_cloud.ply")
+    t = lambda v: torch.tensor(v, dtype=torch.float32)
+    gs_io.save_ply(path, t(xyz), t(dc), t(rest), t(opacity), t(scaling), t(rotation))
+    assert open(path, "rb").read() == golden_header + body
