@@ -9,5 +9,5 @@ NVCC=${NVCC:-nvcc}
 OUT=diff_gaussian_rasterization/lib3dgs_mcmc_b200.so
 SRCS="csrc/swin.cu csrc/knn.cu csrc/activations.cu csrc/loss.cu csrc/optim.cu csrc/dp_exchange.cu csrc/api.cu csrc/preprocess.cu csrc/binning.cu csrc/render_fwd.cu csrc/render_bwd.cu csrc/preprocess_bwd.cu csrc/mcmc.cu"
 $NVCC -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo \
-  -Xcompiler -fPIC -shared ${GS_EXTRA_NVCC_FLAGS:-} -o "$OUT" $SRCS
+  -Xcompiler -fPIC -shared ${GS_EXTRA_NVCC_FLAGS:-} -o "$OUT" $SRCS -ldl
 echo "built $OUT"

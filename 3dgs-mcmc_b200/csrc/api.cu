@@ -11,6 +11,8 @@
 using namespace gs;
 
 #include <cstdlib>
+
+#include <nvtx3/nvToolsExt.h>
 namespace gs {
 // On for large scenes only: measured 3.073 -> 3.034 ms/step at 3M Gaussians / 1080p, but 0.528 -> 0.536 ms at 300K / 800x800,
 // where the chain is bound by the host's launch rate and cudaLaunchKernelEx with an attribute costs the host more per launch.
@@ -73,6 +75,26 @@ inline void prof_mark(cudaStream_t stream, int stage) {
     ++g_prof.n;
 }
 inline void count_launches(int k) { g_prof.launches += (unsigned long long)k; }
+
+// NVTX ranges per stage (tracing): with GS_NVTX=1 in the environment every stage's launches are issued
+// inside a host-side range named like the stage (gs_stage_name), so a timeline tool (nsys) labels the kernels by stage. The
+// reference has no tracing of its own (its only analogue is CHECK_CUDA, cuda_rasterizer/auxiliary.h:166-173). Off by
+// default; the NVTX calls are no-ops anyway unless a tool is attached.
+const bool g_nvtx = [] { const char* e = getenv("GS_NVTX"); return e && atoi(e) != 0; }();
+struct NvtxScope {
+    bool open = false;
+    NvtxScope() = default;
+    explicit NvtxScope(int s) { stage(s); }
+    NvtxScope(const NvtxScope&) = delete;
+    NvtxScope& operator=(const NvtxScope&) = delete;
+    void stage(int s) {
+        if (!g_nvtx) return;
+        if (open) nvtxRangePop();
+        nvtxRangePushA(kStageNames[s]);
+        open = true;
+    }
+    ~NvtxScope() { if (open) nvtxRangePop(); }
+};
 unsigned long long* g_fwd_counters = nullptr;   // set by gs_debug_forward_work for the next forward(s); measurement only
 
 }  // namespace
@@ -173,6 +195,7 @@ static int forward_preprocess_impl(void* stream_, int P, int D, int M, const flo
     pp.rec = g.rec; pp.depth_keys = g.dkeys_a; pp.num_rendered = g.num_rendered;
     pp.rect = g.rect;
     prof_mark(stream, -1);
+    NvtxScope nv(ST_PREPROCESS);
     GS_CUDA_TRY(cudaMemsetAsync(g.num_rendered, 0, 16, stream));
     int rc = launch_preprocess_fwd(pp, stream);
     if (rc) return rc;
@@ -184,6 +207,7 @@ static int forward_preprocess_impl(void* stream_, int P, int D, int M, const flo
     // Depth order of the Gaussians: stable sort of (depth_bits << 32 | idx) on the depth field, then the scan of the tile
     // counts in that order. Small scenes: both in one cooperative kernel; else the kernel chain.
     bool fused = false;
+    nv.stage(ST_DEPTH_SORT);
     rc = launch_small_depth_sort_scan(g.dkeys_a, g.dkeys_b, (uint32_t)P, g.num_rendered + 2, reinterpret_cast<uint32_t*>(g.dsort_scratch),
                                       g.rect, g.emit, g.point_offsets, g.scan_block_sums, stream, &fused);
     if (rc) return rc;
@@ -195,6 +219,7 @@ static int forward_preprocess_impl(void* stream_, int P, int D, int M, const flo
     rc = launch_depth_sort(g.dkeys_a, g.dkeys_b, (uint32_t)P, g.num_rendered + 2, reinterpret_cast<uint32_t*>(g.dsort_scratch), g.rect, g.emit, stream);
     if (rc) return rc;
     prof_mark(stream, ST_DEPTH_SORT);
+    nv.stage(ST_SCAN);
     rc = launch_inclusive_scan(P, g.num_rendered + 2, g.point_offsets, g.emit, g.scan_block_sums, stream);
     if (rc) return rc;
     prof_mark(stream, ST_SCAN);
@@ -242,6 +267,7 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
 
     int rc = GS_OK;
     prof_mark(stream, -1);
+    NvtxScope nv(ST_SORT);
     if (P > 0) GS_CUDA_TRY(cudaMemsetAsync(b.error_flag, 0, 16, stream));
     if (P > 0 && bin_fast_path(tiles, (size_t)P)) {
         // Two fused binning passes (count -> scan -> scatter each); the tile ranges fall out of the second count.
@@ -255,9 +281,11 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
         // Generic path (tile ids wider than two binning digits): emission, multi-pass radix sort, range detection.
         const int passes = sort_passes(tiles);
         if (R > 0) {
+            nv.stage(ST_DUPLICATE);
             rc = launch_emit_instances(P, g.num_rendered + 2, g.emit, grid, b.inst_a, stream);
             if (rc) return rc;
             prof_mark(stream, ST_DUPLICATE);
+            nv.stage(ST_SORT);
             rc = launch_radix_sort(b.inst_a, b.inst_b, R, 32, passes, b.sort_scratch, b.error_flag, stream);
             if (rc) return rc;
             rc = launch_strip_ids(R, b.sorted(passes), b.ids, stream);
@@ -265,6 +293,7 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
             prof_mark(stream, ST_SORT);
             count_launches(4 + passes);
         }
+        nv.stage(ST_PACK);
         rc = launch_tile_ranges(R, b.sorted(passes), img.ranges, tiles, stream);
         if (rc) return rc;
         prof_mark(stream, ST_PACK);
@@ -277,6 +306,7 @@ int gs_forward_render(void* stream_, int P, unsigned int R, int W, int H, const 
     rp.final_T = img.final_T; rp.n_contrib = img.n_contrib; rp.out_color = out_color; rp.is_used = is_used;
     rp.tile_max_contrib = img.tile_max_contrib;
     rp.counters = g_fwd_counters;
+    nv.stage(ST_RENDER_FWD);
     rc = launch_render_fwd(rp, (int)tiles, stream);
     prof_mark(stream, ST_RENDER_FWD);
     count_launches(1);
@@ -308,6 +338,7 @@ int gs_backward_render_ev(void* stream_, int P, unsigned int R, int W, int H, co
     BinningWS b = BinningWS::carve(aligned_base(binning_ws), R, tiles, (size_t)(P > 0 ? P : 0));
     BwdScratch sc = BwdScratch::carve(aligned_base(scratch), (size_t)P);
     prof_mark(stream, -1);
+    NvtxScope nv(ST_BWD_ZERO);
     GS_CUDA_TRY(cudaMemsetAsync(sc.acc_color_opacity, 0, sc.bytes, stream));
     prof_mark(stream, ST_BWD_ZERO);
     if (cleared_event) GS_CUDA_TRY(cudaEventRecord((cudaEvent_t)cleared_event, stream));
@@ -317,6 +348,7 @@ int gs_backward_render_ev(void* stream_, int P, unsigned int R, int W, int H, co
         rb.W = W; rb.H = H; rb.tiles_x = (int)grid.x; rb.bg = background; rb.final_T = img.final_T;
         rb.n_contrib = img.n_contrib; rb.dL_dpix = dL_dpix;
         rb.acc_color_opacity = sc.acc_color_opacity; rb.acc_mean_conic = sc.acc_mean_conic; rb.acc_conic_w = sc.acc_conic_w;
+        nv.stage(ST_RENDER_BWD);
         const int rc = launch_render_bwd(rb, (int)tiles, stream);
         if (rc) return rc;
         prof_mark(stream, ST_RENDER_BWD);
@@ -368,6 +400,7 @@ static int backward_geometry_impl(void* stream_, int P, int D, int M, int W, int
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
     BwdScratch sc = BwdScratch::carve(aligned_base(scratch), (size_t)P);
     prof_mark(stream, -1);
+    NvtxScope nv(ST_PREPROCESS_BWD);
     PreprocessBwdParams pb;
     pb.P = P; pb.D = D; pb.M = M; pb.means3D = means3D; pb.radii = radii; pb.shs = shs; pb.clamped = g.clamped;
     pb.shs_rest = shs_rest; pb.dL_dsh_rest = dL_dsh_rest;
@@ -478,6 +511,7 @@ int gs_dp_grad_record_combine(void* stream_, int P, int D, int M, int V, const f
     if (slot_stride < gs_dp_slot_floats(P, GS_DP_RECORDS) || (slot_stride & 3) || (reinterpret_cast<size_t>(records) & 15))
         return GS_ERR_ARG;
     prof_mark(stream, -1);
+    NvtxScope nv(ST_DP_COMBINE);
     if (!outputs_are_zero) {
         GS_CUDA_TRY(cudaMemsetAsync(dL_dmeans3D, 0, (size_t)P * 3 * sizeof(float), stream));
         GS_CUDA_TRY(cudaMemsetAsync(dL_dopacity, 0, (size_t)P * sizeof(float), stream));
@@ -506,6 +540,7 @@ int gs_dp_color_grad_push(void* stream_, int P, const int* radii, const void* ge
     GeomWS g = GeomWS::carve(aligned_base(geom_ws), (size_t)P);
     BwdScratch sc = BwdScratch::carve(aligned_base(scratch), (size_t)P);
     prof_mark(stream, -1);
+    NvtxScope nv(ST_DP_PUSH);
     if (layout == GS_DP_SPARSE) {
         int dev = 0, sms = 0;
         GS_CUDA_TRY(cudaGetDevice(&dev));
@@ -528,6 +563,7 @@ int gs_dp_sh_grad_combine(void* stream_, int P, int D, int M, int V, const float
     if (slot_stride < (layout == GS_DP_SPARSE ? dp_sparse_slot_floats(P) : (size_t)3 * P)) return GS_ERR_ARG;
     if (layout == GS_DP_SPARSE && ((reinterpret_cast<size_t>(color_grads) & 15) || (slot_stride & 3))) return GS_ERR_ARG;
     prof_mark(stream, -1);
+    NvtxScope nv(ST_DP_COMBINE);
     const int rc = launch_sh_grad_combine(P, D, M, V, means3D, campos_views, color_grads, slot_stride, layout == GS_DP_SPARSE,
                                           dL_dsh, stream);
     prof_mark(stream, ST_DP_COMBINE);
@@ -546,6 +582,7 @@ int gs_dp_slab_all_reduce(void* stream_, float* const* slab_ptrs, int n_ptrs, in
     GS_CUDA_TRY(cudaGetDevice(&dev));
     GS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     prof_mark(stream, -1);
+    NvtxScope nv(ST_DP_ALL_REDUCE);
     rc = launch_slab_all_reduce(peers, multicast != 0, n_floats, rank, world, sms, stream);
     prof_mark(stream, ST_DP_ALL_REDUCE);
     count_launches(1);
@@ -578,6 +615,7 @@ int gs_adam_step(void* stream_, int n_tensors, float* const* params, const float
         T.vec_ok = 0;
     }
     prof_mark(stream, -1);
+    NvtxScope nv(ST_ADAM);
     const int rc = launch_adam_step(L, stream);
     prof_mark(stream, ST_ADAM);
     count_launches(1);
@@ -628,6 +666,7 @@ int gs_photometric_loss_forward(void* stream_, int C, int H, int W, const float*
     if (rc) return rc;
     if (!out_means) return GS_ERR_ARG;
     prof_mark(stream, -1);
+    NvtxScope nv(ST_LOSS_FWD);
     rc = launch_loss_forward(p, out_means, stream);
     prof_mark(stream, ST_LOSS_FWD);
     count_launches(2);
@@ -643,6 +682,7 @@ int gs_photometric_loss_backward(void* stream_, int C, int H, int W, const float
     if (!dL_dimage) return GS_ERR_ARG;
     p.dL_dimg = dL_dimage;
     prof_mark(stream, -1);
+    NvtxScope nv(ST_LOSS_BWD);
     rc = launch_loss_backward(p, c_l1, c_ssim, grad_scale, stream);
     prof_mark(stream, ST_LOSS_BWD);
     count_launches(1);
@@ -656,6 +696,7 @@ int gs_l1_loss_forward(void* stream_, size_t n, const float* x, const float* y, 
     if (n == 0 || !x || !y || !ws || !out_mean) return GS_ERR_ARG;
     float* partial = reinterpret_cast<float*>(align_up(reinterpret_cast<size_t>(ws), kAlign));
     prof_mark(stream, -1);
+    NvtxScope nv(ST_LOSS_FWD);
     const int rc = launch_l1_forward(n, x, y, partial, out_mean, stream);
     prof_mark(stream, ST_LOSS_FWD);
     count_launches(2);
@@ -666,6 +707,7 @@ int gs_l1_loss_backward(void* stream_, size_t n, const float* x, const float* y,
     cudaStream_t stream = (cudaStream_t)stream_;
     if (n == 0 || !x || !y || !dL_dx) return GS_ERR_ARG;
     prof_mark(stream, -1);
+    NvtxScope nv(ST_LOSS_BWD);
     const int rc = launch_l1_backward(n, x, y, grad_scale, dL_dx, stream);
     prof_mark(stream, ST_LOSS_BWD);
     count_launches(1);
@@ -684,6 +726,7 @@ int gs_activate_forward(void* stream_, int P, const float* raw_opacity, const fl
     if (!raw_opacity || !raw_scaling || !raw_rotation || !opacity || !scaling || !rotation || !ws || !out_means) return GS_ERR_ARG;
     if ((reinterpret_cast<size_t>(raw_rotation) | reinterpret_cast<size_t>(rotation)) & 15) return GS_ERR_ARG;
     prof_mark(stream, -1);
+    NvtxScope nv(ST_ACT_FWD);
     const int rc = launch_activate_fwd(P, raw_opacity, raw_scaling, raw_rotation, opacity, scaling, rotation,
                                        reinterpret_cast<float*>(aligned_base(ws)), out_means, stream);
     prof_mark(stream, ST_ACT_FWD);
@@ -702,6 +745,7 @@ int gs_activate_backward(void* stream_, int P, const float* raw_opacity, const f
     if ((reinterpret_cast<size_t>(raw_rotation) | reinterpret_cast<size_t>(d_raw_rotation) | reinterpret_cast<size_t>(g_rotation)) & 15)
         return GS_ERR_ARG;
     prof_mark(stream, -1);
+    NvtxScope nv(ST_ACT_BWD);
     const int rc = launch_activate_bwd(P, raw_opacity, raw_scaling, raw_rotation, g_opacity, g_scaling, g_rotation, c_opacity,
                                        c_scaling, reg_grad, d_raw_opacity, d_raw_scaling, d_raw_rotation, stream);
     prof_mark(stream, ST_ACT_BWD);
@@ -745,6 +789,7 @@ int gs_swin_gather_forward(void* stream_, int Ki, int Km, int M, float frame, in
         return GS_ERR_ARG;
     p.out_xyz = out_xyz; p.out_rot = out_rotation; p.out_feat = out_feature; p.out_opacity = out_opacity; p.out_scaling = out_scaling;
     prof_mark(stream, -1);
+    NvtxScope nv(ST_SWIN_FWD);
     rc = launch_swin_gather_fwd(p, stream);
     prof_mark(stream, ST_SWIN_FWD);
     count_launches(1);
@@ -768,6 +813,7 @@ int gs_swin_gather_backward(void* stream_, int Ki, int M, float frame, int defor
     g.d_scaling = imm_grads[5]; g.d_v = imm_grads[6]; g.d_rotvec = imm_grads[7]; g.d_cen = imm_grads[8];
     if ((reinterpret_cast<size_t>(g.d_rot) | reinterpret_cast<size_t>(g.g_rot)) & 15) return GS_ERR_ARG;
     prof_mark(stream, -1);
+    NvtxScope nv(ST_SWIN_BWD);
     rc = launch_swin_gather_bwd(p, g, stream);
     prof_mark(stream, ST_SWIN_BWD);
     count_launches(1);
@@ -783,6 +829,7 @@ int gs_knn_mean_dist2(void* stream_, int P, const float* points, float* mean_dis
     if (!points || !mean_dist2 || !ws) return GS_ERR_ARG;
     pdl_hint(P);
     prof_mark(stream, -1);
+    NvtxScope nv(ST_KNN);
     const int rc = launch_knn_mean_dist2(P, points, mean_dist2, aligned_base(ws), stream);
     prof_mark(stream, ST_KNN);
     count_launches(6 + 3 * 4);
@@ -818,6 +865,7 @@ int gs_compute_relocation(void* stream_, int P, const float* opacity_old, const 
     if (P < 0 || n_max <= 0) return GS_ERR_ARG;
     if (P > 0 && (!opacity_old || !scale_old || !N || !binoms || !opacity_new || !scale_new)) return GS_ERR_ARG;
     prof_mark((cudaStream_t)stream_, -1);
+    NvtxScope nv(ST_RELOCATION);
     int rc = launch_compute_relocation(P, opacity_old, scale_old, N, binoms, n_max, opacity_new, scale_new, (cudaStream_t)stream_);
     prof_mark((cudaStream_t)stream_, ST_RELOCATION);
     count_launches(P > 0 ? 1 : 0);
@@ -830,6 +878,7 @@ int gs_add_noise(void* stream_, int P, float* xyz, const float* scaling_raw, con
     if (P < 0) return GS_ERR_ARG;
     if (P > 0 && (!xyz || !scaling_raw || !rotation_raw || !opacity_raw)) return GS_ERR_ARG;
     prof_mark((cudaStream_t)stream_, -1);
+    NvtxScope nv(ST_ADD_NOISE);
     int rc = launch_add_noise(P, xyz, scaling_raw, rotation_raw, opacity_raw, noise, lr_scale, seed, offset, (cudaStream_t)stream_);
     prof_mark((cudaStream_t)stream_, ST_ADD_NOISE);
     count_launches(P > 0 ? 1 : 0);

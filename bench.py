@@ -41,6 +41,9 @@ CONFIGS = {
                        name="BASELINE.json config 3: Mip-NeRF360-shaped (garden) cap_max=3M at 1297x840"),
     "large6m": dict(kind="garden", P=6_000_000, W=1920, H=1080, fovx=1.2, cam_radius=6.0,
                     name="BASELINE.json config 4: large scene, 6M Gaussians at 1920x1080, one view per GPU"),
+    "cpu100k": dict(kind="cube", P=100_000, W=800, H=800, fovx=0.6911, cam_radius=4.03,
+                    name="BASELINE.json config 1: random-init 100K Gaussians SH deg 3, one 800x800 camera, fwd+bwd + one MCMC "
+                         "relocate / add_noise step (the CPU-runnable case; its CPU leg is timed in the same run)"),
     "swin": dict(kind="garden", P=800_000, W=1352, H=1014, fovx=1.2, cam_radius=6.0,
                  name="BASELINE.json config 5: train_swin.py sliding-window step, 30 frames, ~300K Gaussians alive per frame "
                       "(2 x 400K stored: immature + matured), 1352x1014"),
@@ -768,6 +771,9 @@ def run_b200_arm(args):
     if n_gpus == 1:
         try:
             line["mcmc"] = mcmc_kernels_leg(torch, dev, s, P, hbm_peak, ev0, ev1, None if args.skip_baselines else "ref")
+            if args.config == "cpu100k":
+                line["config1_step"] = config1_leg(torch, C, dev, s, scene_np, cams, cams_np, bg, dL, P, H, W, ev0, ev1,
+                                                   cpu=not args.skip_baselines)
         except Exception as ex:
             line["mcmc"] = {"unavailable": repr(ex)[:300]}
 
@@ -941,6 +947,74 @@ def ref_cuda_leg(torch, ref_cuda, dev, s, cams, bg, dL, H, W, K, our_ms, our_e2e
                   "synchronous_harness": {"ms_per_step": sync_ms, "speedup_e2e": sync_ms / our_e2e_ms,
                                           "what": "round 2's reference loop: four H2D copies on the main stream and a blocking "
                                                   "loss.item() every step (shown for continuity; it flatters this arm at small scenes)"}}
+    return out
+
+
+def config1_leg(torch, C, dev, s, scene_np, cams, cams_np, bg, dL, P, H, W, ev0, ev1, cpu=True):
+    """BASELINE.json configs[0] as one timed step on both sides: forward + backward of one 800x800 view of 100K Gaussians,
+    then one MCMC relocation (compute_relocation over the K = P / 20 sampled Gaussians, as relocate_gs -> _update_params
+    calls it, scene/gaussian_model_static.py:395-455) and one add_noise (train_static.py:132-140). GPU: this library, CUDA
+    events. CPU: the plain-C / OpenMP port of the same kernels (oracle/, every Gaussian and every tile, nothing sampled) on
+    all host cores, wall clock. The reference has no CPU implementation; north_star's "CPU PyTorch path" is represented by
+    this port (kind "port")."""
+    from diff_gaussian_rasterization import add_noise, compute_relocation
+    from oracle import oracle
+    e = torch.empty(0)
+    g = torch.Generator(device=dev).manual_seed(11)
+    K = max(1, P // 20)
+    probs = s["opacities"].reshape(-1)
+    idx = torch.multinomial(probs / probs.sum(), K, replacement=True, generator=g)
+    N = (torch.bincount(idx, minlength=P)[idx] + 1).clamp_(1, 50).int()
+    op, sc = probs[idx].contiguous(), s["scales"][idx].contiguous()
+    binoms_np = oracle.binoms_table(51)
+    binoms = torch.from_numpy(binoms_np).to(dev)
+    xyz = s["means3D"].clone()
+    raw_s, raw_o = torch.log(s["scales"]), torch.logit(s["opacities"].clamp(1e-4, 1 - 1e-4))
+    noise = torch.randn((P, 3), generator=g, device=dev)
+    c = cams[0]
+
+    def step():
+        R, color, radii, geom, binning, img, is_used = C.rasterize_gaussians(
+            bg, s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+            c["tanfovx"], c["tanfovy"], H, W, s["shs"], 3, c["campos"], False, False)
+        C.rasterize_gaussians_backward(bg, s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e, c["viewmatrix"], c["projmatrix"],
+                                       c["tanfovx"], c["tanfovy"], dL, s["shs"], 3, c["campos"], geom, R, binning, img, False)
+        compute_relocation(op, sc, N, binoms, 51)
+        add_noise(xyz, raw_s, s["rotations"], raw_o, 5e5 * 1.6e-4, noise=noise)
+    for _ in range(5):
+        step()
+    torch.cuda.synchronize()
+    iters = 50
+    ev0.record()
+    for _ in range(iters):
+        step()
+    ev1.record()
+    torch.cuda.synchronize()
+    gpu_ms = ev0.elapsed_time(ev1) / iters
+    out = {"gpu_ms_per_step": round(gpu_ms, 4), "steps": iters, "relocated": K,
+           "what": "fwd + bwd of one 800x800 view (camera 0) + compute_relocation over K sampled Gaussians + add_noise over all P"}
+    if cpu:
+        cores = oracle.set_num_threads()
+        dL_np = dL.cpu().numpy()
+        args_np = (op.cpu().numpy(), sc.cpu().numpy(), N.cpu().numpy(), binoms_np)
+        xyz_np, raw_s_np, raw_o_np = scene_np["means3D"].copy(), raw_s.cpu().numpy(), raw_o.cpu().numpy()
+        rot_np, noise_np = scene_np["rotations"], noise.cpu().numpy()
+        secs = []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            cpu_port_step(scene_np, cams_np[0], dL_np, 1)
+            t1 = time.perf_counter()
+            oracle.compute_relocation(*args_np, 51)
+            t2 = time.perf_counter()
+            oracle.add_noise(xyz_np, raw_s_np, rot_np, raw_o_np, noise_np, 5e5 * 1.6e-4)
+            t3 = time.perf_counter()
+            secs.append((t3 - t0, t1 - t0, t2 - t1, t3 - t2))
+        best = min(secs)
+        out["cpu"] = {"ms_per_step": round(best[0] * 1e3, 2), "cores": cores, "kind": "port", "repeats": 3,
+                      "fwd_bwd_ms": round(best[1] * 1e3, 2), "compute_relocation_ms": round(best[2] * 1e3, 3),
+                      "add_noise_ms": round(best[3] * 1e3, 3),
+                      "sample": "the complete step, best of 3: every Gaussian, every tile, all K relocations"}
+        out["gpu_over_cpu"] = round(best[0] * 1e3 / gpu_ms, 1)
     return out
 
 

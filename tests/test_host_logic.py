@@ -465,7 +465,7 @@ def test_bench_presets_cover_baseline_configs(monkeypatch):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     monkeypatch.syspath_prepend(root)
     bench = importlib.import_module("bench")
-    assert {"headline", "lego300k", "garden1297", "large6m", "swin"} <= set(bench.CONFIGS)
+    assert {"headline", "cpu100k", "lego300k", "garden1297", "large6m", "swin"} <= set(bench.CONFIGS)
     monkeypatch.setattr(sys, "argv", ["bench.py"])
     args = bench.parse()
     assert (args.P, args.width, args.height, args.gpus) == (3_000_000, 1920, 1080, 1) and args.warmup >= 3
