@@ -95,32 +95,12 @@ __global__ void __launch_bounds__(256) add_noise_kernel(int P, float* __restrict
                                                         const float* __restrict__ opacity_raw,
                                                         const float* __restrict__ noise /* [P,3] or null */, float lr_scale,
                                                         unsigned long long seed, unsigned long long offset, bool rot_aligned) {
-    // The [P][3] arrays (xyz, scaling, noise) are 12-byte rows: one thread per Gaussian reading its own row makes every warp
-    // load 3 x 128 B with a stride of 12 B per lane (round 2: 0.52 of HBM peak). Instead the block's 256 rows = 768
-    // consecutive floats per array go through shared memory with fully coalesced accesses; a lane then takes its row from
-    // shared memory at stride 3 (coprime with the 32 banks: no conflicts). Same arithmetic, same bits.
-    __shared__ float s_xyz[768], s_scale[768], s_noise[768];
-    const int tid = threadIdx.x;
-    const int idx = blockIdx.x * blockDim.x + tid;
-    const size_t base = (size_t)blockIdx.x * 768;
-    const size_t total = (size_t)P * 3;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const size_t e = base + (size_t)k * 256 + tid;
-        if (e < total) {
-            s_xyz[k * 256 + tid] = xyz[e];
-            s_scale[k * 256 + tid] = scaling_raw[e];
-            if (noise) s_noise[k * 256 + tid] = noise[e];
-        }
-    }
-    __syncthreads();
-    const bool live = idx < P;
-    const size_t i = live ? (size_t)idx : 0;
-    float3 n = make_float3(0.f, 0.f, 0.f);
-    float3 out = make_float3(0.f, 0.f, 0.f);
-    if (live) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const size_t i = (size_t)idx;
+    float3 n;
     if (noise) {
-        n = make_float3(s_noise[3 * tid], s_noise[3 * tid + 1], s_noise[3 * tid + 2]);
+        n = make_float3(noise[3 * i], noise[3 * i + 1], noise[3 * i + 2]);
     } else {
         const uint4 r = philox4x32_10(make_uint4((uint32_t)idx, (uint32_t)offset, (uint32_t)(offset >> 32), 0u),
                                       make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
@@ -136,7 +116,7 @@ __global__ void __launch_bounds__(256) add_noise_kernel(int P, float* __restrict
     const float4 qr = load_quat(rotation_raw, i, rot_aligned);
     const float norm = sqrtf(qr.x * qr.x + qr.y * qr.y + qr.z * qr.z + qr.w * qr.w);
     const float r = qr.x / norm, x = qr.y / norm, y = qr.z / norm, z = qr.w / norm;
-    const float s0 = expf(s_scale[3 * tid]), s1 = expf(s_scale[3 * tid + 1]), s2 = expf(s_scale[3 * tid + 2]);
+    const float s0 = expf(scaling_raw[3 * i]), s1 = expf(scaling_raw[3 * i + 1]), s2 = expf(scaling_raw[3 * i + 2]);
     // L = R * diag(s), row-major R as in build_rotation.
     const float R00 = 1.f - 2.f * (y * y + z * z), R01 = 2.f * (x * y - r * z), R02 = 2.f * (x * z + r * y);
     const float R10 = 2.f * (x * y + r * z), R11 = 1.f - 2.f * (x * x + z * z), R12 = 2.f * (y * z - r * x);
@@ -148,18 +128,9 @@ __global__ void __launch_bounds__(256) add_noise_kernel(int P, float* __restrict
     const float S00 = L00 * L00 + L01 * L01 + L02 * L02, S01 = L00 * L10 + L01 * L11 + L02 * L12;
     const float S02 = L00 * L20 + L01 * L21 + L02 * L22, S11 = L10 * L10 + L11 * L11 + L12 * L12;
     const float S12 = L10 * L20 + L11 * L21 + L12 * L22, S22 = L20 * L20 + L21 * L21 + L22 * L22;
-    out.x = s_xyz[3 * tid] + (S00 * n.x + S01 * n.y + S02 * n.z);
-    out.y = s_xyz[3 * tid + 1] + (S01 * n.x + S11 * n.y + S12 * n.z);
-    out.z = s_xyz[3 * tid + 2] + (S02 * n.x + S12 * n.y + S22 * n.z);
-    }
-    __syncthreads();   // every lane has read its row (and its scales) before the rows are overwritten
-    if (live) { s_xyz[3 * tid] = out.x; s_xyz[3 * tid + 1] = out.y; s_xyz[3 * tid + 2] = out.z; }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const size_t e = base + (size_t)k * 256 + tid;
-        if (e < total) xyz[e] = s_xyz[k * 256 + tid];
-    }
+    xyz[3 * i] += S00 * n.x + S01 * n.y + S02 * n.z;
+    xyz[3 * i + 1] += S01 * n.x + S11 * n.y + S12 * n.z;
+    xyz[3 * i + 2] += S02 * n.x + S12 * n.y + S22 * n.z;
 }
 
 int launch_add_noise(int P, float* xyz, const float* scaling_raw, const float* rotation_raw, const float* opacity_raw,
